@@ -1,0 +1,76 @@
+/* libopb200 -- C ABI of the B200-native OnePose++ / LoFTR matching hot path.
+ *
+ * The reference (mizeller/OnePose_ST) has no FFI on this path: its operator boundary is a set of
+ * Python nn.Module classes.  This header is the C boundary *below* those classes: the
+ * drop-in modules in onepose_st_b200/ hold the reference's signatures and call these entry points with
+ * raw device pointers.  Each entry point names the reference code it replaces.
+ *
+ * Conventions: plain C types; every pointer is a DEVICE pointer unless named host_*; no allocation
+ * inside (caller passes a workspace whose size the matching *_workspace_bytes() returns); work is
+ * enqueued on `stream` (a cudaStream_t passed as void*); returns 0 on success, a negative code on
+ * failure with a message in opb200_last_error(); never throws; sm_100a only (OPB200_ERR_DEVICE on any
+ * other device -- there is no fallback path).
+ */
+#ifndef OPB200_H_
+#define OPB200_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OPB200_OK 0
+#define OPB200_ERR_ARG (-1)
+#define OPB200_ERR_CUDA (-2)
+#define OPB200_ERR_WORKSPACE (-3)
+#define OPB200_ERR_DEVICE (-4)
+
+/* precision of the tensor-core products: 3 = bf16x3 split (fp32-grade, parity default), 1 = single bf16 */
+#define OPB200_PREC_BF16 1
+#define OPB200_PREC_BF16X3 3
+
+int opb200_version(void);
+const char* opb200_last_error(void);
+
+/* fp32 matrix with element (r,c) at x[r*stride_r + c*stride_c] -> bf16 hi/lo planes [rows, cols]
+ * (lo and f32_copy nullable).  Operand preparation for every tensor-core product below. */
+int opb200_split_planes(const float* x, int64_t stride_r, int64_t stride_c, int rows, int cols, void* hi, void* lo,
+                        float* f32_copy, void* stream);
+
+/* Test hook for the tcgen05/TMA mainloop: c[M,N] = a[M,K] * b[N,K]^T from bf16 planes. */
+int opb200_debug_gemm(const void* a_hi, const void* a_lo, const void* b_hi, const void* b_lo, int M, int N, int K,
+                      int block_n, int precision, float* c, void* stream);
+
+/* ---- LoFTR encoder stack (elu+1 linear attention) --------------------------------------------------
+ * Replaces LoFTREncoderLayer.forward + LinearAttention.forward + LocalFeatureTransformer.forward:
+ *   src/models/OnePosePlus/loftr_module/transformer.py:65-94,133-171
+ *   src/models/OnePosePlus/loftr_module/linear_attention.py:29-61
+ *   submodules/LoFTR/src/loftr/loftr_module/transformer.py:35-58,80-101
+ */
+/* Bytes of one packed layer: bf16 hi/lo planes of [Wq;Wk;Wv], Wmerge, Wmlp0, Wmlp2 + fp32 LN params. */
+size_t opb200_packed_layer_bytes(int d_model);
+/* Pack one encoder layer's weights (device fp32, nn.Linear [out,in] layout) into `packed`. */
+int opb200_pack_layer_weights(const float* wq, const float* wk, const float* wv, const float* wm, const float* w1,
+                              const float* w2, const float* ln1_w, const float* ln1_b, const float* ln2_w,
+                              const float* ln2_b, int d_model, void* packed, void* stream);
+size_t opb200_transformer_workspace_bytes(int d_model, int n_batch, int len0, int len1, int big_groups);
+/* Runs n_layers encoder layers over two token streams.
+ *   host_layer_weights[l] : device pointer to layer l's packed weights;  host_layer_kinds[l]: 0 self, 1 cross
+ *   schedule 0 = OnePosePlus (one layer object serves both streams, both read the pre-update tensors),
+ *            1 = LoFTR (cross step: stream0 = layer(stream0, stream1) then stream1 = layer(stream1, new stream0))
+ *   big_groups 1 = coarse level (d_model 256; one attention group per (stream, batch element)),
+ *              0 = fine level   (d_model 128; n_batch = number of matches, len0/len1 <= 128 tokens)
+ *   stream s element (n, l, c) is read from x{s}[n*sn + l*sl + c*sc]; add{s} (nullable) is a [len, C]
+ *   table added to every batch element (the sine position encoding); mask{s} (nullable) is [n_batch, len]
+ *   bytes, 1 = valid.  Results are written densely: out0 [n_batch, len0, C], out1 [n_batch, len1, C]. */
+int opb200_transformer(const void* const* host_layer_weights, const int* host_layer_kinds, int n_layers, int schedule,
+                       int d_model, int nhead, int n_batch, int len0, int len1, int big_groups, const float* x0,
+                       int64_t x0_sn, int64_t x0_sl, int64_t x0_sc, const float* add0, const float* x1, int64_t x1_sn,
+                       int64_t x1_sl, int64_t x1_sc, const float* add1, const uint8_t* mask0, const uint8_t* mask1,
+                       float* out0, float* out1, void* workspace, size_t workspace_bytes, int precision, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OPB200_H_ */

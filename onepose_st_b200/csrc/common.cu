@@ -1,0 +1,221 @@
+// Error reporting, device checks, TMA descriptor encoding, operand-preparation kernels and the
+// debug GEMM entry point (used by tests to validate the tcgen05/TMA mainloop in isolation).
+#include <mutex>
+#include "host.cuh"
+#include "../../include/opb200.h"
+
+namespace opb {
+
+static thread_local std::string g_last_error;
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+const char* last_error_cstr() { return g_last_error.c_str(); }
+
+int check_device() {
+  int dev = 0;
+  OPB_CHECK_CUDA(cudaGetDevice(&dev));
+  static int cached_dev = -1, cached_major = 0;
+  if (cached_dev != dev) {
+    OPB_CHECK_CUDA(cudaDeviceGetAttribute(&cached_major, cudaDevAttrComputeCapabilityMajor, dev));
+    cached_dev = dev;
+  }
+  if (cached_major != 10) {
+    set_last_error("libopb200 is built for sm_100a only; current device is compute capability " +
+                   std::to_string(cached_major) + ".x (no fallback path exists)");
+    return OPB_ERR_DEVICE;
+  }
+  return OPB_OK;
+}
+
+int num_sms() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  return sms;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess) {
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+  });
+  return fn;
+}
+
+int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_elems,
+                   uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) {
+    set_last_error("cuTensorMapEncodeTiled entry point not available from the driver");
+    return OPB_ERR_CUDA;
+  }
+  OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base address must be 16-byte aligned");
+  OPB_CHECK_ARG((pitch_elems * 2) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes");
+  OPB_CHECK_ARG(box_rows >= 1 && box_rows <= 256, "TMA box rows must be in [1,256]");
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {pitch_elems * 2};
+  cuuint32_t box[2] = {BLOCK_K, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(r)));
+    return OPB_ERR_CUDA;
+  }
+  return OPB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// fp32 (arbitrary element strides) -> bf16 hi/lo planes [rows, cols] (+ optional fp32 copy, + optional
+// additive table).  A 32x32 shared-memory transpose keeps both sides coalesced when the source is
+// column-major-ish (e.g. the reference's channels-first [N,C,L] descriptors or NCHW feature maps).
+// ------------------------------------------------------------------------------------------------
+__global__ void split_planes_kernel(const float* __restrict__ x, long long stride_r, long long stride_c,
+                                    const float* __restrict__ add, long long add_period_rows, int rows, int cols,
+                                    __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo,
+                                    float* __restrict__ f32out, long long ld_out) {
+  __shared__ float tile[32][33];
+  const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;  // 32 x 8
+  if (stride_c == 1) {
+    for (int i = ty; i < 32; i += 8) {
+      int r = r0 + i, c = c0 + tx;
+      tile[i][tx] = (r < rows && c < cols) ? x[r * stride_r + c] : 0.f;
+    }
+  } else {  // source is contiguous along rows: read transposed
+    for (int i = ty; i < 32; i += 8) {
+      int c = c0 + i, r = r0 + tx;
+      tile[tx][i] = (r < rows && c < cols) ? x[r * stride_r + c * stride_c] : 0.f;
+    }
+  }
+  __syncthreads();
+  for (int i = ty; i < 32; i += 8) {
+    int r = r0 + i, c = c0 + tx;
+    if (r < rows && c < cols) {
+      float v = tile[i][tx];
+      if (add != nullptr) v += add[(r % add_period_rows) * cols + c];
+      __nv_bfloat16 h, l;
+      split_bf16(v, h, l);
+      hi[r * ld_out + c] = h;
+      if (lo != nullptr) lo[r * ld_out + c] = l;
+      if (f32out != nullptr) f32out[r * ld_out + c] = v;
+    }
+  }
+}
+
+int split_planes(const float* x, long long stride_r, long long stride_c, const float* add, long long add_period_rows,
+                 int rows, int cols, __nv_bfloat16* hi, __nv_bfloat16* lo, float* f32out, long long ld_out,
+                 cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) return OPB_OK;
+  dim3 grid((cols + 31) / 32, (rows + 31) / 32), block(32, 8);
+  split_planes_kernel<<<grid, block, 0, stream>>>(x, stride_r, stride_c, add, add_period_rows > 0 ? add_period_rows : 1,
+                                                  rows, cols, hi, lo, f32out, ld_out);
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Debug GEMM: C[M,N] = A[M,K] * B[N,K]^T with split-precision operands, plain fp32 store epilogue.
+// ------------------------------------------------------------------------------------------------
+struct EpiStoreF32 {
+  struct Params {
+    float* c;
+    int M, N, ldc, bn;
+  };
+  static constexpr int kSmemBytes = 0;
+  template <int BN>
+  static __device__ __forceinline__ void run_bn(const Params& p, const EpiCtx& ctx) {
+    const int row = ctx.m_tile * BLOCK_M + ctx.quarter * 32 + ctx.lane;
+    for (int c0 = 0; c0 + 32 <= BN; c0 += 32) {
+      float v[32];
+      load_acc32(ctx.tmem_acc + c0, v);
+      const int col = ctx.n_tile * BN + c0;
+      if (row < p.M) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (col + i < p.N) p.c[static_cast<long long>(row) * p.ldc + col + i] = v[i];
+      }
+    }
+    if constexpr (BN % 32 == 16) {
+      uint32_t r[16];
+      ptx::tmem_ld16(ctx.tmem_acc + (BN - 16), r);
+      ptx::tmem_ld_wait();
+      const int col = ctx.n_tile * BN + BN - 16;
+      if (row < p.M) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (col + i < p.N) p.c[static_cast<long long>(row) * p.ldc + col + i] = __uint_as_float(r[i]);
+      }
+    }
+  }
+};
+template <int BN>
+struct EpiStoreF32T : EpiStoreF32 {
+  static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) { run_bn<BN>(p, ctx); }
+};
+
+}  // namespace opb
+
+using namespace opb;
+
+extern "C" {
+
+int opb200_version(void) { return 100; }
+
+const char* opb200_last_error(void) { return opb::last_error_cstr(); }
+
+int opb200_split_planes(const float* x, int64_t stride_r, int64_t stride_c, int rows, int cols, void* hi, void* lo,
+                        float* f32_copy, void* stream) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(x != nullptr && hi != nullptr, "x / hi must not be null");
+  return split_planes(x, stride_r, stride_c, nullptr, 0, rows, cols, static_cast<__nv_bfloat16*>(hi),
+                      static_cast<__nv_bfloat16*>(lo), f32_copy, cols, static_cast<cudaStream_t>(stream));
+}
+
+int opb200_debug_gemm(const void* a_hi, const void* a_lo, const void* b_hi, const void* b_lo, int M, int N, int K,
+                      int block_n, int precision, float* c, void* stream_) {
+  if (int r = check_device()) return r;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  OPB_CHECK_ARG(K % BLOCK_K == 0 && K > 0, "K must be a positive multiple of 64");
+  OPB_CHECK_ARG(precision == 1 || precision == 3, "precision must be 1 (bf16) or 3 (bf16x3 split)");
+  OPB_CHECK_ARG(block_n == 128 || block_n == 256 || block_n == 144, "block_n must be 128, 144 or 256");
+  OPB_CHECK_ARG(a_hi && b_hi && c && (precision == 1 || (a_lo && b_lo)), "null operand");
+  PlanBuilder pb;
+  pb.add_a(a_hi, M, K, K, 0);
+  pb.add_b(b_hi, N, K, K, 0, block_n);
+  if (precision == 3) {
+    pb.add_a(a_lo, M, K, K, 1);
+    pb.add_b(b_lo, N, K, K, 1, block_n);
+  }
+  if (pb.status != OPB_OK) return pb.status;
+  const int nkb = K / BLOCK_K;
+  if (precision == 3) {
+    pb.seg(0, 1, 0, 0, nkb);  // small cross terms first, the dominant hi*hi term last
+    pb.seg(1, 0, 0, 0, nkb);
+  }
+  pb.seg(0, 0, 0, 0, nkb);
+  pb.finish();
+  pb.plan.num_n_tiles = (N + block_n - 1) / block_n;
+  pb.plan.num_tiles = ((M + BLOCK_M - 1) / BLOCK_M) * pb.plan.num_n_tiles;
+  pb.plan.b_rows_per_ntile = block_n;
+  EpiStoreF32::Params ep{c, M, N, N, block_n};
+  if (block_n == 256) return launch_gemm<256, 4, 4, EpiStoreF32T<256>>(pb.plan, ep, stream);
+  if (block_n == 144) return launch_gemm<144, 4, 4, EpiStoreF32T<144>>(pb.plan, ep, stream);
+  return launch_gemm<128, 6, 4, EpiStoreF32T<128>>(pb.plan, ep, stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,833 @@
+// LoFTR encoder layer stack (elu+1 linear attention) on tcgen05 tensor cores.
+//
+// Replaces, for inference:
+//   LoFTREncoderLayer.forward       src/models/OnePosePlus/loftr_module/transformer.py:65-94
+//                                   submodules/LoFTR/src/loftr/loftr_module/transformer.py:35-58
+//   LinearAttention.forward         src/models/OnePosePlus/loftr_module/linear_attention.py:29-61
+//   LocalFeatureTransformer.forward transformer.py:133-171 (OnePosePlus: both streams read pre-update
+//                                   tensors) and LoFTR transformer.py:80-101 (sequential cross update)
+//
+// Data layout ("row space"): every token of both streams of every batch element is one row of a
+// [R, C] matrix.  Stream 0 occupies rows [0, N*P0), stream 1 rows [N*P0, N*(P0+P1)); with big groups
+// (coarse level) each (stream, batch) group is padded to a multiple of 128 rows so a 128-row MMA tile
+// never straddles two groups (the attention B operand differs per group).  For every activation that
+// feeds a tensor-core product the row space holds two bf16 planes (hi = rn(x), lo = rn(x - hi)); the
+// product A*B is evaluated as A_hi*B_lo + A_lo*B_hi + A_hi*B_hi with fp32 accumulation in TMEM, which
+// keeps ~2^-17 relative operand precision (fp32-grade results from the bf16 tensor pipe).
+//
+// One layer step = 7 launches, all persistent tcgen05 GEMMs except the two small KV kernels:
+//   1 QKV      [R,C]x[3C,C]^T   epilogue: phi=elu+1 on q,k; row mask; q -> planes, k,v -> fp32
+//   2 KV       per group/head   sum_s phi(K)^T V and sum_s phi(K)            (CUDA cores, fp32)
+//   3 KVpack   block-diagonal B operand [KV | Ksum] as planes
+//   4 ATTN     phi(Q) x blockdiag(KV)  epilogue: divide by (phi(Q).Ksum + eps)  -> planes
+//   5 MERGE    x Wm^T           epilogue: LayerNorm1 -> planes
+//   6 MLP1     [x|msg] x W1^T   epilogue: ReLU -> planes
+//   7 MLP2     x W2^T           epilogue: LayerNorm2, + residual -> fp32 master + planes (in place)
+#include <cmath>
+#include "host.cuh"
+#include "../../include/opb200.h"
+
+namespace opb {
+
+int split_planes(const float* x, long long stride_r, long long stride_c, const float* add, long long add_period_rows,
+                 int rows, int cols, __nv_bfloat16* hi, __nv_bfloat16* lo, float* f32out, long long ld_out,
+                 cudaStream_t stream);
+
+__device__ __forceinline__ float elu1(float x) {
+  // torch: elu(x) + 1 with elu(x<=0) = expm1(x); keep the same two roundings
+  return x > 0.f ? __fadd_rn(x, 1.0f) : __fadd_rn(expm1f(x), 1.0f);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Epilogues
+// ------------------------------------------------------------------------------------------------
+template <int C>
+struct EpiQKV {
+  struct Params {
+    __nv_bfloat16 *q_hi, *q_lo;  // phi(Q) planes [R,C] (big groups)
+    float* q_f32;                // phi(Q) fp32 [R,C]   (small groups)
+    float *k_f32, *v_f32;        // phi(K), V fp32 [R,C]
+    const uint8_t* row_mask;     // [R], 1 = valid
+  };
+  static constexpr int kSmemBytes = 0;
+  static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
+    const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
+    const float m = p.row_mask[row] ? 1.f : 0.f;
+#pragma unroll 1
+    for (int c0 = 0; c0 < C; c0 += 32) {
+      float v[32];
+      load_acc32(ctx.tmem_acc + c0, v);
+      if (ctx.n_tile == 2) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] *= m;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = elu1(v[i]) * m;
+      }
+      if (ctx.n_tile == 0 && p.q_f32 == nullptr) {
+        store_planes32(v, p.q_hi + row * C + c0, p.q_lo ? p.q_lo + row * C + c0 : nullptr);
+      } else {
+        float* dst = (ctx.n_tile == 0 ? p.q_f32 : ctx.n_tile == 1 ? p.k_f32 : p.v_f32) + row * C + c0;
+        float4* d4 = reinterpret_cast<float4*>(dst);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
+    }
+  }
+};
+
+// ATTN: tile = 128 rows x [128 value columns of 4 heads | 16 denominator columns], D = 32.
+struct EpiAttn {
+  struct Params {
+    __nv_bfloat16 *o_hi, *o_lo;  // [R, 256]
+    float eps;
+  };
+  static constexpr int kSmemBytes = 0;
+  static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
+    const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
+    uint32_t dr[16];
+    ptx::tmem_ld16(ctx.tmem_acc + 128, dr);
+    ptx::tmem_ld_wait();
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      const float z = 1.0f / (__uint_as_float(dr[h]) + p.eps);
+      float v[32];
+      load_acc32(ctx.tmem_acc + h * 32, v);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] *= z;
+      const long long off = row * 256 + ctx.n_tile * 128 + h * 32;
+      store_planes32(v, p.o_hi + off, p.o_lo ? p.o_lo + off : nullptr);
+    }
+  }
+};
+
+// Row LayerNorm straight out of TMEM: the thread owns the whole row, so no cross-thread reduction.
+template <int C>
+__device__ __forceinline__ void row_mean_rstd(uint32_t tmem_acc, float& mean, float& rstd) {
+  float s = 0.f;
+#pragma unroll 1
+  for (int c0 = 0; c0 < C; c0 += 32) {
+    float v[32];
+    load_acc32(tmem_acc + c0, v);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) s += v[i];
+  }
+  mean = s * (1.0f / C);
+  float q = 0.f;
+#pragma unroll 1
+  for (int c0 = 0; c0 < C; c0 += 32) {
+    float v[32];
+    load_acc32(tmem_acc + c0, v);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float d = v[i] - mean;
+      q = fmaf(d, d, q);
+    }
+  }
+  rstd = rsqrtf(q * (1.0f / C) + 1e-5f);
+}
+
+template <int C>
+struct EpiLN {  // MERGE epilogue: LayerNorm1 -> planes
+  struct Params {
+    const float *gamma, *beta;
+    __nv_bfloat16 *o_hi, *o_lo;
+  };
+  static constexpr int kSmemBytes = 0;
+  static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
+    const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
+    float mean, rstd;
+    row_mean_rstd<C>(ctx.tmem_acc, mean, rstd);
+#pragma unroll 1
+    for (int c0 = 0; c0 < C; c0 += 32) {
+      float v[32];
+      load_acc32(ctx.tmem_acc + c0, v);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = (v[i] - mean) * rstd * __ldg(p.gamma + c0 + i) + __ldg(p.beta + c0 + i);
+      store_planes32(v, p.o_hi + row * C + c0, p.o_lo ? p.o_lo + row * C + c0 : nullptr);
+    }
+  }
+};
+
+template <int BN>
+struct EpiRelu {  // MLP1 epilogue: ReLU -> planes [R, ld]
+  struct Params {
+    __nv_bfloat16 *o_hi, *o_lo;
+    int ld;
+  };
+  static constexpr int kSmemBytes = 0;
+  static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
+    const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      float v[32];
+      load_acc32(ctx.tmem_acc + c0, v);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+      const long long off = row * p.ld + ctx.n_tile * BN + c0;
+      store_planes32(v, p.o_hi + off, p.o_lo ? p.o_lo + off : nullptr);
+    }
+  }
+};
+
+template <int C>
+struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc); refresh the planes of x
+  struct Params {
+    const float *gamma, *beta;
+    float* x_f32;
+    __nv_bfloat16 *x_hi, *x_lo;
+  };
+  static constexpr int kSmemBytes = 0;
+  static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
+    const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
+    float mean, rstd;
+    row_mean_rstd<C>(ctx.tmem_acc, mean, rstd);
+#pragma unroll 1
+    for (int c0 = 0; c0 < C; c0 += 32) {
+      float v[32];
+      load_acc32(ctx.tmem_acc + c0, v);
+      float4* x4 = reinterpret_cast<float4*>(p.x_f32 + row * C + c0);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float4 xo = x4[i];
+        const int c = c0 + 4 * i;
+        v[4 * i + 0] = xo.x + ((v[4 * i + 0] - mean) * rstd * __ldg(p.gamma + c + 0) + __ldg(p.beta + c + 0));
+        v[4 * i + 1] = xo.y + ((v[4 * i + 1] - mean) * rstd * __ldg(p.gamma + c + 1) + __ldg(p.beta + c + 1));
+        v[4 * i + 2] = xo.z + ((v[4 * i + 2] - mean) * rstd * __ldg(p.gamma + c + 2) + __ldg(p.beta + c + 2));
+        v[4 * i + 3] = xo.w + ((v[4 * i + 3] - mean) * rstd * __ldg(p.gamma + c + 3) + __ldg(p.beta + c + 3));
+        x4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
+      store_planes32(v, p.x_hi + row * C + c0, p.x_lo ? p.x_lo + row * C + c0 : nullptr);
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// KV reduction for big groups (coarse level: C = 256, H = 8, D = 32)
+// ------------------------------------------------------------------------------------------------
+constexpr int KV_ROWS_PER_BLOCK = 64;
+constexpr int KV_REC = 33;  // per (head, d): 32 KV values + Ksum
+
+struct GroupTable {  // passed by value to small kernels
+  int num_groups;
+  int row_start[64];
+  int len[64];
+};
+
+// grid = (max_chunks, G), block = 256: thread t -> head t/32, d = t%32; accumulates KV[h][d][0..31], Ksum[h][d]
+__global__ void __launch_bounds__(256) kv_partial_kernel(const float* __restrict__ kphi, const float* __restrict__ v,
+                                                         GroupTable gt, unsigned long long group_sel,
+                                                         float* __restrict__ partial, int max_chunks) {
+  const int g = blockIdx.y;
+  if (!((group_sel >> g) & 1ull)) return;
+  const int chunk = blockIdx.x;
+  const int r0 = chunk * KV_ROWS_PER_BLOCK;
+  const int len = gt.len[g];
+  if (r0 >= len) return;
+  const int nrows = min(KV_ROWS_PER_BLOCK, len - r0);
+  __shared__ __align__(16) float vs[8][256];
+  __shared__ float ks[8][256];
+  const int t = threadIdx.x;
+  const int h = t >> 5;
+  float acc[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+  float ksum = 0.f;
+  const long long base = static_cast<long long>(gt.row_start[g] + r0) * 256;
+  for (int rb = 0; rb < nrows; rb += 8) {
+    const int nr = min(8, nrows - rb);
+    __syncthreads();
+    for (int i = 0; i < nr; ++i) {
+      vs[i][t] = v[base + static_cast<long long>(rb + i) * 256 + t];
+      ks[i][t] = kphi[base + static_cast<long long>(rb + i) * 256 + t];
+    }
+    __syncthreads();
+    for (int i = 0; i < nr; ++i) {
+      const float kk = ks[i][t];
+      ksum += kk;
+      const float4* v4 = reinterpret_cast<const float4*>(&vs[i][h * 32]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 vv = v4[j];
+        acc[4 * j + 0] = fmaf(kk, vv.x, acc[4 * j + 0]);
+        acc[4 * j + 1] = fmaf(kk, vv.y, acc[4 * j + 1]);
+        acc[4 * j + 2] = fmaf(kk, vv.z, acc[4 * j + 2]);
+        acc[4 * j + 3] = fmaf(kk, vv.w, acc[4 * j + 3]);
+      }
+    }
+  }
+  float* out = partial + ((static_cast<long long>(g) * max_chunks + chunk) * 256 + t) * KV_REC;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) out[i] = acc[i];
+  out[32] = ksum;
+}
+
+// grid = (2 halves, G), block = 256.  Sums the chunk partials in a fixed order and writes the
+// block-diagonal B operand of the ATTN GEMM for (group, half): 144 rows (n) x 128 (k) bf16 planes,
+//   n <  128 : n = hh*32 + v, k = hh*32 + d  ->  KV[half*4+hh][d][v]      (zero off the diagonal blocks)
+//   n = 128+hh : k = hh*32 + d               ->  Ksum[half*4+hh][d]
+__global__ void __launch_bounds__(256) kv_pack_kernel(const float* __restrict__ partial, GroupTable gt,
+                                                      unsigned long long group_sel, int max_chunks,
+                                                      __nv_bfloat16* __restrict__ b_hi, __nv_bfloat16* __restrict__ b_lo) {
+  const int g = blockIdx.y, half = blockIdx.x;
+  if (!((group_sel >> g) & 1ull)) return;
+  const int nchunks = (gt.len[g] + KV_ROWS_PER_BLOCK - 1) / KV_ROWS_PER_BLOCK;
+  const long long obase = (static_cast<long long>(g) * 2 + half) * 144 * 128;
+  const int t = threadIdx.x;
+  // zero fill (off-diagonal blocks and unused denominator rows)
+  for (int i = t; i < 144 * 128 / 8; i += 256) {
+    reinterpret_cast<uint4*>(b_hi + obase)[i] = make_uint4(0, 0, 0, 0);
+    if (b_lo) reinterpret_cast<uint4*>(b_lo + obase)[i] = make_uint4(0, 0, 0, 0);
+  }
+  __syncthreads();
+  // thread -> (hh = t/64, d = (t%64)/2, v half = t%2 -> 16 values) ; plus Ksum by the v-half-0 threads
+  const int hh = t >> 6, d = (t & 63) >> 1, vh = t & 1;
+  const int hd = (half * 4 + hh) * 32 + d;
+  float acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+  float ksum = 0.f;
+  for (int c = 0; c < nchunks; ++c) {
+    const float* src = partial + ((static_cast<long long>(g) * max_chunks + c) * 256 + hd) * KV_REC;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[i] += src[vh * 16 + i];
+    if (vh == 0) ksum += src[32];
+  }
+  const int k = hh * 32 + d;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int n = hh * 32 + vh * 16 + i;
+    __nv_bfloat16 h_, l_;
+    split_bf16(acc[i], h_, l_);
+    b_hi[obase + n * 128 + k] = h_;
+    if (b_lo) b_lo[obase + n * 128 + k] = l_;
+  }
+  if (vh == 0) {
+    __nv_bfloat16 h_, l_;
+    split_bf16(ksum, h_, l_);
+    b_hi[obase + (128 + hh) * 128 + k] = h_;
+    if (b_lo) b_lo[obase + (128 + hh) * 128 + k] = l_;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Small-group attention (fine level: C = 128, H = 8, D = 16; groups are single matches of <= 128 rows).
+// One block per query group: build KV / Ksum of the source group in shared memory, then apply.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) attn_small_kernel(const float* __restrict__ qphi, const float* __restrict__ kphi,
+                                                         const float* __restrict__ v, int q_row0, int q_len,
+                                                         int s_row0, int s_len, int num_groups, float eps,
+                                                         __nv_bfloat16* __restrict__ o_hi, __nv_bfloat16* __restrict__ o_lo) {
+  constexpr int C = 128, D = 16;
+  const int g = blockIdx.x;
+  if (g >= num_groups) return;
+  const int t = threadIdx.x;  // channel index: head h = t/16, d (or v) = t%16
+  const int h = t >> 4;
+  __shared__ float kv[8][D][D + 1];
+  __shared__ float ksum_s[8][D];
+  __shared__ __align__(16) float rowbuf[2][C];
+  const long long sbase = static_cast<long long>(s_row0 + g * s_len) * C;
+  float acc[D];
+#pragma unroll
+  for (int i = 0; i < D; ++i) acc[i] = 0.f;
+  float ksum = 0.f;
+  for (int r = 0; r < s_len; ++r) {
+    __syncthreads();
+    rowbuf[0][t] = v[sbase + r * C + t];
+    const float kk = kphi[sbase + r * C + t];
+    __syncthreads();
+    ksum += kk;
+#pragma unroll
+    for (int i = 0; i < D; ++i) acc[i] = fmaf(kk, rowbuf[0][h * D + i], acc[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < D; ++i) kv[h][t & 15][i] = acc[i];
+  ksum_s[h][t & 15] = ksum;
+  __syncthreads();
+  const long long qbase = static_cast<long long>(q_row0 + g * q_len) * C;
+  for (int r = 0; r < q_len; ++r) {
+    __syncthreads();
+    rowbuf[1][t] = qphi[qbase + r * C + t];
+    __syncthreads();
+    float num = 0.f, den = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      const float qq = rowbuf[1][h * D + d];
+      num = fmaf(qq, kv[h][d][t & 15], num);
+      den = fmaf(qq, ksum_s[h][d], den);
+    }
+    const float o = num / (den + eps);
+    __nv_bfloat16 hi_, lo_;
+    split_bf16(o, hi_, lo_);
+    o_hi[qbase + r * C + t] = hi_;
+    if (o_lo) o_lo[qbase + r * C + t] = lo_;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Row-space staging
+// ------------------------------------------------------------------------------------------------
+// x element (n, l, c) at x[n*sn + l*sl + c*sc]; optional additive table add[l*C + c] (position encoding).
+// Writes rows [row0 + n*P, +P): valid rows get the data, pad rows zeros; also the row mask.
+__global__ void copy_in_kernel(const float* __restrict__ x, long long sn, long long sl, long long sc,
+                               const float* __restrict__ add, const uint8_t* __restrict__ mask, int len, int P, int C,
+                               int row0, float* __restrict__ xf, __nv_bfloat16* __restrict__ xh,
+                               __nv_bfloat16* __restrict__ xl, uint8_t* __restrict__ row_mask) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z;
+  const int l0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const float* xn = x + n * sn;
+  if (sc == 1) {
+    for (int i = ty; i < 32; i += 8) {
+      const int l = l0 + i, c = c0 + tx;
+      tile[i][tx] = (l < len && c < C) ? xn[l * sl + c] : 0.f;
+    }
+  } else {
+    for (int i = ty; i < 32; i += 8) {
+      const int c = c0 + i, l = l0 + tx;
+      tile[tx][i] = (l < len && c < C) ? xn[l * sl + c * sc] : 0.f;
+    }
+  }
+  __syncthreads();
+  for (int i = ty; i < 32; i += 8) {
+    const int l = l0 + i, c = c0 + tx;
+    if (l < P && c < C) {
+      float val = tile[i][tx];
+      if (add != nullptr && l < len) val += add[static_cast<long long>(l) * C + c];
+      const long long o = (static_cast<long long>(row0) + static_cast<long long>(n) * P + l) * C + c;
+      __nv_bfloat16 h_, l_;
+      split_bf16(val, h_, l_);
+      xf[o] = val;
+      xh[o] = h_;
+      if (xl) xl[o] = l_;
+      if (c == 0)
+        row_mask[row0 + n * P + l] = (l < len) ? (mask ? (mask[static_cast<long long>(n) * len + l] != 0) : 1) : 0;
+    }
+  }
+}
+
+__global__ void copy_out_kernel(const float* __restrict__ xf, int len, int P, int C, int row0, float* __restrict__ out) {
+  const int n = blockIdx.z;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;  // float4 index within [len, C]
+  const long long total4 = static_cast<long long>(len) * C / 4;
+  if (i >= total4) return;
+  const float4 v = reinterpret_cast<const float4*>(xf + (static_cast<long long>(row0) + static_cast<long long>(n) * P) * C)[i];
+  reinterpret_cast<float4*>(out + static_cast<long long>(n) * len * C)[i] = v;
+}
+
+__global__ void fill_row_base_kernel(int* base_self, int* base_cross, int tiles0, int tiles1, int N, int rows_per_group) {
+  const int T0 = N * tiles0, T1 = N * tiles1;
+  for (int t = threadIdx.x + blockIdx.x * blockDim.x; t < T0 + T1; t += blockDim.x * gridDim.x) {
+    int g, partner;
+    if (t < T0) {
+      g = t / tiles0;
+      partner = N + g;
+    } else {
+      g = N + (t - T0) / tiles1;
+      partner = g - N;
+    }
+    base_self[t] = g * rows_per_group;
+    base_cross[t] = partner * rows_per_group;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host driver
+// ------------------------------------------------------------------------------------------------
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct LayerWeights {  // views into one packed buffer (see opb200_pack_layer_weights)
+  const __nv_bfloat16 *qkv_hi, *qkv_lo, *m_hi, *m_lo, *w1_hi, *w1_lo, *w2_hi, *w2_lo;
+  const float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+};
+
+static size_t packed_layer_bytes(int C) {
+  return static_cast<size_t>(10) * C * C * 2 * 2 + static_cast<size_t>(4) * C * 4;
+}
+
+static LayerWeights view_layer(const void* buf, int C) {
+  const __nv_bfloat16* p = static_cast<const __nv_bfloat16*>(buf);
+  const size_t cc = static_cast<size_t>(C) * C;
+  LayerWeights w;
+  w.qkv_hi = p;
+  w.m_hi = w.qkv_hi + 3 * cc;
+  w.w1_hi = w.m_hi + cc;
+  w.w2_hi = w.w1_hi + 4 * cc;
+  const __nv_bfloat16* lo = w.w2_hi + 2 * cc;
+  w.qkv_lo = lo;
+  w.m_lo = w.qkv_lo + 3 * cc;
+  w.w1_lo = w.m_lo + cc;
+  w.w2_lo = w.w1_lo + 4 * cc;
+  const float* f = reinterpret_cast<const float*>(w.w2_lo + 2 * cc);
+  w.ln1_g = f;
+  w.ln1_b = f + C;
+  w.ln2_g = f + 2 * C;
+  w.ln2_b = f + 3 * C;
+  return w;
+}
+
+struct Workspace {
+  float* xf;
+  __nv_bfloat16 *xh, *xl, *qh, *ql, *aoh, *aol, *mh, *ml, *hh, *hl, *kvb_h, *kvb_l;
+  float *qf, *kf, *vf, *kv_partial;
+  uint8_t* row_mask;
+  int *base_self, *base_cross;
+  size_t bytes;
+};
+
+struct Geometry {
+  int C, N, len0, len1, P0, P1, row1, R, big, G, max_chunks, tiles0, tiles1;
+};
+
+static Geometry make_geometry(int C, int N, int len0, int len1, int big) {
+  Geometry g;
+  g.C = C;
+  g.N = N;
+  g.len0 = len0;
+  g.len1 = len1;
+  g.big = big;
+  if (big) {  // every (stream, batch) group padded to whole 128-row tiles
+    g.P0 = static_cast<int>(align_up(len0, 128));
+    g.P1 = static_cast<int>(align_up(len1, 128));
+  } else {    // groups packed back to back; only the two stream regions are tile aligned
+    g.P0 = len0;
+    g.P1 = len1;
+  }
+  g.row1 = static_cast<int>(align_up(static_cast<size_t>(N) * g.P0, 128));
+  g.R = g.row1 + static_cast<int>(align_up(static_cast<size_t>(N) * g.P1, 128));
+  g.G = 2 * N;
+  const int maxlen = len0 > len1 ? len0 : len1;
+  g.max_chunks = (maxlen + KV_ROWS_PER_BLOCK - 1) / KV_ROWS_PER_BLOCK;
+  g.tiles0 = g.P0 / 128;
+  g.tiles1 = g.P1 / 128;
+  return g;
+}
+
+static Workspace carve(void* base, const Geometry& g) {
+  Workspace w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? static_cast<uint8_t*>(base) + off : nullptr;
+    off += align_up(bytes, 1024);
+    return p;
+  };
+  const size_t RC = static_cast<size_t>(g.R) * g.C;
+  w.xf = static_cast<float*>(take(RC * 4));
+  w.xh = static_cast<__nv_bfloat16*>(take(RC * 2));
+  w.xl = static_cast<__nv_bfloat16*>(take(RC * 2));
+  w.qh = static_cast<__nv_bfloat16*>(take(RC * 2));
+  w.ql = static_cast<__nv_bfloat16*>(take(RC * 2));
+  w.qf = static_cast<float*>(take(g.big ? 0 : RC * 4));
+  w.kf = static_cast<float*>(take(RC * 4));
+  w.vf = static_cast<float*>(take(RC * 4));
+  w.aoh = static_cast<__nv_bfloat16*>(take(RC * 2));
+  w.aol = static_cast<__nv_bfloat16*>(take(RC * 2));
+  w.mh = static_cast<__nv_bfloat16*>(take(RC * 2));
+  w.ml = static_cast<__nv_bfloat16*>(take(RC * 2));
+  w.hh = static_cast<__nv_bfloat16*>(take(RC * 2 * 2));
+  w.hl = static_cast<__nv_bfloat16*>(take(RC * 2 * 2));
+  w.kv_partial = static_cast<float*>(take(g.big ? static_cast<size_t>(g.G) * g.max_chunks * 256 * KV_REC * 4 : 0));
+  w.kvb_h = static_cast<__nv_bfloat16*>(take(g.big ? static_cast<size_t>(g.G) * 2 * 144 * 128 * 2 : 0));
+  w.kvb_l = static_cast<__nv_bfloat16*>(take(g.big ? static_cast<size_t>(g.G) * 2 * 144 * 128 * 2 : 0));
+  w.row_mask = static_cast<uint8_t*>(take(g.R));
+  w.base_self = static_cast<int*>(take(static_cast<size_t>(g.R / 128 + 1) * 4));
+  w.base_cross = static_cast<int*>(take(static_cast<size_t>(g.R / 128 + 1) * 4));
+  w.bytes = off;
+  return w;
+}
+
+// which streams are updated ("query side") in a launch: bit0 = stream 0, bit1 = stream 1
+template <int C>
+static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& lw, bool cross, int q_streams,
+                    int prec, cudaStream_t stream) {
+  const bool x3 = prec == 3;
+  const int kbC = C / BLOCK_K;
+  const int R = g.R;
+  const int T0 = g.row1 / 128;  // m tiles of stream 0 / stream 1
+  const int T1 = (R - g.row1) / 128;
+  const int Tall = R / 128;
+  // m-tile range of the query streams / of the source streams
+  auto tile_range = [&](int streams, int& begin, int& count) {
+    if (streams == 3) {
+      begin = 0;
+      count = Tall;
+    } else if (streams == 1) {
+      begin = 0;
+      count = T0;
+    } else {
+      begin = T0;
+      count = T1;
+    }
+  };
+  const int src_streams = cross ? (((q_streams & 1) ? 2 : 0) | ((q_streams & 2) ? 1 : 0)) : q_streams;
+  int qb, qc, sb, sc;
+  tile_range(q_streams, qb, qc);
+  tile_range(src_streams, sb, sc);
+
+  auto add_segs = [&](PlanBuilder& pb, int a_hi, int a_lo, int b_hi, int b_lo, int a_k0, int b_k0, int nkb) {
+    if (x3) {
+      pb.seg(a_hi, b_lo, a_k0, b_k0, nkb);
+      pb.seg(a_lo, b_hi, a_k0, b_k0, nkb);
+    }
+    pb.seg(a_hi, b_hi, a_k0, b_k0, nkb);
+  };
+
+  // ---- 1. QKV
+  {
+    typename EpiQKV<C>::Params ep{w.qh, x3 ? w.ql : nullptr, g.big ? nullptr : w.qf, w.kf, w.vf, w.row_mask};
+    auto launch = [&](int mb, int mc, int nb, int nc) -> int {
+      if (mc <= 0) return OPB_OK;
+      PlanBuilder pb;
+      pb.add_a(w.xh, R, C, C, 0);
+      pb.add_b(lw.qkv_hi, 3 * C, C, C, 0, C);
+      if (x3) {
+        pb.add_a(w.xl, R, C, C, 1);
+        pb.add_b(lw.qkv_lo, 3 * C, C, C, 1, C);
+      }
+      if (pb.status) return pb.status;
+      add_segs(pb, 0, 1, 0, 1, 0, 0, kbC);
+      pb.finish();
+      pb.plan.m_tile_begin = mb;
+      pb.plan.n_tile_begin = nb;
+      pb.plan.num_n_tiles = nc;
+      pb.plan.num_tiles = mc * nc;
+      pb.plan.b_rows_per_ntile = C;
+      return launch_gemm<C, (C == 256 ? 4 : 6), 4, EpiQKV<C>>(pb.plan, ep, stream);
+    };
+    if (q_streams == src_streams) {
+      if (int r = launch(qb, qc, 0, 3)) return r;
+    } else {
+      if (int r = launch(qb, qc, 0, 1)) return r;
+      if (int r = launch(sb, sc, 1, 2)) return r;
+    }
+  }
+  // ---- 2-4. attention
+  if (g.big) {
+    if constexpr (C == 256) {
+      GroupTable gt;
+      gt.num_groups = g.G;
+      unsigned long long sel = 0;
+      for (int i = 0; i < g.G; ++i) {
+        const int s = i / g.N, n = i % g.N;
+        gt.row_start[i] = s == 0 ? n * g.P0 : g.row1 + n * g.P1;
+        gt.len[i] = s == 0 ? g.len0 : g.len1;
+        if (src_streams & (1 << s)) sel |= 1ull << i;
+      }
+      kv_partial_kernel<<<dim3(g.max_chunks, g.G), 256, 0, stream>>>(w.kf, w.vf, gt, sel, w.kv_partial, g.max_chunks);
+      kv_pack_kernel<<<dim3(2, g.G), 256, 0, stream>>>(w.kv_partial, gt, sel, g.max_chunks, w.kvb_h, x3 ? w.kvb_l : nullptr);
+      OPB_CHECK_CUDA(cudaGetLastError());
+      PlanBuilder pb;
+      pb.add_a(w.qh, R, C, C, 0);
+      pb.add_b(w.kvb_h, static_cast<uint64_t>(g.G) * 2 * 144, 128, 128, 0, 144);
+      if (x3) {
+        pb.add_a(w.ql, R, C, C, 1);
+        pb.add_b(w.kvb_l, static_cast<uint64_t>(g.G) * 2 * 144, 128, 128, 1, 144);
+      }
+      if (pb.status) return pb.status;
+      add_segs(pb, 0, 1, 0, 1, 0, 0, 2);
+      pb.finish();
+      pb.plan.a_k_per_ntile = 128;
+      pb.plan.m_tile_begin = qb;
+      pb.plan.num_n_tiles = 2;
+      pb.plan.num_tiles = qc * 2;
+      pb.plan.b_rows_per_ntile = 144;
+      pb.plan.b_row_base = cross ? w.base_cross : w.base_self;
+      EpiAttn::Params ep{w.aoh, x3 ? w.aol : nullptr, 1e-6f};
+      if (int r = launch_gemm<144, 4, 4, EpiAttn>(pb.plan, ep, stream)) return r;
+    } else {
+      set_last_error("big-group attention is implemented for d_model 256 only");
+      return OPB_ERR_ARG;
+    }
+  } else {
+    if constexpr (C == 128) {
+      const int row1 = g.row1;
+      for (int s = 0; s < 2; ++s) {
+        if (!(q_streams & (1 << s))) continue;
+        const int q_row0 = s == 0 ? 0 : row1, q_len = s == 0 ? g.len0 : g.len1;
+        const int ss = cross ? 1 - s : s;
+        const int s_row0 = ss == 0 ? 0 : row1, s_len = ss == 0 ? g.len0 : g.len1;
+        attn_small_kernel<<<g.N, 128, 0, stream>>>(w.qf, w.kf, w.vf, q_row0, q_len, s_row0, s_len, g.N, 1e-6f, w.aoh,
+                                                    x3 ? w.aol : nullptr);
+      }
+      OPB_CHECK_CUDA(cudaGetLastError());
+    } else {
+      set_last_error("small-group attention is implemented for d_model 128 only");
+      return OPB_ERR_ARG;
+    }
+  }
+  const int ub = qb, uc = qc;  // only the tiles of the streams being updated run the row-wise GEMMs
+  // ---- 5. MERGE + LN1
+  {
+    PlanBuilder pb;
+    pb.add_a(w.aoh, R, C, C, 0);
+    pb.add_b(lw.m_hi, C, C, C, 0, C);
+    if (x3) {
+      pb.add_a(w.aol, R, C, C, 1);
+      pb.add_b(lw.m_lo, C, C, C, 1, C);
+    }
+    if (pb.status) return pb.status;
+    add_segs(pb, 0, 1, 0, 1, 0, 0, kbC);
+    pb.finish();
+    pb.plan.m_tile_begin = ub;
+    pb.plan.num_n_tiles = 1;
+    pb.plan.num_tiles = uc;
+    pb.plan.b_rows_per_ntile = C;
+    typename EpiLN<C>::Params ep{lw.ln1_g, lw.ln1_b, w.mh, x3 ? w.ml : nullptr};
+    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 4, EpiLN<C>>(pb.plan, ep, stream)) return r;
+  }
+  // ---- 6. MLP1 + ReLU   (K = [x | msg], N = 2C as two tiles of C)
+  {
+    PlanBuilder pb;
+    pb.add_a(w.xh, R, C, C, 0);
+    pb.add_a(w.mh, R, C, C, 2);
+    pb.add_b(lw.w1_hi, 2 * C, 2 * C, 2 * C, 0, C);
+    if (x3) {
+      pb.add_a(w.xl, R, C, C, 1);
+      pb.add_a(w.ml, R, C, C, 3);
+      pb.add_b(lw.w1_lo, 2 * C, 2 * C, 2 * C, 1, C);
+    }
+    if (pb.status) return pb.status;
+    add_segs(pb, 0, 1, 0, 1, 0, 0, kbC);
+    add_segs(pb, 2, 3, 0, 1, 0, C, kbC);
+    pb.finish();
+    pb.plan.m_tile_begin = ub;
+    pb.plan.num_n_tiles = 2;
+    pb.plan.num_tiles = uc * 2;
+    pb.plan.b_rows_per_ntile = C;
+    typename EpiRelu<C>::Params ep{w.hh, x3 ? w.hl : nullptr, 2 * C};
+    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 4, EpiRelu<C>>(pb.plan, ep, stream)) return r;
+  }
+  // ---- 7. MLP2 + LN2 + residual (in place on the master copy and its planes)
+  {
+    PlanBuilder pb;
+    pb.add_a(w.hh, R, 2 * C, 2 * C, 0);
+    pb.add_b(lw.w2_hi, C, 2 * C, 2 * C, 0, C);
+    if (x3) {
+      pb.add_a(w.hl, R, 2 * C, 2 * C, 1);
+      pb.add_b(lw.w2_lo, C, 2 * C, 2 * C, 1, C);
+    }
+    if (pb.status) return pb.status;
+    add_segs(pb, 0, 1, 0, 1, 0, 0, 2 * kbC);
+    pb.finish();
+    pb.plan.m_tile_begin = ub;
+    pb.plan.num_n_tiles = 1;
+    pb.plan.num_tiles = uc;
+    pb.plan.b_rows_per_ntile = C;
+    typename EpiLNRes<C>::Params ep{lw.ln2_g, lw.ln2_b, w.xf, w.xh, x3 ? w.xl : nullptr};
+    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 4, EpiLNRes<C>>(pb.plan, ep, stream)) return r;
+  }
+  return OPB_OK;
+}
+
+}  // namespace opb
+
+using namespace opb;
+
+extern "C" {
+
+size_t opb200_packed_layer_bytes(int d_model) { return packed_layer_bytes(d_model); }
+
+int opb200_pack_layer_weights(const float* wq, const float* wk, const float* wv, const float* wm, const float* w1,
+                              const float* w2, const float* ln1_w, const float* ln1_b, const float* ln2_w,
+                              const float* ln2_b, int C, void* packed, void* stream_) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(C == 256 || C == 128, "d_model must be 256 or 128");
+  OPB_CHECK_ARG(wq && wk && wv && wm && w1 && w2 && ln1_w && ln1_b && ln2_w && ln2_b && packed, "null pointer");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  LayerWeights v = view_layer(packed, C);
+  auto nc = [](const __nv_bfloat16* p) { return const_cast<__nv_bfloat16*>(p); };
+  const size_t cc = static_cast<size_t>(C) * C;
+  int r;
+  if ((r = split_planes(wq, C, 1, nullptr, 0, C, C, nc(v.qkv_hi), nc(v.qkv_lo), nullptr, C, stream))) return r;
+  if ((r = split_planes(wk, C, 1, nullptr, 0, C, C, nc(v.qkv_hi) + cc, nc(v.qkv_lo) + cc, nullptr, C, stream))) return r;
+  if ((r = split_planes(wv, C, 1, nullptr, 0, C, C, nc(v.qkv_hi) + 2 * cc, nc(v.qkv_lo) + 2 * cc, nullptr, C, stream))) return r;
+  if ((r = split_planes(wm, C, 1, nullptr, 0, C, C, nc(v.m_hi), nc(v.m_lo), nullptr, C, stream))) return r;
+  if ((r = split_planes(w1, 2 * C, 1, nullptr, 0, 2 * C, 2 * C, nc(v.w1_hi), nc(v.w1_lo), nullptr, 2 * C, stream))) return r;
+  if ((r = split_planes(w2, 2 * C, 1, nullptr, 0, C, 2 * C, nc(v.w2_hi), nc(v.w2_lo), nullptr, 2 * C, stream))) return r;
+  float* f = const_cast<float*>(v.ln1_g);
+  OPB_CHECK_CUDA(cudaMemcpyAsync(f, ln1_w, C * 4, cudaMemcpyDeviceToDevice, stream));
+  OPB_CHECK_CUDA(cudaMemcpyAsync(f + C, ln1_b, C * 4, cudaMemcpyDeviceToDevice, stream));
+  OPB_CHECK_CUDA(cudaMemcpyAsync(f + 2 * C, ln2_w, C * 4, cudaMemcpyDeviceToDevice, stream));
+  OPB_CHECK_CUDA(cudaMemcpyAsync(f + 3 * C, ln2_b, C * 4, cudaMemcpyDeviceToDevice, stream));
+  return OPB_OK;
+}
+
+size_t opb200_transformer_workspace_bytes(int d_model, int n_batch, int len0, int len1, int big_groups) {
+  Geometry g = make_geometry(d_model, n_batch, len0, len1, big_groups);
+  return carve(nullptr, g).bytes;
+}
+
+int opb200_transformer(const void* const* host_layer_weights, const int* host_layer_kinds, int n_layers, int schedule,
+                       int d_model, int nhead, int n_batch, int len0, int len1, int big_groups, const float* x0,
+                       int64_t x0_sn, int64_t x0_sl, int64_t x0_sc, const float* add0, const float* x1, int64_t x1_sn,
+                       int64_t x1_sl, int64_t x1_sc, const float* add1, const uint8_t* mask0, const uint8_t* mask1,
+                       float* out0, float* out1, void* workspace, size_t workspace_bytes, int precision,
+                       void* stream_) {
+  if (int r = check_device()) return r;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  OPB_CHECK_ARG(d_model == 256 || d_model == 128, "d_model must be 256 (coarse) or 128 (fine)");
+  OPB_CHECK_ARG(nhead == 8, "nhead must be 8");
+  OPB_CHECK_ARG(precision == 1 || precision == 3, "precision must be 1 or 3");
+  OPB_CHECK_ARG(schedule == 0 || schedule == 1, "schedule: 0 = OnePosePlus (simultaneous), 1 = LoFTR (sequential cross)");
+  OPB_CHECK_ARG(n_batch >= 1 && len0 >= 1 && len1 >= 1, "empty input");
+  OPB_CHECK_ARG(!big_groups || d_model == 256, "big groups need d_model 256");
+  OPB_CHECK_ARG(big_groups || d_model == 128, "small groups need d_model 128");
+  OPB_CHECK_ARG(!big_groups || 2 * n_batch <= 64, "at most 32 batch elements per call with big groups");
+  OPB_CHECK_ARG(big_groups || (len0 <= 128 && len1 <= 128), "small groups hold at most 128 tokens");
+  OPB_CHECK_ARG(x0 && x1 && out0 && out1 && workspace && host_layer_weights && host_layer_kinds, "null pointer");
+  Geometry g = make_geometry(d_model, n_batch, len0, len1, big_groups);
+  Workspace w = carve(workspace, g);
+  if (w.bytes > workspace_bytes) {
+    set_last_error("workspace too small: need " + std::to_string(w.bytes) + " bytes");
+    return OPB_ERR_WORKSPACE;
+  }
+  const int C = d_model;
+  // stage in
+  const int row1 = g.row1;
+  if (!big_groups) {  // zero the pad rows at the end of each stream region (they flow through the GEMMs)
+    const size_t pad_lo[2] = {static_cast<size_t>(n_batch) * len0, static_cast<size_t>(row1) + static_cast<size_t>(n_batch) * len1};
+    const size_t pad_hi[2] = {static_cast<size_t>(row1), static_cast<size_t>(g.R)};
+    for (int s = 0; s < 2; ++s) {
+      const size_t n = pad_hi[s] - pad_lo[s];
+      if (n == 0) continue;
+      OPB_CHECK_CUDA(cudaMemsetAsync(w.xf + pad_lo[s] * C, 0, n * C * 4, stream));
+      OPB_CHECK_CUDA(cudaMemsetAsync(w.xh + pad_lo[s] * C, 0, n * C * 2, stream));
+      OPB_CHECK_CUDA(cudaMemsetAsync(w.xl + pad_lo[s] * C, 0, n * C * 2, stream));
+      OPB_CHECK_CUDA(cudaMemsetAsync(w.row_mask + pad_lo[s], 0, n, stream));
+    }
+  }
+  copy_in_kernel<<<dim3((C + 31) / 32, (g.P0 + 31) / 32, n_batch), dim3(32, 8), 0, stream>>>(
+      x0, x0_sn, x0_sl, x0_sc, add0, mask0, len0, g.P0, C, 0, w.xf, w.xh, w.xl, w.row_mask);
+  copy_in_kernel<<<dim3((C + 31) / 32, (g.P1 + 31) / 32, n_batch), dim3(32, 8), 0, stream>>>(
+      x1, x1_sn, x1_sl, x1_sc, add1, mask1, len1, g.P1, C, row1, w.xf, w.xh, w.xl, w.row_mask);
+  if (big_groups)
+    fill_row_base_kernel<<<1, 256, 0, stream>>>(w.base_self, w.base_cross, g.tiles0, g.tiles1, n_batch, 2 * 144);
+  OPB_CHECK_CUDA(cudaGetLastError());
+
+  for (int l = 0; l < n_layers; ++l) {
+    LayerWeights lw = view_layer(host_layer_weights[l], C);
+    const bool cross = host_layer_kinds[l] == 1;
+    OPB_CHECK_ARG(host_layer_kinds[l] == 0 || host_layer_kinds[l] == 1, "layer kind must be 0 (self) or 1 (cross)");
+    int r;
+    if (cross && schedule == 1) {
+      // LoFTR: feat0 = layer(feat0, feat1); then feat1 = layer(feat1, feat0_new)
+      r = (C == 256) ? run_step<256>(g, w, lw, true, 1, precision, stream) : run_step<128>(g, w, lw, true, 1, precision, stream);
+      if (r) return r;
+      r = (C == 256) ? run_step<256>(g, w, lw, true, 2, precision, stream) : run_step<128>(g, w, lw, true, 2, precision, stream);
+    } else {
+      r = (C == 256) ? run_step<256>(g, w, lw, cross, 3, precision, stream)
+                     : run_step<128>(g, w, lw, cross, 3, precision, stream);
+    }
+    if (r) return r;
+  }
+  const int threads = 256;
+  copy_out_kernel<<<dim3((static_cast<long long>(len0) * C / 4 + threads - 1) / threads, 1, n_batch), threads, 0, stream>>>(
+      w.xf, len0, g.P0, C, 0, out0);
+  copy_out_kernel<<<dim3((static_cast<long long>(len1) * C / 4 + threads - 1) / threads, 1, n_batch), threads, 0, stream>>>(
+      w.xf, len1, g.P1, C, row1, out1);
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,105 @@
+// Host-side helpers shared by the C-ABI translation units: error reporting, TMA descriptor encoding,
+// GEMM plan construction and launch.
+#pragma once
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include "gemm.cuh"
+
+namespace opb {
+
+// ---- status codes returned by every C-ABI entry point
+enum : int {
+  OPB_OK = 0,
+  OPB_ERR_ARG = -1,        // bad argument (null pointer, unsupported size, misalignment)
+  OPB_ERR_CUDA = -2,       // a CUDA runtime/driver call failed (see opb200_last_error)
+  OPB_ERR_WORKSPACE = -3,  // caller-provided workspace too small
+  OPB_ERR_DEVICE = -4,     // not an sm_100 device
+};
+
+void set_last_error(const std::string& msg);
+
+#define OPB_CHECK_ARG(cond, msg)                                             \
+  do {                                                                       \
+    if (!(cond)) {                                                           \
+      ::opb::set_last_error(std::string("argument error: ") + (msg));        \
+      return ::opb::OPB_ERR_ARG;                                             \
+    }                                                                        \
+  } while (0)
+
+#define OPB_CHECK_CUDA(expr)                                                                  \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      ::opb::set_last_error(std::string(#expr) + " failed: " + cudaGetErrorString(_e));       \
+      return ::opb::OPB_ERR_CUDA;                                                             \
+    }                                                                                         \
+  } while (0)
+
+int check_device();  // OPB_OK iff the current device is compute capability 10.x
+int num_sms();
+
+// Encode a 2-D bf16 row-major [rows, cols] tensor (row pitch in elements) as a TMA descriptor whose box
+// is [box_rows x 64] with 128-byte swizzle.  Out-of-bounds rows/cols are zero-filled on load.
+int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_elems,
+                   uint32_t box_rows);
+
+struct PlanBuilder {
+  GemmPlan plan;
+  int status = OPB_OK;
+  PlanBuilder() { std::memset(&plan, 0, sizeof(plan)); }
+  int add_a(const void* base, uint64_t rows, uint64_t cols, uint64_t pitch, int idx) {
+    int r = make_tmap_bf16(&plan.a_maps[idx], base, rows, cols, pitch, BLOCK_M);
+    if (r != OPB_OK) status = r;
+    return idx;
+  }
+  int add_b(const void* base, uint64_t rows, uint64_t cols, uint64_t pitch, int idx, int bn) {
+    int r = make_tmap_bf16(&plan.b_maps[idx], base, rows, cols, pitch, bn);
+    if (r != OPB_OK) status = r;
+    return idx;
+  }
+  void seg(int a_map, int b_map, int a_k0, int b_k0, int nkb) {
+    KSeg& s = plan.segs[plan.nsegs++];
+    s.a_map = a_map;
+    s.b_map = b_map;
+    s.a_k0 = a_k0;
+    s.b_k0 = b_k0;
+    s.nkb = nkb;
+    plan.total_kb += nkb;
+  }
+  // fill unused descriptor slots with a valid one so the kernel's prefetch never sees garbage
+  void finish() {
+    for (int i = 1; i < kNumMaps; ++i) {
+      bool a_used = false, b_used = false;
+      for (int s = 0; s < plan.nsegs; ++s) {
+        a_used |= plan.segs[s].a_map == i;
+        b_used |= plan.segs[s].b_map == i;
+      }
+      if (!a_used) plan.a_maps[i] = plan.a_maps[0];
+      if (!b_used) plan.b_maps[i] = plan.b_maps[0];
+    }
+  }
+};
+
+template <int BN, int STAGES, int NUM_EPI_WARPS, class Epi>
+int launch_gemm(const GemmPlan& plan, const typename Epi::Params& ep, cudaStream_t stream, int max_ctas = 0) {
+  if (plan.num_tiles <= 0) return OPB_OK;
+  auto kern = gemm_kernel<BN, STAGES, NUM_EPI_WARPS, Epi>;
+  constexpr int smem = gemm_smem_bytes(BN, STAGES, Epi::kSmemBytes);
+  static_assert(smem <= 227 * 1024, "shared memory budget exceeded");
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    OPB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  int grid = num_sms();
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (plan.num_tiles < grid) grid = plan.num_tiles;
+  kern<<<grid, 64 + 32 * NUM_EPI_WARPS, smem, stream>>>(plan, ep);
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+}  // namespace opb

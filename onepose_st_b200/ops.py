@@ -1,0 +1,112 @@
+"""Thin Python wrappers over the C-ABI in include/opb200.h: they only extract pointers, sizes and
+strides from torch tensors, own the workspaces, and raise on any non-zero status.  No math here."""
+import ctypes
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+
+PREC_BF16 = 1
+PREC_BF16X3 = 3
+
+_c_i64 = ctypes.c_int64
+_c_sz = ctypes.c_size_t
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.Opb200Error("onepose_st_b200 ops need CUDA tensors (there is no CPU path)")
+
+
+def _f32(t: torch.Tensor) -> torch.Tensor:
+    return t if t.dtype == torch.float32 else t.float()
+
+
+class _Workspaces:
+    """One growable byte buffer per (device, tag); reused across calls so addresses stay stable
+    (needed for CUDA-graph capture) and no allocation happens in steady state."""
+
+    def __init__(self):
+        self._bufs = {}
+
+    def get(self, device, tag: str, nbytes: int) -> torch.Tensor:
+        key = (device.index, tag)
+        buf = self._bufs.get(key)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+            self._bufs[key] = buf
+        return buf
+
+
+workspaces = _Workspaces()
+
+
+def split_planes(x: torch.Tensor):
+    """fp32 [rows, cols] (any strides) -> (hi, lo) bf16 planes."""
+    _need_cuda(x)
+    x = _f32(x)
+    rows, cols = x.shape
+    hi = torch.empty(rows, cols, dtype=torch.bfloat16, device=x.device)
+    lo = torch.empty_like(hi)
+    st = _lib.lib().opb200_split_planes(_lib.ptr(x), _c_i64(x.stride(0)), _c_i64(x.stride(1)), rows, cols,
+                                        _lib.ptr(hi), _lib.ptr(lo), None, _lib.stream_ptr())
+    _lib.check(st, "opb200_split_planes")
+    return hi, lo
+
+
+def packed_layer_bytes(d_model: int) -> int:
+    l = _lib.lib()
+    l.opb200_packed_layer_bytes.restype = _c_sz
+    return int(l.opb200_packed_layer_bytes(d_model))
+
+
+def pack_layer_weights(wq, wk, wv, wm, w1, w2, ln1_w, ln1_b, ln2_w, ln2_b) -> torch.Tensor:
+    """Pack one LoFTREncoderLayer's parameters into the bf16 hi/lo plane layout the kernels read."""
+    ts = [_f32(t.detach()).contiguous() for t in (wq, wk, wv, wm, w1, w2, ln1_w, ln1_b, ln2_w, ln2_b)]
+    _need_cuda(*ts)
+    d_model = ts[0].shape[0]
+    out = torch.empty(packed_layer_bytes(d_model), dtype=torch.uint8, device=ts[0].device)
+    st = _lib.lib().opb200_pack_layer_weights(*[_lib.ptr(t) for t in ts], d_model, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "opb200_pack_layer_weights")
+    return out
+
+
+def transformer(packed_layers: Sequence[torch.Tensor], layer_kinds: Sequence[int], schedule: int, d_model: int,
+                nhead: int, x0: torch.Tensor, x1: torch.Tensor, add0: Optional[torch.Tensor] = None,
+                add1: Optional[torch.Tensor] = None, mask0: Optional[torch.Tensor] = None,
+                mask1: Optional[torch.Tensor] = None, big_groups: bool = True, precision: int = PREC_BF16X3):
+    """x0 [N, len0, C], x1 [N, len1, C] as (possibly permuted) fp32 views -> (out0, out1) contiguous."""
+    _need_cuda(x0, x1)
+    x0, x1 = _f32(x0), _f32(x1)
+    n, len0, c = x0.shape
+    n1, len1, c1 = x1.shape
+    if n != n1 or c != d_model or c1 != d_model:
+        raise _lib.Opb200Error(f"transformer: inconsistent shapes {tuple(x0.shape)} / {tuple(x1.shape)} for d_model {d_model}")
+    l = _lib.lib()
+    l.opb200_transformer_workspace_bytes.restype = _c_sz
+    nbytes = int(l.opb200_transformer_workspace_bytes(d_model, n, len0, len1, int(big_groups)))
+    ws = workspaces.get(x0.device, "transformer%d" % d_model, nbytes)
+    out0 = torch.empty(n, len0, c, dtype=torch.float32, device=x0.device)
+    out1 = torch.empty(n, len1, c, dtype=torch.float32, device=x0.device)
+    nl = len(packed_layers)
+    w_arr = (ctypes.c_void_p * nl)(*[t.data_ptr() for t in packed_layers])
+    k_arr = (ctypes.c_int * nl)(*[int(k) for k in layer_kinds])
+
+    def m8(m, length):
+        if m is None:
+            return None
+        m = m.reshape(n, length)
+        return (m if m.dtype in (torch.bool, torch.uint8) else (m != 0)).contiguous()
+
+    mk0, mk1 = m8(mask0, len0), m8(mask1, len1)
+    a0 = None if add0 is None else _f32(add0).contiguous()
+    a1 = None if add1 is None else _f32(add1).contiguous()
+    st = l.opb200_transformer(w_arr, k_arr, nl, int(schedule), d_model, nhead, n, len0, len1, int(big_groups),
+                              _lib.ptr(x0), _c_i64(x0.stride(0)), _c_i64(x0.stride(1)), _c_i64(x0.stride(2)), _lib.ptr(a0),
+                              _lib.ptr(x1), _c_i64(x1.stride(0)), _c_i64(x1.stride(1)), _c_i64(x1.stride(2)), _lib.ptr(a1),
+                              _lib.ptr(mk0), _lib.ptr(mk1), _lib.ptr(out0), _lib.ptr(out1), _lib.ptr(ws), _c_sz(ws.numel()),
+                              int(precision), _lib.stream_ptr())
+    _lib.check(st, "opb200_transformer")
+    return out0, out1
