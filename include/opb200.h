@@ -70,6 +70,24 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
                        int64_t x1_sl, int64_t x1_sc, const float* add1, const uint8_t* mask0, const uint8_t* mask1,
                        float* out0, float* out1, void* workspace, size_t workspace_bytes, int precision, void* stream);
 
+/* ---- CoarseMatching: dual-softmax + threshold + border + mutual nearest neighbour ------------------
+ * Replaces CoarseMatching.forward / get_coarse_match (eval mode):
+ *   src/models/OnePosePlus/utils/coarse_matching.py:76-242
+ *   submodules/LoFTR/src/loftr/utils/coarse_matching.py:87-261 (match_type dual_softmax)
+ * feat_a [n_batch, L, C], feat_b [n_batch, S, C] fp32 contiguous; masks nullable bytes (1 = valid);
+ * mask_fill 0: sim += -1e9 where masked (OnePosePlus), 1: sim = -1e9 (LoFTR);
+ * scale = 1 / (C * (temperature + eps)); border_mode 0 = OnePosePlus (first border_rm rows/cols of the
+ * h1 x w1 grid), 1 = LoFTR (four sides of both grids; valid_hw nullable [n_batch,4] = valid (h0,w0,h1,w1)
+ * from the padding masks).  Outputs (capacity rows each): b_ids/i_ids/j_ids int64, mconf fp32, in
+ * ascending (b, i) order; count_and_overflow is int[2] on the device: {number of matches, overflow flag}.
+ * conf_matrix (nullable) receives the full [n_batch, L, S] confidence matrix. */
+size_t opb200_coarse_match_workspace_bytes(int n_batch, int L, int S, int C, float thr);
+int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t* mask_a, const uint8_t* mask_b,
+                        int mask_fill, int n_batch, int L, int S, int C, float scale, float thr, int border_rm,
+                        int border_mode, int h0, int w0, int h1, int w1, const int* valid_hw, int64_t* b_ids,
+                        int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity, int* count_and_overflow,
+                        float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

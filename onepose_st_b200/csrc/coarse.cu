@@ -1,0 +1,512 @@
+// CoarseMatching: dual-softmax confidence + threshold + border + mutual-nearest-neighbour selection,
+// without materialising the [L, S] confidence matrix (unless the caller asks for it).
+//
+// Replaces  CoarseMatching.forward / get_coarse_match
+//             src/models/OnePosePlus/utils/coarse_matching.py:76-242   (3D points x query cells)
+//             submodules/LoFTR/src/loftr/utils/coarse_matching.py:87-261 (image0 cells x image1 cells)
+//
+//   sim  = (a . b) * scale                    scale = 1 / (C * (T + eps))
+//   conf = softmax_rows-over-L(sim) * softmax_cols-over-S(sim)
+//        = exp(2 sim - LSErow_i - LSEcol_j)   (LSE = log-sum-exp of the row / of the column)
+//
+// Pass 1 (STATS): tcgen05 GEMM tiles of sim; the epilogue keeps an online (max, sum) per row in the
+//   owning thread and reduces per-tile column (max, sum) through a 32-column shared-memory transpose.
+//   Partials go to small [tiles, rows] / [tiles, cols] arrays; a merge kernel turns them into LSEs.
+// Pass 2 (SELECT): the same GEMM tiles again (bit-identical accumulators); the epilogue forms
+//   t = 2 sim - LSErow - LSEcol and appends (row, col, conf) for the rare elements with conf > thr.
+//   Since sum_j conf_ij <= 1 there are < 1/thr such elements per row, so the candidate list is tiny,
+//   and because any element that beats a candidate is itself a candidate, the row/column maxima over
+//   candidates equal the maxima over the full matrix wherever a match can exist.
+// Resolve: atomicMax of conf bits per row / column, pick the first j per row that equals both maxima
+//   and passes the border rule, then an ordered compaction (ascending (b, i), as torch.where yields).
+// Optional: pass 2 also streams conf to HBM (conf_matrix of the data-dict contract; training/debug).
+#include <cmath>
+#include "host.cuh"
+#include "../../include/opb200.h"
+
+namespace opb {
+
+int split_planes(const float* x, long long stride_r, long long stride_c, const float* add, long long add_period_rows,
+                 int rows, int cols, __nv_bfloat16* hi, __nv_bfloat16* lo, float* f32out, long long ld_out,
+                 cudaStream_t stream);
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kNegInf = -INFINITY;
+constexpr int kNoMatch = 0x7f7f7f7f;  // rowj sentinel (what cudaMemsetAsync(0x7f) leaves)
+
+struct SimGeom {
+  int N, L, S, Lp, Sp;        // valid and padded (per batch element) row / column counts
+  float scale;                // 1 / (C * (T + eps))
+  const uint8_t* mask_a;      // [N, L] nullable
+  const uint8_t* mask_b;      // [N, S] nullable
+  int mask_fill;              // 0: sim += -1e9 (OnePosePlus), 1: sim = -1e9 (LoFTR masked_fill_)
+};
+
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// y = log2(e) * sim with the reference's masking semantics applied to sim first
+__device__ __forceinline__ float sim_log2(float acc, float scale, bool masked, int fill) {
+  // explicit _rn intrinsics: the compiler must not contract these into FMAs -- both passes (and the
+  // subtraction of the row/column maxima that follows) have to see the same ROUNDED value of y
+  float sim = __fmul_rn(acc, scale);
+  if (masked) sim = fill ? -1e9f : __fadd_rn(sim, -1e9f);
+  return __fmul_rn(sim, kLog2e);
+}
+
+template <int BN>
+struct EpiSimStats {
+  struct Params {
+    SimGeom g;
+    float2* rowpart;  // [Sp/BN][N*Lp]
+    float2* colpart;  // [Lp/128][N*Sp]
+  };
+  static constexpr int kSmemBytes = 2 * 128 * 33 * 4 + 2 * 4 * 32 * 8;
+  static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
+    const SimGeom& g = p.g;
+    float(*sc)[128][33] = reinterpret_cast<float(*)[128][33]>(ctx.scratch);
+    float2(*part)[4][32] = reinterpret_cast<float2(*)[4][32]>(ctx.scratch + 2 * 128 * 33 * 4);
+    const int r = ctx.quarter * 32 + ctx.lane;
+    const int grow = ctx.m_tile * BLOCK_M + r;  // padded global row
+    const int n = grow / g.Lp;
+    const int i = grow - n * g.Lp;
+    const bool row_valid = i < g.L;
+    const bool row_masked = row_valid && g.mask_a != nullptr && g.mask_a[static_cast<long long>(n) * g.L + i] == 0;
+    const int mt_in_batch = ctx.m_tile - n * (g.Lp / BLOCK_M);
+    float m = kNegInf, s = 0.f;
+    int buf = 0;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32, buf ^= 1) {
+      float y[32];
+      load_acc32(ctx.tmem_acc + c0, y);
+      const int j0 = ctx.n_tile * BN + c0;
+      float cmax = kNegInf;
+#pragma unroll
+      for (int k = 0; k < 32; ++k) {
+        const int j = j0 + k;
+        const bool col_valid = j < g.S;
+        const bool masked = row_masked || (g.mask_b != nullptr && col_valid && g.mask_b[static_cast<long long>(n) * g.S + j] == 0);
+        const float v = col_valid ? sim_log2(y[k], g.scale, masked, g.mask_fill) : kNegInf;
+        y[k] = v;
+        cmax = fmaxf(cmax, v);
+      }
+      if (cmax > kNegInf) {
+        const float mn = fmaxf(m, cmax);
+        float acc = s * ptx::ex2(m - mn);
+#pragma unroll
+        for (int k = 0; k < 32; ++k) acc += ptx::ex2(y[k] - mn);
+        s = acc;
+        m = mn;
+      }
+#pragma unroll
+      for (int k = 0; k < 32; ++k) sc[buf][r][k] = row_valid ? y[k] : kNegInf;
+      epi_bar();
+      {
+        const int cq = ctx.epi_warp, cc = ctx.lane;
+        float v[32];
+        float pm = kNegInf;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          v[k] = sc[buf][cq * 32 + k][cc];
+          pm = fmaxf(pm, v[k]);
+        }
+        float ps = 0.f;
+        if (pm > kNegInf) {
+#pragma unroll
+          for (int k = 0; k < 32; ++k) ps += ptx::ex2(v[k] - pm);
+        }
+        part[buf][cq][cc] = make_float2(pm, ps);
+      }
+      epi_bar();
+      if (ctx.epi_warp == 0) {
+        float M = kNegInf;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) M = fmaxf(M, part[buf][q][ctx.lane].x);
+        float S = 0.f;
+        if (M > kNegInf) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float2 pq = part[buf][q][ctx.lane];
+            if (pq.x > kNegInf) S += pq.y * ptx::ex2(pq.x - M);
+          }
+        }
+        const int j = j0 + ctx.lane;
+        if (j < g.Sp) p.colpart[static_cast<long long>(mt_in_batch) * g.N * g.Sp + static_cast<long long>(n) * g.Sp + j] = make_float2(M, S);
+      }
+    }
+    p.rowpart[static_cast<long long>(ctx.n_tile) * g.N * g.Lp + grow] = make_float2(m, s);
+  }
+};
+
+// merge (max, sum) partials -> log2-sum-exp per row and per column
+__global__ void merge_stats_kernel(const float2* __restrict__ rowpart, int n_row_parts, long long n_rows,
+                                   const float2* __restrict__ colpart, int n_col_parts, long long n_cols,
+                                   float2* __restrict__ lse_row, float2* __restrict__ lse_col) {
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const float2* part;
+  int nparts;
+  long long stride, idx;
+  float2* out;
+  if (t < n_rows) {
+    part = rowpart, nparts = n_row_parts, stride = n_rows, idx = t, out = lse_row;
+  } else if (t < n_rows + n_cols) {
+    part = colpart, nparts = n_col_parts, stride = n_cols, idx = t - n_rows, out = lse_col;
+  } else {
+    return;
+  }
+  float M = kNegInf;
+  for (int k = 0; k < nparts; ++k) M = fmaxf(M, part[k * stride + idx].x);
+  float S = 0.f;
+  if (M > kNegInf) {
+    for (int k = 0; k < nparts; ++k) {
+      const float2 pk = part[k * stride + idx];
+      if (pk.x > kNegInf) S += pk.y * exp2f(pk.x - M);
+    }
+  }
+  // kept as (max, log2 sum) rather than their sum: for a fully masked row/column max = -1.44e9 and
+  // adding log2(sum) to it would be lost to rounding, turning 1/(L*S) confidences into 1.0
+  out[idx] = make_float2(M, (M > kNegInf) ? log2f(S) : 0.f);
+}
+
+struct Candidate {
+  int row;  // n * L + i
+  int col;  // j
+  float conf;
+  int pad;
+};
+
+// The one place conf is computed; used by both the select and the materialise path so that the value a
+// match reports, the value compared against thr and the value written to conf_matrix are the same bits.
+__device__ __forceinline__ float conf_exponent(float y, float2 lse_r, float2 lse_c) {
+  return __fadd_rn(__fsub_rn(__fsub_rn(y, lse_r.x), lse_r.y), __fsub_rn(__fsub_rn(y, lse_c.x), lse_c.y));
+}
+__device__ __forceinline__ float conf_from(float y, float2 lse_r, float2 lse_c) {
+  return exp2f(conf_exponent(y, lse_r, lse_c));
+}
+
+template <int BN, bool WRITE_CONF>
+struct EpiSimSelect {
+  struct Params {
+    SimGeom g;
+    const float2* lse_row;  // [N*Lp] (max, log2 sum) in log2 units
+    const float2* lse_col;  // [N*Sp]
+    float thr, log2_thr_lo;
+    Candidate* cand;
+    int* cand_count;
+    int cand_cap;
+    float* conf_matrix;  // [N, L, S] (WRITE_CONF only)
+  };
+  static constexpr int kSmemBytes = 0;
+  static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
+    const SimGeom& g = p.g;
+    const int r = ctx.quarter * 32 + ctx.lane;
+    const int grow = ctx.m_tile * BLOCK_M + r;
+    const int n = grow / g.Lp;
+    const int i = grow - n * g.Lp;
+    const bool row_valid = i < g.L;
+    const bool row_masked = row_valid && g.mask_a != nullptr && g.mask_a[static_cast<long long>(n) * g.L + i] == 0;
+    const float2 lr = row_valid ? p.lse_row[grow] : make_float2(0.f, 0.f);
+    const float2* lc = p.lse_col + static_cast<long long>(n) * g.Sp;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      float y[32];
+      load_acc32(ctx.tmem_acc + c0, y);
+      const int j0 = ctx.n_tile * BN + c0;
+      if (!row_valid || j0 >= g.S) continue;
+      float cf[32];
+      float2 lcs[WRITE_CONF ? 1 : 32];
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < 32; ++k) {
+        const int j = j0 + k;
+        const bool col_valid = j < g.S;
+        const bool masked = row_masked || (g.mask_b != nullptr && col_valid && g.mask_b[static_cast<long long>(n) * g.S + j] == 0);
+        const float v = sim_log2(y[k], g.scale, masked, g.mask_fill);
+        const float2 lcj = col_valid ? __ldg(lc + j) : make_float2(0.f, 0.f);
+        if (WRITE_CONF) {
+          cf[k] = col_valid ? conf_from(v, lr, lcj) : 0.f;
+          any |= cf[k] > p.thr;
+        } else {
+          y[k] = v;
+          lcs[WRITE_CONF ? 0 : k] = lcj;
+          any |= col_valid && (conf_exponent(v, lr, lcj) > p.log2_thr_lo);
+        }
+      }
+      if (WRITE_CONF) {
+        float* dst = p.conf_matrix + (static_cast<long long>(n) * g.L + i) * g.S + j0;
+        if ((g.S & 3) == 0 && j0 + 32 <= g.S) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            reinterpret_cast<float4*>(dst)[k] = make_float4(cf[4 * k], cf[4 * k + 1], cf[4 * k + 2], cf[4 * k + 3]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 32; ++k)
+            if (j0 + k < g.S) dst[k] = cf[k];
+        }
+      }
+      if (any) {
+#pragma unroll 1
+        for (int k = 0; k < 32; ++k) {
+          const int j = j0 + k;
+          if (j >= g.S) break;
+          const float c = WRITE_CONF ? cf[k] : conf_from(y[k], lr, lcs[WRITE_CONF ? 0 : k]);
+          if (c > p.thr) {
+            const int slot = atomicAdd(p.cand_count, 1);
+            if (slot < p.cand_cap) p.cand[slot] = Candidate{n * g.L + i, j, c, 0};
+          }
+        }
+      }
+    }
+  }
+};
+
+struct BorderRule {
+  int mode;    // 0: OnePosePlus (query grid, top/left only); 1: LoFTR (both grids, four sides)
+  int b;       // border_rm
+  int h0, w0;  // grid of the rows (LoFTR image0); unused for mode 0
+  int h1, w1;  // grid of the columns (query image / image1)
+  const int* valid_hw;  // nullable [N,4] = (h0, w0, h1, w1) valid extents from the padding masks (LoFTR)
+};
+
+__device__ __forceinline__ bool border_keep(const BorderRule& br, int n, int i, int j) {
+  if (br.b <= 0) return true;
+  const int r1 = j / br.w1, c1 = j - r1 * br.w1;
+  if (br.mode == 0) return r1 >= br.b && c1 >= br.b;
+  const int r0 = i / br.w0, c0 = i - r0 * br.w0;
+  int h0 = br.h0, w0 = br.w0, h1 = br.h1, w1 = br.w1;
+  if (br.valid_hw != nullptr) {
+    h0 = br.valid_hw[4 * n + 0], w0 = br.valid_hw[4 * n + 1], h1 = br.valid_hw[4 * n + 2], w1 = br.valid_hw[4 * n + 3];
+  }
+  return r0 >= br.b && c0 >= br.b && r1 >= br.b && c1 >= br.b && r0 < h0 - br.b && c0 < w0 - br.b && r1 < h1 - br.b &&
+         c1 < w1 - br.b;
+}
+
+__global__ void cand_max_kernel(const Candidate* __restrict__ cand, const int* __restrict__ count, int cap, int L, int S,
+                                unsigned* __restrict__ rowmax, unsigned* __restrict__ colmax) {
+  const int n_c = min(*count, cap);
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_c; t += gridDim.x * blockDim.x) {
+    const Candidate c = cand[t];
+    const unsigned bits = __float_as_uint(c.conf);  // conf > thr > 0: the bit pattern orders like the value
+    atomicMax(&rowmax[c.row], bits);
+    atomicMax(&colmax[(c.row / L) * static_cast<long long>(S) + c.col], bits);
+  }
+}
+
+__global__ void cand_pick_kernel(const Candidate* __restrict__ cand, const int* __restrict__ count, int cap, int L, int S,
+                                 const unsigned* __restrict__ rowmax, const unsigned* __restrict__ colmax, BorderRule br,
+                                 int* __restrict__ rowj) {
+  const int n_c = min(*count, cap);
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_c; t += gridDim.x * blockDim.x) {
+    const Candidate c = cand[t];
+    const unsigned bits = __float_as_uint(c.conf);
+    const int n = c.row / L, i = c.row - n * L;
+    if (bits == rowmax[c.row] && bits == colmax[n * static_cast<long long>(S) + c.col] && border_keep(br, n, i, c.col))
+      atomicMin(&rowj[c.row], c.col);  // ties inside a row: the first j, as mask.max(dim=2) returns
+  }
+}
+
+// single-block ordered compaction over the N*L rows (ascending (b, i) like torch.where)
+__global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ rowj, const unsigned* __restrict__ rowmax,
+                                                       int n_rows, int L, long long* __restrict__ b_ids,
+                                                       long long* __restrict__ i_ids, long long* __restrict__ j_ids,
+                                                       float* __restrict__ mconf, int capacity, int* __restrict__ out_count,
+                                                       const int* __restrict__ cand_count, int cand_cap, int* __restrict__ overflow) {
+  __shared__ int warp_sums[32];
+  __shared__ int carry;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  if (t == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n_rows; base += 1024) {
+    const int row = base + t;
+    const int j = row < n_rows ? rowj[row] : kNoMatch;
+    const int flag = j != kNoMatch;
+    const unsigned ball = __ballot_sync(0xffffffffu, flag);
+    const int in_warp = __popc(ball & ((1u << lane) - 1));
+    if (lane == 0) warp_sums[warp] = __popc(ball);
+    __syncthreads();
+    int off = carry;
+    for (int w = 0; w < warp; ++w) off += warp_sums[w];
+    if (flag) {
+      const int pos = off + in_warp;
+      if (pos < capacity) {
+        b_ids[pos] = row / L;
+        i_ids[pos] = row % L;
+        j_ids[pos] = j;
+        mconf[pos] = __uint_as_float(rowmax[row]);
+      }
+    }
+    __syncthreads();
+    if (t == 0) {
+      int tot = 0;
+      for (int w = 0; w < 32; ++w) tot += warp_sums[w];
+      carry += tot;
+    }
+    __syncthreads();
+  }
+  if (t == 0) {
+    *out_count = carry;
+    *overflow = (*cand_count > cand_cap) || (carry > capacity);
+  }
+}
+
+__global__ void fill_sim_row_base(int* base, int tiles_per_batch, int N, int Sp) {
+  for (int t = threadIdx.x + blockIdx.x * blockDim.x; t < tiles_per_batch * N; t += blockDim.x * gridDim.x)
+    base[t] = (t / tiles_per_batch) * Sp;
+}
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+constexpr int SIM_BN = 128;
+
+struct CoarseWs {
+  __nv_bfloat16 *a_hi, *a_lo, *b_hi, *b_lo;
+  float2 *rowpart, *colpart;
+  float2 *lse_row, *lse_col;
+  Candidate* cand;
+  unsigned *rowmax, *colmax;
+  int *rowj, *row_base, *counters;  // counters: [0] cand_count, [1] overflow
+  int cand_cap;
+  int Lp, Sp;
+  size_t zero_begin, zero_bytes;  // region that must be cleared per call (rowmax, colmax, counters)
+  size_t bytes;
+};
+
+static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) {
+  CoarseWs w;
+  w.Lp = static_cast<int>(align_up(L, BLOCK_M));
+  w.Sp = static_cast<int>(align_up(S, SIM_BN));
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? static_cast<uint8_t*>(base) + off : nullptr;
+    off += align_up(bytes, 1024);
+    return p;
+  };
+  const size_t ra = static_cast<size_t>(N) * w.Lp, rb = static_cast<size_t>(N) * w.Sp;
+  w.a_hi = static_cast<__nv_bfloat16*>(take(ra * C * 2));
+  w.a_lo = static_cast<__nv_bfloat16*>(take(ra * C * 2));
+  w.b_hi = static_cast<__nv_bfloat16*>(take(rb * C * 2));
+  w.b_lo = static_cast<__nv_bfloat16*>(take(rb * C * 2));
+  w.rowpart = static_cast<float2*>(take(static_cast<size_t>(w.Sp / SIM_BN) * ra * 8));
+  w.colpart = static_cast<float2*>(take(static_cast<size_t>(w.Lp / BLOCK_M) * rb * 8));
+  w.lse_row = static_cast<float2*>(take(ra * 8));
+  w.lse_col = static_cast<float2*>(take(rb * 8));
+  const double bound = std::ceil(static_cast<double>(N) * (L < S ? L : S) / (thr > 1e-6f ? thr : 1e-6f)) + 64;
+  const double all = static_cast<double>(N) * L * S;
+  w.cand_cap = static_cast<int>(bound < all ? bound : all);
+  w.cand = static_cast<Candidate*>(take(static_cast<size_t>(w.cand_cap) * sizeof(Candidate)));
+  w.rowj = static_cast<int*>(take(static_cast<size_t>(N) * L * 4));
+  w.row_base = static_cast<int*>(take(ra / BLOCK_M * 4 + 4));
+  w.zero_begin = off;
+  w.rowmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * L * 4));
+  w.colmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * S * 4));
+  w.counters = static_cast<int*>(take(16));
+  w.zero_bytes = off - w.zero_begin;
+  w.bytes = off;
+  return w;
+}
+
+}  // namespace opb
+
+using namespace opb;
+
+extern "C" {
+
+size_t opb200_coarse_match_workspace_bytes(int n_batch, int L, int S, int C, float thr) {
+  return carve_coarse(nullptr, n_batch, L, S, C, thr).bytes;
+}
+
+int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t* mask_a, const uint8_t* mask_b,
+                        int mask_fill, int n_batch, int L, int S, int C, float scale, float thr, int border_rm,
+                        int border_mode, int h0, int w0, int h1, int w1, const int* valid_hw, int64_t* b_ids,
+                        int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity, int* count_and_overflow,
+                        float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, void* stream_) {
+  if (int r = check_device()) return r;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  OPB_CHECK_ARG(feat_a && feat_b && b_ids && i_ids && j_ids && mconf && count_and_overflow && workspace, "null pointer");
+  OPB_CHECK_ARG(n_batch >= 1 && L >= 1 && S >= 1, "empty input");
+  OPB_CHECK_ARG(C % BLOCK_K == 0 && C >= BLOCK_K, "feature dim must be a positive multiple of 64");
+  OPB_CHECK_ARG(thr > 0.f && thr < 1.f, "thr must be in (0,1): the candidate-list selection relies on conf > thr > 0");
+  OPB_CHECK_ARG(precision == 1 || precision == 3, "precision must be 1 or 3");
+  OPB_CHECK_ARG(border_mode == 0 || border_mode == 1, "border_mode must be 0 (OnePosePlus) or 1 (LoFTR)");
+  OPB_CHECK_ARG(h1 * w1 == S && (border_mode == 0 || h0 * w0 == L), "grid shape does not match the token count");
+  OPB_CHECK_ARG(static_cast<long long>(n_batch) * (L > S ? L : S) < (1ll << 30), "problem too large for 32-bit row ids");
+  CoarseWs w = carve_coarse(workspace, n_batch, L, S, C, thr);
+  if (w.bytes > workspace_bytes) {
+    set_last_error("workspace too small: need " + std::to_string(w.bytes) + " bytes");
+    return OPB_ERR_WORKSPACE;
+  }
+  const bool x3 = precision == 3;
+  const int N = n_batch, Lp = w.Lp, Sp = w.Sp;
+  // ---- operand planes (pad rows zero so they add nothing and never produce NaN)
+  if (Lp != L) {
+    OPB_CHECK_CUDA(cudaMemsetAsync(w.a_hi, 0, static_cast<size_t>(N) * Lp * C * 2, stream));
+    if (x3) OPB_CHECK_CUDA(cudaMemsetAsync(w.a_lo, 0, static_cast<size_t>(N) * Lp * C * 2, stream));
+  }
+  if (Sp != S) {
+    OPB_CHECK_CUDA(cudaMemsetAsync(w.b_hi, 0, static_cast<size_t>(N) * Sp * C * 2, stream));
+    if (x3) OPB_CHECK_CUDA(cudaMemsetAsync(w.b_lo, 0, static_cast<size_t>(N) * Sp * C * 2, stream));
+  }
+  for (int n = 0; n < N; ++n) {
+    if (int r = split_planes(feat_a + static_cast<size_t>(n) * L * C, C, 1, nullptr, 0, L, C, w.a_hi + static_cast<size_t>(n) * Lp * C,
+                             x3 ? w.a_lo + static_cast<size_t>(n) * Lp * C : nullptr, nullptr, C, stream))
+      return r;
+    if (int r = split_planes(feat_b + static_cast<size_t>(n) * S * C, C, 1, nullptr, 0, S, C, w.b_hi + static_cast<size_t>(n) * Sp * C,
+                             x3 ? w.b_lo + static_cast<size_t>(n) * Sp * C : nullptr, nullptr, C, stream))
+      return r;
+  }
+  OPB_CHECK_CUDA(cudaMemsetAsync(static_cast<uint8_t*>(workspace) + w.zero_begin, 0, w.zero_bytes, stream));
+  OPB_CHECK_CUDA(cudaMemsetAsync(w.rowj, 0x7f, static_cast<size_t>(N) * L * 4, stream));  // kNoMatch
+  const int m_tiles = N * (Lp / BLOCK_M), n_tiles = Sp / SIM_BN;
+  fill_sim_row_base<<<(m_tiles + 255) / 256, 256, 0, stream>>>(w.row_base, Lp / BLOCK_M, N, Sp);
+
+  PlanBuilder pb;
+  pb.add_a(w.a_hi, static_cast<uint64_t>(N) * Lp, C, C, 0);
+  pb.add_b(w.b_hi, static_cast<uint64_t>(N) * Sp, C, C, 0, SIM_BN);
+  if (x3) {
+    pb.add_a(w.a_lo, static_cast<uint64_t>(N) * Lp, C, C, 1);
+    pb.add_b(w.b_lo, static_cast<uint64_t>(N) * Sp, C, C, 1, SIM_BN);
+  }
+  if (pb.status) return pb.status;
+  const int nkb = C / BLOCK_K;
+  if (x3) {
+    pb.seg(0, 1, 0, 0, nkb);
+    pb.seg(1, 0, 0, 0, nkb);
+  }
+  pb.seg(0, 0, 0, 0, nkb);
+  pb.finish();
+  pb.plan.num_n_tiles = n_tiles;
+  pb.plan.num_tiles = m_tiles * n_tiles;
+  pb.plan.b_rows_per_ntile = SIM_BN;
+  pb.plan.b_row_base = w.row_base;
+
+  SimGeom g{N, L, S, Lp, Sp, scale, mask_a, mask_b, mask_fill};
+  {
+    EpiSimStats<SIM_BN>::Params ep{g, w.rowpart, w.colpart};
+    if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimStats<SIM_BN>>(pb.plan, ep, stream)) return r;
+  }
+  {
+    const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
+    merge_stats_kernel<<<static_cast<unsigned>((nr + nc + 255) / 256), 256, 0, stream>>>(w.rowpart, n_tiles, nr, w.colpart,
+                                                                                        Lp / BLOCK_M, nc, w.lse_row, w.lse_col);
+  }
+  {
+    const float log2_thr_lo = log2f(thr) - 1e-3f;
+    if (conf_matrix != nullptr) {
+      EpiSimSelect<SIM_BN, true>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, conf_matrix};
+      if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, true>>(pb.plan, ep, stream)) return r;
+    } else {
+      EpiSimSelect<SIM_BN, false>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, nullptr};
+      if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, false>>(pb.plan, ep, stream)) return r;
+    }
+  }
+  BorderRule br{border_mode, border_rm, h0, w0, h1, w1, valid_hw};
+  const int cb = (w.cand_cap + 255) / 256 < 592 ? (w.cand_cap + 255) / 256 : 592;
+  cand_max_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.rowmax, w.colmax);
+  cand_pick_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.rowmax, w.colmax, br, w.rowj);
+  compact_kernel<<<1, 1024, 0, stream>>>(w.rowj, w.rowmax, N * L, L, reinterpret_cast<long long*>(b_ids),
+                                         reinterpret_cast<long long*>(i_ids), reinterpret_cast<long long*>(j_ids), mconf, capacity,
+                                         count_and_overflow, w.counters, w.cand_cap, count_and_overflow + 1);
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+}  // extern "C"

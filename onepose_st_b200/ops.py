@@ -110,3 +110,55 @@ def transformer(packed_layers: Sequence[torch.Tensor], layer_kinds: Sequence[int
                               int(precision), _lib.stream_ptr())
     _lib.check(st, "opb200_transformer")
     return out0, out1
+
+
+def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, thr: float, border_rm: int,
+                 border_mode: int, grid_a, grid_b, mask_a: Optional[torch.Tensor] = None,
+                 mask_b: Optional[torch.Tensor] = None, mask_fill: int = 0, valid_hw: Optional[torch.Tensor] = None,
+                 materialize_conf: bool = False, precision: int = PREC_BF16X3):
+    """Dual-softmax + mutual-NN selection.  Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None).
+
+    One host sync (reading the match count) -- the reference syncs at the same point (torch.where)."""
+    _need_cuda(feat_a, feat_b)
+    feat_a, feat_b = _f32(feat_a).contiguous(), _f32(feat_b).contiguous()
+    n, L, C = feat_a.shape
+    S = feat_b.shape[1]
+    if not (0.0 < thr < 1.0):
+        raise NotImplementedError(f"coarse matching threshold must be in (0,1), got {thr}")
+    dev = feat_a.device
+    l = _lib.lib()
+    l.opb200_coarse_match_workspace_bytes.restype = _c_sz
+    nbytes = int(l.opb200_coarse_match_workspace_bytes(n, L, S, C, ctypes.c_float(thr)))
+    ws = workspaces.get(dev, "coarse", nbytes)
+    cap = n * min(L, S)
+    b_ids = torch.empty(cap, dtype=torch.int64, device=dev)
+    i_ids = torch.empty(cap, dtype=torch.int64, device=dev)
+    j_ids = torch.empty(cap, dtype=torch.int64, device=dev)
+    mconf = torch.empty(cap, dtype=torch.float32, device=dev)
+    cnt = torch.zeros(2, dtype=torch.int32, device=dev)
+    conf = torch.empty(n, L, S, dtype=torch.float32, device=dev) if materialize_conf else None
+
+    def m8(m, length):
+        if m is None:
+            return None
+        m = m.reshape(n, length)
+        return (m if m.dtype in (torch.bool, torch.uint8) else (m != 0)).contiguous()
+
+    ma, mb = m8(mask_a, L), m8(mask_b, S)
+    vhw = None if valid_hw is None else valid_hw.to(device=dev, dtype=torch.int32).contiguous()
+    h0, w0 = (int(grid_a[0]), int(grid_a[1])) if grid_a is not None else (1, L)
+    h1, w1 = int(grid_b[0]), int(grid_b[1])
+    st = l.opb200_coarse_match(_lib.ptr(feat_a), _lib.ptr(feat_b), _lib.ptr(ma), _lib.ptr(mb), int(mask_fill), n, L, S, C,
+                               ctypes.c_float(scale), ctypes.c_float(thr), int(border_rm), int(border_mode), h0, w0, h1, w1,
+                               _lib.ptr(vhw), _lib.ptr(b_ids), _lib.ptr(i_ids), _lib.ptr(j_ids), _lib.ptr(mconf), cap,
+                               _lib.ptr(cnt), _lib.ptr(conf), _lib.ptr(ws), _c_sz(ws.numel()), int(precision),
+                               _lib.stream_ptr())
+    _lib.check(st, "opb200_coarse_match")
+    m, overflow = cnt.tolist()
+    if overflow:
+        import os
+        if os.environ.get("OPB200_DEBUG_OVERFLOW"):
+            print("DEBUG overflow: count", m, "cap", cap)
+            return b_ids[:min(m, cap)], i_ids[:min(m, cap)], j_ids[:min(m, cap)], mconf[:min(m, cap)], conf
+        raise _lib.Opb200Error("coarse_match: candidate/match buffer overflow (internal capacity bound violated)")
+    return b_ids[:m], i_ids[:m], j_ids[:m], mconf[:m], conf
