@@ -88,6 +88,25 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
                         int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity, int* count_and_overflow,
                         float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, void* stream);
 
+/* ---- Fine level --------------------------------------------------------------------------------------
+ * opb200_fine_gather replaces F.unfold + index in FinePreprocess (OnePosePlus fine_preprocess.py:43-53,
+ * LoFTR fine_preprocess.py:40-47): out[m, wy*W+wx, c] = feat[b_ids[m], c, 4r - W/2 + wy, 4c - W/2 + wx]
+ * for coarse cell cell_ids[m] = r*Wc + c (zero outside the map).  feat element (n,c,y,x) is read from
+ * feat[n*sn + c*sc + y*sh + x*sw] (any memory format; channels-last is the coalesced one).
+ * Out-of-range ids (the reference raises IndexError) set *err_flag = 1 and produce zeros. */
+int opb200_fine_gather(const float* feat, int64_t sn, int64_t sc, int64_t sh, int64_t sw, int n_batch, int Cf, int Hf,
+                       int Wf, const int64_t* b_ids, const int64_t* cell_ids, int M, int W, int stride, int Hc, int Wc,
+                       float* out, int* err_flag, void* stream);
+/* out[m, c] = src[b_ids[m]*sn + c*sc + i_ids[m]*sl]: descriptors3d_db.permute(0,2,1)[b_ids, i_ids]
+ * (OnePosePlus fine_preprocess.py:44,51). */
+int opb200_gather_rows(const float* src, int64_t sn, int64_t sc, int64_t sl, int n_batch, int C, int L,
+                       const int64_t* b_ids, const int64_t* i_ids, int M, float* out, int* err_flag, void* stream);
+/* FineMatching._s2d_heatmap (OnePosePlus fine_matching.py:78-94; LoFTR fine_matching.py:43-57):
+ * sim = win[m] . q[m]; heat = softmax(sim / sqrt(Cf)); expec_f[m] = (E[x], E[y], sqrt(var_x) + sqrt(var_y))
+ * over the kornia-0.4.1 normalised W x W grid.  q row m starts at q + m*q_stride. */
+int opb200_fine_match(const float* q, int64_t q_stride, const float* win, int M, int W, int Cf, float* expec_f,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif

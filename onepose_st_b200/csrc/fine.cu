@@ -1,0 +1,184 @@
+// Fine level: window gather (FinePreprocess) and correlation + softmax expectation (FineMatching).
+//
+// Replaces
+//   FinePreprocess.forward     src/models/OnePosePlus/loftr_module/fine_preprocess.py:32-55
+//                              submodules/LoFTR/src/loftr/loftr_module/fine_preprocess.py:29-59
+//   FineMatching.forward       src/models/OnePosePlus/utils/fine_matching.py:28-110
+//                              submodules/LoFTR/src/loftr/utils/fine_matching.py:15-74
+//
+// The reference unfolds ALL H_c*W_c windows of the fine map (52 MB at W=5, 170 MB at W=9 per image) and
+// then indexes M of them; here the M windows are gathered directly: algorithmic traffic per match is
+// 4*Cf*(WW+1) bytes in + the same out.  Both kernels are HBM-bound (0.5 flop/B).
+#include "host.cuh"
+#include "../../include/opb200.h"
+
+namespace opb {
+
+// one block per match, one thread per channel; coalesced when the feature map is channels-last (sc == 1)
+__global__ void fine_gather_kernel(const float* __restrict__ feat, long long sn, long long sc, long long sh, long long sw,
+                                   int N, int Cf, int Hf, int Wf, const long long* __restrict__ b_ids,
+                                   const long long* __restrict__ cell_ids, int M, int W, int stride, int Wc, int n_cells,
+                                   float* __restrict__ out, int* __restrict__ err_flag) {
+  const int m = blockIdx.x;
+  if (m >= M) return;
+  const long long b = b_ids[m], cell = cell_ids[m];
+  const int WW = W * W;
+  float* o = out + static_cast<long long>(m) * WW * Cf;
+  if (b < 0 || b >= N || cell < 0 || cell >= n_cells) {  // the reference raises IndexError here
+    if (threadIdx.x == 0) atomicExch(err_flag, 1);
+    for (int idx = threadIdx.x; idx < WW * Cf; idx += blockDim.x) o[idx] = 0.f;
+    return;
+  }
+  const int r = static_cast<int>(cell) / Wc, c = static_cast<int>(cell) % Wc;
+  const int y0 = r * stride - W / 2, x0 = c * stride - W / 2;
+  const float* fb = feat + b * sn;
+  for (int ch = threadIdx.x; ch < Cf; ch += blockDim.x) {
+    for (int wy = 0; wy < W; ++wy) {
+      const int y = y0 + wy;
+      for (int wx = 0; wx < W; ++wx) {
+        const int x = x0 + wx;
+        float v = 0.f;  // F.unfold zero padding
+        if (y >= 0 && y < Hf && x >= 0 && x < Wf) v = __ldg(fb + ch * sc + y * sh + x * sw);
+        o[(wy * W + wx) * Cf + ch] = v;
+      }
+    }
+  }
+}
+
+// out[m, c] = src[b_ids[m]*sn + c*sc + i_ids[m]*sl]   (descriptors3d_db.permute(0,2,1)[b_ids, i_ids])
+__global__ void gather_rows_kernel(const float* __restrict__ src, long long sn, long long sc, long long sl, int N, int C,
+                                   int L, const long long* __restrict__ b_ids, const long long* __restrict__ i_ids, int M,
+                                   float* __restrict__ out, int* __restrict__ err_flag) {
+  const int m = blockIdx.x;
+  if (m >= M) return;
+  const long long b = b_ids[m], i = i_ids[m];
+  const bool bad = b < 0 || b >= N || i < 0 || i >= L;
+  if (bad && threadIdx.x == 0) atomicExch(err_flag, 1);
+  for (int c = threadIdx.x; c < C; c += blockDim.x)
+    out[static_cast<long long>(m) * C + c] = bad ? 0.f : __ldg(src + b * sn + c * sc + i * sl);
+}
+
+// one block (4 warps) per match: warp w correlates window rows w, w+4, ... with the query vector
+// (float4 per lane, Cf = 128), then warp 0 does the softmax expectation over the WW scores.
+template <int CF>
+__global__ void __launch_bounds__(128) fine_match_kernel(const float* __restrict__ q, long long q_stride,
+                                                         const float* __restrict__ win, int M, int W,
+                                                         float* __restrict__ expec_f) {
+  static_assert(CF == 128, "one float4 per lane");
+  const int m = blockIdx.x;
+  if (m >= M) return;
+  __shared__ float sim[128];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int WW = W * W;
+  const float4 qv = reinterpret_cast<const float4*>(q + m * q_stride)[lane];
+  const float4* wbase = reinterpret_cast<const float4*>(win + static_cast<long long>(m) * WW * CF);
+  for (int r = warp; r < WW; r += 4) {
+    const float4 wv = __ldg(wbase + r * (CF / 4) + lane);
+    float d = qv.x * wv.x;
+    d = fmaf(qv.y, wv.y, d);
+    d = fmaf(qv.z, wv.z, d);
+    d = fmaf(qv.w, wv.w, d);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+    if (lane == 0) sim[r] = d;
+  }
+  __syncthreads();
+  if (warp != 0) return;
+  const float temp = 1.0f / sqrtf(static_cast<float>(CF));  // softmax_temp = 1 / C**.5
+  float x[4];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int r = lane + 32 * k;
+    x[k] = r < WW ? sim[r] * temp : -INFINITY;
+    mx = fmaxf(mx, x[k]);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float e[4], sum = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    e[k] = (lane + 32 * k) < WW ? expf(x[k] - mx) : 0.f;
+    sum += e[k];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  // grid = (linspace(0, W-1, W) / (W-1) - 0.5) * 2, (x, y) order (kornia 0.4.1 create_meshgrid)
+  float ex = 0.f, ey = 0.f, exx = 0.f, eyy = 0.f;
+  const float wm1 = static_cast<float>(W - 1);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int r = lane + 32 * k;
+    if (r < WW) {
+      const float p = e[k] / sum;
+      const float gx = (static_cast<float>(r % W) / wm1 - 0.5f) * 2.f;
+      const float gy = (static_cast<float>(r / W) / wm1 - 0.5f) * 2.f;
+      ex = fmaf(gx, p, ex);
+      ey = fmaf(gy, p, ey);
+      exx = fmaf(gx * gx, p, exx);
+      eyy = fmaf(gy * gy, p, eyy);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ex += __shfl_xor_sync(0xffffffffu, ex, o);
+    ey += __shfl_xor_sync(0xffffffffu, ey, o);
+    exx += __shfl_xor_sync(0xffffffffu, exx, o);
+    eyy += __shfl_xor_sync(0xffffffffu, eyy, o);
+  }
+  if (lane == 0) {
+    const float vx = fmaxf(exx - ex * ex, 1e-10f), vy = fmaxf(eyy - ey * ey, 1e-10f);
+    expec_f[3 * m + 0] = ex;
+    expec_f[3 * m + 1] = ey;
+    expec_f[3 * m + 2] = sqrtf(vx) + sqrtf(vy);
+  }
+}
+
+}  // namespace opb
+
+using namespace opb;
+
+extern "C" {
+
+int opb200_fine_gather(const float* feat, int64_t sn, int64_t sc, int64_t sh, int64_t sw, int n_batch, int Cf, int Hf,
+                       int Wf, const int64_t* b_ids, const int64_t* cell_ids, int M, int W, int stride, int Hc, int Wc,
+                       float* out, int* err_flag, void* stream_) {
+  if (int r = check_device()) return r;
+  if (M <= 0) return OPB_OK;
+  OPB_CHECK_ARG(feat && b_ids && cell_ids && out && err_flag, "null pointer");
+  OPB_CHECK_ARG(W >= 1 && (W & 1) == 1 && W <= 11, "window size must be odd and <= 11");
+  OPB_CHECK_ARG(stride >= 1 && Hc >= 1 && Wc >= 1, "bad grid");
+  fine_gather_kernel<<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
+      feat, sn, sc, sh, sw, n_batch, Cf, Hf, Wf, reinterpret_cast<const long long*>(b_ids),
+      reinterpret_cast<const long long*>(cell_ids), M, W, stride, Wc, Hc * Wc, out, err_flag);
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_gather_rows(const float* src, int64_t sn, int64_t sc, int64_t sl, int n_batch, int C, int L,
+                       const int64_t* b_ids, const int64_t* i_ids, int M, float* out, int* err_flag, void* stream_) {
+  if (int r = check_device()) return r;
+  if (M <= 0) return OPB_OK;
+  OPB_CHECK_ARG(src && b_ids && i_ids && out && err_flag, "null pointer");
+  gather_rows_kernel<<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
+      src, sn, sc, sl, n_batch, C, L, reinterpret_cast<const long long*>(b_ids), reinterpret_cast<const long long*>(i_ids), M,
+      out, err_flag);
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_fine_match(const float* q, int64_t q_stride, const float* win, int M, int W, int Cf, float* expec_f,
+                      void* stream_) {
+  if (int r = check_device()) return r;
+  if (M <= 0) return OPB_OK;
+  OPB_CHECK_ARG(q && win && expec_f, "null pointer");
+  OPB_CHECK_ARG(Cf == 128, "fine feature dim must be 128");
+  OPB_CHECK_ARG(W >= 3 && (W & 1) == 1 && W * W <= 128, "window size must be odd with W*W <= 128");
+  OPB_CHECK_ARG(q_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(q) & 15) == 0 && (reinterpret_cast<uintptr_t>(win) & 15) == 0,
+                "q / win must be 16-byte aligned");
+  fine_match_kernel<128><<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(q, q_stride, win, M, W, expec_f);
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+}  // extern "C"

@@ -162,3 +162,60 @@ def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, th
             return b_ids[:min(m, cap)], i_ids[:min(m, cap)], j_ids[:min(m, cap)], mconf[:min(m, cap)], conf
         raise _lib.Opb200Error("coarse_match: candidate/match buffer overflow (internal capacity bound violated)")
     return b_ids[:m], i_ids[:m], j_ids[:m], mconf[:m], conf
+
+
+def _err_flag(dev) -> torch.Tensor:
+    return torch.zeros(1, dtype=torch.int32, device=dev)
+
+
+def fine_gather(feat: torch.Tensor, b_ids: torch.Tensor, cell_ids: torch.Tensor, W: int, stride: int, hc: int, wc: int,
+                err_flag: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """feat [N,Cf,Hf,Wf] (any memory format) -> windows [M, W*W, Cf] of the coarse cells cell_ids."""
+    _need_cuda(feat, b_ids, cell_ids)
+    feat = _f32(feat)
+    n, cf, hf, wf = feat.shape
+    m = int(b_ids.shape[0])
+    out = torch.empty(m, W * W, cf, dtype=torch.float32, device=feat.device)
+    if m == 0:
+        return out
+    flag = err_flag if err_flag is not None else _err_flag(feat.device)
+    b_ids, cell_ids = b_ids.long().contiguous(), cell_ids.long().contiguous()
+    st = _lib.lib().opb200_fine_gather(_lib.ptr(feat), _c_i64(feat.stride(0)), _c_i64(feat.stride(1)), _c_i64(feat.stride(2)),
+                                       _c_i64(feat.stride(3)), n, cf, hf, wf, _lib.ptr(b_ids), _lib.ptr(cell_ids), m, int(W),
+                                       int(stride), int(hc), int(wc), _lib.ptr(out), _lib.ptr(flag), _lib.stream_ptr())
+    _lib.check(st, "opb200_fine_gather")
+    return out
+
+
+def gather_rows(src_ncl: torch.Tensor, b_ids: torch.Tensor, i_ids: torch.Tensor,
+                err_flag: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """src [N, C, L] -> [M, C] rows src[b, :, i]."""
+    _need_cuda(src_ncl, b_ids, i_ids)
+    src = _f32(src_ncl)
+    n, c, L = src.shape
+    m = int(b_ids.shape[0])
+    out = torch.empty(m, c, dtype=torch.float32, device=src.device)
+    if m == 0:
+        return out
+    flag = err_flag if err_flag is not None else _err_flag(src.device)
+    b_ids, i_ids = b_ids.long().contiguous(), i_ids.long().contiguous()
+    st = _lib.lib().opb200_gather_rows(_lib.ptr(src), _c_i64(src.stride(0)), _c_i64(src.stride(1)), _c_i64(src.stride(2)), n, c, L,
+                                       _lib.ptr(b_ids), _lib.ptr(i_ids), m, _lib.ptr(out), _lib.ptr(flag), _lib.stream_ptr())
+    _lib.check(st, "opb200_gather_rows")
+    return out
+
+
+def fine_match(q: torch.Tensor, win: torch.Tensor) -> torch.Tensor:
+    """q [M, Cf] (row stride free), win [M, WW, Cf] contiguous -> expec_f [M, 3]."""
+    _need_cuda(q, win)
+    q, win = _f32(q), _f32(win).contiguous()
+    m, ww, cf = win.shape
+    w = int(round(ww ** 0.5))
+    if q.stride(1) != 1:
+        q = q.contiguous()
+    out = torch.empty(m, 3, dtype=torch.float32, device=win.device)
+    if m == 0:
+        return out
+    st = _lib.lib().opb200_fine_match(_lib.ptr(q), _c_i64(q.stride(0)), _lib.ptr(win), m, w, cf, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "opb200_fine_match")
+    return out
