@@ -107,6 +107,13 @@ int opb200_gather_rows(const float* src, int64_t sn, int64_t sc, int64_t sl, int
 int opb200_fine_match(const float* q, int64_t q_stride, const float* win, int M, int W, int Cf, float* expec_f,
                       void* stream);
 
+/* ---- Standalone LinearAttention.forward (linear_attention.py:29-61 / LoFTR :20-47) -----------------
+ * q [n, L, H, D], k, v [n, S, H, D] fp32 contiguous; masks nullable bytes [n, L] / [n, S]; out [n, L, H, D]. */
+size_t opb200_linear_attention_workspace_bytes(int n_batch, int S, int H, int D);
+int opb200_linear_attention(const float* q, const float* k, const float* v, const uint8_t* q_mask,
+                            const uint8_t* kv_mask, int n_batch, int L, int S, int H, int D, float eps, float* out,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,215 @@
+"""Building blocks shared by the OnePosePlus (2D-3D) and LoFTR (2D-2D) drop-in matchers.
+
+Everything that is a hot-path operator calls the sm_100a C-ABI through ``ops``; the modules here only
+hold parameters under the reference's names (so reference checkpoints load with ``strict=True``),
+cache packed weights, and move pointers around.  The ResNet-FPN backbone stays PyTorch/cuDNN
+(not one of north_star's kernels; first of the "next" rows in 8f).
+"""
+import math
+from typing import Optional, Sequence
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+
+
+# --------------------------------------------------------------------------------------------------
+# Backbone: ResNetFPN_8_2 (reference: src/models/OnePosePlus/backbone/resnet.py:85-164 and
+# submodules/LoFTR/src/loftr/backbone/resnet_fpn.py:43-118).  Same parameter names, PyTorch/cuDNN math.
+# --------------------------------------------------------------------------------------------------
+class BasicBlock(nn.Module):
+    def __init__(self, cin: int, cout: int, stride: int = 1):
+        super().__init__()
+        self.conv1 = nn.Conv2d(cin, cout, 3, stride, 1, bias=False)
+        self.conv2 = nn.Conv2d(cout, cout, 3, 1, 1, bias=False)
+        self.bn1 = nn.BatchNorm2d(cout)
+        self.bn2 = nn.BatchNorm2d(cout)
+        self.relu = nn.ReLU(inplace=True)
+        self.downsample = None
+        if stride != 1:
+            self.downsample = nn.Sequential(nn.Conv2d(cin, cout, 1, stride, 0, bias=False), nn.BatchNorm2d(cout))
+
+    def forward(self, x):
+        y = self.bn2(self.conv2(self.relu(self.bn1(self.conv1(x)))))
+        if self.downsample is not None:
+            x = self.downsample(x)
+        return self.relu(x + y)
+
+
+class ResNetFPN_8_2(nn.Module):
+    """ResNet + FPN with 1/8 (coarse) and 1/2 (fine) outputs.  ``forward`` returns (coarse, fine)."""
+
+    def __init__(self, config):
+        super().__init__()
+        if config.get("block_type", "BasicBlock") != "BasicBlock":
+            raise NotImplementedError("only BasicBlock backbones are supported")
+        d0 = config["initial_dim"]
+        d1, d2, d3 = config["block_dims"]
+        self.conv1 = nn.Conv2d(1, d0, 7, 2, 3, bias=False)
+        self.bn1 = nn.BatchNorm2d(d0)
+        self.relu = nn.ReLU(inplace=True)
+        self.layer1 = nn.Sequential(BasicBlock(d0, d1, 1), BasicBlock(d1, d1, 1))
+        self.layer2 = nn.Sequential(BasicBlock(d1, d2, 2), BasicBlock(d2, d2, 1))
+        self.layer3 = nn.Sequential(BasicBlock(d2, d3, 2), BasicBlock(d3, d3, 1))
+        self.layer3_outconv = nn.Conv2d(d3, d3, 1, bias=False)
+        self.layer2_outconv = nn.Conv2d(d2, d3, 1, bias=False)
+        self.layer2_outconv2 = self._head(d3, d3, d2)
+        self.layer1_outconv = nn.Conv2d(d1, d2, 1, bias=False)
+        self.layer1_outconv2 = self._head(d2, d2, d1)
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+
+    @staticmethod
+    def _head(cin, cmid, cout):
+        return nn.Sequential(nn.Conv2d(cin, cmid, 3, 1, 1, bias=False), nn.BatchNorm2d(cmid), nn.LeakyReLU(),
+                             nn.Conv2d(cmid, cout, 3, 1, 1, bias=False))
+
+    def forward(self, x):
+        x1 = self.layer1(self.relu(self.bn1(self.conv1(x))))
+        x2 = self.layer2(x1)
+        x3 = self.layer3(x2)
+        c3 = self.layer3_outconv(x3)
+        up = lambda t: F.interpolate(t, scale_factor=2.0, mode="bilinear", align_corners=True)
+        c2 = self.layer2_outconv2(self.layer2_outconv(x2) + up(c3))
+        c1 = self.layer1_outconv2(self.layer1_outconv(x1) + up(c2))
+        return c3, c1
+
+
+# --------------------------------------------------------------------------------------------------
+# Sine position encoding (reference: OnePosePlus utils/position_encoding.py:13-42; LoFTR :11-42).
+# ``pe`` stays a non-persistent buffer of the reference's shape; a token-major [H*W, C] table of the
+# current feature-map size is cached and added inside the transformer's stage-in kernel.
+# --------------------------------------------------------------------------------------------------
+class PositionEncodingSine(nn.Module):
+    def __init__(self, d_model, max_shape=(256, 256), temp_bug_fix=False):
+        super().__init__()
+        h, w = tuple(max_shape)
+        ypos = torch.arange(1, h + 1, dtype=torch.float32).view(1, h, 1).expand(1, h, w)
+        xpos = torch.arange(1, w + 1, dtype=torch.float32).view(1, 1, w).expand(1, h, w)
+        # NB: without temp_bug_fix the reference evaluates -log(1e4)/d_model//2 == -1.0 (floor division)
+        coef = (-math.log(10000.0) / (d_model // 2)) if temp_bug_fix else (-math.log(10000.0) / d_model // 2)
+        div = torch.exp(torch.arange(0, d_model // 2, 2).float() * coef)[:, None, None]
+        pe = torch.zeros(d_model, h, w)
+        pe[0::4], pe[1::4] = torch.sin(xpos * div), torch.cos(xpos * div)
+        pe[2::4], pe[3::4] = torch.sin(ypos * div), torch.cos(ypos * div)
+        self.register_buffer("pe", pe.unsqueeze(0), persistent=False)
+        self._tables = {}
+
+    def forward(self, x):
+        return x + self.pe[:, :, : x.size(2), : x.size(3)]
+
+    def token_table(self, h: int, w: int) -> torch.Tensor:
+        """[h*w, C] fp32 table equal to ``pe[0, :, :h, :w]`` rearranged 'c h w -> (h w) c'."""
+        key = (h, w, self.pe.device)
+        t = self._tables.get(key)
+        if t is None:
+            t = self.pe[0, :, :h, :w].reshape(self.pe.shape[1], h * w).t().contiguous()
+            self._tables = {key: t}
+        return t
+
+
+# --------------------------------------------------------------------------------------------------
+# Encoder layer parameter holder + transformer base
+# --------------------------------------------------------------------------------------------------
+class LinearAttention(nn.Module):
+    """elu+1 linear attention (reference: loftr_module/linear_attention.py:22-61).  Inside the encoder
+    stack the attention is fused into the tcgen05 kernels; this standalone module serves callers that
+    use the operator on its own."""
+
+    def __init__(self, d_head=None, kernel_fn="elu + 1", eps=1e-6, redraw_interval=2, d_kernel=None):
+        super().__init__()
+        if kernel_fn not in (None, "elu + 1"):
+            raise ValueError(f"unsupported kernel_fn {kernel_fn!r}")
+        self.eps = eps
+
+    def forward(self, queries, keys, values, q_mask=None, kv_mask=None):
+        return ops.linear_attention(queries, keys, values, q_mask, kv_mask, self.eps)
+
+
+class LoFTREncoderLayer(nn.Module):
+    """Holds q/k/v/merge/mlp/norm parameters under the reference's names
+    (transformer.py:10-63) and packs them for the kernels on demand."""
+
+    def __init__(self, d_model, nhead, dropout=0.0, attention="linear", kernel_fn="elu + 1", redraw_interval=1,
+                 d_kernel=None, rezero=None, norm_method="layernorm"):
+        super().__init__()
+        if attention != "linear":
+            raise NotImplementedError("only attention='linear' is implemented (FullAttention is never configured)")
+        if kernel_fn != "elu + 1":
+            raise ValueError(f"unsupported kernel_fn {kernel_fn!r}")
+        if norm_method != "layernorm":
+            raise NotImplementedError("encoder layers support norm_method='layernorm' only")
+        if rezero is not None:
+            raise NotImplementedError("rezero is not supported")
+        if dropout not in (0, 0.0, None):
+            raise NotImplementedError("inference path: dropout must be 0")
+        self.dim, self.nhead = d_model // nhead, nhead
+        self.q_proj = nn.Linear(d_model, d_model, bias=False)
+        self.k_proj = nn.Linear(d_model, d_model, bias=False)
+        self.v_proj = nn.Linear(d_model, d_model, bias=False)
+        self.attention = LinearAttention(self.dim)
+        self.merge = nn.Linear(d_model, d_model, bias=False)
+        self.mlp = nn.Sequential(nn.Linear(2 * d_model, 2 * d_model, bias=False), nn.ReLU(True),
+                                 nn.Linear(2 * d_model, d_model, bias=False))
+        self.norm1 = nn.LayerNorm(d_model)
+        self.norm2 = nn.LayerNorm(d_model)
+        self._packed = None
+        self._packed_key = None
+
+    def _params(self):
+        return (self.q_proj.weight, self.k_proj.weight, self.v_proj.weight, self.merge.weight, self.mlp[0].weight,
+                self.mlp[2].weight, self.norm1.weight, self.norm1.bias, self.norm2.weight, self.norm2.bias)
+
+    def packed(self) -> torch.Tensor:
+        ps = self._params()
+        key = tuple((p.data_ptr(), p._version, str(p.device)) for p in ps)
+        if self._packed is None or key != self._packed_key:
+            self._packed = ops.pack_layer_weights(*ps)
+            self._packed_key = key
+        return self._packed
+
+    def __getstate__(self):  # the packed buffer is a cache: rebuild after unpickling (Ray ships models by pickle)
+        st = self.__dict__.copy()
+        st["_packed"], st["_packed_key"] = None, None
+        return st
+
+    def forward(self, x, source, x_mask=None, source_mask=None):
+        """Single layer call x <- layer(x, source): a one-step sequential cross schedule whose second
+        half (the update of ``source``) is discarded."""
+        d_model = x.shape[-1]
+        out, _ = ops.transformer([self.packed()], [1], 1, d_model, self.nhead, x, source, mask0=x_mask, mask1=source_mask,
+                                 big_groups=(d_model == 256))
+        return out
+
+
+class _TransformerBase(nn.Module):
+    schedule = 0  # 0: OnePosePlus (simultaneous), 1: LoFTR (sequential cross)
+
+    def _build(self, d_model: int, nhead: int, layer_names: Sequence[str], **layer_kw):
+        self.d_model, self.nhead = d_model, nhead
+        self.layer_names = list(layer_names)
+        for n in self.layer_names:
+            if n not in ("self", "cross"):
+                raise NotImplementedError(f"unknown layer name {n!r}")
+        self.layers = nn.ModuleList([LoFTREncoderLayer(d_model, nhead, **layer_kw) for _ in self.layer_names])
+        for p in self.parameters():
+            if p.dim() > 1:
+                nn.init.xavier_uniform_(p)
+
+    def _run(self, x0, x1, mask0=None, mask1=None, add0=None, add1=None, upto: Optional[int] = None):
+        layers = list(self.layers)[:upto]
+        kinds = [0 if n == "self" else 1 for n in self.layer_names[:upto]]
+        return ops.transformer([l.packed() for l in layers], kinds, self.schedule, self.d_model, self.nhead, x0, x1,
+                               add0=add0, add1=add1, mask0=mask0, mask1=mask1, big_groups=(self.d_model == 256),
+                               precision=getattr(self, "precision", ops.PREC_BF16X3))
+
+
+# --------------------------------------------------------------------------------------------------
+# Fine matching core shared by both variants
+# --------------------------------------------------------------------------------------------------
+def fine_expectation(query_vec: torch.Tensor, win: torch.Tensor) -> torch.Tensor:
+    """query_vec [M, Cf] (strided view allowed), win [M, WW, Cf] -> expec_f [M,3] = (x, y, std)."""
+    return ops.fine_match(query_vec, win)

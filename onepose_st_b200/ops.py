@@ -219,3 +219,27 @@ def fine_match(q: torch.Tensor, win: torch.Tensor) -> torch.Tensor:
     st = _lib.lib().opb200_fine_match(_lib.ptr(q), _c_i64(q.stride(0)), _lib.ptr(win), m, w, cf, _lib.ptr(out), _lib.stream_ptr())
     _lib.check(st, "opb200_fine_match")
     return out
+
+
+def linear_attention(q, k, v, q_mask=None, kv_mask=None, eps: float = 1e-6) -> torch.Tensor:
+    """Standalone elu+1 linear attention: q [N,L,H,D], k/v [N,S,H,D] -> [N,L,H,D]."""
+    _need_cuda(q, k, v)
+    q, k, v = _f32(q).contiguous(), _f32(k).contiguous(), _f32(v).contiguous()
+    n, L, H, D = q.shape
+    S = k.shape[1]
+    l = _lib.lib()
+    l.opb200_linear_attention_workspace_bytes.restype = _c_sz
+    ws = workspaces.get(q.device, "linattn", int(l.opb200_linear_attention_workspace_bytes(n, S, H, D)))
+    out = torch.empty_like(q)
+
+    def m8(m, length):
+        if m is None:
+            return None
+        m = m.reshape(n, length)
+        return (m if m.dtype in (torch.bool, torch.uint8) else (m != 0)).contiguous()
+
+    qm, km = m8(q_mask, L), m8(kv_mask, S)
+    st = l.opb200_linear_attention(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(qm), _lib.ptr(km), n, L, S, H, D,
+                                   ctypes.c_float(eps), _lib.ptr(out), _lib.ptr(ws), _c_sz(ws.numel()), _lib.stream_ptr())
+    _lib.check(st, "opb200_linear_attention")
+    return out
