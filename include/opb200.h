@@ -32,6 +32,8 @@ extern "C" {
 
 int opb200_version(void);
 const char* opb200_last_error(void);
+/* Number of CUDA kernels this library has launched in this process (bench.py's gpu_launches evidence). */
+long long opb200_launch_count(void);
 
 /* fp32 matrix with element (r,c) at x[r*stride_r + c*stride_c] -> bf16 hi/lo planes [rows, cols]
  * (lo and f32_copy nullable).  Operand preparation for every tensor-core product below. */

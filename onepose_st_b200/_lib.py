@@ -46,6 +46,27 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
+def declared_symbols():
+    """Every entry point include/opb200.h declares (parsed from the header)."""
+    import re
+    hdr = os.path.join(os.path.dirname(_HERE), "include", "opb200.h")
+    with open(hdr) as f:
+        text = f.read()
+    return sorted(set(re.findall(r"\b(opb200_[a-z0-9_]+)\s*\(", text)))
+
+
+def missing_symbols():
+    """Declared-but-not-exported symbols of the built library (loads it; launches nothing)."""
+    l = lib()
+    return [s for s in declared_symbols() if not hasattr(l, s)]
+
+
+def launch_count() -> int:
+    l = lib()
+    l.opb200_launch_count.restype = ctypes.c_longlong
+    return int(l.opb200_launch_count())
+
+
 def check(status: int, what: str) -> None:
     if status != 0:
         msg = lib().opb200_last_error()

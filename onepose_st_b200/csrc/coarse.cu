@@ -457,6 +457,7 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
   OPB_CHECK_CUDA(cudaMemsetAsync(w.rowj, 0x7f, static_cast<size_t>(N) * L * 4, stream));  // kNoMatch
   const int m_tiles = N * (Lp / BLOCK_M), n_tiles = Sp / SIM_BN;
   fill_sim_row_base<<<(m_tiles + 255) / 256, 256, 0, stream>>>(w.row_base, Lp / BLOCK_M, N, Sp);
+  count_launch();
 
   PlanBuilder pb;
   pb.add_a(w.a_hi, static_cast<uint64_t>(N) * Lp, C, C, 0);
@@ -487,6 +488,7 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
     const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
     merge_stats_kernel<<<static_cast<unsigned>((nr + nc + 255) / 256), 256, 0, stream>>>(w.rowpart, n_tiles, nr, w.colpart,
                                                                                         Lp / BLOCK_M, nc, w.lse_row, w.lse_col);
+    count_launch();
   }
   {
     const float log2_thr_lo = log2f(thr) - 1e-3f;
@@ -505,6 +507,7 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
   compact_kernel<<<1, 1024, 0, stream>>>(w.rowj, w.rowmax, N * L, L, reinterpret_cast<long long*>(b_ids),
                                          reinterpret_cast<long long*>(i_ids), reinterpret_cast<long long*>(j_ids), mconf, capacity,
                                          count_and_overflow, w.counters, w.cand_cap, count_and_overflow + 1);
+  count_launch(3);
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
 }

@@ -1,5 +1,6 @@
 // Error reporting, device checks, TMA descriptor encoding, operand-preparation kernels and the
 // debug GEMM entry point (used by tests to validate the tcgen05/TMA mainloop in isolation).
+#include <atomic>
 #include <mutex>
 #include "host.cuh"
 #include "../../include/opb200.h"
@@ -9,6 +10,10 @@ namespace opb {
 static thread_local std::string g_last_error;
 void set_last_error(const std::string& msg) { g_last_error = msg; }
 const char* last_error_cstr() { return g_last_error.c_str(); }
+
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
 
 int check_device() {
   int dev = 0;
@@ -124,6 +129,7 @@ int split_planes(const float* x, long long stride_r, long long stride_c, const f
   dim3 grid((cols + 31) / 32, (rows + 31) / 32), block(32, 8);
   split_planes_kernel<<<grid, block, 0, stream>>>(x, stride_r, stride_c, add, add_period_rows > 0 ? add_period_rows : 1,
                                                   rows, cols, hi, lo, f32out, ld_out);
+  count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
 }
@@ -175,6 +181,8 @@ using namespace opb;
 extern "C" {
 
 int opb200_version(void) { return 100; }
+
+long long opb200_launch_count(void) { return opb::launch_count(); }
 
 const char* opb200_last_error(void) { return opb::last_error_cstr(); }
 

@@ -616,6 +616,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       }
       kv_partial_kernel<<<dim3(g.max_chunks, g.G), 256, 0, stream>>>(w.kf, w.vf, gt, sel, w.kv_partial, g.max_chunks);
       kv_pack_kernel<<<dim3(2, g.G), 256, 0, stream>>>(w.kv_partial, gt, sel, g.max_chunks, w.kvb_h, x3 ? w.kvb_l : nullptr);
+      count_launch(2);
       OPB_CHECK_CUDA(cudaGetLastError());
       PlanBuilder pb;
       pb.add_a(w.qh, R, C, C, 0);
@@ -649,6 +650,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
         const int s_row0 = ss == 0 ? 0 : row1, s_len = ss == 0 ? g.len0 : g.len1;
         attn_small_kernel<<<g.N, 128, 0, stream>>>(w.qf, w.kf, w.vf, q_row0, q_len, s_row0, s_len, g.N, 1e-6f, w.aoh,
                                                     x3 ? w.aol : nullptr);
+        count_launch();
       }
       OPB_CHECK_CUDA(cudaGetLastError());
     } else {
@@ -801,6 +803,7 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
       x0, x0_sn, x0_sl, x0_sc, add0, mask0, len0, g.P0, C, 0, w.xf, w.xh, w.xl, w.row_mask);
   copy_in_kernel<<<dim3((C + 31) / 32, (g.P1 + 31) / 32, n_batch), dim3(32, 8), 0, stream>>>(
       x1, x1_sn, x1_sl, x1_sc, add1, mask1, len1, g.P1, C, row1, w.xf, w.xh, w.xl, w.row_mask);
+  count_launch(2 + (big_groups ? 1 : 0));
   if (big_groups)
     fill_row_base_kernel<<<1, 256, 0, stream>>>(w.base_self, w.base_cross, g.tiles0, g.tiles1, n_batch, 2 * 144);
   OPB_CHECK_CUDA(cudaGetLastError());
@@ -826,6 +829,7 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
       w.xf, len0, g.P0, C, 0, out0);
   copy_out_kernel<<<dim3((static_cast<long long>(len1) * C / 4 + threads - 1) / threads, 1, n_batch), threads, 0, stream>>>(
       w.xf, len1, g.P1, C, row1, out1);
+  count_launch(2);
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
 }

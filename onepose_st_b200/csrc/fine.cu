@@ -151,6 +151,7 @@ int opb200_fine_gather(const float* feat, int64_t sn, int64_t sc, int64_t sh, in
   fine_gather_kernel<<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
       feat, sn, sc, sh, sw, n_batch, Cf, Hf, Wf, reinterpret_cast<const long long*>(b_ids),
       reinterpret_cast<const long long*>(cell_ids), M, W, stride, Wc, Hc * Wc, out, err_flag);
+  count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
 }
@@ -163,6 +164,7 @@ int opb200_gather_rows(const float* src, int64_t sn, int64_t sc, int64_t sl, int
   gather_rows_kernel<<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
       src, sn, sc, sl, n_batch, C, L, reinterpret_cast<const long long*>(b_ids), reinterpret_cast<const long long*>(i_ids), M,
       out, err_flag);
+  count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
 }
@@ -177,6 +179,7 @@ int opb200_fine_match(const float* q, int64_t q_stride, const float* win, int M,
   OPB_CHECK_ARG(q_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(q) & 15) == 0 && (reinterpret_cast<uintptr_t>(win) & 15) == 0,
                 "q / win must be 16-byte aligned");
   fine_match_kernel<128><<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(q, q_stride, win, M, W, expec_f);
+  count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
 }

@@ -38,6 +38,7 @@ void set_last_error(const std::string& msg);
     }                                                                                         \
   } while (0)
 
+void count_launch(int n = 1);  // bumps the counter opb200_launch_count() reports
 int check_device();  // OPB_OK iff the current device is compute capability 10.x
 int num_sms();
 
@@ -98,6 +99,7 @@ int launch_gemm(const GemmPlan& plan, const typename Epi::Params& ep, cudaStream
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (plan.num_tiles < grid) grid = plan.num_tiles;
   kern<<<grid, 64 + 32 * NUM_EPI_WARPS, smem, stream>>>(plan, ep);
+  count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
 }

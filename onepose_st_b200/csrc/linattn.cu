@@ -120,6 +120,7 @@ int opb200_linear_attention(const float* q, const float* k, const float* v, cons
   la_kv_kernel<<<dim3(chunks, H, n_batch), 256, 0, stream>>>(k, v, kv_mask, S, H, D, chunks, partial);
   la_reduce_kernel<<<dim3(H, n_batch), 256, 0, stream>>>(partial, D, chunks, kv);
   la_apply_kernel<<<dim3((L + 127) / 128, H, n_batch), 128, (D * D + D) * 4, stream>>>(q, q_mask, kv, L, S, H, D, eps, out);
+  count_launch(3);
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
 }

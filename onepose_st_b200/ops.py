@@ -43,6 +43,31 @@ class _Workspaces:
 workspaces = _Workspaces()
 
 
+class _Stage:
+    """Optional CUDA-event bracket around one C-ABI call.  ``stage_events`` is None in normal use (zero
+    cost); bench.py sets it to a dict and reads per-op device durations after a synchronize.  Events are
+    recorded on the stream the kernels are launched on (torch's current stream)."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if stage_events is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *a):
+        if stage_events is not None:
+            self.e1.record()
+            stage_events.setdefault(self.name, []).append((self.e0, self.e1))
+        return False
+
+
+stage_events = None
+
+
 def split_planes(x: torch.Tensor):
     """fp32 [rows, cols] (any strides) -> (hi, lo) bf16 planes."""
     _need_cuda(x)
@@ -103,7 +128,8 @@ def transformer(packed_layers: Sequence[torch.Tensor], layer_kinds: Sequence[int
     mk0, mk1 = m8(mask0, len0), m8(mask1, len1)
     a0 = None if add0 is None else _f32(add0).contiguous()
     a1 = None if add1 is None else _f32(add1).contiguous()
-    st = l.opb200_transformer(w_arr, k_arr, nl, int(schedule), d_model, nhead, n, len0, len1, int(big_groups),
+    with _Stage("transformer%d" % d_model):
+        st = l.opb200_transformer(w_arr, k_arr, nl, int(schedule), d_model, nhead, n, len0, len1, int(big_groups),
                               _lib.ptr(x0), _c_i64(x0.stride(0)), _c_i64(x0.stride(1)), _c_i64(x0.stride(2)), _lib.ptr(a0),
                               _lib.ptr(x1), _c_i64(x1.stride(0)), _c_i64(x1.stride(1)), _c_i64(x1.stride(2)), _lib.ptr(a1),
                               _lib.ptr(mk0), _lib.ptr(mk1), _lib.ptr(out0), _lib.ptr(out1), _lib.ptr(ws), _c_sz(ws.numel()),
@@ -148,7 +174,8 @@ def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, th
     vhw = None if valid_hw is None else valid_hw.to(device=dev, dtype=torch.int32).contiguous()
     h0, w0 = (int(grid_a[0]), int(grid_a[1])) if grid_a is not None else (1, L)
     h1, w1 = int(grid_b[0]), int(grid_b[1])
-    st = l.opb200_coarse_match(_lib.ptr(feat_a), _lib.ptr(feat_b), _lib.ptr(ma), _lib.ptr(mb), int(mask_fill), n, L, S, C,
+    with _Stage("coarse_match"):
+        st = l.opb200_coarse_match(_lib.ptr(feat_a), _lib.ptr(feat_b), _lib.ptr(ma), _lib.ptr(mb), int(mask_fill), n, L, S, C,
                                ctypes.c_float(scale), ctypes.c_float(thr), int(border_rm), int(border_mode), h0, w0, h1, w1,
                                _lib.ptr(vhw), _lib.ptr(b_ids), _lib.ptr(i_ids), _lib.ptr(j_ids), _lib.ptr(mconf), cap,
                                _lib.ptr(cnt), _lib.ptr(conf), _lib.ptr(ws), _c_sz(ws.numel()), int(precision),
@@ -180,7 +207,8 @@ def fine_gather(feat: torch.Tensor, b_ids: torch.Tensor, cell_ids: torch.Tensor,
         return out
     flag = err_flag if err_flag is not None else _err_flag(feat.device)
     b_ids, cell_ids = b_ids.long().contiguous(), cell_ids.long().contiguous()
-    st = _lib.lib().opb200_fine_gather(_lib.ptr(feat), _c_i64(feat.stride(0)), _c_i64(feat.stride(1)), _c_i64(feat.stride(2)),
+    with _Stage("fine_gather"):
+        st = _lib.lib().opb200_fine_gather(_lib.ptr(feat), _c_i64(feat.stride(0)), _c_i64(feat.stride(1)), _c_i64(feat.stride(2)),
                                        _c_i64(feat.stride(3)), n, cf, hf, wf, _lib.ptr(b_ids), _lib.ptr(cell_ids), m, int(W),
                                        int(stride), int(hc), int(wc), _lib.ptr(out), _lib.ptr(flag), _lib.stream_ptr())
     _lib.check(st, "opb200_fine_gather")
@@ -216,7 +244,8 @@ def fine_match(q: torch.Tensor, win: torch.Tensor) -> torch.Tensor:
     out = torch.empty(m, 3, dtype=torch.float32, device=win.device)
     if m == 0:
         return out
-    st = _lib.lib().opb200_fine_match(_lib.ptr(q), _c_i64(q.stride(0)), _lib.ptr(win), m, w, cf, _lib.ptr(out), _lib.stream_ptr())
+    with _Stage("fine_match"):
+        st = _lib.lib().opb200_fine_match(_lib.ptr(q), _c_i64(q.stride(0)), _lib.ptr(win), m, w, cf, _lib.ptr(out), _lib.stream_ptr())
     _lib.check(st, "opb200_fine_match")
     return out
 
