@@ -68,6 +68,8 @@ class ResNetFPN_8_2(nn.Module):
                              nn.Conv2d(cmid, cout, 3, 1, 1, bias=False))
 
     def forward(self, x):
+        if x.is_cuda and not self.training and not torch.is_grad_enabled():
+            return self.fused()(x)
         x1 = self.layer1(self.relu(self.bn1(self.conv1(x))))
         x2 = self.layer2(x1)
         x3 = self.layer3(x2)
@@ -75,6 +77,89 @@ class ResNetFPN_8_2(nn.Module):
         up = lambda t: F.interpolate(t, scale_factor=2.0, mode="bilinear", align_corners=True)
         c2 = self.layer2_outconv2(self.layer2_outconv(x2) + up(c3))
         c1 = self.layer1_outconv2(self.layer1_outconv(x1) + up(c2))
+        return c3, c1
+
+    def fused(self) -> "FusedBackbone":
+        """Inference executor (BN folded into the convolutions, channels-last, cuDNN fused
+        conv+bias(+residual)+ReLU); rebuilt whenever a parameter or buffer changes."""
+        key = tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers()))
+        fb = self.__dict__.get("_fused_cache")
+        if fb is None or fb[0] != key:
+            fb = (key, FusedBackbone(self))
+            self.__dict__["_fused_cache"] = fb
+        return fb[1]
+
+    def __getstate__(self):
+        st = self.__dict__.copy()
+        st.pop("_fused_cache", None)
+        return st
+
+
+def _fold_bn(conv: nn.Conv2d, bn: Optional[nn.BatchNorm2d]):
+    """Eval-mode BatchNorm folded into the preceding bias-free convolution: (w', b')."""
+    w = conv.weight.detach().float()
+    if bn is None:
+        b = conv.bias.detach().float() if conv.bias is not None else torch.zeros(w.shape[0], device=w.device)
+        return w.contiguous(memory_format=torch.channels_last), b
+    g = bn.weight.detach().float() / torch.sqrt(bn.running_var.float() + bn.eps)
+    w = w * g[:, None, None, None]
+    b = bn.bias.detach().float() - bn.running_mean.float() * g
+    if conv.bias is not None:
+        b = b + conv.bias.detach().float() * g
+    return w.contiguous(memory_format=torch.channels_last), b.contiguous()
+
+
+class FusedBackbone:
+    """Inference-only executor of a ``ResNetFPN_8_2``: same math with BatchNorm folded into the conv
+    weights, NHWC (channels-last) activations end to end, and cuDNN's fused conv+bias+ReLU /
+    conv+bias+residual+ReLU kernels for the BasicBlocks.  Outputs are channels-last, which is also the
+    layout the transformer stage-in and the fine window gather read coalesced.  (PyTorch/cuDNN library
+    code: the backbone is not one of north_star's hand-written kernels)"""
+
+    def __init__(self, m: "ResNetFPN_8_2"):
+        self.stem = _fold_bn(m.conv1, m.bn1)
+        self.blocks = []
+        for layer in (m.layer1, m.layer2, m.layer3):
+            for blk in layer:
+                ds = _fold_bn(blk.downsample[0], blk.downsample[1]) if blk.downsample is not None else None
+                self.blocks.append((_fold_bn(blk.conv1, blk.bn1), _fold_bn(blk.conv2, blk.bn2), ds, blk.conv1.stride))
+        self.l3_out = _fold_bn(m.layer3_outconv, None)
+        self.l2_out = _fold_bn(m.layer2_outconv, None)
+        self.l1_out = _fold_bn(m.layer1_outconv, None)
+        self.head2 = (_fold_bn(m.layer2_outconv2[0], m.layer2_outconv2[1]), _fold_bn(m.layer2_outconv2[3], None),
+                      m.layer2_outconv2[2].negative_slope)
+        self.head1 = (_fold_bn(m.layer1_outconv2[0], m.layer1_outconv2[1]), _fold_bn(m.layer1_outconv2[3], None),
+                      m.layer1_outconv2[2].negative_slope)
+
+    @staticmethod
+    def _conv_relu(x, wb, stride, padding):
+        return torch.cudnn_convolution_relu(x, wb[0], wb[1], stride, padding, (1, 1), 1)
+
+    def _block(self, x, blk):
+        c1, c2, ds, stride = blk
+        y = self._conv_relu(x, c1, stride, (1, 1))
+        if ds is not None:
+            x = F.conv2d(x, ds[0], ds[1], stride)
+        return torch.cudnn_convolution_add_relu(y, c2[0], x, 1.0, c2[1], (1, 1), (1, 1), (1, 1), 1)
+
+    @staticmethod
+    def _head(x, head):
+        (w0, b0), (w1, b1), slope = head
+        return F.conv2d(F.leaky_relu(F.conv2d(x, w0, b0, 1, 1), slope, inplace=True), w1, None, 1, 1)
+
+    def __call__(self, x):
+        x = x.float().contiguous(memory_format=torch.channels_last)
+        x = self._conv_relu(x, self.stem, (2, 2), (3, 3))
+        feats = []
+        for i, blk in enumerate(self.blocks):
+            x = self._block(x, blk)
+            if i % 2 == 1:
+                feats.append(x)
+        x1, x2, x3 = feats
+        up = lambda t: F.interpolate(t, scale_factor=2.0, mode="bilinear", align_corners=True)
+        c3 = F.conv2d(x3, self.l3_out[0])
+        c2 = self._head(F.conv2d(x2, self.l2_out[0]).add_(up(c3)), self.head2)
+        c1 = self._head(F.conv2d(x1, self.l1_out[0]).add_(up(c2)), self.head1)
         return c3, c1
 
 

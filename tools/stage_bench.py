@@ -1,0 +1,154 @@
+#!/usr/bin/env python
+"""Stage-level timing of the hot-path operators on one GPU (CUDA events, L2 flushed between iterations).
+
+Covers the BASELINE.json configs that are stage-level by nature:
+  coarse       CoarseMatching on planted features (config 3: 30k points x 64x64; also 5k / 8k)
+  transformer  the coarse / fine LoFTR encoder stacks
+  fine         FineMatching sweep W in {5, 9}, M in {2k..20k} (config 5), fp32 error vs an fp64 evaluation
+Each line is JSON with the op's algorithmic work and the fraction of the measured roofline.
+Also the thing to put under ncu: ``ncu -k regex:gemm_kernel ... python tools/stage_bench.py coarse --iters 1``.
+"""
+import argparse
+import json
+import math
+import os
+import sys
+
+import torch
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, REPO)
+from onepose_st_b200 import ops, synthetic  # noqa: E402
+
+
+def peaks():
+    p = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["hbm_gbs"], d["bf16_tflops"], "measured"
+    return 6650.0, 1590.0, "fallback"
+
+
+def time_op(fn, iters, warmup=3):
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for i in range(iters):
+        flush.fill_(i & 0xFF)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def run_coarse(a):
+    hbm, tf, src = peaks()
+    hc = wc = a.grid
+    S, C = hc * wc, 256
+    for L in a.points:
+        f3d, f2d = synthetic.planted_coarse_pair(21, 1, L, S, C, min(3000, L // 2), hc, wc, device="cuda")
+        scale = 1.0 / (C * 0.0801)
+        for mat in ([False, True] if a.materialize else [False]):
+            def fn():
+                return ops.coarse_match(f3d, f2d, scale=scale, thr=0.1, border_rm=2, border_mode=0, grid_a=None,
+                                        grid_b=(hc, wc), materialize_conf=mat, precision=a.precision)
+            ops.stage_events = {}
+            med, best = time_op(fn, a.iters, warmup=0 if a.iters == 1 else 3)
+            evs = ops.stage_events["coarse_match"][-a.iters:]
+            ops.stage_events = None
+            dev_ms = sorted(x.elapsed_time(y) for x, y in evs)[len(evs) // 2]
+            m = fn()[0].numel()
+            flops = 2.0 * L * S * C
+            line = {"op": "coarse_match", "L": L, "S": S, "C": C, "materialize_conf": mat, "precision": a.precision,
+                    "matches": m, "ms_call_incl_host_sync": med, "ms_device": dev_ms,
+                    "algorithmic_gflop": flops / 1e9, "tflops": flops / dev_ms / 1e9,
+                    "frac_tensor": flops / dev_ms / 1e9 / tf, "peak": f"{tf} TFLOP/s bf16 burst ({src})"}
+            if mat:
+                by = 4.0 * L * S + 4.0 * C * (L + S)
+                line.update({"algorithmic_mb": by / 1e6, "gbs": by / dev_ms / 1e6, "frac_hbm": by / dev_ms / 1e6 / hbm})
+            print(json.dumps(line), flush=True)
+
+
+def run_transformer(a):
+    hbm, tf, src = peaks()
+    from onepose_st_b200.onepose_plus import LocalFeatureTransformer
+    cfgs = synthetic.onepose_plus_cfg()
+    torch.manual_seed(0)
+    S = a.grid * a.grid
+    tr = LocalFeatureTransformer(cfgs["loftr_coarse"]).cuda().eval()
+    tr.precision = a.precision
+    for L in a.points:
+        d3 = torch.randn(1, 256, L, device="cuda")
+        d2 = torch.randn(1, S, 256, device="cuda")
+        ops.stage_events = {}
+        med, best = time_op(lambda: tr(d3, d2), a.iters, warmup=0 if a.iters == 1 else 3)
+        evs = ops.stage_events["transformer256"][-a.iters:]
+        ops.stage_events = None
+        dev_ms = sorted(x.elapsed_time(y) for x, y in evs)[len(evs) // 2]
+        flops = 120.0 * (L + S) * 256 * 256
+        print(json.dumps({"op": "loftr_coarse (6 layers x 2 streams)", "L": L, "S": S, "precision": a.precision,
+                          "ms_device": dev_ms, "algorithmic_gflop": flops / 1e9, "tflops": flops / dev_ms / 1e9,
+                          "frac_tensor": flops / dev_ms / 1e9 / tf, "peak": f"{tf} TFLOP/s bf16 burst ({src})"}), flush=True)
+    trf = LocalFeatureTransformer(cfgs["loftr_fine"]).cuda().eval()
+    trf.precision = a.precision
+    for M in a.matches:
+        f3 = torch.randn(M, 128, 1, device="cuda")
+        win = torch.randn(M, 25, 128, device="cuda")
+        ops.stage_events = {}
+        time_op(lambda: trf(f3, win), a.iters, warmup=0 if a.iters == 1 else 3)
+        evs = ops.stage_events["transformer128"][-a.iters:]
+        ops.stage_events = None
+        dev_ms = sorted(x.elapsed_time(y) for x, y in evs)[len(evs) // 2]
+        flops = 17.0e6 * M
+        print(json.dumps({"op": "loftr_fine (W=5)", "M": M, "ms_device": dev_ms, "algorithmic_gflop": flops / 1e9,
+                          "tflops": flops / dev_ms / 1e9}), flush=True)
+
+
+def run_fine(a):
+    hbm, tf, src = peaks()
+    for W in (5, 9):
+        for M in a.matches:
+            q, win, r = synthetic.planted_fine_windows(31, M, W, device="cuda")
+            ops.stage_events = {}
+            time_op(lambda: ops.fine_match(q, win), a.iters, warmup=0 if a.iters == 1 else 3)
+            evs = ops.stage_events["fine_match"][-a.iters:]
+            ops.stage_events = None
+            dev_ms = sorted(x.elapsed_time(y) for x, y in evs)[len(evs) // 2]
+            got = ops.fine_match(q, win).double()
+            # fp64 evaluation of the same formula (torch, on the device) for the error report
+            sim = torch.einsum("mc,mrc->mr", q.double(), win.double()) / math.sqrt(128.0)
+            heat = torch.softmax(sim, dim=1)
+            lin = (torch.linspace(0, W - 1, W, device="cuda", dtype=torch.float64) / (W - 1) - 0.5) * 2
+            gx, gy = lin.repeat(W), lin.repeat_interleave(W)
+            ex, ey = heat @ gx, heat @ gy
+            vx = (heat @ (gx * gx) - ex * ex).clamp_min(1e-10)
+            vy = (heat @ (gy * gy) - ey * ey).clamp_min(1e-10)
+            ref = torch.stack([ex, ey, vx.sqrt() + vy.sqrt()], 1)
+            by = M * (4.0 * 128 * (W * W + 1) + 20)
+            print(json.dumps({"op": "fine_match", "W": W, "M": M, "ms_device": dev_ms, "algorithmic_mb": by / 1e6,
+                              "gbs": by / dev_ms / 1e6, "frac_hbm": by / dev_ms / 1e6 / hbm,
+                              "max_abs_err_vs_fp64": (got - ref).abs().max().item(),
+                              "peak": f"{hbm} GB/s ({src})"}), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("what", choices=["coarse", "transformer", "fine"])
+    ap.add_argument("--points", type=int, nargs="+", default=[5000, 8000, 30000])
+    ap.add_argument("--matches", type=int, nargs="+", default=[2000, 5000, 10000, 20000])
+    ap.add_argument("--grid", type=int, default=64)
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--precision", type=int, default=3)
+    ap.add_argument("--materialize", action="store_true")
+    a = ap.parse_args()
+    {"coarse": run_coarse, "transformer": run_transformer, "fine": run_fine}[a.what](a)
+
+
+if __name__ == "__main__":
+    main()
