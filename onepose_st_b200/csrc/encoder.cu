@@ -24,6 +24,7 @@
 //   6 MLP1     [x|msg] x W1^T   epilogue: ReLU -> planes
 //   7 MLP2     x W2^T           epilogue: LayerNorm2, + residual -> fp32 master + planes (in place)
 #include <cmath>
+#include <cuda_pipeline.h>
 #include "host.cuh"
 #include "../../include/opb200.h"
 
@@ -214,7 +215,9 @@ struct GroupTable {  // passed by value to small kernels
   int len[64];
 };
 
-// grid = (max_chunks, G), block = 256: thread t -> head t/32, d = t%32; accumulates KV[h][d][0..31], Ksum[h][d]
+// grid = (max_chunks, G), block = 256: thread t -> head t/32, d = t%32; accumulates KV[h][d][0..31] and Ksum[h][d]
+// over the chunk's rows.  Rows are staged 8 at a time through a cp.async double buffer (coalesced 16-byte
+// copies); partials are written j-major ([33][256]) so that both this store and the reduce are coalesced.
 __global__ void __launch_bounds__(256) kv_partial_kernel(const float* __restrict__ kphi, const float* __restrict__ v,
                                                          GroupTable gt, unsigned long long group_sel,
                                                          float* __restrict__ partial, int max_chunks) {
@@ -225,27 +228,43 @@ __global__ void __launch_bounds__(256) kv_partial_kernel(const float* __restrict
   const int len = gt.len[g];
   if (r0 >= len) return;
   const int nrows = min(KV_ROWS_PER_BLOCK, len - r0);
-  __shared__ __align__(16) float vs[8][256];
-  __shared__ float ks[8][256];
+  __shared__ __align__(16) float vs[2][8][256];
+  __shared__ __align__(16) float ks[2][8][256];
   const int t = threadIdx.x;
   const int h = t >> 5;
   float acc[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) acc[i] = 0.f;
   float ksum = 0.f;
-  const long long base = static_cast<long long>(gt.row_start[g] + r0) * 256;
-  for (int rb = 0; rb < nrows; rb += 8) {
-    const int nr = min(8, nrows - rb);
-    __syncthreads();
-    for (int i = 0; i < nr; ++i) {
-      vs[i][t] = v[base + static_cast<long long>(rb + i) * 256 + t];
-      ks[i][t] = kphi[base + static_cast<long long>(rb + i) * 256 + t];
+  const float* kbase = kphi + static_cast<long long>(gt.row_start[g] + r0) * 256;
+  const float* vbase = v + static_cast<long long>(gt.row_start[g] + r0) * 256;
+  const int nb = (nrows + 7) / 8;
+  auto issue = [&](int b) {  // 8 rows x 256 floats = 512 float4 per operand, 2 per thread
+    const int buf = b & 1;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int f4 = t + 256 * q;           // float4 index within the 8-row batch
+      const int row = b * 8 + (f4 >> 6);
+      if (row < nrows) {
+        const long long off = static_cast<long long>(row) * 256 + (f4 & 63) * 4;
+        __pipeline_memcpy_async(&ks[buf][f4 >> 6][(f4 & 63) * 4], kbase + off, 16);
+        __pipeline_memcpy_async(&vs[buf][f4 >> 6][(f4 & 63) * 4], vbase + off, 16);
+      }
     }
+    __pipeline_commit();
+  };
+  issue(0);
+  for (int b = 0; b < nb; ++b) {
+    if (b + 1 < nb) issue(b + 1);
+    else __pipeline_commit();
+    __pipeline_wait_prior(1);
     __syncthreads();
+    const int buf = b & 1;
+    const int nr = min(8, nrows - b * 8);
     for (int i = 0; i < nr; ++i) {
-      const float kk = ks[i][t];
+      const float kk = ks[buf][i][t];
       ksum += kk;
-      const float4* v4 = reinterpret_cast<const float4*>(&vs[i][h * 32]);
+      const float4* v4 = reinterpret_cast<const float4*>(&vs[buf][i][h * 32]);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float4 vv = v4[j];
@@ -255,59 +274,45 @@ __global__ void __launch_bounds__(256) kv_partial_kernel(const float* __restrict
         acc[4 * j + 3] = fmaf(kk, vv.w, acc[4 * j + 3]);
       }
     }
+    __syncthreads();
   }
-  float* out = partial + ((static_cast<long long>(g) * max_chunks + chunk) * 256 + t) * KV_REC;
+  float* out = partial + (static_cast<long long>(g) * max_chunks + chunk) * (KV_REC * 256) + t;
 #pragma unroll
-  for (int i = 0; i < 32; ++i) out[i] = acc[i];
-  out[32] = ksum;
+  for (int i = 0; i < 32; ++i) out[i * 256] = acc[i];
+  out[32 * 256] = ksum;
 }
 
-// grid = (2 halves, G), block = 256.  Sums the chunk partials in a fixed order and writes the
-// block-diagonal B operand of the ATTN GEMM for (group, half): 144 rows (n) x 128 (k) bf16 planes,
+// grid = (33, G), block = 256 (thread t = head*32 + d).  Sums the chunk partials of record j = blockIdx.x in a
+// fixed order (deterministic) and writes the bf16 planes of the block-diagonal B operand of the ATTN GEMM.
+// Per (group, half) the operand is 144 rows (n) x 128 (k):
 //   n <  128 : n = hh*32 + v, k = hh*32 + d  ->  KV[half*4+hh][d][v]      (zero off the diagonal blocks)
 //   n = 128+hh : k = hh*32 + d               ->  Ksum[half*4+hh][d]
+// The zero entries are written once per transformer call (memset), never here.
 __global__ void __launch_bounds__(256) kv_pack_kernel(const float* __restrict__ partial, GroupTable gt,
                                                       unsigned long long group_sel, int max_chunks,
                                                       __nv_bfloat16* __restrict__ b_hi, __nv_bfloat16* __restrict__ b_lo) {
-  const int g = blockIdx.y, half = blockIdx.x;
+  const int g = blockIdx.y, j = blockIdx.x;
   if (!((group_sel >> g) & 1ull)) return;
   const int nchunks = (gt.len[g] + KV_ROWS_PER_BLOCK - 1) / KV_ROWS_PER_BLOCK;
-  const long long obase = (static_cast<long long>(g) * 2 + half) * 144 * 128;
   const int t = threadIdx.x;
-  // zero fill (off-diagonal blocks and unused denominator rows)
-  for (int i = t; i < 144 * 128 / 8; i += 256) {
-    reinterpret_cast<uint4*>(b_hi + obase)[i] = make_uint4(0, 0, 0, 0);
-    if (b_lo) reinterpret_cast<uint4*>(b_lo + obase)[i] = make_uint4(0, 0, 0, 0);
+  const float* src = partial + static_cast<long long>(g) * max_chunks * (KV_REC * 256) + j * 256 + t;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  int c = 0;
+  for (; c + 4 <= nchunks; c += 4) {
+    a0 += src[static_cast<long long>(c + 0) * (KV_REC * 256)];
+    a1 += src[static_cast<long long>(c + 1) * (KV_REC * 256)];
+    a2 += src[static_cast<long long>(c + 2) * (KV_REC * 256)];
+    a3 += src[static_cast<long long>(c + 3) * (KV_REC * 256)];
   }
-  __syncthreads();
-  // thread -> (hh = t/64, d = (t%64)/2, v half = t%2 -> 16 values) ; plus Ksum by the v-half-0 threads
-  const int hh = t >> 6, d = (t & 63) >> 1, vh = t & 1;
-  const int hd = (half * 4 + hh) * 32 + d;
-  float acc[16];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) acc[i] = 0.f;
-  float ksum = 0.f;
-  for (int c = 0; c < nchunks; ++c) {
-    const float* src = partial + ((static_cast<long long>(g) * max_chunks + c) * 256 + hd) * KV_REC;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) acc[i] += src[vh * 16 + i];
-    if (vh == 0) ksum += src[32];
-  }
-  const int k = hh * 32 + d;
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const int n = hh * 32 + vh * 16 + i;
-    __nv_bfloat16 h_, l_;
-    split_bf16(acc[i], h_, l_);
-    b_hi[obase + n * 128 + k] = h_;
-    if (b_lo) b_lo[obase + n * 128 + k] = l_;
-  }
-  if (vh == 0) {
-    __nv_bfloat16 h_, l_;
-    split_bf16(ksum, h_, l_);
-    b_hi[obase + (128 + hh) * 128 + k] = h_;
-    if (b_lo) b_lo[obase + (128 + hh) * 128 + k] = l_;
-  }
+  for (; c < nchunks; ++c) a0 += src[static_cast<long long>(c) * (KV_REC * 256)];
+  const float sum = (a0 + a1) + (a2 + a3);
+  const int h = t >> 5, d = t & 31, half = h >> 2, hh = h & 3;
+  const int n = (j < 32) ? hh * 32 + j : 128 + hh;
+  const long long o = (static_cast<long long>(g) * 2 + half) * 144 * 128 + n * 128 + hh * 32 + d;
+  __nv_bfloat16 h_, l_;
+  split_bf16(sum, h_, l_);
+  b_hi[o] = h_;
+  if (b_lo) b_lo[o] = l_;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -615,7 +620,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
         if (src_streams & (1 << s)) sel |= 1ull << i;
       }
       kv_partial_kernel<<<dim3(g.max_chunks, g.G), 256, 0, stream>>>(w.kf, w.vf, gt, sel, w.kv_partial, g.max_chunks);
-      kv_pack_kernel<<<dim3(2, g.G), 256, 0, stream>>>(w.kv_partial, gt, sel, g.max_chunks, w.kvb_h, x3 ? w.kvb_l : nullptr);
+      kv_pack_kernel<<<dim3(KV_REC, g.G), 256, 0, stream>>>(w.kv_partial, gt, sel, g.max_chunks, w.kvb_h, x3 ? w.kvb_l : nullptr);
       count_launch(2);
       OPB_CHECK_CUDA(cudaGetLastError());
       PlanBuilder pb;
@@ -804,6 +809,10 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
   copy_in_kernel<<<dim3((C + 31) / 32, (g.P1 + 31) / 32, n_batch), dim3(32, 8), 0, stream>>>(
       x1, x1_sn, x1_sl, x1_sc, add1, mask1, len1, g.P1, C, row1, w.xf, w.xh, w.xl, w.row_mask);
   count_launch(2 + (big_groups ? 1 : 0));
+  if (big_groups) {  // off-diagonal / unused entries of the block-diagonal attention operand stay zero
+    OPB_CHECK_CUDA(cudaMemsetAsync(w.kvb_h, 0, static_cast<size_t>(g.G) * 2 * 144 * 128 * 2, stream));
+    OPB_CHECK_CUDA(cudaMemsetAsync(w.kvb_l, 0, static_cast<size_t>(g.G) * 2 * 144 * 128 * 2, stream));
+  }
   if (big_groups)
     fill_row_base_kernel<<<1, 256, 0, stream>>>(w.base_self, w.base_cross, g.tiles0, g.tiles1, n_batch, 2 * 144);
   OPB_CHECK_CUDA(cudaGetLastError());
