@@ -81,14 +81,20 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
  * scale = 1 / (C * (temperature + eps)); border_mode 0 = OnePosePlus (first border_rm rows/cols of the
  * h1 x w1 grid), 1 = LoFTR (four sides of both grids; valid_hw nullable [n_batch,4] = valid (h0,w0,h1,w1)
  * from the padding masks).  Outputs (capacity rows each): b_ids/i_ids/j_ids int64, mconf fp32, in
- * ascending (b, i) order; count_and_overflow is int[2] on the device: {number of matches, overflow flag}.
- * conf_matrix (nullable) receives the full [n_batch, L, S] confidence matrix. */
+ * ascending (b, i) order; count_and_overflow is int[3] on the device: {number of matches, overflow flag,
+ * rerun flag}.  conf_matrix (nullable) receives the full [n_batch, L, S] confidence matrix.
+ * algo 0 = auto: when there are no masks, no conf_matrix, C == 256 and precision 3, ONE pass over the
+ * similarity tiles computes the softmax statistics and captures the candidate matches; if that pass sees a
+ * partial sum near the flush-to-zero range (or fills its candidate list) it sets the rerun flag, the outputs
+ * are then undefined and the caller must call again with algo 1 = the two-pass path (per-row / per-column
+ * maxima, no dynamic-range limit). */
 size_t opb200_coarse_match_workspace_bytes(int n_batch, int L, int S, int C, float thr);
 int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t* mask_a, const uint8_t* mask_b,
                         int mask_fill, int n_batch, int L, int S, int C, float scale, float thr, int border_rm,
                         int border_mode, int h0, int w0, int h1, int w1, const int* valid_hw, int64_t* b_ids,
                         int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity, int* count_and_overflow,
-                        float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, void* stream);
+                        float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, int algo,
+                        void* stream);
 
 /* ---- Fine level --------------------------------------------------------------------------------------
  * opb200_fine_gather replaces F.unfold + index in FinePreprocess (OnePosePlus fine_preprocess.py:43-53,

@@ -32,7 +32,8 @@ int split_planes(const float* x, long long stride_r, long long stride_c, const f
 
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kNegInf = -INFINITY;
-constexpr int kNoMatch = 0x7f7f7f7f;  // rowj sentinel (what cudaMemsetAsync(0x7f) leaves)
+constexpr int kNoMatch = 0x7f7f7f7f;
+constexpr int SIM_BN = 128;  // rowj sentinel (what cudaMemsetAsync(0x7f) leaves)
 
 struct SimGeom {
   int N, L, S, Lp, Sp;        // valid and padded (per batch element) row / column counts
@@ -259,6 +260,302 @@ struct EpiSimSelect {
   }
 };
 
+
+// ================================================================================================
+// FAST PATH: one pass over the similarity tiles (no masks, conf matrix not requested, C == 256).
+//
+//   * The 128-row A block (bf16 hi + lo planes, all of K = 256: 128 KB) stays RESIDENT in shared memory
+//     while the CTA sweeps its n tiles; only B (hi + lo k-blocks, 32 KB per stage) streams through a
+//     3-stage TMA ring.  Shared-memory fill per 128x128 tile drops from 384 KB to 128 KB, which is what
+//     keeps the tcgen05 pipe from starving on L2 bandwidth ("sim GEMM").
+//   * Four epilogue groups (4 warps each) own one TMEM accumulator stage each, so up to four tiles are in
+//     their epilogue while the MMA warp works on the next one.
+//   * Epilogue, per warp = 32 rows x 128 columns, no shared memory and no block barrier:
+//       e_ij = 2^(y_ij - T) with T a warp-uniform running reference (block max);   y = acc * scale * log2(e)
+//       row partial  (T, sum_j e_ij)  -> rowpart[n_tile][row]
+//       col partial  (T, sum_i e_ij)  -> colpart[m_tile*4 + quarter][col]   (31-shuffle transpose-reduce)
+//     Any partial that is not safely above the flush-to-zero range raises *needs_robust (the caller then
+//     reruns the two-pass path, which keeps a separate maximum per row / column).
+//   * Candidates are captured in the SAME pass: conf_ij > thr requires 2^(y_ij - LSErow_i) > thr, and the
+//     row sum over this tile only under-estimates the full row sum, so  e_ij > thr * (tile row sum)  is a
+//     necessary condition.  (row, col, y) of the few survivors go to the candidate list; their exact
+//     confidence is evaluated once the LSEs are final, with the same conf_from() as the two-pass path.
+// ================================================================================================
+constexpr int FAST_GROUPS = 4;
+constexpr int FAST_BSTAGES = 3;
+constexpr int FAST_C = 256;
+constexpr int FAST_KB = FAST_C / BLOCK_K;           // 4 k-blocks
+constexpr int FAST_SUB = BLOCK_M * BLOCK_K * 2;     // one [128 x 64] bf16 sub-tile: 16 KB
+constexpr int FAST_A_BYTES = 2 * FAST_KB * FAST_SUB;  // hi + lo planes of the resident A block
+constexpr int FAST_BSTAGE_BYTES = 2 * FAST_SUB;     // B hi + lo k-block
+constexpr int FAST_SMEM = 1024 + FAST_A_BYTES + FAST_BSTAGES * FAST_BSTAGE_BYTES + 256;
+constexpr float kTinySum = 7.888609e-31f;           // 2^-100: partial sums below this may have lost terms to FTZ
+
+struct SimFastParams {
+  CUtensorMap a_hi, a_lo, b_hi, b_lo;  // [rows, 256] bf16, box 128 x 64, 128B swizzle
+  int N, L, S, Lp, Sp;
+  int n_tiles;      // Sp / 128
+  int total_tiles;  // N * (Lp/128) * n_tiles, m-major
+  float c;          // scale * log2(e)
+  float thr_lim;    // 0.99 * thr (slack for the approximate exponentials)
+  float2* rowpart;  // [n_tiles][N*Lp]
+  float2* colpart;  // [4*Lp/128][N*Sp]
+  Candidate* cand;
+  int* cand_count;
+  int cand_cap;
+  int* needs_robust;
+};
+
+// lane j <- sum over the 32 lanes of e[j]  (recursive halving: 31 shuffles)
+__device__ __forceinline__ float warp_transpose_sum(float (&e)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int k = 0; k < off; ++k) {
+      const float keep = up ? e[k + off] : e[k];
+      const float send = up ? e[k] : e[k + off];
+      e[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return e[0];
+}
+
+template <bool RAGGED>
+__device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32_t tmem_acc, int m_tile, int n_tile,
+                                                  int quarter, int lane) {
+  const int tiles_per_batch = p.Lp / BLOCK_M;
+  const int n = m_tile / tiles_per_batch;
+  const int mt_in_batch = m_tile - n * tiles_per_batch;
+  const int i = mt_in_batch * BLOCK_M + quarter * 32 + lane;  // row within the batch element
+  const bool row_valid = !RAGGED || i < p.L;
+  const long long grow = static_cast<long long>(n) * p.Lp + i;
+  float T = kNegInf, s = 0.f, amax = kNegInf;
+  float2* cp = p.colpart + (static_cast<long long>(mt_in_batch) * 4 + quarter) * p.N * p.Sp + static_cast<long long>(n) * p.Sp;
+  bool tiny = false;
+#pragma unroll 1
+  for (int c0 = 0; c0 < SIM_BN; c0 += 32) {
+    float v[32];
+    load_acc32(tmem_acc + c0, v);
+    const int j0 = n_tile * SIM_BN + c0;
+    if (RAGGED) {
+#pragma unroll
+      for (int k = 0; k < 32; ++k)
+        if (!row_valid || j0 + k >= p.S) v[k] = kNegInf;
+    }
+    float tm = v[0];
+#pragma unroll
+    for (int k = 1; k < 32; ++k) tm = fmaxf(tm, v[k]);
+    amax = fmaxf(amax, tm);
+    float wm = tm;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wm = fmaxf(wm, __shfl_xor_sync(0xffffffffu, wm, o));
+    const float Tn = fmaxf(T, wm * p.c);
+    if (Tn == kNegInf) {  // nothing valid in this 32 x 32 block (ragged edge only)
+      if (j0 + lane < p.Sp) cp[j0 + lane] = make_float2(kNegInf, 0.f);
+      continue;
+    }
+    if (T > kNegInf) s *= ptx::ex2(T - Tn);
+    T = Tn;
+    float rs0 = 0.f, rs1 = 0.f, rs2 = 0.f, rs3 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 32; k += 4) {
+      v[k + 0] = ptx::ex2(fmaf(v[k + 0], p.c, -T));
+      v[k + 1] = ptx::ex2(fmaf(v[k + 1], p.c, -T));
+      v[k + 2] = ptx::ex2(fmaf(v[k + 2], p.c, -T));
+      v[k + 3] = ptx::ex2(fmaf(v[k + 3], p.c, -T));
+      rs0 += v[k + 0];
+      rs1 += v[k + 1];
+      rs2 += v[k + 2];
+      rs3 += v[k + 3];
+    }
+    s += (rs0 + rs1) + (rs2 + rs3);
+    const float cs = warp_transpose_sum(v, lane);
+    const int j = j0 + lane;
+    if (j < p.Sp) cp[j] = make_float2(T, cs);
+    if ((!RAGGED || j < p.S) && cs < kTinySum) tiny = true;
+  }
+  p.rowpart[static_cast<long long>(n_tile) * p.N * p.Lp + grow] = make_float2(T, s);
+  if (row_valid && s < kTinySum) tiny = true;
+  if (__any_sync(0xffffffffu, tiny) && lane == 0) atomicExch(p.needs_robust, 1);
+  // candidate capture: e_max > thr * (row sum over this tile) is necessary for any conf > thr in this row
+  const float lim = p.thr_lim * s;
+  const bool need = row_valid && ptx::ex2(fmaf(amax, p.c, -T)) > lim;
+  if (__any_sync(0xffffffffu, need)) {
+#pragma unroll 1
+    for (int c0 = 0; c0 < SIM_BN; c0 += 32) {
+      float v[32];
+      load_acc32(tmem_acc + c0, v);
+      if (need) {
+        const int j0 = n_tile * SIM_BN + c0;
+#pragma unroll 1
+        for (int k = 0; k < 32; ++k) {
+          if (RAGGED && j0 + k >= p.S) break;
+          if (ptx::ex2(fmaf(v[k], p.c, -T)) > lim) {
+            const int slot = atomicAdd(p.cand_count, 1);
+            if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i, j0 + k, __fmul_rn(v[k], p.c), 1};
+          }
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(const __grid_constant__ SimFastParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;                  // [plane 0/1][kb][128 x 64]
+  uint8_t* smem_b = smem + FAST_A_BYTES;   // [stage][plane 0/1][128 x 64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + FAST_BSTAGES * FAST_BSTAGE_BYTES);
+  uint64_t* a_full = bars;                 // 1
+  uint64_t* a_empty = bars + 1;            // 1
+  uint64_t* b_full = bars + 2;             // FAST_BSTAGES
+  uint64_t* b_empty = b_full + FAST_BSTAGES;
+  uint64_t* tfull = b_empty + FAST_BSTAGES;  // FAST_GROUPS
+  uint64_t* tempty = tfull + FAST_GROUPS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + FAST_GROUPS);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // contiguous, balanced range of the m-major tile list: at most two A blocks per CTA at these sizes
+  const int t_begin = static_cast<int>(static_cast<long long>(p.total_tiles) * blockIdx.x / gridDim.x);
+  const int t_end = static_cast<int>(static_cast<long long>(p.total_tiles) * (blockIdx.x + 1) / gridDim.x);
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&p.a_hi);
+    ptx::prefetch_tmap(&p.a_lo);
+    ptx::prefetch_tmap(&p.b_hi);
+    ptx::prefetch_tmap(&p.b_lo);
+    ptx::mbar_init(a_full, 1);
+    ptx::mbar_init(a_empty, 1);
+    for (int s = 0; s < FAST_BSTAGES; ++s) {
+      ptx::mbar_init(&b_full[s], 1);
+      ptx::mbar_init(&b_empty[s], 1);
+    }
+    for (int g = 0; g < FAST_GROUPS; ++g) {
+      ptx::mbar_init(&tfull[g], 1);
+      ptx::mbar_init(&tempty[g], 4);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int tiles_per_batch = p.Lp / BLOCK_M;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (ptx::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0, a_phase = 0;
+      int cur_m = -1;
+      for (int t = t_begin; t < t_end; ++t) {
+        const int m_tile = t / p.n_tiles, n_tile = t - m_tile * p.n_tiles;
+        if (m_tile != cur_m) {
+          ptx::mbar_wait(a_empty, a_phase ^ 1);
+          ptx::mbar_arrive_expect_tx(a_full, FAST_A_BYTES);
+          for (int kb = 0; kb < FAST_KB; ++kb) {
+            ptx::tma_load_2d(smem_a + kb * FAST_SUB, &p.a_hi, a_full, kb * BLOCK_K, m_tile * BLOCK_M);
+            ptx::tma_load_2d(smem_a + (FAST_KB + kb) * FAST_SUB, &p.a_lo, a_full, kb * BLOCK_K, m_tile * BLOCK_M);
+          }
+          a_phase ^= 1;
+          cur_m = m_tile;
+        }
+        const int b_row = (m_tile / tiles_per_batch) * p.Sp + n_tile * SIM_BN;
+        for (int kb = 0; kb < FAST_KB; ++kb) {
+          ptx::mbar_wait(&b_empty[stage], phase ^ 1);
+          ptx::mbar_arrive_expect_tx(&b_full[stage], FAST_BSTAGE_BYTES);
+          uint8_t* sb = smem_b + stage * FAST_BSTAGE_BYTES;
+          ptx::tma_load_2d(sb, &p.b_hi, &b_full[stage], kb * BLOCK_K, b_row);
+          ptx::tma_load_2d(sb + FAST_SUB, &p.b_lo, &b_full[stage], kb * BLOCK_K, b_row);
+          if (++stage == FAST_BSTAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, SIM_BN);
+    int stage = 0;
+    uint32_t phase = 0, a_phase = 0;
+    int cur_m = -1;
+    int it = 0;
+    for (int t = t_begin; t < t_end; ++t, ++it) {
+      const int m_tile = t / p.n_tiles;
+      if (m_tile != cur_m) {
+        ptx::mbar_wait(a_full, a_phase);
+        a_phase ^= 1;
+        cur_m = m_tile;
+      }
+      const bool last_of_a = (t + 1 == t_end) || ((t + 1) / p.n_tiles != m_tile);
+      const int acc = it % FAST_GROUPS;
+      ptx::mbar_wait(&tempty[acc], ((it / FAST_GROUPS) & 1) ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * SIM_BN;
+      for (int kb = 0; kb < FAST_KB; ++kb) {
+        ptx::mbar_wait(&b_full[stage], phase);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          const uint64_t ah = ptx::make_desc_sw128(ptx::smem_u32(smem_a + kb * FAST_SUB));
+          const uint64_t al = ptx::make_desc_sw128(ptx::smem_u32(smem_a + (FAST_KB + kb) * FAST_SUB));
+          const uint32_t sb = ptx::smem_u32(smem_b + stage * FAST_BSTAGE_BYTES);
+          const uint64_t bh = ptx::make_desc_sw128(sb);
+          const uint64_t bl = ptx::make_desc_sw128(sb + FAST_SUB);
+          // small cross terms first, the dominant hi*hi term last
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bl + 2 * k, idesc, (kb | k) != 0);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, al + 2 * k, bh + 2 * k, idesc, 1);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bh + 2 * k, idesc, 1);
+          ptx::mma_commit(&b_empty[stage]);
+          if (kb == FAST_KB - 1) {
+            ptx::mma_commit(&tfull[acc]);
+            if (last_of_a) ptx::mma_commit(a_empty);
+          }
+        }
+        __syncwarp();
+        if (++stage == FAST_BSTAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue groups
+    const int ew = warp - 2;
+    const int group = ew >> 2;
+    const int quarter = warp & 3;
+    int it = 0;
+    for (int t = t_begin; t < t_end; ++t, ++it) {
+      if (it % FAST_GROUPS != group) continue;
+      const int m_tile = t / p.n_tiles, n_tile = t - m_tile * p.n_tiles;
+      ptx::mbar_wait(&tfull[group], (it / FAST_GROUPS) & 1);
+      ptx::tc_fence_after();
+      const uint32_t tacc = tmem_base + group * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);
+      const int mt_in_batch = m_tile % tiles_per_batch;
+      const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || ((n_tile + 1) * SIM_BN > p.S);
+      if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, n_tile, quarter, lane);
+      else sim_fast_epilogue<false>(p, tacc, m_tile, n_tile, quarter, lane);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty[group]);
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
 struct BorderRule {
   int mode;    // 0: OnePosePlus (query grid, top/left only); 1: LoFTR (both grids, four sides)
   int b;       // border_rm
@@ -280,11 +577,20 @@ __device__ __forceinline__ bool border_keep(const BorderRule& br, int n, int i, 
          c1 < w1 - br.b;
 }
 
-__global__ void cand_max_kernel(const Candidate* __restrict__ cand, const int* __restrict__ count, int cap, int L, int S,
+__global__ void cand_max_kernel(Candidate* __restrict__ cand, const int* __restrict__ count, int cap, int L, int S,
+                                const float2* __restrict__ lse_row, const float2* __restrict__ lse_col, int Lp, int Sp, float thr,
                                 unsigned* __restrict__ rowmax, unsigned* __restrict__ colmax) {
   const int n_c = min(*count, cap);
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_c; t += gridDim.x * blockDim.x) {
-    const Candidate c = cand[t];
+    Candidate c = cand[t];
+    if (c.pad == 1) {  // fast path: the entry holds y; its confidence can be formed now that the LSEs are final
+      const int n = c.row / L, i = c.row - n * L;
+      const float cf = conf_from(c.conf, lse_row[static_cast<long long>(n) * Lp + i], lse_col[static_cast<long long>(n) * Sp + c.col]);
+      c.conf = cf > thr ? cf : 0.f;
+      c.pad = 0;
+      cand[t] = c;
+    }
+    if (c.conf == 0.f) continue;
     const unsigned bits = __float_as_uint(c.conf);  // conf > thr > 0: the bit pattern orders like the value
     atomicMax(&rowmax[c.row], bits);
     atomicMax(&colmax[(c.row / L) * static_cast<long long>(S) + c.col], bits);
@@ -297,6 +603,7 @@ __global__ void cand_pick_kernel(const Candidate* __restrict__ cand, const int* 
   const int n_c = min(*count, cap);
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_c; t += gridDim.x * blockDim.x) {
     const Candidate c = cand[t];
+    if (c.conf == 0.f) continue;  // fast-path candidate that did not reach thr
     const unsigned bits = __float_as_uint(c.conf);
     const int n = c.row / L, i = c.row - n * L;
     if (bits == rowmax[c.row] && bits == colmax[n * static_cast<long long>(S) + c.col] && border_keep(br, n, i, c.col))
@@ -309,7 +616,8 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
                                                        int n_rows, int L, long long* __restrict__ b_ids,
                                                        long long* __restrict__ i_ids, long long* __restrict__ j_ids,
                                                        float* __restrict__ mconf, int capacity, int* __restrict__ out_count,
-                                                       const int* __restrict__ cand_count, int cand_cap, int* __restrict__ overflow) {
+                                                       const int* __restrict__ cand_count, int cand_cap, int* __restrict__ overflow,
+                                                       int fast) {
   __shared__ int warp_sums[32];
   __shared__ int carry;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -344,7 +652,10 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
   }
   if (t == 0) {
     *out_count = carry;
-    *overflow = (*cand_count > cand_cap) || (carry > capacity);
+    const bool cand_over = *cand_count > cand_cap;
+    // fast path: a full candidate list or an FTZ-endangered partial asks for the two-pass rerun instead
+    overflow[0] = (!fast && cand_over) || (carry > capacity);
+    overflow[1] = fast && (cand_over || cand_count[2] != 0);
   }
 }
 
@@ -354,8 +665,6 @@ __global__ void fill_sim_row_base(int* base, int tiles_per_batch, int N, int Sp)
 }
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-
-constexpr int SIM_BN = 128;
 
 struct CoarseWs {
   __nv_bfloat16 *a_hi, *a_lo, *b_hi, *b_lo;
@@ -386,12 +695,13 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.b_hi = static_cast<__nv_bfloat16*>(take(rb * C * 2));
   w.b_lo = static_cast<__nv_bfloat16*>(take(rb * C * 2));
   w.rowpart = static_cast<float2*>(take(static_cast<size_t>(w.Sp / SIM_BN) * ra * 8));
-  w.colpart = static_cast<float2*>(take(static_cast<size_t>(w.Lp / BLOCK_M) * rb * 8));
+  w.colpart = static_cast<float2*>(take(static_cast<size_t>(4) * (w.Lp / BLOCK_M) * rb * 8));  // fast path: one record per 32-row block
   w.lse_row = static_cast<float2*>(take(ra * 8));
   w.lse_col = static_cast<float2*>(take(rb * 8));
   const double bound = std::ceil(static_cast<double>(N) * (L < S ? L : S) / (thr > 1e-6f ? thr : 1e-6f)) + 64;
   const double all = static_cast<double>(N) * L * S;
-  w.cand_cap = static_cast<int>(bound < all ? bound : all);
+  const double roomy = bound + 8.0 * N * L + 65536;  // the single-pass capture also lists near misses
+  w.cand_cap = static_cast<int>(roomy < all ? roomy : all);
   w.cand = static_cast<Candidate*>(take(static_cast<size_t>(w.cand_cap) * sizeof(Candidate)));
   w.rowj = static_cast<int*>(take(static_cast<size_t>(N) * L * 4));
   w.row_base = static_cast<int*>(take(ra / BLOCK_M * 4 + 4));
@@ -418,9 +728,11 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
                         int mask_fill, int n_batch, int L, int S, int C, float scale, float thr, int border_rm,
                         int border_mode, int h0, int w0, int h1, int w1, const int* valid_hw, int64_t* b_ids,
                         int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity, int* count_and_overflow,
-                        float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, void* stream_) {
+                        float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, int algo,
+                        void* stream_) {
   if (int r = check_device()) return r;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  OPB_CHECK_ARG(algo == 0 || algo == 1, "algo must be 0 (auto: single-pass where legal) or 1 (two-pass)");
   OPB_CHECK_ARG(feat_a && feat_b && b_ids && i_ids && j_ids && mconf && count_and_overflow && workspace, "null pointer");
   OPB_CHECK_ARG(n_batch >= 1 && L >= 1 && S >= 1, "empty input");
   OPB_CHECK_ARG(C % BLOCK_K == 0 && C >= BLOCK_K, "feature dim must be a positive multiple of 64");
@@ -459,54 +771,87 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
   fill_sim_row_base<<<(m_tiles + 255) / 256, 256, 0, stream>>>(w.row_base, Lp / BLOCK_M, N, Sp);
   count_launch();
 
-  PlanBuilder pb;
-  pb.add_a(w.a_hi, static_cast<uint64_t>(N) * Lp, C, C, 0);
-  pb.add_b(w.b_hi, static_cast<uint64_t>(N) * Sp, C, C, 0, SIM_BN);
-  if (x3) {
-    pb.add_a(w.a_lo, static_cast<uint64_t>(N) * Lp, C, C, 1);
-    pb.add_b(w.b_lo, static_cast<uint64_t>(N) * Sp, C, C, 1, SIM_BN);
-  }
-  if (pb.status) return pb.status;
-  const int nkb = C / BLOCK_K;
-  if (x3) {
-    pb.seg(0, 1, 0, 0, nkb);
-    pb.seg(1, 0, 0, 0, nkb);
-  }
-  pb.seg(0, 0, 0, 0, nkb);
-  pb.finish();
-  pb.plan.num_n_tiles = n_tiles;
-  pb.plan.num_tiles = m_tiles * n_tiles;
-  pb.plan.b_rows_per_ntile = SIM_BN;
-  pb.plan.b_row_base = w.row_base;
-
-  SimGeom g{N, L, S, Lp, Sp, scale, mask_a, mask_b, mask_fill};
-  {
-    EpiSimStats<SIM_BN>::Params ep{g, w.rowpart, w.colpart};
-    if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimStats<SIM_BN>>(pb.plan, ep, stream)) return r;
-  }
-  {
-    const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
-    merge_stats_kernel<<<static_cast<unsigned>((nr + nc + 255) / 256), 256, 0, stream>>>(w.rowpart, n_tiles, nr, w.colpart,
-                                                                                        Lp / BLOCK_M, nc, w.lse_row, w.lse_col);
+  const bool fast = algo == 0 && x3 && C == FAST_C && mask_a == nullptr && mask_b == nullptr && conf_matrix == nullptr;
+  int n_row_parts = n_tiles, n_col_parts = Lp / BLOCK_M;
+  if (fast) {
+    SimFastParams fp;
+    int r;
+    if ((r = make_tmap_bf16(&fp.a_hi, w.a_hi, static_cast<uint64_t>(N) * Lp, C, C, BLOCK_M))) return r;
+    if ((r = make_tmap_bf16(&fp.a_lo, w.a_lo, static_cast<uint64_t>(N) * Lp, C, C, BLOCK_M))) return r;
+    if ((r = make_tmap_bf16(&fp.b_hi, w.b_hi, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
+    if ((r = make_tmap_bf16(&fp.b_lo, w.b_lo, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
+    fp.N = N, fp.L = L, fp.S = S, fp.Lp = Lp, fp.Sp = Sp;
+    fp.n_tiles = n_tiles;
+    fp.total_tiles = m_tiles * n_tiles;
+    fp.c = scale * kLog2e;
+    fp.thr_lim = 0.99f * thr;
+    fp.rowpart = w.rowpart, fp.colpart = w.colpart;
+    fp.cand = w.cand, fp.cand_count = w.counters, fp.cand_cap = w.cand_cap;
+    fp.needs_robust = w.counters + 2;
+    static bool configured = false;
+    if (!configured) {
+      OPB_CHECK_CUDA(cudaFuncSetAttribute(sim_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FAST_SMEM));
+      configured = true;
+    }
+    const int grid = fp.total_tiles < num_sms() ? fp.total_tiles : num_sms();
+    sim_fast_kernel<<<grid, 64 + 128 * FAST_GROUPS, FAST_SMEM, stream>>>(fp);
     count_launch();
-  }
-  {
-    const float log2_thr_lo = log2f(thr) - 1e-3f;
-    if (conf_matrix != nullptr) {
-      EpiSimSelect<SIM_BN, true>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, conf_matrix};
-      if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, true>>(pb.plan, ep, stream)) return r;
-    } else {
-      EpiSimSelect<SIM_BN, false>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, nullptr};
-      if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, false>>(pb.plan, ep, stream)) return r;
+    OPB_CHECK_CUDA(cudaGetLastError());
+    n_col_parts = 4 * (Lp / BLOCK_M);
+    const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
+    merge_stats_kernel<<<static_cast<unsigned>((nr + nc + 255) / 256), 256, 0, stream>>>(w.rowpart, n_row_parts, nr, w.colpart,
+                                                                                        n_col_parts, nc, w.lse_row, w.lse_col);
+    count_launch();
+  } else {
+    PlanBuilder pb;
+    pb.add_a(w.a_hi, static_cast<uint64_t>(N) * Lp, C, C, 0);
+    pb.add_b(w.b_hi, static_cast<uint64_t>(N) * Sp, C, C, 0, SIM_BN);
+    if (x3) {
+      pb.add_a(w.a_lo, static_cast<uint64_t>(N) * Lp, C, C, 1);
+      pb.add_b(w.b_lo, static_cast<uint64_t>(N) * Sp, C, C, 1, SIM_BN);
+    }
+    if (pb.status) return pb.status;
+    const int nkb = C / BLOCK_K;
+    if (x3) {
+      pb.seg(0, 1, 0, 0, nkb);
+      pb.seg(1, 0, 0, 0, nkb);
+    }
+    pb.seg(0, 0, 0, 0, nkb);
+    pb.finish();
+    pb.plan.num_n_tiles = n_tiles;
+    pb.plan.num_tiles = m_tiles * n_tiles;
+    pb.plan.b_rows_per_ntile = SIM_BN;
+    pb.plan.b_row_base = w.row_base;
+
+    SimGeom g{N, L, S, Lp, Sp, scale, mask_a, mask_b, mask_fill};
+    {
+      EpiSimStats<SIM_BN>::Params ep{g, w.rowpart, w.colpart};
+      if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimStats<SIM_BN>>(pb.plan, ep, stream)) return r;
+    }
+    {
+      const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
+      merge_stats_kernel<<<static_cast<unsigned>((nr + nc + 255) / 256), 256, 0, stream>>>(w.rowpart, n_tiles, nr, w.colpart,
+                                                                                          Lp / BLOCK_M, nc, w.lse_row, w.lse_col);
+      count_launch();
+    }
+    {
+      const float log2_thr_lo = log2f(thr) - 1e-3f;
+      if (conf_matrix != nullptr) {
+        EpiSimSelect<SIM_BN, true>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, conf_matrix};
+        if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, true>>(pb.plan, ep, stream)) return r;
+      } else {
+        EpiSimSelect<SIM_BN, false>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, nullptr};
+        if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, false>>(pb.plan, ep, stream)) return r;
+      }
     }
   }
   BorderRule br{border_mode, border_rm, h0, w0, h1, w1, valid_hw};
   const int cb = (w.cand_cap + 255) / 256 < 592 ? (w.cand_cap + 255) / 256 : 592;
-  cand_max_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.rowmax, w.colmax);
+  cand_max_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.lse_row, w.lse_col, Lp, Sp, thr, w.rowmax, w.colmax);
   cand_pick_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.rowmax, w.colmax, br, w.rowj);
   compact_kernel<<<1, 1024, 0, stream>>>(w.rowj, w.rowmax, N * L, L, reinterpret_cast<long long*>(b_ids),
                                          reinterpret_cast<long long*>(i_ids), reinterpret_cast<long long*>(j_ids), mconf, capacity,
-                                         count_and_overflow, w.counters, w.cand_cap, count_and_overflow + 1);
+                                         count_and_overflow, w.counters, w.cand_cap, count_and_overflow + 1, fast ? 1 : 0);
   count_launch(3);
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;

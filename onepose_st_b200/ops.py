@@ -141,7 +141,7 @@ def transformer(packed_layers: Sequence[torch.Tensor], layer_kinds: Sequence[int
 def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, thr: float, border_rm: int,
                  border_mode: int, grid_a, grid_b, mask_a: Optional[torch.Tensor] = None,
                  mask_b: Optional[torch.Tensor] = None, mask_fill: int = 0, valid_hw: Optional[torch.Tensor] = None,
-                 materialize_conf: bool = False, precision: int = PREC_BF16X3):
+                 materialize_conf: bool = False, precision: int = PREC_BF16X3, algo: int = 0):
     """Dual-softmax + mutual-NN selection.  Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None).
 
     One host sync (reading the match count) -- the reference syncs at the same point (torch.where)."""
@@ -161,7 +161,7 @@ def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, th
     i_ids = torch.empty(cap, dtype=torch.int64, device=dev)
     j_ids = torch.empty(cap, dtype=torch.int64, device=dev)
     mconf = torch.empty(cap, dtype=torch.float32, device=dev)
-    cnt = torch.zeros(2, dtype=torch.int32, device=dev)
+    cnt = torch.zeros(3, dtype=torch.int32, device=dev)
     conf = torch.empty(n, L, S, dtype=torch.float32, device=dev) if materialize_conf else None
 
     def m8(m, length):
@@ -178,10 +178,14 @@ def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, th
         st = l.opb200_coarse_match(_lib.ptr(feat_a), _lib.ptr(feat_b), _lib.ptr(ma), _lib.ptr(mb), int(mask_fill), n, L, S, C,
                                ctypes.c_float(scale), ctypes.c_float(thr), int(border_rm), int(border_mode), h0, w0, h1, w1,
                                _lib.ptr(vhw), _lib.ptr(b_ids), _lib.ptr(i_ids), _lib.ptr(j_ids), _lib.ptr(mconf), cap,
-                               _lib.ptr(cnt), _lib.ptr(conf), _lib.ptr(ws), _c_sz(ws.numel()), int(precision),
+                               _lib.ptr(cnt), _lib.ptr(conf), _lib.ptr(ws), _c_sz(ws.numel()), int(precision), int(algo),
                                _lib.stream_ptr())
     _lib.check(st, "opb200_coarse_match")
-    m, overflow = cnt.tolist()
+    m, overflow, rerun = cnt.tolist()
+    if rerun:  # the single-pass statistics hit their dynamic-range guard: take the two-pass path
+        return coarse_match(feat_a, feat_b, scale=scale, thr=thr, border_rm=border_rm, border_mode=border_mode,
+                            grid_a=grid_a, grid_b=grid_b, mask_a=mask_a, mask_b=mask_b, mask_fill=mask_fill,
+                            valid_hw=valid_hw, materialize_conf=materialize_conf, precision=precision, algo=1)
     if overflow:
         import os
         if os.environ.get("OPB200_DEBUG_OVERFLOW"):

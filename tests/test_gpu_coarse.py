@@ -94,13 +94,15 @@ def test_loftr_vs_golden(golden, variant):
 
 @pytest.mark.parametrize("L,S,hw", [(5000, 4096, (64, 64)), (30000, 4096, (64, 64)), (777, 1200, (30, 40))])
 def test_large_no_materialize_matches_materialize(L, S, hw):
-    """BASELINE configs 1/3 sizes: the default path (no conf matrix) must pick exactly the matches the
-    materialising path picks, and those must be what the reference selection finds in that matrix."""
+    """BASELINE configs 1/3 sizes.  The two-pass path without a conf matrix must pick exactly (bitwise) the
+    matches the materialising path picks, and those must be what the reference selection finds in that
+    matrix.  The default single-pass path (different accumulation order, approximate-exp statistics) must
+    find the same index sets with confidences within 1e-5."""
     from onepose_st_b200 import ops
     dev = "cuda"
     f3d, f2d = cases.planted_pair(21, 1, L, S, 256, min(3000, S // 2), hw[0], hw[1], 2, gain=0.6)
     kw = dict(scale=1.0 / (256 * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=hw)
-    a = ops.coarse_match(f3d.to(dev), f2d.to(dev), **kw)
+    a = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=1, **kw)
     bm = ops.coarse_match(f3d.to(dev), f2d.to(dev), materialize_conf=True, **kw)
     for x, y in zip(a[:4], bm[:4]):
         assert torch.equal(x, y)
@@ -115,3 +117,55 @@ def test_large_no_materialize_matches_materialize(L, S, hw):
     sim = (f3d.to(dev)[0] @ f2d.to(dev)[0].t()) / (256 * 0.0801)
     ref = torch.softmax(sim, 0) * torch.softmax(sim, 1)
     assert (conf[0] - ref).abs().max().item() < CONF_TOL
+    # single-pass default
+    f = ops.coarse_match(f3d.to(dev), f2d.to(dev), **kw)
+    got, want = _sets(f[0], f[1], f[2]), _sets(a[0], a[1], a[2])
+    for (bb, ii, jj) in got ^ want:  # only threshold-straddling entries may differ
+        assert abs(conf[bb, ii, jj].item() - 0.1) < 1e-4
+    assert len(got ^ want) <= 2
+    if got == want:
+        assert torch.equal(f[1], a[1]) and torch.equal(f[2], a[2])
+        err = (f[3] - a[3]).abs().max().item()
+        print(f"single-pass vs two-pass mconf max abs diff {err:.2e}")
+        assert err < 1e-5
+
+
+@pytest.mark.parametrize("n,L,S,hw", [(2, 300, 256, (16, 16)), (1, 128, 128, (8, 16)), (3, 129, 200, (10, 20))])
+def test_single_pass_small_and_batched(n, L, S, hw):
+    """Ragged tiles in both dimensions and several batch elements through the single-pass kernel."""
+    from onepose_st_b200 import ops
+    dev = "cuda"
+    f3d, f2d = cases.planted_pair(33, n, L, S, 256, min(100, L // 2), hw[0], hw[1], 2, gain=0.6)
+    kw = dict(scale=1.0 / (256 * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=hw)
+    f = ops.coarse_match(f3d.to(dev), f2d.to(dev), **kw)
+    a = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=1, **kw)
+    assert torch.equal(f[0], a[0]) and torch.equal(f[1], a[1]) and torch.equal(f[2], a[2])
+    assert (f[3] - a[3]).abs().max().item() < 1e-5
+    assert len(f[0]) > 20 * n
+    sim = torch.einsum("nlc,nsc->nls", f3d, f2d).double() / (256 * 0.0801)
+    conf = torch.softmax(sim, 1) * torch.softmax(sim, 2)
+    keep = R._border_keep_onepose(n, L, hw[0], hw[1], 2, "cpu")
+    rb, ri, rj, rc = R.coarse_select(conf.float(), 0.1, keep)
+    assert torch.equal(rb, f[0].cpu()) and torch.equal(ri, f[1].cpu()) and torch.equal(rj, f[2].cpu())
+    assert (rc - f[3].cpu()).abs().max().item() < CONF_TOL
+
+
+def test_single_pass_dynamic_range_guard_reruns_two_pass():
+    """A row block whose similarities sit ~2^-300 below its neighbours' makes the single-pass partial sums
+    underflow; the kernel must flag it and the wrapper must return the two-pass result."""
+    from onepose_st_b200 import ops
+    dev = "cuda"
+    hw = (16, 16)
+    f3d, f2d = cases.planted_pair(34, 1, 256, 256, 256, 80, hw[0], hw[1], 2, gain=0.8)
+    f3d = f3d.clone()
+    f3d[0, 5] = f2d[0, 40] * 60.0     # one enormous row: sim ~ +750 (in the same 32-row block as rows 0..31)
+    kw = dict(scale=1.0 / (256 * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=hw)
+    f = ops.coarse_match(f3d.to(dev), f2d.to(dev), **kw)
+    a = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=1, **kw)
+    for x, y in zip(f[:4], a[:4]):
+        assert torch.equal(x, y)  # identical bits: the wrapper fell back to the same two-pass code
+    sim = (f3d[0].double() @ f2d[0].double().t()) / (256 * 0.0801)
+    conf = (torch.softmax(sim, 0) * torch.softmax(sim, 1))[None].float()
+    keep = R._border_keep_onepose(1, 256, hw[0], hw[1], 2, "cpu")
+    rb, ri, rj, rc = R.coarse_select(conf, 0.1, keep)
+    assert torch.equal(ri, a[1].cpu()) and torch.equal(rj, a[2].cpu())
