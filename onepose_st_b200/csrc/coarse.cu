@@ -138,34 +138,55 @@ struct EpiSimStats {
   }
 };
 
-// merge (max, sum) partials -> log2-sum-exp per row and per column
-__global__ void merge_stats_kernel(const float2* __restrict__ rowpart, int n_row_parts, long long n_rows,
-                                   const float2* __restrict__ colpart, int n_col_parts, long long n_cols,
-                                   float2* __restrict__ lse_row, float2* __restrict__ lse_col) {
-  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+// merge (max, sum) partials -> (max, log2 sum) per row and per column.  Block = 32 outputs x 8 slices of the
+// part list: reads stay coalesced along the output index, each thread folds its slice online, the eight
+// slices are combined through shared memory in a fixed order (deterministic).
+__global__ void __launch_bounds__(256) merge_stats_kernel(const float2* __restrict__ rowpart, int n_row_parts, long long n_rows,
+                                                          const float2* __restrict__ colpart, int n_col_parts, long long n_cols,
+                                                          float2* __restrict__ lse_row, float2* __restrict__ lse_col) {
+  __shared__ float2 sm[8][33];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const long long t = static_cast<long long>(blockIdx.x) * 32 + lane;
+  const long long row_blocks = (n_rows + 31) / 32;  // row outputs and column outputs never share a block
   const float2* part;
   int nparts;
   long long stride, idx;
   float2* out;
-  if (t < n_rows) {
-    part = rowpart, nparts = n_row_parts, stride = n_rows, idx = t, out = lse_row;
-  } else if (t < n_rows + n_cols) {
-    part = colpart, nparts = n_col_parts, stride = n_cols, idx = t - n_rows, out = lse_col;
+  bool valid;
+  if (blockIdx.x < row_blocks) {
+    part = rowpart, nparts = n_row_parts, stride = n_rows, idx = t, out = lse_row, valid = idx < n_rows;
   } else {
-    return;
+    part = colpart, nparts = n_col_parts, stride = n_cols, idx = t - row_blocks * 32, out = lse_col, valid = idx < n_cols;
   }
-  float M = kNegInf;
-  for (int k = 0; k < nparts; ++k) M = fmaxf(M, part[k * stride + idx].x);
-  float S = 0.f;
-  if (M > kNegInf) {
-    for (int k = 0; k < nparts; ++k) {
+  float M = kNegInf, S = 0.f;
+  if (valid) {
+    for (int k = slice; k < nparts; k += 8) {
       const float2 pk = part[k * stride + idx];
-      if (pk.x > kNegInf) S += pk.y * exp2f(pk.x - M);
+      if (pk.x > kNegInf) {
+        const float Mn = fmaxf(M, pk.x);
+        S = S * exp2f(M - Mn) + pk.y * exp2f(pk.x - Mn);  // exp2f(-inf) = 0 covers the first term
+        M = Mn;
+      }
     }
   }
-  // kept as (max, log2 sum) rather than their sum: for a fully masked row/column max = -1.44e9 and
-  // adding log2(sum) to it would be lost to rounding, turning 1/(L*S) confidences into 1.0
-  out[idx] = make_float2(M, (M > kNegInf) ? log2f(S) : 0.f);
+  sm[slice][lane] = make_float2(M, S);
+  __syncthreads();
+  if (slice == 0 && valid) {
+    float Mt = kNegInf;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) Mt = fmaxf(Mt, sm[q][lane].x);
+    float St = 0.f;
+    if (Mt > kNegInf) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float2 pq = sm[q][lane];
+        if (pq.x > kNegInf) St += pq.y * exp2f(pq.x - Mt);
+      }
+    }
+    // kept as (max, log2 sum) rather than their sum: for a fully masked row/column max = -1.44e9 and
+    // adding log2(sum) to it would be lost to rounding, turning 1/(L*S) confidences into 1.0
+    out[idx] = make_float2(Mt, (Mt > kNegInf) ? log2f(St) : 0.f);
+  }
 }
 
 struct Candidate {
@@ -378,23 +399,31 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
   p.rowpart[static_cast<long long>(n_tile) * p.N * p.Lp + grow] = make_float2(T, s);
   if (row_valid && s < kTinySum) tiny = true;
   if (__any_sync(0xffffffffu, tiny) && lane == 0) atomicExch(p.needs_robust, 1);
-  // candidate capture: e_max > thr * (row sum over this tile) is necessary for any conf > thr in this row
+  // candidate capture: conf_ij > thr needs e_ij > thr * (row sum over this tile), i.e. acc_ij > vlim_i in raw
+  // accumulator units -- one compare per element on a second sweep over TMEM, taken only when some row of the
+  // warp has its maximum above the limit
   const float lim = p.thr_lim * s;
-  const bool need = row_valid && ptx::ex2(fmaf(amax, p.c, -T)) > lim;
-  if (__any_sync(0xffffffffu, need)) {
+  const float vlim = (row_valid && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
+  if (__any_sync(0xffffffffu, amax > vlim)) {
 #pragma unroll 1
     for (int c0 = 0; c0 < SIM_BN; c0 += 32) {
       float v[32];
       load_acc32(tmem_acc + c0, v);
-      if (need) {
-        const int j0 = n_tile * SIM_BN + c0;
-#pragma unroll 1
-        for (int k = 0; k < 32; ++k) {
-          if (RAGGED && j0 + k >= p.S) break;
-          if (ptx::ex2(fmaf(v[k], p.c, -T)) > lim) {
-            const int slot = atomicAdd(p.cand_count, 1);
-            if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i, j0 + k, __fmul_rn(v[k], p.c), 1};
-          }
+      const int j0 = n_tile * SIM_BN + c0;
+      unsigned mask = 0;
+#pragma unroll
+      for (int k = 0; k < 32; ++k)
+        if (v[k] > vlim && (!RAGGED || j0 + k < p.S)) mask |= 1u << k;
+      unsigned any = __reduce_or_sync(0xffffffffu, mask);
+      while (any) {  // warp-uniform loop over the (rare) columns with a candidate in some lane
+        const int k = __ffs(any) - 1;
+        any &= any - 1;
+        float val = v[0];
+#pragma unroll
+        for (int q = 1; q < 32; ++q) val = (k == q) ? v[q] : val;
+        if ((mask >> k) & 1u) {
+          const int slot = atomicAdd(p.cand_count, 1);
+          if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i, j0 + k, __fmul_rn(val, p.c), 1};
         }
       }
     }
@@ -611,7 +640,8 @@ __global__ void cand_pick_kernel(const Candidate* __restrict__ cand, const int* 
   }
 }
 
-// single-block ordered compaction over the N*L rows (ascending (b, i) like torch.where)
+// single-block ordered compaction over the N*L rows (ascending (b, i) like torch.where): every thread owns a
+// contiguous range of rows, counts its matches, one block-wide exclusive scan, then writes its range
 __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ rowj, const unsigned* __restrict__ rowmax,
                                                        int n_rows, int L, long long* __restrict__ b_ids,
                                                        long long* __restrict__ i_ids, long long* __restrict__ j_ids,
@@ -619,43 +649,49 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
                                                        const int* __restrict__ cand_count, int cand_cap, int* __restrict__ overflow,
                                                        int fast) {
   __shared__ int warp_sums[32];
-  __shared__ int carry;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  if (t == 0) carry = 0;
-  __syncthreads();
-  for (int base = 0; base < n_rows; base += 1024) {
-    const int row = base + t;
-    const int j = row < n_rows ? rowj[row] : kNoMatch;
-    const int flag = j != kNoMatch;
-    const unsigned ball = __ballot_sync(0xffffffffu, flag);
-    const int in_warp = __popc(ball & ((1u << lane) - 1));
-    if (lane == 0) warp_sums[warp] = __popc(ball);
-    __syncthreads();
-    int off = carry;
-    for (int w = 0; w < warp; ++w) off += warp_sums[w];
-    if (flag) {
-      const int pos = off + in_warp;
-      if (pos < capacity) {
-        b_ids[pos] = row / L;
-        i_ids[pos] = row % L;
-        j_ids[pos] = j;
-        mconf[pos] = __uint_as_float(rowmax[row]);
-      }
-    }
-    __syncthreads();
-    if (t == 0) {
-      int tot = 0;
-      for (int w = 0; w < 32; ++w) tot += warp_sums[w];
-      carry += tot;
-    }
-    __syncthreads();
+  const int per = (n_rows + 1023) / 1024;
+  const int r0 = min(t * per, n_rows), r1 = min(r0 + per, n_rows);
+  int cnt = 0;
+  for (int r = r0; r < r1; ++r) cnt += rowj[r] != kNoMatch;
+  int incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int y = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += y;
   }
-  if (t == 0) {
-    *out_count = carry;
-    const bool cand_over = *cand_count > cand_cap;
-    // fast path: a full candidate list or an FTZ-endangered partial asks for the two-pass rerun instead
-    overflow[0] = (!fast && cand_over) || (carry > capacity);
-    overflow[1] = fast && (cand_over || cand_count[2] != 0);
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int ws = warp_sums[lane], wi = ws;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane >= o) wi += y;
+    }
+    warp_sums[lane] = wi - ws;  // exclusive prefix of the warp totals
+    if (lane == 31) {
+      const int total = wi;
+      *out_count = total;
+      const bool cand_over = *cand_count > cand_cap;
+      // fast path: a full candidate list or an FTZ-endangered partial asks for the two-pass rerun instead
+      overflow[0] = (!fast && cand_over) || (total > capacity);
+      overflow[1] = fast && (cand_over || cand_count[2] != 0);
+    }
+  }
+  __syncthreads();
+  int pos = warp_sums[warp] + incl - cnt;
+  for (int r = r0; r < r1; ++r) {
+    const int j = rowj[r];
+    if (j != kNoMatch) {
+      if (pos < capacity) {
+        b_ids[pos] = r / L;
+        i_ids[pos] = r % L;
+        j_ids[pos] = j;
+        mconf[pos] = __uint_as_float(rowmax[r]);
+      }
+      ++pos;
+    }
   }
 }
 
@@ -768,8 +804,6 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
   OPB_CHECK_CUDA(cudaMemsetAsync(static_cast<uint8_t*>(workspace) + w.zero_begin, 0, w.zero_bytes, stream));
   OPB_CHECK_CUDA(cudaMemsetAsync(w.rowj, 0x7f, static_cast<size_t>(N) * L * 4, stream));  // kNoMatch
   const int m_tiles = N * (Lp / BLOCK_M), n_tiles = Sp / SIM_BN;
-  fill_sim_row_base<<<(m_tiles + 255) / 256, 256, 0, stream>>>(w.row_base, Lp / BLOCK_M, N, Sp);
-  count_launch();
 
   const bool fast = algo == 0 && x3 && C == FAST_C && mask_a == nullptr && mask_b == nullptr && conf_matrix == nullptr;
   int n_row_parts = n_tiles, n_col_parts = Lp / BLOCK_M;
@@ -799,10 +833,12 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
     OPB_CHECK_CUDA(cudaGetLastError());
     n_col_parts = 4 * (Lp / BLOCK_M);
     const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
-    merge_stats_kernel<<<static_cast<unsigned>((nr + nc + 255) / 256), 256, 0, stream>>>(w.rowpart, n_row_parts, nr, w.colpart,
-                                                                                        n_col_parts, nc, w.lse_row, w.lse_col);
+    merge_stats_kernel<<<static_cast<unsigned>((nr + 31) / 32 + (nc + 31) / 32), 256, 0, stream>>>(
+        w.rowpart, n_row_parts, nr, w.colpart, n_col_parts, nc, w.lse_row, w.lse_col);
     count_launch();
   } else {
+    fill_sim_row_base<<<(m_tiles + 255) / 256, 256, 0, stream>>>(w.row_base, Lp / BLOCK_M, N, Sp);
+    count_launch();
     PlanBuilder pb;
     pb.add_a(w.a_hi, static_cast<uint64_t>(N) * Lp, C, C, 0);
     pb.add_b(w.b_hi, static_cast<uint64_t>(N) * Sp, C, C, 0, SIM_BN);
@@ -830,8 +866,8 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
     }
     {
       const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
-      merge_stats_kernel<<<static_cast<unsigned>((nr + nc + 255) / 256), 256, 0, stream>>>(w.rowpart, n_tiles, nr, w.colpart,
-                                                                                          Lp / BLOCK_M, nc, w.lse_row, w.lse_col);
+      merge_stats_kernel<<<static_cast<unsigned>((nr + 31) / 32 + (nc + 31) / 32), 256, 0, stream>>>(
+          w.rowpart, n_tiles, nr, w.colpart, Lp / BLOCK_M, nc, w.lse_row, w.lse_col);
       count_launch();
     }
     {
