@@ -43,7 +43,7 @@ struct SimGeom {
   int mask_fill;              // 0: sim += -1e9 (OnePosePlus), 1: sim = -1e9 (LoFTR masked_fill_)
 };
 
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }  // robust path runs one epilogue group
 
 // y = log2(e) * sim with the reference's masking semantics applied to sim first
 __device__ __forceinline__ float sim_log2(float acc, float scale, bool masked, int fill) {
@@ -102,7 +102,7 @@ struct EpiSimStats {
       for (int k = 0; k < 32; ++k) sc[buf][r][k] = row_valid ? y[k] : kNegInf;
       epi_bar();
       {
-        const int cq = ctx.epi_warp, cc = ctx.lane;
+        const int cq = ctx.epi_warp, cc = ctx.lane;  // NB: epi_warp != quarter; any bijection of the 4 warps works here
         float v[32];
         float pm = kNegInf;
 #pragma unroll
@@ -862,7 +862,7 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
     SimGeom g{N, L, S, Lp, Sp, scale, mask_a, mask_b, mask_fill};
     {
       EpiSimStats<SIM_BN>::Params ep{g, w.rowpart, w.colpart};
-      if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimStats<SIM_BN>>(pb.plan, ep, stream)) return r;
+      if (int r = launch_gemm<SIM_BN, 5, 1, EpiSimStats<SIM_BN>>(pb.plan, ep, stream)) return r;
     }
     {
       const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
@@ -874,10 +874,10 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
       const float log2_thr_lo = log2f(thr) - 1e-3f;
       if (conf_matrix != nullptr) {
         EpiSimSelect<SIM_BN, true>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, conf_matrix};
-        if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, true>>(pb.plan, ep, stream)) return r;
+        if (int r = launch_gemm<SIM_BN, 5, 1, EpiSimSelect<SIM_BN, true>>(pb.plan, ep, stream)) return r;
       } else {
         EpiSimSelect<SIM_BN, false>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, nullptr};
-        if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, false>>(pb.plan, ep, stream)) return r;
+        if (int r = launch_gemm<SIM_BN, 5, 1, EpiSimSelect<SIM_BN, false>>(pb.plan, ep, stream)) return r;
       }
     }
   }

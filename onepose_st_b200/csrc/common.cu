@@ -253,9 +253,9 @@ int opb200_debug_gemm(const void* a_hi, const void* a_lo, const void* b_hi, cons
   pb.plan.num_tiles = ((M + BLOCK_M - 1) / BLOCK_M) * pb.plan.num_n_tiles;
   pb.plan.b_rows_per_ntile = block_n;
   EpiStoreF32::Params ep{c, M, N, N, block_n};
-  if (block_n == 256) return launch_gemm<256, 4, 4, EpiStoreF32T<256>>(pb.plan, ep, stream);
-  if (block_n == 144) return launch_gemm<144, 4, 4, EpiStoreF32T<144>>(pb.plan, ep, stream);
-  return launch_gemm<128, 6, 4, EpiStoreF32T<128>>(pb.plan, ep, stream);
+  if (block_n == 256) return launch_gemm<256, 4, 1, EpiStoreF32T<256>>(pb.plan, ep, stream);
+  if (block_n == 144) return launch_gemm<144, 4, 1, EpiStoreF32T<144>>(pb.plan, ep, stream);
+  return launch_gemm<128, 6, 1, EpiStoreF32T<128>>(pb.plan, ep, stream);
 }
 
 }  // extern "C"

@@ -598,7 +598,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       pb.plan.num_n_tiles = nc;
       pb.plan.num_tiles = mc * nc;
       pb.plan.b_rows_per_ntile = C;
-      return launch_gemm<C, (C == 256 ? 4 : 6), 4, EpiQKV<C>>(pb.plan, ep, stream);
+      return launch_gemm<C, (C == 256 ? 4 : 6), (C == 256 ? 2 : 4), EpiQKV<C>>(pb.plan, ep, stream);
     };
     if (q_streams == src_streams) {
       if (int r = launch(qb, qc, 0, 3)) return r;
@@ -640,7 +640,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       pb.plan.b_rows_per_ntile = 144;
       pb.plan.b_row_base = cross ? w.base_cross : w.base_self;
       EpiAttn::Params ep{w.aoh, x3 ? w.aol : nullptr, 1e-6f};
-      if (int r = launch_gemm<144, 4, 4, EpiAttn>(pb.plan, ep, stream)) return r;
+      if (int r = launch_gemm<144, 4, 3, EpiAttn>(pb.plan, ep, stream)) return r;
     } else {
       set_last_error("big-group attention is implemented for d_model 256 only");
       return OPB_ERR_ARG;
@@ -681,7 +681,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_tiles = uc;
     pb.plan.b_rows_per_ntile = C;
     typename EpiLN<C>::Params ep{lw.ln1_g, lw.ln1_b, w.mh, x3 ? w.ml : nullptr};
-    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 4, EpiLN<C>>(pb.plan, ep, stream)) return r;
+    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), (C == 256 ? 2 : 4), EpiLN<C>>(pb.plan, ep, stream)) return r;
   }
   // ---- 6. MLP1 + ReLU   (K = [x | msg], N = 2C as two tiles of C)
   {
@@ -703,7 +703,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_tiles = uc * 2;
     pb.plan.b_rows_per_ntile = C;
     typename EpiRelu<C>::Params ep{w.hh, x3 ? w.hl : nullptr, 2 * C};
-    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 4, EpiRelu<C>>(pb.plan, ep, stream)) return r;
+    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), (C == 256 ? 2 : 4), EpiRelu<C>>(pb.plan, ep, stream)) return r;
   }
   // ---- 7. MLP2 + LN2 + residual (in place on the master copy and its planes)
   {
@@ -722,7 +722,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_tiles = uc;
     pb.plan.b_rows_per_ntile = C;
     typename EpiLNRes<C>::Params ep{lw.ln2_g, lw.ln2_b, w.xf, w.xh, x3 ? w.xl : nullptr};
-    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 4, EpiLNRes<C>>(pb.plan, ep, stream)) return r;
+    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), (C == 256 ? 2 : 4), EpiLNRes<C>>(pb.plan, ep, stream)) return r;
   }
   return OPB_OK;
 }

@@ -45,12 +45,17 @@ struct GemmPlan {
   int b_rows_per_ntile;   // row distance between consecutive n tiles of B
 };
 
-template <int BN>
+// GROUPS = number of epilogue warpgroups (4 warps each).  With one group the accumulator is double-buffered
+// (when it fits) so the next tile's MMAs overlap the epilogue; with G > 1 groups there are G accumulator
+// stages, group g owns stage g and handles every G-th tile of the CTA, so up to G epilogues run concurrently
+// (4*G warps hide each other's TMEM / memory latency) while the MMA warp fills the next free stage.
+template <int BN, int GROUPS = 1>
 struct GemmCfg {
   static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
   static constexpr int B_BYTES = BN * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int ACC_STAGES = (2 * BN <= 512) ? 2 : 1;
+  static constexpr int ACC_STAGES = GROUPS > 1 ? GROUPS : ((2 * BN <= 512) ? 2 : 1);
+  static_assert(ACC_STAGES * BN <= 512, "accumulator stages exceed the 512 TMEM columns");
   static constexpr int TMEM_COLS = (ACC_STAGES * BN <= 32)    ? 32
                                    : (ACC_STAGES * BN <= 64)  ? 64
                                    : (ACC_STAGES * BN <= 128) ? 128
@@ -60,7 +65,7 @@ struct GemmCfg {
   static_assert(STAGE_BYTES % 1024 == 0, "stage buffers must stay 1024-byte aligned for SWIZZLE_128B");
 };
 
-__host__ __device__ constexpr int gemm_smem_bytes(int BN, int stages, int epi_scratch) {
+__host__ __device__ constexpr int gemm_smem_bytes(int BN, int stages, int epi_scratch /* all groups */) {
   return 1024 /*alignment slack*/ + stages * (BLOCK_M * BLOCK_K * 2 + BN * BLOCK_K * 2) + 256 /*barriers*/ + epi_scratch;
 }
 
@@ -70,23 +75,23 @@ struct EpiCtx {
   uint32_t tmem_acc;  // TMEM address of column 0 of this tile's accumulator, lane field already = 32*quarter
   int quarter;        // TMEM lane quarter of this warp (rows quarter*32 .. +32 of the tile)
   int lane;           // lane id; this thread owns tile row quarter*32 + lane
-  int epi_warp;       // 0 .. NUM_EPI_WARPS-1
-  int col_half;       // with 8 epilogue warps: which half of the columns this warp handles (else 0)
-  uint8_t* scratch;   // Epi::kSmemBytes of shared memory shared by the epilogue warps
+  int epi_warp;       // 0 .. 3 within the group
+  int group;          // epilogue group (named barrier 1 + group is reserved for it)
+  uint8_t* scratch;   // Epi::kSmemBytes of shared memory private to this epilogue group
 };
 
-template <int BN, int STAGES, int NUM_EPI_WARPS, class Epi>
-__global__ void __launch_bounds__(64 + 32 * NUM_EPI_WARPS, 1)
+template <int BN, int STAGES, int GROUPS, class Epi>
+__global__ void __launch_bounds__(64 + 128 * GROUPS, 1)
 gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep) {
-  using Cfg = GemmCfg<BN>;
-  static_assert(NUM_EPI_WARPS == 4 || NUM_EPI_WARPS == 8, "epilogue warps must cover the 4 TMEM lane quarters");
+  using Cfg = GemmCfg<BN, GROUPS>;
+  static_assert(GROUPS >= 1 && GROUPS <= 4, "1..4 epilogue groups");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
-  uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* tempty_bar = tfull_bar + 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 4);
   uint8_t* scratch = smem + STAGES * Cfg::STAGE_BYTES + 256;
 
   const int warp = threadIdx.x >> 5;
@@ -101,9 +106,9 @@ gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep
       ptx::mbar_init(&full_bar[s], 1);
       ptx::mbar_init(&empty_bar[s], 1);
     }
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < 4; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
-      ptx::mbar_init(&tempty_bar[s], NUM_EPI_WARPS);
+      ptx::mbar_init(&tempty_bar[s], 4);
     }
     ptx::fence_barrier_init();
   }
@@ -189,11 +194,12 @@ gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep
     EpiCtx ctx;
     ctx.quarter = warp & 3;
     ctx.lane = lane;
-    ctx.epi_warp = warp - 2;
-    ctx.col_half = (NUM_EPI_WARPS == 8) ? ((warp - 2) >> 2) : 0;
-    ctx.scratch = scratch;
+    ctx.epi_warp = (warp - 2) & 3;
+    ctx.group = (warp - 2) >> 2;
+    ctx.scratch = scratch + ctx.group * Epi::kSmemBytes;
     int it = 0;
     for (int t = blockIdx.x; t < plan.num_tiles; t += gridDim.x, ++it) {
+      if (GROUPS > 1 && it % GROUPS != ctx.group) continue;
       const int acc = it % Cfg::ACC_STAGES;
       const uint32_t acc_phase = (it / Cfg::ACC_STAGES) & 1;
       tile_coords(t, ctx.m_tile, ctx.n_tile);

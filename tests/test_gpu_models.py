@@ -76,8 +76,12 @@ def test_onepose_model_default_omits_conf_matrix_and_matches():
     a(da)
     b(db)
     assert "conf_matrix" not in db
-    for k in ("i_ids", "j_ids", "mconf", "mkpts_query_f", "expec_f"):
+    # the default (single-pass) coarse matcher accumulates in a different order than the materialising
+    # two-pass one: same index sets, values to fp32 rounding
+    for k in ("i_ids", "j_ids"):
         assert torch.equal(da[k], db[k])
+    for k, tol in (("mconf", 1e-5), ("mkpts_query_f", 1e-3), ("expec_f", 1e-4)):
+        assert (da[k] - db[k]).abs().max().item() < tol, k
 
 
 def test_onepose_model_no_matches():
