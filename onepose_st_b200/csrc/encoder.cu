@@ -34,13 +34,16 @@ int split_planes(const float* x, long long stride_r, long long stride_c, const f
                  int rows, int cols, __nv_bfloat16* hi, __nv_bfloat16* lo, float* f32out, long long ld_out,
                  cudaStream_t stream);
 
+constexpr int EPI_SPLIT = 4;  // 16 epilogue warps: every thread owns one row and BN/4 of its columns
+
 __device__ __forceinline__ float elu1(float x) {
-  // torch: elu(x) + 1 with elu(x<=0) = expm1(x); keep the same two roundings
-  return x > 0.f ? __fadd_rn(x, 1.0f) : __fadd_rn(expm1f(x), 1.0f);
+  // elu(x) + 1 = x + 1 (x > 0) | exp(x) (x <= 0); ex2.approx keeps ~2^-22 relative error
+  return x > 0.f ? x + 1.0f : ptx::ex2(x * 1.4426950408889634f);
 }
 
 // ------------------------------------------------------------------------------------------------
-// Epilogues
+// Epilogues.  Thread = (row of the tile, column slice `part`); values come out of TMEM 32 columns at a
+// time; every global store is a full 32-byte sector per lane (STG.256).
 // ------------------------------------------------------------------------------------------------
 template <int C>
 struct EpiQKV {
@@ -51,11 +54,12 @@ struct EpiQKV {
     const uint8_t* row_mask;     // [R], 1 = valid
   };
   static constexpr int kSmemBytes = 0;
+  static constexpr int CPT = C / EPI_SPLIT;
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
     const float m = p.row_mask[row] ? 1.f : 0.f;
 #pragma unroll 1
-    for (int c0 = 0; c0 < C; c0 += 32) {
+    for (int c0 = ctx.part * CPT; c0 < (ctx.part + 1) * CPT; c0 += 32) {
       float v[32];
       load_acc32(ctx.tmem_acc + c0, v);
       if (ctx.n_tile == 2) {
@@ -66,18 +70,15 @@ struct EpiQKV {
         for (int i = 0; i < 32; ++i) v[i] = elu1(v[i]) * m;
       }
       if (ctx.n_tile == 0 && p.q_f32 == nullptr) {
-        store_planes32(v, p.q_hi + row * C + c0, p.q_lo ? p.q_lo + row * C + c0 : nullptr);
+        store_planes32_v8(v, p.q_hi + row * C + c0, p.q_lo ? p.q_lo + row * C + c0 : nullptr);
       } else {
-        float* dst = (ctx.n_tile == 0 ? p.q_f32 : ctx.n_tile == 1 ? p.k_f32 : p.v_f32) + row * C + c0;
-        float4* d4 = reinterpret_cast<float4*>(dst);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) d4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        store_f32x32_v8(v, (ctx.n_tile == 0 ? p.q_f32 : ctx.n_tile == 1 ? p.k_f32 : p.v_f32) + row * C + c0);
       }
     }
   }
 };
 
-// ATTN: tile = 128 rows x [128 value columns of 4 heads | 16 denominator columns], D = 32.
+// ATTN: tile = 128 rows x [128 value columns of 4 heads | 16 denominator columns], D = 32; part = head
 struct EpiAttn {
   struct Params {
     __nv_bfloat16 *o_hi, *o_lo;  // [R, 256]
@@ -89,43 +90,73 @@ struct EpiAttn {
     uint32_t dr[16];
     ptx::tmem_ld16(ctx.tmem_acc + 128, dr);
     ptx::tmem_ld_wait();
+    const int h = ctx.part;
+    float den = __uint_as_float(dr[0]);
+    den = h == 1 ? __uint_as_float(dr[1]) : den;
+    den = h == 2 ? __uint_as_float(dr[2]) : den;
+    den = h == 3 ? __uint_as_float(dr[3]) : den;
+    const float z = 1.0f / (den + p.eps);
+    float v[32];
+    load_acc32(ctx.tmem_acc + h * 32, v);
 #pragma unroll
-    for (int h = 0; h < 4; ++h) {
-      const float z = 1.0f / (__uint_as_float(dr[h]) + p.eps);
-      float v[32];
-      load_acc32(ctx.tmem_acc + h * 32, v);
-#pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] *= z;
-      const long long off = row * 256 + ctx.n_tile * 128 + h * 32;
-      store_planes32(v, p.o_hi + off, p.o_lo ? p.o_lo + off : nullptr);
-    }
+    for (int i = 0; i < 32; ++i) v[i] *= z;
+    const long long off = row * 256 + ctx.n_tile * 128 + h * 32;
+    store_planes32_v8(v, p.o_hi + off, p.o_lo ? p.o_lo + off : nullptr);
   }
 };
 
-// Row LayerNorm straight out of TMEM: the thread owns the whole row, so no cross-thread reduction.
-template <int C>
-__device__ __forceinline__ void row_mean_rstd(uint32_t tmem_acc, float& mean, float& rstd) {
-  float s = 0.f;
-#pragma unroll 1
-  for (int c0 = 0; c0 < C; c0 += 32) {
-    float v[32];
-    load_acc32(tmem_acc + c0, v);
+// Row LayerNorm statistics with the row's columns spread over EPI_SPLIT warps: each thread keeps its CPT
+// values in registers (one TMEM read), partial sums meet in shared memory behind a per-quarter named
+// barrier; two-pass (mean, then centred squares) like torch.
+template <int CPT>
+__device__ __forceinline__ void row_mean_rstd_split(const EpiCtx& ctx, const float (&x)[CPT], int C, float& mean, float& rstd) {
+  float* red = reinterpret_cast<float*>(ctx.scratch);  // [2][4 quarters][EPI_SPLIT][32]
+  const int bar_id = 1 + ctx.group * 4 + ctx.quarter;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) s += v[i];
+  for (int i = 0; i < CPT; i += 4) {
+    s0 += x[i];
+    s1 += x[i + 1];
+    s2 += x[i + 2];
+    s3 += x[i + 3];
   }
-  mean = s * (1.0f / C);
-  float q = 0.f;
-#pragma unroll 1
-  for (int c0 = 0; c0 < C; c0 += 32) {
-    float v[32];
-    load_acc32(tmem_acc + c0, v);
+  float* slot = red + (ctx.quarter * EPI_SPLIT) * 32 + ctx.lane;
+  slot[ctx.part * 32] = (s0 + s1) + (s2 + s3);
+  ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);
+  float tot = 0.f;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const float d = v[i] - mean;
-      q = fmaf(d, d, q);
-    }
+  for (int q = 0; q < EPI_SPLIT; ++q) tot += slot[q * 32];
+  mean = tot / static_cast<float>(C);
+  float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+#pragma unroll
+  for (int i = 0; i < CPT; i += 4) {
+    const float d0 = x[i] - mean, d1 = x[i + 1] - mean, d2 = x[i + 2] - mean, d3 = x[i + 3] - mean;
+    q0 = fmaf(d0, d0, q0);
+    q1 = fmaf(d1, d1, q1);
+    q2 = fmaf(d2, d2, q2);
+    q3 = fmaf(d3, d3, q3);
   }
-  rstd = rsqrtf(q * (1.0f / C) + 1e-5f);
+  float* slot2 = slot + 4 * EPI_SPLIT * 32;
+  slot2[ctx.part * 32] = (q0 + q1) + (q2 + q3);
+  ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);
+  float var = 0.f;
+#pragma unroll
+  for (int q = 0; q < EPI_SPLIT; ++q) var += slot2[q * 32];
+  rstd = rsqrtf(var / static_cast<float>(C) + 1e-5f);
+}
+
+constexpr int kLnScratch = 2 * 4 * EPI_SPLIT * 32 * 4;
+
+template <int CPT>
+__device__ __forceinline__ void load_row_slice(const EpiCtx& ctx, float (&x)[CPT]) {
+#pragma unroll
+  for (int c = 0; c < CPT; c += 32) {
+    uint32_t r[32];
+    ptx::tmem_ld32(ctx.tmem_acc + ctx.part * CPT + c, r);
+    ptx::tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) x[c + i] = __uint_as_float(r[i]);
+  }
 }
 
 template <int C>
@@ -134,18 +165,21 @@ struct EpiLN {  // MERGE epilogue: LayerNorm1 -> planes
     const float *gamma, *beta;
     __nv_bfloat16 *o_hi, *o_lo;
   };
-  static constexpr int kSmemBytes = 0;
+  static constexpr int kSmemBytes = kLnScratch;
+  static constexpr int CPT = C / EPI_SPLIT;
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
+    float x[CPT];
+    load_row_slice<CPT>(ctx, x);
     float mean, rstd;
-    row_mean_rstd<C>(ctx.tmem_acc, mean, rstd);
-#pragma unroll 1
-    for (int c0 = 0; c0 < C; c0 += 32) {
-      float v[32];
-      load_acc32(ctx.tmem_acc + c0, v);
+    row_mean_rstd_split<CPT>(ctx, x, C, mean, rstd);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = (v[i] - mean) * rstd * __ldg(p.gamma + c0 + i) + __ldg(p.beta + c0 + i);
-      store_planes32(v, p.o_hi + row * C + c0, p.o_lo ? p.o_lo + row * C + c0 : nullptr);
+    for (int c = 0; c < CPT; c += 32) {
+      const int c0 = ctx.part * CPT + c;
+      float v[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = (x[c + i] - mean) * rstd * __ldg(p.gamma + c0 + i) + __ldg(p.beta + c0 + i);
+      store_planes32_v8(v, p.o_hi + row * C + c0, p.o_lo ? p.o_lo + row * C + c0 : nullptr);
     }
   }
 };
@@ -157,16 +191,17 @@ struct EpiRelu {  // MLP1 epilogue: ReLU -> planes [R, ld]
     int ld;
   };
   static constexpr int kSmemBytes = 0;
+  static constexpr int CPT = BN / EPI_SPLIT;
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
+    for (int c0 = ctx.part * CPT; c0 < (ctx.part + 1) * CPT; c0 += 32) {
       float v[32];
       load_acc32(ctx.tmem_acc + c0, v);
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
       const long long off = row * p.ld + ctx.n_tile * BN + c0;
-      store_planes32(v, p.o_hi + off, p.o_lo ? p.o_lo + off : nullptr);
+      store_planes32_v8(v, p.o_hi + off, p.o_lo ? p.o_lo + off : nullptr);
     }
   }
 };
@@ -178,27 +213,31 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc); refresh the plane
     float* x_f32;
     __nv_bfloat16 *x_hi, *x_lo;
   };
-  static constexpr int kSmemBytes = 0;
+  static constexpr int kSmemBytes = kLnScratch;
+  static constexpr int CPT = C / EPI_SPLIT;
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
+    float x[CPT];
+    load_row_slice<CPT>(ctx, x);
     float mean, rstd;
-    row_mean_rstd<C>(ctx.tmem_acc, mean, rstd);
-#pragma unroll 1
-    for (int c0 = 0; c0 < C; c0 += 32) {
-      float v[32];
-      load_acc32(ctx.tmem_acc + c0, v);
-      float4* x4 = reinterpret_cast<float4*>(p.x_f32 + row * C + c0);
+    row_mean_rstd_split<CPT>(ctx, x, C, mean, rstd);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float4 xo = x4[i];
-        const int c = c0 + 4 * i;
-        v[4 * i + 0] = xo.x + ((v[4 * i + 0] - mean) * rstd * __ldg(p.gamma + c + 0) + __ldg(p.beta + c + 0));
-        v[4 * i + 1] = xo.y + ((v[4 * i + 1] - mean) * rstd * __ldg(p.gamma + c + 1) + __ldg(p.beta + c + 1));
-        v[4 * i + 2] = xo.z + ((v[4 * i + 2] - mean) * rstd * __ldg(p.gamma + c + 2) + __ldg(p.beta + c + 2));
-        v[4 * i + 3] = xo.w + ((v[4 * i + 3] - mean) * rstd * __ldg(p.gamma + c + 3) + __ldg(p.beta + c + 3));
-        x4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    for (int c = 0; c < CPT; c += 32) {
+      const int c0 = ctx.part * CPT + c;
+      float* xr = p.x_f32 + row * C + c0;
+      float v[32];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint32_t o[8];
+        ptx::ld_global_v8(xr + 8 * i, o);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int cc = c0 + 8 * i + k;
+          v[8 * i + k] = __uint_as_float(o[k]) + ((x[c + 8 * i + k] - mean) * rstd * __ldg(p.gamma + cc) + __ldg(p.beta + cc));
+        }
       }
-      store_planes32(v, p.x_hi + row * C + c0, p.x_lo ? p.x_lo + row * C + c0 : nullptr);
+      store_f32x32_v8(v, xr);
+      store_planes32_v8(v, p.x_hi + row * C + c0, p.x_lo ? p.x_lo + row * C + c0 : nullptr);
     }
   }
 };
@@ -598,7 +637,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       pb.plan.num_n_tiles = nc;
       pb.plan.num_tiles = mc * nc;
       pb.plan.b_rows_per_ntile = C;
-      return launch_gemm<C, (C == 256 ? 4 : 6), (C == 256 ? 2 : 4), EpiQKV<C>>(pb.plan, ep, stream);
+      return launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiQKV<C>, EPI_SPLIT>(pb.plan, ep, stream);
     };
     if (q_streams == src_streams) {
       if (int r = launch(qb, qc, 0, 3)) return r;
@@ -640,7 +679,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       pb.plan.b_rows_per_ntile = 144;
       pb.plan.b_row_base = cross ? w.base_cross : w.base_self;
       EpiAttn::Params ep{w.aoh, x3 ? w.aol : nullptr, 1e-6f};
-      if (int r = launch_gemm<144, 4, 3, EpiAttn>(pb.plan, ep, stream)) return r;
+      if (int r = launch_gemm<144, 4, 1, EpiAttn, EPI_SPLIT>(pb.plan, ep, stream)) return r;
     } else {
       set_last_error("big-group attention is implemented for d_model 256 only");
       return OPB_ERR_ARG;
@@ -681,7 +720,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_tiles = uc;
     pb.plan.b_rows_per_ntile = C;
     typename EpiLN<C>::Params ep{lw.ln1_g, lw.ln1_b, w.mh, x3 ? w.ml : nullptr};
-    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), (C == 256 ? 2 : 4), EpiLN<C>>(pb.plan, ep, stream)) return r;
+    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLN<C>, EPI_SPLIT>(pb.plan, ep, stream)) return r;
   }
   // ---- 6. MLP1 + ReLU   (K = [x | msg], N = 2C as two tiles of C)
   {
@@ -703,7 +742,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_tiles = uc * 2;
     pb.plan.b_rows_per_ntile = C;
     typename EpiRelu<C>::Params ep{w.hh, x3 ? w.hl : nullptr, 2 * C};
-    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), (C == 256 ? 2 : 4), EpiRelu<C>>(pb.plan, ep, stream)) return r;
+    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiRelu<C>, EPI_SPLIT>(pb.plan, ep, stream)) return r;
   }
   // ---- 7. MLP2 + LN2 + residual (in place on the master copy and its planes)
   {
@@ -722,7 +761,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_tiles = uc;
     pb.plan.b_rows_per_ntile = C;
     typename EpiLNRes<C>::Params ep{lw.ln2_g, lw.ln2_b, w.xf, w.xh, x3 ? w.xl : nullptr};
-    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), (C == 256 ? 2 : 4), EpiLNRes<C>>(pb.plan, ep, stream)) return r;
+    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLNRes<C>, EPI_SPLIT>(pb.plan, ep, stream)) return r;
   }
   return OPB_OK;
 }

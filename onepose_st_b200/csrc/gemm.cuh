@@ -76,15 +76,20 @@ struct EpiCtx {
   int quarter;        // TMEM lane quarter of this warp (rows quarter*32 .. +32 of the tile)
   int lane;           // lane id; this thread owns tile row quarter*32 + lane
   int epi_warp;       // 0 .. 3 within the group
-  int group;          // epilogue group (named barrier 1 + group is reserved for it)
+  int group;          // epilogue group (named barriers 1 + 4*group .. 4 + 4*group are reserved for it)
+  int part;           // with SPLIT > 1: which slice of the tile's columns this warp handles (0 .. SPLIT-1)
   uint8_t* scratch;   // Epi::kSmemBytes of shared memory private to this epilogue group
 };
 
-template <int BN, int STAGES, int GROUPS, class Epi>
-__global__ void __launch_bounds__(64 + 128 * GROUPS, 1)
+// SPLIT = warps per TMEM lane quarter inside one group: the tile's columns are divided among them, so a
+// single tile's epilogue runs on 4*SPLIT warps (what matters when a CTA has only one or two tiles).
+template <int BN, int STAGES, int GROUPS, int SPLIT, class Epi>
+__global__ void __launch_bounds__(64 + 128 * GROUPS * SPLIT, 1)
 gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep) {
   using Cfg = GemmCfg<BN, GROUPS>;
   static_assert(GROUPS >= 1 && GROUPS <= 4, "1..4 epilogue groups");
+  static_assert(SPLIT == 1 || SPLIT == 2 || SPLIT == 4, "1, 2 or 4 warps per lane quarter");
+  static_assert(GROUPS * SPLIT <= 4, "at most 16 epilogue warps");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
@@ -108,7 +113,7 @@ gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep
     }
     for (int s = 0; s < 4; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
-      ptx::mbar_init(&tempty_bar[s], 4);
+      ptx::mbar_init(&tempty_bar[s], 4 * SPLIT);
     }
     ptx::fence_barrier_init();
   }
@@ -195,7 +200,8 @@ gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep
     ctx.quarter = warp & 3;
     ctx.lane = lane;
     ctx.epi_warp = (warp - 2) & 3;
-    ctx.group = (warp - 2) >> 2;
+    ctx.group = ((warp - 2) >> 2) / SPLIT;
+    ctx.part = ((warp - 2) >> 2) % SPLIT;
     ctx.scratch = scratch + ctx.group * Epi::kSmemBytes;
     int it = 0;
     for (int t = blockIdx.x; t < plan.num_tiles; t += gridDim.x, ++it) {
@@ -249,6 +255,33 @@ __device__ __forceinline__ void store_planes32(const float (&v)[32], __nv_bfloat
 #pragma unroll
     for (int i = 0; i < 4; ++i) pl[i] = make_uint4(l[4 * i], l[4 * i + 1], l[4 * i + 2], l[4 * i + 3]);
   }
+}
+
+// Same as store_planes32 with 256-bit stores (hi / lo must be 32-byte aligned).
+__device__ __forceinline__ void store_planes32_v8(const float (&v)[32], __nv_bfloat16* hi, __nv_bfloat16* lo) {
+  uint32_t h[16], l[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const __nv_bfloat162 hh = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    const float2 hf = __bfloat1622float2(hh);
+    const __nv_bfloat162 ll = __floats2bfloat162_rn(v[2 * i] - hf.x, v[2 * i + 1] - hf.y);
+    h[i] = *reinterpret_cast<const uint32_t*>(&hh);
+    l[i] = *reinterpret_cast<const uint32_t*>(&ll);
+  }
+  ptx::st_global_v8(hi, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+  ptx::st_global_v8(hi + 16, h[8], h[9], h[10], h[11], h[12], h[13], h[14], h[15]);
+  if (lo != nullptr) {
+    ptx::st_global_v8(lo, l[0], l[1], l[2], l[3], l[4], l[5], l[6], l[7]);
+    ptx::st_global_v8(lo + 16, l[8], l[9], l[10], l[11], l[12], l[13], l[14], l[15]);
+  }
+}
+// 32 consecutive fp32 values of one row with 256-bit stores (dst 32-byte aligned)
+__device__ __forceinline__ void store_f32x32_v8(const float (&v)[32], float* dst) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    ptx::st_global_v8(dst + 8 * i, __float_as_uint(v[8 * i]), __float_as_uint(v[8 * i + 1]), __float_as_uint(v[8 * i + 2]),
+                      __float_as_uint(v[8 * i + 3]), __float_as_uint(v[8 * i + 4]), __float_as_uint(v[8 * i + 5]),
+                      __float_as_uint(v[8 * i + 6]), __float_as_uint(v[8 * i + 7]));
 }
 
 __device__ __forceinline__ void load_acc32(uint32_t taddr, float (&v)[32]) {

@@ -84,10 +84,10 @@ struct PlanBuilder {
   }
 };
 
-template <int BN, int STAGES, int GROUPS, class Epi>
+template <int BN, int STAGES, int GROUPS, class Epi, int SPLIT = 1>
 int launch_gemm(const GemmPlan& plan, const typename Epi::Params& ep, cudaStream_t stream, int max_ctas = 0) {
   if (plan.num_tiles <= 0) return OPB_OK;
-  auto kern = gemm_kernel<BN, STAGES, GROUPS, Epi>;
+  auto kern = gemm_kernel<BN, STAGES, GROUPS, SPLIT, Epi>;
   constexpr int smem = gemm_smem_bytes(BN, STAGES, GROUPS * Epi::kSmemBytes);
   static_assert(smem <= 227 * 1024, "shared memory budget exceeded");
   static bool configured = false;  // per instantiation
@@ -98,7 +98,7 @@ int launch_gemm(const GemmPlan& plan, const typename Epi::Params& ep, cudaStream
   int grid = num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (plan.num_tiles < grid) grid = plan.num_tiles;
-  kern<<<grid, 64 + 128 * GROUPS, smem, stream>>>(plan, ep);
+  kern<<<grid, 64 + 128 * GROUPS * SPLIT, smem, stream>>>(plan, ep);
   count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
