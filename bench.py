@@ -38,7 +38,7 @@ def parse_args():
     ap.add_argument("--points", type=int, default=8000, help="3D points of the object model (L)")
     ap.add_argument("--size", type=int, default=512, help="query crop side (pixels)")
     ap.add_argument("--frames-per-step", type=int, default=16, help="frames each rank processes per step")
-    ap.add_argument("--batch", type=int, default=1, help="frames per forward call (dict contract N)")
+    ap.add_argument("--batch", type=int, default=8, help="frames per forward call (dict contract N)")
     ap.add_argument("--pool", type=int, default=500, help="frames of the synthetic sequence")
     ap.add_argument("--plant", type=int, default=1000, help="planted 2D-3D correspondences")
     ap.add_argument("--precision", type=int, default=3, choices=[1, 3], help="3 = bf16x3 split (fp32-grade), 1 = bf16")
