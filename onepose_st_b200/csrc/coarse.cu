@@ -640,8 +640,9 @@ __global__ void cand_pick_kernel(const Candidate* __restrict__ cand, const int* 
   }
 }
 
-// single-block ordered compaction over the N*L rows (ascending (b, i) like torch.where): every thread owns a
-// contiguous range of rows, counts its matches, one block-wide exclusive scan, then writes its range
+// single-block ordered compaction over the N*L rows (ascending (b, i) like torch.where).  Warp w owns the
+// contiguous row segment [w*seg, (w+1)*seg) and walks it 32 rows at a time (coalesced loads, ballot + popc for
+// the in-warp order); one block-wide scan of the 32 warp totals in between the counting and the writing walk.
 __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ rowj, const unsigned* __restrict__ rowmax,
                                                        int n_rows, int L, long long* __restrict__ b_ids,
                                                        long long* __restrict__ i_ids, long long* __restrict__ j_ids,
@@ -650,20 +651,19 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
                                                        int fast) {
   __shared__ int warp_sums[32];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const int per = (n_rows + 1023) / 1024;
-  const int r0 = min(t * per, n_rows), r1 = min(r0 + per, n_rows);
+  const int seg = ((n_rows + 31) / 32 + 31) / 32 * 32;  // rows per warp, a multiple of 32
+  const int r0 = warp * seg, r1 = min(r0 + seg, n_rows);
   int cnt = 0;
-  for (int r = r0; r < r1; ++r) cnt += rowj[r] != kNoMatch;
-  int incl = cnt;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int y = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += y;
+  for (int base = r0; base < r1; base += 32) {
+    const int r = base + lane;
+    const bool f = r < r1 && rowj[r] != kNoMatch;
+    cnt += __popc(__ballot_sync(0xffffffffu, f));
   }
-  if (lane == 31) warp_sums[warp] = incl;
+  if (lane == 0) warp_sums[warp] = cnt;
   __syncthreads();
   if (warp == 0) {
-    int ws = warp_sums[lane], wi = ws;
+    const int ws = warp_sums[lane];
+    int wi = ws;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const int y = __shfl_up_sync(0xffffffffu, wi, o);
@@ -680,18 +680,21 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
     }
   }
   __syncthreads();
-  int pos = warp_sums[warp] + incl - cnt;
-  for (int r = r0; r < r1; ++r) {
-    const int j = rowj[r];
+  int pos = warp_sums[warp];
+  for (int base = r0; base < r1; base += 32) {
+    const int r = base + lane;
+    const int j = r < r1 ? rowj[r] : kNoMatch;
+    const unsigned ball = __ballot_sync(0xffffffffu, j != kNoMatch);
     if (j != kNoMatch) {
-      if (pos < capacity) {
-        b_ids[pos] = r / L;
-        i_ids[pos] = r % L;
-        j_ids[pos] = j;
-        mconf[pos] = __uint_as_float(rowmax[r]);
+      const int o = pos + __popc(ball & ((1u << lane) - 1));
+      if (o < capacity) {
+        b_ids[o] = r / L;
+        i_ids[o] = r % L;
+        j_ids[o] = j;
+        mconf[o] = __uint_as_float(rowmax[r]);
       }
-      ++pos;
     }
+    pos += __popc(ball);
   }
 }
 

@@ -22,7 +22,7 @@
 //   4 ATTN     phi(Q) x blockdiag(KV)  epilogue: divide by (phi(Q).Ksum + eps)  -> planes
 //   5 MERGE    x Wm^T           epilogue: LayerNorm1 -> planes
 //   6 MLP1     [x|msg] x W1^T   epilogue: ReLU -> planes
-//   7 MLP2     x W2^T           epilogue: LayerNorm2, + residual -> fp32 master + planes (in place)
+//   7 MLP2     x W2^T           epilogue: LayerNorm2, + residual -> planes of x (in place; x = hi + lo is the master)
 #include <cmath>
 #include <cuda_pipeline.h>
 #include "host.cuh"
@@ -207,10 +207,9 @@ struct EpiRelu {  // MLP1 epilogue: ReLU -> planes [R, ld]
 };
 
 template <int C>
-struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc); refresh the planes of x
-  struct Params {
+struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual stream lives in its two bf16 planes
+  struct Params {   // (x = hi + lo, ~2^-17 relative): no separate fp32 master copy is read or written.
     const float *gamma, *beta;
-    float* x_f32;
     __nv_bfloat16 *x_hi, *x_lo;
   };
   static constexpr int kSmemBytes = kLnScratch;
@@ -224,20 +223,24 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc); refresh the plane
 #pragma unroll
     for (int c = 0; c < CPT; c += 32) {
       const int c0 = ctx.part * CPT + c;
-      float* xr = p.x_f32 + row * C + c0;
+      __nv_bfloat16* ph = p.x_hi + row * C + c0;
+      __nv_bfloat16* pl = p.x_lo + row * C + c0;
       float v[32];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint32_t o[8];
-        ptx::ld_global_v8(xr + 8 * i, o);
+      for (int i = 0; i < 2; ++i) {
+        uint32_t h[8], l[8];
+        ptx::ld_global_v8(ph + 16 * i, h);
+        ptx::ld_global_v8(pl + 16 * i, l);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          const int cc = c0 + 8 * i + k;
-          v[8 * i + k] = __uint_as_float(o[k]) + ((x[c + 8 * i + k] - mean) * rstd * __ldg(p.gamma + cc) + __ldg(p.beta + cc));
+          const float2 hf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h[k]));
+          const float2 lf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&l[k]));
+          const int e = 16 * i + 2 * k, cc = c0 + e;
+          v[e] = (hf.x + lf.x) + ((x[c + e] - mean) * rstd * __ldg(p.gamma + cc) + __ldg(p.beta + cc));
+          v[e + 1] = (hf.y + lf.y) + ((x[c + e + 1] - mean) * rstd * __ldg(p.gamma + cc + 1) + __ldg(p.beta + cc + 1));
         }
       }
-      store_f32x32_v8(v, xr);
-      store_planes32_v8(v, p.x_hi + row * C + c0, p.x_lo ? p.x_lo + row * C + c0 : nullptr);
+      store_planes32_v8(v, ph, pl);
     }
   }
 };
@@ -415,7 +418,7 @@ __global__ void __launch_bounds__(128) attn_small_kernel(const float* __restrict
 // Writes rows [row0 + n*P, +P): valid rows get the data, pad rows zeros; also the row mask.
 __global__ void copy_in_kernel(const float* __restrict__ x, long long sn, long long sl, long long sc,
                                const float* __restrict__ add, const uint8_t* __restrict__ mask, int len, int P, int C,
-                               int row0, float* __restrict__ xf, __nv_bfloat16* __restrict__ xh,
+                               int row0, __nv_bfloat16* __restrict__ xh,
                                __nv_bfloat16* __restrict__ xl, uint8_t* __restrict__ row_mask) {
   __shared__ float tile[32][33];
   const int n = blockIdx.z;
@@ -442,22 +445,35 @@ __global__ void copy_in_kernel(const float* __restrict__ x, long long sn, long l
       const long long o = (static_cast<long long>(row0) + static_cast<long long>(n) * P + l) * C + c;
       __nv_bfloat16 h_, l_;
       split_bf16(val, h_, l_);
-      xf[o] = val;
       xh[o] = h_;
-      if (xl) xl[o] = l_;
+      xl[o] = l_;
       if (c == 0)
         row_mask[row0 + n * P + l] = (l < len) ? (mask ? (mask[static_cast<long long>(n) * len + l] != 0) : 1) : 0;
     }
   }
 }
 
-__global__ void copy_out_kernel(const float* __restrict__ xf, int len, int P, int C, int row0, float* __restrict__ out) {
+__global__ void copy_out_kernel(const __nv_bfloat16* __restrict__ xh, const __nv_bfloat16* __restrict__ xl, int len, int P,
+                                int C, int row0, float* __restrict__ out) {
   const int n = blockIdx.z;
-  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;  // float4 index within [len, C]
-  const long long total4 = static_cast<long long>(len) * C / 4;
-  if (i >= total4) return;
-  const float4 v = reinterpret_cast<const float4*>(xf + (static_cast<long long>(row0) + static_cast<long long>(n) * P) * C)[i];
-  reinterpret_cast<float4*>(out + static_cast<long long>(n) * len * C)[i] = v;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;  // group of 8 elements within [len, C]
+  const long long total8 = static_cast<long long>(len) * C / 8;
+  if (i >= total8) return;
+  const long long src = (static_cast<long long>(row0) + static_cast<long long>(n) * P) * C + i * 8;
+  const uint4 h = *reinterpret_cast<const uint4*>(xh + src);
+  const uint4 l = *reinterpret_cast<const uint4*>(xl + src);
+  const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
+  float v[8];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 hf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&hw[k]));
+    const float2 lf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&lw[k]));
+    v[2 * k] = hf.x + lf.x;
+    v[2 * k + 1] = hf.y + lf.y;
+  }
+  float4* o = reinterpret_cast<float4*>(out + static_cast<long long>(n) * len * C + i * 8);
+  o[0] = make_float4(v[0], v[1], v[2], v[3]);
+  o[1] = make_float4(v[4], v[5], v[6], v[7]);
 }
 
 __global__ void fill_row_base_kernel(int* base_self, int* base_cross, int tiles0, int tiles1, int N, int rows_per_group) {
@@ -512,7 +528,6 @@ static LayerWeights view_layer(const void* buf, int C) {
 }
 
 struct Workspace {
-  float* xf;
   __nv_bfloat16 *xh, *xl, *qh, *ql, *aoh, *aol, *mh, *ml, *hh, *hl, *kvb_h, *kvb_l;
   float *qf, *kf, *vf, *kv_partial;
   uint8_t* row_mask;
@@ -557,7 +572,6 @@ static Workspace carve(void* base, const Geometry& g) {
     return p;
   };
   const size_t RC = static_cast<size_t>(g.R) * g.C;
-  w.xf = static_cast<float*>(take(RC * 4));
   w.xh = static_cast<__nv_bfloat16*>(take(RC * 2));
   w.xl = static_cast<__nv_bfloat16*>(take(RC * 2));
   w.qh = static_cast<__nv_bfloat16*>(take(RC * 2));
@@ -760,7 +774,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_n_tiles = 1;
     pb.plan.num_tiles = uc;
     pb.plan.b_rows_per_ntile = C;
-    typename EpiLNRes<C>::Params ep{lw.ln2_g, lw.ln2_b, w.xf, w.xh, x3 ? w.xl : nullptr};
+    typename EpiLNRes<C>::Params ep{lw.ln2_g, lw.ln2_b, w.xh, w.xl};
     if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLNRes<C>, EPI_SPLIT>(pb.plan, ep, stream)) return r;
   }
   return OPB_OK;
@@ -837,16 +851,15 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
     for (int s = 0; s < 2; ++s) {
       const size_t n = pad_hi[s] - pad_lo[s];
       if (n == 0) continue;
-      OPB_CHECK_CUDA(cudaMemsetAsync(w.xf + pad_lo[s] * C, 0, n * C * 4, stream));
       OPB_CHECK_CUDA(cudaMemsetAsync(w.xh + pad_lo[s] * C, 0, n * C * 2, stream));
       OPB_CHECK_CUDA(cudaMemsetAsync(w.xl + pad_lo[s] * C, 0, n * C * 2, stream));
       OPB_CHECK_CUDA(cudaMemsetAsync(w.row_mask + pad_lo[s], 0, n, stream));
     }
   }
   copy_in_kernel<<<dim3((C + 31) / 32, (g.P0 + 31) / 32, n_batch), dim3(32, 8), 0, stream>>>(
-      x0, x0_sn, x0_sl, x0_sc, add0, mask0, len0, g.P0, C, 0, w.xf, w.xh, w.xl, w.row_mask);
+      x0, x0_sn, x0_sl, x0_sc, add0, mask0, len0, g.P0, C, 0, w.xh, w.xl, w.row_mask);
   copy_in_kernel<<<dim3((C + 31) / 32, (g.P1 + 31) / 32, n_batch), dim3(32, 8), 0, stream>>>(
-      x1, x1_sn, x1_sl, x1_sc, add1, mask1, len1, g.P1, C, row1, w.xf, w.xh, w.xl, w.row_mask);
+      x1, x1_sn, x1_sl, x1_sc, add1, mask1, len1, g.P1, C, row1, w.xh, w.xl, w.row_mask);
   count_launch(2 + (big_groups ? 1 : 0));
   if (big_groups) {  // off-diagonal / unused entries of the block-diagonal attention operand stay zero
     OPB_CHECK_CUDA(cudaMemsetAsync(w.kvb_h, 0, static_cast<size_t>(g.G) * 2 * 144 * 128 * 2, stream));
@@ -873,10 +886,10 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
     if (r) return r;
   }
   const int threads = 256;
-  copy_out_kernel<<<dim3((static_cast<long long>(len0) * C / 4 + threads - 1) / threads, 1, n_batch), threads, 0, stream>>>(
-      w.xf, len0, g.P0, C, 0, out0);
-  copy_out_kernel<<<dim3((static_cast<long long>(len1) * C / 4 + threads - 1) / threads, 1, n_batch), threads, 0, stream>>>(
-      w.xf, len1, g.P1, C, row1, out1);
+  copy_out_kernel<<<dim3((static_cast<long long>(len0) * C / 8 + threads - 1) / threads, 1, n_batch), threads, 0, stream>>>(
+      w.xh, w.xl, len0, g.P0, C, 0, out0);
+  copy_out_kernel<<<dim3((static_cast<long long>(len1) * C / 8 + threads - 1) / threads, 1, n_batch), threads, 0, stream>>>(
+      w.xh, w.xl, len1, g.P1, C, row1, out1);
   count_launch(2);
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
