@@ -122,6 +122,13 @@ int opb200_linear_attention(const float* q, const float* k, const float* v, cons
                             const uint8_t* kv_mask, int n_batch, int L, int S, int H, int D, float eps, float* out,
                             void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- Backbone glue (channels-last fp32; the convolutions stay cuDNN) -----------------------------------
+ * dst[n, y, x, c] += bilinear x2 upsampling (align_corners = True) of src[n, :, :, c]: the FPN top-down add of
+ * ResNetFPN_8_2.forward (src/models/OnePosePlus/backbone/resnet.py:141-164).  src [n, Hs, Ws, C], dst [n, 2Hs, 2Ws, C]. */
+int opb200_upsample2x_add_nhwc(const float* src, int n_batch, int Hs, int Ws, int C, float* dst, void* stream);
+/* x[p, c] = leaky_relu(x[p, c] + bias[c], slope): folded-BatchNorm shift + nn.LeakyReLU of the FPN heads. */
+int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels, int C, float slope, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,100 @@
+// Memory-bound glue of the ResNet-FPN backbone (channels-last fp32), fused so each FPN level makes one pass:
+//   opb200_upsample2x_add_nhwc   dst += bilinear_x2(src), align_corners=True
+//                                (F.interpolate(scale_factor=2, mode='bilinear', align_corners=True) + add;
+//                                 reference: src/models/OnePosePlus/backbone/resnet.py:141-164 FPN top-down path,
+//                                 submodules/LoFTR/src/loftr/backbone/resnet_fpn.py:100-118)
+//   opb200_bias_leaky_relu_nhwc  x = leaky_relu(x + bias[c])   (folded BatchNorm shift + nn.LeakyReLU of the
+//                                 layer{1,2}_outconv2 heads)
+// The convolutions themselves stay cuDNN; these two kernels only remove extra full
+// passes over the 1/2- and 1/4-resolution maps.  HBM-bound: 8 B (read+write dst) + ~1 B (src) per element.
+#include "host.cuh"
+#include "../../include/opb200.h"
+
+namespace opb {
+
+__global__ void __launch_bounds__(256) upsample2x_add_kernel(const float4* __restrict__ src, int N, int Hs, int Ws, int C4,
+                                                             float4* __restrict__ dst, float ry, float rx) {
+  const int Ho = 2 * Hs, Wo = 2 * Ws;
+  const long long total = static_cast<long long>(N) * Ho * Wo * C4;
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % C4);
+    long long p = t / C4;
+    const int x = static_cast<int>(p % Wo);
+    p /= Wo;
+    const int y = static_cast<int>(p % Ho);
+    const int n = static_cast<int>(p / Ho);
+    // torch's area_pixel_compute_source_index(align_corners=True): src = scale * dst
+    const float sy = ry * y, sx = rx * x;
+    const int y0 = static_cast<int>(sy), x0 = static_cast<int>(sx);
+    const int y1 = y0 + (y0 < Hs - 1), x1 = x0 + (x0 < Ws - 1);
+    const float ly1 = sy - y0, lx1 = sx - x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
+    const float4* s = src + static_cast<long long>(n) * Hs * Ws * C4;
+    const float4 v00 = __ldg(s + (static_cast<long long>(y0) * Ws + x0) * C4 + c);
+    const float4 v01 = __ldg(s + (static_cast<long long>(y0) * Ws + x1) * C4 + c);
+    const float4 v10 = __ldg(s + (static_cast<long long>(y1) * Ws + x0) * C4 + c);
+    const float4 v11 = __ldg(s + (static_cast<long long>(y1) * Ws + x1) * C4 + c);
+    float4 d = dst[t];
+    d.x += ly0 * (lx0 * v00.x + lx1 * v01.x) + ly1 * (lx0 * v10.x + lx1 * v11.x);
+    d.y += ly0 * (lx0 * v00.y + lx1 * v01.y) + ly1 * (lx0 * v10.y + lx1 * v11.y);
+    d.z += ly0 * (lx0 * v00.z + lx1 * v01.z) + ly1 * (lx0 * v10.z + lx1 * v11.z);
+    d.w += ly0 * (lx0 * v00.w + lx1 * v01.w) + ly1 * (lx0 * v10.w + lx1 * v11.w);
+    dst[t] = d;
+  }
+}
+
+__global__ void __launch_bounds__(256) bias_leaky_relu_kernel(float4* __restrict__ x, const float4* __restrict__ bias,
+                                                              long long total4, int C4, float slope) {
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total4;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float4 b = __ldg(bias + t % C4);
+    float4 v = x[t];
+    v.x += b.x, v.y += b.y, v.z += b.z, v.w += b.w;
+    v.x = v.x > 0.f ? v.x : v.x * slope;
+    v.y = v.y > 0.f ? v.y : v.y * slope;
+    v.z = v.z > 0.f ? v.z : v.z * slope;
+    v.w = v.w > 0.f ? v.w : v.w * slope;
+    x[t] = v;
+  }
+}
+
+}  // namespace opb
+
+using namespace opb;
+
+extern "C" {
+
+int opb200_upsample2x_add_nhwc(const float* src, int n_batch, int Hs, int Ws, int C, float* dst, void* stream_) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(src && dst, "null pointer");
+  OPB_CHECK_ARG(n_batch >= 1 && Hs >= 1 && Ws >= 1 && C >= 4 && C % 4 == 0, "bad shape (C must be a multiple of 4)");
+  OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0, "16-byte alignment");
+  const long long total = static_cast<long long>(n_batch) * 4 * Hs * Ws * (C / 4);
+  const float ry = Hs > 1 ? static_cast<float>(Hs - 1) / static_cast<float>(2 * Hs - 1) : 0.f;
+  const float rx = Ws > 1 ? static_cast<float>(Ws - 1) / static_cast<float>(2 * Ws - 1) : 0.f;
+  const long long blocks = (total + 255) / 256;
+  const int grid = static_cast<int>(blocks < num_sms() * 16LL ? blocks : num_sms() * 16LL);
+  upsample2x_add_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      reinterpret_cast<const float4*>(src), n_batch, Hs, Ws, C / 4, reinterpret_cast<float4*>(dst), ry, rx);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels, int C, float slope, void* stream_) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(x && bias, "null pointer");
+  OPB_CHECK_ARG(n_pixels >= 1 && C >= 4 && C % 4 == 0, "bad shape (C must be a multiple of 4)");
+  OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(bias) & 15) == 0, "16-byte alignment");
+  const long long total4 = n_pixels * (C / 4);
+  const long long blocks = (total4 + 255) / 256;
+  const int grid = static_cast<int>(blocks < num_sms() * 16LL ? blocks : num_sms() * 16LL);
+  bias_leaky_relu_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(reinterpret_cast<float4*>(x),
+                                                                                reinterpret_cast<const float4*>(bias), total4,
+                                                                                C / 4, slope);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+}  // extern "C"

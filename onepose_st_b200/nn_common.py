@@ -145,7 +145,8 @@ class FusedBackbone:
     @staticmethod
     def _head(x, head):
         (w0, b0), (w1, b1), slope = head
-        return F.conv2d(F.leaky_relu(F.conv2d(x, w0, b0, 1, 1), slope, inplace=True), w1, None, 1, 1)
+        y = F.conv2d(x, w0, None, 1, 1).contiguous(memory_format=torch.channels_last)
+        return F.conv2d(ops.bias_leaky_relu_(y, b0, slope), w1, None, 1, 1)
 
     def __call__(self, x):
         x = x.float().contiguous(memory_format=torch.channels_last)
@@ -156,11 +157,14 @@ class FusedBackbone:
             if i % 2 == 1:
                 feats.append(x)
         x1, x2, x3 = feats
-        up = lambda t: F.interpolate(t, scale_factor=2.0, mode="bilinear", align_corners=True)
         c3 = F.conv2d(x3, self.l3_out[0])
-        c2 = self._head(F.conv2d(x2, self.l2_out[0]).add_(up(c3)), self.head2)
-        c1 = self._head(F.conv2d(x1, self.l1_out[0]).add_(up(c2)), self.head1)
-        return c3, c1
+        if c3.shape[1] % 4 == 0 and x2.shape[2] == 2 * x3.shape[2] and x1.shape[2] == 2 * x2.shape[2] \
+                and x2.shape[3] == 2 * x3.shape[3] and x1.shape[3] == 2 * x2.shape[3]:
+            cl = lambda t: t.contiguous(memory_format=torch.channels_last)
+            c2 = self._head(ops.upsample2x_add_(cl(F.conv2d(x2, self.l2_out[0])), cl(c3)), self.head2)
+            c1 = self._head(ops.upsample2x_add_(cl(F.conv2d(x1, self.l1_out[0])), cl(c2)), self.head1)
+            return c3, c1
+        raise NotImplementedError("ResNetFPN_8_2 on CUDA needs image sides that are multiples of 8")
 
 
 # --------------------------------------------------------------------------------------------------

@@ -254,6 +254,35 @@ def fine_match(q: torch.Tensor, win: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def upsample2x_add_(dst: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    """dst [N,C,2H,2W] += bilinear x2 (align_corners=True) of src [N,C,H,W]; both channels-last fp32; in place."""
+    _need_cuda(dst, src)
+    n, c, hs, ws = src.shape
+    if tuple(dst.shape) != (n, c, 2 * hs, 2 * ws):
+        raise _lib.Opb200Error(f"upsample2x_add_: shapes {tuple(src.shape)} -> {tuple(dst.shape)}")
+    if not (src.is_contiguous(memory_format=torch.channels_last) and dst.is_contiguous(memory_format=torch.channels_last)
+            and src.dtype == torch.float32 and dst.dtype == torch.float32):
+        raise _lib.Opb200Error("upsample2x_add_: channels-last fp32 tensors required")
+    with _Stage("backbone_glue"):
+        st = _lib.lib().opb200_upsample2x_add_nhwc(_lib.ptr(src), n, hs, ws, c, _lib.ptr(dst), _lib.stream_ptr())
+    _lib.check(st, "opb200_upsample2x_add_nhwc")
+    return dst
+
+
+def bias_leaky_relu_(x: torch.Tensor, bias: torch.Tensor, slope: float) -> torch.Tensor:
+    """x [N,C,H,W] channels-last fp32 <- leaky_relu(x + bias[c]); in place."""
+    _need_cuda(x, bias)
+    n, c, h, w = x.shape
+    if not (x.is_contiguous(memory_format=torch.channels_last) and x.dtype == torch.float32):
+        raise _lib.Opb200Error("bias_leaky_relu_: channels-last fp32 tensor required")
+    bias = _f32(bias).contiguous()
+    with _Stage("backbone_glue"):
+        st = _lib.lib().opb200_bias_leaky_relu_nhwc(_lib.ptr(x), _lib.ptr(bias), ctypes.c_longlong(n * h * w), c,
+                                                    ctypes.c_float(slope), _lib.stream_ptr())
+    _lib.check(st, "opb200_bias_leaky_relu_nhwc")
+    return x
+
+
 def linear_attention(q, k, v, q_mask=None, kv_mask=None, eps: float = 1e-6) -> torch.Tensor:
     """Standalone elu+1 linear attention: q [N,L,H,D], k/v [N,S,H,D] -> [N,L,H,D]."""
     _need_cuda(q, k, v)

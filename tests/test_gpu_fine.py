@@ -78,3 +78,45 @@ def test_fine_match_sweep_vs_oracle(W, M):
     assert torch.corrcoef(torch.stack([ec[:, 0], lin[r % W]]))[0, 1].item() > 0.9
     assert torch.corrcoef(torch.stack([ec[:, 1], lin[r // W]]))[0, 1].item() > 0.9
     assert (ec[:, :2].abs() <= 1.0).all() and (ec[:, 2] >= 0).all()
+
+
+def test_backbone_glue_ops_match_torch():
+    """FPN glue kernels (channels-last fp32) against the PyTorch ops they fuse."""
+    import torch.nn.functional as F
+    from onepose_st_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    src = torch.randn(2, 12, 5, 7, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    dst = torch.randn(2, 12, 10, 14, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    want = dst + F.interpolate(src, scale_factor=2.0, mode="bilinear", align_corners=True)
+    got = ops.upsample2x_add_(dst.clone(memory_format=torch.channels_last), src)
+    assert (got - want).abs().max().item() < 1e-5
+    x = torch.randn(3, 8, 6, 4, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    b = torch.randn(8, generator=g).cuda()
+    want = F.leaky_relu(x + b[None, :, None, None], 0.01)
+    got = ops.bias_leaky_relu_(x.clone(memory_format=torch.channels_last), b, 0.01)
+    assert (got - want).abs().max().item() < 1e-6
+    with pytest.raises(Exception):
+        ops.upsample2x_add_(dst.contiguous(), src)  # NCHW-contiguous input is refused, not silently converted
+
+
+def test_backbone_fused_vs_plain_module(golden):
+    """Fused inference backbone (folded BN, cuDNN fused blocks, glue kernels) vs the reference's golden maps."""
+    import cases
+    from onepose_st_b200.nn_common import ResNetFPN_8_2
+    c = cases.case_backbone()
+    m = ResNetFPN_8_2({"block_type": "BasicBlock", "initial_dim": 128, "block_dims": [128, 196, 256]})
+    m.load_state_dict({k[len("backbone."):]: v for k, v in c["sd"].items()}, strict=True)
+    m = m.cuda().eval()
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        with torch.no_grad():
+            fc, ff = m(c["image"].cuda())
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    g = golden("backbone")
+    gc, gf = g["feat_c"], g["feat_f_sub"]
+    ec = (fc.cpu() - gc).abs().max().item() / gc.abs().max().item()
+    ef = (ff.cpu()[:, ::8, ::4, ::4] - gf).abs().max().item() / gf.abs().max().item()
+    print(f"backbone rel err coarse {ec:.2e} fine {ef:.2e}")
+    assert ec < 1e-4 and ef < 1e-4
