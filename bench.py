@@ -241,6 +241,8 @@ def run_ours(args):
     def timed(e2e):
         ragged.reset()
         run_steps(0, args.warmup, e2e)
+        # the gather is warmed up too (first NCCL all_gather sets up channels; first sort/scatter compiles nothing but allocates)
+        sharding.gather_matches(ragged.rows(), ragged.counts, world * F * args.warmup)
         ragged.reset()
         ops.stage_events = {} if not e2e else None
         sampler = ClockSampler(local_rank)
