@@ -126,6 +126,11 @@ int opb200_linear_attention(const float* q, const float* k, const float* v, cons
  * dst[n, y, x, c] += bilinear x2 upsampling (align_corners = True) of src[n, :, :, c]: the FPN top-down add of
  * ResNetFPN_8_2.forward (src/models/OnePosePlus/backbone/resnet.py:141-164).  src [n, Hs, Ws, C], dst [n, 2Hs, 2Ws, C]. */
 int opb200_upsample2x_add_nhwc(const float* src, int n_batch, int Hs, int Ws, int C, float* dst, void* stream);
+/* Stem: out[n, y, x, c] = relu(bias[c] + sum_{ky,kx} image[n, 2y-3+ky, 2x-3+kx] * w[ky*7+kx][c]) -- Conv2d(1, Cout, 7, stride 2,
+ * pad 3) + folded BatchNorm + ReLU of ResNetFPN_8_2 (backbone/resnet.py:85-141), channels-last output
+ * [n, Ho, Wo, Cout]; image is [n, H, W] fp32; weight_tap_major is [49][Cout]; Cout must be 128. */
+int opb200_stem_conv7x7_s2_relu_nhwc(const float* image, const float* weight_tap_major, const float* bias, int n_batch, int H,
+                                     int W, int Cout, float* out, void* stream);
 /* x[p, c] = leaky_relu(x[p, c] + bias[c], slope): folded-BatchNorm shift + nn.LeakyReLU of the FPN heads. */
 int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels, int C, float slope, void* stream);
 

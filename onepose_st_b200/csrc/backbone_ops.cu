@@ -58,6 +58,71 @@ __global__ void __launch_bounds__(256) bias_leaky_relu_kernel(float4* __restrict
   }
 }
 
+
+// Stem of ResNetFPN_8_2: 7x7 stride-2 pad-3 convolution of a 1-channel image + folded-BatchNorm bias + ReLU,
+// written channels-last (reference: backbone/resnet.py:141 `relu(bn1(conv1(x)))`, conv1 = Conv2d(1, 128, 7, 2, 3)).
+// One block = 16 x 16 output pixels of one image; the 37 x 37 input patch and the [49][COUT] weights sit in shared
+// memory; a thread owns two output pixels (rows ty and ty + 8) and walks the output channels 32 at a time, so
+// every broadcast weight float4 feeds two pixels.  fp32 FMA (exact w.r.t. the fp32 reference up to summation
+// order).  Output traffic dominates: 4 * COUT bytes per output pixel.
+template <int COUT>
+__global__ void __launch_bounds__(128) stem_conv7x7_s2_kernel(const float* __restrict__ img, const float* __restrict__ w,
+                                                              const float* __restrict__ bias, int H, int W, int Ho, int Wo,
+                                                              float* __restrict__ out) {
+  __shared__ float patch[37][38];
+  __shared__ __align__(16) float ws[49][COUT];
+  const int n = blockIdx.z, oy0 = blockIdx.y * 16, ox0 = blockIdx.x * 16;
+  const int t = threadIdx.x;
+  for (int i = t; i < 49 * COUT; i += 128) ws[i / COUT][i % COUT] = w[i];  // w is [49][COUT] (tap-major)
+  const float* im = img + static_cast<long long>(n) * H * W;
+  const int iy0 = oy0 * 2 - 3, ix0 = ox0 * 2 - 3;
+  for (int i = t; i < 37 * 37; i += 128) {
+    const int py = i / 37, px = i - py * 37;
+    const int y = iy0 + py, x = ix0 + px;
+    patch[py][px] = (y >= 0 && y < H && x >= 0 && x < W) ? __ldg(im + static_cast<long long>(y) * W + x) : 0.f;
+  }
+  __syncthreads();
+  const int tx = t & 15, ty = t >> 4;  // ty in 0..7: pixels (ty, tx) and (ty + 8, tx)
+#pragma unroll 1
+  for (int c0 = 0; c0 < COUT; c0 += 32) {
+    float a0[32], a1[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) a0[k] = a1[k] = __ldg(bias + c0 + k);
+#pragma unroll 1
+    for (int ky = 0; ky < 7; ++ky) {
+#pragma unroll
+      for (int kx = 0; kx < 7; ++kx) {
+        const float p0 = patch[2 * ty + ky][2 * tx + kx];
+        const float p1 = patch[2 * (ty + 8) + ky][2 * tx + kx];
+        const float4* wv = reinterpret_cast<const float4*>(&ws[ky * 7 + kx][c0]);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 f = wv[q];
+          a0[4 * q + 0] = fmaf(p0, f.x, a0[4 * q + 0]);
+          a0[4 * q + 1] = fmaf(p0, f.y, a0[4 * q + 1]);
+          a0[4 * q + 2] = fmaf(p0, f.z, a0[4 * q + 2]);
+          a0[4 * q + 3] = fmaf(p0, f.w, a0[4 * q + 3]);
+          a1[4 * q + 0] = fmaf(p1, f.x, a1[4 * q + 0]);
+          a1[4 * q + 1] = fmaf(p1, f.y, a1[4 * q + 1]);
+          a1[4 * q + 2] = fmaf(p1, f.z, a1[4 * q + 2]);
+          a1[4 * q + 3] = fmaf(p1, f.w, a1[4 * q + 3]);
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+      a0[k] = fmaxf(a0[k], 0.f);
+      a1[k] = fmaxf(a1[k], 0.f);
+    }
+    const int ox = ox0 + tx;
+    if (ox < Wo) {
+      const int oya = oy0 + ty, oyb = oy0 + ty + 8;
+      if (oya < Ho) store_f32x32_v8(a0, out + ((static_cast<long long>(n) * Ho + oya) * Wo + ox) * COUT + c0);
+      if (oyb < Ho) store_f32x32_v8(a1, out + ((static_cast<long long>(n) * Ho + oyb) * Wo + ox) * COUT + c0);
+    }
+  }
+}
+
 }  // namespace opb
 
 using namespace opb;
@@ -92,6 +157,21 @@ int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels,
   bias_leaky_relu_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(reinterpret_cast<float4*>(x),
                                                                                 reinterpret_cast<const float4*>(bias), total4,
                                                                                 C / 4, slope);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_stem_conv7x7_s2_relu_nhwc(const float* image, const float* weight_tap_major, const float* bias, int n_batch, int H,
+                                     int W, int Cout, float* out, void* stream_) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(image && weight_tap_major && bias && out, "null pointer");
+  OPB_CHECK_ARG(n_batch >= 1 && H >= 1 && W >= 1, "bad shape");
+  OPB_CHECK_ARG(Cout == 128, "stem kernel is instantiated for 128 output channels (initial_dim of ResNetFPN_8_2)");
+  OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(out) & 31) == 0, "output must be 32-byte aligned");
+  const int Ho = (H + 2 * 3 - 7) / 2 + 1, Wo = (W + 2 * 3 - 7) / 2 + 1;
+  dim3 grid((Wo + 15) / 16, (Ho + 15) / 16, n_batch);
+  stem_conv7x7_s2_kernel<128><<<grid, 128, 0, static_cast<cudaStream_t>(stream_)>>>(image, weight_tap_major, bias, H, W, Ho, Wo, out);
   count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;

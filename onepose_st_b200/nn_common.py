@@ -118,6 +118,11 @@ class FusedBackbone:
 
     def __init__(self, m: "ResNetFPN_8_2"):
         self.stem = _fold_bn(m.conv1, m.bn1)
+        # own stem kernel (Conv2d(1, 128, 7, 2, 3) + bias + ReLU, channels-last output): weights tap-major [49][Cout]
+        self.stem_tap_major = None
+        if tuple(m.conv1.weight.shape[1:]) == (1, 7, 7) and m.conv1.weight.shape[0] == 128 and m.conv1.stride == (2, 2) \
+                and m.conv1.padding == (3, 3):
+            self.stem_tap_major = self.stem[0].reshape(128, 49).t().contiguous()
         self.blocks = []
         for layer in (m.layer1, m.layer2, m.layer3):
             for blk in layer:
@@ -149,8 +154,10 @@ class FusedBackbone:
         return F.conv2d(ops.bias_leaky_relu_(y, b0, slope), w1, None, 1, 1)
 
     def __call__(self, x):
-        x = x.float().contiguous(memory_format=torch.channels_last)
-        x = self._conv_relu(x, self.stem, (2, 2), (3, 3))
+        if self.stem_tap_major is not None:
+            x = ops.stem_conv_relu(x, self.stem_tap_major, self.stem[1])
+        else:  # non-default initial_dim: cuDNN stem (its NCHW result is converted once)
+            x = self._conv_relu(x.float(), self.stem, (2, 2), (3, 3)).contiguous(memory_format=torch.channels_last)
         feats = []
         for i, blk in enumerate(self.blocks):
             x = self._block(x, blk)

@@ -269,6 +269,23 @@ def upsample2x_add_(dst: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
     return dst
 
 
+def stem_conv_relu(image: torch.Tensor, weight_tap_major: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
+    """image [N,1,H,W] fp32 -> relu(conv7x7/2(image) + bias) as a channels-last [N,Cout,Ho,Wo] tensor."""
+    _need_cuda(image, weight_tap_major, bias)
+    n, cin, h, w = image.shape
+    if cin != 1:
+        raise _lib.Opb200Error("stem_conv_relu: single-channel images only")
+    image = _f32(image).contiguous()
+    cout = weight_tap_major.shape[1]
+    ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    out = torch.empty(n, cout, ho, wo, dtype=torch.float32, device=image.device, memory_format=torch.channels_last)
+    with _Stage("backbone_glue"):
+        st = _lib.lib().opb200_stem_conv7x7_s2_relu_nhwc(_lib.ptr(image), _lib.ptr(weight_tap_major), _lib.ptr(bias), n, h, w, cout,
+                                                         _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "opb200_stem_conv7x7_s2_relu_nhwc")
+    return out
+
+
 def bias_leaky_relu_(x: torch.Tensor, bias: torch.Tensor, slope: float) -> torch.Tensor:
     """x [N,C,H,W] channels-last fp32 <- leaky_relu(x + bias[c]); in place."""
     _need_cuda(x, bias)
