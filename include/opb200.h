@@ -72,6 +72,13 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
                        int64_t x1_sl, int64_t x1_sc, const float* add1, const uint8_t* mask0, const uint8_t* mask1,
                        float* out0, float* out1, void* workspace, size_t workspace_bytes, int precision, void* stream);
 
+/* After opb200_transformer: where the final token features live inside `workspace` as bf16 hi/lo planes
+ * (x = hi + lo).  planes[4] = {stream0 hi, stream0 lo, stream1 hi, stream1 lo}, each [n_batch * padded_len[s], d_model]
+ * row-major with batch element n at row n * padded_len[s].  opb200_transformer may be called with out0 = out1 = NULL
+ * when the only consumer is opb200_coarse_match_planes (no fp32 copy-out, no re-splitting). */
+int opb200_transformer_planes(void* workspace, int d_model, int n_batch, int len0, int len1, int big_groups, void** planes,
+                              int* padded_len);
+
 /* ---- CoarseMatching: dual-softmax + threshold + border + mutual nearest neighbour ------------------
  * Replaces CoarseMatching.forward / get_coarse_match (eval mode):
  *   src/models/OnePosePlus/utils/coarse_matching.py:76-242
@@ -95,6 +102,15 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
                         int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity, int* count_and_overflow,
                         float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, int algo,
                         void* stream);
+
+/* Same as opb200_coarse_match with the operands already split into bf16 planes [n_batch*Lp, C] / [n_batch*Sp, C]
+ * (Lp, Sp = L, S rounded up to 128; pad rows may hold any finite values).  Same workspace size. */
+int opb200_coarse_match_planes(const void* a_hi, const void* a_lo, const void* b_hi, const void* b_lo, const uint8_t* mask_a,
+                               const uint8_t* mask_b, int mask_fill, int n_batch, int L, int S, int C, float scale, float thr,
+                               int border_rm, int border_mode, int h0, int w0, int h1, int w1, const int* valid_hw,
+                               int64_t* b_ids, int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity,
+                               int* count_and_overflow, float* conf_matrix, void* workspace, size_t workspace_bytes,
+                               int precision, int algo, void* stream);
 
 /* ---- Fine level --------------------------------------------------------------------------------------
  * opb200_fine_gather replaces F.unfold + index in FinePreprocess (OnePosePlus fine_preprocess.py:43-53,

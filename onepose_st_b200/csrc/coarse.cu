@@ -763,16 +763,19 @@ size_t opb200_coarse_match_workspace_bytes(int n_batch, int L, int S, int C, flo
   return carve_coarse(nullptr, n_batch, L, S, C, thr).bytes;
 }
 
-int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t* mask_a, const uint8_t* mask_b,
-                        int mask_fill, int n_batch, int L, int S, int C, float scale, float thr, int border_rm,
-                        int border_mode, int h0, int w0, int h1, int w1, const int* valid_hw, int64_t* b_ids,
-                        int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity, int* count_and_overflow,
-                        float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, int algo,
-                        void* stream_) {
+}  // extern "C"
+
+// ext[4] (nullable) = caller-provided operand planes {a_hi, a_lo, b_hi, b_lo} laid out [n_batch*Lp, C] / [n_batch*Sp, C]
+static int coarse_match_impl(const float* feat_a, const float* feat_b, const void* const* ext, const uint8_t* mask_a,
+                             const uint8_t* mask_b, int mask_fill, int n_batch, int L, int S, int C, float scale, float thr,
+                             int border_rm, int border_mode, int h0, int w0, int h1, int w1, const int* valid_hw,
+                             int64_t* b_ids, int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity,
+                             int* count_and_overflow, float* conf_matrix, void* workspace, size_t workspace_bytes,
+                             int precision, int algo, void* stream_) {
   if (int r = check_device()) return r;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   OPB_CHECK_ARG(algo == 0 || algo == 1, "algo must be 0 (auto: single-pass where legal) or 1 (two-pass)");
-  OPB_CHECK_ARG(feat_a && feat_b && b_ids && i_ids && j_ids && mconf && count_and_overflow && workspace, "null pointer");
+  OPB_CHECK_ARG(((feat_a && feat_b) || ext) && b_ids && i_ids && j_ids && mconf && count_and_overflow && workspace, "null pointer");
   OPB_CHECK_ARG(n_batch >= 1 && L >= 1 && S >= 1, "empty input");
   OPB_CHECK_ARG(C % BLOCK_K == 0 && C >= BLOCK_K, "feature dim must be a positive multiple of 64");
   OPB_CHECK_ARG(thr > 0.f && thr < 1.f, "thr must be in (0,1): the candidate-list selection relies on conf > thr > 0");
@@ -788,15 +791,22 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
   const bool x3 = precision == 3;
   const int N = n_batch, Lp = w.Lp, Sp = w.Sp;
   // ---- operand planes (pad rows zero so they add nothing and never produce NaN)
-  if (Lp != L) {
+  if (ext != nullptr) {  // planes written by the encoder stack; its pad rows are finite and masked by row/col validity
+    OPB_CHECK_ARG(ext[0] && ext[2] && (!x3 || (ext[1] && ext[3])), "null operand plane");
+    w.a_hi = static_cast<__nv_bfloat16*>(const_cast<void*>(ext[0]));
+    w.a_lo = static_cast<__nv_bfloat16*>(const_cast<void*>(ext[1]));
+    w.b_hi = static_cast<__nv_bfloat16*>(const_cast<void*>(ext[2]));
+    w.b_lo = static_cast<__nv_bfloat16*>(const_cast<void*>(ext[3]));
+  }
+  if (ext == nullptr && Lp != L) {
     OPB_CHECK_CUDA(cudaMemsetAsync(w.a_hi, 0, static_cast<size_t>(N) * Lp * C * 2, stream));
     if (x3) OPB_CHECK_CUDA(cudaMemsetAsync(w.a_lo, 0, static_cast<size_t>(N) * Lp * C * 2, stream));
   }
-  if (Sp != S) {
+  if (ext == nullptr && Sp != S) {
     OPB_CHECK_CUDA(cudaMemsetAsync(w.b_hi, 0, static_cast<size_t>(N) * Sp * C * 2, stream));
     if (x3) OPB_CHECK_CUDA(cudaMemsetAsync(w.b_lo, 0, static_cast<size_t>(N) * Sp * C * 2, stream));
   }
-  for (int n = 0; n < N; ++n) {
+  for (int n = 0; ext == nullptr && n < N; ++n) {
     if (int r = split_planes(feat_a + static_cast<size_t>(n) * L * C, C, 1, nullptr, 0, L, C, w.a_hi + static_cast<size_t>(n) * Lp * C,
                              x3 ? w.a_lo + static_cast<size_t>(n) * Lp * C : nullptr, nullptr, C, stream))
       return r;
@@ -894,6 +904,31 @@ int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t*
   count_launch(3);
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
+}
+
+extern "C" {
+
+int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t* mask_a, const uint8_t* mask_b,
+                        int mask_fill, int n_batch, int L, int S, int C, float scale, float thr, int border_rm,
+                        int border_mode, int h0, int w0, int h1, int w1, const int* valid_hw, int64_t* b_ids,
+                        int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity, int* count_and_overflow,
+                        float* conf_matrix, void* workspace, size_t workspace_bytes, int precision, int algo,
+                        void* stream) {
+  return coarse_match_impl(feat_a, feat_b, nullptr, mask_a, mask_b, mask_fill, n_batch, L, S, C, scale, thr, border_rm,
+                           border_mode, h0, w0, h1, w1, valid_hw, b_ids, i_ids, j_ids, mconf, capacity, count_and_overflow,
+                           conf_matrix, workspace, workspace_bytes, precision, algo, stream);
+}
+
+int opb200_coarse_match_planes(const void* a_hi, const void* a_lo, const void* b_hi, const void* b_lo, const uint8_t* mask_a,
+                               const uint8_t* mask_b, int mask_fill, int n_batch, int L, int S, int C, float scale, float thr,
+                               int border_rm, int border_mode, int h0, int w0, int h1, int w1, const int* valid_hw,
+                               int64_t* b_ids, int64_t* i_ids, int64_t* j_ids, float* mconf, int capacity,
+                               int* count_and_overflow, float* conf_matrix, void* workspace, size_t workspace_bytes,
+                               int precision, int algo, void* stream) {
+  const void* ext[4] = {a_hi, a_lo, b_hi, b_lo};
+  return coarse_match_impl(nullptr, nullptr, ext, mask_a, mask_b, mask_fill, n_batch, L, S, C, scale, thr, border_rm,
+                           border_mode, h0, w0, h1, w1, valid_hw, b_ids, i_ids, j_ids, mconf, capacity, count_and_overflow,
+                           conf_matrix, workspace, workspace_bytes, precision, algo, stream);
 }
 
 }  // extern "C"

@@ -835,7 +835,8 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
   OPB_CHECK_ARG(big_groups || d_model == 128, "small groups need d_model 128");
   OPB_CHECK_ARG(!big_groups || 2 * n_batch <= 64, "at most 32 batch elements per call with big groups");
   OPB_CHECK_ARG(big_groups || (len0 <= 128 && len1 <= 128), "small groups hold at most 128 tokens");
-  OPB_CHECK_ARG(x0 && x1 && out0 && out1 && workspace && host_layer_weights && host_layer_kinds, "null pointer");
+  OPB_CHECK_ARG(x0 && x1 && workspace && host_layer_weights && host_layer_kinds, "null pointer");
+  OPB_CHECK_ARG((out0 == nullptr) == (out1 == nullptr), "out0 / out1 must both be given or both be null");
   Geometry g = make_geometry(d_model, n_batch, len0, len1, big_groups);
   Workspace w = carve(workspace, g);
   if (w.bytes > workspace_bytes) {
@@ -885,6 +886,7 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
     }
     if (r) return r;
   }
+  if (out0 == nullptr) return OPB_OK;  // the caller consumes the planes in the workspace (opb200_transformer_planes)
   const int threads = 256;
   copy_out_kernel<<<dim3((static_cast<long long>(len0) * C / 8 + threads - 1) / threads, 1, n_batch), threads, 0, stream>>>(
       w.xh, w.xl, len0, g.P0, C, 0, out0);
@@ -892,6 +894,21 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
       w.xh, w.xl, len1, g.P1, C, row1, out1);
   count_launch(2);
   OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_transformer_planes(void* workspace, int d_model, int n_batch, int len0, int len1, int big_groups, void** planes,
+                              int* padded_len) {
+  OPB_CHECK_ARG(workspace && planes && padded_len, "null pointer");
+  OPB_CHECK_ARG(d_model == 256 || d_model == 128, "d_model must be 256 or 128");
+  Geometry g = make_geometry(d_model, n_batch, len0, len1, big_groups);
+  Workspace w = carve(workspace, g);
+  planes[0] = w.xh;
+  planes[1] = w.xl;
+  planes[2] = w.xh + static_cast<size_t>(g.row1) * d_model;
+  planes[3] = w.xl + static_cast<size_t>(g.row1) * d_model;
+  padded_len[0] = g.P0;
+  padded_len[1] = g.P1;
   return OPB_OK;
 }
 

@@ -59,9 +59,9 @@ class LocalFeatureTransformer(_TransformerBase):
         self.config = config
         self._build(config["d_model"], config["nhead"], config["layer_names"], attention=config["attention"])
 
-    def forward(self, feat0, feat1, mask0=None, mask1=None, _add0=None, _add1=None):
+    def forward(self, feat0, feat1, mask0=None, mask1=None, _add0=None, _add1=None, _planes_only=False):
         assert self.d_model == feat0.size(2), "the feature number of src and transformer must be equal"
-        return self._run(feat0, feat1, mask0, mask1, _add0, _add1)
+        return self._run(feat0, feat1, mask0, mask1, _add0, _add1, planes_only=_planes_only)
 
 
 class CoarseMatching(nn.Module):
@@ -87,7 +87,8 @@ class CoarseMatching(nn.Module):
     def forward(self, feat_c0, feat_c1, data, mask_c0=None, mask_c1=None):
         if self.training:
             raise NotImplementedError("training-time coarse matching is out of scope of the inference path")
-        n, L, C = feat_c0.shape
+        planes = feat_c0 if isinstance(feat_c0, ops.FeaturePlanes) else None  # internal fused hand-over
+        C = planes.c if planes is not None else feat_c0.shape[2]
         h0, w0 = int(data["hw0_c"][0]), int(data["hw0_c"][1])
         h1, w1 = int(data["hw1_c"][0]), int(data["hw1_c"][1])
         vhw = None
@@ -99,7 +100,7 @@ class CoarseMatching(nn.Module):
         b_ids, i_ids, j_ids, mconf, conf = ops.coarse_match(
             feat_c0, feat_c1, scale=1.0 / (C * self.temperature), thr=self.thr, border_rm=self.border_rm, border_mode=1,
             grid_a=(h0, w0), grid_b=(h1, w1), mask_a=mask_c0, mask_b=mask_c1, mask_fill=1, valid_hw=vhw,
-            materialize_conf=self.materialize_conf_matrix, precision=self.precision)
+            materialize_conf=self.materialize_conf_matrix, precision=self.precision, planes=planes)
         if conf is not None:
             data.update({"conf_matrix": conf})
         scale = data["hw0_i"][0] / data["hw0_c"][0]
@@ -212,8 +213,8 @@ class LoFTR_for_OnePose_Plus(nn.Module):
             mask_c0 = mask_c1 = None
             if "mask0" in data:
                 mask_c0, mask_c1 = data["mask0"].flatten(-2), data["mask1"].flatten(-2)
-            s0, s1 = self.loftr_coarse(s0, s1, mask_c0, mask_c1, _add0=add0, _add1=add1)
-            self.coarse_matching(s0, s1, data, mask_c0=mask_c0, mask_c1=mask_c1)
+            planes = self.loftr_coarse(s0, s1, mask_c0, mask_c1, _add0=add0, _add1=add1, _planes_only=True)
+            self.coarse_matching(planes, None, data, mask_c0=mask_c0, mask_c1=mask_c1)
         else:
             # fine-only entry (loftr.py:79-115): clips the caller's tensors in place, batch size 1
             k0, k1 = data["mkpts0_c"], data["mkpts1_c"]

@@ -295,12 +295,13 @@ class _TransformerBase(nn.Module):
             if p.dim() > 1:
                 nn.init.xavier_uniform_(p)
 
-    def _run(self, x0, x1, mask0=None, mask1=None, add0=None, add1=None, upto: Optional[int] = None):
+    def _run(self, x0, x1, mask0=None, mask1=None, add0=None, add1=None, upto: Optional[int] = None,
+             planes_only: bool = False):
         layers = list(self.layers)[:upto]
         kinds = [0 if n == "self" else 1 for n in self.layer_names[:upto]]
         return ops.transformer([l.packed() for l in layers], kinds, self.schedule, self.d_model, self.nhead, x0, x1,
                                add0=add0, add1=add1, mask0=mask0, mask1=mask1, big_groups=(self.d_model == 256),
-                               precision=getattr(self, "precision", ops.PREC_BF16X3))
+                               precision=getattr(self, "precision", ops.PREC_BF16X3), planes_only=planes_only)
 
 
 # --------------------------------------------------------------------------------------------------

@@ -113,9 +113,13 @@ class LocalFeatureTransformer(_TransformerBase):
                     redraw_interval=ri, d_kernel=config.get("d_kernel"), rezero=config.get("rezero"),
                     norm_method=config["norm_method"])
 
-    def forward(self, desc3d_db, desc2d_query, query_mask=None, return_middle_layer_features=False, _add2d=None):
-        """desc3d_db [N, C, L] (channels first), desc2d_query [N, P, C] -> (desc3d [N,L,C], desc2d [N,P,C])."""
+    def forward(self, desc3d_db, desc2d_query, query_mask=None, return_middle_layer_features=False, _add2d=None,
+                _planes_only=False):
+        """desc3d_db [N, C, L] (channels first), desc2d_query [N, P, C] -> (desc3d [N,L,C], desc2d [N,P,C]).
+        ``_planes_only`` (internal): return an ``ops.FeaturePlanes`` handle for CoarseMatching instead."""
         x3 = desc3d_db.permute(0, 2, 1)  # view; the stage-in kernel reads it strided
+        if _planes_only and not return_middle_layer_features:
+            return self._run(x3, desc2d_query, mask1=query_mask, add1=_add2d, planes_only=True)
         if not return_middle_layer_features:
             d3, d2 = self._run(x3, desc2d_query, mask1=query_mask, add1=_add2d)
             return d3, d2
@@ -153,14 +157,15 @@ class CoarseMatching(nn.Module):
             raise NotImplementedError("training-time coarse matching (GT padding) is out of scope of the inference path")
         if "mask0" in data:
             raise NotImplementedError
-        n, L, C = feat_db_3d.shape
+        planes = feat_db_3d if isinstance(feat_db_3d, ops.FeaturePlanes) else None  # internal fused hand-over
+        C = planes.c if planes is not None else feat_db_3d.shape[2]
         hc, wc = int(data["q_hw_c"][0]), int(data["q_hw_c"][1])
         scale = 1.0 / (C * (self.temperature + 1e-4))  # (a/sqrt C).(b/sqrt C) / (T + 1e-4)
         with self.profiler.record_function("LoFTR/coarse-matching/get_coarse_match"):
             b_ids, i_ids, j_ids, mconf, conf = ops.coarse_match(
                 feat_db_3d, feat_query, scale=scale, thr=self.thr, border_rm=self.border_rm, border_mode=0, grid_a=None,
                 grid_b=(hc, wc), mask_b=mask_query, mask_fill=0, materialize_conf=self.materialize_conf_matrix,
-                precision=self.precision)
+                precision=self.precision, planes=planes)
         if conf is not None:
             data.update({"conf_matrix": conf})
         scale_c = data["q_hw_i"][0] / data["q_hw_c"][0]
@@ -308,8 +313,9 @@ class OnePosePlus_model(nn.Module):
         add2d = self.dense_pos_encoding.token_table(hc, wc) if self.dense_pos_encoding is not None else None
         desc3d = self._encode_3d(data)
         qmask = data["query_image_mask"].flatten(-2) if "query_image_mask" in data else None
-        desc3d, q2d = self.loftr_coarse(desc3d, q2d, query_mask=qmask, _add2d=add2d)
-        self.coarse_matching(desc3d, q2d, data, mask_query=qmask)
+        # the coarse features are consumed by CoarseMatching only: hand them over as bf16 planes
+        planes = self.loftr_coarse(desc3d, q2d, query_mask=qmask, _add2d=add2d, _planes_only=True)
+        self.coarse_matching(planes, None, data, mask_query=qmask)
         if not self.config["fine_matching"]["enable"]:
             data.update({"mkpts_3d_db": data["mkpts_3d_db"], "mkpts_query_f": data["mkpts_query_c"]})
             return

@@ -98,11 +98,22 @@ def pack_layer_weights(wq, wk, wv, wm, w1, w2, ln1_w, ln1_b, ln2_w, ln2_b) -> to
     return out
 
 
+class FeaturePlanes:
+    """Final token features of an encoder stack left in its workspace as bf16 hi/lo planes (x = hi + lo), the
+    operand format of ``coarse_match``: passing them on skips the fp32 copy-out and the re-splitting."""
+
+    def __init__(self, ptrs, padded, n, len0, len1, c, ws):
+        self.ptrs, self.padded, self.n, self.len0, self.len1, self.c = ptrs, padded, n, len0, len1, c
+        self.ws = ws  # keeps the workspace alive; valid until the next transformer call of the same width
+
+
 def transformer(packed_layers: Sequence[torch.Tensor], layer_kinds: Sequence[int], schedule: int, d_model: int,
                 nhead: int, x0: torch.Tensor, x1: torch.Tensor, add0: Optional[torch.Tensor] = None,
                 add1: Optional[torch.Tensor] = None, mask0: Optional[torch.Tensor] = None,
-                mask1: Optional[torch.Tensor] = None, big_groups: bool = True, precision: int = PREC_BF16X3):
-    """x0 [N, len0, C], x1 [N, len1, C] as (possibly permuted) fp32 views -> (out0, out1) contiguous."""
+                mask1: Optional[torch.Tensor] = None, big_groups: bool = True, precision: int = PREC_BF16X3,
+                planes_only: bool = False):
+    """x0 [N, len0, C], x1 [N, len1, C] as (possibly permuted) fp32 views -> (out0, out1) contiguous, or with
+    ``planes_only`` a ``FeaturePlanes`` handle (no fp32 outputs are written)."""
     _need_cuda(x0, x1)
     x0, x1 = _f32(x0), _f32(x1)
     n, len0, c = x0.shape
@@ -113,8 +124,8 @@ def transformer(packed_layers: Sequence[torch.Tensor], layer_kinds: Sequence[int
     l.opb200_transformer_workspace_bytes.restype = _c_sz
     nbytes = int(l.opb200_transformer_workspace_bytes(d_model, n, len0, len1, int(big_groups)))
     ws = workspaces.get(x0.device, "transformer%d" % d_model, nbytes)
-    out0 = torch.empty(n, len0, c, dtype=torch.float32, device=x0.device)
-    out1 = torch.empty(n, len1, c, dtype=torch.float32, device=x0.device)
+    out0 = None if planes_only else torch.empty(n, len0, c, dtype=torch.float32, device=x0.device)
+    out1 = None if planes_only else torch.empty(n, len1, c, dtype=torch.float32, device=x0.device)
     nl = len(packed_layers)
     w_arr = (ctypes.c_void_p * nl)(*[t.data_ptr() for t in packed_layers])
     k_arr = (ctypes.c_int * nl)(*[int(k) for k in layer_kinds])
@@ -135,23 +146,37 @@ def transformer(packed_layers: Sequence[torch.Tensor], layer_kinds: Sequence[int
                               _lib.ptr(mk0), _lib.ptr(mk1), _lib.ptr(out0), _lib.ptr(out1), _lib.ptr(ws), _c_sz(ws.numel()),
                               int(precision), _lib.stream_ptr())
     _lib.check(st, "opb200_transformer")
+    if planes_only:
+        ptrs = (ctypes.c_void_p * 4)()
+        padded = (ctypes.c_int * 2)()
+        st = l.opb200_transformer_planes(_lib.ptr(ws), d_model, n, len0, len1, int(big_groups), ptrs, padded)
+        _lib.check(st, "opb200_transformer_planes")
+        return FeaturePlanes([int(p or 0) for p in ptrs], (int(padded[0]), int(padded[1])), n, len0, len1, c, ws)
     return out0, out1
 
 
 def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, thr: float, border_rm: int,
                  border_mode: int, grid_a, grid_b, mask_a: Optional[torch.Tensor] = None,
                  mask_b: Optional[torch.Tensor] = None, mask_fill: int = 0, valid_hw: Optional[torch.Tensor] = None,
-                 materialize_conf: bool = False, precision: int = PREC_BF16X3, algo: int = 0):
+                 materialize_conf: bool = False, precision: int = PREC_BF16X3, algo: int = 0,
+                 planes: Optional[FeaturePlanes] = None):
     """Dual-softmax + mutual-NN selection.  Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None).
+    With ``planes`` (from ``transformer(..., planes_only=True)``) feat_a / feat_b are ignored.
 
     One host sync (reading the match count) -- the reference syncs at the same point (torch.where)."""
-    _need_cuda(feat_a, feat_b)
-    feat_a, feat_b = _f32(feat_a).contiguous(), _f32(feat_b).contiguous()
-    n, L, C = feat_a.shape
-    S = feat_b.shape[1]
+    if planes is not None:
+        n, L, S, C = planes.n, planes.len0, planes.len1, planes.c
+        if planes.padded != ((L + 127) // 128 * 128, (S + 127) // 128 * 128):
+            raise _lib.Opb200Error("coarse_match: feature planes are not padded to 128-row groups (coarse-level stack only)")
+        dev = planes.ws.device
+    else:
+        _need_cuda(feat_a, feat_b)
+        feat_a, feat_b = _f32(feat_a).contiguous(), _f32(feat_b).contiguous()
+        n, L, C = feat_a.shape
+        S = feat_b.shape[1]
+        dev = feat_a.device
     if not (0.0 < thr < 1.0):
         raise NotImplementedError(f"coarse matching threshold must be in (0,1), got {thr}")
-    dev = feat_a.device
     l = _lib.lib()
     l.opb200_coarse_match_workspace_bytes.restype = _c_sz
     nbytes = int(l.opb200_coarse_match_workspace_bytes(n, L, S, C, ctypes.c_float(thr)))
@@ -175,7 +200,13 @@ def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, th
     h0, w0 = (int(grid_a[0]), int(grid_a[1])) if grid_a is not None else (1, L)
     h1, w1 = int(grid_b[0]), int(grid_b[1])
     with _Stage("coarse_match"):
-        st = l.opb200_coarse_match(_lib.ptr(feat_a), _lib.ptr(feat_b), _lib.ptr(ma), _lib.ptr(mb), int(mask_fill), n, L, S, C,
+        if planes is not None:
+            head = [ctypes.c_void_p(p) for p in planes.ptrs]
+            fn = l.opb200_coarse_match_planes
+        else:
+            head = [_lib.ptr(feat_a), _lib.ptr(feat_b)]
+            fn = l.opb200_coarse_match
+        st = fn(*head, _lib.ptr(ma), _lib.ptr(mb), int(mask_fill), n, L, S, C,
                                ctypes.c_float(scale), ctypes.c_float(thr), int(border_rm), int(border_mode), h0, w0, h1, w1,
                                _lib.ptr(vhw), _lib.ptr(b_ids), _lib.ptr(i_ids), _lib.ptr(j_ids), _lib.ptr(mconf), cap,
                                _lib.ptr(cnt), _lib.ptr(conf), _lib.ptr(ws), _c_sz(ws.numel()), int(precision), int(algo),
@@ -185,7 +216,7 @@ def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, th
     if rerun:  # the single-pass statistics hit their dynamic-range guard: take the two-pass path
         return coarse_match(feat_a, feat_b, scale=scale, thr=thr, border_rm=border_rm, border_mode=border_mode,
                             grid_a=grid_a, grid_b=grid_b, mask_a=mask_a, mask_b=mask_b, mask_fill=mask_fill,
-                            valid_hw=valid_hw, materialize_conf=materialize_conf, precision=precision, algo=1)
+                            valid_hw=valid_hw, materialize_conf=materialize_conf, precision=precision, algo=1, planes=planes)
     if overflow:
         import os
         if os.environ.get("OPB200_DEBUG_OVERFLOW"):

@@ -137,9 +137,36 @@ def run_fine(a):
                               "peak": f"{hbm} GB/s ({src})"}), flush=True)
 
 
+def run_loftr(a):
+    """BASELINE config 4: LoFTR wsize9 pair matching on 512x512 pairs (identical images + calibrated weights so that
+    matches exist), coarse-only and coarse+fine, pairs/s through LoFTR_for_OnePose_Plus.forward."""
+    from onepose_st_b200.loftr import LoFTR_for_OnePose_Plus, default_cfg
+    torch.manual_seed(0)
+    for fine in (False, True):
+        m = LoFTR_for_OnePose_Plus(default_cfg, enable_fine_matching=fine).eval()
+        m.load_state_dict(synthetic.calibrate_loftr_state_dict(m.state_dict()))
+        m = m.cuda()
+        for nb in a.pair_batch:
+            g = torch.Generator().manual_seed(2000)
+            img0 = torch.rand(nb, 1, a.size, a.size, generator=g).cuda()
+            img1 = img0.clone()
+            one = torch.ones(nb, 2, device="cuda")
+            out = {}
+
+            def fn():
+                d = {"image0": img0, "image1": img1, "scale0": one, "scale1": one}
+                m(d)
+                out["m"] = int(d["mconf"].shape[0])
+            med, best = time_op(fn, a.iters, warmup=0 if a.iters == 1 else 3)
+            print(json.dumps({"op": "LoFTR_for_OnePose_Plus.forward", "fine": fine, "pairs_per_forward": nb, "image": a.size,
+                              "matches_per_pair": out["m"] / nb, "ms_per_forward": med, "pairs_per_s": nb / med * 1e3}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["coarse", "transformer", "fine"])
+    ap.add_argument("what", choices=["coarse", "transformer", "fine", "loftr"])
+    ap.add_argument("--size", type=int, default=512)
+    ap.add_argument("--pair-batch", type=int, nargs="+", default=[1, 4])
     ap.add_argument("--points", type=int, nargs="+", default=[5000, 8000, 30000])
     ap.add_argument("--matches", type=int, nargs="+", default=[2000, 5000, 10000, 20000])
     ap.add_argument("--grid", type=int, default=64)
@@ -147,7 +174,7 @@ def main():
     ap.add_argument("--precision", type=int, default=3)
     ap.add_argument("--materialize", action="store_true")
     a = ap.parse_args()
-    {"coarse": run_coarse, "transformer": run_transformer, "fine": run_fine}[a.what](a)
+    {"coarse": run_coarse, "transformer": run_transformer, "fine": run_fine, "loftr": run_loftr}[a.what](a)
 
 
 if __name__ == "__main__":
