@@ -62,6 +62,7 @@ struct EpiSimStats {
     float2* colpart;  // [Lp/128][N*Sp]
   };
   static constexpr int kSmemBytes = 2 * 128 * 33 * 4 + 2 * 4 * 32 * 8;
+  static __device__ __forceinline__ void prefetch(const Params&, const EpiCtx&) {}
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const SimGeom& g = p.g;
     float(*sc)[128][33] = reinterpret_cast<float(*)[128][33]>(ctx.scratch);
@@ -218,6 +219,7 @@ struct EpiSimSelect {
     float* conf_matrix;  // [N, L, S] (WRITE_CONF only)
   };
   static constexpr int kSmemBytes = 0;
+  static __device__ __forceinline__ void prefetch(const Params&, const EpiCtx&) {}
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const SimGeom& g = p.g;
     const int r = ctx.quarter * 32 + ctx.lane;

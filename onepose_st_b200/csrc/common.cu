@@ -207,6 +207,7 @@ struct EpiStoreF32 {
 };
 template <int BN>
 struct EpiStoreF32T : EpiStoreF32 {
+  static __device__ __forceinline__ void prefetch(const Params&, const EpiCtx&) {}
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) { run_bn<BN>(p, ctx); }
 };
 

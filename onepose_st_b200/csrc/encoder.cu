@@ -55,6 +55,7 @@ struct EpiQKV {
   };
   static constexpr int kSmemBytes = 0;
   static constexpr int CPT = C / EPI_SPLIT;
+  static __device__ __forceinline__ void prefetch(const Params&, const EpiCtx&) {}
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
     const float m = p.row_mask[row] ? 1.f : 0.f;
@@ -85,6 +86,7 @@ struct EpiAttn {
     float eps;
   };
   static constexpr int kSmemBytes = 0;
+  static __device__ __forceinline__ void prefetch(const Params&, const EpiCtx&) {}
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
     uint32_t dr[16];
@@ -167,6 +169,7 @@ struct EpiLN {  // MERGE epilogue: LayerNorm1 -> planes
   };
   static constexpr int kSmemBytes = kLnScratch;
   static constexpr int CPT = C / EPI_SPLIT;
+  static __device__ __forceinline__ void prefetch(const Params&, const EpiCtx&) {}
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
     float x[CPT];
@@ -178,7 +181,14 @@ struct EpiLN {  // MERGE epilogue: LayerNorm1 -> planes
       const int c0 = ctx.part * CPT + c;
       float v[32];
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = (x[c + i] - mean) * rstd * __ldg(p.gamma + c0 + i) + __ldg(p.beta + c0 + i);
+      for (int i = 0; i < 32; i += 4) {  // warp-uniform addresses: one broadcast 16-byte load per 4 columns
+        const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.gamma + c0 + i));
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.beta + c0 + i));
+        v[i + 0] = (x[c + i + 0] - mean) * rstd * g4.x + b4.x;
+        v[i + 1] = (x[c + i + 1] - mean) * rstd * g4.y + b4.y;
+        v[i + 2] = (x[c + i + 2] - mean) * rstd * g4.z + b4.z;
+        v[i + 3] = (x[c + i + 3] - mean) * rstd * g4.w + b4.w;
+      }
       store_planes32_v8(v, p.o_hi + row * C + c0, p.o_lo ? p.o_lo + row * C + c0 : nullptr);
     }
   }
@@ -192,6 +202,7 @@ struct EpiRelu {  // MLP1 epilogue: ReLU -> planes [R, ld]
   };
   static constexpr int kSmemBytes = 0;
   static constexpr int CPT = BN / EPI_SPLIT;
+  static __device__ __forceinline__ void prefetch(const Params&, const EpiCtx&) {}
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
 #pragma unroll 1
@@ -214,6 +225,12 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual str
   };
   static constexpr int kSmemBytes = kLnScratch;
   static constexpr int CPT = C / EPI_SPLIT;
+  static __device__ __forceinline__ void prefetch(const Params& p, const EpiCtx& ctx) {
+    // the residual planes of this thread's row slice (2 x CPT bf16 = 2 x 128 B at C = 256) come from HBM: start early
+    const long long off = (static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane) * C + ctx.part * (C / EPI_SPLIT);
+    ptx::prefetch_l2(p.x_hi + off);
+    ptx::prefetch_l2(p.x_lo + off);
+  }
   static __device__ __forceinline__ void run(const Params& p, const EpiCtx& ctx) {
     const long long row = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32 + ctx.lane;
     float x[CPT];
@@ -232,12 +249,18 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual str
         ptx::ld_global_v8(ph + 16 * i, h);
         ptx::ld_global_v8(pl + 16 * i, l);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const float2 hf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h[k]));
-          const float2 lf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&l[k]));
+        for (int k = 0; k < 8; k += 2) {
           const int e = 16 * i + 2 * k, cc = c0 + e;
-          v[e] = (hf.x + lf.x) + ((x[c + e] - mean) * rstd * __ldg(p.gamma + cc) + __ldg(p.beta + cc));
-          v[e + 1] = (hf.y + lf.y) + ((x[c + e + 1] - mean) * rstd * __ldg(p.gamma + cc + 1) + __ldg(p.beta + cc + 1));
+          const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.gamma + cc));
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.beta + cc));
+          const float2 h0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h[k]));
+          const float2 l0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&l[k]));
+          const float2 h1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h[k + 1]));
+          const float2 l1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&l[k + 1]));
+          v[e + 0] = (h0.x + l0.x) + ((x[c + e + 0] - mean) * rstd * g4.x + b4.x);
+          v[e + 1] = (h0.y + l0.y) + ((x[c + e + 1] - mean) * rstd * g4.y + b4.y);
+          v[e + 2] = (h1.x + l1.x) + ((x[c + e + 2] - mean) * rstd * g4.z + b4.z);
+          v[e + 3] = (h1.y + l1.y) + ((x[c + e + 3] - mean) * rstd * g4.w + b4.w);
         }
       }
       store_planes32_v8(v, ph, pl);

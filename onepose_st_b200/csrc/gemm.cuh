@@ -209,6 +209,7 @@ gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep
       const int acc = it % Cfg::ACC_STAGES;
       const uint32_t acc_phase = (it / Cfg::ACC_STAGES) & 1;
       tile_coords(t, ctx.m_tile, ctx.n_tile);
+      Epi::prefetch(ep, ctx);  // global operands of the epilogue that do not depend on the accumulator
       ptx::mbar_wait(&tfull_bar[acc], acc_phase);
       ptx::tc_fence_after();
       ctx.tmem_acc = tmem_base + acc * BN + (static_cast<uint32_t>(ctx.quarter * 32) << 16);

@@ -160,6 +160,9 @@ __device__ __forceinline__ void ld_global_v8(const void* p, uint32_t (&r)[8]) {
                : "l"(p)
                : "memory");
 }
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
