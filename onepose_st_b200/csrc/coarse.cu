@@ -43,7 +43,8 @@ struct SimGeom {
   int mask_fill;              // 0: sim += -1e9 (OnePosePlus), 1: sim = -1e9 (LoFTR masked_fill_)
 };
 
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }  // robust path runs one epilogue group
+// named barrier of one epilogue group (4 warps); ids 1.. are reserved for the groups
+__device__ __forceinline__ void epi_bar(int group) { ptx::named_bar_sync(1 + group, 128); }
 
 // y = log2(e) * sim with the reference's masking semantics applied to sim first
 __device__ __forceinline__ float sim_log2(float acc, float scale, bool masked, int fill) {
@@ -101,7 +102,7 @@ struct EpiSimStats {
       }
 #pragma unroll
       for (int k = 0; k < 32; ++k) sc[buf][r][k] = row_valid ? y[k] : kNegInf;
-      epi_bar();
+      epi_bar(ctx.group);
       {
         const int cq = ctx.epi_warp, cc = ctx.lane;  // NB: epi_warp != quarter; any bijection of the 4 warps works here
         float v[32];
@@ -118,7 +119,7 @@ struct EpiSimStats {
         }
         part[buf][cq][cc] = make_float2(pm, ps);
       }
-      epi_bar();
+      epi_bar(ctx.group);
       if (ctx.epi_warp == 0) {
         float M = kNegInf;
 #pragma unroll
@@ -257,10 +258,8 @@ struct EpiSimSelect {
       }
       if (WRITE_CONF) {
         float* dst = p.conf_matrix + (static_cast<long long>(n) * g.L + i) * g.S + j0;
-        if ((g.S & 3) == 0 && j0 + 32 <= g.S) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k)
-            reinterpret_cast<float4*>(dst)[k] = make_float4(cf[4 * k], cf[4 * k + 1], cf[4 * k + 2], cf[4 * k + 3]);
+        if ((g.S & 7) == 0 && j0 + 32 <= g.S && (reinterpret_cast<uintptr_t>(p.conf_matrix) & 31) == 0) {
+          store_f32x32_v8(cf, dst);
         } else {
 #pragma unroll
           for (int k = 0; k < 32; ++k)
@@ -877,7 +876,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     SimGeom g{N, L, S, Lp, Sp, scale, mask_a, mask_b, mask_fill};
     {
       EpiSimStats<SIM_BN>::Params ep{g, w.rowpart, w.colpart};
-      if (int r = launch_gemm<SIM_BN, 5, 1, EpiSimStats<SIM_BN>>(pb.plan, ep, stream)) return r;
+      if (int r = launch_gemm<SIM_BN, 4, 2, EpiSimStats<SIM_BN>>(pb.plan, ep, stream)) return r;
     }
     {
       const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
@@ -889,10 +888,10 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       const float log2_thr_lo = log2f(thr) - 1e-3f;
       if (conf_matrix != nullptr) {
         EpiSimSelect<SIM_BN, true>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, conf_matrix};
-        if (int r = launch_gemm<SIM_BN, 5, 1, EpiSimSelect<SIM_BN, true>>(pb.plan, ep, stream)) return r;
+        if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, true>>(pb.plan, ep, stream)) return r;
       } else {
         EpiSimSelect<SIM_BN, false>::Params ep{g, w.lse_row, w.lse_col, thr, log2_thr_lo, w.cand, w.counters, w.cand_cap, nullptr};
-        if (int r = launch_gemm<SIM_BN, 5, 1, EpiSimSelect<SIM_BN, false>>(pb.plan, ep, stream)) return r;
+        if (int r = launch_gemm<SIM_BN, 5, 4, EpiSimSelect<SIM_BN, false>>(pb.plan, ep, stream)) return r;
       }
     }
   }
