@@ -57,7 +57,8 @@ def _worker(rank, world, port, n_units, width, q):
         for k in sharding.shard_units(n_units, rank, world):
             rr.append(_unit_rows(k, width))
         rows, counts = sharding.gather_matches(rr.rows(), rr.counts, n_units)
-        q.put((rank, rows, counts))
+        # plain lists: a tensor in an mp.Queue is shared through an fd that dies with the worker
+        q.put((rank, rows.tolist(), counts.tolist()))
     finally:
         dist.destroy_process_group()
 
@@ -77,8 +78,8 @@ def test_gather_gloo(world, n_units, width):
     want_rows = torch.cat([_unit_rows(k, width) for k in range(n_units)]) if n_units else torch.empty(0, width)
     want_counts = [_unit_rows(k, width).shape[0] for k in range(n_units)]
     for rank, rows, counts in got:
-        assert counts.tolist() == want_counts, rank
-        assert torch.equal(rows, want_rows), rank
+        assert counts == want_counts, rank
+        assert rows == want_rows.tolist(), rank
 
 
 def test_rows_layout():
