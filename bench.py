@@ -308,6 +308,18 @@ def run_ours(args):
                                        "frac": flops / t / 1e12 / peak, "traffic": None,
                                        "algorithmic": f"120*(L+S)*C^2 = {flops / 1e9:.1f} GFLOP per frame",
                                        "executed_flop_multiple": (3 if args.precision == 3 else 1)}
+    if "backbone_conv" in stages:
+        t = stages["backbone_conv"]["ms_per_frame"] * 1e-3
+        h2, h4, h8 = args.size // 2, args.size // 4, args.size // 8
+        flops = 2.0 * (h2 * h2 * (4 * 9 * 128 * 128 + 9 * 196 * 196 + 9 * 196 * 128 + 128 * 196)
+                       + h4 * h4 * (9 * 128 * 196 + 128 * 196 + 3 * 9 * 196 * 196 + 9 * 256 * 256 + 9 * 256 * 196 + 196 * 256)
+                       + h8 * h8 * (9 * 196 * 256 + 196 * 256 + 3 * 9 * 256 * 256 + 256 * 256))
+        peak = peaks["bf16_tflops_sustained"]
+        rooflines["backbone_conv"] = {"bound": "tensor", "achieved": flops / t / 1e12, "peak": peak, "unit": "TFLOP/s",
+                                      "frac": flops / t / 1e12 / peak, "traffic": None,
+                                      "kernel": "conv_kernel: fp16-operand tcgen05 implicit GEMM, 23 convolutions of ResNetFPN_8_2",
+                                      "algorithmic": f"sum 2*Ho*Wo*k*k*Cin*Cout = {flops / 1e9:.1f} GFLOP per frame",
+                                      "executed_flop_multiple": 1}
     if "fine_match" in stages and m_per_frame > 0:
         t = stages["fine_match"]["ms_per_frame"] * 1e-3
         by = m_per_frame * (4 * 128 * (25 + 1) + 20)
@@ -321,7 +333,9 @@ def run_ours(args):
         value = total_frames / (res["ms"] * 1e-3)
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": res["ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-               "dtype": "bf16x3 split products, f32 accumulate/IO" if args.precision == 3 else "bf16, f32 accumulate/IO",
+               "dtype": ("bf16x3 split products (matcher), " if args.precision == 3 else "bf16 (matcher), ")
+               + ("fp16 operands (backbone convolutions, TF32-grade like the reference on a GPU), "
+                  if torch.backends.cudnn.allow_tf32 else "fp32 cuDNN backbone, ") + "f32 accumulate/IO",
                "data": "synthetic", "config": config_dict(args, world),
                "matches_per_frame": m_per_frame, "gpu_launches": res["launches"], "clocks": res["clocks"],
                "stages_ms_per_frame": {k: round(v["ms_per_frame"], 4) for k, v in stages.items()},

@@ -150,6 +150,25 @@ int opb200_stem_conv7x7_s2_relu_nhwc(const float* image, const float* weight_tap
 /* x[p, c] = leaky_relu(x[p, c] + bias[c], slope): folded-BatchNorm shift + nn.LeakyReLU of the FPN heads. */
 int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels, int C, float slope, void* stream);
 
+/* ---- Backbone convolutions on tcgen05 (NHWC fp16 activations, fp32 accumulation) ----------------------
+ * Conv2d(k in {1,3}, stride in {1,2}, padding k/2, no dilation/groups) with BatchNorm folded into the weights, plus the
+ * BasicBlock / FPN-head tails: y = act(conv(x) + bias + res).  Replaces conv3x3/conv1x1 + BatchNorm2d + ReLU /
+ * LeakyReLU + residual add of BasicBlock.forward and the layer*_outconv* heads (src/models/OnePosePlus/backbone/
+ * resnet.py:11-60, 85-164; submodules/LoFTR/src/loftr/backbone/resnet_fpn.py).  fp16 operands carry the same 11-bit
+ * significand as the TF32 operands of the reference's cuDNN convolutions on a GPU.
+ *   x    [n, Hi, Wi, cin_s]  fp16, cin_s = input channels padded to a multiple of 16 (pad channels hold zeros)
+ *   w    [k*k][cout_s][cin_s] fp16 (tap-major, zero in padded rows/cols); cout_s in {128, 208, 256}
+ *   bias [cout_s] fp32 or NULL;  res [n, Ho, Wo, cout_s] fp16 or NULL
+ *   y16  [n, Ho, Wo, cout_s] fp16 and/or y32 (same shape, fp32); at least one non-NULL
+ *   act  0 none, 1 ReLU, 2 LeakyReLU(slope) */
+int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride,
+                           int cout_s, const float* bias, const void* res, void* y16, float* y32, int act, float slope,
+                           void* stream);
+/* fp16-output variant of opb200_stem_conv7x7_s2_relu_nhwc and fp16 variant of opb200_upsample2x_add_nhwc (C % 8 == 0). */
+int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight_tap_major, const float* bias, int n_batch,
+                                         int H, int W, int Cout, void* out_f16, void* stream);
+int opb200_upsample2x_add_nhwc_f16(const void* src, int n_batch, int Hs, int Ws, int C, void* dst, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

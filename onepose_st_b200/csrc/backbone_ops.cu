@@ -7,6 +7,7 @@
 //                                 layer{1,2}_outconv2 heads)
 // The convolutions themselves stay cuDNN; these two kernels only remove extra full
 // passes over the 1/2- and 1/4-resolution maps.  HBM-bound: 8 B (read+write dst) + ~1 B (src) per element.
+#include <cuda_fp16.h>
 #include "host.cuh"
 #include "../../include/opb200.h"
 
@@ -59,16 +60,72 @@ __global__ void __launch_bounds__(256) bias_leaky_relu_kernel(float4* __restrict
 }
 
 
+// fp16 NHWC variant: dst (fp16) += bilinear_x2(src (fp16)), interpolation in fp32, 8 channels per thread.
+__global__ void __launch_bounds__(256) upsample2x_add_f16_kernel(const uint4* __restrict__ src, int N, int Hs, int Ws, int C8,
+                                                                 uint4* __restrict__ dst, float ry, float rx) {
+  const int Ho = 2 * Hs, Wo = 2 * Ws;
+  const long long total = static_cast<long long>(N) * Ho * Wo * C8;
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % C8);
+    long long p = t / C8;
+    const int x = static_cast<int>(p % Wo);
+    p /= Wo;
+    const int y = static_cast<int>(p % Ho);
+    const int n = static_cast<int>(p / Ho);
+    const float sy = ry * y, sx = rx * x;
+    const int y0 = static_cast<int>(sy), x0 = static_cast<int>(sx);
+    const int y1 = y0 + (y0 < Hs - 1), x1 = x0 + (x0 < Ws - 1);
+    const float ly1 = sy - y0, lx1 = sx - x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
+    const uint4* s = src + static_cast<long long>(n) * Hs * Ws * C8;
+    const uint4 q00 = __ldg(s + (static_cast<long long>(y0) * Ws + x0) * C8 + c);
+    const uint4 q01 = __ldg(s + (static_cast<long long>(y0) * Ws + x1) * C8 + c);
+    const uint4 q10 = __ldg(s + (static_cast<long long>(y1) * Ws + x0) * C8 + c);
+    const uint4 q11 = __ldg(s + (static_cast<long long>(y1) * Ws + x1) * C8 + c);
+    uint4 d = dst[t];
+    const uint32_t* a00 = reinterpret_cast<const uint32_t*>(&q00);
+    const uint32_t* a01 = reinterpret_cast<const uint32_t*>(&q01);
+    const uint32_t* a10 = reinterpret_cast<const uint32_t*>(&q10);
+    const uint32_t* a11 = reinterpret_cast<const uint32_t*>(&q11);
+    uint32_t* dd = reinterpret_cast<uint32_t*>(&d);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 v00 = __half22float2(*reinterpret_cast<const __half2*>(&a00[i]));
+      const float2 v01 = __half22float2(*reinterpret_cast<const __half2*>(&a01[i]));
+      const float2 v10 = __half22float2(*reinterpret_cast<const __half2*>(&a10[i]));
+      const float2 v11 = __half22float2(*reinterpret_cast<const __half2*>(&a11[i]));
+      float2 o = __half22float2(*reinterpret_cast<const __half2*>(&dd[i]));
+      o.x += ly0 * (lx0 * v00.x + lx1 * v01.x) + ly1 * (lx0 * v10.x + lx1 * v11.x);
+      o.y += ly0 * (lx0 * v00.y + lx1 * v01.y) + ly1 * (lx0 * v10.y + lx1 * v11.y);
+      const __half2 h = __floats2half2_rn(o.x, o.y);
+      dd[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    dst[t] = d;
+  }
+}
+
 // Stem of ResNetFPN_8_2: 7x7 stride-2 pad-3 convolution of a 1-channel image + folded-BatchNorm bias + ReLU,
 // written channels-last (reference: backbone/resnet.py:141 `relu(bn1(conv1(x)))`, conv1 = Conv2d(1, 128, 7, 2, 3)).
 // One block = 16 x 16 output pixels of one image; the 37 x 37 input patch and the [49][COUT] weights sit in shared
 // memory; a thread owns two output pixels (rows ty and ty + 8) and walks the output channels 32 at a time, so
 // every broadcast weight float4 feeds two pixels.  fp32 FMA (exact w.r.t. the fp32 reference up to summation
 // order).  Output traffic dominates: 4 * COUT bytes per output pixel.
-template <int COUT>
+__device__ __forceinline__ void stem_store32(const float (&v)[32], float* dst) { store_f32x32_v8(v, dst); }
+__device__ __forceinline__ void stem_store32(const float (&v)[32], __half* dst) {
+  uint32_t h[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const __half2 p = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+    h[i] = *reinterpret_cast<const uint32_t*>(&p);
+  }
+  ptx::st_global_v8(dst, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+  ptx::st_global_v8(dst + 16, h[8], h[9], h[10], h[11], h[12], h[13], h[14], h[15]);
+}
+
+template <int COUT, typename OutT>
 __global__ void __launch_bounds__(128) stem_conv7x7_s2_kernel(const float* __restrict__ img, const float* __restrict__ w,
                                                               const float* __restrict__ bias, int H, int W, int Ho, int Wo,
-                                                              float* __restrict__ out) {
+                                                              OutT* __restrict__ out) {
   __shared__ float patch[37][38];
   __shared__ __align__(16) float ws[49][COUT];
   const int n = blockIdx.z, oy0 = blockIdx.y * 16, ox0 = blockIdx.x * 16;
@@ -117,8 +174,8 @@ __global__ void __launch_bounds__(128) stem_conv7x7_s2_kernel(const float* __res
     const int ox = ox0 + tx;
     if (ox < Wo) {
       const int oya = oy0 + ty, oyb = oy0 + ty + 8;
-      if (oya < Ho) store_f32x32_v8(a0, out + ((static_cast<long long>(n) * Ho + oya) * Wo + ox) * COUT + c0);
-      if (oyb < Ho) store_f32x32_v8(a1, out + ((static_cast<long long>(n) * Ho + oyb) * Wo + ox) * COUT + c0);
+      if (oya < Ho) stem_store32(a0, out + ((static_cast<long long>(n) * Ho + oya) * Wo + ox) * COUT + c0);
+      if (oyb < Ho) stem_store32(a1, out + ((static_cast<long long>(n) * Ho + oyb) * Wo + ox) * COUT + c0);
     }
   }
 }
@@ -171,7 +228,40 @@ int opb200_stem_conv7x7_s2_relu_nhwc(const float* image, const float* weight_tap
   OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(out) & 31) == 0, "output must be 32-byte aligned");
   const int Ho = (H + 2 * 3 - 7) / 2 + 1, Wo = (W + 2 * 3 - 7) / 2 + 1;
   dim3 grid((Wo + 15) / 16, (Ho + 15) / 16, n_batch);
-  stem_conv7x7_s2_kernel<128><<<grid, 128, 0, static_cast<cudaStream_t>(stream_)>>>(image, weight_tap_major, bias, H, W, Ho, Wo, out);
+  stem_conv7x7_s2_kernel<128, float><<<grid, 128, 0, static_cast<cudaStream_t>(stream_)>>>(image, weight_tap_major, bias, H, W, Ho, Wo, out);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight_tap_major, const float* bias, int n_batch,
+                                         int H, int W, int Cout, void* out_f16, void* stream_) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(image && weight_tap_major && bias && out_f16, "null pointer");
+  OPB_CHECK_ARG(n_batch >= 1 && H >= 1 && W >= 1, "bad shape");
+  OPB_CHECK_ARG(Cout == 128, "stem kernel is instantiated for 128 output channels (initial_dim of ResNetFPN_8_2)");
+  OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(out_f16) & 31) == 0, "output must be 32-byte aligned");
+  const int Ho = (H + 2 * 3 - 7) / 2 + 1, Wo = (W + 2 * 3 - 7) / 2 + 1;
+  dim3 grid((Wo + 15) / 16, (Ho + 15) / 16, n_batch);
+  stem_conv7x7_s2_kernel<128, __half><<<grid, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
+      image, weight_tap_major, bias, H, W, Ho, Wo, static_cast<__half*>(out_f16));
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_upsample2x_add_nhwc_f16(const void* src, int n_batch, int Hs, int Ws, int C, void* dst, void* stream_) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(src && dst, "null pointer");
+  OPB_CHECK_ARG(n_batch >= 1 && Hs >= 1 && Ws >= 1 && C >= 8 && C % 8 == 0, "bad shape (C must be a multiple of 8)");
+  OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0, "16-byte alignment");
+  const long long total = static_cast<long long>(n_batch) * 4 * Hs * Ws * (C / 8);
+  const float ry = Hs > 1 ? static_cast<float>(Hs - 1) / static_cast<float>(2 * Hs - 1) : 0.f;
+  const float rx = Ws > 1 ? static_cast<float>(Ws - 1) / static_cast<float>(2 * Ws - 1) : 0.f;
+  const long long blocks = (total + 255) / 256;
+  const int grid = static_cast<int>(blocks < num_sms() * 16LL ? blocks : num_sms() * 16LL);
+  upsample2x_add_f16_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const uint4*>(src), n_batch, Hs, Ws, C / 8, static_cast<uint4*>(dst), ry, rx);
   count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;

@@ -60,6 +60,37 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
+int encode_tmap_16bit(CUtensorMap* out, bool fp16, int rank, const void* base, const uint64_t* gdim,
+                      const uint64_t* gstride_bytes, const uint32_t* box, const uint32_t* elem_strides) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) {
+    set_last_error("cuTensorMapEncodeTiled entry point not available from the driver");
+    return OPB_ERR_CUDA;
+  }
+  OPB_CHECK_ARG(rank >= 2 && rank <= 5, "TMA rank must be 2..5");
+  OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base address must be 16-byte aligned");
+  cuuint64_t gd[5], gs[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gd[i] = gdim[i];
+    bx[i] = box[i];
+    es[i] = elem_strides[i];
+    OPB_CHECK_ARG(box[i] >= 1 && box[i] <= 256, "TMA box extent must be in [1,256]");
+    if (i + 1 < rank) {
+      gs[i] = gstride_bytes[i];
+      OPB_CHECK_ARG(gs[i] % 16 == 0, "TMA global strides must be multiples of 16 bytes");
+    }
+  }
+  CUresult r = fn(out, fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank,
+                  const_cast<void*>(base), gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(r)));
+    return OPB_ERR_CUDA;
+  }
+  return OPB_OK;
+}
+
 int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_elems,
                    uint32_t box_rows) {
   EncodeTiledFn fn = get_encode_fn();

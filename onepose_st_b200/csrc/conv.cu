@@ -1,0 +1,370 @@
+// Implicit-GEMM convolution (1x1 / 3x3, stride 1 / 2, "same" padding) on tcgen05 tensor cores for the ResNet-FPN
+// backbone of the matchers (reference: src/models/OnePosePlus/backbone/resnet.py:11-164 BasicBlock / ResNetFPN_8_2,
+// submodules/LoFTR/src/loftr/backbone/resnet_fpn.py).  Activations are NHWC fp16, weights fp16 [tap][Cout][Cin]
+// with BatchNorm folded in; accumulation is fp32 in TMEM.  fp16 carries the same 11-bit significand as the TF32
+// operands the reference's cuDNN convolutions use on a GPU (torch.backends.cudnn.allow_tf32 defaults to True), at
+// twice the tensor-core rate and half the activation traffic.
+//
+//   D[pixels x Cout] = sum over taps (ky,kx) and 64-channel chunks  X[pixel + (ky,kx) - pad][chunk] * W[tap][Cout][chunk]^T
+//
+// One output tile = MSUB sub-tiles of 8 x 16 output pixels (128 GEMM rows each) x all BN = Cout channels.  The A operand
+// of one (tap, chunk) k-block is ONE 4-D TMA box {64 ch, 16 (x stride), 8*MSUB (x stride), 1} of the NHWC tensor placed at
+// the shifted pixel origin: TMA's out-of-bounds zero fill IS the convolution's zero padding, and its element strides
+// give the stride-2 sampling, so no im2col buffer ever exists.  The B operand is the [BN x 64] weight slab of that tap.
+// Both sub-tiles consume the same weight slab (MSUB = 2 halves the weight refetch per flop).
+// Warp roles as in gemm.cuh: warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2..9 epilogue
+// (bias + residual + ReLU / LeakyReLU, fp16 and/or fp32 NHWC stores, 32 bytes per lane per store).
+#include <cuda_fp16.h>
+#include "host.cuh"
+#include "../../include/opb200.h"
+
+namespace opb {
+
+constexpr int CONV_TW = 16;  // output pixels per tile row
+constexpr int CONV_TH = 8;   // output rows per sub-tile (8 x 16 = 128 GEMM rows)
+
+struct ConvPlan {
+  CUtensorMap x_map;  // 4-D (C, W, H, N) fp16
+  CUtensorMap w_map;  // 2-D [taps * BN, Cin_s] fp16
+  int n_img, Ho, Wo;
+  int tiles_x, tiles_y, num_tiles;
+  int ksize, pad, stride;
+  int nchunks;  // 64-channel chunks per tap
+  int nk_last;  // K=16 MMAs in the last chunk (1..4)
+};
+
+struct ConvEpi {
+  const float* bias;  // [BN] or null
+  const __half* res;  // NHWC [n, Ho, Wo, BN] residual added before the activation, or null
+  __half* y16;        // NHWC fp16 output or null
+  float* y32;         // NHWC fp32 output or null
+  int act;            // 0 none, 1 ReLU, 2 LeakyReLU(slope)
+  float slope;
+};
+
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
+  return (1u << 4) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
+}
+
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const void* tmap, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(ptx::smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(ptx::smem_u32(bar)), "r"(c0), "r"(c1),
+      "r"(c2), "r"(c3)
+      : "memory");
+}
+
+template <int BN, int MSUB>
+struct ConvCfg {
+  static constexpr int A_BYTES = MSUB * BLOCK_M * BLOCK_K * 2;
+  static constexpr int B_BYTES = BN * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int ACC_COLS = MSUB * BN;
+  static constexpr int ACC_STAGES = (2 * ACC_COLS <= 512) ? 2 : 1;
+  static constexpr int TMEM_COLS = (ACC_STAGES * ACC_COLS <= 128) ? 128 : (ACC_STAGES * ACC_COLS <= 256) ? 256 : 512;
+  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 6 ? 6 : (200 * 1024) / STAGE_BYTES;
+  static constexpr int SMEM = 1024 + STAGES * STAGE_BYTES + 256;
+  static_assert(BN % 16 == 0 && BN >= 16 && BN <= 256, "UMMA N");
+  static_assert(STAGE_BYTES % 1024 == 0, "stage alignment");
+  static_assert(ACC_COLS <= 512, "TMEM");
+  static_assert(STAGES >= 3, "ring too shallow");
+};
+
+// 16 accumulator columns of one pixel: bias, residual, activation, stores.
+__device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const ConvEpi& ep, long long off, int c0) {
+  float v[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+  if (ep.bias != nullptr) {
+    const float4* b = reinterpret_cast<const float4*>(ep.bias + c0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 f = __ldg(b + q);
+      v[4 * q] += f.x, v[4 * q + 1] += f.y, v[4 * q + 2] += f.z, v[4 * q + 3] += f.w;
+    }
+  }
+  if (ep.res != nullptr) {
+    uint32_t h[8];
+    ptx::ld_global_v8(ep.res + off + c0, h);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&h[i]));
+      v[2 * i] += f.x, v[2 * i + 1] += f.y;
+    }
+  }
+  if (ep.act == 1) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+  } else if (ep.act == 2) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * ep.slope;
+  }
+  if (ep.y16 != nullptr) {
+    uint32_t h[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const __half2 p = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+      h[i] = *reinterpret_cast<const uint32_t*>(&p);
+    }
+    ptx::st_global_v8(ep.y16 + off + c0, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+  }
+  if (ep.y32 != nullptr) {
+    float* d = ep.y32 + off + c0;
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+      ptx::st_global_v8(d + 8 * q, __float_as_uint(v[8 * q]), __float_as_uint(v[8 * q + 1]), __float_as_uint(v[8 * q + 2]),
+                        __float_as_uint(v[8 * q + 3]), __float_as_uint(v[8 * q + 4]), __float_as_uint(v[8 * q + 5]),
+                        __float_as_uint(v[8 * q + 6]), __float_as_uint(v[8 * q + 7]));
+  }
+}
+
+template <int BN, int MSUB>
+__global__ void __launch_bounds__(64 + 256, 1) conv_kernel(const __grid_constant__ ConvPlan plan, const ConvEpi ep) {
+  using Cfg = ConvCfg<BN, MSUB>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&plan.x_map);
+    ptx::prefetch_tmap(&plan.w_map);
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tfull_bar[s], 1);
+      ptx::mbar_init(&tempty_bar[s], 8);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int taps = plan.ksize * plan.ksize;
+  const int tiles_per_img = plan.tiles_x * plan.tiles_y;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (ptx::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < plan.num_tiles; t += gridDim.x) {
+        const int n = t / tiles_per_img;
+        const int r = t - n * tiles_per_img;
+        const int ty = r / plan.tiles_x, tx = r - ty * plan.tiles_x;
+        const int ix0 = tx * CONV_TW * plan.stride - plan.pad;
+        const int iy0 = ty * (CONV_TH * MSUB) * plan.stride - plan.pad;
+        for (int tap = 0; tap < taps; ++tap) {
+          const int ky = tap / plan.ksize, kx = tap - ky * plan.ksize;
+          for (int ch = 0; ch < plan.nchunks; ++ch) {
+            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+            ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+            uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+            tma_load_4d(sa, &plan.x_map, &full_bar[stage], ch * BLOCK_K, ix0 + kx, iy0 + ky, n);
+            ptx::tma_load_2d(sa + Cfg::A_BYTES, &plan.w_map, &full_bar[stage], ch * BLOCK_K, tap * BN);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = make_idesc_f16(BLOCK_M, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    const int total_kb = taps * plan.nchunks;
+    for (int t = blockIdx.x; t < plan.num_tiles; t += gridDim.x, ++it) {
+      const int acc = it % Cfg::ACC_STAGES;
+      const uint32_t acc_phase = (it / Cfg::ACC_STAGES) & 1;
+      ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_COLS;
+      int ch = 0;
+      for (int kb = 0; kb < total_kb; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase);
+        ptx::tc_fence_after();
+        const int nk = (ch == plan.nchunks - 1) ? plan.nk_last : BLOCK_K / 16;
+        if (ptx::elect_one()) {
+          const uint32_t a_addr = ptx::smem_u32(smem + stage * Cfg::STAGE_BYTES);
+          const uint64_t b_desc = ptx::make_desc_sw128(a_addr + Cfg::A_BYTES);
+#pragma unroll
+          for (int s = 0; s < MSUB; ++s) {
+            const uint64_t a_desc = ptx::make_desc_sw128(a_addr + s * (BLOCK_M * BLOCK_K * 2));
+            for (int k = 0; k < nk; ++k)
+              ptx::mma_bf16(d_tmem + s * BN, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+          }
+          ptx::mma_commit(&empty_bar[stage]);
+          if (kb == total_kb - 1) ptx::mma_commit(&tfull_bar[acc]);
+        }
+        __syncwarp();
+        if (++ch == plan.nchunks) ch = 0;
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue: 8 warps, two per TMEM lane quarter
+    const int quarter = warp & 3;
+    const int part = (warp - 2) >> 2;  // MSUB == 2: the sub-tile; MSUB == 1: which half of the 16-column chunks
+    constexpr int NCH = BN / 16;
+    const int sub = MSUB == 2 ? part : 0;
+    const int ch_begin = MSUB == 2 ? 0 : (part == 0 ? 0 : (NCH + 1) / 2);
+    const int ch_end = MSUB == 2 ? NCH : (part == 0 ? (NCH + 1) / 2 : NCH);
+    const int row = quarter * 32 + lane;  // GEMM row inside the sub-tile
+    const int hy = row / CONV_TW, wx = row - hy * CONV_TW;
+    int it = 0;
+    for (int t = blockIdx.x; t < plan.num_tiles; t += gridDim.x, ++it) {
+      const int acc = it % Cfg::ACC_STAGES;
+      const uint32_t acc_phase = (it / Cfg::ACC_STAGES) & 1;
+      const int n = t / tiles_per_img;
+      const int r = t - n * tiles_per_img;
+      const int ty = r / plan.tiles_x, tx = r - ty * plan.tiles_x;
+      const int oy = ty * (CONV_TH * MSUB) + sub * CONV_TH + hy, ox = tx * CONV_TW + wx;
+      const bool valid = oy < plan.Ho && ox < plan.Wo;
+      const long long off = ((static_cast<long long>(n) * plan.Ho + oy) * plan.Wo + ox) * BN;
+      if (valid && ep.res != nullptr) ptx::prefetch_l2(ep.res + off + ch_begin * 16);
+      ptx::mbar_wait(&tfull_bar[acc], acc_phase);
+      ptx::tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * Cfg::ACC_COLS + sub * BN + (static_cast<uint32_t>(quarter * 32) << 16);
+      int c = ch_begin;
+      for (; c + 1 < ch_end; c += 2) {
+        uint32_t r0[16], r1[16];
+        ptx::tmem_ld16(taddr + c * 16, r0);
+        ptx::tmem_ld16(taddr + c * 16 + 16, r1);
+        ptx::tmem_ld_wait();
+        if (valid) {
+          conv_epi_chunk(r0, ep, off, c * 16);
+          conv_epi_chunk(r1, ep, off, c * 16 + 16);
+        }
+      }
+      if (c < ch_end) {
+        uint32_t r0[16];
+        ptx::tmem_ld16(taddr + c * 16, r0);
+        ptx::tmem_ld_wait();
+        if (valid) conv_epi_chunk(r0, ep, off, c * 16);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty_bar[acc]);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+template <int BN, int MSUB>
+static int launch_conv(const ConvPlan& plan, const ConvEpi& ep, cudaStream_t stream) {
+  using Cfg = ConvCfg<BN, MSUB>;
+  auto kern = conv_kernel<BN, MSUB>;
+  static_assert(Cfg::SMEM <= 227 * 1024, "shared memory budget exceeded");
+  static bool configured = false;
+  if (!configured) {
+    OPB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    configured = true;
+  }
+  int grid = num_sms();
+  if (plan.num_tiles < grid) grid = plan.num_tiles;
+  kern<<<grid, 64 + 256, Cfg::SMEM, stream>>>(plan, ep);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+template <int BN>
+static int conv_dispatch(ConvPlan& plan, const ConvEpi& ep, const void* x, int Hi, int Wi, int cin_s, cudaStream_t stream) {
+  // two stacked sub-tiles per CTA tile when that still leaves every SM at least two tiles
+  const int tx = (plan.Wo + CONV_TW - 1) / CONV_TW;
+  const int ty2 = (plan.Ho + 2 * CONV_TH - 1) / (2 * CONV_TH);
+  const bool two = static_cast<long long>(plan.n_img) * tx * ty2 >= 2LL * num_sms();
+  const int msub = two ? 2 : 1;
+  plan.tiles_x = tx;
+  plan.tiles_y = (plan.Ho + msub * CONV_TH - 1) / (msub * CONV_TH);
+  plan.num_tiles = plan.n_img * plan.tiles_x * plan.tiles_y;
+  const uint32_t s = static_cast<uint32_t>(plan.stride);
+  const uint64_t gdim[4] = {static_cast<uint64_t>(cin_s), static_cast<uint64_t>(Wi), static_cast<uint64_t>(Hi),
+                            static_cast<uint64_t>(plan.n_img)};
+  const uint64_t gstr[3] = {static_cast<uint64_t>(cin_s) * 2, static_cast<uint64_t>(cin_s) * 2 * Wi,
+                            static_cast<uint64_t>(cin_s) * 2 * Wi * Hi};
+  const uint32_t box[4] = {BLOCK_K, CONV_TW * s, static_cast<uint32_t>(CONV_TH * msub) * s, 1};
+  const uint32_t estr[4] = {1, s, s, 1};
+  if (int r = encode_tmap_16bit(&plan.x_map, true, 4, x, gdim, gstr, box, estr)) return r;
+  return two ? launch_conv<BN, 2>(plan, ep, stream) : launch_conv<BN, 1>(plan, ep, stream);
+}
+
+}  // namespace opb
+
+using namespace opb;
+
+extern "C" {
+
+int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride, int cout_s,
+                           const float* bias, const void* res, void* y16, float* y32, int act, float slope, void* stream_) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(x && w && (y16 || y32), "null pointer");
+  OPB_CHECK_ARG(n_img >= 1 && Hi >= 1 && Wi >= 1, "bad shape");
+  OPB_CHECK_ARG(ksize == 1 || ksize == 3, "kernel size must be 1 or 3");
+  OPB_CHECK_ARG(stride == 1 || stride == 2, "stride must be 1 or 2");
+  OPB_CHECK_ARG(cin_s >= 16 && cin_s % 16 == 0, "input channel stride must be a multiple of 16");
+  OPB_CHECK_ARG(cout_s == 128 || cout_s == 208 || cout_s == 256, "output channel stride must be 128, 208 or 256");
+  OPB_CHECK_ARG(act >= 0 && act <= 2, "act must be 0 (none), 1 (ReLU) or 2 (LeakyReLU)");
+  OPB_CHECK_ARG(((reinterpret_cast<uintptr_t>(y16) | reinterpret_cast<uintptr_t>(y32) | reinterpret_cast<uintptr_t>(res) |
+                  reinterpret_cast<uintptr_t>(bias)) & 31) == 0, "bias / residual / outputs must be 32-byte aligned");
+  ConvPlan plan;
+  std::memset(&plan, 0, sizeof(plan));
+  plan.n_img = n_img;
+  plan.ksize = ksize;
+  plan.pad = ksize / 2;
+  plan.stride = stride;
+  plan.Ho = (Hi + 2 * plan.pad - ksize) / stride + 1;
+  plan.Wo = (Wi + 2 * plan.pad - ksize) / stride + 1;
+  plan.nchunks = (cin_s + BLOCK_K - 1) / BLOCK_K;
+  plan.nk_last = (cin_s - (plan.nchunks - 1) * BLOCK_K) / 16;
+  ConvEpi ep;
+  ep.bias = bias;
+  ep.res = static_cast<const __half*>(res);
+  ep.y16 = static_cast<__half*>(y16);
+  ep.y32 = y32;
+  ep.act = act;
+  ep.slope = slope;
+  {
+    const uint64_t gdim[2] = {static_cast<uint64_t>(cin_s), static_cast<uint64_t>(ksize) * ksize * cout_s};
+    const uint64_t gstr[1] = {static_cast<uint64_t>(cin_s) * 2};
+    const uint32_t box[2] = {BLOCK_K, static_cast<uint32_t>(cout_s)};
+    const uint32_t estr[2] = {1, 1};
+    if (int r = encode_tmap_16bit(&plan.w_map, true, 2, w, gdim, gstr, box, estr)) return r;
+  }
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  switch (cout_s) {
+    case 128: return conv_dispatch<128>(plan, ep, x, Hi, Wi, cin_s, stream);
+    case 208: return conv_dispatch<208>(plan, ep, x, Hi, Wi, cin_s, stream);
+    default: return conv_dispatch<256>(plan, ep, x, Hi, Wi, cin_s, stream);
+  }
+}
+
+}  // extern "C"

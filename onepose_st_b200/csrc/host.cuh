@@ -47,6 +47,11 @@ int num_sms();
 int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_elems,
                    uint32_t box_rows);
 
+// General 16-bit (bf16 / fp16) tiled descriptor of rank 2..5 with 128-byte swizzle (innermost box extent must be 64
+// elements); gdim / box / elem_strides innermost first, gstride_bytes for dims 1..rank-1.
+int encode_tmap_16bit(CUtensorMap* out, bool fp16, int rank, const void* base, const uint64_t* gdim,
+                      const uint64_t* gstride_bytes, const uint32_t* box, const uint32_t* elem_strides);
+
 struct PlanBuilder {
   GemmPlan plan;
   int status = OPB_OK;

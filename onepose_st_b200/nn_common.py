@@ -2,8 +2,8 @@
 
 Everything that is a hot-path operator calls the sm_100a C-ABI through ``ops``; the modules here only
 hold parameters under the reference's names (so reference checkpoints load with ``strict=True``),
-cache packed weights, and move pointers around.  The ResNet-FPN backbone stays PyTorch/cuDNN
-(not one of north_star's kernels; first of the "next" rows in 8f).
+cache packed weights, and move pointers around.  The ResNet-FPN backbone (SURVEY.md 8a row a2 / first of the
+"next" rows in 8f) runs on own tcgen05 convolutions at TF32-grade precision, or on cuDNN when exact fp32 is asked.
 """
 import math
 from typing import Optional, Sequence
@@ -79,13 +79,20 @@ class ResNetFPN_8_2(nn.Module):
         c1 = self.layer1_outconv2(self.layer1_outconv(x1) + up(c2))
         return c3, c1
 
-    def fused(self) -> "FusedBackbone":
-        """Inference executor (BN folded into the convolutions, channels-last, cuDNN fused
-        conv+bias(+residual)+ReLU); rebuilt whenever a parameter or buffer changes."""
-        key = tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers()))
+    # "auto": follow torch.backends.cudnn.allow_tf32, the switch that decides the precision of the reference's own
+    # convolutions on a GPU -- True (torch's default): fp16-operand tcgen05 convolutions (same 11-bit significand as
+    # TF32); False: exact-fp32 cuDNN executor.  "f16" / "fp32" force one.
+    conv_precision = "auto"
+
+    def fused(self):
+        """Inference executor (BN folded into the convolutions, NHWC): ``FusedBackboneF16`` (own tcgen05 implicit-GEMM
+        convolutions) or ``FusedBackbone`` (cuDNN fp32); rebuilt whenever a parameter or buffer changes."""
+        f16 = self.conv_precision == "f16" or (self.conv_precision == "auto" and torch.backends.cudnn.allow_tf32)
+        f16 = f16 and FusedBackboneF16.supports(self)
+        key = (f16,) + tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers()))
         fb = self.__dict__.get("_fused_cache")
         if fb is None or fb[0] != key:
-            fb = (key, FusedBackbone(self))
+            fb = (key, FusedBackboneF16(self) if f16 else FusedBackbone(self))
             self.__dict__["_fused_cache"] = fb
         return fb[1]
 
@@ -107,6 +114,25 @@ def _fold_bn(conv: nn.Conv2d, bn: Optional[nn.BatchNorm2d]):
     if conv.bias is not None:
         b = b + conv.bias.detach().float() * g
     return w.contiguous(memory_format=torch.channels_last), b.contiguous()
+
+
+def _cs(c: int) -> int:
+    """Channel count padded to the multiple of 16 the fp16 tensor-core convolution works in."""
+    return (c + 15) // 16 * 16
+
+
+def pack_conv_f16(w: torch.Tensor, b: Optional[torch.Tensor]):
+    """[Cout, Cin, k, k] fp32 (BatchNorm already folded) -> ([k*k*Cout_s, Cin_s] fp16 tap-major, [Cout_s] fp32 bias or
+    None), zero in the padded rows / columns."""
+    cout, cin, k, _ = w.shape
+    cin_s, cout_s = _cs(cin), _cs(cout)
+    wp = torch.zeros(k * k, cout_s, cin_s, dtype=torch.float32, device=w.device)
+    wp[:, :cout, :cin] = w.detach().float().permute(2, 3, 0, 1).reshape(k * k, cout, cin)
+    bp = None
+    if b is not None:
+        bp = torch.zeros(cout_s, dtype=torch.float32, device=w.device)
+        bp[:cout] = b.detach().float()
+    return wp.reshape(k * k * cout_s, cin_s).half().contiguous(), bp
 
 
 class FusedBackbone:
@@ -172,6 +198,68 @@ class FusedBackbone:
             c1 = self._head(ops.upsample2x_add_(cl(F.conv2d(x1, self.l1_out[0])), cl(c2)), self.head1)
             return c3, c1
         raise NotImplementedError("ResNetFPN_8_2 on CUDA needs image sides that are multiples of 8")
+
+
+class FusedBackboneF16:
+    """Inference-only executor of a ``ResNetFPN_8_2`` on the tcgen05 convolution kernel (csrc/conv.cu): BatchNorm
+    folded, NHWC fp16 activations (channels padded to a multiple of 16), fp32 accumulation, bias / residual / ReLU /
+    LeakyReLU fused into the convolution epilogues; only the 7x7 stem and the bilinear x2 + add of the FPN are
+    separate (own) kernels.  The two outputs are written in fp32 by the last epilogues and returned as
+    channels-last [N,C,H,W] views, like ``FusedBackbone``."""
+
+    @staticmethod
+    def supports(m: "ResNetFPN_8_2") -> bool:
+        d0 = m.conv1.weight.shape[0]
+        dims = [m.layer1[0].conv1.weight.shape[0], m.layer2[0].conv1.weight.shape[0], m.layer3[0].conv1.weight.shape[0]]
+        return (tuple(m.conv1.weight.shape) == (128, 1, 7, 7) and d0 == 128 and all(_cs(d) in (128, 208, 256) for d in dims)
+                and _cs(dims[2]) == dims[2] and _cs(dims[0]) == dims[0])
+
+    def __init__(self, m: "ResNetFPN_8_2"):
+        w, b = _fold_bn(m.conv1, m.bn1)
+        self.stem = (w.reshape(128, 49).t().contiguous(), b)
+        pk = lambda conv, bn: pack_conv_f16(*_fold_bn(conv, bn)) if (bn is not None or conv.bias is not None) \
+            else (pack_conv_f16(conv.weight, None)[0], None)
+        self.blocks = []
+        for layer in (m.layer1, m.layer2, m.layer3):
+            for blk in layer:
+                ds = pk(blk.downsample[0], blk.downsample[1]) if blk.downsample is not None else None
+                self.blocks.append((pk(blk.conv1, blk.bn1), pk(blk.conv2, blk.bn2), ds, blk.conv1.stride[0]))
+        self.l3_out, self.l2_out, self.l1_out = pk(m.layer3_outconv, None), pk(m.layer2_outconv, None), pk(m.layer1_outconv, None)
+        self.head2 = (pk(m.layer2_outconv2[0], m.layer2_outconv2[1]), pk(m.layer2_outconv2[3], None),
+                      m.layer2_outconv2[2].negative_slope)
+        self.head1 = (pk(m.layer1_outconv2[0], m.layer1_outconv2[1]), pk(m.layer1_outconv2[3], None),
+                      m.layer1_outconv2[2].negative_slope)
+
+    @staticmethod
+    def _block(x, blk):
+        (w1, b1), (w2, b2), ds, stride = blk
+        y = ops.conv2d_nhwc_f16(x, w1, 3, stride, b1, None, 1)
+        if ds is not None:
+            x = ops.conv2d_nhwc_f16(x, ds[0], 1, stride, ds[1], None, 0)
+        return ops.conv2d_nhwc_f16(y, w2, 3, 1, b2, x, 1)
+
+    @staticmethod
+    def _head(x, head, out_f32):
+        (w0, b0), (w1, b1), slope = head
+        y = ops.conv2d_nhwc_f16(x, w0, 3, 1, b0, None, 2, slope)
+        return ops.conv2d_nhwc_f16(y, w1, 3, 1, b1, None, 0, out_f16=not out_f32, out_f32=out_f32)
+
+    def __call__(self, x):
+        if x.shape[2] % 8 or x.shape[3] % 8:
+            raise NotImplementedError("ResNetFPN_8_2 on CUDA needs image sides that are multiples of 8")
+        x = ops.stem_conv_relu_f16(x, self.stem[0], self.stem[1])
+        feats = []
+        for i, blk in enumerate(self.blocks):
+            x = self._block(x, blk)
+            if i % 2 == 1:
+                feats.append(x)
+        x1, x2, x3 = feats
+        c3_16, c3 = ops.conv2d_nhwc_f16(x3, self.l3_out[0], 1, 1, self.l3_out[1], None, 0, out_f16=True, out_f32=True)
+        l2 = ops.upsample2x_add_f16_(ops.conv2d_nhwc_f16(x2, self.l2_out[0], 1, 1, self.l2_out[1], None, 0), c3_16)
+        c2 = self._head(l2, self.head2, False)
+        l1 = ops.upsample2x_add_f16_(ops.conv2d_nhwc_f16(x1, self.l1_out[0], 1, 1, self.l1_out[1], None, 0), c2)
+        c1 = self._head(l1, self.head1, True)
+        return c3.permute(0, 3, 1, 2), c1.permute(0, 3, 1, 2)
 
 
 # --------------------------------------------------------------------------------------------------

@@ -353,3 +353,67 @@ def linear_attention(q, k, v, q_mask=None, kv_mask=None, eps: float = 1e-6) -> t
                                    ctypes.c_float(eps), _lib.ptr(out), _lib.ptr(ws), _c_sz(ws.numel()), _lib.stream_ptr())
     _lib.check(st, "opb200_linear_attention")
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# fp16 NHWC backbone (tcgen05 implicit-GEMM convolutions).  Tensors here are plain contiguous
+# [N, H, W, Cs] fp16 with Cs = channels padded to a multiple of 16 (pad channels are zero).
+# ------------------------------------------------------------------------------------------------
+def conv2d_nhwc_f16(x: torch.Tensor, w: torch.Tensor, ksize: int, stride: int = 1, bias: Optional[torch.Tensor] = None,
+                    res: Optional[torch.Tensor] = None, act: int = 0, slope: float = 0.0, out_f16: bool = True,
+                    out_f32: bool = False, stage: str = "backbone_conv"):
+    """y = act(conv_k(x) + bias + res): x [N,Hi,Wi,Cin_s] fp16, w [k*k*Cout_s, Cin_s] fp16 tap-major, bias [Cout_s] fp32,
+    res [N,Ho,Wo,Cout_s] fp16.  Returns the fp16 output, the fp32 output, or (fp16, fp32) when both are asked."""
+    _need_cuda(x, w, bias, res)
+    if x.dtype != torch.float16 or w.dtype != torch.float16 or not x.is_contiguous() or not w.is_contiguous() or x.dim() != 4:
+        raise _lib.Opb200Error("conv2d_nhwc_f16: contiguous fp16 [N,H,W,C] input and fp16 weights required")
+    n, hi, wi, cin_s = x.shape
+    if w.dim() != 2 or w.shape[1] != cin_s or w.shape[0] % (ksize * ksize):
+        raise _lib.Opb200Error(f"conv2d_nhwc_f16: weight shape {tuple(w.shape)} does not fit k={ksize}, Cin_s={cin_s}")
+    cout_s = w.shape[0] // (ksize * ksize)
+    pad = ksize // 2
+    ho, wo = (hi + 2 * pad - ksize) // stride + 1, (wi + 2 * pad - ksize) // stride + 1
+    if res is not None and (res.dtype != torch.float16 or tuple(res.shape) != (n, ho, wo, cout_s) or not res.is_contiguous()):
+        raise _lib.Opb200Error("conv2d_nhwc_f16: residual must be contiguous fp16 [N,Ho,Wo,Cout_s]")
+    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout_s):
+        raise _lib.Opb200Error("conv2d_nhwc_f16: bias must be fp32 [Cout_s]")
+    y16 = torch.empty(n, ho, wo, cout_s, dtype=torch.float16, device=x.device) if out_f16 else None
+    y32 = torch.empty(n, ho, wo, cout_s, dtype=torch.float32, device=x.device) if out_f32 else None
+    with _Stage(stage):
+        st = _lib.lib().opb200_conv2d_nhwc_f16(_lib.ptr(x), n, hi, wi, cin_s, _lib.ptr(w), ksize, stride, cout_s, _lib.ptr(bias),
+                                               _lib.ptr(res), _lib.ptr(y16), _lib.ptr(y32), act, ctypes.c_float(slope),
+                                               _lib.stream_ptr())
+    _lib.check(st, "opb200_conv2d_nhwc_f16")
+    if out_f16 and out_f32:
+        return y16, y32
+    return y16 if out_f16 else y32
+
+
+def stem_conv_relu_f16(image: torch.Tensor, weight_tap_major: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
+    """image [N,1,H,W] fp32 -> relu(conv7x7/2(image) + bias) as [N,Ho,Wo,Cout] fp16."""
+    _need_cuda(image, weight_tap_major, bias)
+    n, cin, h, w = image.shape
+    if cin != 1:
+        raise _lib.Opb200Error("stem_conv_relu_f16: single-channel images only")
+    image = _f32(image).contiguous()
+    cout = weight_tap_major.shape[1]
+    ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    out = torch.empty(n, ho, wo, cout, dtype=torch.float16, device=image.device)
+    with _Stage("backbone_glue"):
+        st = _lib.lib().opb200_stem_conv7x7_s2_relu_nhwc_f16(_lib.ptr(image), _lib.ptr(weight_tap_major), _lib.ptr(bias), n, h, w,
+                                                             cout, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "opb200_stem_conv7x7_s2_relu_nhwc_f16")
+    return out
+
+
+def upsample2x_add_f16_(dst: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    """dst [N,2H,2W,C] fp16 += bilinear x2 (align_corners=True) of src [N,H,W,C] fp16; in place."""
+    _need_cuda(dst, src)
+    n, hs, ws, c = src.shape
+    if tuple(dst.shape) != (n, 2 * hs, 2 * ws, c) or dst.dtype != torch.float16 or src.dtype != torch.float16 \
+            or not dst.is_contiguous() or not src.is_contiguous():
+        raise _lib.Opb200Error(f"upsample2x_add_f16_: contiguous fp16 NHWC {tuple(src.shape)} -> {tuple(dst.shape)} required")
+    with _Stage("backbone_glue"):
+        st = _lib.lib().opb200_upsample2x_add_nhwc_f16(_lib.ptr(src), n, hs, ws, c, _lib.ptr(dst), _lib.stream_ptr())
+    _lib.check(st, "opb200_upsample2x_add_nhwc_f16")
+    return dst

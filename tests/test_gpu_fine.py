@@ -120,3 +120,38 @@ def test_backbone_fused_vs_plain_module(golden):
     ef = (ff.cpu()[:, ::8, ::4, ::4] - gf).abs().max().item() / gf.abs().max().item()
     print(f"backbone rel err coarse {ec:.2e} fine {ef:.2e}")
     assert ec < 1e-4 and ef < 1e-4
+
+
+def test_backbone_f16_tensor_core_path_is_tf32_grade(golden):
+    """The tcgen05 fp16 backbone (what runs when torch.backends.cudnn.allow_tf32 is True, torch's default) against the
+    reference's golden fp32 maps: its error must be of the size of the error the reference's own cuDNN TF32
+    convolutions make on the same input (both have 11-bit operand significands)."""
+    import cases
+    from onepose_st_b200.nn_common import ResNetFPN_8_2, FusedBackbone, FusedBackboneF16
+    c = cases.case_backbone()
+    m = ResNetFPN_8_2({"block_type": "BasicBlock", "initial_dim": 128, "block_dims": [128, 196, 256]})
+    m.load_state_dict({k[len("backbone."):]: v for k, v in c["sd"].items()}, strict=True)
+    m = m.cuda().eval()
+    assert FusedBackboneF16.supports(m)
+    g = golden("backbone")
+    gc, gf = g["feat_c"], g["feat_f_sub"]
+
+    def errs(fc, ff):
+        return ((fc.cpu() - gc).abs().max().item() / gc.abs().max().item(),
+                (ff.cpu()[:, ::8, ::4, ::4] - gf).abs().max().item() / gf.abs().max().item())
+    old = torch.backends.cudnn.allow_tf32
+    try:
+        torch.backends.cudnn.allow_tf32 = True
+        with torch.no_grad():
+            ex = m.fused()
+            assert isinstance(ex, FusedBackboneF16)
+            e16 = errs(*m(c["image"].cuda()))
+            etf = errs(*FusedBackbone(m)(c["image"].cuda()))       # cuDNN executor with TF32 convolutions
+        torch.backends.cudnn.allow_tf32 = False
+        with torch.no_grad():
+            assert isinstance(m.fused(), FusedBackbone)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    print(f"backbone rel err vs fp32 golden: fp16 tcgen05 coarse {e16[0]:.2e} fine {e16[1]:.2e}; cuDNN TF32 coarse {etf[0]:.2e} fine {etf[1]:.2e}")
+    assert e16[0] < 5e-3 and e16[1] < 5e-3
+    assert e16[0] < 3 * etf[0] + 1e-4 and e16[1] < 3 * etf[1] + 1e-4

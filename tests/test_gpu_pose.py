@@ -95,3 +95,39 @@ def test_pnp_pose_parity_with_oracle():
     print(f"pose ours vs oracle: {d_deg:.4f} deg, {d_cm:.4f} cm (inliers {ng} vs {no}); ours vs ground truth: {g_deg:.3f} deg, {g_cm:.3f} cm")
     assert d_deg < 1.0 and d_cm < 1.0   # north_star: 1 cm / 1 degree
     assert g_deg < 1.0 and g_cm < 1.0
+
+
+def test_pnp_pose_parity_tf32_grade_backbone():
+    """Same scene with torch's default allow_tf32=True, i.e. the fp16-operand tcgen05 backbone (the configuration
+    bench.py times): the pose must still agree with the fp32 oracle within north_star's 1 cm / 1 degree, and the
+    match set must be essentially the oracle's."""
+    pytest.importorskip("cv2")
+    from onepose_st_b200.onepose_plus import OnePosePlus_model
+    from onepose_st_b200.nn_common import FusedBackboneF16
+    cfg, sd, data, Kmat, Rgt, tgt = _scene()
+    ref = {k: v.clone() for k, v in data.items()}
+    with torch.no_grad():
+        R.onepose_plus_forward(sd, cfg, ref)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = True
+    try:
+        model = OnePosePlus_model(copy.deepcopy(cfg))
+        model.load_state_dict(sd, strict=True)
+        model = model.cuda().eval()
+        ours = {k: v.cuda() for k, v in data.items()}
+        model(ours)
+        assert isinstance(model.backbone.fused(), FusedBackboneF16)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    ref_pairs = set(zip(ref["i_ids"].tolist(), ref["j_ids"].tolist()))
+    our_pairs = set(zip(ours["i_ids"].cpu().tolist(), ours["j_ids"].cpu().tolist()))
+    common = len(ref_pairs & our_pairs)
+    print(f"matches: ours {len(our_pairs)}, oracle {len(ref_pairs)}, common {common}")
+    assert common >= 0.9 * len(ref_pairs) and len(our_pairs) <= 1.1 * len(ref_pairs)
+    Ro, to, no = _pnp(ref["mkpts_3d_db"].numpy(), ref["mkpts_query_f"].numpy(), Kmat)
+    Rg, tg, ng = _pnp(ours["mkpts_3d_db"].cpu().numpy(), ours["mkpts_query_f"].cpu().numpy(), Kmat)
+    d_deg, d_cm = _pose_diff(Rg, tg, Ro, to)
+    g_deg, g_cm = _pose_diff(Rg, tg, Rgt, tgt)
+    print(f"[tf32-grade backbone] pose ours vs oracle: {d_deg:.4f} deg, {d_cm:.4f} cm (inliers {ng} vs {no}); vs ground truth: {g_deg:.3f} deg, {g_cm:.3f} cm")
+    assert d_deg < 1.0 and d_cm < 1.0
+    assert g_deg < 1.0 and g_cm < 1.0

@@ -162,9 +162,52 @@ def run_loftr(a):
                               "matches_per_pair": out["m"] / nb, "ms_per_forward": med, "pairs_per_s": nb / med * 1e3}), flush=True)
 
 
+def run_conv(a):
+    """Every convolution shape of ResNetFPN_8_2 at 512x512 (BASELINE configs 1-4), N images per launch: own tcgen05
+    fp16 implicit GEMM vs cuDNN TF32 channels-last (what the reference runs on a GPU)."""
+    import torch.nn.functional as F
+    from onepose_st_b200.nn_common import pack_conv_f16, _cs
+    hbm, tf, src = peaks()
+    n = a.pair_batch[-1] if a.pair_batch != [1, 4] else 8
+    h2, h4, h8 = a.size // 2, a.size // 4, a.size // 8
+    shapes = [("layer1 3x3 128->128", h2, 128, 128, 3, 1, 4), ("layer2.0 3x3/2 128->196", h2, 128, 196, 3, 2, 1),
+              ("layer2 3x3 196->196", h4, 196, 196, 3, 1, 3), ("layer3.0 3x3/2 196->256", h4, 196, 256, 3, 2, 1),
+              ("layer3 3x3 256->256", h8, 256, 256, 3, 1, 3), ("head2 3x3 256->256", h4, 256, 256, 3, 1, 1),
+              ("head2 3x3 256->196", h4, 256, 196, 3, 1, 1), ("head1 3x3 196->196", h2, 196, 196, 3, 1, 1),
+              ("head1 3x3 196->128", h2, 196, 128, 3, 1, 1), ("lateral1 1x1 128->196", h2, 128, 196, 1, 1, 1),
+              ("lateral2 1x1 196->256", h4, 196, 256, 1, 1, 1), ("lateral3 1x1 256->256", h8, 256, 256, 1, 1, 1)]
+    tot_own = tot_cudnn = tot_flop = 0.0
+    for name, hw, cin, cout, k, stride, count in shapes:
+        x16 = torch.zeros(n, hw, hw, _cs(cin), dtype=torch.float16, device="cuda")
+        x16[..., :cin] = torch.randn(n, hw, hw, cin, device="cuda").half()
+        w = torch.randn(cout, cin, k, k, device="cuda") / (cin * k * k) ** 0.5
+        b = torch.randn(cout, device="cuda")
+        wp, bp = pack_conv_f16(w, b)
+        ops.stage_events = {}
+        time_op(lambda: ops.conv2d_nhwc_f16(x16, wp, k, stride, bp, None, 1), a.iters, warmup=0 if a.iters == 1 else 3)
+        evs = ops.stage_events["backbone_conv"][-a.iters:]
+        ops.stage_events = None
+        own_ms = sorted(x.elapsed_time(y) for x, y in evs)[len(evs) // 2]
+        xc = x16[..., :cin].float().permute(0, 3, 1, 2).contiguous(memory_format=torch.channels_last)
+        wc = w.contiguous(memory_format=torch.channels_last)
+        cu_ms, _ = time_op(lambda: torch.cudnn_convolution_relu(xc, wc, b, (stride, stride), (k // 2, k // 2), (1, 1), 1)
+                           if k == 3 else F.conv2d(xc, wc, b, stride), a.iters, warmup=0 if a.iters == 1 else 3)
+        ho = (hw + 2 * (k // 2) - k) // stride + 1
+        flop = 2.0 * n * ho * ho * cin * cout * k * k
+        tot_own += own_ms * count
+        tot_cudnn += cu_ms * count
+        tot_flop += flop * count
+        print(json.dumps({"op": "conv " + name, "images": n, "out_hw": ho, "ms_own_fp16_tcgen05": own_ms,
+                          "tflops_own": flop / own_ms / 1e9, "frac_tensor": flop / own_ms / 1e9 / tf,
+                          "ms_cudnn_tf32": cu_ms, "tflops_cudnn": flop / cu_ms / 1e9, "per_backbone": count}), flush=True)
+    print(json.dumps({"op": "backbone convolutions total", "images": n, "ms_own": tot_own, "ms_cudnn_tf32": tot_cudnn,
+                      "algorithmic_gflop": tot_flop / 1e9, "tflops_own": tot_flop / tot_own / 1e9,
+                      "frac_tensor": tot_flop / tot_own / 1e9 / tf, "peak": f"{tf} TFLOP/s bf16/fp16 burst ({src})"}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["coarse", "transformer", "fine", "loftr"])
+    ap.add_argument("what", choices=["coarse", "transformer", "fine", "loftr", "conv"])
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--pair-batch", type=int, nargs="+", default=[1, 4])
     ap.add_argument("--points", type=int, nargs="+", default=[5000, 8000, 30000])
@@ -174,7 +217,7 @@ def main():
     ap.add_argument("--precision", type=int, default=3)
     ap.add_argument("--materialize", action="store_true")
     a = ap.parse_args()
-    {"coarse": run_coarse, "transformer": run_transformer, "fine": run_fine, "loftr": run_loftr}[a.what](a)
+    {"coarse": run_coarse, "transformer": run_transformer, "fine": run_fine, "loftr": run_loftr, "conv": run_conv}[a.what](a)
 
 
 if __name__ == "__main__":
