@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--precision", type=int, default=3, choices=[1, 3], help="3 = bf16x3 split (fp32-grade), 1 = bf16")
     ap.add_argument("--cpu-sample-frames", type=int, default=4, help="frames timed for cpu_baseline (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--streams", type=int, default=3, help="host threads x CUDA streams per GPU that pull frame batches")
     return ap.parse_args()
 
 
@@ -58,7 +59,7 @@ def load_peaks():
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons of one GPU every 100 ms through NVML while the timed region runs."""
+    """Samples SM clock and throttle reasons of one GPU every 20 ms through NVML while the timed region runs."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
@@ -94,7 +95,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(n)
             except Exception:
                 pass
-            self._stop_ev.wait(0.1)
+            self._stop_ev.wait(0.02)
 
     def stop(self):
         self._stop_ev.set()
@@ -112,6 +113,8 @@ def config_dict(args, n_gpus):
             "frames_per_step_per_gpu": args.frames_per_step, "frames_per_forward": args.batch,
             "planted_matches": args.plant, "precision": "bf16x3-split (fp32-grade)" if args.precision == 3 else "bf16",
             "sharding": f"frames round-robin over {n_gpus} GPU(s); one NCCL gather of matches at the end",
+            "host_pipeline": f"{args.streams} host threads x CUDA streams per GPU pull frame batches from one queue "
+                             "(onepose_st_b200.pipeline.StreamPipeline)",
             "l2": "256 MiB buffer written between steps (inside the timed region)"}
 
 
@@ -170,7 +173,8 @@ def run_reference(args):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from onepose_st_b200 import _lib, ops, sharding, synthetic
+    import threading
+    from onepose_st_b200 import _lib, ops, pipeline, sharding, synthetic
     from onepose_st_b200.onepose_plus import OnePosePlus_model
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -197,11 +201,11 @@ def run_ours(args):
     frames_host = frames_dev.cpu().pin_memory()
     B, F = args.batch, args.frames_per_step
     assert F % B == 0, "--frames-per-step must be a multiple of --batch"
-    kp = seq["keypoints3d"].expand(B, -1, -1).contiguous()
-    d_f = seq["descriptors3d_db"].expand(B, -1, -1).contiguous()
-    d_c = seq["descriptors3d_coarse_db"].expand(B, -1, -1).contiguous()
+    kp = seq["keypoints3d"].expand(B, -1, -1)  # one 3D model for every frame of the batch: broadcast views
+    d_f = seq["descriptors3d_db"].expand(B, -1, -1)
+    d_c = seq["descriptors3d_coarse_db"].expand(B, -1, -1)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    stage = torch.empty(B, 1, args.size, args.size, device=dev)
+    tl = threading.local()  # per host thread: device staging buffer of the end-to-end arm
     ragged = sharding.RaggedRows(6, dev, capacity_rows=1 << 18)
     n_units_total = world * F * (args.steps + args.warmup)
 
@@ -214,37 +218,51 @@ def run_ours(args):
         model(data)
         return data
 
-    def run_steps(first, count, e2e):
+    def one_forward(job):
+        """One forward of B frames on the calling thread's current stream; returns (rows [M,6], per-frame counts, D2H bytes)."""
+        s, b0, e2e = job
+        if b0 == 0:
+            flush.fill_(s & 0xFF)  # L2 flush between steps
+        idx = unit_frames(s, b0)
+        nbytes = 0
+        if e2e:
+            stage = getattr(tl, "stage", None)
+            if stage is None:
+                stage = tl.stage = torch.empty(B, 1, args.size, args.size, device=dev)
+            for i, f in enumerate(idx):
+                stage[i].copy_(frames_host[f], non_blocking=True)
+            data = forward(stage)
+            rows = sharding.rows_onepose(data)
+            host_rows = rows.cpu()  # D2H of the step's result (synchronises this stream)
+            nbytes = host_rows.numel() * 4
+        else:
+            data = forward(frames_dev[idx] if B > 1 else frames_dev[idx[0]][None])
+            rows = sharding.rows_onepose(data)
+        counts = torch.bincount(data["b_ids"], minlength=B).tolist() if B > 1 else [rows.shape[0]]
+        return rows, counts, nbytes
+
+    def run_steps(first, count, e2e, pipe):
+        jobs = [(s, b0, e2e) for s in range(first, first + count) for b0 in range(0, F, B)]
         d2h = 0
-        for s in range(first, first + count):
-            flush.fill_(s & 0xFF)
-            for b0 in range(0, F, B):
-                idx = unit_frames(s, b0)
-                if e2e:
-                    for i, f in enumerate(idx):
-                        stage[i].copy_(frames_host[f], non_blocking=True)
-                    data = forward(stage)
-                    rows = sharding.rows_onepose(data)
-                    host_rows = rows.cpu()  # D2H of the step's result (synchronises)
-                    d2h += host_rows.numel() * 4
-                    counts = torch.bincount(data["b_ids"], minlength=B).tolist() if B > 1 else [rows.shape[0]]
-                else:
-                    data = forward(frames_dev[idx] if B > 1 else frames_dev[idx[0]][None])
-                    rows = sharding.rows_onepose(data)
-                    counts = torch.bincount(data["b_ids"], minlength=B).tolist() if B > 1 else [rows.shape[0]]
-                off = 0
-                for c in counts:
-                    ragged.append(rows[off: off + c])
-                    off += c
+        for rows, counts, nbytes in pipe.map(one_forward, jobs):
+            rows.record_stream(torch.cuda.current_stream())
+            off = 0
+            for c in counts:
+                ragged.append(rows[off: off + c])
+                off += c
+            d2h += nbytes
         return d2h
 
-    def timed(e2e):
+    def timed(e2e, n_streams, stage_events=False):
+        pipe = pipeline.StreamPipeline(n_streams, dev)
         ragged.reset()
-        run_steps(0, args.warmup, e2e)
+        one_forward((0, 0, e2e))  # builds the per-model caches (packed weights, encoded 3D model) on one stream
+        torch.cuda.synchronize()
+        run_steps(0, args.warmup, e2e, pipe)
         # the gather is warmed up too (first NCCL all_gather sets up channels; first sort/scatter compiles nothing but allocates)
         sharding.gather_matches(ragged.rows(), ragged.counts, world * F * args.warmup)
         ragged.reset()
-        ops.stage_events = {} if not e2e else None
+        ops.stage_events = {} if stage_events else None
         sampler = ClockSampler(local_rank)
         if world > 1:
             dist.barrier()
@@ -253,7 +271,7 @@ def run_ours(args):
         l0 = _lib.launch_count()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
-        d2h = run_steps(args.warmup, args.steps, e2e)
+        d2h = run_steps(args.warmup, args.steps, e2e, pipe)
         n_units = world * F * args.steps
         rows_all, counts_all = sharding.gather_matches(ragged.rows(), ragged.counts, n_units)
         ev1.record()
@@ -269,14 +287,17 @@ def run_ours(args):
         return {"ms": float(ms.item()), "launches": launches, "clocks": clocks, "events": events, "d2h": d2h,
                 "matches": int(rows_all.shape[0]), "units": n_units}
 
-    res = timed(e2e=False)
-    res_e2e = None if args.no_e2e else timed(e2e=True)
+    res = timed(e2e=False, n_streams=args.streams)
+    res_e2e = None if args.no_e2e else timed(e2e=True, n_streams=args.streams)
+    # per-op device time: the same K steps once more on ONE stream, so that the CUDA-event bracket around each C-ABI
+    # call (recorded on the launching stream, inside this timed region) holds that call's kernels only -- with two
+    # streams in flight a bracket would also span the other stream's kernels.
+    res_ops = timed(e2e=False, n_streams=1, stage_events=True)
 
-    # per-op device time (CUDA events on the launching stream, inside the timed region)
     frames_rank = F * args.steps
     L, S, C = args.points, (args.size // 8) ** 2, 256
     stages = {}
-    for name, evs in (res["events"] or {}).items():
+    for name, evs in (res_ops["events"] or {}).items():
         tot = sum(a.elapsed_time(b) for a, b in evs)
         stages[name] = {"calls": len(evs), "ms_per_frame": tot / frames_rank}
     m_per_frame = res["matches"] / max(1, res["units"])
@@ -338,6 +359,9 @@ def run_ours(args):
                   if torch.backends.cudnn.allow_tf32 else "fp32 cuDNN backbone, ") + "f32 accumulate/IO",
                "data": "synthetic", "config": config_dict(args, world),
                "matches_per_frame": m_per_frame, "gpu_launches": res["launches"], "clocks": res["clocks"],
+               "streams": args.streams,
+               "single_stream": {"value": total_frames / (res_ops["ms"] * 1e-3), "unit": UNIT,
+                                 "note": "same steps on one CUDA stream; stages_ms_per_frame and the rooflines are timed in this pass"},
                "stages_ms_per_frame": {k: round(v["ms_per_frame"], 4) for k, v in stages.items()},
                "roofline": rooflines.get("coarse_match"),
                "roofline_other": {k: v for k, v in rooflines.items() if k != "coarse_match"}}

@@ -44,6 +44,11 @@ int opb200_split_planes(const float* x, int64_t stride_r, int64_t stride_c, int 
 int opb200_debug_gemm(const void* a_hi, const void* a_lo, const void* b_hi, const void* b_lo, int M, int N, int K,
                       int block_n, int precision, float* c, void* stream);
 
+/* Debug: arm (buffer != NULL, zero-filled device memory) or disarm per-tile timestamp tracing of the tcgen05 GEMM
+ * launches; launch i writes [148][32][4] int64 SM-clock stamps {first TMA, MMA start, accumulator full, epilogue
+ * done} at slot i.  Returns the number of slots the buffer holds.  Used by tools/gemm_trace.py only. */
+int opb200_debug_trace(void* buffer, long long bytes);
+
 /* ---- LoFTR encoder stack (elu+1 linear attention) --------------------------------------------------
  * Replaces LoFTREncoderLayer.forward + LinearAttention.forward + LocalFeatureTransformer.forward:
  *   src/models/OnePosePlus/loftr_module/transformer.py:65-94,133-171
@@ -58,7 +63,10 @@ int opb200_pack_layer_weights(const float* wq, const float* wk, const float* wv,
                               const float* ln2_b, int d_model, void* packed, void* stream);
 size_t opb200_transformer_workspace_bytes(int d_model, int n_batch, int len0, int len1, int big_groups);
 /* Runs n_layers encoder layers over two token streams.
- *   host_layer_weights[l] : device pointer to layer l's packed weights;  host_layer_kinds[l]: 0 self, 1 cross
+ *   host_layer_weights[l] : device pointer to layer l's packed weights;  host_layer_kinds[l]: 0 self, 1 cross,
+ *            2 = self layer applied to stream 1 only, 3 = to stream 0 only (the other stream's rows are untouched:
+ *            how a caller reuses a stream whose first self layer it has already computed, e.g. the fixed 3D model
+ *            of a OnePose++ sequence)
  *   schedule 0 = OnePosePlus (one layer object serves both streams, both read the pre-update tensors),
  *            1 = LoFTR (cross step: stream0 = layer(stream0, stream1) then stream1 = layer(stream1, new stream0))
  *   big_groups 1 = coarse level (d_model 256; one attention group per (stream, batch element)),

@@ -15,6 +15,22 @@ static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
 
+// ---- debug tracing of GEMM launches: launch i writes its per-CTA tile timestamps at base + i * slot
+static long long* g_trace_base = nullptr;
+static long long g_trace_slots = 0;
+static std::atomic<long long> g_trace_next{0};
+long long* next_trace_slot(int grid) {
+  if (g_trace_base == nullptr) return nullptr;
+  const long long i = g_trace_next.fetch_add(1, std::memory_order_relaxed);
+  if (i >= g_trace_slots || grid > 148) return nullptr;
+  return g_trace_base + i * (148LL * kTraceTilesPerCta * 4);
+}
+void arm_trace(long long* base, long long slots) {
+  g_trace_base = base;
+  g_trace_slots = slots;
+  g_trace_next.store(0, std::memory_order_relaxed);
+}
+
 int check_device() {
   int dev = 0;
   OPB_CHECK_CUDA(cudaGetDevice(&dev));
@@ -61,13 +77,15 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 int encode_tmap_16bit(CUtensorMap* out, bool fp16, int rank, const void* base, const uint64_t* gdim,
-                      const uint64_t* gstride_bytes, const uint32_t* box, const uint32_t* elem_strides) {
+                      const uint64_t* gstride_bytes, const uint32_t* box, const uint32_t* elem_strides, int swizzle_bytes) {
   EncodeTiledFn fn = get_encode_fn();
   if (fn == nullptr) {
     set_last_error("cuTensorMapEncodeTiled entry point not available from the driver");
     return OPB_ERR_CUDA;
   }
   OPB_CHECK_ARG(rank >= 2 && rank <= 5, "TMA rank must be 2..5");
+  OPB_CHECK_ARG((swizzle_bytes == 128 || swizzle_bytes == 64) && box[0] * 2 == static_cast<uint32_t>(swizzle_bytes),
+                "innermost box extent must span exactly one swizzle row");
   OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base address must be 16-byte aligned");
   cuuint64_t gd[5], gs[4];
   cuuint32_t bx[5], es[5];
@@ -82,7 +100,8 @@ int encode_tmap_16bit(CUtensorMap* out, bool fp16, int rank, const void* base, c
     }
   }
   CUresult r = fn(out, fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank,
-                  const_cast<void*>(base), gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  const_cast<void*>(base), gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_last_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(r)));
@@ -260,6 +279,14 @@ int opb200_split_planes(const float* x, int64_t stride_r, int64_t stride_c, int 
   OPB_CHECK_ARG(x != nullptr && hi != nullptr, "x / hi must not be null");
   return split_planes(x, stride_r, stride_c, nullptr, 0, rows, cols, static_cast<__nv_bfloat16*>(hi),
                       static_cast<__nv_bfloat16*>(lo), f32_copy, cols, static_cast<cudaStream_t>(stream));
+}
+
+int opb200_debug_trace(void* buffer, long long bytes) {
+  // buffer: device memory, zero-filled by the caller; launch i of gemm_kernel (in host launch order) records
+  // [148 CTAs][32 tiles][4] int64 clock64() stamps at slot i.  buffer == NULL disarms.  Returns the slot count.
+  const long long slot = 148LL * kTraceTilesPerCta * 4 * static_cast<long long>(sizeof(long long));
+  arm_trace(static_cast<long long*>(buffer), buffer ? bytes / slot : 0);
+  return static_cast<int>(buffer ? bytes / slot : 0);
 }
 
 int opb200_debug_gemm(const void* a_hi, const void* a_lo, const void* b_hi, const void* b_lo, int M, int N, int K,

@@ -648,10 +648,10 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
 
   auto add_segs = [&](PlanBuilder& pb, int a_hi, int a_lo, int b_hi, int b_lo, int a_k0, int b_k0, int nkb) {
     if (x3) {
-      pb.seg(a_hi, b_lo, a_k0, b_k0, nkb);
-      pb.seg(a_lo, b_hi, a_k0, b_k0, nkb);
+      pb.seg3(a_hi, a_lo, b_hi, b_lo, a_k0, b_k0, 2 * nkb);  // fused split-precision mainloop: 32-wide k-blocks
+    } else {
+      pb.seg(a_hi, b_hi, a_k0, b_k0, nkb);
     }
-    pb.seg(a_hi, b_hi, a_k0, b_k0, nkb);
   };
 
   // ---- 1. QKV
@@ -659,7 +659,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     typename EpiQKV<C>::Params ep{w.qh, x3 ? w.ql : nullptr, g.big ? nullptr : w.qf, w.kf, w.vf, w.row_mask};
     auto launch = [&](int mb, int mc, int nb, int nc) -> int {
       if (mc <= 0) return OPB_OK;
-      PlanBuilder pb;
+      PlanBuilder pb(x3);
       pb.add_a(w.xh, R, C, C, 0);
       pb.add_b(lw.qkv_hi, 3 * C, C, C, 0, C);
       if (x3) {
@@ -674,7 +674,8 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       pb.plan.num_n_tiles = nc;
       pb.plan.num_tiles = mc * nc;
       pb.plan.b_rows_per_ntile = C;
-      return launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiQKV<C>, EPI_SPLIT>(pb.plan, ep, stream);
+      return x3 ? launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiQKV<C>, EPI_SPLIT, true>(pb.plan, ep, stream)
+                : launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiQKV<C>, EPI_SPLIT>(pb.plan, ep, stream);
     };
     if (q_streams == src_streams) {
       if (int r = launch(qb, qc, 0, 3)) return r;
@@ -707,7 +708,11 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
         pb.add_b(w.kvb_l, static_cast<uint64_t>(g.G) * 2 * 144, 128, 128, 1, 144);
       }
       if (pb.status) return pb.status;
-      add_segs(pb, 0, 1, 0, 1, 0, 0, 2);
+      if (x3) {  // K = 128 per n tile: the three products as three K segments (small; not worth the fused mainloop)
+        pb.seg(0, 1, 0, 0, 2);
+        pb.seg(1, 0, 0, 0, 2);
+      }
+      pb.seg(0, 0, 0, 0, 2);
       pb.finish();
       pb.plan.a_k_per_ntile = 128;
       pb.plan.m_tile_begin = qb;
@@ -742,7 +747,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
   const int ub = qb, uc = qc;  // only the tiles of the streams being updated run the row-wise GEMMs
   // ---- 5. MERGE + LN1
   {
-    PlanBuilder pb;
+    PlanBuilder pb(x3);
     pb.add_a(w.aoh, R, C, C, 0);
     pb.add_b(lw.m_hi, C, C, C, 0, C);
     if (x3) {
@@ -757,11 +762,13 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_tiles = uc;
     pb.plan.b_rows_per_ntile = C;
     typename EpiLN<C>::Params ep{lw.ln1_g, lw.ln1_b, w.mh, x3 ? w.ml : nullptr};
-    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLN<C>, EPI_SPLIT>(pb.plan, ep, stream)) return r;
+    if (int r = x3 ? launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLN<C>, EPI_SPLIT, true>(pb.plan, ep, stream)
+                   : launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLN<C>, EPI_SPLIT>(pb.plan, ep, stream))
+      return r;
   }
   // ---- 6. MLP1 + ReLU   (K = [x | msg], N = 2C as two tiles of C)
   {
-    PlanBuilder pb;
+    PlanBuilder pb(x3);
     pb.add_a(w.xh, R, C, C, 0);
     pb.add_a(w.mh, R, C, C, 2);
     pb.add_b(lw.w1_hi, 2 * C, 2 * C, 2 * C, 0, C);
@@ -779,11 +786,13 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_tiles = uc * 2;
     pb.plan.b_rows_per_ntile = C;
     typename EpiRelu<C>::Params ep{w.hh, x3 ? w.hl : nullptr, 2 * C};
-    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiRelu<C>, EPI_SPLIT>(pb.plan, ep, stream)) return r;
+    if (int r = x3 ? launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiRelu<C>, EPI_SPLIT, true>(pb.plan, ep, stream)
+                   : launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiRelu<C>, EPI_SPLIT>(pb.plan, ep, stream))
+      return r;
   }
   // ---- 7. MLP2 + LN2 + residual (in place on the master copy and its planes)
   {
-    PlanBuilder pb;
+    PlanBuilder pb(x3);
     pb.add_a(w.hh, R, 2 * C, 2 * C, 0);
     pb.add_b(lw.w2_hi, C, 2 * C, 2 * C, 0, C);
     if (x3) {
@@ -798,7 +807,9 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     pb.plan.num_tiles = uc;
     pb.plan.b_rows_per_ntile = C;
     typename EpiLNRes<C>::Params ep{lw.ln2_g, lw.ln2_b, w.xh, w.xl};
-    if (int r = launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLNRes<C>, EPI_SPLIT>(pb.plan, ep, stream)) return r;
+    if (int r = x3 ? launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLNRes<C>, EPI_SPLIT, true>(pb.plan, ep, stream)
+                   : launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLNRes<C>, EPI_SPLIT>(pb.plan, ep, stream))
+      return r;
   }
   return OPB_OK;
 }
@@ -895,10 +906,14 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
 
   for (int l = 0; l < n_layers; ++l) {
     LayerWeights lw = view_layer(host_layer_weights[l], C);
-    const bool cross = host_layer_kinds[l] == 1;
-    OPB_CHECK_ARG(host_layer_kinds[l] == 0 || host_layer_kinds[l] == 1, "layer kind must be 0 (self) or 1 (cross)");
+    const int kind = host_layer_kinds[l];
+    const bool cross = kind == 1;
+    OPB_CHECK_ARG(kind >= 0 && kind <= 3, "layer kind must be 0 (self), 1 (cross), 2 (self, stream 1 only) or 3 (self, stream 0 only)");
     int r;
-    if (cross && schedule == 1) {
+    if (kind >= 2) {  // self layer applied to one stream; the other stream's rows are left as they are
+      const int qs = kind == 2 ? 2 : 1;
+      r = (C == 256) ? run_step<256>(g, w, lw, false, qs, precision, stream) : run_step<128>(g, w, lw, false, qs, precision, stream);
+    } else if (cross && schedule == 1) {
       // LoFTR: feat0 = layer(feat0, feat1); then feat1 = layer(feat1, feat0_new)
       r = (C == 256) ? run_step<256>(g, w, lw, true, 1, precision, stream) : run_step<128>(g, w, lw, true, 1, precision, stream);
       if (r) return r;

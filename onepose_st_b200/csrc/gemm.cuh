@@ -25,9 +25,10 @@ constexpr int kNumMaps = 4;
 constexpr int kMaxSegs = 8;
 
 struct KSeg {
-  int a_map, b_map;  // indices into GemmPlan::a_maps / b_maps
-  int a_k0, b_k0;    // starting K coordinate (elements) in each
-  int nkb;           // number of 64-wide k-blocks
+  int a_map, b_map;    // indices into GemmPlan::a_maps / b_maps (fused split mode: the hi planes)
+  int a_map2, b_map2;  // fused split mode only: the lo planes
+  int a_k0, b_k0;      // starting K coordinate (elements) in each
+  int nkb;             // number of k-blocks (64 wide; 32 wide in fused split mode)
 };
 
 struct GemmPlan {
@@ -43,7 +44,10 @@ struct GemmPlan {
   int a_k_per_ntile;      // extra A K-offset per n tile (block-diagonal B: each n tile reads its own K slice)
   const int* b_row_base;  // optional per-m-tile base row into B (per-group / per-batch B operand)
   int b_rows_per_ntile;   // row distance between consecutive n tiles of B
+  long long* trace;       // debug (opb200_debug_trace): per CTA and tile {first TMA issued, MMA start, accumulator full,
+                          // epilogue done} in SM clock cycles; null in normal use
 };
+constexpr int kTraceTilesPerCta = 32;
 
 // GROUPS = number of epilogue warpgroups (4 warps each).  With one group the accumulator is double-buffered
 // (when it fits) so the next tile's MMAs overlap the epilogue; with G > 1 groups there are G accumulator
@@ -83,7 +87,13 @@ struct EpiCtx {
 
 // SPLIT = warps per TMEM lane quarter inside one group: the tile's columns are divided among them, so a
 // single tile's epilogue runs on 4*SPLIT warps (what matters when a CTA has only one or two tiles).
-template <int BN, int STAGES, int GROUPS, int SPLIT, class Epi>
+//
+// F3 = fused split-precision mainloop.  The segment form of A_hi*B_lo + A_lo*B_hi + A_hi*B_hi walks K three times
+// and so fills shared memory with six operand tiles per k-block for three MMA groups; these GEMMs are bound by the
+// L2 -> SM fill rate, not by the tensor pipe.  With F3 one stage holds the four distinct tiles of a 32-wide k-block
+// {A_hi, A_lo, B_hi, B_lo} (64-byte swizzle; same stage size as one 64-wide {A, B} pair) and the MMA warp issues
+// the three products from it: 2/3 of the shared-memory fill per flop.
+template <int BN, int STAGES, int GROUPS, int SPLIT, class Epi, bool F3 = false>
 __global__ void __launch_bounds__(64 + 128 * GROUPS * SPLIT, 1)
 gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep) {
   using Cfg = GemmCfg<BN, GROUPS>;
@@ -142,16 +152,28 @@ gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep
         tile_coords(t, m_tile, n_tile);
         const int a_row = m_tile * BLOCK_M;
         const int b_row = (plan.b_row_base ? plan.b_row_base[m_tile] : 0) + n_tile * plan.b_rows_per_ntile;
+        if (plan.trace != nullptr) {
+          const int it = (t - blockIdx.x) / gridDim.x;
+          if (it < kTraceTilesPerCta) plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 0] = clock64();
+        }
         for (int s = 0; s < plan.nsegs; ++s) {
           const KSeg seg = plan.segs[s];
           for (int kb = 0; kb < seg.nkb; ++kb) {
             ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
             ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
             uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
-            ptx::tma_load_2d(sa, &plan.a_maps[seg.a_map], &full_bar[stage],
-                             seg.a_k0 + n_tile * plan.a_k_per_ntile + kb * BLOCK_K, a_row);
-            ptx::tma_load_2d(sa + Cfg::A_BYTES, &plan.b_maps[seg.b_map], &full_bar[stage], seg.b_k0 + kb * BLOCK_K,
-                             b_row);
+            if constexpr (F3) {
+              const int ka = seg.a_k0 + n_tile * plan.a_k_per_ntile + kb * 32, kbb = seg.b_k0 + kb * 32;
+              ptx::tma_load_2d(sa, &plan.a_maps[seg.a_map], &full_bar[stage], ka, a_row);
+              ptx::tma_load_2d(sa + Cfg::A_BYTES / 2, &plan.a_maps[seg.a_map2], &full_bar[stage], ka, a_row);
+              ptx::tma_load_2d(sa + Cfg::A_BYTES, &plan.b_maps[seg.b_map], &full_bar[stage], kbb, b_row);
+              ptx::tma_load_2d(sa + Cfg::A_BYTES + Cfg::B_BYTES / 2, &plan.b_maps[seg.b_map2], &full_bar[stage], kbb, b_row);
+            } else {
+              ptx::tma_load_2d(sa, &plan.a_maps[seg.a_map], &full_bar[stage],
+                               seg.a_k0 + n_tile * plan.a_k_per_ntile + kb * BLOCK_K, a_row);
+              ptx::tma_load_2d(sa + Cfg::A_BYTES, &plan.b_maps[seg.b_map], &full_bar[stage], seg.b_k0 + kb * BLOCK_K,
+                               b_row);
+            }
             if (++stage == STAGES) {
               stage = 0;
               phase ^= 1;
@@ -171,18 +193,32 @@ gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep
       const uint32_t acc_phase = (it / Cfg::ACC_STAGES) & 1;
       ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
       ptx::tc_fence_after();
+      if (plan.trace != nullptr && it < kTraceTilesPerCta && lane == 0)
+        plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 1] = clock64();
       const uint32_t d_tmem = tmem_base + acc * BN;
       for (int kb = 0; kb < plan.total_kb; ++kb) {
         ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           const uint32_t a_addr = ptx::smem_u32(smem + stage * Cfg::STAGE_BYTES);
-          const uint64_t a_desc = ptx::make_desc_sw128(a_addr);
-          const uint64_t b_desc = ptx::make_desc_sw128(a_addr + Cfg::A_BYTES);
+          if constexpr (F3) {
+            const uint64_t a_hi = ptx::make_desc_sw64(a_addr), a_lo = ptx::make_desc_sw64(a_addr + Cfg::A_BYTES / 2);
+            const uint64_t b_hi = ptx::make_desc_sw64(a_addr + Cfg::A_BYTES);
+            const uint64_t b_lo = ptx::make_desc_sw64(a_addr + Cfg::A_BYTES + Cfg::B_BYTES / 2);
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the (addr >> 4) field
-            ptx::mma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(d_tmem, a_hi + 2 * k, b_hi + 2 * k, idesc, (kb | k) != 0);
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(d_tmem, a_lo + 2 * k, b_hi + 2 * k, idesc, true);
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(d_tmem, a_hi + 2 * k, b_lo + 2 * k, idesc, true);
+          } else {
+            const uint64_t a_desc = ptx::make_desc_sw128(a_addr);
+            const uint64_t b_desc = ptx::make_desc_sw128(a_addr + Cfg::A_BYTES);
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k) {
+              // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the (addr >> 4) field
+              ptx::mma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+            }
           }
           ptx::mma_commit(&empty_bar[stage]);
           if (kb == plan.total_kb - 1) ptx::mma_commit(&tfull_bar[acc]);
@@ -212,11 +248,14 @@ gemm_kernel(const __grid_constant__ GemmPlan plan, const typename Epi::Params ep
       Epi::prefetch(ep, ctx);  // global operands of the epilogue that do not depend on the accumulator
       ptx::mbar_wait(&tfull_bar[acc], acc_phase);
       ptx::tc_fence_after();
+      const bool tr = plan.trace != nullptr && it < kTraceTilesPerCta && warp == 2 && lane == 0;
+      if (tr) plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 2] = clock64();
       ctx.tmem_acc = tmem_base + acc * BN + (static_cast<uint32_t>(ctx.quarter * 32) << 16);
       Epi::run(ep, ctx);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty_bar[acc]);
+      if (tr) plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 3] = clock64();
     }
   }
 

@@ -288,10 +288,17 @@ class OnePosePlus_model(nn.Module):
         if self.kpt_3d_pos_encoding is None:
             return desc
         kp = data["keypoints3d"]
-        key = (kp.data_ptr(), kp._version, tuple(kp.shape), desc.data_ptr(), desc._version, tuple(desc.shape),
+        key = (kp.data_ptr(), kp._version, tuple(kp.shape), tuple(kp.stride()), desc.data_ptr(), desc._version,
+               tuple(desc.shape), tuple(desc.stride()),
                tuple(p._version for p in self.kpt_3d_pos_encoding.parameters()))
         if self._kpt_cache is None or self._kpt_cache[0] != key:
-            self._kpt_cache = (key, self.kpt_3d_pos_encoding(normalize_3d_keypoints(kp), desc))
+            if kp.shape[0] > 1 and kp.stride(0) == 0 and desc.stride(0) == 0:
+                # one 3D model broadcast over the batch: encode it once, hand out a broadcast view (stride 0), which is
+                # also what lets the coarse transformer reuse its first self layer on this stream
+                enc = self.kpt_3d_pos_encoding(normalize_3d_keypoints(kp[:1]), desc[:1]).expand(kp.shape[0], -1, -1)
+            else:
+                enc = self.kpt_3d_pos_encoding(normalize_3d_keypoints(kp), desc)
+            self._kpt_cache = (key, enc)
         return self._kpt_cache[1]
 
     def __getstate__(self):

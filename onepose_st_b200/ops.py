@@ -25,14 +25,15 @@ def _f32(t: torch.Tensor) -> torch.Tensor:
 
 
 class _Workspaces:
-    """One growable byte buffer per (device, tag); reused across calls so addresses stay stable
+    """One growable byte buffer per (device, stream, tag); reused across calls so addresses stay stable
     (needed for CUDA-graph capture) and no allocation happens in steady state."""
 
     def __init__(self):
         self._bufs = {}
 
     def get(self, device, tag: str, nbytes: int) -> torch.Tensor:
-        key = (device.index, tag)
+        # one buffer per (device, stream, tag): forwards in flight on different streams never share scratch
+        key = (device.index, torch.cuda.current_stream(device).cuda_stream, tag)
         buf = self._bufs.get(key)
         if buf is None or buf.numel() < nbytes:
             buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)

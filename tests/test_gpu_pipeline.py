@@ -1,0 +1,80 @@
+"""GPU: forwards issued from two host threads on two CUDA streams (pipeline.StreamPipeline) give bit-identical
+matches to the same forwards run one after the other -- per-stream workspaces, no shared scratch."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def test_stream_pipeline_matches_sequential():
+    from onepose_st_b200 import pipeline, sharding, synthetic
+    from onepose_st_b200.onepose_plus import OnePosePlus_model
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    model = OnePosePlus_model(synthetic.onepose_plus_cfg()).eval()
+    model.load_state_dict(synthetic.calibrate_onepose_state_dict(model.state_dict()), strict=True)
+    model = model.to(dev)
+    B, n_batches = 2, 6
+    seq = synthetic.make_onepose_sequence(model, 1500, B * n_batches, 256, 256, 300, device=dev)
+    kp = seq["keypoints3d"].expand(B, -1, -1).contiguous()
+    d_f = seq["descriptors3d_db"].expand(B, -1, -1).contiguous()
+    d_c = seq["descriptors3d_coarse_db"].expand(B, -1, -1).contiguous()
+
+    def run(k):
+        data = {"keypoints3d": kp, "descriptors3d_db": d_f, "descriptors3d_coarse_db": d_c,
+                "query_image": seq["frames"][k * B: (k + 1) * B]}
+        model(data)
+        return sharding.rows_onepose(data).cpu(), data["b_ids"].cpu()
+
+    with torch.no_grad():
+        want = [run(k) for k in range(n_batches)]
+        torch.cuda.synchronize()
+        for n_streams in (1, 2, 3):
+            got = pipeline.StreamPipeline(n_streams).map(run, range(n_batches))
+            torch.cuda.synchronize()
+            for (r0, b0), (r1, b1) in zip(want, got):
+                assert r0.shape[0] > 20
+                assert torch.equal(b0, b1) and torch.equal(r0, r1)
+
+
+def test_stream_pipeline_propagates_errors_and_orders_results():
+    from onepose_st_b200 import pipeline
+    pipe = pipeline.StreamPipeline(2)
+    out = pipe.map(lambda i: (torch.full((4,), float(i), device="cuda") * 2).sum().item(), range(9))
+    assert out == [8.0 * i for i in range(9)]
+    with pytest.raises(ZeroDivisionError):
+        pipe.map(lambda i: 1 // (i - 3), range(6))
+    assert pipe.map(lambda i: i, []) == []
+
+
+def test_broadcast_3d_model_reuses_first_self_layer():
+    """A 3D model passed as a broadcast (stride-0) batch is encoded once and its first self-attention layer is
+    computed once per sequence; the matches must equal those of the plain batched evaluation."""
+    from onepose_st_b200 import sharding, synthetic
+    from onepose_st_b200.onepose_plus import OnePosePlus_model
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    model = OnePosePlus_model(synthetic.onepose_plus_cfg()).eval()
+    model.load_state_dict(synthetic.calibrate_onepose_state_dict(model.state_dict()), strict=True)
+    model = model.to(dev)
+    B = 3
+    seq = synthetic.make_onepose_sequence(model, 1500, B, 256, 256, 300, device=dev)
+
+    def run(broadcast):
+        f = (lambda t: t.expand(B, -1, -1)) if broadcast else (lambda t: t.expand(B, -1, -1).contiguous())
+        data = {"keypoints3d": f(seq["keypoints3d"]), "descriptors3d_db": f(seq["descriptors3d_db"]),
+                "descriptors3d_coarse_db": f(seq["descriptors3d_coarse_db"]), "query_image": seq["frames"][:B]}
+        model(data)
+        return data
+
+    with torch.no_grad():
+        plain = run(False)
+        assert "_stream0_cache" not in model.loftr_coarse.__dict__
+        cached = run(True)
+        assert "_stream0_cache" in model.loftr_coarse.__dict__
+        again = run(True)                                   # second forward: served from the cache
+    for d in (cached, again):
+        assert torch.equal(plain["b_ids"], d["b_ids"]) and torch.equal(plain["i_ids"], d["i_ids"])
+        assert torch.equal(plain["j_ids"], d["j_ids"]) and plain["mconf"].numel() > 50
+        assert (plain["mconf"] - d["mconf"]).abs().max().item() < 1e-4   # fp32 round trip of the cached stream
+        assert (sharding.rows_onepose(plain) - sharding.rows_onepose(d)).abs().max().item() < 1e-3
