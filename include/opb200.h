@@ -167,11 +167,14 @@ int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels,
  *   x    [n, Hi, Wi, cin_s]  fp16, cin_s = input channels padded to a multiple of 16 (pad channels hold zeros)
  *   w    [k*k][cout_s][cin_s] fp16 (tap-major, zero in padded rows/cols); cout_s in {128, 208, 256}
  *   bias [cout_s] fp32 or NULL;  res [n, Ho, Wo, cout_s] fp16 or NULL
+ *   up   [n, Ho/2, Wo/2, cout_s] fp16 or NULL: adds F.interpolate(up, scale_factor=2, mode='bilinear',
+ *        align_corners=True) before the activation -- the FPN top-down add (resnet.py:155-162) fused into the lateral
+ *        1x1 convolution
  *   y16  [n, Ho, Wo, cout_s] fp16 and/or y32 (same shape, fp32); at least one non-NULL
  *   act  0 none, 1 ReLU, 2 LeakyReLU(slope) */
 int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride,
-                           int cout_s, const float* bias, const void* res, void* y16, float* y32, int act, float slope,
-                           void* stream);
+                           int cout_s, const float* bias, const void* res, const void* up, void* y16, float* y32, int act,
+                           float slope, void* stream);
 /* fp16-output variant of opb200_stem_conv7x7_s2_relu_nhwc and fp16 variant of opb200_upsample2x_add_nhwc (C % 8 == 0). */
 int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight_tap_major, const float* bias, int n_batch,
                                          int H, int W, int Cout, void* out_f16, void* stream);

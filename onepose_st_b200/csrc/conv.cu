@@ -12,7 +12,7 @@
 // the shifted pixel origin: TMA's out-of-bounds zero fill IS the convolution's zero padding, and its element strides
 // give the stride-2 sampling, so no im2col buffer ever exists.  The B operand is the [BN x 64] weight slab of that tap.
 // Both sub-tiles consume the same weight slab (MSUB = 2 halves the weight refetch per flop).
-// Warp roles as in gemm.cuh: warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2..9 epilogue
+// Warp roles as in gemm.cuh: warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2..17 epilogue
 // (bias + residual + ReLU / LeakyReLU, fp16 and/or fp32 NHWC stores, 32 bytes per lane per store).
 #include <cuda_fp16.h>
 #include "host.cuh"
@@ -31,6 +31,7 @@ struct ConvPlan {
   int ksize, pad, stride;
   int nchunks;  // 64-channel chunks per tap
   int nk_last;  // K=16 MMAs in the last chunk (1..4)
+  long long* trace;  // debug (opb200_debug_trace): per CTA and tile {first TMA, MMA start, accumulator full, epilogue done}
 };
 
 struct ConvEpi {
@@ -40,6 +41,14 @@ struct ConvEpi {
   float* y32;         // NHWC fp32 output or null
   int act;            // 0 none, 1 ReLU, 2 LeakyReLU(slope)
   float slope;
+  // FPN top-down path fused in: y += bilinear x2 (align_corners = True) of up [n, Ho/2, Wo/2, BN] fp16 (null = off)
+  const __half* up;
+  float up_ry, up_rx;
+};
+
+struct UpTaps {  // the four source pixels (element offsets) and weights of one output pixel
+  long long o00, o01, o10, o11;
+  float w00, w01, w10, w11;
 };
 
 __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
@@ -71,10 +80,27 @@ struct ConvCfg {
 };
 
 // 16 accumulator columns of one pixel: bias, residual, activation, stores.
-__device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const ConvEpi& ep, long long off, int c0) {
+__device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const ConvEpi& ep, long long off, int c0,
+                                               const UpTaps& ut) {
   float v[16];
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+  if (ep.up != nullptr) {
+    uint32_t a[8], b[8], c[8], d[8];
+    ptx::ld_global_v8(ep.up + ut.o00 + c0, a);
+    ptx::ld_global_v8(ep.up + ut.o01 + c0, b);
+    ptx::ld_global_v8(ep.up + ut.o10 + c0, c);
+    ptx::ld_global_v8(ep.up + ut.o11 + c0, d);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float2 fa = __half22float2(*reinterpret_cast<const __half2*>(&a[i]));
+      const float2 fb = __half22float2(*reinterpret_cast<const __half2*>(&b[i]));
+      const float2 fc = __half22float2(*reinterpret_cast<const __half2*>(&c[i]));
+      const float2 fd = __half22float2(*reinterpret_cast<const __half2*>(&d[i]));
+      v[2 * i] += ut.w00 * fa.x + ut.w01 * fb.x + ut.w10 * fc.x + ut.w11 * fd.x;
+      v[2 * i + 1] += ut.w00 * fa.y + ut.w01 * fb.y + ut.w10 * fc.y + ut.w11 * fd.y;
+    }
+  }
   if (ep.bias != nullptr) {
     const float4* b = reinterpret_cast<const float4*>(ep.bias + c0);
 #pragma unroll
@@ -119,7 +145,7 @@ __device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const Co
 }
 
 template <int BN, int MSUB>
-__global__ void __launch_bounds__(64 + 256, 1) conv_kernel(const __grid_constant__ ConvPlan plan, const ConvEpi ep) {
+__global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant__ ConvPlan plan, const ConvEpi ep) {
   using Cfg = ConvCfg<BN, MSUB>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
@@ -142,7 +168,7 @@ __global__ void __launch_bounds__(64 + 256, 1) conv_kernel(const __grid_constant
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
-      ptx::mbar_init(&tempty_bar[s], 8);
+      ptx::mbar_init(&tempty_bar[s], 16);
     }
     ptx::fence_barrier_init();
   }
@@ -169,6 +195,10 @@ __global__ void __launch_bounds__(64 + 256, 1) conv_kernel(const __grid_constant
         const int ty = r / plan.tiles_x, tx = r - ty * plan.tiles_x;
         const int ix0 = tx * CONV_TW * plan.stride - plan.pad;
         const int iy0 = ty * (CONV_TH * MSUB) * plan.stride - plan.pad;
+        if (plan.trace != nullptr) {
+          const int it = (t - blockIdx.x) / gridDim.x;
+          if (it < kTraceTilesPerCta) plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 0] = clock64();
+        }
         for (int tap = 0; tap < taps; ++tap) {
           const int ky = tap / plan.ksize, kx = tap - ky * plan.ksize;
           for (int ch = 0; ch < plan.nchunks; ++ch) {
@@ -198,6 +228,8 @@ __global__ void __launch_bounds__(64 + 256, 1) conv_kernel(const __grid_constant
       ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_COLS;
+      if (plan.trace != nullptr && it < kTraceTilesPerCta && lane == 0)
+        plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 1] = clock64();
       int ch = 0;
       for (int kb = 0; kb < total_kb; ++kb) {
         ptx::mbar_wait(&full_bar[stage], phase);
@@ -224,13 +256,16 @@ __global__ void __launch_bounds__(64 + 256, 1) conv_kernel(const __grid_constant
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue: 8 warps, two per TMEM lane quarter
+    // ------------------------------------------------------------------ epilogue: 16 warps, four per TMEM lane quarter
+    // (two per SM sub-partition is too few to hide the TMEM / global latencies of this loop)
     const int quarter = warp & 3;
-    const int part = (warp - 2) >> 2;  // MSUB == 2: the sub-tile; MSUB == 1: which half of the 16-column chunks
+    const int part = (warp - 2) >> 2;  // 0..3: MSUB == 2 -> (sub-tile, column half); MSUB == 1 -> column quarter
     constexpr int NCH = BN / 16;
-    const int sub = MSUB == 2 ? part : 0;
-    const int ch_begin = MSUB == 2 ? 0 : (part == 0 ? 0 : (NCH + 1) / 2);
-    const int ch_end = MSUB == 2 ? NCH : (part == 0 ? (NCH + 1) / 2 : NCH);
+    constexpr int NSPLIT = MSUB == 2 ? 2 : 4;
+    const int sub = MSUB == 2 ? (part & 1) : 0;
+    const int cpart = MSUB == 2 ? (part >> 1) : part;
+    const int ch_begin = (NCH * cpart) / NSPLIT;
+    const int ch_end = (NCH * (cpart + 1)) / NSPLIT;
     const int row = quarter * 32 + lane;  // GEMM row inside the sub-tile
     const int hy = row / CONV_TW, wx = row - hy * CONV_TW;
     int it = 0;
@@ -244,8 +279,24 @@ __global__ void __launch_bounds__(64 + 256, 1) conv_kernel(const __grid_constant
       const bool valid = oy < plan.Ho && ox < plan.Wo;
       const long long off = ((static_cast<long long>(n) * plan.Ho + oy) * plan.Wo + ox) * BN;
       if (valid && ep.res != nullptr) ptx::prefetch_l2(ep.res + off + ch_begin * 16);
+      UpTaps ut = {};
+      if (ep.up != nullptr && valid) {  // torch's align_corners=True source index: src = dst * (in - 1) / (out - 1)
+        const int Hs = plan.Ho >> 1, Ws = plan.Wo >> 1;
+        const float sy = ep.up_ry * oy, sx = ep.up_rx * ox;
+        const int y0 = static_cast<int>(sy), x0 = static_cast<int>(sx);
+        const int y1 = y0 + (y0 < Hs - 1), x1 = x0 + (x0 < Ws - 1);
+        const float ly1 = sy - y0, lx1 = sx - x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
+        const long long base = static_cast<long long>(n) * Hs * Ws;
+        ut.o00 = (base + static_cast<long long>(y0) * Ws + x0) * BN;
+        ut.o01 = (base + static_cast<long long>(y0) * Ws + x1) * BN;
+        ut.o10 = (base + static_cast<long long>(y1) * Ws + x0) * BN;
+        ut.o11 = (base + static_cast<long long>(y1) * Ws + x1) * BN;
+        ut.w00 = ly0 * lx0, ut.w01 = ly0 * lx1, ut.w10 = ly1 * lx0, ut.w11 = ly1 * lx1;
+      }
       ptx::mbar_wait(&tfull_bar[acc], acc_phase);
       ptx::tc_fence_after();
+      const bool tr = plan.trace != nullptr && it < kTraceTilesPerCta && warp == 2 && lane == 0;
+      if (tr) plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 2] = clock64();
       const uint32_t taddr = tmem_base + acc * Cfg::ACC_COLS + sub * BN + (static_cast<uint32_t>(quarter * 32) << 16);
       int c = ch_begin;
       for (; c + 1 < ch_end; c += 2) {
@@ -254,19 +305,20 @@ __global__ void __launch_bounds__(64 + 256, 1) conv_kernel(const __grid_constant
         ptx::tmem_ld16(taddr + c * 16 + 16, r1);
         ptx::tmem_ld_wait();
         if (valid) {
-          conv_epi_chunk(r0, ep, off, c * 16);
-          conv_epi_chunk(r1, ep, off, c * 16 + 16);
+          conv_epi_chunk(r0, ep, off, c * 16, ut);
+          conv_epi_chunk(r1, ep, off, c * 16 + 16, ut);
         }
       }
       if (c < ch_end) {
         uint32_t r0[16];
         ptx::tmem_ld16(taddr + c * 16, r0);
         ptx::tmem_ld_wait();
-        if (valid) conv_epi_chunk(r0, ep, off, c * 16);
+        if (valid) conv_epi_chunk(r0, ep, off, c * 16, ut);
       }
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty_bar[acc]);
+      if (tr) plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 3] = clock64();
     }
   }
 
@@ -290,7 +342,13 @@ static int launch_conv(const ConvPlan& plan, const ConvEpi& ep, cudaStream_t str
   }
   int grid = num_sms();
   if (plan.num_tiles < grid) grid = plan.num_tiles;
-  kern<<<grid, 64 + 256, Cfg::SMEM, stream>>>(plan, ep);
+  if (long long* tr = next_trace_slot(grid)) {
+    ConvPlan traced = plan;
+    traced.trace = tr;
+    kern<<<grid, 64 + 512, Cfg::SMEM, stream>>>(traced, ep);
+  } else {
+    kern<<<grid, 64 + 512, Cfg::SMEM, stream>>>(plan, ep);
+  }
   count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
@@ -301,7 +359,10 @@ static int conv_dispatch(ConvPlan& plan, const ConvEpi& ep, const void* x, int H
   // two stacked sub-tiles per CTA tile when that still leaves every SM at least two tiles
   const int tx = (plan.Wo + CONV_TW - 1) / CONV_TW;
   const int ty2 = (plan.Ho + 2 * CONV_TH - 1) / (2 * CONV_TH);
-  const bool two = static_cast<long long>(plan.n_img) * tx * ty2 >= 2LL * num_sms();
+  // BN = 128: two sub-tiles still double-buffer in TMEM (4 x 128 columns).  BN = 208: two sub-tiles fill TMEM with one
+  // accumulator set, so the epilogue runs behind the mainloop, but the halved weight refetch still wins (measured
+  // 19.9 vs 24.2 us per 256 pixels).  BN = 256: one sub-tile, double-buffered (23.1 vs 25.1 us).
+  const bool two = BN <= 208 && static_cast<long long>(plan.n_img) * tx * ty2 >= 2LL * num_sms();
   const int msub = two ? 2 : 1;
   plan.tiles_x = tx;
   plan.tiles_y = (plan.Ho + msub * CONV_TH - 1) / (msub * CONV_TH);
@@ -324,7 +385,8 @@ using namespace opb;
 extern "C" {
 
 int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride, int cout_s,
-                           const float* bias, const void* res, void* y16, float* y32, int act, float slope, void* stream_) {
+                           const float* bias, const void* res, const void* up, void* y16, float* y32, int act, float slope,
+                           void* stream_) {
   if (int r = check_device()) return r;
   OPB_CHECK_ARG(x && w && (y16 || y32), "null pointer");
   OPB_CHECK_ARG(n_img >= 1 && Hi >= 1 && Wi >= 1, "bad shape");
@@ -352,6 +414,15 @@ int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, 
   ep.y32 = y32;
   ep.act = act;
   ep.slope = slope;
+  ep.up = static_cast<const __half*>(up);
+  ep.up_ry = ep.up_rx = 0.f;
+  if (up != nullptr) {
+    OPB_CHECK_ARG(plan.Ho % 2 == 0 && plan.Wo % 2 == 0, "fused x2 upsampling needs even output sides");
+    OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(up) & 31) == 0, "up must be 32-byte aligned");
+    const int Hs = plan.Ho / 2, Ws = plan.Wo / 2;
+    ep.up_ry = Hs > 1 ? static_cast<float>(Hs - 1) / static_cast<float>(plan.Ho - 1) : 0.f;
+    ep.up_rx = Ws > 1 ? static_cast<float>(Ws - 1) / static_cast<float>(plan.Wo - 1) : 0.f;
+  }
   {
     const uint64_t gdim[2] = {static_cast<uint64_t>(cin_s), static_cast<uint64_t>(ksize) * ksize * cout_s};
     const uint64_t gstr[1] = {static_cast<uint64_t>(cin_s) * 2};

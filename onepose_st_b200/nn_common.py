@@ -255,9 +255,10 @@ class FusedBackboneF16:
                 feats.append(x)
         x1, x2, x3 = feats
         c3_16, c3 = ops.conv2d_nhwc_f16(x3, self.l3_out[0], 1, 1, self.l3_out[1], None, 0, out_f16=True, out_f32=True)
-        l2 = ops.upsample2x_add_f16_(ops.conv2d_nhwc_f16(x2, self.l2_out[0], 1, 1, self.l2_out[1], None, 0), c3_16)
+        # lateral 1x1 convolution + bilinear x2 of the coarser level, one kernel per FPN level
+        l2 = ops.conv2d_nhwc_f16(x2, self.l2_out[0], 1, 1, self.l2_out[1], None, 0, up=c3_16)
         c2 = self._head(l2, self.head2, False)
-        l1 = ops.upsample2x_add_f16_(ops.conv2d_nhwc_f16(x1, self.l1_out[0], 1, 1, self.l1_out[1], None, 0), c2)
+        l1 = ops.conv2d_nhwc_f16(x1, self.l1_out[0], 1, 1, self.l1_out[1], None, 0, up=c2)
         c1 = self._head(l1, self.head1, True)
         return c3.permute(0, 3, 1, 2), c1.permute(0, 3, 1, 2)
 

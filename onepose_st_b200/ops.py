@@ -362,9 +362,9 @@ def linear_attention(q, k, v, q_mask=None, kv_mask=None, eps: float = 1e-6) -> t
 # ------------------------------------------------------------------------------------------------
 def conv2d_nhwc_f16(x: torch.Tensor, w: torch.Tensor, ksize: int, stride: int = 1, bias: Optional[torch.Tensor] = None,
                     res: Optional[torch.Tensor] = None, act: int = 0, slope: float = 0.0, out_f16: bool = True,
-                    out_f32: bool = False, stage: str = "backbone_conv"):
+                    out_f32: bool = False, stage: str = "backbone_conv", up: Optional[torch.Tensor] = None):
     """y = act(conv_k(x) + bias + res): x [N,Hi,Wi,Cin_s] fp16, w [k*k*Cout_s, Cin_s] fp16 tap-major, bias [Cout_s] fp32,
-    res [N,Ho,Wo,Cout_s] fp16.  Returns the fp16 output, the fp32 output, or (fp16, fp32) when both are asked."""
+    res [N,Ho,Wo,Cout_s] fp16, up [N,Ho/2,Wo/2,Cout_s] fp16 (bilinear x2, align_corners=True, added before act).  Returns the fp16 output, the fp32 output, or (fp16, fp32) when both are asked."""
     _need_cuda(x, w, bias, res)
     if x.dtype != torch.float16 or w.dtype != torch.float16 or not x.is_contiguous() or not w.is_contiguous() or x.dim() != 4:
         raise _lib.Opb200Error("conv2d_nhwc_f16: contiguous fp16 [N,H,W,C] input and fp16 weights required")
@@ -376,13 +376,16 @@ def conv2d_nhwc_f16(x: torch.Tensor, w: torch.Tensor, ksize: int, stride: int = 
     ho, wo = (hi + 2 * pad - ksize) // stride + 1, (wi + 2 * pad - ksize) // stride + 1
     if res is not None and (res.dtype != torch.float16 or tuple(res.shape) != (n, ho, wo, cout_s) or not res.is_contiguous()):
         raise _lib.Opb200Error("conv2d_nhwc_f16: residual must be contiguous fp16 [N,Ho,Wo,Cout_s]")
+    if up is not None and (up.dtype != torch.float16 or not up.is_contiguous() or ho % 2 or wo % 2
+                           or tuple(up.shape) != (n, ho // 2, wo // 2, cout_s)):
+        raise _lib.Opb200Error("conv2d_nhwc_f16: up must be contiguous fp16 [N,Ho/2,Wo/2,Cout_s]")
     if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout_s):
         raise _lib.Opb200Error("conv2d_nhwc_f16: bias must be fp32 [Cout_s]")
     y16 = torch.empty(n, ho, wo, cout_s, dtype=torch.float16, device=x.device) if out_f16 else None
     y32 = torch.empty(n, ho, wo, cout_s, dtype=torch.float32, device=x.device) if out_f32 else None
     with _Stage(stage):
         st = _lib.lib().opb200_conv2d_nhwc_f16(_lib.ptr(x), n, hi, wi, cin_s, _lib.ptr(w), ksize, stride, cout_s, _lib.ptr(bias),
-                                               _lib.ptr(res), _lib.ptr(y16), _lib.ptr(y32), act, ctypes.c_float(slope),
+                                               _lib.ptr(res), _lib.ptr(up), _lib.ptr(y16), _lib.ptr(y32), act, ctypes.c_float(slope),
                                                _lib.stream_ptr())
     _lib.check(st, "opb200_conv2d_nhwc_f16")
     if out_f16 and out_f32:

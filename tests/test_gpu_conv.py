@@ -86,3 +86,30 @@ def test_stem_and_upsample_f16():
                                        align_corners=True).permute(0, 2, 3, 1)
     got = ops.upsample2x_add_f16_(dst.clone(), src)
     assert (got.float() - want).abs().max().item() < 4e-3        # one fp16 rounding of an O(4) value
+
+
+@pytest.mark.parametrize("n,H,W,cin,cout", [(2, 24, 40, 128, 196), (1, 64, 64, 196, 256), (8, 128, 128, 128, 196)])
+def test_lateral_conv_with_fused_upsample_add(n, H, W, cin, cout):
+    """1x1 lateral convolution + bilinear x2 (align_corners=True) of the coarser FPN level in one epilogue."""
+    from onepose_st_b200 import ops
+    from onepose_st_b200.nn_common import pack_conv_f16, _cs
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        g = torch.Generator(device="cuda").manual_seed(99 + H)
+        cin_s, cout_s = _cs(cin), _cs(cout)
+        x16 = torch.zeros(n, H, W, cin_s, dtype=torch.float16, device="cuda")
+        x16[..., :cin] = torch.randn(n, H, W, cin, device="cuda", generator=g).half()
+        up16 = torch.zeros(n, H // 2, W // 2, cout_s, dtype=torch.float16, device="cuda")
+        up16[..., :cout] = torch.randn(n, H // 2, W // 2, cout, device="cuda", generator=g).half()
+        w = torch.randn(cout, cin, 1, 1, device="cuda", generator=g) / cin ** 0.5
+        wp, _ = pack_conv_f16(w, None)
+        got = ops.conv2d_nhwc_f16(x16, wp, 1, 1, None, None, 0, up=up16, out_f16=False, out_f32=True)
+        want = _ref(x16, w, None, None, 1, 1, 0, 0.0) + F.interpolate(
+            up16[..., :cout].float().permute(0, 3, 1, 2), scale_factor=2.0, mode="bilinear", align_corners=True).permute(0, 2, 3, 1)
+        err = (got[..., :cout] - want).abs().max().item()
+        assert err < 2e-4, err
+        if cout_s > cout:
+            assert (got[..., cout:] == 0).all()
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
