@@ -655,10 +655,15 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
   const int seg = ((n_rows + 31) / 32 + 31) / 32 * 32;  // rows per warp, a multiple of 32
   const int r0 = warp * seg, r1 = min(r0 + seg, n_rows);
   int cnt = 0;
-  for (int base = r0; base < r1; base += 32) {
-    const int r = base + lane;
-    const bool f = r < r1 && rowj[r] != kNoMatch;
-    cnt += __popc(__ballot_sync(0xffffffffu, f));
+  for (int base = r0; base < r1; base += 32 * 8) {  // 8 independent loads in flight per lane: the walk is latency-bound
+    int jv[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int r = base + u * 32 + lane;
+      jv[u] = r < r1 ? rowj[r] : kNoMatch;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) cnt += __popc(__ballot_sync(0xffffffffu, jv[u] != kNoMatch));
   }
   if (lane == 0) warp_sums[warp] = cnt;
   __syncthreads();
@@ -682,20 +687,29 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
   }
   __syncthreads();
   int pos = warp_sums[warp];
-  for (int base = r0; base < r1; base += 32) {
-    const int r = base + lane;
-    const int j = r < r1 ? rowj[r] : kNoMatch;
-    const unsigned ball = __ballot_sync(0xffffffffu, j != kNoMatch);
-    if (j != kNoMatch) {
-      const int o = pos + __popc(ball & ((1u << lane) - 1));
-      if (o < capacity) {
-        b_ids[o] = r / L;
-        i_ids[o] = r % L;
-        j_ids[o] = j;
-        mconf[o] = __uint_as_float(rowmax[r]);
-      }
+  for (int base = r0; base < r1; base += 32 * 8) {
+    int jv[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int r = base + u * 32 + lane;
+      jv[u] = r < r1 ? rowj[r] : kNoMatch;
     }
-    pos += __popc(ball);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int r = base + u * 32 + lane;
+      const int j = jv[u];
+      const unsigned ball = __ballot_sync(0xffffffffu, j != kNoMatch);
+      if (j != kNoMatch) {
+        const int o = pos + __popc(ball & ((1u << lane) - 1));
+        if (o < capacity) {
+          b_ids[o] = r / L;
+          i_ids[o] = r % L;
+          j_ids[o] = j;
+          mconf[o] = __uint_as_float(rowmax[r]);
+        }
+      }
+      pos += __popc(ball);
+    }
   }
 }
 

@@ -341,7 +341,8 @@ static int launch_conv(const ConvPlan& plan, const ConvEpi& ep, cudaStream_t str
     configured = true;
   }
   int grid = num_sms();
-  if (plan.num_tiles < grid) grid = plan.num_tiles;
+  const int waves = (plan.num_tiles + grid - 1) / grid;  // fewest CTAs for the same number of tile waves
+  grid = (plan.num_tiles + waves - 1) / waves;
   if (long long* tr = next_trace_slot(grid)) {
     ConvPlan traced = plan;
     traced.trace = tr;

@@ -176,20 +176,30 @@ struct EpiLN {  // MERGE epilogue: LayerNorm1 -> planes
     load_row_slice<CPT>(ctx, x);
     float mean, rstd;
     row_mean_rstd_split<CPT>(ctx, x, C, mean, rstd);
+    const int cb = ctx.part * CPT;
 #pragma unroll
-    for (int c = 0; c < CPT; c += 32) {
-      const int c0 = ctx.part * CPT + c;
-      float v[32];
+    for (int i = 0; i < CPT; i += 4) {  // warp-uniform addresses: one broadcast 16-byte load per 4 columns
+      const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.gamma + cb + i));
+      const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.beta + cb + i));
+      x[i + 0] = (x[i + 0] - mean) * rstd * g4.x + b4.x;
+      x[i + 1] = (x[i + 1] - mean) * rstd * g4.y + b4.y;
+      x[i + 2] = (x[i + 2] - mean) * rstd * g4.z + b4.z;
+      x[i + 3] = (x[i + 3] - mean) * rstd * g4.w + b4.w;
+    }
+    const long long wrow0 = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32;
+    if constexpr (CPT == 64) {
+      uint32_t h[4][8], l[4][8];
+      pack_planes64(x, h, l);
+      store_row64_bf16_quad(h, p.o_hi + wrow0 * C + cb, C, ctx.lane);
+      if (p.o_lo) store_row64_bf16_quad(l, p.o_lo + wrow0 * C + cb, C, ctx.lane);
+    } else {
 #pragma unroll
-      for (int i = 0; i < 32; i += 4) {  // warp-uniform addresses: one broadcast 16-byte load per 4 columns
-        const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.gamma + c0 + i));
-        const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.beta + c0 + i));
-        v[i + 0] = (x[c + i + 0] - mean) * rstd * g4.x + b4.x;
-        v[i + 1] = (x[c + i + 1] - mean) * rstd * g4.y + b4.y;
-        v[i + 2] = (x[c + i + 2] - mean) * rstd * g4.z + b4.z;
-        v[i + 3] = (x[c + i + 3] - mean) * rstd * g4.w + b4.w;
+      for (int c = 0; c < CPT; c += 32) {
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = x[c + i];
+        store_planes32_v8(v, p.o_hi + row * C + cb + c, p.o_lo ? p.o_lo + row * C + cb + c : nullptr);
       }
-      store_planes32_v8(v, p.o_hi + row * C + c0, p.o_lo ? p.o_lo + row * C + c0 : nullptr);
     }
   }
 };
@@ -237,33 +247,61 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual str
     load_row_slice<CPT>(ctx, x);
     float mean, rstd;
     row_mean_rstd_split<CPT>(ctx, x, C, mean, rstd);
+    const int cb = ctx.part * CPT;
 #pragma unroll
-    for (int c = 0; c < CPT; c += 32) {
-      const int c0 = ctx.part * CPT + c;
-      __nv_bfloat16* ph = p.x_hi + row * C + c0;
-      __nv_bfloat16* pl = p.x_lo + row * C + c0;
-      float v[32];
+    for (int i = 0; i < CPT; i += 4) {
+      const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.gamma + cb + i));
+      const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.beta + cb + i));
+      x[i + 0] = (x[i + 0] - mean) * rstd * g4.x + b4.x;
+      x[i + 1] = (x[i + 1] - mean) * rstd * g4.y + b4.y;
+      x[i + 2] = (x[i + 2] - mean) * rstd * g4.z + b4.z;
+      x[i + 3] = (x[i + 3] - mean) * rstd * g4.w + b4.w;
+    }
+    if constexpr (CPT == 64) {  // residual planes in and out through the quad transpose (one line per quad and instruction)
+      const long long wrow0 = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32;
+      __nv_bfloat16* ph = p.x_hi + wrow0 * C + cb;
+      __nv_bfloat16* pl = p.x_lo + wrow0 * C + cb;
+      uint32_t h[4][8], l[4][8];
+      // one plane at a time (x[64] + two planes in flight would not fit the 112 registers of a 576-thread CTA); the small
+      // lo plane is added first so that the sum is (lo + LN) + hi
+      load_row64_bf16_quad(l, pl, C, ctx.lane);
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        uint32_t h[8], l[8];
-        ptx::ld_global_v8(ph + 16 * i, h);
-        ptx::ld_global_v8(pl + 16 * i, l);
-#pragma unroll
-        for (int k = 0; k < 8; k += 2) {
-          const int e = 16 * i + 2 * k, cc = c0 + e;
-          const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.gamma + cc));
-          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.beta + cc));
-          const float2 h0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h[k]));
-          const float2 l0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&l[k]));
-          const float2 h1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h[k + 1]));
-          const float2 l1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&l[k + 1]));
-          v[e + 0] = (h0.x + l0.x) + ((x[c + e + 0] - mean) * rstd * g4.x + b4.x);
-          v[e + 1] = (h0.y + l0.y) + ((x[c + e + 1] - mean) * rstd * g4.y + b4.y);
-          v[e + 2] = (h1.x + l1.x) + ((x[c + e + 2] - mean) * rstd * g4.z + b4.z);
-          v[e + 3] = (h1.y + l1.y) + ((x[c + e + 3] - mean) * rstd * g4.w + b4.w);
-        }
+      for (int i = 0; i < 32; ++i) {
+        const float2 lf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&l[i >> 3][i & 7]));
+        x[2 * i] += lf.x;
+        x[2 * i + 1] += lf.y;
       }
-      store_planes32_v8(v, ph, pl);
+      load_row64_bf16_quad(h, ph, C, ctx.lane);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float2 hf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h[i >> 3][i & 7]));
+        x[2 * i] += hf.x;
+        x[2 * i + 1] += hf.y;
+      }
+      pack_planes64(x, h, l);
+      store_row64_bf16_quad(h, ph, C, ctx.lane);
+      store_row64_bf16_quad(l, pl, C, ctx.lane);
+    } else {
+#pragma unroll
+      for (int c = 0; c < CPT; c += 32) {
+        __nv_bfloat16* ph = p.x_hi + row * C + cb + c;
+        __nv_bfloat16* pl = p.x_lo + row * C + cb + c;
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          uint32_t h[8], l[8];
+          ptx::ld_global_v8(ph + 16 * i, h);
+          ptx::ld_global_v8(pl + 16 * i, l);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float2 hf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h[k]));
+            const float2 lf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&l[k]));
+            v[16 * i + 2 * k] = (hf.x + lf.x) + x[c + 16 * i + 2 * k];
+            v[16 * i + 2 * k + 1] = (hf.y + lf.y) + x[c + 16 * i + 2 * k + 1];
+          }
+        }
+        store_planes32_v8(v, ph, pl);
+      }
     }
   }
 };
@@ -384,53 +422,121 @@ __global__ void __launch_bounds__(256) kv_pack_kernel(const float* __restrict__ 
 // Small-group attention (fine level: C = 128, H = 8, D = 16; groups are single matches of <= 128 rows).
 // One block per query group: build KV / Ksum of the source group in shared memory, then apply.
 // ------------------------------------------------------------------------------------------------
+struct SmallAttnJob {  // one (query stream, source stream) pairing of a layer step
+  int q_row0, q_len, s_row0, s_len;
+};
+struct SmallAttnJobs {
+  SmallAttnJob job[2];
+};
+
+// grid = (groups, jobs), block = 128 threads = channels (head h = t / 16, d or v index = t % 16).  Source / query rows are
+// staged 32 at a time through shared memory with coalesced 16-byte loads (three barriers per chunk instead of two
+// per row); the 16 x 16 KV block of a head and its Ksum stay in registers for the apply phase.
 __global__ void __launch_bounds__(128) attn_small_kernel(const float* __restrict__ qphi, const float* __restrict__ kphi,
-                                                         const float* __restrict__ v, int q_row0, int q_len,
-                                                         int s_row0, int s_len, int num_groups, float eps,
-                                                         __nv_bfloat16* __restrict__ o_hi, __nv_bfloat16* __restrict__ o_lo) {
-  constexpr int C = 128, D = 16;
+                                                         const float* __restrict__ v, SmallAttnJobs jobs, int num_groups,
+                                                         float eps, __nv_bfloat16* __restrict__ o_hi,
+                                                         __nv_bfloat16* __restrict__ o_lo) {
+  constexpr int C = 128, D = 16, CH = 32;
   const int g = blockIdx.x;
   if (g >= num_groups) return;
-  const int t = threadIdx.x;  // channel index: head h = t/16, d (or v) = t%16
-  const int h = t >> 4;
-  __shared__ float kv[8][D][D + 1];
+  const SmallAttnJob jb = jobs.job[blockIdx.y];
+  const int t = threadIdx.x;
+  const int h = t >> 4, dv = t & 15;
+  __shared__ __align__(16) float abuf[CH][C];  // K rows, later Q rows
+  __shared__ __align__(16) float bbuf[CH][C];  // V rows
+  __shared__ float kv_s[8][D][D + 1];
   __shared__ float ksum_s[8][D];
-  __shared__ __align__(16) float rowbuf[2][C];
-  const long long sbase = static_cast<long long>(s_row0 + g * s_len) * C;
+  const float4* k4 = reinterpret_cast<const float4*>(kphi + static_cast<long long>(jb.s_row0 + g * jb.s_len) * C);
+  const float4* v4 = reinterpret_cast<const float4*>(v + static_cast<long long>(jb.s_row0 + g * jb.s_len) * C);
   float acc[D];
 #pragma unroll
   for (int i = 0; i < D; ++i) acc[i] = 0.f;
   float ksum = 0.f;
-  for (int r = 0; r < s_len; ++r) {
+  for (int r0 = 0; r0 < jb.s_len; r0 += CH) {
+    const int nr = min(CH, jb.s_len - r0);
     __syncthreads();
-    rowbuf[0][t] = v[sbase + r * C + t];
-    const float kk = kphi[sbase + r * C + t];
-    __syncthreads();
-    ksum += kk;
+    {  // all 16 loads of a thread in flight before the first shared-memory store
+      float4 kr[CH * (C / 4) / 128], vr[CH * (C / 4) / 128];
 #pragma unroll
-    for (int i = 0; i < D; ++i) acc[i] = fmaf(kk, rowbuf[0][h * D + i], acc[i]);
-  }
+      for (int u = 0; u < CH * (C / 4) / 128; ++u) {
+        const int i = t + u * 128;
+        if (i < nr * (C / 4)) {
+          kr[u] = __ldg(k4 + r0 * (C / 4) + i);
+          vr[u] = __ldg(v4 + r0 * (C / 4) + i);
+        }
+      }
 #pragma unroll
-  for (int i = 0; i < D; ++i) kv[h][t & 15][i] = acc[i];
-  ksum_s[h][t & 15] = ksum;
-  __syncthreads();
-  const long long qbase = static_cast<long long>(q_row0 + g * q_len) * C;
-  for (int r = 0; r < q_len; ++r) {
-    __syncthreads();
-    rowbuf[1][t] = qphi[qbase + r * C + t];
-    __syncthreads();
-    float num = 0.f, den = 0.f;
-#pragma unroll
-    for (int d = 0; d < D; ++d) {
-      const float qq = rowbuf[1][h * D + d];
-      num = fmaf(qq, kv[h][d][t & 15], num);
-      den = fmaf(qq, ksum_s[h][d], den);
+      for (int u = 0; u < CH * (C / 4) / 128; ++u) {
+        const int i = t + u * 128;
+        if (i < nr * (C / 4)) {
+          reinterpret_cast<float4*>(&abuf[0][0])[i] = kr[u];
+          reinterpret_cast<float4*>(&bbuf[0][0])[i] = vr[u];
+        }
+      }
     }
-    const float o = num / (den + eps);
-    __nv_bfloat16 hi_, lo_;
-    split_bf16(o, hi_, lo_);
-    o_hi[qbase + r * C + t] = hi_;
-    if (o_lo) o_lo[qbase + r * C + t] = lo_;
+    __syncthreads();
+    for (int r = 0; r < nr; ++r) {
+      const float kk = abuf[r][t];
+      ksum += kk;
+      const float4* vv = reinterpret_cast<const float4*>(&bbuf[r][h * D]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 f = vv[q];
+        acc[4 * q + 0] = fmaf(kk, f.x, acc[4 * q + 0]);
+        acc[4 * q + 1] = fmaf(kk, f.y, acc[4 * q + 1]);
+        acc[4 * q + 2] = fmaf(kk, f.z, acc[4 * q + 2]);
+        acc[4 * q + 3] = fmaf(kk, f.w, acc[4 * q + 3]);
+      }
+    }
+  }
+  // thread (h, d) holds KV[h][d][0..15]; the apply phase wants thread (h, i) to hold KV[h][0..15][i]: transpose via smem
+#pragma unroll
+  for (int i = 0; i < D; ++i) kv_s[h][dv][i] = acc[i];
+  ksum_s[h][dv] = ksum;
+  __syncthreads();
+  float kvr[D], ksr[D];
+#pragma unroll
+  for (int d = 0; d < D; ++d) {
+    kvr[d] = kv_s[h][d][dv];
+    ksr[d] = ksum_s[h][d];
+  }
+  const long long qbase = static_cast<long long>(jb.q_row0 + g * jb.q_len) * C;
+  const float4* q4 = reinterpret_cast<const float4*>(qphi + qbase);
+  for (int r0 = 0; r0 < jb.q_len; r0 += CH) {
+    const int nr = min(CH, jb.q_len - r0);
+    __syncthreads();
+    {
+      float4 qr[CH * (C / 4) / 128];
+#pragma unroll
+      for (int u = 0; u < CH * (C / 4) / 128; ++u) {
+        const int i = t + u * 128;
+        if (i < nr * (C / 4)) qr[u] = __ldg(q4 + r0 * (C / 4) + i);
+      }
+#pragma unroll
+      for (int u = 0; u < CH * (C / 4) / 128; ++u) {
+        const int i = t + u * 128;
+        if (i < nr * (C / 4)) reinterpret_cast<float4*>(&abuf[0][0])[i] = qr[u];
+      }
+    }
+    __syncthreads();
+    for (int r = 0; r < nr; ++r) {
+      const float4* qq = reinterpret_cast<const float4*>(&abuf[r][h * D]);
+      float num = 0.f, den = 0.f;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 f = qq[q];
+        num = fmaf(f.x, kvr[4 * q + 0], num), den = fmaf(f.x, ksr[4 * q + 0], den);
+        num = fmaf(f.y, kvr[4 * q + 1], num), den = fmaf(f.y, ksr[4 * q + 1], den);
+        num = fmaf(f.z, kvr[4 * q + 2], num), den = fmaf(f.z, ksr[4 * q + 2], den);
+        num = fmaf(f.w, kvr[4 * q + 3], num), den = fmaf(f.w, ksr[4 * q + 3], den);
+      }
+      const float o = num / (den + eps);
+      __nv_bfloat16 hi_, lo_;
+      split_bf16(o, hi_, lo_);
+      const long long idx = qbase + static_cast<long long>(r0 + r) * C + t;
+      o_hi[idx] = hi_;
+      if (o_lo) o_lo[idx] = lo_;
+    }
   }
 }
 
@@ -729,13 +835,16 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
   } else {
     if constexpr (C == 128) {
       const int row1 = g.row1;
+      SmallAttnJobs jobs;
+      int nj = 0;
       for (int s = 0; s < 2; ++s) {
         if (!(q_streams & (1 << s))) continue;
-        const int q_row0 = s == 0 ? 0 : row1, q_len = s == 0 ? g.len0 : g.len1;
         const int ss = cross ? 1 - s : s;
-        const int s_row0 = ss == 0 ? 0 : row1, s_len = ss == 0 ? g.len0 : g.len1;
-        attn_small_kernel<<<g.N, 128, 0, stream>>>(w.qf, w.kf, w.vf, q_row0, q_len, s_row0, s_len, g.N, 1e-6f, w.aoh,
-                                                    x3 ? w.aol : nullptr);
+        jobs.job[nj++] = SmallAttnJob{s == 0 ? 0 : row1, s == 0 ? g.len0 : g.len1, ss == 0 ? 0 : row1,
+                                      ss == 0 ? g.len0 : g.len1};
+      }
+      if (nj > 0) {
+        attn_small_kernel<<<dim3(g.N, nj), 128, 0, stream>>>(w.qf, w.kf, w.vf, jobs, g.N, 1e-6f, w.aoh, x3 ? w.aol : nullptr);
         count_launch();
       }
       OPB_CHECK_CUDA(cudaGetLastError());

@@ -315,6 +315,60 @@ __device__ __forceinline__ void store_planes32_v8(const float (&v)[32], __nv_bfl
     ptx::st_global_v8(lo + 16, l[8], l[9], l[10], l[11], l[12], l[13], l[14], l[15]);
   }
 }
+// ---- quad-transposed global access --------------------------------------------------------------------------
+// In the TMEM epilogues lane i owns row i, so a 32-byte store per lane touches 32 different 128-byte lines per
+// instruction; the LSU serialises on lines, and that -- not bytes -- bounds the LayerNorm epilogues.  A 4 x 4 transpose
+// of 32-byte items inside each quad of lanes (two xor-shuffle rounds) lets the four lanes of a quad write the four
+// sectors of ONE line per instruction: 8 lines per instruction instead of 32.
+// Before: it[j] = sector j of this lane's row.  After: it[k] = sector (lane % 4) of row (lane & ~3) + k.  Involution.
+__device__ __forceinline__ void quad_transpose(uint32_t (&it)[4][8], int lane) {
+  const bool b0 = lane & 1, b1 = lane & 2;
+#pragma unroll
+  for (int j = 0; j < 4; j += 2) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const uint32_t x = b0 ? it[j][r] : it[j + 1][r];
+      const uint32_t y = __shfl_xor_sync(0xffffffffu, x, 1);
+      if (b0) it[j][r] = y; else it[j + 1][r] = y;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const uint32_t x = b1 ? it[j][r] : it[j + 2][r];
+      const uint32_t y = __shfl_xor_sync(0xffffffffu, x, 2);
+      if (b1) it[j][r] = y; else it[j + 2][r] = y;
+    }
+  }
+}
+// 64 consecutive bf16 of this lane's row (4 sectors, already packed two per register) written through the quad
+// transpose.  `tile_row0` points at column c0 of the row of lane 0 of this warp; ld = row pitch in elements.
+__device__ __forceinline__ void store_row64_bf16_quad(uint32_t (&it)[4][8], __nv_bfloat16* warp_row0, long long ld, int lane) {
+  quad_transpose(it, lane);
+  __nv_bfloat16* base = warp_row0 + static_cast<long long>(lane & ~3) * ld + (lane & 3) * 16;
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    ptx::st_global_v8(base + k * ld, it[k][0], it[k][1], it[k][2], it[k][3], it[k][4], it[k][5], it[k][6], it[k][7]);
+}
+__device__ __forceinline__ void load_row64_bf16_quad(uint32_t (&it)[4][8], const __nv_bfloat16* warp_row0, long long ld, int lane) {
+  const __nv_bfloat16* base = warp_row0 + static_cast<long long>(lane & ~3) * ld + (lane & 3) * 16;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) ptx::ld_global_v8(base + k * ld, it[k]);
+  quad_transpose(it, lane);
+}
+// fp32 row slice -> packed bf16 hi / lo sectors (64 columns)
+__device__ __forceinline__ void pack_planes64(const float* x, uint32_t (&h)[4][8], uint32_t (&l)[4][8]) {
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    const __nv_bfloat162 hh = __floats2bfloat162_rn(x[2 * i], x[2 * i + 1]);
+    const float2 hf = __bfloat1622float2(hh);
+    const __nv_bfloat162 ll = __floats2bfloat162_rn(x[2 * i] - hf.x, x[2 * i + 1] - hf.y);
+    h[i >> 3][i & 7] = *reinterpret_cast<const uint32_t*>(&hh);
+    l[i >> 3][i & 7] = *reinterpret_cast<const uint32_t*>(&ll);
+  }
+}
+
 // 32 consecutive fp32 values of one row with 256-bit stores (dst 32-byte aligned)
 __device__ __forceinline__ void store_f32x32_v8(const float (&v)[32], float* dst) {
 #pragma unroll

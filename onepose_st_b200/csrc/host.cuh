@@ -125,7 +125,10 @@ int launch_gemm(const GemmPlan& plan, const typename Epi::Params& ep, cudaStream
   }
   int grid = num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
-  if (plan.num_tiles < grid) grid = plan.num_tiles;
+  // the fewest CTAs that finish in the same number of tile waves: SMs a launch cannot use anyway stay free for
+  // kernels of the other streams in flight (pipeline.StreamPipeline)
+  const int waves = (plan.num_tiles + grid - 1) / grid;
+  grid = (plan.num_tiles + waves - 1) / waves;
   if (long long* tr = next_trace_slot(grid)) {
     GemmPlan traced = plan;
     traced.trace = tr;

@@ -8,6 +8,8 @@ import logging
 import math
 from math import log
 
+import threading
+
 import torch
 import torch.nn as nn
 
@@ -153,6 +155,10 @@ class CoarseMatching(nn.Module):
         self.precision = ops.PREC_BF16X3
 
     def forward(self, feat_db_3d, feat_query, data, mask_query=None):
+        self.finish(self.launch(feat_db_3d, feat_query, data, mask_query), data)
+
+    def launch(self, feat_db_3d, feat_query, data, mask_query=None) -> "ops.CoarseLaunch":
+        """Enqueue the matching kernels (no host sync; needs data['q_hw_c'])."""
         if self.training:
             raise NotImplementedError("training-time coarse matching (GT padding) is out of scope of the inference path")
         if "mask0" in data:
@@ -162,10 +168,15 @@ class CoarseMatching(nn.Module):
         hc, wc = int(data["q_hw_c"][0]), int(data["q_hw_c"][1])
         scale = 1.0 / (C * (self.temperature + 1e-4))  # (a/sqrt C).(b/sqrt C) / (T + 1e-4)
         with self.profiler.record_function("LoFTR/coarse-matching/get_coarse_match"):
-            b_ids, i_ids, j_ids, mconf, conf = ops.coarse_match(
+            return ops.coarse_match_launch(
                 feat_db_3d, feat_query, scale=scale, thr=self.thr, border_rm=self.border_rm, border_mode=0, grid_a=None,
                 grid_b=(hc, wc), mask_b=mask_query, mask_fill=0, materialize_conf=self.materialize_conf_matrix,
                 precision=self.precision, planes=planes)
+
+    def finish(self, handle: "ops.CoarseLaunch", data, copy: bool = False):
+        """Read the match count (the forward's host sync) and fill the reference's coarse-level ``data`` keys."""
+        wc = int(data["q_hw_c"][1])
+        b_ids, i_ids, j_ids, mconf, conf = ops.coarse_match_finish(handle, copy=copy)
         if conf is not None:
             data.update({"conf_matrix": conf})
         scale_c = data["q_hw_i"][0] / data["q_hw_c"][0]
@@ -282,6 +293,7 @@ class OnePosePlus_model(nn.Module):
                 for p in self.backbone.parameters():
                     p.requires_grad = False
         self._kpt_cache = None  # (key, encoded descriptors): the 3D model is fixed across a sequence
+        self._graphs = {}       # CUDA graphs of the head, see _graphed_head
 
     def _encode_3d(self, data):
         desc = data["descriptors3d_coarse_db"] if "descriptors3d_coarse_db" in data else data["descriptors3d_db"]
@@ -304,7 +316,68 @@ class OnePosePlus_model(nn.Module):
     def __getstate__(self):
         st = self.__dict__.copy()
         st["_kpt_cache"] = None
+        st["_graphs"] = {}
         return st
+
+    def _head(self, data, img, qmask):
+        """Backbone -> coarse LoFTR stack -> coarse matching kernels: everything before the forward's host sync.
+        Returns (coarse launch handle, fine feature map, (hc, wc)); sets data['q_hw_c']."""
+        feat_c, feat_f = self.backbone(img)
+        data.update({"q_hw_c": feat_c.shape[2:]})
+        n, c, hc, wc = feat_c.shape
+        # 'n c h w -> n (h w) c' (+ PE) happens inside the transformer's stage-in kernel
+        q2d = feat_c.flatten(2).permute(0, 2, 1)
+        add2d = self.dense_pos_encoding.token_table(hc, wc) if self.dense_pos_encoding is not None else None
+        desc3d = self._encode_3d(data)
+        # the coarse features are consumed by CoarseMatching only: hand them over as bf16 planes
+        planes = self.loftr_coarse(desc3d, q2d, query_mask=qmask, _add2d=add2d, _planes_only=True)
+        return self.coarse_matching.launch(planes, None, data, mask_query=qmask), feat_f, feat_c.shape[2:]
+
+    # ---- CUDA graph of the head --------------------------------------------------------------------------------
+    # The head is ~85 kernel launches of fixed shape for a given (image size, batch, 3D model): with ``cuda_graph``
+    # on it is captured once per (CUDA stream, key) and replayed as ONE launch, which is what keeps the host ahead of
+    # the GPU when several forwards are in flight (pipeline.StreamPipeline).  Opt-in: a replay reuses static buffers
+    # and assumes the weights are not modified in place between forwards.
+    cuda_graph = False
+    _capture_lock = threading.Lock()
+    _graph_serial = 0
+
+    def _graphed_head(self, data, img):
+        kp = data["keypoints3d"]
+        desc = data["descriptors3d_coarse_db"] if "descriptors3d_coarse_db" in data else data["descriptors3d_db"]
+        key = (torch.cuda.current_stream(img.device).cuda_stream, img.device.index, tuple(img.shape), kp.data_ptr(), kp._version, tuple(kp.shape),
+               tuple(kp.stride()), desc.data_ptr(), desc._version, tuple(desc.shape), tuple(desc.stride()),
+               self.coarse_matching.precision, getattr(self.loftr_coarse, "precision", ops.PREC_BF16X3),
+               torch.backends.cudnn.allow_tf32,
+               self.coarse_matching.materialize_conf_matrix)
+        def cache_ids():  # tensors the captured kernels read by address besides the weights
+            c0, k0 = self.loftr_coarse.__dict__.get("_stream0_cache"), self._kpt_cache
+            return (None if c0 is None else c0[1].data_ptr(), None if k0 is None else k0[1].data_ptr())
+
+        ent = self._graphs.get(key)
+        if ent is not None and ent[5] != cache_ids():
+            ent = None  # another 3D model was matched in between and the per-sequence caches were rebuilt
+        if ent is None:
+            static_img = torch.empty_like(img, memory_format=torch.contiguous_format)
+            static_img.copy_(img)
+            scratch = dict(data)
+            self._head(scratch, static_img, None)  # eager run: builds every cache / workspace / function attribute
+            torch.cuda.current_stream(img.device).synchronize()
+            with OnePosePlus_model._capture_lock:
+                g = torch.cuda.CUDAGraph()
+                scratch = dict(data)
+                OnePosePlus_model._graph_serial += 1
+                with ops.workspaces.scope(("graph", OnePosePlus_model._graph_serial)), \
+                        torch.cuda.graph(g, capture_error_mode="thread_local"):
+                    handle, feat_f, hw_c = self._head(scratch, static_img, None)
+            ent = (g, static_img, handle, feat_f, tuple(hw_c), cache_ids())
+            if len(self._graphs) >= 16:
+                self._graphs.clear()
+            self._graphs[key] = ent
+        g, static_img, handle, feat_f, hw_c, _ = ent
+        static_img.copy_(img, non_blocking=True)
+        g.replay()
+        return handle, feat_f, torch.Size(hw_c)
 
     @torch.no_grad()
     def forward(self, data):
@@ -312,17 +385,15 @@ class OnePosePlus_model(nn.Module):
             raise NotImplementedError("onepose_st_b200 implements the inference forward only; call .eval()")
         img = data["query_image"]
         data.update({"bs": img.size(0), "q_hw_i": img.shape[2:]})
-        feat_c, feat_f = self.backbone(img)
-        data.update({"q_hw_c": feat_c.shape[2:], "q_hw_f": feat_f.shape[2:]})
-        n, c, hc, wc = feat_c.shape
-        # 'n c h w -> n (h w) c' (+ PE) happens inside the transformer's stage-in kernel
-        q2d = feat_c.flatten(2).permute(0, 2, 1)
-        add2d = self.dense_pos_encoding.token_table(hc, wc) if self.dense_pos_encoding is not None else None
-        desc3d = self._encode_3d(data)
         qmask = data["query_image_mask"].flatten(-2) if "query_image_mask" in data else None
-        # the coarse features are consumed by CoarseMatching only: hand them over as bf16 planes
-        planes = self.loftr_coarse(desc3d, q2d, query_mask=qmask, _add2d=add2d, _planes_only=True)
-        self.coarse_matching(planes, None, data, mask_query=qmask)
+        if self.cuda_graph and qmask is None and img.is_cuda:
+            handle, feat_f, hw_c = self._graphed_head(data, img)
+            data.update({"q_hw_c": hw_c, "q_hw_f": feat_f.shape[2:]})
+            self.coarse_matching.finish(handle, data, copy=True)
+        else:
+            handle, feat_f, hw_c = self._head(data, img, qmask)
+            data.update({"q_hw_f": feat_f.shape[2:]})
+            self.coarse_matching.finish(handle, data)
         if not self.config["fine_matching"]["enable"]:
             data.update({"mkpts_3d_db": data["mkpts_3d_db"], "mkpts_query_f": data["mkpts_query_c"]})
             return

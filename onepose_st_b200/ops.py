@@ -1,6 +1,7 @@
 """Thin Python wrappers over the C-ABI in include/opb200.h: they only extract pointers, sizes and
 strides from torch tensors, own the workspaces, and raise on any non-zero status.  No math here."""
 import ctypes
+import threading
 from typing import List, Optional, Sequence
 
 import torch
@@ -30,10 +31,33 @@ class _Workspaces:
 
     def __init__(self):
         self._bufs = {}
+        self._tl = threading.local()
+
+    def scope(self, name):
+        """Context manager: workspaces requested inside belong to ``name`` instead of to the current stream.  A CUDA
+        graph capture uses it so that every graph owns its scratch (torch captures all graphs on one shared side
+        stream, and graphs replayed concurrently on different streams must not share workspaces)."""
+        ws = self
+
+        class _Scope:
+            def __enter__(self_):
+                self_.prev = getattr(ws._tl, "scope", None)
+                ws._tl.scope = name
+
+            def __exit__(self_, *exc):
+                ws._tl.scope = self_.prev
+                return False
+        return _Scope()
+
+    def drop_scope(self, name) -> None:
+        for k in [k for k in self._bufs if k[1] == ("scope", name)]:
+            del self._bufs[k]
 
     def get(self, device, tag: str, nbytes: int) -> torch.Tensor:
-        # one buffer per (device, stream, tag): forwards in flight on different streams never share scratch
-        key = (device.index, torch.cuda.current_stream(device).cuda_stream, tag)
+        # one buffer per (device, stream | scope, tag): forwards in flight on different streams never share scratch
+        sc = getattr(self._tl, "scope", None)
+        owner = ("scope", sc) if sc is not None else torch.cuda.current_stream(device).cuda_stream
+        key = (device.index, owner, tag)
         buf = self._bufs.get(key)
         if buf is None or buf.numel() < nbytes:
             buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
@@ -156,15 +180,20 @@ def transformer(packed_layers: Sequence[torch.Tensor], layer_kinds: Sequence[int
     return out0, out1
 
 
-def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, thr: float, border_rm: int,
-                 border_mode: int, grid_a, grid_b, mask_a: Optional[torch.Tensor] = None,
-                 mask_b: Optional[torch.Tensor] = None, mask_fill: int = 0, valid_hw: Optional[torch.Tensor] = None,
-                 materialize_conf: bool = False, precision: int = PREC_BF16X3, algo: int = 0,
-                 planes: Optional[FeaturePlanes] = None):
-    """Dual-softmax + mutual-NN selection.  Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None).
-    With ``planes`` (from ``transformer(..., planes_only=True)``) feat_a / feat_b are ignored.
+class CoarseLaunch:
+    """Everything ``coarse_match_launch`` enqueued and allocated; ``coarse_match_finish`` turns it into results."""
 
-    One host sync (reading the match count) -- the reference syncs at the same point (torch.where)."""
+    def __init__(self, outs, cnt, conf, cap, retry):
+        self.outs, self.cnt, self.conf, self.cap, self.retry = outs, cnt, conf, cap, retry
+
+
+def coarse_match_launch(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, thr: float, border_rm: int,
+                        border_mode: int, grid_a, grid_b, mask_a: Optional[torch.Tensor] = None,
+                        mask_b: Optional[torch.Tensor] = None, mask_fill: int = 0,
+                        valid_hw: Optional[torch.Tensor] = None, materialize_conf: bool = False,
+                        precision: int = PREC_BF16X3, algo: int = 0, planes: Optional[FeaturePlanes] = None) -> CoarseLaunch:
+    """Enqueues the dual-softmax + mutual-NN kernels on the current stream; no host synchronisation (capturable in
+    a CUDA graph).  With ``planes`` (from ``transformer(..., planes_only=True)``) feat_a / feat_b are ignored."""
     if planes is not None:
         n, L, S, C = planes.n, planes.len0, planes.len1, planes.c
         if planes.padded != ((L + 127) // 128 * 128, (S + 127) // 128 * 128):
@@ -213,18 +242,38 @@ def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, th
                                _lib.ptr(cnt), _lib.ptr(conf), _lib.ptr(ws), _c_sz(ws.numel()), int(precision), int(algo),
                                _lib.stream_ptr())
     _lib.check(st, "opb200_coarse_match")
-    m, overflow, rerun = cnt.tolist()
+    retry = dict(feat_a=feat_a, feat_b=feat_b, scale=scale, thr=thr, border_rm=border_rm, border_mode=border_mode,
+                 grid_a=grid_a, grid_b=grid_b, mask_a=mask_a, mask_b=mask_b, mask_fill=mask_fill, valid_hw=valid_hw,
+                 materialize_conf=materialize_conf, precision=precision, planes=planes)
+    return CoarseLaunch((b_ids, i_ids, j_ids, mconf), cnt, conf, cap, retry)
+
+
+def coarse_match_finish(h: CoarseLaunch, copy: bool = False):
+    """The one host sync of the matcher (reading the match count; the reference syncs at the same point through
+    torch.where).  Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None); ``copy`` detaches the results from the
+    launch's buffers (needed when those are the static buffers of a CUDA graph)."""
+    m, overflow, rerun = h.cnt.tolist()
     if rerun:  # the single-pass statistics hit their dynamic-range guard: take the two-pass path
-        return coarse_match(feat_a, feat_b, scale=scale, thr=thr, border_rm=border_rm, border_mode=border_mode,
-                            grid_a=grid_a, grid_b=grid_b, mask_a=mask_a, mask_b=mask_b, mask_fill=mask_fill,
-                            valid_hw=valid_hw, materialize_conf=materialize_conf, precision=precision, algo=1, planes=planes)
+        kw = dict(h.retry)
+        a, b = kw.pop("feat_a"), kw.pop("feat_b")
+        return coarse_match(a, b, algo=1, **kw)
+    b_ids, i_ids, j_ids, mconf = h.outs
     if overflow:
         import os
         if os.environ.get("OPB200_DEBUG_OVERFLOW"):
-            print("DEBUG overflow: count", m, "cap", cap)
-            return b_ids[:min(m, cap)], i_ids[:min(m, cap)], j_ids[:min(m, cap)], mconf[:min(m, cap)], conf
+            print("DEBUG overflow: count", m, "cap", h.cap)
+            m = min(m, h.cap)
+            return b_ids[:m], i_ids[:m], j_ids[:m], mconf[:m], h.conf
         raise _lib.Opb200Error("coarse_match: candidate/match buffer overflow (internal capacity bound violated)")
-    return b_ids[:m], i_ids[:m], j_ids[:m], mconf[:m], conf
+    if copy:
+        return b_ids[:m].clone(), i_ids[:m].clone(), j_ids[:m].clone(), mconf[:m].clone(), h.conf
+    return b_ids[:m], i_ids[:m], j_ids[:m], mconf[:m], h.conf
+
+
+def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, **kw):
+    """Dual-softmax + mutual-NN selection: ``coarse_match_launch`` + ``coarse_match_finish``.
+    Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None)."""
+    return coarse_match_finish(coarse_match_launch(feat_a, feat_b, **kw))
 
 
 def _err_flag(dev) -> torch.Tensor:

@@ -32,6 +32,19 @@ class StreamPipeline:
         self.n_streams = n_streams
         self.streams = [torch.cuda.Stream(device=self.device) for _ in range(n_streams)]
 
+    def warm(self, fn: Callable) -> None:
+        """Run ``fn()`` once on every worker stream, one after the other, from the calling thread (builds per-stream
+        state such as workspaces and CUDA graphs outside any timed region)."""
+        for s in self.streams if self.n_streams > 1 else []:
+            s.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(s), torch.no_grad():
+                fn()
+            s.synchronize()
+        if self.n_streams == 1:
+            with torch.no_grad():
+                fn()
+            torch.cuda.current_stream(self.device).synchronize()
+
     def map(self, fn: Callable, items: Iterable) -> List:
         items = list(items)
         results = [None] * len(items)

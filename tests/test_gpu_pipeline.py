@@ -78,3 +78,39 @@ def test_broadcast_3d_model_reuses_first_self_layer():
         assert torch.equal(plain["j_ids"], d["j_ids"]) and plain["mconf"].numel() > 50
         assert (plain["mconf"] - d["mconf"]).abs().max().item() < 1e-4   # fp32 round trip of the cached stream
         assert (sharding.rows_onepose(plain) - sharding.rows_onepose(d)).abs().max().item() < 1e-3
+
+
+def test_cuda_graph_head_matches_eager():
+    """The forward with its head replayed as a CUDA graph (model.cuda_graph = True) against the eager forward: same
+    matches for several frames through the same graph, and after switching to another 3D model and back."""
+    from onepose_st_b200 import synthetic
+    from onepose_st_b200.onepose_plus import OnePosePlus_model
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    model = OnePosePlus_model(synthetic.onepose_plus_cfg()).eval()
+    model.load_state_dict(synthetic.calibrate_onepose_state_dict(model.state_dict()), strict=True)
+    model = model.to(dev)
+    B = 2
+    seq_a = synthetic.make_onepose_sequence(model, 1500, 3 * B, 256, 256, 300, device=dev)
+    seq_b = synthetic.make_onepose_sequence(model, 1500, B, 256, 256, 300, seed=77, device=dev)
+
+    def run(seq, k):
+        f = lambda t: t.expand(B, -1, -1)
+        data = {"keypoints3d": f(seq["keypoints3d"]), "descriptors3d_db": f(seq["descriptors3d_db"]),
+                "descriptors3d_coarse_db": f(seq["descriptors3d_coarse_db"]), "query_image": seq["frames"][k * B: (k + 1) * B]}
+        model(data)
+        return {k_: data[k_].clone() for k_ in ("b_ids", "i_ids", "j_ids", "mconf", "mkpts_query_f", "mkpts_3d_db")}
+
+    order = [(seq_a, 0), (seq_a, 1), (seq_b, 0), (seq_a, 2), (seq_a, 0)]
+    with torch.no_grad():
+        model.cuda_graph = False
+        want = [run(s, k) for s, k in order]
+        model.cuda_graph = True
+        got = [run(s, k) for s, k in order]
+        assert len(model._graphs) >= 2
+    for w, g in zip(want, got):
+        assert w["mconf"].numel() > 50
+        for k_ in ("b_ids", "i_ids", "j_ids"):
+            assert torch.equal(w[k_], g[k_]), k_
+        assert (w["mconf"] - g["mconf"]).abs().max().item() < 1e-5
+        assert (w["mkpts_query_f"] - g["mkpts_query_f"]).abs().max().item() < 1e-3
