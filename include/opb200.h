@@ -34,6 +34,8 @@ int opb200_version(void);
 const char* opb200_last_error(void);
 /* Number of CUDA kernels this library has launched in this process (bench.py's gpu_launches evidence). */
 long long opb200_launch_count(void);
+/* Adds n to that counter: a caller that replays a CUDA graph of n captured launches of this library accounts for them here. */
+void opb200_launch_count_add(long long n);
 
 /* fp32 matrix with element (r,c) at x[r*stride_r + c*stride_c] -> bf16 hi/lo planes [rows, cols]
  * (lo and f32_copy nullable).  Operand preparation for every tensor-core product below. */

@@ -81,3 +81,8 @@ def ptr(t):
 def stream_ptr():
     import torch
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def launch_count_add(n: int) -> None:
+    """Account for ``n`` kernels of this library launched by a CUDA-graph replay."""
+    lib().opb200_launch_count_add(ctypes.c_longlong(int(n)))

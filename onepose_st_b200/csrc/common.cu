@@ -281,6 +281,8 @@ int opb200_split_planes(const float* x, int64_t stride_r, int64_t stride_c, int 
                       static_cast<__nv_bfloat16*>(lo), f32_copy, cols, static_cast<cudaStream_t>(stream));
 }
 
+void opb200_launch_count_add(long long n) { opb::count_launch(static_cast<int>(n)); }
+
 int opb200_debug_trace(void* buffer, long long bytes) {
   // buffer: device memory, zero-filled by the caller; launch i of gemm_kernel (in host launch order) records
   // [148 CTAs][32 tiles][4] int64 clock64() stamps at slot i.  buffer == NULL disarms.  Returns the slot count.

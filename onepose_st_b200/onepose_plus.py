@@ -13,7 +13,7 @@ import threading
 import torch
 import torch.nn as nn
 
-from . import ops
+from . import _lib, ops
 from .nn_common import (LinearAttention, LoFTREncoderLayer, PositionEncodingSine, ResNetFPN_8_2, _TransformerBase,
                         fine_expectation)
 
@@ -367,16 +367,19 @@ class OnePosePlus_model(nn.Module):
                 g = torch.cuda.CUDAGraph()
                 scratch = dict(data)
                 OnePosePlus_model._graph_serial += 1
+                l0 = _lib.launch_count()
                 with ops.workspaces.scope(("graph", OnePosePlus_model._graph_serial)), \
                         torch.cuda.graph(g, capture_error_mode="thread_local"):
                     handle, feat_f, hw_c = self._head(scratch, static_img, None)
-            ent = (g, static_img, handle, feat_f, tuple(hw_c), cache_ids())
+                n_launch = _lib.launch_count() - l0  # library kernels inside one replay
+            ent = (g, static_img, handle, feat_f, tuple(hw_c), cache_ids(), n_launch)
             if len(self._graphs) >= 16:
                 self._graphs.clear()
             self._graphs[key] = ent
-        g, static_img, handle, feat_f, hw_c, _ = ent
+        g, static_img, handle, feat_f, hw_c, _, n_launch = ent
         static_img.copy_(img, non_blocking=True)
         g.replay()
+        _lib.launch_count_add(n_launch)
         return handle, feat_f, torch.Size(hw_c)
 
     @torch.no_grad()

@@ -63,9 +63,30 @@ def trace_conv(a):
     report(buf.view(-1, 148, 32, 4).cpu().double(), cnt, [s_[0] for s_ in shapes], len(shapes))
 
 
+def trace_fine(a):
+    tr = LocalFeatureTransformer(synthetic.onepose_plus_cfg()["loftr_fine"]).cuda().eval()
+    M = a.matches
+    f3 = torch.randn(M, 128, 1, device="cuda")
+    win = torch.randn(M, 25, 128, device="cuda")
+    with torch.no_grad():
+        for _ in range(2):
+            tr(f3, win)
+        torch.cuda.synchronize()
+        slot = 148 * 32 * 4
+        buf = torch.zeros(16 * slot, dtype=torch.int64, device="cuda")
+        lib = _lib.lib()
+        n = lib.opb200_debug_trace(ctypes.c_void_p(buf.data_ptr()), ctypes.c_longlong(buf.numel() * 8))
+        tr(f3, win)
+        torch.cuda.synchronize()
+        lib.opb200_debug_trace(None, ctypes.c_longlong(0))
+    report(buf.view(-1, 148, 32, 4).cpu().double(), n, ["QKV128", "MERGE+LN128", "MLP1+ReLU128", "MLP2+LN+res128"], 8)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--conv", action="store_true")
+    ap.add_argument("--fine", action="store_true")
+    ap.add_argument("--matches", type=int, default=5300)
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--points", type=int, default=8000)
     ap.add_argument("--grid", type=int, default=64)
@@ -74,6 +95,8 @@ def main():
     torch.manual_seed(0)
     if a.conv:
         return trace_conv(a)
+    if a.fine:
+        return trace_fine(a)
     tr = LocalFeatureTransformer(synthetic.onepose_plus_cfg()["loftr_coarse"]).cuda().eval()
     d3 = torch.randn(a.batch, 256, a.points, device="cuda")
     d2 = torch.randn(a.batch, a.grid * a.grid, 256, device="cuda")
