@@ -180,6 +180,134 @@ __global__ void __launch_bounds__(128) stem_conv7x7_s2_kernel(const float* __res
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// The same stem on the tensor cores (fp16 operands, fp32 accumulation: the TF32-grade precision of the other
+// backbone convolutions).  GEMM view: 128 output pixels (8 x 16) x 128 channels x K = 49 taps padded to 64.
+// The A tile is an im2col of the shared-memory image patch that the threads write straight into the 128-byte-swizzled
+// K-major layout tcgen05.mma reads (generic-proxy stores + fence.proxy.async); B = the weights, built once per CTA.
+// Persistent CTAs (4 per SM: TMEM 128 columns each); per tile: patch -> A -> 4 MMAs -> epilogue (bias, ReLU, fp16,
+// quad-transposed 128-byte-line stores).  Write-bound: 256 bytes per output pixel.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) stem_tc_kernel(const float* __restrict__ img, const float* __restrict__ w,
+                                                      const float* __restrict__ bias, int H, int W, int Ho, int Wo,
+                                                      int tiles_x, int tiles_y, int num_tiles, __half* __restrict__ out) {
+  __shared__ __align__(1024) uint8_t a_tile[128 * 128];
+  __shared__ __align__(1024) uint8_t b_tile[128 * 128];
+  __shared__ float patch[21][40];
+  __shared__ __align__(8) uint64_t mma_bar;
+  __shared__ uint32_t tmem_slot;
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  if (t == 0) {
+    ptx::mbar_init(&mma_bar, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 0) {
+    ptx::tmem_alloc(&tmem_slot, 128);
+    ptx::tmem_relinquish();
+  }
+  {  // B row n = output channel t: 64 K values (49 taps + zeros), 16-byte chunk c stored at chunk position c ^ (n % 8)
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      uint32_t p[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k0 = 8 * c + 2 * j, k1 = k0 + 1;
+        const float f0 = k0 < 49 ? __ldg(w + k0 * 128 + t) : 0.f;
+        const float f1 = k1 < 49 ? __ldg(w + k1 * 128 + t) : 0.f;
+        const __half2 hh = __floats2half2_rn(f0, f1);
+        p[j] = *reinterpret_cast<const uint32_t*>(&hh);
+      }
+      *reinterpret_cast<uint4*>(b_tile + t * 128 + ((c ^ (t & 7)) << 4)) = make_uint4(p[0], p[1], p[2], p[3]);
+    }
+  }
+  ptx::fence_proxy_async();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  constexpr uint32_t idesc = ptx::make_idesc_f16(128, 128);
+  const int py = t >> 4, px = t & 15;  // this thread's output pixel inside the 8 x 16 tile (GEMM row t)
+  float bv[4];  // bias is re-read per 4 columns below; keep nothing resident
+  (void)bv;
+  uint32_t phase = 0;
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int n = tile / (tiles_x * tiles_y);
+    const int r = tile - n * tiles_x * tiles_y;
+    const int ty = r / tiles_x, tx = r - ty * tiles_x;
+    const int oy0 = ty * 8, ox0 = tx * 16;
+    const int iy0 = oy0 * 2 - 3, ix0 = ox0 * 2 - 3;
+    const float* im = img + static_cast<long long>(n) * H * W;
+    for (int i = t; i < 21 * 37; i += 128) {
+      const int yy = i / 37, xx = i - yy * 37;
+      const int y = iy0 + yy, x = ix0 + xx;
+      patch[yy][xx] = (y >= 0 && y < H && x >= 0 && x < W) ? __ldg(im + static_cast<long long>(y) * W + x) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      uint32_t p[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k0 = 8 * c + 2 * j, k1 = k0 + 1;
+        const float f0 = k0 < 49 ? patch[2 * py + k0 / 7][2 * px + k0 % 7] : 0.f;
+        const float f1 = k1 < 49 ? patch[2 * py + k1 / 7][2 * px + k1 % 7] : 0.f;
+        const __half2 hh = __floats2half2_rn(f0, f1);
+        p[j] = *reinterpret_cast<const uint32_t*>(&hh);
+      }
+      *reinterpret_cast<uint4*>(a_tile + t * 128 + ((c ^ (t & 7)) << 4)) = make_uint4(p[0], p[1], p[2], p[3]);
+    }
+    ptx::fence_proxy_async();
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (t == 0) {
+      ptx::tc_fence_after();
+      const uint64_t a_desc = ptx::make_desc_sw128(ptx::smem_u32(a_tile));
+      const uint64_t b_desc = ptx::make_desc_sw128(ptx::smem_u32(b_tile));
+#pragma unroll
+      for (int k = 0; k < 4; ++k) ptx::mma_bf16(tmem_base, a_desc + 2 * k, b_desc + 2 * k, idesc, k != 0);
+      ptx::mma_commit(&mma_bar);
+    }
+    ptx::mbar_wait(&mma_bar, phase);
+    phase ^= 1;
+    ptx::tc_fence_after();
+    // epilogue: lane owns GEMM row 32 * warp + lane; stores go through the quad transpose (one 128-byte line per quad)
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      uint32_t r0[32], r1[32];
+      ptx::tmem_ld32(taddr + half * 64, r0);
+      ptx::tmem_ld32(taddr + half * 64 + 32, r1);
+      ptx::tmem_ld_wait();
+      uint32_t it[4][8];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int c0 = half * 64 + 2 * i;
+        const float2 b2 = __ldg(reinterpret_cast<const float2*>(bias + c0));
+        const float v0 = fmaxf(__uint_as_float(i < 16 ? r0[2 * i] : r1[2 * i - 32]) + b2.x, 0.f);
+        const float v1 = fmaxf(__uint_as_float(i < 16 ? r0[2 * i + 1] : r1[2 * i - 31]) + b2.y, 0.f);
+        const __half2 hh = __floats2half2_rn(v0, v1);
+        it[i >> 3][i & 7] = *reinterpret_cast<const uint32_t*>(&hh);
+      }
+      quad_transpose(it, lane);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int rr = warp * 32 + (lane & ~3) + k;  // GEMM row whose sector (lane % 4) this lane now holds
+        const int oy = oy0 + (rr >> 4), ox = ox0 + (rr & 15);
+        if (oy < Ho && ox < Wo) {
+          __half* dst = out + ((static_cast<long long>(n) * Ho + oy) * Wo + ox) * 128 + half * 64 + (lane & 3) * 16;
+          ptx::st_global_v8(dst, it[k][0], it[k][1], it[k][2], it[k][3], it[k][4], it[k][5], it[k][6], it[k][7]);
+        }
+      }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();  // TMEM accumulator, A tile and patch are free for the next tile
+  }
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 128);
+  }
+}
+
 }  // namespace opb
 
 using namespace opb;
@@ -243,8 +371,12 @@ int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight
   OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(out_f16) & 31) == 0, "output must be 32-byte aligned");
   const int Ho = (H + 2 * 3 - 7) / 2 + 1, Wo = (W + 2 * 3 - 7) / 2 + 1;
   dim3 grid((Wo + 15) / 16, (Ho + 15) / 16, n_batch);
-  stem_conv7x7_s2_kernel<128, __half><<<grid, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
-      image, weight_tap_major, bias, H, W, Ho, Wo, static_cast<__half*>(out_f16));
+  (void)grid;
+  const int tiles_x = (Wo + 15) / 16, tiles_y = (Ho + 7) / 8;
+  const int num_tiles = n_batch * tiles_x * tiles_y;
+  const int ctas = num_tiles < 4 * num_sms() ? num_tiles : 4 * num_sms();
+  stem_tc_kernel<<<ctas, 128, 12 * 1024 /* unused: caps residency at 4 CTAs per SM = 4 x 128 TMEM columns */, static_cast<cudaStream_t>(stream_)>>>(image, weight_tap_major, bias, H, W, Ho, Wo, tiles_x,
+                                                                      tiles_y, num_tiles, static_cast<__half*>(out_f16));
   count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;

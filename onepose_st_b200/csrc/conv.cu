@@ -51,10 +51,6 @@ struct UpTaps {  // the four source pixels (element offsets) and weights of one 
   float w00, w01, w10, w11;
 };
 
-__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
-  return (1u << 4) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
-}
-
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const void* tmap, uint64_t* bar, int c0, int c1, int c2, int c3) {
   asm volatile(
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
@@ -217,7 +213,7 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc = make_idesc_f16(BLOCK_M, BN);
+    constexpr uint32_t idesc = ptx::make_idesc_f16(BLOCK_M, BN);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;

@@ -309,7 +309,7 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual str
 // ------------------------------------------------------------------------------------------------
 // KV reduction for big groups (coarse level: C = 256, H = 8, D = 32)
 // ------------------------------------------------------------------------------------------------
-constexpr int KV_ROWS_PER_BLOCK = 64;
+constexpr int KV_ROWS_PER_BLOCK = 128;
 constexpr int KV_REC = 33;  // per (head, d): 32 KV values + Ksum
 
 struct GroupTable {  // passed by value to small kernels
@@ -318,10 +318,12 @@ struct GroupTable {  // passed by value to small kernels
   int len[64];
 };
 
-// grid = (max_chunks, G), block = 256: thread t -> head t/32, d = t%32; accumulates KV[h][d][0..31] and Ksum[h][d]
-// over the chunk's rows.  Rows are staged 8 at a time through a cp.async double buffer (coalesced 16-byte
-// copies); partials are written j-major ([33][256]) so that both this store and the reduce are coalesced.
-__global__ void __launch_bounds__(256) kv_partial_kernel(const float* __restrict__ kphi, const float* __restrict__ v,
+// grid = (max_chunks, G), block = 128: thread t -> head t/16, d pair (2*(t%16), +1); accumulates KV[h][d][0..31] and
+// Ksum[h][d] of its two d over the chunk's rows: 64 FMAs per 8 broadcast 16-byte V reads + one 8-byte K read, so the
+// FMA pipe is the bound.  Rows are staged 8 at a time through a cp.async double buffer (coalesced 16-byte copies; a third slab
+// measured slower: occupancy);
+// partials are written j-major ([33][256]) so that both this store and the reduce are coalesced.
+__global__ void __launch_bounds__(128) kv_partial_kernel(const float* __restrict__ kphi, const float* __restrict__ v,
                                                          GroupTable gt, unsigned long long group_sel,
                                                          float* __restrict__ partial, int max_chunks) {
   const int g = blockIdx.y;
@@ -334,19 +336,19 @@ __global__ void __launch_bounds__(256) kv_partial_kernel(const float* __restrict
   __shared__ __align__(16) float vs[2][8][256];
   __shared__ __align__(16) float ks[2][8][256];
   const int t = threadIdx.x;
-  const int h = t >> 5;
-  float acc[32];
+  const int h = t >> 4, d0 = (t & 15) * 2;
+  float acc0[32], acc1[32];
 #pragma unroll
-  for (int i = 0; i < 32; ++i) acc[i] = 0.f;
-  float ksum = 0.f;
+  for (int i = 0; i < 32; ++i) acc0[i] = acc1[i] = 0.f;
+  float ksum0 = 0.f, ksum1 = 0.f;
   const float* kbase = kphi + static_cast<long long>(gt.row_start[g] + r0) * 256;
   const float* vbase = v + static_cast<long long>(gt.row_start[g] + r0) * 256;
   const int nb = (nrows + 7) / 8;
-  auto issue = [&](int b) {  // 8 rows x 256 floats = 512 float4 per operand, 2 per thread
+  auto issue = [&](int b) {  // 8 rows x 256 floats = 512 float4 per operand, 4 per thread
     const int buf = b & 1;
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const int f4 = t + 256 * q;           // float4 index within the 8-row batch
+    for (int q = 0; q < 4; ++q) {
+      const int f4 = t + 128 * q;           // float4 index within the 8-row batch
       const int row = b * 8 + (f4 >> 6);
       if (row < nrows) {
         const long long off = static_cast<long long>(row) * 256 + (f4 & 63) * 4;
@@ -365,24 +367,29 @@ __global__ void __launch_bounds__(256) kv_partial_kernel(const float* __restrict
     const int buf = b & 1;
     const int nr = min(8, nrows - b * 8);
     for (int i = 0; i < nr; ++i) {
-      const float kk = ks[buf][i][t];
-      ksum += kk;
+      const float2 kk = *reinterpret_cast<const float2*>(&ks[buf][i][h * 32 + d0]);
+      ksum0 += kk.x;
+      ksum1 += kk.y;
       const float4* v4 = reinterpret_cast<const float4*>(&vs[buf][i][h * 32]);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float4 vv = v4[j];
-        acc[4 * j + 0] = fmaf(kk, vv.x, acc[4 * j + 0]);
-        acc[4 * j + 1] = fmaf(kk, vv.y, acc[4 * j + 1]);
-        acc[4 * j + 2] = fmaf(kk, vv.z, acc[4 * j + 2]);
-        acc[4 * j + 3] = fmaf(kk, vv.w, acc[4 * j + 3]);
+        acc0[4 * j + 0] = fmaf(kk.x, vv.x, acc0[4 * j + 0]);
+        acc0[4 * j + 1] = fmaf(kk.x, vv.y, acc0[4 * j + 1]);
+        acc0[4 * j + 2] = fmaf(kk.x, vv.z, acc0[4 * j + 2]);
+        acc0[4 * j + 3] = fmaf(kk.x, vv.w, acc0[4 * j + 3]);
+        acc1[4 * j + 0] = fmaf(kk.y, vv.x, acc1[4 * j + 0]);
+        acc1[4 * j + 1] = fmaf(kk.y, vv.y, acc1[4 * j + 1]);
+        acc1[4 * j + 2] = fmaf(kk.y, vv.z, acc1[4 * j + 2]);
+        acc1[4 * j + 3] = fmaf(kk.y, vv.w, acc1[4 * j + 3]);
       }
     }
     __syncthreads();
   }
-  float* out = partial + (static_cast<long long>(g) * max_chunks + chunk) * (KV_REC * 256) + t;
+  float2* out = reinterpret_cast<float2*>(partial + (static_cast<long long>(g) * max_chunks + chunk) * (KV_REC * 256) + h * 32 + d0);
 #pragma unroll
-  for (int i = 0; i < 32; ++i) out[i * 256] = acc[i];
-  out[32 * 256] = ksum;
+  for (int i = 0; i < 32; ++i) out[i * 128] = make_float2(acc0[i], acc1[i]);
+  out[32 * 128] = make_float2(ksum0, ksum1);
 }
 
 // grid = (33, G), block = 256 (thread t = head*32 + d).  Sums the chunk partials of record j = blockIdx.x in a
@@ -802,7 +809,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
         gt.len[i] = s == 0 ? g.len0 : g.len1;
         if (src_streams & (1 << s)) sel |= 1ull << i;
       }
-      kv_partial_kernel<<<dim3(g.max_chunks, g.G), 256, 0, stream>>>(w.kf, w.vf, gt, sel, w.kv_partial, g.max_chunks);
+      kv_partial_kernel<<<dim3(g.max_chunks, g.G), 128, 0, stream>>>(w.kf, w.vf, gt, sel, w.kv_partial, g.max_chunks);
       kv_pack_kernel<<<dim3(KV_REC, g.G), 256, 0, stream>>>(w.kv_partial, gt, sel, g.max_chunks, w.kvb_h, x3 ? w.kvb_l : nullptr);
       count_launch(2);
       OPB_CHECK_CUDA(cudaGetLastError());

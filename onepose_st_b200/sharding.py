@@ -108,18 +108,17 @@ def gather_matches(rows: torch.Tensor, counts: Sequence[int], n_units: int, grou
     cnt_all = torch.empty(world, max_units, dtype=torch.int64, device=dev)
     _all_gather(cnt_all, cnt, group)
     per_rank = cnt_all.sum(dim=1)
-    max_rows = int(per_rank.max().item())  # the one host sync of the gather
+    max_rows = int(per_rank.max().item())  # host sync 1: how far to pad
     padded = torch.zeros(max_rows, width, dtype=torch.float32, device=dev)
     padded[: rows.shape[0]] = rows
     rows_all = torch.empty(world, max_rows, width, dtype=torch.float32, device=dev)
     _all_gather(rows_all, padded, group)
-    # unit id of every (rank, row) slot; pad slots get n_units so they sort last
-    local_k = torch.arange(max_units, device=dev)
-    unit_of = torch.full((world, max_rows), n_units, dtype=torch.int64, device=dev)
-    for r in range(world):
-        ids = torch.repeat_interleave(local_k * world + r, cnt_all[r])
-        unit_of[r, : ids.numel()] = ids
-    order = torch.sort(unit_of.flatten(), stable=True).indices[: int(per_rank.sum().item())]
-    out_rows = rows_all.reshape(world * max_rows, width)[order]
+    # unit id of every real row, rank-major (the order the rows sit in rows_all once the padding is dropped):
+    # unit of (rank r, local position k) is k * world + r
+    unit_ids = (torch.arange(max_units, device=dev)[None, :] * world + torch.arange(world, device=dev)[:, None]).reshape(-1)
+    unit_of_row = torch.repeat_interleave(unit_ids, cnt_all.reshape(-1))  # host sync 2 (output size)
+    real = torch.arange(max_rows, device=dev)[None, :] < per_rank[:, None]
+    rows_rank_major = rows_all[real]  # [sum M, width]; same length as unit_of_row
+    order = torch.sort(unit_of_row, stable=True).indices
     counts_units = cnt_all.t().reshape(-1)[:n_units]  # [max_units, world] flattened = unit order
-    return out_rows, counts_units
+    return rows_rank_major[order], counts_units

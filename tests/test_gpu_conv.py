@@ -70,16 +70,26 @@ def test_conv_f16_vs_torch(n, H, W, cin, cout, k, stride, use_bias, use_res, act
         torch.backends.cudnn.allow_tf32 = old
 
 
-def test_stem_and_upsample_f16():
+@pytest.mark.parametrize("hw", [(96, 80), (104, 72), (512, 512)])
+def test_stem_and_upsample_f16(hw):
     from onepose_st_b200 import ops
     g = torch.Generator(device="cuda").manual_seed(7)
-    img = torch.rand(2, 1, 96, 80, device="cuda", generator=g)
+    img = torch.rand(2, 1, hw[0], hw[1], device="cuda", generator=g)
     w = torch.randn(128, 1, 7, 7, device="cuda", generator=g) * 0.1
     b = torch.randn(128, device="cuda", generator=g) * 0.1
     tap_major = w.reshape(128, 49).t().contiguous()
-    a32 = ops.stem_conv_relu(img, tap_major, b)                  # channels-last [N,C,H,W]
-    a16 = ops.stem_conv_relu_f16(img, tap_major, b)              # [N,H,W,C] fp16
-    assert torch.equal(a32.permute(0, 2, 3, 1).half(), a16)
+    a32 = ops.stem_conv_relu(img, tap_major, b)                  # fp32 CUDA-core kernel, channels-last [N,C,H,W]
+    a16 = ops.stem_conv_relu_f16(img, tap_major, b)              # tensor-core kernel (fp16 operands), [N,H,W,C] fp16
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        want32 = F.relu(F.conv2d(img, w, b, 2, 3)).permute(0, 2, 3, 1)
+        want16 = F.relu(F.conv2d(img.half().float(), w.half().float(), b, 2, 3)).permute(0, 2, 3, 1)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    assert (a32.permute(0, 2, 3, 1) - want32).abs().max().item() < 1e-5
+    assert (a16.float() - want16).abs().max().item() < 2e-3     # same fp16 operands: fp16 rounding of the O(1) output only
+    assert (a16.float() - want32).abs().max().item() < 5e-3     # TF32-grade w.r.t. the fp32 stem
     src = torch.randn(2, 12, 10, 208, device="cuda", generator=g).half()
     dst = torch.randn(2, 24, 20, 208, device="cuda", generator=g).half()
     want = dst.float() + F.interpolate(src.float().permute(0, 3, 1, 2), scale_factor=2.0, mode="bilinear",
