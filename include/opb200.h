@@ -177,6 +177,10 @@ int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels,
 int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride,
                            int cout_s, const float* bias, const void* res, const void* up, void* y16, float* y32, int act,
                            float slope, void* stream);
+/* Option of opb200_conv2d_nhwc_f16: run as clusters of two CTAs that multicast the weight slabs to each other (TMA
+ * multicast; halves the L2 -> SM weight traffic).  on = 1 / 0 sets it, on < 0 only queries; returns the previous
+ * setting.  Default off (no gain measured on B200, see csrc/conv.cu); also settable with OPB200_CONV_CLUSTER=1. */
+int opb200_conv_cluster(int on);
 /* fp16-output variant of opb200_stem_conv7x7_s2_relu_nhwc and fp16 variant of opb200_upsample2x_add_nhwc (C % 8 == 0). */
 int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight_tap_major, const float* bias, int n_batch,
                                          int H, int W, int Cout, void* out_f16, void* stream);

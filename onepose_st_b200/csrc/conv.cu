@@ -14,6 +14,7 @@
 // Both sub-tiles consume the same weight slab (MSUB = 2 halves the weight refetch per flop).
 // Warp roles as in gemm.cuh: warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2..17 epilogue
 // (bias + residual + ReLU / LeakyReLU, fp16 and/or fp32 NHWC stores, 32 bytes per lane per store).
+#include <cstdlib>
 #include <cuda_fp16.h>
 #include "host.cuh"
 #include "../../include/opb200.h"
@@ -140,7 +141,11 @@ __device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const Co
   }
 }
 
-template <int BN, int MSUB>
+// CL2: the kernel runs as clusters of two CTAs that walk their tiles in lockstep; every k-block each CTA fetches HALF of
+// the weight slab and multicasts it into both CTAs' shared memory, so the L2 -> SM weight traffic per flop halves
+// (the BN = 208 layers are bound by that fill, not by the tensor pipe).  A stage is refilled only after the MMAs of
+// both CTAs have read it (empty barriers count two multicast commits).
+template <int BN, int MSUB, bool CL2>
 __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant__ ConvPlan plan, const ConvEpi ep) {
   using Cfg = ConvCfg<BN, MSUB>;
   constexpr int STAGES = Cfg::STAGES;
@@ -160,7 +165,7 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
     ptx::prefetch_tmap(&plan.w_map);
     for (int s = 0; s < STAGES; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], CL2 ? 2 : 1);
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
@@ -173,26 +178,34 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
     ptx::tmem_relinquish();
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  if constexpr (CL2) ptx::cluster_sync();  // the peer's barriers are initialised before anything is multicast to them
+  else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   const int taps = plan.ksize * plan.ksize;
   const int tiles_per_img = plan.tiles_x * plan.tiles_y;
+  // tile walk: plain = blockIdx.x, += gridDim.x; CL2 = the pair takes tiles (2q, 2q + 1), q = pair, += number of pairs;
+  // both CTAs of a pair run the same number of iterations (a tile index past the end is a ghost: loads and MMAs on the
+  // last tile's data, no stores)
+  const int crank = CL2 ? static_cast<int>(ptx::cluster_ctarank()) : 0;
+  const int t_first = CL2 ? 2 * static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int t_step = CL2 ? static_cast<int>(gridDim.x) : static_cast<int>(gridDim.x);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < plan.num_tiles; t += gridDim.x) {
+      for (int tq = t_first; tq < plan.num_tiles; tq += t_step) {
+        const int t = min(tq + crank, plan.num_tiles - 1);
         const int n = t / tiles_per_img;
         const int r = t - n * tiles_per_img;
         const int ty = r / plan.tiles_x, tx = r - ty * plan.tiles_x;
         const int ix0 = tx * CONV_TW * plan.stride - plan.pad;
         const int iy0 = ty * (CONV_TH * MSUB) * plan.stride - plan.pad;
         if (plan.trace != nullptr) {
-          const int it = (t - blockIdx.x) / gridDim.x;
+          const int it = (tq - t_first) / t_step;
           if (it < kTraceTilesPerCta) plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 0] = clock64();
         }
         for (int tap = 0; tap < taps; ++tap) {
@@ -202,7 +215,12 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
             ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
             uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
             tma_load_4d(sa, &plan.x_map, &full_bar[stage], ch * BLOCK_K, ix0 + kx, iy0 + ky, n);
-            ptx::tma_load_2d(sa + Cfg::A_BYTES, &plan.w_map, &full_bar[stage], ch * BLOCK_K, tap * BN);
+            if constexpr (CL2) {
+              ptx::tma_load_2d_multicast(sa + Cfg::A_BYTES + crank * (Cfg::B_BYTES / 2), &plan.w_map, &full_bar[stage],
+                                         ch * BLOCK_K, tap * BN + crank * (BN / 2), 3);
+            } else {
+              ptx::tma_load_2d(sa + Cfg::A_BYTES, &plan.w_map, &full_bar[stage], ch * BLOCK_K, tap * BN);
+            }
             if (++stage == STAGES) {
               stage = 0;
               phase ^= 1;
@@ -218,7 +236,7 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
     uint32_t phase = 0;
     int it = 0;
     const int total_kb = taps * plan.nchunks;
-    for (int t = blockIdx.x; t < plan.num_tiles; t += gridDim.x, ++it) {
+    for (int tq = t_first; tq < plan.num_tiles; tq += t_step, ++it) {
       const int acc = it % Cfg::ACC_STAGES;
       const uint32_t acc_phase = (it / Cfg::ACC_STAGES) & 1;
       ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
@@ -240,7 +258,8 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
             for (int k = 0; k < nk; ++k)
               ptx::mma_bf16(d_tmem + s * BN, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
           }
-          ptx::mma_commit(&empty_bar[stage]);
+          if constexpr (CL2) ptx::mma_commit_multicast(&empty_bar[stage], 3);
+          else ptx::mma_commit(&empty_bar[stage]);
           if (kb == total_kb - 1) ptx::mma_commit(&tfull_bar[acc]);
         }
         __syncwarp();
@@ -265,14 +284,16 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
     const int row = quarter * 32 + lane;  // GEMM row inside the sub-tile
     const int hy = row / CONV_TW, wx = row - hy * CONV_TW;
     int it = 0;
-    for (int t = blockIdx.x; t < plan.num_tiles; t += gridDim.x, ++it) {
+    for (int tq = t_first; tq < plan.num_tiles; tq += t_step, ++it) {
       const int acc = it % Cfg::ACC_STAGES;
       const uint32_t acc_phase = (it / Cfg::ACC_STAGES) & 1;
+      const bool ghost = tq + crank >= plan.num_tiles;
+      const int t = min(tq + crank, plan.num_tiles - 1);
       const int n = t / tiles_per_img;
       const int r = t - n * tiles_per_img;
       const int ty = r / plan.tiles_x, tx = r - ty * plan.tiles_x;
       const int oy = ty * (CONV_TH * MSUB) + sub * CONV_TH + hy, ox = tx * CONV_TW + wx;
-      const bool valid = oy < plan.Ho && ox < plan.Wo;
+      const bool valid = oy < plan.Ho && ox < plan.Wo && !ghost;
       const long long off = ((static_cast<long long>(n) * plan.Ho + oy) * plan.Wo + ox) * BN;
       if (valid && ep.res != nullptr) ptx::prefetch_l2(ep.res + off + ch_begin * 16);
       UpTaps ut = {};
@@ -319,51 +340,99 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
   }
 
   ptx::tc_fence_before();
-  __syncthreads();
+  if constexpr (CL2) ptx::cluster_sync();  // no CTA leaves while its peer may still multicast into it or arrive on its barriers
+  else __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
 }
 
-template <int BN, int MSUB>
-static int launch_conv(const ConvPlan& plan, const ConvEpi& ep, cudaStream_t stream) {
+template <int BN, int MSUB, bool CL2>
+static int launch_conv(const ConvPlan& plan_in, const ConvEpi& ep, cudaStream_t stream) {
   using Cfg = ConvCfg<BN, MSUB>;
-  auto kern = conv_kernel<BN, MSUB>;
+  auto kern = conv_kernel<BN, MSUB, CL2>;
   static_assert(Cfg::SMEM <= 227 * 1024, "shared memory budget exceeded");
   static bool configured = false;
+  static int max_clusters = 0;
   if (!configured) {
     OPB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    if (CL2) {
+      cudaLaunchConfig_t q = {};
+      q.gridDim = dim3(2 * num_sms());
+      q.blockDim = dim3(64 + 512);
+      q.dynamicSmemBytes = Cfg::SMEM;
+      cudaLaunchAttribute a[1];
+      a[0].id = cudaLaunchAttributeClusterDimension;
+      a[0].val.clusterDim.x = 2;
+      a[0].val.clusterDim.y = 1;
+      a[0].val.clusterDim.z = 1;
+      q.attrs = a;
+      q.numAttrs = 1;
+      OPB_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &q));
+      if (max_clusters < 1) max_clusters = 1;
+    }
     configured = true;
   }
-  int grid = num_sms();
-  const int waves = (plan.num_tiles + grid - 1) / grid;  // fewest CTAs for the same number of tile waves
-  grid = (plan.num_tiles + waves - 1) / waves;
-  if (long long* tr = next_trace_slot(grid)) {
-    ConvPlan traced = plan;
-    traced.trace = tr;
-    kern<<<grid, 64 + 512, Cfg::SMEM, stream>>>(traced, ep);
+  ConvPlan plan = plan_in;
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  int grid;
+  if (CL2) {
+    const int pairs_needed = (plan.num_tiles + 1) / 2;
+    int pairs = pairs_needed < max_clusters ? pairs_needed : max_clusters;
+    const int waves = (pairs_needed + pairs - 1) / pairs;
+    pairs = (pairs_needed + waves - 1) / waves;
+    grid = 2 * pairs;
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
   } else {
-    kern<<<grid, 64 + 512, Cfg::SMEM, stream>>>(plan, ep);
+    grid = num_sms();
+    const int waves = (plan.num_tiles + grid - 1) / grid;  // fewest CTAs for the same number of tile waves
+    grid = (plan.num_tiles + waves - 1) / waves;
   }
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(64 + 512);
+  cfg.dynamicSmemBytes = Cfg::SMEM;
+  cfg.stream = stream;
+  if (grid <= 148) plan.trace = next_trace_slot(grid);
+  OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, plan, ep));
   count_launch();
-  OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
 }
 
+// Off by default: measured on B200 the convolution mainloops already run at the tensor pipe's practical rate
+// (10.5 / 12.2 / 13 TFLOP/s per SM for BN = 128 / 208 / 256, i.e. at or above the cuBLAS-measured peak), so halving
+// the weight fill changed nothing (2.145 vs 2.153 ms for the 23 convolutions of 8 frames).  Kept as a tested option
+// (opb200_conv_cluster / OPB200_CONV_CLUSTER=1) for parts where the L2 -> SM fill is the bound.
+static int g_conv_cluster = -1;
+static bool conv_use_cluster() {
+  if (g_conv_cluster < 0) {
+    const char* e = std::getenv("OPB200_CONV_CLUSTER");
+    g_conv_cluster = e ? (e[0] != '0') : 0;
+  }
+  return g_conv_cluster != 0;
+}
+
 template <int BN>
-static int conv_dispatch(ConvPlan& plan, const ConvEpi& ep, const void* x, int Hi, int Wi, int cin_s, cudaStream_t stream) {
-  // two stacked sub-tiles per CTA tile when that still leaves every SM at least two tiles
-  const int tx = (plan.Wo + CONV_TW - 1) / CONV_TW;
-  const int ty2 = (plan.Ho + 2 * CONV_TH - 1) / (2 * CONV_TH);
+static int conv_dispatch(ConvPlan& plan, const ConvEpi& ep, const void* x, int Hi, int Wi, int cin_s, const void* w,
+                         cudaStream_t stream) {
   // BN = 128: two sub-tiles still double-buffer in TMEM (4 x 128 columns).  BN = 208: two sub-tiles fill TMEM with one
   // accumulator set, so the epilogue runs behind the mainloop, but the halved weight refetch still wins (measured
   // 19.9 vs 24.2 us per 256 pixels).  BN = 256: one sub-tile, double-buffered (23.1 vs 25.1 us).
+  const int tx = (plan.Wo + CONV_TW - 1) / CONV_TW;
+  const int ty2 = (plan.Ho + 2 * CONV_TH - 1) / (2 * CONV_TH);
   const bool two = BN <= 208 && static_cast<long long>(plan.n_img) * tx * ty2 >= 2LL * num_sms();
   const int msub = two ? 2 : 1;
   plan.tiles_x = tx;
   plan.tiles_y = (plan.Ho + msub * CONV_TH - 1) / (msub * CONV_TH);
   plan.num_tiles = plan.n_img * plan.tiles_x * plan.tiles_y;
+  // clusters of two CTAs sharing the weight slab pay off once every SM has tiles to walk in lockstep
+  const bool cl2 = conv_use_cluster() && plan.num_tiles >= 2 * num_sms();
   const uint32_t s = static_cast<uint32_t>(plan.stride);
   const uint64_t gdim[4] = {static_cast<uint64_t>(cin_s), static_cast<uint64_t>(Wi), static_cast<uint64_t>(Hi),
                             static_cast<uint64_t>(plan.n_img)};
@@ -372,7 +441,15 @@ static int conv_dispatch(ConvPlan& plan, const ConvEpi& ep, const void* x, int H
   const uint32_t box[4] = {BLOCK_K, CONV_TW * s, static_cast<uint32_t>(CONV_TH * msub) * s, 1};
   const uint32_t estr[4] = {1, s, s, 1};
   if (int r = encode_tmap_16bit(&plan.x_map, true, 4, x, gdim, gstr, box, estr)) return r;
-  return two ? launch_conv<BN, 2>(plan, ep, stream) : launch_conv<BN, 1>(plan, ep, stream);
+  {
+    const uint64_t wdim[2] = {static_cast<uint64_t>(cin_s), static_cast<uint64_t>(plan.ksize) * plan.ksize * BN};
+    const uint64_t wstr[1] = {static_cast<uint64_t>(cin_s) * 2};
+    const uint32_t wbox[2] = {BLOCK_K, static_cast<uint32_t>(cl2 ? BN / 2 : BN)};
+    const uint32_t westr[2] = {1, 1};
+    if (int r = encode_tmap_16bit(&plan.w_map, true, 2, w, wdim, wstr, wbox, westr)) return r;
+  }
+  if (cl2) return two ? launch_conv<BN, 2, true>(plan, ep, stream) : launch_conv<BN, 1, true>(plan, ep, stream);
+  return two ? launch_conv<BN, 2, false>(plan, ep, stream) : launch_conv<BN, 1, false>(plan, ep, stream);
 }
 
 }  // namespace opb
@@ -380,6 +457,12 @@ static int conv_dispatch(ConvPlan& plan, const ConvEpi& ep, const void* x, int H
 using namespace opb;
 
 extern "C" {
+
+int opb200_conv_cluster(int on) {
+  const int prev = conv_use_cluster() ? 1 : 0;
+  if (on >= 0) g_conv_cluster = on ? 1 : 0;
+  return prev;
+}
 
 int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride, int cout_s,
                            const float* bias, const void* res, const void* up, void* y16, float* y32, int act, float slope,
@@ -420,18 +503,11 @@ int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, 
     ep.up_ry = Hs > 1 ? static_cast<float>(Hs - 1) / static_cast<float>(plan.Ho - 1) : 0.f;
     ep.up_rx = Ws > 1 ? static_cast<float>(Ws - 1) / static_cast<float>(plan.Wo - 1) : 0.f;
   }
-  {
-    const uint64_t gdim[2] = {static_cast<uint64_t>(cin_s), static_cast<uint64_t>(ksize) * ksize * cout_s};
-    const uint64_t gstr[1] = {static_cast<uint64_t>(cin_s) * 2};
-    const uint32_t box[2] = {BLOCK_K, static_cast<uint32_t>(cout_s)};
-    const uint32_t estr[2] = {1, 1};
-    if (int r = encode_tmap_16bit(&plan.w_map, true, 2, w, gdim, gstr, box, estr)) return r;
-  }
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   switch (cout_s) {
-    case 128: return conv_dispatch<128>(plan, ep, x, Hi, Wi, cin_s, stream);
-    case 208: return conv_dispatch<208>(plan, ep, x, Hi, Wi, cin_s, stream);
-    default: return conv_dispatch<256>(plan, ep, x, Hi, Wi, cin_s, stream);
+    case 128: return conv_dispatch<128>(plan, ep, x, Hi, Wi, cin_s, w, stream);
+    case 208: return conv_dispatch<208>(plan, ep, x, Hi, Wi, cin_s, w, stream);
+    default: return conv_dispatch<256>(plan, ep, x, Hi, Wi, cin_s, w, stream);
   }
 }
 

@@ -123,3 +123,24 @@ def test_lateral_conv_with_fused_upsample_add(n, H, W, cin, cout):
             assert (got[..., cout:] == 0).all()
     finally:
         torch.backends.cudnn.allow_tf32 = old
+
+
+def test_conv_cluster_multicast_option_is_bit_identical():
+    """Clusters of two CTAs multicasting the weight slabs (TMA multicast) must give the same bits as the plain kernel."""
+    from onepose_st_b200 import _lib, ops
+    from onepose_st_b200.nn_common import pack_conv_f16, _cs
+    g = torch.Generator(device="cuda").manual_seed(5)
+    lib = _lib.lib()
+    for cin, cout, hw in [(128, 128, 128), (196, 196, 128), (256, 256, 128), (196, 196, 120)]:
+        x16 = torch.zeros(8, hw, hw, _cs(cin), dtype=torch.float16, device="cuda")
+        x16[..., :cin] = torch.randn(8, hw, hw, cin, device="cuda", generator=g).half()
+        wp, bp = pack_conv_f16(torch.randn(cout, cin, 3, 3, device="cuda", generator=g) / (cin * 9) ** 0.5,
+                               torch.randn(cout, device="cuda", generator=g))
+        prev = lib.opb200_conv_cluster(0)
+        try:
+            plain = ops.conv2d_nhwc_f16(x16, wp, 3, 1, bp, None, 1)
+            lib.opb200_conv_cluster(1)
+            clustered = ops.conv2d_nhwc_f16(x16, wp, 3, 1, bp, None, 1)
+        finally:
+            lib.opb200_conv_cluster(prev)
+        assert torch.equal(plain, clustered)

@@ -155,3 +155,32 @@ def test_backbone_f16_tensor_core_path_is_tf32_grade(golden):
     print(f"backbone rel err vs fp32 golden: fp16 tcgen05 coarse {e16[0]:.2e} fine {e16[1]:.2e}; cuDNN TF32 coarse {etf[0]:.2e} fine {etf[1]:.2e}")
     assert e16[0] < 5e-3 and e16[1] < 5e-3
     assert e16[0] < 3 * etf[0] + 1e-4 and e16[1] < 3 * etf[1] + 1e-4
+
+
+@pytest.mark.parametrize("hw,n", [((480, 640), 2), ((136, 104), 3), ((64, 64), 1)])
+def test_backbone_f16_vs_fp32_executor_other_sizes(hw, n):
+    """tcgen05 backbone against the exact-fp32 cuDNN executor on non-square / small / ragged-tile image sizes."""
+    from onepose_st_b200.nn_common import ResNetFPN_8_2, FusedBackbone, FusedBackboneF16
+    torch.manual_seed(3)
+    m = ResNetFPN_8_2({"block_type": "BasicBlock", "initial_dim": 128, "block_dims": [128, 196, 256]})
+    for mod in m.modules():  # non-trivial BatchNorm statistics so that the folding is exercised
+        if isinstance(mod, torch.nn.BatchNorm2d):
+            mod.running_mean.normal_(0, 0.1)
+            mod.running_var.uniform_(0.5, 1.5)
+            mod.weight.data.uniform_(0.5, 1.5)
+            mod.bias.data.normal_(0, 0.1)
+    m = m.cuda().eval()
+    img = torch.rand(n, 1, hw[0], hw[1], device="cuda")
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        with torch.no_grad():
+            rc, rf = FusedBackbone(m)(img)
+            gc, gf = FusedBackboneF16(m)(img)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    assert gc.shape == rc.shape and gf.shape == rf.shape
+    ec = (gc - rc).abs().max().item() / rc.abs().max().item()
+    ef = (gf - rf).abs().max().item() / rf.abs().max().item()
+    print(f"backbone {hw} x{n}: rel err coarse {ec:.2e} fine {ef:.2e}")
+    assert ec < 5e-3 and ef < 5e-3
