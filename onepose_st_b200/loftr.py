@@ -8,7 +8,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from . import ops
-from .nn_common import (LinearAttention, LoFTREncoderLayer, PositionEncodingSine as _PE, ResNetFPN_8_2, _TransformerBase,
+from .nn_common import (HeadGraphs, LinearAttention, LoFTREncoderLayer, PositionEncodingSine as _PE, ResNetFPN_8_2, _TransformerBase,
                         fine_expectation)
 
 __all__ = ["LoFTR_for_OnePose_Plus", "LocalFeatureTransformer", "CoarseMatching", "FinePreprocess", "FineMatching",
@@ -85,6 +85,10 @@ class CoarseMatching(nn.Module):
         self.precision = ops.PREC_BF16X3
 
     def forward(self, feat_c0, feat_c1, data, mask_c0=None, mask_c1=None):
+        self.finish(self.launch(feat_c0, feat_c1, data, mask_c0, mask_c1), data)
+
+    def launch(self, feat_c0, feat_c1, data, mask_c0=None, mask_c1=None) -> "ops.CoarseLaunch":
+        """Enqueue the matching kernels (no host sync; needs data['hw0_c'] / data['hw1_c'])."""
         if self.training:
             raise NotImplementedError("training-time coarse matching is out of scope of the inference path")
         planes = feat_c0 if isinstance(feat_c0, ops.FeaturePlanes) else None  # internal fused hand-over
@@ -97,10 +101,15 @@ class CoarseMatching(nn.Module):
             vhw = torch.stack([k0.sum(1).max(-1)[0], k0.sum(-1).max(-1)[0], k1.sum(1).max(-1)[0], k1.sum(-1).max(-1)[0]], 1).int()
         if (mask_c0 is None) != (mask_c1 is None):
             raise ValueError("mask_c0 and mask_c1 must be given together")
-        b_ids, i_ids, j_ids, mconf, conf = ops.coarse_match(
+        return ops.coarse_match_launch(
             feat_c0, feat_c1, scale=1.0 / (C * self.temperature), thr=self.thr, border_rm=self.border_rm, border_mode=1,
             grid_a=(h0, w0), grid_b=(h1, w1), mask_a=mask_c0, mask_b=mask_c1, mask_fill=1, valid_hw=vhw,
             materialize_conf=self.materialize_conf_matrix, precision=self.precision, planes=planes)
+
+    def finish(self, handle: "ops.CoarseLaunch", data, copy: bool = False):
+        """Read the match count (the forward's host sync) and fill the reference's coarse-level ``data`` keys."""
+        w0, w1 = int(data["hw0_c"][1]), int(data["hw1_c"][1])
+        b_ids, i_ids, j_ids, mconf, conf = ops.coarse_match_finish(handle, copy=copy)
         if conf is not None:
             data.update({"conf_matrix": conf})
         scale = data["hw0_i"][0] / data["hw0_c"][0]
@@ -192,20 +201,31 @@ class LoFTR_for_OnePose_Plus(nn.Module):
         self.fine_preprocess = FinePreprocess(config)
         self.loftr_fine = LocalFeatureTransformer(config["fine"])
         self.fine_matching = FineMatching()
+        self._graphs = HeadGraphs()
 
-    @torch.no_grad()
-    def forward(self, data, **kwargs):
-        if self.training:
-            raise NotImplementedError("onepose_st_b200 implements the inference forward only; call .eval()")
-        data.update({"bs": data["image0"].size(0), "hw0_i": data["image0"].shape[2:], "hw1_i": data["image1"].shape[2:]})
-        if data["hw0_i"] == data["hw1_i"]:
-            feats_c, feats_f = self.backbone(torch.cat([data["image0"], data["image1"]], dim=0))
-            (feat_c0, feat_c1), (feat_f0, feat_f1) = feats_c.split(data["bs"]), feats_f.split(data["bs"])
+    # CUDA graph of the head (nn_common.HeadGraphs): opt-in, no padding masks, weights not modified in place
+    cuda_graph = False
+
+    def __getstate__(self):
+        st = self.__dict__.copy()
+        st["_graphs"] = HeadGraphs()
+        return st
+
+    def _head(self, data, image0, image1, coarse):
+        """Backbone of both images (+ coarse LoFTR stack and coarse matching kernels when ``coarse``): everything before
+        the forward's host sync.  Returns ((feat_c0, feat_c1, feat_f0, feat_f1), launch handle | None, hw dict) and
+        sets the hw*_c / hw*_f keys of ``data``."""
+        if image0.shape[2:] == image1.shape[2:]:
+            feats_c, feats_f = self.backbone(torch.cat([image0, image1], dim=0))
+            (feat_c0, feat_c1), (feat_f0, feat_f1) = feats_c.split(image0.size(0)), feats_f.split(image0.size(0))
         else:
-            (feat_c0, feat_f0), (feat_c1, feat_f1) = self.backbone(data["image0"]), self.backbone(data["image1"])
+            (feat_c0, feat_f0), (feat_c1, feat_f1) = self.backbone(image0), self.backbone(image1)
+        hw = {"hw0_c": tuple(feat_c0.shape[2:]), "hw1_c": tuple(feat_c1.shape[2:]), "hw0_f": tuple(feat_f0.shape[2:]),
+              "hw1_f": tuple(feat_f1.shape[2:])}
         data.update({"hw0_c": feat_c0.shape[2:], "hw1_c": feat_c1.shape[2:], "hw0_f": feat_f0.shape[2:],
                      "hw1_f": feat_f1.shape[2:]})
-        if "mkpts0_c" not in data:
+        handle = None
+        if coarse:
             s0 = feat_c0.flatten(2).permute(0, 2, 1)
             s1 = feat_c1.flatten(2).permute(0, 2, 1)
             add0 = self.pos_encoding.token_table(*feat_c0.shape[2:])
@@ -214,8 +234,29 @@ class LoFTR_for_OnePose_Plus(nn.Module):
             if "mask0" in data:
                 mask_c0, mask_c1 = data["mask0"].flatten(-2), data["mask1"].flatten(-2)
             planes = self.loftr_coarse(s0, s1, mask_c0, mask_c1, _add0=add0, _add1=add1, _planes_only=True)
-            self.coarse_matching(planes, None, data, mask_c0=mask_c0, mask_c1=mask_c1)
+            handle = self.coarse_matching.launch(planes, None, data, mask_c0=mask_c0, mask_c1=mask_c1)
+        return (feat_c0, feat_c1, feat_f0, feat_f1), handle, hw
+
+    @torch.no_grad()
+    def forward(self, data, **kwargs):
+        if self.training:
+            raise NotImplementedError("onepose_st_b200 implements the inference forward only; call .eval()")
+        data.update({"bs": data["image0"].size(0), "hw0_i": data["image0"].shape[2:], "hw1_i": data["image1"].shape[2:]})
+        coarse = "mkpts0_c" not in data
+        if self.cuda_graph and coarse and "mask0" not in data and data["image0"].is_cuda:
+            key = (self.coarse_matching.precision, getattr(self.loftr_coarse, "precision", ops.PREC_BF16X3),
+                   torch.backends.cudnn.allow_tf32, self.coarse_matching.materialize_conf_matrix)
+            proto = {k: data[k] for k in ("bs", "hw0_i", "hw1_i")}
+            feats, handle, hw = self._graphs.run(key, (data["image0"], data["image1"]),
+                                                 lambda i0, i1: self._head(dict(proto), i0, i1, True))
+            feat_c0, feat_c1, feat_f0, feat_f1 = feats
+            data.update({k: torch.Size(v) for k, v in hw.items()})
+            self.coarse_matching.finish(handle, data, copy=True)
         else:
+            (feat_c0, feat_c1, feat_f0, feat_f1), handle, _ = self._head(data, data["image0"], data["image1"], coarse)
+            if coarse:
+                self.coarse_matching.finish(handle, data)
+        if not coarse:
             # fine-only entry (loftr.py:79-115): clips the caller's tensors in place, batch size 1
             k0, k1 = data["mkpts0_c"], data["mkpts1_c"]
             b_ids = torch.zeros((k0.shape[0],), device=k0.device).long()

@@ -6,13 +6,14 @@ cache packed weights, and move pointers around.  The ResNet-FPN backbone (SURVEY
 "next" rows in 8f) runs on own tcgen05 convolutions at TF32-grade precision, or on cuDNN when exact fp32 is asked.
 """
 import math
+import threading
 from typing import Optional, Sequence
 
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from . import ops
+from . import _lib, ops
 
 
 # --------------------------------------------------------------------------------------------------
@@ -264,6 +265,60 @@ class FusedBackboneF16:
 
 
 # --------------------------------------------------------------------------------------------------
+# CUDA graphs of the shape-static head of a matcher forward (backbone -> coarse stack -> coarse matching kernels).
+# --------------------------------------------------------------------------------------------------
+class HeadGraphs:
+    """The head is ~70-110 kernel launches of fixed shape for given input sizes: captured once per (CUDA stream, key)
+    and replayed as ONE launch, which keeps the host ahead of the GPU when several forwards are in flight
+    (pipeline.StreamPipeline).  Each graph owns its workspaces (``ops.workspaces.scope``) and static input buffers;
+    whatever ``fn`` returns stays alive with the graph and is overwritten by the next replay on that stream."""
+
+    _lock = threading.Lock()
+    _serial = 0
+
+    def __init__(self, max_entries: int = 16):
+        self.entries = {}
+        self.max_entries = max_entries
+
+    def __len__(self):
+        return len(self.entries)
+
+    def run(self, key, inputs, fn, guard=None):
+        """``fn(*static_inputs)`` replayed on the current stream with ``inputs`` copied into the static buffers.
+        ``guard()`` (optional) is compared with its value at capture time: a mismatch (a per-sequence cache was rebuilt
+        at another address) drops the graph."""
+        dev = inputs[0].device
+        key = (torch.cuda.current_stream(dev).cuda_stream, dev.index) + tuple(key) + tuple(tuple(t.shape) for t in inputs)
+        ent = self.entries.get(key)
+        if ent is not None and guard is not None and ent[4] != guard():
+            ent = None
+        if ent is None:
+            static = [torch.empty_like(t, memory_format=torch.contiguous_format) for t in inputs]
+            for st, t in zip(static, inputs):
+                st.copy_(t)
+            fn(*static)  # eager run: builds every cache / workspace / function attribute the capture relies on
+            torch.cuda.current_stream(dev).synchronize()
+            with HeadGraphs._lock:
+                HeadGraphs._serial += 1
+                g = torch.cuda.CUDAGraph()
+                l0 = _lib.launch_count()
+                with ops.workspaces.scope(("graph", HeadGraphs._serial)), \
+                        torch.cuda.graph(g, capture_error_mode="thread_local"):
+                    out = fn(*static)
+                n_launch = _lib.launch_count() - l0  # this library's kernels inside one replay
+            ent = (g, static, out, n_launch, None if guard is None else guard())
+            if len(self.entries) >= self.max_entries:
+                self.entries.clear()
+            self.entries[key] = ent
+        g, static, out, n_launch, _ = ent
+        for st, t in zip(static, inputs):
+            st.copy_(t, non_blocking=True)
+        g.replay()
+        _lib.launch_count_add(n_launch)
+        return out
+
+
+# --------------------------------------------------------------------------------------------------
 # Sine position encoding (reference: OnePosePlus utils/position_encoding.py:13-42; LoFTR :11-42).
 # ``pe`` stays a non-persistent buffer of the reference's shape; a token-major [H*W, C] table of the
 # current feature-map size is cached and added inside the transformer's stage-in kernel.
@@ -292,7 +347,9 @@ class PositionEncodingSine(nn.Module):
         t = self._tables.get(key)
         if t is None:
             t = self.pe[0, :, :h, :w].reshape(self.pe.shape[1], h * w).t().contiguous()
-            self._tables = {key: t}
+            if len(self._tables) >= 8:  # tables stay alive (CUDA graphs of the matcher head read them by address)
+                self._tables = {}
+            self._tables[key] = t
         return t
 
 

@@ -14,8 +14,8 @@ import torch
 import torch.nn as nn
 
 from . import _lib, ops
-from .nn_common import (LinearAttention, LoFTREncoderLayer, PositionEncodingSine, ResNetFPN_8_2, _TransformerBase,
-                        fine_expectation)
+from .nn_common import (HeadGraphs, LinearAttention, LoFTREncoderLayer, PositionEncodingSine, ResNetFPN_8_2,
+                        _TransformerBase, fine_expectation)
 
 logger = logging.getLogger("onepose_st_b200")
 
@@ -293,7 +293,7 @@ class OnePosePlus_model(nn.Module):
                 for p in self.backbone.parameters():
                     p.requires_grad = False
         self._kpt_cache = None  # (key, encoded descriptors): the 3D model is fixed across a sequence
-        self._graphs = {}       # CUDA graphs of the head, see _graphed_head
+        self._graphs = HeadGraphs()  # CUDA graphs of the head, see _graphed_head
 
     def _encode_3d(self, data):
         desc = data["descriptors3d_coarse_db"] if "descriptors3d_coarse_db" in data else data["descriptors3d_db"]
@@ -316,7 +316,7 @@ class OnePosePlus_model(nn.Module):
     def __getstate__(self):
         st = self.__dict__.copy()
         st["_kpt_cache"] = None
-        st["_graphs"] = {}
+        st["_graphs"] = HeadGraphs()
         return st
 
     def _head(self, data, img, qmask):
@@ -333,53 +333,27 @@ class OnePosePlus_model(nn.Module):
         planes = self.loftr_coarse(desc3d, q2d, query_mask=qmask, _add2d=add2d, _planes_only=True)
         return self.coarse_matching.launch(planes, None, data, mask_query=qmask), feat_f, feat_c.shape[2:]
 
-    # ---- CUDA graph of the head --------------------------------------------------------------------------------
-    # The head is ~85 kernel launches of fixed shape for a given (image size, batch, 3D model): with ``cuda_graph``
-    # on it is captured once per (CUDA stream, key) and replayed as ONE launch, which is what keeps the host ahead of
-    # the GPU when several forwards are in flight (pipeline.StreamPipeline).  Opt-in: a replay reuses static buffers
-    # and assumes the weights are not modified in place between forwards.
+    # ---- CUDA graph of the head (nn_common.HeadGraphs) ----------------------------------------------------------
+    # Opt-in: a replay reuses static buffers and assumes the weights are not modified in place between forwards.
     cuda_graph = False
-    _capture_lock = threading.Lock()
-    _graph_serial = 0
 
     def _graphed_head(self, data, img):
         kp = data["keypoints3d"]
         desc = data["descriptors3d_coarse_db"] if "descriptors3d_coarse_db" in data else data["descriptors3d_db"]
-        key = (torch.cuda.current_stream(img.device).cuda_stream, img.device.index, tuple(img.shape), kp.data_ptr(), kp._version, tuple(kp.shape),
-               tuple(kp.stride()), desc.data_ptr(), desc._version, tuple(desc.shape), tuple(desc.stride()),
-               self.coarse_matching.precision, getattr(self.loftr_coarse, "precision", ops.PREC_BF16X3),
-               torch.backends.cudnn.allow_tf32,
+        key = (kp.data_ptr(), kp._version, tuple(kp.shape), tuple(kp.stride()), desc.data_ptr(), desc._version,
+               tuple(desc.shape), tuple(desc.stride()), self.coarse_matching.precision,
+               getattr(self.loftr_coarse, "precision", ops.PREC_BF16X3), torch.backends.cudnn.allow_tf32,
                self.coarse_matching.materialize_conf_matrix)
+
         def cache_ids():  # tensors the captured kernels read by address besides the weights
             c0, k0 = self.loftr_coarse.__dict__.get("_stream0_cache"), self._kpt_cache
             return (None if c0 is None else c0[1].data_ptr(), None if k0 is None else k0[1].data_ptr())
 
-        ent = self._graphs.get(key)
-        if ent is not None and ent[5] != cache_ids():
-            ent = None  # another 3D model was matched in between and the per-sequence caches were rebuilt
-        if ent is None:
-            static_img = torch.empty_like(img, memory_format=torch.contiguous_format)
-            static_img.copy_(img)
-            scratch = dict(data)
-            self._head(scratch, static_img, None)  # eager run: builds every cache / workspace / function attribute
-            torch.cuda.current_stream(img.device).synchronize()
-            with OnePosePlus_model._capture_lock:
-                g = torch.cuda.CUDAGraph()
-                scratch = dict(data)
-                OnePosePlus_model._graph_serial += 1
-                l0 = _lib.launch_count()
-                with ops.workspaces.scope(("graph", OnePosePlus_model._graph_serial)), \
-                        torch.cuda.graph(g, capture_error_mode="thread_local"):
-                    handle, feat_f, hw_c = self._head(scratch, static_img, None)
-                n_launch = _lib.launch_count() - l0  # library kernels inside one replay
-            ent = (g, static_img, handle, feat_f, tuple(hw_c), cache_ids(), n_launch)
-            if len(self._graphs) >= 16:
-                self._graphs.clear()
-            self._graphs[key] = ent
-        g, static_img, handle, feat_f, hw_c, _, n_launch = ent
-        static_img.copy_(img, non_blocking=True)
-        g.replay()
-        _lib.launch_count_add(n_launch)
+        def head(static_img):
+            handle, feat_f, hw_c = self._head(dict(data), static_img, None)
+            return handle, feat_f, tuple(hw_c)
+
+        handle, feat_f, hw_c = self._graphs.run(key, (img,), head, guard=cache_ids)
         return handle, feat_f, torch.Size(hw_c)
 
     @torch.no_grad()

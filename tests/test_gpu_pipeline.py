@@ -114,3 +114,37 @@ def test_cuda_graph_head_matches_eager():
             assert torch.equal(w[k_], g[k_]), k_
         assert (w["mconf"] - g["mconf"]).abs().max().item() < 1e-5
         assert (w["mkpts_query_f"] - g["mkpts_query_f"]).abs().max().item() < 1e-3
+
+
+def test_loftr_cuda_graph_head_matches_eager():
+    """LoFTR_for_OnePose_Plus with the head replayed as a CUDA graph: same matches as the eager forward."""
+    from onepose_st_b200 import synthetic
+    from onepose_st_b200.loftr import LoFTR_for_OnePose_Plus, default_cfg
+    torch.manual_seed(0)
+    m = LoFTR_for_OnePose_Plus(default_cfg, enable_fine_matching=True).eval()
+    m.load_state_dict(synthetic.calibrate_loftr_state_dict(m.state_dict()))
+    m = m.cuda()
+    g = torch.Generator().manual_seed(11)
+    pairs = []
+    for _ in range(3):
+        img = torch.rand(2, 1, 256, 256, generator=g).cuda()
+        pairs.append((img, (img + 0.01 * torch.randn(img.shape, generator=g).cuda()).clamp(0, 1)))
+    one = torch.ones(2, 2, device="cuda")
+
+    def run(i0, i1):
+        d = {"image0": i0, "image1": i1, "scale0": one, "scale1": one}
+        m(d)
+        return {k: d[k].clone() for k in ("b_ids", "i_ids", "j_ids", "mconf", "mkpts0_f", "mkpts1_f")}
+
+    with torch.no_grad():
+        m.cuda_graph = False
+        want = [run(*p) for p in pairs]
+        m.cuda_graph = True
+        got = [run(*p) for p in pairs + pairs[:1]]
+    assert len(m._graphs) == 1
+    for w, g_ in zip(want + want[:1], got):
+        assert w["mconf"].numel() > 20
+        for k in ("b_ids", "i_ids", "j_ids"):
+            assert torch.equal(w[k], g_[k]), k
+        assert (w["mconf"] - g_["mconf"]).abs().max().item() < 1e-5
+        assert (w["mkpts1_f"] - g_["mkpts1_f"]).abs().max().item() < 1e-3

@@ -157,9 +157,26 @@ def run_loftr(a):
                 d = {"image0": img0, "image1": img1, "scale0": one, "scale1": one}
                 m(d)
                 out["m"] = int(d["mconf"].shape[0])
+            m.cuda_graph = False
             med, best = time_op(fn, a.iters, warmup=0 if a.iters == 1 else 3)
-            print(json.dumps({"op": "LoFTR_for_OnePose_Plus.forward", "fine": fine, "pairs_per_forward": nb, "image": a.size,
-                              "matches_per_pair": out["m"] / nb, "ms_per_forward": med, "pairs_per_s": nb / med * 1e3}), flush=True)
+            line = {"op": "LoFTR_for_OnePose_Plus.forward", "fine": fine, "pairs_per_forward": nb, "image": a.size,
+                    "matches_per_pair": out["m"] / nb, "ms_per_forward": med, "pairs_per_s": nb / med * 1e3}
+            # throughput mode: CUDA-graph head + three host threads x CUDA streams (pipeline.StreamPipeline)
+            from onepose_st_b200 import pipeline
+            m.cuda_graph = True
+            pipe = pipeline.StreamPipeline(3)
+            pipe.warm(fn)
+            n_fw = 24
+            pipe.map(lambda _: fn(), range(6))
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            pipe.map(lambda _: fn(), range(n_fw))
+            e1.record()
+            torch.cuda.synchronize()
+            line["pairs_per_s_pipelined_graph"] = nb * n_fw / e0.elapsed_time(e1) * 1e3
+            m.cuda_graph = False
+            print(json.dumps(line), flush=True)
 
 
 def run_conv(a):
