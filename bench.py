@@ -188,7 +188,8 @@ def run_ours(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"  # keeps NCCL's version banner off stdout (rank 0 prints exactly one JSON line)
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's banner / warnings off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
 
@@ -277,7 +278,7 @@ def run_ours(args):
         # the gather is warmed up too (first NCCL all_gather sets up channels; first sort/scatter compiles nothing but allocates)
         # at the size of the timed region (the warm-up rows repeated), so that the timed gather finds its buffers in the
         # caching allocator instead of calling cudaMalloc
-        rep_ = max(1, -(-args.steps // max(1, args.warmup)))
+        rep_ = max(1, -(-args.steps // max(1, args.warmup))) + 1  # a little larger: bigger cached blocks serve smaller requests
         sharding.gather_matches(ragged.rows().repeat(rep_, 1), list(ragged.counts) * rep_, world * F * args.warmup * rep_)
         ragged.reset()
         ops.stage_events = {} if stage_events else None
@@ -287,10 +288,12 @@ def run_ours(args):
         torch.cuda.synchronize()
         sampler.start()
         l0 = _lib.launch_count()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        mallocs0 = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
+        ev0, ev1, evg = (torch.cuda.Event(enable_timing=True) for _ in range(3))
         ev0.record()
         d2h = run_steps(args.warmup, args.steps, e2e, pipe)
         n_units = world * F * args.steps
+        evg.record()
         rows_all, counts_all = sharding.gather_matches(ragged.rows(), ragged.counts, n_units)
         ev1.record()
         torch.cuda.synchronize()
@@ -299,11 +302,17 @@ def run_ours(args):
         launches = _lib.launch_count() - l0
         clocks = sampler.stop()
         ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+        per_rank = [float(ms.item())]
         if world > 1:
+            allms = torch.empty(world, device=dev)
+            dist.all_gather_into_tensor(allms, ms)
+            per_rank = [round(v, 2) for v in allms.tolist()]
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         events, ops.stage_events = ops.stage_events, None
+        diag = {"ms_per_rank": per_rank, "gather_ms_rank0": round(evg.elapsed_time(ev1), 3),
+                "cuda_mallocs_in_timed_region": torch.cuda.memory_stats(dev).get("num_device_alloc", 0) - mallocs0}
         return {"ms": float(ms.item()), "launches": launches, "clocks": clocks, "events": events, "d2h": d2h,
-                "matches": int(rows_all.shape[0]), "units": n_units}
+                "matches": int(rows_all.shape[0]), "units": n_units, "diag": diag}
 
     res = timed(e2e=False, n_streams=args.streams)
     res_e2e = None if args.no_e2e else timed(e2e=True, n_streams=args.streams)
@@ -377,7 +386,7 @@ def run_ours(args):
                   if torch.backends.cudnn.allow_tf32 else "fp32 cuDNN backbone, ") + "f32 accumulate/IO",
                "data": "synthetic", "config": config_dict(args, world),
                "matches_per_frame": m_per_frame, "gpu_launches": res["launches"], "clocks": res["clocks"],
-               "streams": args.streams,
+               "streams": args.streams, "diag": res["diag"],
                "single_stream": {"value": total_frames / (res_ops["ms"] * 1e-3), "unit": UNIT,
                                  "note": "same steps on one CUDA stream; stages_ms_per_frame and the rooflines are timed in this pass"},
                "stages_ms_per_frame": {k: round(v["ms_per_frame"], 4) for k, v in stages.items()},
@@ -388,7 +397,7 @@ def run_ours(args):
                           "h2d_bytes_per_step": F * args.size * args.size * 4,
                           "d2h_bytes_per_step": res_e2e["d2h"] // max(1, args.steps),
                           "ms_per_step": res_e2e["ms"] / args.steps, "gpu_launches": res_e2e["launches"],
-                          "clocks": res_e2e["clocks"],
+                          "clocks": res_e2e["clocks"], "diag": res_e2e["diag"],
                           "api": "OnePosePlus_model.forward(data): pinned-host frame -> H2D -> forward -> D2H of [M,6] match rows"}
     # CPU baseline: the reference algorithm's CPU port on this box's host cores (rank 0, N=1 only)
     if rank == 0 and world == 1 and args.cpu_sample_frames > 0:
