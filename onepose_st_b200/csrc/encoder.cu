@@ -337,9 +337,11 @@ __global__ void __launch_bounds__(128) kv_partial_kernel(const float* __restrict
   __shared__ __align__(16) float ks[2][8][256];
   const int t = threadIdx.x;
   const int h = t >> 4, d0 = (t & 15) * 2;
-  float acc0[32], acc1[32];
+  // accumulators as packed fp32 pairs (v, v + 1): one FFMA2 updates two of them, halving the FMA issue slots this
+  // kernel is bound by (ncu: issue slots 74 % busy with scalar FFMA); results are bit-identical to scalar fmaf
+  uint64_t acc0[16], acc1[16];
 #pragma unroll
-  for (int i = 0; i < 32; ++i) acc0[i] = acc1[i] = 0.f;
+  for (int i = 0; i < 16; ++i) acc0[i] = acc1[i] = 0ull;
   float ksum0 = 0.f, ksum1 = 0.f;
   const float* kbase = kphi + static_cast<long long>(gt.row_start[g] + r0) * 256;
   const float* vbase = v + static_cast<long long>(gt.row_start[g] + r0) * 256;
@@ -370,25 +372,28 @@ __global__ void __launch_bounds__(128) kv_partial_kernel(const float* __restrict
       const float2 kk = *reinterpret_cast<const float2*>(&ks[buf][i][h * 32 + d0]);
       ksum0 += kk.x;
       ksum1 += kk.y;
-      const float4* v4 = reinterpret_cast<const float4*>(&vs[buf][i][h * 32]);
+      const uint64_t k0 = ptx::pack_f32x2(kk.x, kk.x), k1 = ptx::pack_f32x2(kk.y, kk.y);
+      const ulonglong2* v2 = reinterpret_cast<const ulonglong2*>(&vs[buf][i][h * 32]);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float4 vv = v4[j];
-        acc0[4 * j + 0] = fmaf(kk.x, vv.x, acc0[4 * j + 0]);
-        acc0[4 * j + 1] = fmaf(kk.x, vv.y, acc0[4 * j + 1]);
-        acc0[4 * j + 2] = fmaf(kk.x, vv.z, acc0[4 * j + 2]);
-        acc0[4 * j + 3] = fmaf(kk.x, vv.w, acc0[4 * j + 3]);
-        acc1[4 * j + 0] = fmaf(kk.y, vv.x, acc1[4 * j + 0]);
-        acc1[4 * j + 1] = fmaf(kk.y, vv.y, acc1[4 * j + 1]);
-        acc1[4 * j + 2] = fmaf(kk.y, vv.z, acc1[4 * j + 2]);
-        acc1[4 * j + 3] = fmaf(kk.y, vv.w, acc1[4 * j + 3]);
+        const ulonglong2 vv = v2[j];  // (v[4j], v[4j+1]), (v[4j+2], v[4j+3])
+        acc0[2 * j + 0] = ptx::fma_f32x2(k0, vv.x, acc0[2 * j + 0]);
+        acc0[2 * j + 1] = ptx::fma_f32x2(k0, vv.y, acc0[2 * j + 1]);
+        acc1[2 * j + 0] = ptx::fma_f32x2(k1, vv.x, acc1[2 * j + 0]);
+        acc1[2 * j + 1] = ptx::fma_f32x2(k1, vv.y, acc1[2 * j + 1]);
       }
     }
     __syncthreads();
   }
   float2* out = reinterpret_cast<float2*>(partial + (static_cast<long long>(g) * max_chunks + chunk) * (KV_REC * 256) + h * 32 + d0);
 #pragma unroll
-  for (int i = 0; i < 32; ++i) out[i * 128] = make_float2(acc0[i], acc1[i]);
+  for (int i = 0; i < 16; ++i) {
+    float a0, a1, b0, b1;
+    ptx::unpack_f32x2(acc0[i], a0, a1);
+    ptx::unpack_f32x2(acc1[i], b0, b1);
+    out[(2 * i) * 128] = make_float2(a0, b0);
+    out[(2 * i + 1) * 128] = make_float2(a1, b1);
+  }
   out[32 * 128] = make_float2(ksum0, ksum1);
 }
 
@@ -462,25 +467,13 @@ __global__ void __launch_bounds__(128) attn_small_kernel(const float* __restrict
   for (int r0 = 0; r0 < jb.s_len; r0 += CH) {
     const int nr = min(CH, jb.s_len - r0);
     __syncthreads();
-    {  // all 16 loads of a thread in flight before the first shared-memory store
-      float4 kr[CH * (C / 4) / 128], vr[CH * (C / 4) / 128];
-#pragma unroll
-      for (int u = 0; u < CH * (C / 4) / 128; ++u) {
-        const int i = t + u * 128;
-        if (i < nr * (C / 4)) {
-          kr[u] = __ldg(k4 + r0 * (C / 4) + i);
-          vr[u] = __ldg(v4 + r0 * (C / 4) + i);
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < CH * (C / 4) / 128; ++u) {
-        const int i = t + u * 128;
-        if (i < nr * (C / 4)) {
-          reinterpret_cast<float4*>(&abuf[0][0])[i] = kr[u];
-          reinterpret_cast<float4*>(&bbuf[0][0])[i] = vr[u];
-        }
-      }
+    // cp.async: every 16-byte copy of the chunk in flight at once, no staging registers (occupancy)
+    for (int i = t; i < nr * (C / 4); i += 128) {
+      __pipeline_memcpy_async(reinterpret_cast<float4*>(&abuf[0][0]) + i, k4 + r0 * (C / 4) + i, 16);
+      __pipeline_memcpy_async(reinterpret_cast<float4*>(&bbuf[0][0]) + i, v4 + r0 * (C / 4) + i, 16);
     }
+    __pipeline_commit();
+    __pipeline_wait_prior(0);
     __syncthreads();
     for (int r = 0; r < nr; ++r) {
       const float kk = abuf[r][t];
@@ -512,19 +505,10 @@ __global__ void __launch_bounds__(128) attn_small_kernel(const float* __restrict
   for (int r0 = 0; r0 < jb.q_len; r0 += CH) {
     const int nr = min(CH, jb.q_len - r0);
     __syncthreads();
-    {
-      float4 qr[CH * (C / 4) / 128];
-#pragma unroll
-      for (int u = 0; u < CH * (C / 4) / 128; ++u) {
-        const int i = t + u * 128;
-        if (i < nr * (C / 4)) qr[u] = __ldg(q4 + r0 * (C / 4) + i);
-      }
-#pragma unroll
-      for (int u = 0; u < CH * (C / 4) / 128; ++u) {
-        const int i = t + u * 128;
-        if (i < nr * (C / 4)) reinterpret_cast<float4*>(&abuf[0][0])[i] = qr[u];
-      }
-    }
+    for (int i = t; i < nr * (C / 4); i += 128)
+      __pipeline_memcpy_async(reinterpret_cast<float4*>(&abuf[0][0]) + i, q4 + r0 * (C / 4) + i, 16);
+    __pipeline_commit();
+    __pipeline_wait_prior(0);
     __syncthreads();
     for (int r = 0; r < nr; ++r) {
       const float4* qq = reinterpret_cast<const float4*>(&abuf[r][h * D]);
@@ -587,6 +571,41 @@ __global__ void copy_in_kernel(const float* __restrict__ x, long long sn, long l
         row_mask[row0 + n * P + l] = (l < len) ? (mask ? (mask[static_cast<long long>(n) * len + l] != 0) : 1) : 0;
     }
   }
+}
+
+// Row-major fast path of copy_in_kernel (sc == 1, sl % 4 == 0, 16-byte aligned, C % 128 == 0): one warp per row,
+// 16-byte loads, 8-byte plane stores; pad rows (l >= len) are zero-filled.  grid = (ceil(P / 8), 1, n_batch), block 256.
+__global__ void __launch_bounds__(256) copy_in_rows_kernel(const float* __restrict__ x, long long sn, long long sl,
+                                                           const float* __restrict__ add, const uint8_t* __restrict__ mask,
+                                                           int len, int P, int C, int row0, __nv_bfloat16* __restrict__ xh,
+                                                           __nv_bfloat16* __restrict__ xl, uint8_t* __restrict__ row_mask) {
+  const int n = blockIdx.z;
+  const int l = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (l >= P) return;
+  const long long orow = static_cast<long long>(row0) + static_cast<long long>(n) * P + l;
+  const bool live = l < len;
+  const float4* src = reinterpret_cast<const float4*>(x + n * sn + static_cast<long long>(l) * sl);
+  const float4* ad = add != nullptr ? reinterpret_cast<const float4*>(add + static_cast<long long>(l) * C) : nullptr;
+  for (int c4 = lane; c4 < C / 4; c4 += 32) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (live) {
+      v = __ldg(src + c4);
+      if (ad != nullptr) {
+        const float4 a = __ldg(ad + c4);
+        v.x += a.x, v.y += a.y, v.z += a.z, v.w += a.w;
+      }
+    }
+    const __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
+    const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+    const __nv_bfloat162 l0 = __floats2bfloat162_rn(v.x - f0.x, v.y - f0.y), l1 = __floats2bfloat162_rn(v.z - f1.x, v.w - f1.y);
+    uint2 ph, pl;
+    ph.x = *reinterpret_cast<const uint32_t*>(&h0), ph.y = *reinterpret_cast<const uint32_t*>(&h1);
+    pl.x = *reinterpret_cast<const uint32_t*>(&l0), pl.y = *reinterpret_cast<const uint32_t*>(&l1);
+    *reinterpret_cast<uint2*>(xh + orow * C + c4 * 4) = ph;
+    *reinterpret_cast<uint2*>(xl + orow * C + c4 * 4) = pl;
+  }
+  if (lane == 0) row_mask[orow] = live ? (mask ? (mask[static_cast<long long>(n) * len + l] != 0) : 1) : 0;
 }
 
 __global__ void copy_out_kernel(const __nv_bfloat16* __restrict__ xh, const __nv_bfloat16* __restrict__ xl, int len, int P,
@@ -1007,10 +1026,20 @@ int opb200_transformer(const void* const* host_layer_weights, const int* host_la
       OPB_CHECK_CUDA(cudaMemsetAsync(w.row_mask + pad_lo[s], 0, n, stream));
     }
   }
-  copy_in_kernel<<<dim3((C + 31) / 32, (g.P0 + 31) / 32, n_batch), dim3(32, 8), 0, stream>>>(
-      x0, x0_sn, x0_sl, x0_sc, add0, mask0, len0, g.P0, C, 0, w.xh, w.xl, w.row_mask);
-  copy_in_kernel<<<dim3((C + 31) / 32, (g.P1 + 31) / 32, n_batch), dim3(32, 8), 0, stream>>>(
-      x1, x1_sn, x1_sl, x1_sc, add1, mask1, len1, g.P1, C, row1, w.xh, w.xl, w.row_mask);
+  auto stage_in = [&](const float* x, int64_t sn, int64_t sl, int64_t sc, const float* add, const uint8_t* mask, int len,
+                      int P, int row_begin) {
+    const bool rows = sc == 1 && (sl % 4 == 0 || len == 1) && sn % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 &&
+                      (add == nullptr || (reinterpret_cast<uintptr_t>(add) & 15) == 0);
+    if (rows) {
+      copy_in_rows_kernel<<<dim3((P + 7) / 8, 1, n_batch), 256, 0, stream>>>(x, sn, sl, add, mask, len, P, C, row_begin, w.xh,
+                                                                               w.xl, w.row_mask);
+    } else {  // channels-first / arbitrary strides: 32 x 32 shared-memory transpose
+      copy_in_kernel<<<dim3((C + 31) / 32, (P + 31) / 32, n_batch), dim3(32, 8), 0, stream>>>(x, sn, sl, sc, add, mask, len, P, C,
+                                                                                             row_begin, w.xh, w.xl, w.row_mask);
+    }
+  };
+  stage_in(x0, x0_sn, x0_sl, x0_sc, add0, mask0, len0, g.P0, 0);
+  stage_in(x1, x1_sn, x1_sl, x1_sc, add1, mask1, len1, g.P1, row1);
   count_launch(2 + (big_groups ? 1 : 0));
   if (big_groups) {  // off-diagonal / unused entries of the block-diagonal attention operand stay zero
     OPB_CHECK_CUDA(cudaMemsetAsync(w.kvb_h, 0, static_cast<size_t>(g.G) * 2 * 144 * 128 * 2, stream));
