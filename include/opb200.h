@@ -101,10 +101,14 @@ int opb200_transformer_planes(void* workspace, int d_model, int n_batch, int len
  * ascending (b, i) order; count_and_overflow is int[3] on the device: {number of matches, overflow flag,
  * rerun flag}.  conf_matrix (nullable) receives the full [n_batch, L, S] confidence matrix.
  * algo 0 = auto: when there are no masks, no conf_matrix, C == 256 and precision 3, ONE pass over the
- * similarity tiles computes the softmax statistics and captures the candidate matches; if that pass sees a
- * partial sum near the flush-to-zero range (or fills its candidate list) it sets the rerun flag, the outputs
- * are then undefined and the caller must call again with algo 1 = the two-pass path (per-row / per-column
- * maxima, no dynamic-range limit). */
+ * similarity tiles computes the softmax statistics and captures the candidate matches.  That sweep runs a single
+ * fp16 x fp16 product; every captured element is then re-evaluated from the split planes in fp32 and its term in
+ * the row / column sums replaced by the exact one (confidences within the 1e-3 contract, measured 6e-4).
+ * algo 2 = the same single pass on the three bf16 split products (fp32-grade everywhere, 3x the tensor work).
+ * If the pass cannot be trusted it sets the rerun flag, the outputs are then undefined and the caller must call
+ * again: flag 1 (a partial sum near the flush-to-zero range, or a full candidate list) -> algo 1 = the two-pass
+ * path (per-row / per-column maxima, no dynamic-range limit); flag 2 (a feature beyond +-1024, outside the range
+ * in which fp16 operands keep 11 bits against any partner) -> algo 2. */
 size_t opb200_coarse_match_workspace_bytes(int n_batch, int L, int S, int C, float thr);
 int opb200_coarse_match(const float* feat_a, const float* feat_b, const uint8_t* mask_a, const uint8_t* mask_b,
                         int mask_fill, int n_batch, int L, int S, int C, float scale, float thr, int border_rm,

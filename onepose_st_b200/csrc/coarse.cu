@@ -303,23 +303,39 @@ struct EpiSimSelect {
 //     necessary condition.  (row, col, y) of the few survivors go to the candidate list; their exact
 //     confidence is evaluated once the LSEs are final, with the same conf_from() as the two-pass path.
 // ================================================================================================
+//
+// SCREEN variant (the default single-pass mode): the sweep over all L x S similarities runs ONE fp16 x fp16 product
+// (11-bit significands, fp32 accumulation) instead of the three bf16 split products -- a third of the tensor work and
+// half of the shared-memory fill.  What the sweep decides is only (a) which elements can reach thr (captured with a
+// 10 % margin) and (b) the diffuse part of the row / column sums; every captured element is then re-evaluated from the
+// hi + lo planes in fp32 (cand_rescore_kernel) and its term in the two log-sum-exps is REPLACED by the exact one
+// (fixed-point integer atomics, so the result does not depend on the order of arrival).  The confidence of a match is
+// therefore exact in its own similarity and in every other large term of its row and column; the remaining error is
+// the fp16-operand error of the many small terms, which averages out (measured max 6e-4 on the bench workload
+// against the 1e-3 contract; tests/test_gpu_coarse.py).
 constexpr int FAST_GROUPS = 4;
-constexpr int FAST_BSTAGES = 3;
 constexpr int FAST_C = 256;
 constexpr int FAST_KB = FAST_C / BLOCK_K;           // 4 k-blocks
-constexpr int FAST_SUB = BLOCK_M * BLOCK_K * 2;     // one [128 x 64] bf16 sub-tile: 16 KB
-constexpr int FAST_A_BYTES = 2 * FAST_KB * FAST_SUB;  // hi + lo planes of the resident A block
-constexpr int FAST_BSTAGE_BYTES = 2 * FAST_SUB;     // B hi + lo k-block
-constexpr int FAST_SMEM = 1024 + FAST_A_BYTES + FAST_BSTAGES * FAST_BSTAGE_BYTES + 256;
+constexpr int FAST_SUB = BLOCK_M * BLOCK_K * 2;     // one [128 x 64] 16-bit sub-tile: 16 KB
+template <bool SCREEN>
+struct FastCfg {
+  static constexpr int PLANES = SCREEN ? 1 : 2;                   // fp16 plane | bf16 hi + lo planes
+  static constexpr int BSTAGES = SCREEN ? 6 : 3;
+  static constexpr int A_BYTES = PLANES * FAST_KB * FAST_SUB;     // the resident A block
+  static constexpr int BSTAGE_BYTES = PLANES * FAST_SUB;          // one B k-block
+  static constexpr int SMEM = 1024 + A_BYTES + BSTAGES * BSTAGE_BYTES + 256;
+};
 constexpr float kTinySum = 7.888609e-31f;           // 2^-100: partial sums below this may have lost terms to FTZ
+constexpr double kDeltaScale = 1099511627776.0;     // 2^40: fixed-point unit of the LSE corrections
 
 struct SimFastParams {
-  CUtensorMap a_hi, a_lo, b_hi, b_lo;  // [rows, 256] bf16, box 128 x 64, 128B swizzle
+  CUtensorMap a_hi, a_lo, b_hi, b_lo;  // [rows, 256] bf16, box 128 x 64, 128B swizzle (SCREEN: a_hi / b_hi = the fp16 planes)
   int N, L, S, Lp, Sp;
   int n_tiles;      // Sp / 128
   int total_tiles;  // N * (Lp/128) * n_tiles, m-major
   float c;          // scale * log2(e)
-  float thr_lim;    // 0.99 * thr (slack for the approximate exponentials)
+  float thr_lim;    // 0.99 * thr (slack for the approximate exponentials); 0.9 * thr when screening
+  int cand_tag;     // Candidate::pad of captured elements: 1 = y is final, 2 = y is the screening value (rescore)
   float2* rowpart;  // [n_tiles][N*Lp]
   float2* colpart;  // [4*Lp/128][N*Sp]
   Candidate* cand;
@@ -399,7 +415,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
   }
   p.rowpart[static_cast<long long>(n_tile) * p.N * p.Lp + grow] = make_float2(T, s);
   if (row_valid && s < kTinySum) tiny = true;
-  if (__any_sync(0xffffffffu, tiny) && lane == 0) atomicExch(p.needs_robust, 1);
+  if (__any_sync(0xffffffffu, tiny) && lane == 0) atomicOr(p.needs_robust, 1);
   // candidate capture: conf_ij > thr needs e_ij > thr * (row sum over this tile), i.e. acc_ij > vlim_i in raw
   // accumulator units -- one compare per element on a second sweep over TMEM, taken only when some row of the
   // warp has its maximum above the limit
@@ -424,14 +440,17 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
         for (int q = 1; q < 32; ++q) val = (k == q) ? v[q] : val;
         if ((mask >> k) & 1u) {
           const int slot = atomicAdd(p.cand_count, 1);
-          if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i, j0 + k, __fmul_rn(val, p.c), 1};
+          if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i, j0 + k, __fmul_rn(val, p.c), p.cand_tag};
         }
       }
     }
   }
 }
 
+template <bool SCREEN>
 __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(const __grid_constant__ SimFastParams p) {
+  constexpr int FAST_A_BYTES = FastCfg<SCREEN>::A_BYTES, FAST_BSTAGES = FastCfg<SCREEN>::BSTAGES;
+  constexpr int FAST_BSTAGE_BYTES = FastCfg<SCREEN>::BSTAGE_BYTES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;                  // [plane 0/1][kb][128 x 64]
@@ -452,9 +471,11 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.a_hi);
-    ptx::prefetch_tmap(&p.a_lo);
     ptx::prefetch_tmap(&p.b_hi);
-    ptx::prefetch_tmap(&p.b_lo);
+    if (!SCREEN) {
+      ptx::prefetch_tmap(&p.a_lo);
+      ptx::prefetch_tmap(&p.b_lo);
+    }
     ptx::mbar_init(a_full, 1);
     ptx::mbar_init(a_empty, 1);
     for (int s = 0; s < FAST_BSTAGES; ++s) {
@@ -490,7 +511,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
           ptx::mbar_arrive_expect_tx(a_full, FAST_A_BYTES);
           for (int kb = 0; kb < FAST_KB; ++kb) {
             ptx::tma_load_2d(smem_a + kb * FAST_SUB, &p.a_hi, a_full, kb * BLOCK_K, m_tile * BLOCK_M);
-            ptx::tma_load_2d(smem_a + (FAST_KB + kb) * FAST_SUB, &p.a_lo, a_full, kb * BLOCK_K, m_tile * BLOCK_M);
+            if (!SCREEN) ptx::tma_load_2d(smem_a + (FAST_KB + kb) * FAST_SUB, &p.a_lo, a_full, kb * BLOCK_K, m_tile * BLOCK_M);
           }
           a_phase ^= 1;
           cur_m = m_tile;
@@ -501,7 +522,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
           ptx::mbar_arrive_expect_tx(&b_full[stage], FAST_BSTAGE_BYTES);
           uint8_t* sb = smem_b + stage * FAST_BSTAGE_BYTES;
           ptx::tma_load_2d(sb, &p.b_hi, &b_full[stage], kb * BLOCK_K, b_row);
-          ptx::tma_load_2d(sb + FAST_SUB, &p.b_lo, &b_full[stage], kb * BLOCK_K, b_row);
+          if (!SCREEN) ptx::tma_load_2d(sb + FAST_SUB, &p.b_lo, &b_full[stage], kb * BLOCK_K, b_row);
           if (++stage == FAST_BSTAGES) {
             stage = 0;
             phase ^= 1;
@@ -511,7 +532,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, SIM_BN);
+    constexpr uint32_t idesc = SCREEN ? ptx::make_idesc_f16(BLOCK_M, SIM_BN) : ptx::make_idesc_bf16(BLOCK_M, SIM_BN);
     int stage = 0;
     uint32_t phase = 0, a_phase = 0;
     int cur_m = -1;
@@ -533,17 +554,22 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           const uint64_t ah = ptx::make_desc_sw128(ptx::smem_u32(smem_a + kb * FAST_SUB));
-          const uint64_t al = ptx::make_desc_sw128(ptx::smem_u32(smem_a + (FAST_KB + kb) * FAST_SUB));
           const uint32_t sb = ptx::smem_u32(smem_b + stage * FAST_BSTAGE_BYTES);
           const uint64_t bh = ptx::make_desc_sw128(sb);
-          const uint64_t bl = ptx::make_desc_sw128(sb + FAST_SUB);
-          // small cross terms first, the dominant hi*hi term last
+          if (SCREEN) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bl + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bh + 2 * k, idesc, (kb | k) != 0);
+          } else {
+            const uint64_t al = ptx::make_desc_sw128(ptx::smem_u32(smem_a + (FAST_KB + kb) * FAST_SUB));
+            const uint64_t bl = ptx::make_desc_sw128(sb + FAST_SUB);
+            // small cross terms first, the dominant hi*hi term last
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, al + 2 * k, bh + 2 * k, idesc, 1);
+            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bl + 2 * k, idesc, (kb | k) != 0);
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bh + 2 * k, idesc, 1);
+            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, al + 2 * k, bh + 2 * k, idesc, 1);
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bh + 2 * k, idesc, 1);
+          }
           ptx::mma_commit(&b_empty[stage]);
           if (kb == FAST_KB - 1) {
             ptx::mma_commit(&tfull[acc]);
@@ -607,12 +633,102 @@ __device__ __forceinline__ bool border_keep(const BorderRule& br, int n, int i, 
          c1 < w1 - br.b;
 }
 
+// fp16 operand plane of the screening sweep from the bf16 hi + lo planes (8 elements per thread).  fp16 keeps 11
+// significant bits only between 2^-14 and 65504: a feature above kScreenMaxAbs (whose partner's sub-normal rounding
+// error of 2^-25 would then matter) sets bit 1 of *needs_robust and the caller repeats the call with algo 2.
+constexpr float kScreenMaxAbs = 1024.f;
+__global__ void __launch_bounds__(256) pack_f16_kernel(const uint4* __restrict__ hi, const uint4* __restrict__ lo,
+                                                       uint4* __restrict__ out, long long n_vec, int* __restrict__ needs_robust) {
+  bool big = false;
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n_vec;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint4 h = hi[t], l = lo[t];
+    const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
+    uint32_t ow[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float x0 = __uint_as_float(hw[q] << 16) + __uint_as_float(lw[q] << 16);
+      const float x1 = __uint_as_float(hw[q] & 0xffff0000u) + __uint_as_float(lw[q] & 0xffff0000u);
+      big |= !(fabsf(x0) <= kScreenMaxAbs) || !(fabsf(x1) <= kScreenMaxAbs);
+      const __half2 v = __floats2half2_rn(x0, x1);
+      ow[q] = *reinterpret_cast<const uint32_t*>(&v);
+    }
+    out[t] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  }
+  if (big) atomicOr(needs_robust, 2);
+}
+
+// One warp per captured element of the screening sweep: the similarity again from the hi + lo planes in fp32, and the
+// exchange of its term in the row / column sums:  delta = 2^(y_exact - LSE) - 2^(y_screen - LSE)  in units of the
+// screening sum, accumulated as 2^-40 fixed point (integer atomics: independent of the order of arrival).
+__global__ void __launch_bounds__(256) cand_rescore_kernel(Candidate* __restrict__ cand, const int* __restrict__ count, int cap,
+                                                           int L, int Lp, int Sp, const __nv_bfloat16* __restrict__ a_hi,
+                                                           const __nv_bfloat16* __restrict__ a_lo,
+                                                           const __nv_bfloat16* __restrict__ b_hi,
+                                                           const __nv_bfloat16* __restrict__ b_lo, float c,
+                                                           const float2* __restrict__ lse_row, const float2* __restrict__ lse_col,
+                                                           unsigned long long* __restrict__ rowdelta,
+                                                           unsigned long long* __restrict__ coldelta) {
+  const int n_c = min(*count, cap);
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < n_c; t += warps) {
+    const Candidate cd = cand[t];
+    if (cd.pad != 2) continue;
+    const int n = cd.row / L, i = cd.row - n * L;
+    const long long ra = static_cast<long long>(n) * Lp + i, rb = static_cast<long long>(n) * Sp + cd.col;
+    const uint4 ah = *reinterpret_cast<const uint4*>(a_hi + ra * FAST_C + lane * 8);
+    const uint4 al = *reinterpret_cast<const uint4*>(a_lo + ra * FAST_C + lane * 8);
+    const uint4 bh = *reinterpret_cast<const uint4*>(b_hi + rb * FAST_C + lane * 8);
+    const uint4 bl = *reinterpret_cast<const uint4*>(b_lo + rb * FAST_C + lane * 8);
+    const uint32_t ahw[4] = {ah.x, ah.y, ah.z, ah.w}, alw[4] = {al.x, al.y, al.z, al.w};
+    const uint32_t bhw[4] = {bh.x, bh.y, bh.z, bh.w}, blw[4] = {bl.x, bl.y, bl.z, bl.w};
+    float acc = 0.f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float a0 = __uint_as_float(ahw[q] << 16) + __uint_as_float(alw[q] << 16);
+      const float a1 = __uint_as_float(ahw[q] & 0xffff0000u) + __uint_as_float(alw[q] & 0xffff0000u);
+      const float b0 = __uint_as_float(bhw[q] << 16) + __uint_as_float(blw[q] << 16);
+      const float b1 = __uint_as_float(bhw[q] & 0xffff0000u) + __uint_as_float(blw[q] & 0xffff0000u);
+      acc = fmaf(a0, b0, acc);
+      acc = fmaf(a1, b1, acc);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+      const float y = __fmul_rn(acc, c);
+      const float2 lr = lse_row[ra], lc = lse_col[rb];
+      const float dr = exp2f((y - lr.x) - lr.y) - exp2f((cd.conf - lr.x) - lr.y);
+      const float dc = exp2f((y - lc.x) - lc.y) - exp2f((cd.conf - lc.x) - lc.y);
+      atomicAdd(&rowdelta[ra], static_cast<unsigned long long>(__double2ll_rn(static_cast<double>(dr) * kDeltaScale)));
+      atomicAdd(&coldelta[rb], static_cast<unsigned long long>(__double2ll_rn(static_cast<double>(dc) * kDeltaScale)));
+      cand[t].conf = y;
+    }
+  }
+}
+
+// LSE of a row / column whose captured terms were exchanged for their exact values: log2(sum * (1 + delta))
+__device__ __forceinline__ float2 corrected_lse(float2 lse, unsigned long long delta_fx) {
+  const float rel = 1.f + static_cast<float>(static_cast<double>(static_cast<long long>(delta_fx)) * (1.0 / kDeltaScale));
+  lse.y += log2f(fmaxf(rel, 1e-30f));
+  return lse;
+}
+
 __global__ void cand_max_kernel(Candidate* __restrict__ cand, const int* __restrict__ count, int cap, int L, int S,
                                 const float2* __restrict__ lse_row, const float2* __restrict__ lse_col, int Lp, int Sp, float thr,
+                                const unsigned long long* __restrict__ rowdelta, const unsigned long long* __restrict__ coldelta,
                                 unsigned* __restrict__ rowmax, unsigned* __restrict__ colmax) {
   const int n_c = min(*count, cap);
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_c; t += gridDim.x * blockDim.x) {
     Candidate c = cand[t];
+    if (c.pad == 2) {  // screening sweep: y is the rescored value, the LSEs take their corrections
+      const int n = c.row / L, i = c.row - n * L;
+      const long long ra = static_cast<long long>(n) * Lp + i, rb = static_cast<long long>(n) * Sp + c.col;
+      const float cf = conf_from(c.conf, corrected_lse(lse_row[ra], rowdelta[ra]), corrected_lse(lse_col[rb], coldelta[rb]));
+      c.conf = cf > thr ? cf : 0.f;
+      c.pad = 0;
+      cand[t] = c;
+    }
     if (c.pad == 1) {  // fast path: the entry holds y; its confidence can be formed now that the LSEs are final
       const int n = c.row / L, i = c.row - n * L;
       const float cf = conf_from(c.conf, lse_row[static_cast<long long>(n) * Lp + i], lse_col[static_cast<long long>(n) * Sp + c.col]);
@@ -682,7 +798,9 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
       const bool cand_over = *cand_count > cand_cap;
       // fast path: a full candidate list or an FTZ-endangered partial asks for the two-pass rerun instead
       overflow[0] = (!fast && cand_over) || (total > capacity);
-      overflow[1] = fast && (cand_over || cand_count[2] != 0);
+      // rerun code: 1 = take the two-pass path, 2 = repeat single-pass with the three split products (fp16 range)
+      const int flag = cand_count[2];
+      overflow[1] = !fast ? 0 : ((cand_over || (flag & 1)) ? 1 : ((flag & 2) ? 2 : 0));
     }
   }
   __syncthreads();
@@ -722,6 +840,8 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 
 struct CoarseWs {
   __nv_bfloat16 *a_hi, *a_lo, *b_hi, *b_lo;
+  __half *a_f16, *b_f16;                       // operand planes of the screening sweep
+  unsigned long long *rowdelta, *coldelta;     // [N*Lp], [N*Sp] fixed-point LSE corrections (cleared per call)
   float2 *rowpart, *colpart;
   float2 *lse_row, *lse_col;
   Candidate* cand;
@@ -748,6 +868,8 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.a_lo = static_cast<__nv_bfloat16*>(take(ra * C * 2));
   w.b_hi = static_cast<__nv_bfloat16*>(take(rb * C * 2));
   w.b_lo = static_cast<__nv_bfloat16*>(take(rb * C * 2));
+  w.a_f16 = static_cast<__half*>(take(ra * C * 2));
+  w.b_f16 = static_cast<__half*>(take(rb * C * 2));
   w.rowpart = static_cast<float2*>(take(static_cast<size_t>(w.Sp / SIM_BN) * ra * 8));
   w.colpart = static_cast<float2*>(take(static_cast<size_t>(4) * (w.Lp / BLOCK_M) * rb * 8));  // fast path: one record per 32-row block
   w.lse_row = static_cast<float2*>(take(ra * 8));
@@ -763,6 +885,8 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.rowmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * L * 4));
   w.colmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * S * 4));
   w.counters = static_cast<int*>(take(16));
+  w.rowdelta = static_cast<unsigned long long*>(take(ra * 8));
+  w.coldelta = static_cast<unsigned long long*>(take(rb * 8));
   w.zero_bytes = off - w.zero_begin;
   w.bytes = off;
   return w;
@@ -789,7 +913,9 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
                              int precision, int algo, void* stream_) {
   if (int r = check_device()) return r;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  OPB_CHECK_ARG(algo == 0 || algo == 1, "algo must be 0 (auto: single-pass where legal) or 1 (two-pass)");
+  OPB_CHECK_ARG(algo >= 0 && algo <= 2,
+                "algo must be 0 (auto: single-pass with the fp16 screening sweep where legal), 1 (two-pass) or 2 (single-pass, "
+                "three split products)");
   OPB_CHECK_ARG(((feat_a && feat_b) || ext) && b_ids && i_ids && j_ids && mconf && count_and_overflow && workspace, "null pointer");
   OPB_CHECK_ARG(n_batch >= 1 && L >= 1 && S >= 1, "empty input");
   OPB_CHECK_ARG(C % BLOCK_K == 0 && C >= BLOCK_K, "feature dim must be a positive multiple of 64");
@@ -833,30 +959,48 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
   OPB_CHECK_CUDA(cudaMemsetAsync(w.rowj, 0x7f, static_cast<size_t>(N) * L * 4, stream));  // kNoMatch
   const int m_tiles = N * (Lp / BLOCK_M), n_tiles = Sp / SIM_BN;
 
-  const bool fast = algo == 0 && x3 && C == FAST_C && mask_a == nullptr && mask_b == nullptr && conf_matrix == nullptr;
+  const bool fast = algo != 1 && x3 && C == FAST_C && mask_a == nullptr && mask_b == nullptr && conf_matrix == nullptr;
+  const bool screen = fast && algo == 0;
   int n_row_parts = n_tiles, n_col_parts = Lp / BLOCK_M;
   if (fast) {
     SimFastParams fp;
     int r;
-    if ((r = make_tmap_bf16(&fp.a_hi, w.a_hi, static_cast<uint64_t>(N) * Lp, C, C, BLOCK_M))) return r;
-    if ((r = make_tmap_bf16(&fp.a_lo, w.a_lo, static_cast<uint64_t>(N) * Lp, C, C, BLOCK_M))) return r;
-    if ((r = make_tmap_bf16(&fp.b_hi, w.b_hi, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
-    if ((r = make_tmap_bf16(&fp.b_lo, w.b_lo, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
+    if (screen) {  // fp16 operand planes of the sweep (the data type of a tensor map only matters for its fill value)
+      const long long va = static_cast<long long>(N) * Lp * C / 8, vb = static_cast<long long>(N) * Sp * C / 8;
+      pack_f16_kernel<<<static_cast<unsigned>((va + 255) / 256 < 1184 ? (va + 255) / 256 : 1184), 256, 0, stream>>>(
+          reinterpret_cast<const uint4*>(w.a_hi), reinterpret_cast<const uint4*>(w.a_lo), reinterpret_cast<uint4*>(w.a_f16), va,
+          w.counters + 2);
+      pack_f16_kernel<<<static_cast<unsigned>((vb + 255) / 256 < 1184 ? (vb + 255) / 256 : 1184), 256, 0, stream>>>(
+          reinterpret_cast<const uint4*>(w.b_hi), reinterpret_cast<const uint4*>(w.b_lo), reinterpret_cast<uint4*>(w.b_f16), vb,
+          w.counters + 2);
+      count_launch(2);
+      if ((r = make_tmap_bf16(&fp.a_hi, w.a_f16, static_cast<uint64_t>(N) * Lp, C, C, BLOCK_M))) return r;
+      if ((r = make_tmap_bf16(&fp.b_hi, w.b_f16, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
+      fp.a_lo = fp.a_hi, fp.b_lo = fp.b_hi;
+    } else {
+      if ((r = make_tmap_bf16(&fp.a_hi, w.a_hi, static_cast<uint64_t>(N) * Lp, C, C, BLOCK_M))) return r;
+      if ((r = make_tmap_bf16(&fp.a_lo, w.a_lo, static_cast<uint64_t>(N) * Lp, C, C, BLOCK_M))) return r;
+      if ((r = make_tmap_bf16(&fp.b_hi, w.b_hi, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
+      if ((r = make_tmap_bf16(&fp.b_lo, w.b_lo, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
+    }
     fp.N = N, fp.L = L, fp.S = S, fp.Lp = Lp, fp.Sp = Sp;
     fp.n_tiles = n_tiles;
     fp.total_tiles = m_tiles * n_tiles;
     fp.c = scale * kLog2e;
-    fp.thr_lim = 0.99f * thr;
+    fp.thr_lim = (screen ? 0.9f : 0.99f) * thr;
+    fp.cand_tag = screen ? 2 : 1;
     fp.rowpart = w.rowpart, fp.colpart = w.colpart;
     fp.cand = w.cand, fp.cand_count = w.counters, fp.cand_cap = w.cand_cap;
     fp.needs_robust = w.counters + 2;
     static bool configured = false;
     if (!configured) {
-      OPB_CHECK_CUDA(cudaFuncSetAttribute(sim_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FAST_SMEM));
+      OPB_CHECK_CUDA(cudaFuncSetAttribute(sim_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FastCfg<false>::SMEM));
+      OPB_CHECK_CUDA(cudaFuncSetAttribute(sim_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FastCfg<true>::SMEM));
       configured = true;
     }
     const int grid = fp.total_tiles < num_sms() ? fp.total_tiles : num_sms();
-    sim_fast_kernel<<<grid, 64 + 128 * FAST_GROUPS, FAST_SMEM, stream>>>(fp);
+    if (screen) sim_fast_kernel<true><<<grid, 64 + 128 * FAST_GROUPS, FastCfg<true>::SMEM, stream>>>(fp);
+    else sim_fast_kernel<false><<<grid, 64 + 128 * FAST_GROUPS, FastCfg<false>::SMEM, stream>>>(fp);
     count_launch();
     OPB_CHECK_CUDA(cudaGetLastError());
     n_col_parts = 4 * (Lp / BLOCK_M);
@@ -911,7 +1055,13 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
   }
   BorderRule br{border_mode, border_rm, h0, w0, h1, w1, valid_hw};
   const int cb = (w.cand_cap + 255) / 256 < 592 ? (w.cand_cap + 255) / 256 : 592;
-  cand_max_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.lse_row, w.lse_col, Lp, Sp, thr, w.rowmax, w.colmax);
+  if (screen) {
+    cand_rescore_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, Lp, Sp, w.a_hi, w.a_lo, w.b_hi, w.b_lo,
+                                                scale * kLog2e, w.lse_row, w.lse_col, w.rowdelta, w.coldelta);
+    count_launch();
+  }
+  cand_max_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.lse_row, w.lse_col, Lp, Sp, thr, w.rowdelta,
+                                          w.coldelta, w.rowmax, w.colmax);
   cand_pick_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.rowmax, w.colmax, br, w.rowj);
   compact_kernel<<<1, 1024, 0, stream>>>(w.rowj, w.rowmax, N * L, L, reinterpret_cast<long long*>(b_ids),
                                          reinterpret_cast<long long*>(i_ids), reinterpret_cast<long long*>(j_ids), mconf, capacity,

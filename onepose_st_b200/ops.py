@@ -253,10 +253,10 @@ def coarse_match_finish(h: CoarseLaunch, copy: bool = False):
     torch.where).  Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None); ``copy`` detaches the results from the
     launch's buffers (needed when those are the static buffers of a CUDA graph)."""
     m, overflow, rerun = h.cnt.tolist()
-    if rerun:  # the single-pass statistics hit their dynamic-range guard: take the two-pass path
-        kw = dict(h.retry)
+    if rerun:  # 1: the single-pass statistics hit their dynamic-range guard -> two-pass path;
+        kw = dict(h.retry)  # 2: features outside the fp16 screening range -> single pass on the three split products
         a, b = kw.pop("feat_a"), kw.pop("feat_b")
-        return coarse_match(a, b, algo=1, **kw)
+        return coarse_match(a, b, algo=1 if rerun == 1 else 2, **kw)
     b_ids, i_ids, j_ids, mconf = h.outs
     if overflow:
         import os

@@ -117,17 +117,20 @@ def test_large_no_materialize_matches_materialize(L, S, hw):
     sim = (f3d.to(dev)[0] @ f2d.to(dev)[0].t()) / (256 * 0.0801)
     ref = torch.softmax(sim, 0) * torch.softmax(sim, 1)
     assert (conf[0] - ref).abs().max().item() < CONF_TOL
-    # single-pass default
-    f = ops.coarse_match(f3d.to(dev), f2d.to(dev), **kw)
-    got, want = _sets(f[0], f[1], f[2]), _sets(a[0], a[1], a[2])
-    for (bb, ii, jj) in got ^ want:  # only threshold-straddling entries may differ
-        assert abs(conf[bb, ii, jj].item() - 0.1) < 1e-4
-    assert len(got ^ want) <= 2
-    if got == want:
-        assert torch.equal(f[1], a[1]) and torch.equal(f[2], a[2])
-        err = (f[3] - a[3]).abs().max().item()
-        print(f"single-pass vs two-pass mconf max abs diff {err:.2e}")
-        assert err < 1e-5
+    # single-pass: algo 2 = three split products (same precision as two-pass), algo 0 = default, fp16 screening sweep
+    # with exact re-evaluation of every captured element (confidence contract: max-abs CONF_TOL)
+    for algo, tol in ((2, 1e-5), (0, CONF_TOL)):
+        f = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=algo, **kw)
+        got, want = _sets(f[0], f[1], f[2]), _sets(a[0], a[1], a[2])
+        for (bb, ii, jj) in got ^ want:  # only threshold-straddling entries may differ
+            assert abs(conf[bb, ii, jj].item() - 0.1) < 10 * tol
+        assert len(got ^ want) <= (2 if algo == 2 else 8)
+        both = sorted(got & want)
+        fi = {k: v for k, v in zip(zip(f[0].tolist(), f[1].tolist(), f[2].tolist()), f[3].tolist())}
+        ai = {k: v for k, v in zip(zip(a[0].tolist(), a[1].tolist(), a[2].tolist()), a[3].tolist())}
+        err = max(abs(fi[k] - ai[k]) for k in both)
+        print(f"single-pass (algo {algo}) vs two-pass mconf max abs diff {err:.2e}, set difference {len(got ^ want)}")
+        assert err < tol
 
 
 @pytest.mark.parametrize("n,L,S,hw", [(2, 300, 256, (16, 16)), (1, 128, 128, (8, 16)), (3, 129, 200, (10, 20))])
@@ -137,10 +140,13 @@ def test_single_pass_small_and_batched(n, L, S, hw):
     dev = "cuda"
     f3d, f2d = cases.planted_pair(33, n, L, S, 256, min(100, L // 2), hw[0], hw[1], 2, gain=0.6)
     kw = dict(scale=1.0 / (256 * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=hw)
-    f = ops.coarse_match(f3d.to(dev), f2d.to(dev), **kw)
     a = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=1, **kw)
-    assert torch.equal(f[0], a[0]) and torch.equal(f[1], a[1]) and torch.equal(f[2], a[2])
-    assert (f[3] - a[3]).abs().max().item() < 1e-5
+    for algo, tol in ((2, 1e-5), (0, CONF_TOL)):
+        f = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=algo, **kw)
+        assert torch.equal(f[0], a[0]) and torch.equal(f[1], a[1]) and torch.equal(f[2], a[2])
+        err = (f[3] - a[3]).abs().max().item()
+        print(f"single-pass (algo {algo}) vs two-pass mconf max abs diff {err:.2e}")
+        assert err < tol
     assert len(f[0]) > 20 * n
     sim = torch.einsum("nlc,nsc->nls", f3d, f2d).double() / (256 * 0.0801)
     conf = torch.softmax(sim, 1) * torch.softmax(sim, 2)
@@ -169,3 +175,21 @@ def test_single_pass_dynamic_range_guard_reruns_two_pass():
     keep = R._border_keep_onepose(1, 256, hw[0], hw[1], 2, "cpu")
     rb, ri, rj, rc = R.coarse_select(conf, 0.1, keep)
     assert torch.equal(ri, a[1].cpu()) and torch.equal(rj, a[2].cpu())
+
+
+def test_screening_sweep_fp16_range_guard_reruns_on_split_products():
+    """Features beyond +-1024 are outside the range in which the fp16 screening operands keep their 11 bits against
+    any partner: the call must flag it and the wrapper must return the three-product single-pass result."""
+    from onepose_st_b200 import ops
+    dev = "cuda"
+    hw = (16, 16)
+    f3d, f2d = cases.planted_pair(35, 1, 256, 256, 256, 80, hw[0], hw[1], 2, gain=0.6)
+    f3d, f2d = f3d * 4096.0, f2d / 4096.0      # same similarities, operands far apart in magnitude
+    kw = dict(scale=1.0 / (256 * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=hw)
+    f = ops.coarse_match(f3d.to(dev), f2d.to(dev), **kw)
+    e = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=2, **kw)
+    for x, y in zip(f[:4], e[:4]):
+        assert torch.equal(x, y)
+    a = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=1, **kw)
+    assert torch.equal(e[1], a[1]) and torch.equal(e[2], a[2]) and len(a[0]) > 20
+    assert (e[3] - a[3]).abs().max().item() < 1e-5

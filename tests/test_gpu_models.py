@@ -76,11 +76,12 @@ def test_onepose_model_default_omits_conf_matrix_and_matches():
     a(da)
     b(db)
     assert "conf_matrix" not in db
-    # the default (single-pass) coarse matcher accumulates in a different order than the materialising
-    # two-pass one: same index sets, values to fp32 rounding
+    # the default (single-pass) coarse matcher sweeps the similarities with one fp16 product and re-evaluates the
+    # captured elements exactly: same index sets, confidences inside the 1e-3 contract (measured ~1e-5 here)
     for k in ("i_ids", "j_ids"):
         assert torch.equal(da[k], db[k])
-    for k, tol in (("mconf", 1e-5), ("mkpts_query_f", 1e-3), ("expec_f", 1e-4)):
+    print("default vs materialising path: mconf max abs diff", (da["mconf"] - db["mconf"]).abs().max().item())
+    for k, tol in (("mconf", 1e-3), ("mkpts_query_f", 1e-3), ("expec_f", 1e-4)):
         assert (da[k] - db[k]).abs().max().item() < tol, k
 
 

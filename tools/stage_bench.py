@@ -57,7 +57,7 @@ def run_coarse(a):
         for mat in ([False, True] if a.materialize else [False]):
             def fn():
                 return ops.coarse_match(f3d, f2d, scale=scale, thr=0.1, border_rm=2, border_mode=0, grid_a=None,
-                                        grid_b=(hc, wc), materialize_conf=mat, precision=a.precision)
+                                        grid_b=(hc, wc), materialize_conf=mat, precision=a.precision, algo=a.algo)
             ops.stage_events = {}
             med, best = time_op(fn, a.iters, warmup=0 if a.iters == 1 else 3)
             evs = ops.stage_events["coarse_match"][-a.iters:]
@@ -65,7 +65,7 @@ def run_coarse(a):
             dev_ms = sorted(x.elapsed_time(y) for x, y in evs)[len(evs) // 2]
             m = fn()[0].numel()
             flops = 2.0 * L * S * C
-            line = {"op": "coarse_match", "L": L, "S": S, "C": C, "materialize_conf": mat, "precision": a.precision,
+            line = {"op": "coarse_match", "L": L, "S": S, "C": C, "materialize_conf": mat, "precision": a.precision, "algo": a.algo,
                     "matches": m, "ms_call_incl_host_sync": med, "ms_device": dev_ms,
                     "algorithmic_gflop": flops / 1e9, "tflops": flops / dev_ms / 1e9,
                     "frac_tensor": flops / dev_ms / 1e9 / tf, "peak": f"{tf} TFLOP/s bf16 burst ({src})"}
@@ -232,6 +232,7 @@ def main():
     ap.add_argument("--grid", type=int, default=64)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--precision", type=int, default=3)
+    ap.add_argument("--algo", type=int, default=0, help="coarse: 0 = fp16 screening sweep, 1 = two-pass, 2 = single pass x3")
     ap.add_argument("--materialize", action="store_true")
     a = ap.parse_args()
     {"coarse": run_coarse, "transformer": run_transformer, "fine": run_fine, "loftr": run_loftr, "conv": run_conv}[a.what](a)
