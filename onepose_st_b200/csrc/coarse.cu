@@ -33,6 +33,7 @@ int split_planes(const float* x, long long stride_r, long long stride_c, const f
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kNegInf = -INFINITY;
 constexpr int kNoMatch = 0x7f7f7f7f;
+constexpr float kTinySum = 1.262177e-29f;  // 2^-96: single-pass sums below this may have lost terms to flush-to-zero
 constexpr int SIM_BN = 128;  // rowj sentinel (what cudaMemsetAsync(0x7f) leaves)
 
 struct SimGeom {
@@ -145,7 +146,8 @@ struct EpiSimStats {
 // slices are combined through shared memory in a fixed order (deterministic).
 __global__ void __launch_bounds__(256) merge_stats_kernel(const float2* __restrict__ rowpart, int n_row_parts, long long n_rows,
                                                           const float2* __restrict__ colpart, int n_col_parts, long long n_cols,
-                                                          float2* __restrict__ lse_row, float2* __restrict__ lse_col) {
+                                                          float2* __restrict__ lse_row, float2* __restrict__ lse_col,
+                                                          int* __restrict__ needs_robust) {
   __shared__ float2 sm[8][33];
   const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
   const long long t = static_cast<long long>(blockIdx.x) * 32 + lane;
@@ -188,6 +190,8 @@ __global__ void __launch_bounds__(256) merge_stats_kernel(const float2* __restri
     // kept as (max, log2 sum) rather than their sum: for a fully masked row/column max = -1.44e9 and
     // adding log2(sum) to it would be lost to rounding, turning 1/(L*S) confidences into 1.0
     out[idx] = make_float2(Mt, (Mt > kNegInf) ? log2f(St) : 0.f);
+    // single-pass sweep: a finished sum that is not safely above the flush-to-zero range (or is NaN) cannot be trusted
+    if (needs_robust != nullptr && Mt > kNegInf && !(St >= kTinySum)) atomicOr(needs_robust, 1);
   }
 }
 
@@ -317,152 +321,272 @@ constexpr int FAST_GROUPS = 4;
 constexpr int FAST_C = 256;
 constexpr int FAST_KB = FAST_C / BLOCK_K;           // 4 k-blocks
 constexpr int FAST_SUB = BLOCK_M * BLOCK_K * 2;     // one [128 x 64] 16-bit sub-tile: 16 KB
+constexpr int FAST_COLBUF_ONE = 4 * SIM_BN + 4;                   // [quarter][128] column sums of one tile + the 4 references
+constexpr int FAST_COLBUF = FAST_GROUPS * 2 * FAST_COLBUF_ONE * 4;  // [group][tile parity]
 template <bool SCREEN>
 struct FastCfg {
   static constexpr int PLANES = SCREEN ? 1 : 2;                   // fp16 plane | bf16 hi + lo planes
-  static constexpr int BSTAGES = SCREEN ? 6 : 3;
+  // N of one MMA.  At N = 128 a 128 x 128 x 16 MMA reads 8 KB of shared memory in its 64 clocks -- all of the 128 B/clk
+  // an SM has, with the TMA fill on top; N = 256 needs 96 B/clk.  The split variant has no room for 256-wide stages.
+  static constexpr int BN = 128;
+  static constexpr int HALVES = BN / SIM_BN;                      // 128-column halves of an accumulator, one per epilogue group
+  static constexpr int TSTAGES = 512 / BN;                        // accumulator stages in TMEM
+  static constexpr int BSTAGES = SCREEN ? 6 : 2;
   static constexpr int A_BYTES = PLANES * FAST_KB * FAST_SUB;     // the resident A block
-  static constexpr int BSTAGE_BYTES = PLANES * FAST_SUB;          // one B k-block
-  static constexpr int SMEM = 1024 + A_BYTES + BSTAGES * BSTAGE_BYTES + 256;
+  static constexpr int BSTAGE_BYTES = PLANES * HALVES * FAST_SUB; // one B k-block: [plane][BN rows x 64]
+  static constexpr int SMEM = 1024 + A_BYTES + BSTAGES * BSTAGE_BYTES + 256 + FAST_COLBUF;
 };
-constexpr float kTinySum = 7.888609e-31f;           // 2^-100: partial sums below this may have lost terms to FTZ
 constexpr double kDeltaScale = 1099511627776.0;     // 2^40: fixed-point unit of the LSE corrections
 
 struct SimFastParams {
   CUtensorMap a_hi, a_lo, b_hi, b_lo;  // [rows, 256] bf16, box 128 x 64, 128B swizzle (SCREEN: a_hi / b_hi = the fp16 planes)
   int N, L, S, Lp, Sp;
-  int n_tiles;      // Sp / 128
+  int n_tiles;      // ceil(Sp / BN) column tiles of the sweep
   int total_tiles;  // N * (Lp/128) * n_tiles, m-major
-  float c;          // scale * log2(e)
+  float c;          // scale * log2(e)  (> 0)
   float thr_lim;    // 0.99 * thr (slack for the approximate exponentials); 0.9 * thr when screening
   int cand_tag;     // Candidate::pad of captured elements: 1 = y is final, 2 = y is the screening value (rescore)
-  float2* rowpart;  // [n_tiles][N*Lp]
-  float2* colpart;  // [4*Lp/128][N*Sp]
+  float2* rowpart;  // [Sp/128][N*Lp]    (T, sum_j e_ij) over 128 columns
+  float2* colpart;  // [Lp/128][N*Sp]    (T, sum_i e_ij) over the tile's rows
   Candidate* cand;
   int* cand_count;
   int cand_cap;
-  int* needs_robust;
 };
 
-// lane j <- sum over the 32 lanes of e[j]  (recursive halving: 31 shuffles)
-__device__ __forceinline__ float warp_transpose_sum(float (&e)[32], int lane) {
-#pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) {
-    const bool up = (lane & off) != 0;
-#pragma unroll
-    for (int k = 0; k < off; ++k) {
-      const float keep = up ? e[k + off] : e[k];
-      const float send = up ? e[k] : e[k + off];
-      e[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-    }
-  }
-  return e[0];
+// (e0, e1) = 2^(c v - T) of two neighbouring columns: one packed FMA, two MUFU
+__device__ __forceinline__ uint64_t exp2_pair(uint32_t v0, uint32_t v1, uint64_t c2, uint64_t t2) {
+  float x0, x1;
+  ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(v0), __uint_as_float(v1)), c2, t2), x0, x1);
+  return ptx::pack_f32x2(ptx::ex2(x0), ptx::ex2(x1));
 }
 
+// order-preserving map of a float's bits to a signed integer (for redux.sync.max)
+__device__ __forceinline__ int float_key(float v) {
+  const int b = __float_as_int(v);
+  return b ^ ((b >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float key_float(int k) { return __int_as_float(k ^ ((k >> 31) & 0x7fffffff)); }
+
+constexpr float kRefWindow = 60.f;  // a tile keeps its reference exponent while its maximum stays within +-60 octaves of it
+
+// Epilogue of one warp = 32 rows x 128 columns of a tile, read in the mma C-fragment layout (tmem_ld_16x256b_x4):
+// thread t holds rows rsub + 8h (rsub = t/4, h = 0..3) and, per 32-column chunk, the column pairs 8k + 2(t%4) + {0,1}.
+// Row sums therefore stay in registers until the tile ends (two xor-shuffles over t%4), and a column sum needs only the
+// 8 threads t/4: a 7-shuffle halving butterfly per chunk leaves one finished column in every lane (the lane = row
+// layout needs 31).  All adds run as packed f32x2.
+//   e_ij = 2^(y_ij - T) with ONE reference T for the warp's whole 32 x 128 block, so a single ex2 serves the row and
+// the column sum.  T is a guess -- the block maximum this warp saw on its previous tile -- checked after the fact: the
+// raw maximum of the block is tracked alongside (FMNMX3, no dependency on T), and if it left the window
+// [T - 60, T + 60] octaves the block is simply swept again from TMEM with T = its own maximum (rare: neighbouring
+// tiles of the same rows have similar maxima; always on a warp's first tile).  Partials are (T, sum) records; the four
+// warps of the group merge their quarters through shared memory (one named barrier per tile, buffers alternate with
+// the tile parity) and merge_stats_kernel folds the records of different tiles.
+// Carried by a warp from tile to tile: the reference guess, and -- while the tiles belong to the same 128-row block -- a
+// lower bound of each row's full sum (everything this warp has seen of the row so far), which is what the candidate
+// limit is taken from: the more of a row has gone by, the fewer of its elements can still reach thr.
+struct FastWarpState {
+  float T = INFINITY;     // no guess yet: the first tile is swept twice
+  int run_m = -1;         // m tile of the running sums
+  float run_T = 0.f;      // their reference
+  float run_s[4] = {0.f, 0.f, 0.f, 0.f};
+};
+
 template <bool RAGGED>
-__device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32_t tmem_acc, int m_tile, int n_tile,
-                                                  int quarter, int lane) {
+__device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32_t tmem_acc, int m_tile, int jt, int quarter,
+                                                  int lane, float* __restrict__ colbuf, int group, FastWarpState& st,
+                                                  uint64_t* __restrict__ tempty_bar) {
+  float T = st.T;
   const int tiles_per_batch = p.Lp / BLOCK_M;
   const int n = m_tile / tiles_per_batch;
   const int mt_in_batch = m_tile - n * tiles_per_batch;
-  const int i = mt_in_batch * BLOCK_M + quarter * 32 + lane;  // row within the batch element
-  const bool row_valid = !RAGGED || i < p.L;
-  const long long grow = static_cast<long long>(n) * p.Lp + i;
-  float T = kNegInf, s = 0.f, amax = kNegInf;
-  float2* cp = p.colpart + (static_cast<long long>(mt_in_batch) * 4 + quarter) * p.N * p.Sp + static_cast<long long>(n) * p.Sp;
-  bool tiny = false;
+  const int cq = (lane & 3) * 2;
+  const int i0 = mt_in_batch * BLOCK_M + quarter * 32 + (lane >> 2);  // this thread's rows: i0 + 8h
+  const uint64_t c2 = ptx::pack_f32x2(p.c, p.c);
+  bool rv[4];
+#pragma unroll
+  for (int h = 0; h < 4; ++h) rv[h] = !RAGGED || i0 + 8 * h < p.L;
+  uint64_t racc[4];
+  float rmax[4];  // raw accumulator maxima per row
+  float ymax;
 #pragma unroll 1
-  for (int c0 = 0; c0 < SIM_BN; c0 += 32) {
-    float v[32];
-    load_acc32(tmem_acc + c0, v);
-    const int j0 = n_tile * SIM_BN + c0;
-    if (RAGGED) {
+  for (int attempt = 0;; ++attempt) {
+    const uint64_t t2 = ptx::pack_f32x2(-T, -T);
 #pragma unroll
-      for (int k = 0; k < 32; ++k)
-        if (!row_valid || j0 + k >= p.S) v[k] = kNegInf;
-    }
-    float tm = v[0];
-#pragma unroll
-    for (int k = 1; k < 32; ++k) tm = fmaxf(tm, v[k]);
-    amax = fmaxf(amax, tm);
-    float wm = tm;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) wm = fmaxf(wm, __shfl_xor_sync(0xffffffffu, wm, o));
-    const float Tn = fmaxf(T, wm * p.c);
-    if (Tn == kNegInf) {  // nothing valid in this 32 x 32 block (ragged edge only)
-      if (j0 + lane < p.Sp) cp[j0 + lane] = make_float2(kNegInf, 0.f);
-      continue;
-    }
-    if (T > kNegInf) s *= ptx::ex2(T - Tn);
-    T = Tn;
-    float rs0 = 0.f, rs1 = 0.f, rs2 = 0.f, rs3 = 0.f;
-#pragma unroll
-    for (int k = 0; k < 32; k += 4) {
-      v[k + 0] = ptx::ex2(fmaf(v[k + 0], p.c, -T));
-      v[k + 1] = ptx::ex2(fmaf(v[k + 1], p.c, -T));
-      v[k + 2] = ptx::ex2(fmaf(v[k + 2], p.c, -T));
-      v[k + 3] = ptx::ex2(fmaf(v[k + 3], p.c, -T));
-      rs0 += v[k + 0];
-      rs1 += v[k + 1];
-      rs2 += v[k + 2];
-      rs3 += v[k + 3];
-    }
-    s += (rs0 + rs1) + (rs2 + rs3);
-    const float cs = warp_transpose_sum(v, lane);
-    const int j = j0 + lane;
-    if (j < p.Sp) cp[j] = make_float2(T, cs);
-    if ((!RAGGED || j < p.S) && cs < kTinySum) tiny = true;
-  }
-  p.rowpart[static_cast<long long>(n_tile) * p.N * p.Lp + grow] = make_float2(T, s);
-  if (row_valid && s < kTinySum) tiny = true;
-  if (__any_sync(0xffffffffu, tiny) && lane == 0) atomicOr(p.needs_robust, 1);
-  // candidate capture: conf_ij > thr needs e_ij > thr * (row sum over this tile), i.e. acc_ij > vlim_i in raw
-  // accumulator units -- one compare per element on a second sweep over TMEM, taken only when some row of the
-  // warp has its maximum above the limit
-  const float lim = p.thr_lim * s;
-  const float vlim = (row_valid && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
-  if (__any_sync(0xffffffffu, amax > vlim)) {
+    for (int h = 0; h < 4; ++h) racc[h] = 0ull, rmax[h] = kNegInf;
 #pragma unroll 1
-    for (int c0 = 0; c0 < SIM_BN; c0 += 32) {
-      float v[32];
-      load_acc32(tmem_acc + c0, v);
-      const int j0 = n_tile * SIM_BN + c0;
-      unsigned mask = 0;
+    for (int ch = 0; ch < SIM_BN / 32; ++ch) {
+      uint32_t va[16], vb[16];
+      ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
+      ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
+      ptx::tmem_ld_wait();
+      if (RAGGED) {  // rows / columns that do not exist: -inf, i.e. e = 0 and no say in the maximum
 #pragma unroll
-      for (int k = 0; k < 32; ++k)
-        if (v[k] > vlim && (!RAGGED || j0 + k < p.S)) mask |= 1u << k;
-      unsigned any = __reduce_or_sync(0xffffffffu, mask);
-      while (any) {  // warp-uniform loop over the (rare) columns with a candidate in some lane
-        const int k = __ffs(any) - 1;
-        any &= any - 1;
-        float val = v[0];
-#pragma unroll
-        for (int q = 1; q < 32; ++q) val = (k == q) ? v[q] : val;
-        if ((mask >> k) & 1u) {
-          const int slot = atomicAdd(p.cand_count, 1);
-          if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i, j0 + k, __fmul_rn(val, p.c), p.cand_tag};
+        for (int q = 0; q < 16; ++q) {
+          const bool cv = jt + ch * 32 + 8 * (q >> 2) + cq + (q & 1) < p.S;
+          if (!cv || !rv[(q >> 1) & 1]) va[q] = __float_as_uint(kNegInf);
+          if (!cv || !rv[2 + ((q >> 1) & 1)]) vb[q] = __float_as_uint(kNegInf);
         }
       }
+      float f[4][2];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        rmax[0] = ptx::max3(rmax[0], __uint_as_float(va[4 * k]), __uint_as_float(va[4 * k + 1]));
+        rmax[1] = ptx::max3(rmax[1], __uint_as_float(va[4 * k + 2]), __uint_as_float(va[4 * k + 3]));
+        rmax[2] = ptx::max3(rmax[2], __uint_as_float(vb[4 * k]), __uint_as_float(vb[4 * k + 1]));
+        rmax[3] = ptx::max3(rmax[3], __uint_as_float(vb[4 * k + 2]), __uint_as_float(vb[4 * k + 3]));
+        const uint64_t e0 = exp2_pair(va[4 * k], va[4 * k + 1], c2, t2), e1 = exp2_pair(va[4 * k + 2], va[4 * k + 3], c2, t2);
+        const uint64_t e2 = exp2_pair(vb[4 * k], vb[4 * k + 1], c2, t2), e3 = exp2_pair(vb[4 * k + 2], vb[4 * k + 3], c2, t2);
+        racc[0] = ptx::add_f32x2(racc[0], e0);
+        racc[1] = ptx::add_f32x2(racc[1], e1);
+        racc[2] = ptx::add_f32x2(racc[2], e2);
+        racc[3] = ptx::add_f32x2(racc[3], e3);
+        ptx::unpack_f32x2(ptx::add_f32x2(ptx::add_f32x2(e0, e1), ptx::add_f32x2(e2, e3)), f[k][0], f[k][1]);
+      }
+      // halving butterfly over the row bits of the lane id (16, 8, 4): 4 + 2 + 1 shuffles
+      float g[2][2], hh[2];
+      {
+        const bool up = (lane & 16) != 0;
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            const float keep = up ? f[kk + 2][b] : f[kk][b];
+            const float send = up ? f[kk][b] : f[kk + 2][b];
+            g[kk][b] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+          }
+      }
+      {
+        const bool up = (lane & 8) != 0;
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          const float keep = up ? g[1][b] : g[0][b];
+          const float send = up ? g[0][b] : g[1][b];
+          hh[b] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+      }
+      const bool up4 = (lane & 4) != 0;
+      const float cs = (up4 ? hh[1] : hh[0]) + __shfl_xor_sync(0xffffffffu, up4 ? hh[0] : hh[1], 4);
+      // lane bits 4,3 select k, bit 2 selects the column of the pair
+      colbuf[quarter * SIM_BN + ch * 32 + ((lane >> 3) & 3) * 8 + cq + ((lane >> 2) & 1)] = cs;
+    }
+    const float tm = fmaxf(fmaxf(rmax[0], rmax[1]), fmaxf(rmax[2], rmax[3]));
+    ymax = key_float(__reduce_max_sync(0xffffffffu, float_key(tm))) * p.c;
+    // the maximum is inside the window (or there is nothing here at all, or this already is the second sweep)
+    if (attempt > 0 || ymax == kNegInf || fabsf(ymax - T) <= kRefWindow) break;
+    T = ymax;
+  }
+  const bool empty = ymax == kNegInf;  // ragged edge: no existing element in this warp's block
+  float s[4], mx[4];
+#pragma unroll
+  for (int h = 0; h < 4; ++h) {
+    float lo, hi;
+    ptx::unpack_f32x2(racc[h], lo, hi);
+    float v = lo + hi;
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    s[h] = v;
+    float m = rmax[h];
+    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+    mx[h] = m;
+  }
+  // candidate capture: conf_ij > thr needs e_ij > thr * (row sum), and the part of the row this warp has seen so far
+  // bounds that sum from below, i.e. acc_ij > vlim_i in raw accumulator units -- one compare per element on a second
+  // sweep over TMEM, taken only when some row of the warp has its maximum above the limit
+  float vlim[4];
+  bool trig = false;
+  if (!empty) {
+    if (st.run_m != m_tile) {
+      st.run_m = m_tile, st.run_T = T;
+#pragma unroll
+      for (int h = 0; h < 4; ++h) st.run_s[h] = 0.f;
+    }
+    // (clamps keep it a finite lower bound when the reference moves far down)
+    const float f = ptx::ex2(fminf(st.run_T - T, 60.f));
+    st.run_T = T;
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      st.run_s[h] = fminf(st.run_s[h] * f, 1e30f) + s[h];
+      const float lim = p.thr_lim * st.run_s[h];
+      vlim[h] = (rv[h] && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
+      trig |= mx[h] > vlim[h];
     }
   }
+  if (__any_sync(0xffffffffu, trig)) {
+#pragma unroll 1
+    for (int ch = 0; ch < SIM_BN / 32; ++ch) {
+      uint32_t va[16], vb[16];
+      ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
+      ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
+      ptx::tmem_ld_wait();
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          any |= __uint_as_float(va[4 * k + q]) > vlim[q >> 1];
+          any |= __uint_as_float(vb[4 * k + q]) > vlim[2 + (q >> 1)];
+        }
+      if (!__any_sync(0xffffffffu, any)) continue;
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int h = q >> 1, b = q & 1;
+          const float val = __uint_as_float(h < 2 ? va[4 * k + 2 * h + b] : vb[4 * k + 2 * (h - 2) + b]);
+          const int j = jt + ch * 32 + 8 * k + cq + b;
+          if (val > vlim[h] && (!RAGGED || j < p.S)) {
+            const int slot = atomicAdd(p.cand_count, 1);
+            if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i0 + 8 * h, j, __fmul_rn(val, p.c), p.cand_tag};
+          }
+        }
+    }
+  }
+  // the accumulator is no longer needed: hand the TMEM stage back before the bookkeeping below
+  ptx::tc_fence_before();
+  __syncwarp();
+  if (lane == 0) ptx::mbar_arrive(tempty_bar);
+  {
+    const int h = lane & 3;
+    const float sv = h == 0 ? s[0] : (h == 1 ? s[1] : (h == 2 ? s[2] : s[3]));
+    const bool ex = !empty && (!RAGGED || i0 + 8 * h < p.L);
+    p.rowpart[(static_cast<long long>(jt / SIM_BN) * p.N + n) * p.Lp + i0 + 8 * h] = make_float2(ex ? T : kNegInf, ex ? sv : 0.f);
+  }
+  if (lane == 0) colbuf[4 * SIM_BN + quarter] = empty ? kNegInf : T;
+  epi_bar(group);
+  {
+    const int j = quarter * 32 + lane;
+    const float t0 = colbuf[4 * SIM_BN], t1 = colbuf[4 * SIM_BN + 1], t2q = colbuf[4 * SIM_BN + 2], t3 = colbuf[4 * SIM_BN + 3];
+    const float tm = fmaxf(fmaxf(t0, t1), fmaxf(t2q, t3));
+    float cs = 0.f;
+    if (tm > kNegInf) {  // fixed order; 2^(-inf) = 0 drops an empty quarter, equal references scale by exactly 1
+      cs = (colbuf[j] * ptx::ex2(t0 - tm) + colbuf[SIM_BN + j] * ptx::ex2(t1 - tm)) +
+           (colbuf[2 * SIM_BN + j] * ptx::ex2(t2q - tm) + colbuf[3 * SIM_BN + j] * ptx::ex2(t3 - tm));
+    }
+    const bool ex = tm > kNegInf && (!RAGGED || jt + j < p.S);
+    p.colpart[(static_cast<long long>(mt_in_batch) * p.N + n) * p.Sp + jt + j] = make_float2(ex ? tm : kNegInf, ex ? cs : 0.f);
+  }
+  if (!empty) st.T = ymax;  // the next tile's guess
 }
 
 template <bool SCREEN>
 __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(const __grid_constant__ SimFastParams p) {
   constexpr int FAST_A_BYTES = FastCfg<SCREEN>::A_BYTES, FAST_BSTAGES = FastCfg<SCREEN>::BSTAGES;
   constexpr int FAST_BSTAGE_BYTES = FastCfg<SCREEN>::BSTAGE_BYTES;
+  constexpr int BN = FastCfg<SCREEN>::BN, HALVES = FastCfg<SCREEN>::HALVES, TSTAGES = FastCfg<SCREEN>::TSTAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;                  // [plane 0/1][kb][128 x 64]
-  uint8_t* smem_b = smem + FAST_A_BYTES;   // [stage][plane 0/1][128 x 64]
+  uint8_t* smem_b = smem + FAST_A_BYTES;   // [stage][plane 0/1][BN x 64]
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + FAST_BSTAGES * FAST_BSTAGE_BYTES);
   uint64_t* a_full = bars;                 // 1
   uint64_t* a_empty = bars + 1;            // 1
   uint64_t* b_full = bars + 2;             // FAST_BSTAGES
   uint64_t* b_empty = b_full + FAST_BSTAGES;
-  uint64_t* tfull = b_empty + FAST_BSTAGES;  // FAST_GROUPS
-  uint64_t* tempty = tfull + FAST_GROUPS;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + FAST_GROUPS);
+  uint64_t* tfull = b_empty + FAST_BSTAGES;  // TSTAGES
+  uint64_t* tempty = tfull + TSTAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + TSTAGES);
+  float* colbuf = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // contiguous, balanced range of the m-major tile list: at most two A blocks per CTA at these sizes
@@ -482,9 +606,9 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
       ptx::mbar_init(&b_full[s], 1);
       ptx::mbar_init(&b_empty[s], 1);
     }
-    for (int g = 0; g < FAST_GROUPS; ++g) {
+    for (int g = 0; g < TSTAGES; ++g) {
       ptx::mbar_init(&tfull[g], 1);
-      ptx::mbar_init(&tempty[g], 4);
+      ptx::mbar_init(&tempty[g], 4 * HALVES);
     }
     ptx::fence_barrier_init();
   }
@@ -516,13 +640,17 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
           a_phase ^= 1;
           cur_m = m_tile;
         }
-        const int b_row = (m_tile / tiles_per_batch) * p.Sp + n_tile * SIM_BN;
+        const int b_row = (m_tile / tiles_per_batch) * p.Sp + n_tile * BN;
         for (int kb = 0; kb < FAST_KB; ++kb) {
           ptx::mbar_wait(&b_empty[stage], phase ^ 1);
           ptx::mbar_arrive_expect_tx(&b_full[stage], FAST_BSTAGE_BYTES);
           uint8_t* sb = smem_b + stage * FAST_BSTAGE_BYTES;
-          ptx::tma_load_2d(sb, &p.b_hi, &b_full[stage], kb * BLOCK_K, b_row);
-          if (!SCREEN) ptx::tma_load_2d(sb + FAST_SUB, &p.b_lo, &b_full[stage], kb * BLOCK_K, b_row);
+          // 128-row boxes; rows past the tensor (odd half of the last tile) arrive as zeros and are never read back
+#pragma unroll
+          for (int hf = 0; hf < HALVES; ++hf) {
+            ptx::tma_load_2d(sb + hf * FAST_SUB, &p.b_hi, &b_full[stage], kb * BLOCK_K, b_row + hf * SIM_BN);
+            if (!SCREEN) ptx::tma_load_2d(sb + (HALVES + hf) * FAST_SUB, &p.b_lo, &b_full[stage], kb * BLOCK_K, b_row + hf * SIM_BN);
+          }
           if (++stage == FAST_BSTAGES) {
             stage = 0;
             phase ^= 1;
@@ -532,7 +660,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc = SCREEN ? ptx::make_idesc_f16(BLOCK_M, SIM_BN) : ptx::make_idesc_bf16(BLOCK_M, SIM_BN);
+    constexpr uint32_t idesc = SCREEN ? ptx::make_idesc_f16(BLOCK_M, BN) : ptx::make_idesc_bf16(BLOCK_M, BN);
     int stage = 0;
     uint32_t phase = 0, a_phase = 0;
     int cur_m = -1;
@@ -545,10 +673,10 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
         cur_m = m_tile;
       }
       const bool last_of_a = (t + 1 == t_end) || ((t + 1) / p.n_tiles != m_tile);
-      const int acc = it % FAST_GROUPS;
-      ptx::mbar_wait(&tempty[acc], ((it / FAST_GROUPS) & 1) ^ 1);
+      const int acc = it % TSTAGES;
+      ptx::mbar_wait(&tempty[acc], ((it / TSTAGES) & 1) ^ 1);
       ptx::tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * SIM_BN;
+      const uint32_t d_tmem = tmem_base + acc * BN;
       for (int kb = 0; kb < FAST_KB; ++kb) {
         ptx::mbar_wait(&b_full[stage], phase);
         ptx::tc_fence_after();
@@ -561,7 +689,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
             for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bh + 2 * k, idesc, (kb | k) != 0);
           } else {
             const uint64_t al = ptx::make_desc_sw128(ptx::smem_u32(smem_a + (FAST_KB + kb) * FAST_SUB));
-            const uint64_t bl = ptx::make_desc_sw128(sb + FAST_SUB);
+            const uint64_t bl = ptx::make_desc_sw128(sb + HALVES * FAST_SUB);
             // small cross terms first, the dominant hi*hi term last
 #pragma unroll
             for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bl + 2 * k, idesc, (kb | k) != 0);
@@ -586,22 +714,30 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   } else {
     // ------------------------------------------------------------------ epilogue groups
     const int ew = warp - 2;
-    const int group = ew >> 2;
+    const int group = ew >> 2;                          // owns half (group % HALVES) of accumulator stage (group / HALVES)
+    const int tstage = group / HALVES, half = group % HALVES;
     const int quarter = warp & 3;
-    int it = 0;
+    int it = 0, done = 0;
+    FastWarpState st;
     for (int t = t_begin; t < t_end; ++t, ++it) {
-      if (it % FAST_GROUPS != group) continue;
+      if (it % TSTAGES != tstage) continue;
       const int m_tile = t / p.n_tiles, n_tile = t - m_tile * p.n_tiles;
-      ptx::mbar_wait(&tfull[group], (it / FAST_GROUPS) & 1);
+      ptx::mbar_wait(&tfull[tstage], (it / TSTAGES) & 1);
       ptx::tc_fence_after();
-      const uint32_t tacc = tmem_base + group * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);
-      const int mt_in_batch = m_tile % tiles_per_batch;
-      const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || ((n_tile + 1) * SIM_BN > p.S);
-      if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, n_tile, quarter, lane);
-      else sim_fast_epilogue<false>(p, tacc, m_tile, n_tile, quarter, lane);
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&tempty[group]);
+      const int jt = n_tile * BN + half * SIM_BN;
+      if (jt < p.Sp) {  // (the odd half of the last tile lies outside the padded width)
+        const uint32_t tacc = tmem_base + tstage * BN + half * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);
+        const int mt_in_batch = m_tile % tiles_per_batch;
+        const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || (jt + SIM_BN > p.S);
+        float* cb = colbuf + (group * 2 + (done & 1)) * FAST_COLBUF_ONE;
+        if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, jt, quarter, lane, cb, group, st, &tempty[tstage]);
+        else sim_fast_epilogue<false>(p, tacc, m_tile, jt, quarter, lane, cb, group, st, &tempty[tstage]);
+        ++done;
+      } else {
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&tempty[tstage]);
+      }
     }
   }
   ptx::tc_fence_before();
@@ -633,16 +769,24 @@ __device__ __forceinline__ bool border_keep(const BorderRule& br, int n, int i, 
          c1 < w1 - br.b;
 }
 
-// fp16 operand plane of the screening sweep from the bf16 hi + lo planes (8 elements per thread).  fp16 keeps 11
-// significant bits only between 2^-14 and 65504: a feature above kScreenMaxAbs (whose partner's sub-normal rounding
-// error of 2^-25 would then matter) sets bit 1 of *needs_robust and the caller repeats the call with algo 2.
+// fp16 operand planes of the screening sweep from the bf16 hi + lo planes, both sides in one launch (8 elements per
+// thread).  fp16 keeps 11 significant bits only between 2^-14 and 65504: a feature above kScreenMaxAbs (whose partner's
+// sub-normal rounding error of 2^-25 would then matter) sets bit 1 of *needs_robust and the caller repeats the call
+// with algo 2.
 constexpr float kScreenMaxAbs = 1024.f;
-__global__ void __launch_bounds__(256) pack_f16_kernel(const uint4* __restrict__ hi, const uint4* __restrict__ lo,
-                                                       uint4* __restrict__ out, long long n_vec, int* __restrict__ needs_robust) {
+struct PackSide {
+  const uint4* hi;
+  const uint4* lo;
+  uint4* out;
+  long long n_vec;
+};
+__global__ void __launch_bounds__(256) pack_f16_kernel(PackSide sa, PackSide sb, int blocks_a, int* __restrict__ needs_robust) {
+  const bool second = static_cast<int>(blockIdx.x) >= blocks_a;
+  const PackSide& sd = second ? sb : sa;
+  const long long bid = second ? blockIdx.x - blocks_a : blockIdx.x, nblk = second ? gridDim.x - blocks_a : blocks_a;
   bool big = false;
-  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n_vec;
-       t += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const uint4 h = hi[t], l = lo[t];
+  for (long long t = bid * 256 + threadIdx.x; t < sd.n_vec; t += nblk * 256) {
+    const uint4 h = sd.hi[t], l = sd.lo[t];
     const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
     uint32_t ow[4];
 #pragma unroll
@@ -653,7 +797,7 @@ __global__ void __launch_bounds__(256) pack_f16_kernel(const uint4* __restrict__
       const __half2 v = __floats2half2_rn(x0, x1);
       ow[q] = *reinterpret_cast<const uint32_t*>(&v);
     }
-    out[t] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    sd.out[t] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
   }
   if (big) atomicOr(needs_robust, 2);
 }
@@ -757,21 +901,29 @@ __global__ void cand_pick_kernel(const Candidate* __restrict__ cand, const int* 
   }
 }
 
-// single-block ordered compaction over the N*L rows (ascending (b, i) like torch.where).  Warp w owns the
-// contiguous row segment [w*seg, (w+1)*seg) and walks it 32 rows at a time (coalesced loads, ballot + popc for
-// the in-warp order); one block-wide scan of the 32 warp totals in between the counting and the writing walk.
-__global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ rowj, const unsigned* __restrict__ rowmax,
-                                                       int n_rows, int L, long long* __restrict__ b_ids,
-                                                       long long* __restrict__ i_ids, long long* __restrict__ j_ids,
-                                                       float* __restrict__ mconf, int capacity, int* __restrict__ out_count,
-                                                       const int* __restrict__ cand_count, int cand_cap, int* __restrict__ overflow,
-                                                       int fast) {
-  __shared__ int warp_sums[32];
+// Ordered compaction over the N*L rows (ascending (b, i) like torch.where) on up to COMPACT_BLOCKS blocks.  A block
+// takes the next row segment by ticket (so every segment before it is owned by a block that is already running),
+// counts its matches, publishes the count as one 64-bit word {1, count}, and sums the words of the segments before it
+// (decoupled look-back: all blocks count in parallel, the wait is one L2 round trip).  Inside a block, warp w owns a
+// contiguous slice and walks it 32 rows at a time (coalesced loads, ballot + popc for the in-warp order).
+constexpr int COMPACT_BLOCKS = 64;
+__global__ void __launch_bounds__(256) compact_kernel(const int* __restrict__ rowj, const unsigned* __restrict__ rowmax,
+                                                      int n_rows, int L, long long* __restrict__ b_ids,
+                                                      long long* __restrict__ i_ids, long long* __restrict__ j_ids,
+                                                      float* __restrict__ mconf, int capacity, int* __restrict__ out_count,
+                                                      const int* __restrict__ cand_count, int cand_cap, int* __restrict__ overflow,
+                                                      int fast, unsigned long long* __restrict__ agg, int* __restrict__ ticket) {
+  __shared__ int seg_s, base_s;
+  __shared__ int warp_cnt[8], warp_look[8];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const int seg = ((n_rows + 31) / 32 + 31) / 32 * 32;  // rows per warp, a multiple of 32
-  const int r0 = warp * seg, r1 = min(r0 + seg, n_rows);
+  if (t == 0) seg_s = atomicAdd(ticket, 1);
+  __syncthreads();
+  const int seg = seg_s;
+  const int per_seg = ((n_rows + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x) + 255) / 256 * 256;
+  const int per_warp = per_seg / 8;  // a multiple of 32
+  const int r0 = min(seg * per_seg + warp * per_warp, n_rows), r1 = min(r0 + per_warp, n_rows);
   int cnt = 0;
-  for (int base = r0; base < r1; base += 32 * 8) {  // 8 independent loads in flight per lane: the walk is latency-bound
+  for (int base = r0; base < r1; base += 32 * 8) {  // 8 independent loads in flight per lane
     int jv[8];
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
@@ -781,22 +933,34 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
 #pragma unroll
     for (int u = 0; u < 8; ++u) cnt += __popc(__ballot_sync(0xffffffffu, jv[u] != kNoMatch));
   }
-  if (lane == 0) warp_sums[warp] = cnt;
+  if (lane == 0) warp_cnt[warp] = cnt;
   __syncthreads();
-  if (warp == 0) {
-    const int ws = warp_sums[lane];
-    int wi = ws;
+  int block_total = 0;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int y = __shfl_up_sync(0xffffffffu, wi, o);
-      if (lane >= o) wi += y;
-    }
-    warp_sums[lane] = wi - ws;  // exclusive prefix of the warp totals
-    if (lane == 31) {
-      const int total = wi;
+  for (int q = 0; q < 8; ++q) block_total += warp_cnt[q];
+  if (t == 0) atomicExch(&agg[seg], (1ull << 32) | static_cast<unsigned>(block_total));
+  int look = 0;
+  for (int k = t; k < seg; k += 256) {
+    unsigned long long v;
+    do {
+      v = *reinterpret_cast<const volatile unsigned long long*>(&agg[k]);
+    } while ((v >> 32) == 0ull);
+    look += static_cast<int>(v & 0xffffffffull);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) look += __shfl_xor_sync(0xffffffffu, look, o);
+  if (lane == 0) warp_look[warp] = look;
+  __syncthreads();
+  if (t == 0) {
+    int base = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) base += warp_look[q];
+    base_s = base;
+    if (seg == static_cast<int>(gridDim.x) - 1) {
+      const int total = base + block_total;
       *out_count = total;
       const bool cand_over = *cand_count > cand_cap;
-      // fast path: a full candidate list or an FTZ-endangered partial asks for the two-pass rerun instead
+      // fast path: a full candidate list or an FTZ-endangered sum asks for the two-pass rerun instead
       overflow[0] = (!fast && cand_over) || (total > capacity);
       // rerun code: 1 = take the two-pass path, 2 = repeat single-pass with the three split products (fp16 range)
       const int flag = cand_count[2];
@@ -804,7 +968,8 @@ __global__ void __launch_bounds__(1024) compact_kernel(const int* __restrict__ r
     }
   }
   __syncthreads();
-  int pos = warp_sums[warp];
+  int pos = base_s;
+  for (int q = 0; q < warp; ++q) pos += warp_cnt[q];
   for (int base = r0; base < r1; base += 32 * 8) {
     int jv[8];
 #pragma unroll
@@ -842,8 +1007,10 @@ struct CoarseWs {
   __nv_bfloat16 *a_hi, *a_lo, *b_hi, *b_lo;
   __half *a_f16, *b_f16;                       // operand planes of the screening sweep
   unsigned long long *rowdelta, *coldelta;     // [N*Lp], [N*Sp] fixed-point LSE corrections (cleared per call)
-  float2 *rowpart, *colpart;
+  float2 *rowpart, *colpart;                   // two-pass: (max, sum) records; single pass: plain float sums
   float2 *lse_row, *lse_col;
+  unsigned long long* agg;                     // [COMPACT_BLOCKS] look-back words of the compaction (cleared per call)
+  int* ticket;
   Candidate* cand;
   unsigned *rowmax, *colmax;
   int *rowj, *row_base, *counters;  // counters: [0] cand_count, [1] overflow
@@ -871,7 +1038,7 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.a_f16 = static_cast<__half*>(take(ra * C * 2));
   w.b_f16 = static_cast<__half*>(take(rb * C * 2));
   w.rowpart = static_cast<float2*>(take(static_cast<size_t>(w.Sp / SIM_BN) * ra * 8));
-  w.colpart = static_cast<float2*>(take(static_cast<size_t>(4) * (w.Lp / BLOCK_M) * rb * 8));  // fast path: one record per 32-row block
+  w.colpart = static_cast<float2*>(take(static_cast<size_t>(w.Lp / BLOCK_M) * rb * 8));
   w.lse_row = static_cast<float2*>(take(ra * 8));
   w.lse_col = static_cast<float2*>(take(rb * 8));
   const double bound = std::ceil(static_cast<double>(N) * (L < S ? L : S) / (thr > 1e-6f ? thr : 1e-6f)) + 64;
@@ -885,6 +1052,8 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.rowmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * L * 4));
   w.colmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * S * 4));
   w.counters = static_cast<int*>(take(16));
+  w.agg = static_cast<unsigned long long*>(take(COMPACT_BLOCKS * 8));
+  w.ticket = static_cast<int*>(take(4));
   w.rowdelta = static_cast<unsigned long long*>(take(ra * 8));
   w.coldelta = static_cast<unsigned long long*>(take(rb * 8));
   w.zero_bytes = off - w.zero_begin;
@@ -919,6 +1088,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
   OPB_CHECK_ARG(((feat_a && feat_b) || ext) && b_ids && i_ids && j_ids && mconf && count_and_overflow && workspace, "null pointer");
   OPB_CHECK_ARG(n_batch >= 1 && L >= 1 && S >= 1, "empty input");
   OPB_CHECK_ARG(C % BLOCK_K == 0 && C >= BLOCK_K, "feature dim must be a positive multiple of 64");
+  OPB_CHECK_ARG(scale > 0.f, "scale must be positive");
   OPB_CHECK_ARG(thr > 0.f && thr < 1.f, "thr must be in (0,1): the candidate-list selection relies on conf > thr > 0");
   OPB_CHECK_ARG(precision == 1 || precision == 3, "precision must be 1 or 3");
   OPB_CHECK_ARG(border_mode == 0 || border_mode == 1, "border_mode must be 0 (OnePosePlus) or 1 (LoFTR)");
@@ -961,19 +1131,19 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
 
   const bool fast = algo != 1 && x3 && C == FAST_C && mask_a == nullptr && mask_b == nullptr && conf_matrix == nullptr;
   const bool screen = fast && algo == 0;
-  int n_row_parts = n_tiles, n_col_parts = Lp / BLOCK_M;
   if (fast) {
     SimFastParams fp;
     int r;
-    if (screen) {  // fp16 operand planes of the sweep (the data type of a tensor map only matters for its fill value)
+    if (screen) {  // fp16 operand planes of the sweep
       const long long va = static_cast<long long>(N) * Lp * C / 8, vb = static_cast<long long>(N) * Sp * C / 8;
-      pack_f16_kernel<<<static_cast<unsigned>((va + 255) / 256 < 1184 ? (va + 255) / 256 : 1184), 256, 0, stream>>>(
-          reinterpret_cast<const uint4*>(w.a_hi), reinterpret_cast<const uint4*>(w.a_lo), reinterpret_cast<uint4*>(w.a_f16), va,
-          w.counters + 2);
-      pack_f16_kernel<<<static_cast<unsigned>((vb + 255) / 256 < 1184 ? (vb + 255) / 256 : 1184), 256, 0, stream>>>(
-          reinterpret_cast<const uint4*>(w.b_hi), reinterpret_cast<const uint4*>(w.b_lo), reinterpret_cast<uint4*>(w.b_f16), vb,
-          w.counters + 2);
-      count_launch(2);
+      PackSide sa{reinterpret_cast<const uint4*>(w.a_hi), reinterpret_cast<const uint4*>(w.a_lo), reinterpret_cast<uint4*>(w.a_f16), va};
+      PackSide sb{reinterpret_cast<const uint4*>(w.b_hi), reinterpret_cast<const uint4*>(w.b_lo), reinterpret_cast<uint4*>(w.b_f16), vb};
+      const int ba = static_cast<int>((va + 255) / 256 < 8 * num_sms() ? (va + 255) / 256 : 8 * num_sms());
+      const int bb = static_cast<int>((vb + 255) / 256 < 4 * num_sms() ? (vb + 255) / 256 : 4 * num_sms());
+      pack_f16_kernel<<<ba + bb, 256, 0, stream>>>(sa, sb, ba, w.counters + 2);
+      count_launch();
+    }
+    if (screen) {  // the data type of a tensor map only matters for its fill value
       if ((r = make_tmap_bf16(&fp.a_hi, w.a_f16, static_cast<uint64_t>(N) * Lp, C, C, BLOCK_M))) return r;
       if ((r = make_tmap_bf16(&fp.b_hi, w.b_f16, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
       fp.a_lo = fp.a_hi, fp.b_lo = fp.b_hi;
@@ -984,14 +1154,13 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       if ((r = make_tmap_bf16(&fp.b_lo, w.b_lo, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
     }
     fp.N = N, fp.L = L, fp.S = S, fp.Lp = Lp, fp.Sp = Sp;
-    fp.n_tiles = n_tiles;
-    fp.total_tiles = m_tiles * n_tiles;
+    fp.n_tiles = screen ? (Sp + FastCfg<true>::BN - 1) / FastCfg<true>::BN : (Sp + FastCfg<false>::BN - 1) / FastCfg<false>::BN;
+    fp.total_tiles = m_tiles * fp.n_tiles;
     fp.c = scale * kLog2e;
     fp.thr_lim = (screen ? 0.9f : 0.99f) * thr;
     fp.cand_tag = screen ? 2 : 1;
     fp.rowpart = w.rowpart, fp.colpart = w.colpart;
     fp.cand = w.cand, fp.cand_count = w.counters, fp.cand_cap = w.cand_cap;
-    fp.needs_robust = w.counters + 2;
     static bool configured = false;
     if (!configured) {
       OPB_CHECK_CUDA(cudaFuncSetAttribute(sim_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FastCfg<false>::SMEM));
@@ -1003,10 +1172,9 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     else sim_fast_kernel<false><<<grid, 64 + 128 * FAST_GROUPS, FastCfg<false>::SMEM, stream>>>(fp);
     count_launch();
     OPB_CHECK_CUDA(cudaGetLastError());
-    n_col_parts = 4 * (Lp / BLOCK_M);
     const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
     merge_stats_kernel<<<static_cast<unsigned>((nr + 31) / 32 + (nc + 31) / 32), 256, 0, stream>>>(
-        w.rowpart, n_row_parts, nr, w.colpart, n_col_parts, nc, w.lse_row, w.lse_col);
+        w.rowpart, n_tiles, nr, w.colpart, Lp / BLOCK_M, nc, w.lse_row, w.lse_col, w.counters + 2);
     count_launch();
   } else {
     fill_sim_row_base<<<(m_tiles + 255) / 256, 256, 0, stream>>>(w.row_base, Lp / BLOCK_M, N, Sp);
@@ -1039,7 +1207,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     {
       const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
       merge_stats_kernel<<<static_cast<unsigned>((nr + 31) / 32 + (nc + 31) / 32), 256, 0, stream>>>(
-          w.rowpart, n_tiles, nr, w.colpart, Lp / BLOCK_M, nc, w.lse_row, w.lse_col);
+          w.rowpart, n_tiles, nr, w.colpart, Lp / BLOCK_M, nc, w.lse_row, w.lse_col, nullptr);
       count_launch();
     }
     {
@@ -1063,9 +1231,11 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
   cand_max_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.lse_row, w.lse_col, Lp, Sp, thr, w.rowdelta,
                                           w.coldelta, w.rowmax, w.colmax);
   cand_pick_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.rowmax, w.colmax, br, w.rowj);
-  compact_kernel<<<1, 1024, 0, stream>>>(w.rowj, w.rowmax, N * L, L, reinterpret_cast<long long*>(b_ids),
-                                         reinterpret_cast<long long*>(i_ids), reinterpret_cast<long long*>(j_ids), mconf, capacity,
-                                         count_and_overflow, w.counters, w.cand_cap, count_and_overflow + 1, fast ? 1 : 0);
+  const int compact_blocks = (N * L + 2047) / 2048 < COMPACT_BLOCKS ? (N * L + 2047) / 2048 : COMPACT_BLOCKS;
+  compact_kernel<<<compact_blocks, 256, 0, stream>>>(w.rowj, w.rowmax, N * L, L, reinterpret_cast<long long*>(b_ids),
+                                                     reinterpret_cast<long long*>(i_ids), reinterpret_cast<long long*>(j_ids), mconf,
+                                                     capacity, count_and_overflow, w.counters, w.cand_cap, count_and_overflow + 1,
+                                                     fast ? 1 : 0, w.agg, w.ticket);
   count_launch(3);
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
