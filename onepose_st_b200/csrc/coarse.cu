@@ -321,8 +321,6 @@ constexpr int FAST_GROUPS = 4;
 constexpr int FAST_C = 256;
 constexpr int FAST_KB = FAST_C / BLOCK_K;           // 4 k-blocks
 constexpr int FAST_SUB = BLOCK_M * BLOCK_K * 2;     // one [128 x 64] 16-bit sub-tile: 16 KB
-constexpr int FAST_COLBUF_ONE = 4 * SIM_BN + 4;                   // [quarter][128] column sums of one tile + the 4 references
-constexpr int FAST_COLBUF = FAST_GROUPS * 2 * FAST_COLBUF_ONE * 4;  // [group][tile parity]
 template <bool SCREEN>
 struct FastCfg {
   static constexpr int PLANES = SCREEN ? 1 : 2;                   // fp16 plane | bf16 hi + lo planes
@@ -334,7 +332,7 @@ struct FastCfg {
   static constexpr int BSTAGES = SCREEN ? 6 : 2;
   static constexpr int A_BYTES = PLANES * FAST_KB * FAST_SUB;     // the resident A block
   static constexpr int BSTAGE_BYTES = PLANES * HALVES * FAST_SUB; // one B k-block: [plane][BN rows x 64]
-  static constexpr int SMEM = 1024 + A_BYTES + BSTAGES * BSTAGE_BYTES + 256 + FAST_COLBUF;
+  static constexpr int SMEM = 1024 + A_BYTES + BSTAGES * BSTAGE_BYTES + 256;
 };
 constexpr double kDeltaScale = 1099511627776.0;     // 2^40: fixed-point unit of the LSE corrections
 
@@ -346,8 +344,9 @@ struct SimFastParams {
   float c;          // scale * log2(e)  (> 0)
   float thr_lim;    // 0.99 * thr (slack for the approximate exponentials); 0.9 * thr when screening
   int cand_tag;     // Candidate::pad of captured elements: 1 = y is final, 2 = y is the screening value (rescore)
-  float2* rowpart;  // [Sp/128][N*Lp]    (T, sum_j e_ij) over 128 columns
-  float2* colpart;  // [Lp/128][N*Sp]    (T, sum_i e_ij) over the tile's rows
+  float* rowpart;   // [Sp/128][N*Lp]        sum_j e_ij over the 128 columns of a tile
+  float* colpart;   // [4*Lp/128][N*Sp]      sum_i e_ij over the 32 rows of a warp's block
+  float* tile_ref;  // [N*Lp/128][4][Sp/128] the reference T of each warp block (-inf: nothing there)
   Candidate* cand;
   int* cand_count;
   int cand_cap;
@@ -378,9 +377,8 @@ constexpr float kRefWindow = 60.f;  // a tile keeps its reference exponent while
 // the column sum.  T is a guess -- the block maximum this warp saw on its previous tile -- checked after the fact: the
 // raw maximum of the block is tracked alongside (FMNMX3, no dependency on T), and if it left the window
 // [T - 60, T + 60] octaves the block is simply swept again from TMEM with T = its own maximum (rare: neighbouring
-// tiles of the same rows have similar maxima; always on a warp's first tile).  Partials are (T, sum) records; the four
-// warps of the group merge their quarters through shared memory (one named barrier per tile, buffers alternate with
-// the tile parity) and merge_stats_kernel folds the records of different tiles.
+// tiles of the same rows have similar maxima; always on a warp's first tile).  A warp shares nothing with the other
+// warps: its row sums, column sums and T go to global memory as they are and merge_fast_kernel folds them.
 // Carried by a warp from tile to tile: the reference guess, and -- while the tiles belong to the same 128-row block -- a
 // lower bound of each row's full sum (everything this warp has seen of the row so far), which is what the candidate
 // limit is taken from: the more of a row has gone by, the fewer of its elements can still reach thr.
@@ -392,19 +390,17 @@ struct FastWarpState {
 };
 
 template <bool RAGGED>
-__device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32_t tmem_acc, int m_tile, int jt, int quarter,
-                                                  int lane, float* __restrict__ colbuf, int group, FastWarpState& st,
+__device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32_t tmem_acc, int m_tile, int n, int mt_in_batch,
+                                                  int jt, int quarter, int lane, FastWarpState& st,
                                                   uint64_t* __restrict__ tempty_bar) {
   float T = st.T;
-  const int tiles_per_batch = p.Lp / BLOCK_M;
-  const int n = m_tile / tiles_per_batch;
-  const int mt_in_batch = m_tile - n * tiles_per_batch;
   const int cq = (lane & 3) * 2;
   const int i0 = mt_in_batch * BLOCK_M + quarter * 32 + (lane >> 2);  // this thread's rows: i0 + 8h
   const uint64_t c2 = ptx::pack_f32x2(p.c, p.c);
   bool rv[4];
 #pragma unroll
   for (int h = 0; h < 4; ++h) rv[h] = !RAGGED || i0 + 8 * h < p.L;
+  float* __restrict__ colp = p.colpart + ((static_cast<long long>(mt_in_batch) * 4 + quarter) * p.N + n) * p.Sp + jt;
   uint64_t racc[4];
   float rmax[4];  // raw accumulator maxima per row
   float ymax;
@@ -467,7 +463,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
       const bool up4 = (lane & 4) != 0;
       const float cs = (up4 ? hh[1] : hh[0]) + __shfl_xor_sync(0xffffffffu, up4 ? hh[0] : hh[1], 4);
       // lane bits 4,3 select k, bit 2 selects the column of the pair
-      colbuf[quarter * SIM_BN + ch * 32 + ((lane >> 3) & 3) * 8 + cq + ((lane >> 2) & 1)] = cs;
+      colp[ch * 32 + ((lane >> 3) & 3) * 8 + cq + ((lane >> 2) & 1)] = cs;  // (a repeated sweep overwrites it)
     }
     const float tm = fmaxf(fmaxf(rmax[0], rmax[1]), fmaxf(rmax[2], rmax[3]));
     ymax = key_float(__reduce_max_sync(0xffffffffu, float_key(tm))) * p.c;
@@ -549,23 +545,9 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
   {
     const int h = lane & 3;
     const float sv = h == 0 ? s[0] : (h == 1 ? s[1] : (h == 2 ? s[2] : s[3]));
-    const bool ex = !empty && (!RAGGED || i0 + 8 * h < p.L);
-    p.rowpart[(static_cast<long long>(jt / SIM_BN) * p.N + n) * p.Lp + i0 + 8 * h] = make_float2(ex ? T : kNegInf, ex ? sv : 0.f);
+    p.rowpart[(static_cast<long long>(jt / SIM_BN) * p.N + n) * p.Lp + i0 + 8 * h] = sv;  // rows that do not exist hold 0
   }
-  if (lane == 0) colbuf[4 * SIM_BN + quarter] = empty ? kNegInf : T;
-  epi_bar(group);
-  {
-    const int j = quarter * 32 + lane;
-    const float t0 = colbuf[4 * SIM_BN], t1 = colbuf[4 * SIM_BN + 1], t2q = colbuf[4 * SIM_BN + 2], t3 = colbuf[4 * SIM_BN + 3];
-    const float tm = fmaxf(fmaxf(t0, t1), fmaxf(t2q, t3));
-    float cs = 0.f;
-    if (tm > kNegInf) {  // fixed order; 2^(-inf) = 0 drops an empty quarter, equal references scale by exactly 1
-      cs = (colbuf[j] * ptx::ex2(t0 - tm) + colbuf[SIM_BN + j] * ptx::ex2(t1 - tm)) +
-           (colbuf[2 * SIM_BN + j] * ptx::ex2(t2q - tm) + colbuf[3 * SIM_BN + j] * ptx::ex2(t3 - tm));
-    }
-    const bool ex = tm > kNegInf && (!RAGGED || jt + j < p.S);
-    p.colpart[(static_cast<long long>(mt_in_batch) * p.N + n) * p.Sp + jt + j] = make_float2(ex ? tm : kNegInf, ex ? cs : 0.f);
-  }
+  if (lane == 0) p.tile_ref[(static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / SIM_BN) + jt / SIM_BN] = empty ? kNegInf : T;
   if (!empty) st.T = ymax;  // the next tile's guess
 }
 
@@ -574,6 +556,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   constexpr int FAST_A_BYTES = FastCfg<SCREEN>::A_BYTES, FAST_BSTAGES = FastCfg<SCREEN>::BSTAGES;
   constexpr int FAST_BSTAGE_BYTES = FastCfg<SCREEN>::BSTAGE_BYTES;
   constexpr int BN = FastCfg<SCREEN>::BN, HALVES = FastCfg<SCREEN>::HALVES, TSTAGES = FastCfg<SCREEN>::TSTAGES;
+  constexpr int PLANES = FastCfg<SCREEN>::PLANES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;                  // [plane 0/1][kb][128 x 64]
@@ -586,7 +569,6 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   uint64_t* tfull = b_empty + FAST_BSTAGES;  // TSTAGES
   uint64_t* tempty = tfull + TSTAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + TSTAGES);
-  float* colbuf = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // contiguous, balanced range of the m-major tile list: at most two A blocks per CTA at these sizes
@@ -622,25 +604,32 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   const uint32_t tmem_base = *tmem_slot;
   const int tiles_per_batch = p.Lp / BLOCK_M;
 
+  // Every role walks the same tile list t_begin .. t_end with an incrementally kept (m_tile, n_tile): the two
+  // single-thread loops below (TMA, MMA issue) are what paces the kernel once the epilogue keeps up, so they carry no
+  // divisions, no per-step election and no descriptor construction.
+  const int m_first = t_begin / p.n_tiles, n_first = t_begin - m_first * p.n_tiles;
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0, a_phase = 0;
-      int cur_m = -1;
+      int m_tile = m_first, n_tile = n_first;
+      int b_row0 = (m_tile / tiles_per_batch) * p.Sp, mt_in_batch = m_tile % tiles_per_batch;
+      bool new_a = true;
       for (int t = t_begin; t < t_end; ++t) {
-        const int m_tile = t / p.n_tiles, n_tile = t - m_tile * p.n_tiles;
-        if (m_tile != cur_m) {
+        if (new_a) {
           ptx::mbar_wait(a_empty, a_phase ^ 1);
           ptx::mbar_arrive_expect_tx(a_full, FAST_A_BYTES);
+#pragma unroll
           for (int kb = 0; kb < FAST_KB; ++kb) {
             ptx::tma_load_2d(smem_a + kb * FAST_SUB, &p.a_hi, a_full, kb * BLOCK_K, m_tile * BLOCK_M);
             if (!SCREEN) ptx::tma_load_2d(smem_a + (FAST_KB + kb) * FAST_SUB, &p.a_lo, a_full, kb * BLOCK_K, m_tile * BLOCK_M);
           }
           a_phase ^= 1;
-          cur_m = m_tile;
+          new_a = false;
         }
-        const int b_row = (m_tile / tiles_per_batch) * p.Sp + n_tile * BN;
+        const int b_row = b_row0 + n_tile * BN;
+#pragma unroll
         for (int kb = 0; kb < FAST_KB; ++kb) {
           ptx::mbar_wait(&b_empty[stage], phase ^ 1);
           ptx::mbar_arrive_expect_tx(&b_full[stage], FAST_BSTAGE_BYTES);
@@ -656,59 +645,63 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
             phase ^= 1;
           }
         }
+        if (++n_tile == p.n_tiles) {
+          n_tile = 0, ++m_tile, new_a = true;
+          if (++mt_in_batch == tiles_per_batch) mt_in_batch = 0, b_row0 += p.Sp;
+        }
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc = SCREEN ? ptx::make_idesc_f16(BLOCK_M, BN) : ptx::make_idesc_bf16(BLOCK_M, BN);
-    int stage = 0;
-    uint32_t phase = 0, a_phase = 0;
-    int cur_m = -1;
-    int it = 0;
-    for (int t = t_begin; t < t_end; ++t, ++it) {
-      const int m_tile = t / p.n_tiles;
-      if (m_tile != cur_m) {
-        ptx::mbar_wait(a_full, a_phase);
-        a_phase ^= 1;
-        cur_m = m_tile;
-      }
-      const bool last_of_a = (t + 1 == t_end) || ((t + 1) / p.n_tiles != m_tile);
-      const int acc = it % TSTAGES;
-      ptx::mbar_wait(&tempty[acc], ((it / TSTAGES) & 1) ^ 1);
-      ptx::tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * BN;
-      for (int kb = 0; kb < FAST_KB; ++kb) {
-        ptx::mbar_wait(&b_full[stage], phase);
+    // ------------------------------------------------------------------ MMA issuer (one thread)
+    if (ptx::elect_one()) {
+      constexpr uint32_t idesc = SCREEN ? ptx::make_idesc_f16(BLOCK_M, BN) : ptx::make_idesc_bf16(BLOCK_M, BN);
+      uint64_t a_desc[PLANES][FAST_KB];
+#pragma unroll
+      for (int pl = 0; pl < PLANES; ++pl)
+#pragma unroll
+        for (int kb = 0; kb < FAST_KB; ++kb) a_desc[pl][kb] = ptx::make_desc_sw128(ptx::smem_u32(smem_a + (pl * FAST_KB + kb) * FAST_SUB));
+      const uint64_t b_desc0 = ptx::make_desc_sw128(ptx::smem_u32(smem_b));  // + (byte offset >> 4): the start-address field
+      int stage = 0;
+      uint32_t phase = 0, a_phase = 0;
+      int n_tile = n_first;
+      bool new_a = true;
+      for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
+        if (new_a) {
+          ptx::mbar_wait(a_full, a_phase);
+          a_phase ^= 1;
+          new_a = false;
+        }
+        const int acc = it % TSTAGES;
+        ptx::mbar_wait(&tempty[acc], ((it / TSTAGES) & 1) ^ 1);
         ptx::tc_fence_after();
-        if (ptx::elect_one()) {
-          const uint64_t ah = ptx::make_desc_sw128(ptx::smem_u32(smem_a + kb * FAST_SUB));
-          const uint32_t sb = ptx::smem_u32(smem_b + stage * FAST_BSTAGE_BYTES);
-          const uint64_t bh = ptx::make_desc_sw128(sb);
+        const uint32_t d_tmem = tmem_base + acc * BN;
+#pragma unroll
+        for (int kb = 0; kb < FAST_KB; ++kb) {
+          ptx::mbar_wait(&b_full[stage], phase);
+          const uint64_t bh = b_desc0 + static_cast<uint64_t>((stage * FAST_BSTAGE_BYTES) >> 4);
           if (SCREEN) {
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bh + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, a_desc[0][kb] + 2 * k, bh + 2 * k, idesc, (kb | k) != 0);
           } else {
-            const uint64_t al = ptx::make_desc_sw128(ptx::smem_u32(smem_a + (FAST_KB + kb) * FAST_SUB));
-            const uint64_t bl = ptx::make_desc_sw128(sb + HALVES * FAST_SUB);
+            const uint64_t bl = bh + static_cast<uint64_t>((HALVES * FAST_SUB) >> 4);
             // small cross terms first, the dominant hi*hi term last
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bl + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, a_desc[0][kb] + 2 * k, bl + 2 * k, idesc, (kb | k) != 0);
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, al + 2 * k, bh + 2 * k, idesc, 1);
+            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, a_desc[PLANES - 1][kb] + 2 * k, bh + 2 * k, idesc, 1);
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, ah + 2 * k, bh + 2 * k, idesc, 1);
+            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, a_desc[0][kb] + 2 * k, bh + 2 * k, idesc, 1);
           }
           ptx::mma_commit(&b_empty[stage]);
-          if (kb == FAST_KB - 1) {
-            ptx::mma_commit(&tfull[acc]);
-            if (last_of_a) ptx::mma_commit(a_empty);
+          if (++stage == FAST_BSTAGES) {
+            stage = 0;
+            phase ^= 1;
           }
         }
-        __syncwarp();
-        if (++stage == FAST_BSTAGES) {
-          stage = 0;
-          phase ^= 1;
-        }
+        ptx::mma_commit(&tfull[acc]);
+        const bool last_n = ++n_tile == p.n_tiles;
+        if (last_n || t + 1 == t_end) ptx::mma_commit(a_empty);
+        if (last_n) n_tile = 0, new_a = true;
       }
     }
   } else {
@@ -717,22 +710,22 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
     const int group = ew >> 2;                          // owns half (group % HALVES) of accumulator stage (group / HALVES)
     const int tstage = group / HALVES, half = group % HALVES;
     const int quarter = warp & 3;
-    int it = 0, done = 0;
     FastWarpState st;
-    for (int t = t_begin; t < t_end; ++t, ++it) {
-      if (it % TSTAGES != tstage) continue;
-      const int m_tile = t / p.n_tiles, n_tile = t - m_tile * p.n_tiles;
-      ptx::mbar_wait(&tfull[tstage], (it / TSTAGES) & 1);
+    int m_tile = m_first, n_tile = n_first + tstage;
+    int n_batch = m_tile / tiles_per_batch, mt_in_batch = m_tile % tiles_per_batch;
+    for (int t = t_begin + tstage, round = 0; t < t_end; t += TSTAGES, n_tile += TSTAGES, ++round) {
+      while (n_tile >= p.n_tiles) {
+        n_tile -= p.n_tiles, ++m_tile;
+        if (++mt_in_batch == tiles_per_batch) mt_in_batch = 0, ++n_batch;
+      }
+      ptx::mbar_wait(&tfull[tstage], round & 1);
       ptx::tc_fence_after();
       const int jt = n_tile * BN + half * SIM_BN;
       if (jt < p.Sp) {  // (the odd half of the last tile lies outside the padded width)
         const uint32_t tacc = tmem_base + tstage * BN + half * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);
-        const int mt_in_batch = m_tile % tiles_per_batch;
         const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || (jt + SIM_BN > p.S);
-        float* cb = colbuf + (group * 2 + (done & 1)) * FAST_COLBUF_ONE;
-        if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, jt, quarter, lane, cb, group, st, &tempty[tstage]);
-        else sim_fast_epilogue<false>(p, tacc, m_tile, jt, quarter, lane, cb, group, st, &tempty[tstage]);
-        ++done;
+        if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage]);
+        else sim_fast_epilogue<false>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage]);
       } else {
         ptx::tc_fence_before();
         __syncwarp();
@@ -745,6 +738,68 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// Partial sums of the single-pass sweep -> (reference, log2 sum) per row and per column.  Block = 32 outputs x 8 slices
+// of the part list (coalesced along the output index), slices combined through shared memory in a fixed order.  The
+// reference of a part is that of the warp block it came from (tile_ref).  A finished sum of an existing row / column
+// that is not safely above the flush-to-zero range (or is NaN) raises bit 0 of *needs_robust.
+__global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict__ rowpart, const float* __restrict__ colpart,
+                                                         const float* __restrict__ tile_ref, int N, int L, int S, int Lp, int Sp,
+                                                         float2* __restrict__ lse_row, float2* __restrict__ lse_col,
+                                                         int* __restrict__ needs_robust) {
+  __shared__ float2 sm[8][33];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const long long n_rows = static_cast<long long>(N) * Lp, n_cols = static_cast<long long>(N) * Sp;
+  const long long row_blocks = n_rows / 32;  // Lp and Sp are multiples of 128
+  const bool is_row = blockIdx.x < row_blocks;
+  const long long idx = (is_row ? blockIdx.x : blockIdx.x - row_blocks) * 32ll + lane;
+  const int mtb = Lp / BLOCK_M, ntb = Sp / SIM_BN;
+  float M = kNegInf, Sm = 0.f;
+  bool exists;
+  if (is_row) {
+    const int n = static_cast<int>(idx / Lp), i = static_cast<int>(idx - static_cast<long long>(n) * Lp);
+    exists = i < L;
+    const float* tr = tile_ref + ((static_cast<long long>(n) * mtb + i / BLOCK_M) * 4 + (i % BLOCK_M) / 32) * ntb;
+    for (int k = slice; k < ntb; k += 8) {
+      const float T = tr[k], v = rowpart[k * n_rows + idx];
+      if (T > kNegInf) {
+        const float Mn = fmaxf(M, T);
+        Sm = Sm * exp2f(M - Mn) + v * exp2f(T - Mn);  // exp2f(-inf) = 0 covers the first term
+        M = Mn;
+      }
+    }
+  } else {
+    const int n = static_cast<int>(idx / Sp), j = static_cast<int>(idx - static_cast<long long>(n) * Sp);
+    exists = j < S;
+    const float* tr = tile_ref + static_cast<long long>(n) * mtb * 4 * ntb + j / SIM_BN;
+    for (int k = slice; k < 4 * mtb; k += 8) {  // k = (m tile, quarter)
+      const float T = tr[static_cast<long long>(k) * ntb], v = colpart[(static_cast<long long>(k) * N + n) * Sp + j];
+      if (T > kNegInf) {
+        const float Mn = fmaxf(M, T);
+        Sm = Sm * exp2f(M - Mn) + v * exp2f(T - Mn);
+        M = Mn;
+      }
+    }
+  }
+  sm[slice][lane] = make_float2(M, Sm);
+  __syncthreads();
+  if (slice == 0) {
+    float Mt = kNegInf;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) Mt = fmaxf(Mt, sm[q][lane].x);
+    float St = 0.f;
+    if (Mt > kNegInf) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float2 pq = sm[q][lane];
+        if (pq.x > kNegInf) St += pq.y * exp2f(pq.x - Mt);
+      }
+    }
+    const bool ok = exists && Mt > kNegInf;
+    (is_row ? lse_row : lse_col)[idx] = make_float2(ok ? Mt : kNegInf, ok ? log2f(St) : 0.f);
+    if (ok && !(St >= kTinySum)) atomicOr(needs_robust, 1);
   }
 }
 
@@ -1009,6 +1064,7 @@ struct CoarseWs {
   unsigned long long *rowdelta, *coldelta;     // [N*Lp], [N*Sp] fixed-point LSE corrections (cleared per call)
   float2 *rowpart, *colpart;                   // two-pass: (max, sum) records; single pass: plain float sums
   float2 *lse_row, *lse_col;
+  float* tile_ref;                             // single pass: reference exponent per (m tile, quarter, n tile)
   unsigned long long* agg;                     // [COMPACT_BLOCKS] look-back words of the compaction (cleared per call)
   int* ticket;
   Candidate* cand;
@@ -1038,7 +1094,8 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.a_f16 = static_cast<__half*>(take(ra * C * 2));
   w.b_f16 = static_cast<__half*>(take(rb * C * 2));
   w.rowpart = static_cast<float2*>(take(static_cast<size_t>(w.Sp / SIM_BN) * ra * 8));
-  w.colpart = static_cast<float2*>(take(static_cast<size_t>(w.Lp / BLOCK_M) * rb * 8));
+  w.colpart = static_cast<float2*>(take(static_cast<size_t>(w.Lp / BLOCK_M) * rb * 16));  // single pass: 4 float rows per m tile
+  w.tile_ref = static_cast<float*>(take(ra / BLOCK_M * 4 * (w.Sp / SIM_BN) * 4));
   w.lse_row = static_cast<float2*>(take(ra * 8));
   w.lse_col = static_cast<float2*>(take(rb * 8));
   const double bound = std::ceil(static_cast<double>(N) * (L < S ? L : S) / (thr > 1e-6f ? thr : 1e-6f)) + 64;
@@ -1159,7 +1216,8 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     fp.c = scale * kLog2e;
     fp.thr_lim = (screen ? 0.9f : 0.99f) * thr;
     fp.cand_tag = screen ? 2 : 1;
-    fp.rowpart = w.rowpart, fp.colpart = w.colpart;
+    fp.rowpart = reinterpret_cast<float*>(w.rowpart), fp.colpart = reinterpret_cast<float*>(w.colpart);
+    fp.tile_ref = w.tile_ref;
     fp.cand = w.cand, fp.cand_count = w.counters, fp.cand_cap = w.cand_cap;
     static bool configured = false;
     if (!configured) {
@@ -1173,8 +1231,8 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     count_launch();
     OPB_CHECK_CUDA(cudaGetLastError());
     const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
-    merge_stats_kernel<<<static_cast<unsigned>((nr + 31) / 32 + (nc + 31) / 32), 256, 0, stream>>>(
-        w.rowpart, n_tiles, nr, w.colpart, Lp / BLOCK_M, nc, w.lse_row, w.lse_col, w.counters + 2);
+    merge_fast_kernel<<<static_cast<unsigned>(nr / 32 + nc / 32), 256, 0, stream>>>(fp.rowpart, fp.colpart, w.tile_ref, N, L, S, Lp, Sp,
+                                                                                    w.lse_row, w.lse_col, w.counters + 2);
     count_launch();
   } else {
     fill_sim_row_base<<<(m_tiles + 255) / 256, 256, 0, stream>>>(w.row_base, Lp / BLOCK_M, N, Sp);
