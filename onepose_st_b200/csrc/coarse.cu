@@ -343,6 +343,7 @@ struct SimFastParams {
   int total_tiles;  // N * (Lp/128) * n_tiles, m-major
   float c;          // scale * log2(e)  (> 0)
   float thr_lim;    // 0.99 * thr (slack for the approximate exponentials); 0.9 * thr when screening
+  int debug;        // OPB200_SIM_DEBUG: 1 = epilogue warps only hand the accumulators back, 2 = no MMAs are issued (timing experiments)
   int cand_tag;     // Candidate::pad of captured elements: 1 = y is final, 2 = y is the screening value (rescore)
   float* rowpart;   // [Sp/128][N*Lp]        sum_j e_ij over the 128 columns of a tile
   float* colpart;   // [4*Lp/128][N*Sp]      sum_i e_ij over the 32 rows of a warp's block
@@ -381,13 +382,25 @@ constexpr float kRefWindow = 60.f;  // a tile keeps its reference exponent while
 // warps: its row sums, column sums and T go to global memory as they are and merge_fast_kernel folds them.
 // Carried by a warp from tile to tile: the reference guess, and -- while the tiles belong to the same 128-row block -- a
 // lower bound of each row's full sum (everything this warp has seen of the row so far), which is what the candidate
-// limit is taken from: the more of a row has gone by, the fewer of its elements can still reach thr.
+// limit is taken from: the more of a row has gone by, the fewer of its elements can still reach thr.  Lane t owns row
+// t/4 + 8 (t%4) of the warp's block (its sums arrive there through a 3-shuffle transposing reduction); vlim[] is the
+// limit of the thread's own four rows in raw accumulator units, as of the previous tile.
 struct FastWarpState {
   float T = INFINITY;     // no guess yet: the first tile is swept twice
   int run_m = -1;         // m tile of the running sums
-  float run_T = 0.f;      // their reference
-  float run_s[4] = {0.f, 0.f, 0.f, 0.f};
+  float run_T = 0.f;      // owner lane: reference of run_s
+  float run_s = 0.f;      // owner lane: running sum of its row
+  float vlim[4] = {kNegInf, kNegInf, kNegInf, kNegInf};
 };
+
+// lane t <- reduction over its quad (lanes t ^ 1, t ^ 2, t ^ 3) of v[t % 4]
+template <typename Op>
+__device__ __forceinline__ float quad_transpose_reduce(const float (&v)[4], int lane, Op op) {
+  const bool b0 = (lane & 1) != 0, b1 = (lane & 2) != 0;
+  const float a0 = op(b0 ? v[1] : v[0], __shfl_xor_sync(0xffffffffu, b0 ? v[0] : v[1], 1));
+  const float a1 = op(b0 ? v[3] : v[2], __shfl_xor_sync(0xffffffffu, b0 ? v[2] : v[3], 1));
+  return op(b1 ? a1 : a0, __shfl_xor_sync(0xffffffffu, b1 ? a0 : a1, 2));
+}
 
 template <bool RAGGED>
 __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32_t tmem_acc, int m_tile, int n, int mt_in_batch,
@@ -401,20 +414,39 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
 #pragma unroll
   for (int h = 0; h < 4; ++h) rv[h] = !RAGGED || i0 + 8 * h < p.L;
   float* __restrict__ colp = p.colpart + ((static_cast<long long>(mt_in_batch) * 4 + quarter) * p.N + n) * p.Sp + jt;
+  if (st.run_m != m_tile) {  // a new block of rows: nothing known about their sums yet
+    st.run_m = m_tile, st.run_s = 0.f, st.run_T = 0.f;
+#pragma unroll
+    for (int h = 0; h < 4; ++h) st.vlim[h] = kNegInf;
+  }
   uint64_t racc[4];
   float rmax[4];  // raw accumulator maxima per row
-  float ymax;
+  float ymax = kNegInf;
+  bool released = false;
+  auto release = [&]() {  // the accumulator is no longer needed: hand the TMEM stage back
+    ptx::tc_fence_before();
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(tempty_bar);
+    released = true;
+  };
 #pragma unroll 1
   for (int attempt = 0;; ++attempt) {
     const uint64_t t2 = ptx::pack_f32x2(-T, -T);
+    bool redo = false;
 #pragma unroll
     for (int h = 0; h < 4; ++h) racc[h] = 0ull, rmax[h] = kNegInf;
 #pragma unroll 1
     for (int ch = 0; ch < SIM_BN / 32; ++ch) {
       uint32_t va[16], vb[16];
-      ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
-      ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
-      ptx::tmem_ld_wait();
+      if (p.debug != 4) {
+        ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
+        ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
+        ptx::tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int q = 0; q < 16; ++q) va[q] = vb[q] = __float_as_uint(static_cast<float>(q + ch + lane));
+      }
+      if (p.debug == 3) continue;
       if (RAGGED) {  // rows / columns that do not exist: -inf, i.e. e = 0 and no say in the maximum
 #pragma unroll
         for (int q = 0; q < 16; ++q) {
@@ -423,13 +455,26 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
           if (!cv || !rv[2 + ((q >> 1) & 1)]) vb[q] = __float_as_uint(kNegInf);
         }
       }
-      float f[4][2];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         rmax[0] = ptx::max3(rmax[0], __uint_as_float(va[4 * k]), __uint_as_float(va[4 * k + 1]));
         rmax[1] = ptx::max3(rmax[1], __uint_as_float(va[4 * k + 2]), __uint_as_float(va[4 * k + 3]));
         rmax[2] = ptx::max3(rmax[2], __uint_as_float(vb[4 * k]), __uint_as_float(vb[4 * k + 1]));
         rmax[3] = ptx::max3(rmax[3], __uint_as_float(vb[4 * k + 2]), __uint_as_float(vb[4 * k + 3]));
+      }
+      if (ch == SIM_BN / 32 - 1) {
+        // Everything of the tile is in registers or behind us.  Its maximum decides whether T held (else: once more
+        // with T = the maximum), and if no element beats even the limits known before this tile -- which can only
+        // have risen since -- nothing here can become a candidate: the accumulator goes back right away.
+        const float tm = fmaxf(fmaxf(rmax[0], rmax[1]), fmaxf(rmax[2], rmax[3]));
+        ymax = key_float(__reduce_max_sync(0xffffffffu, float_key(tm))) * p.c;
+        redo = attempt == 0 && ymax > kNegInf && !(fabsf(ymax - T) <= kRefWindow);
+        const bool maybe = rmax[0] > st.vlim[0] || rmax[1] > st.vlim[1] || rmax[2] > st.vlim[2] || rmax[3] > st.vlim[3];
+        if (!redo && !__any_sync(0xffffffffu, maybe)) release();
+      }
+      float f[4][2];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
         const uint64_t e0 = exp2_pair(va[4 * k], va[4 * k + 1], c2, t2), e1 = exp2_pair(va[4 * k + 2], va[4 * k + 3], c2, t2);
         const uint64_t e2 = exp2_pair(vb[4 * k], vb[4 * k + 1], c2, t2), e3 = exp2_pair(vb[4 * k + 2], vb[4 * k + 3], c2, t2);
         racc[0] = ptx::add_f32x2(racc[0], e0);
@@ -465,90 +510,68 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
       // lane bits 4,3 select k, bit 2 selects the column of the pair
       colp[ch * 32 + ((lane >> 3) & 3) * 8 + cq + ((lane >> 2) & 1)] = cs;  // (a repeated sweep overwrites it)
     }
-    const float tm = fmaxf(fmaxf(rmax[0], rmax[1]), fmaxf(rmax[2], rmax[3]));
-    ymax = key_float(__reduce_max_sync(0xffffffffu, float_key(tm))) * p.c;
-    // the maximum is inside the window (or there is nothing here at all, or this already is the second sweep)
-    if (attempt > 0 || ymax == kNegInf || fabsf(ymax - T) <= kRefWindow) break;
+    if (!redo) break;
     T = ymax;
   }
   const bool empty = ymax == kNegInf;  // ragged edge: no existing element in this warp's block
-  float s[4], mx[4];
+  const int own = lane & 3;
+  float s[4];
 #pragma unroll
   for (int h = 0; h < 4; ++h) {
     float lo, hi;
     ptx::unpack_f32x2(racc[h], lo, hi);
-    float v = lo + hi;
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    s[h] = v;
-    float m = rmax[h];
-    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-    mx[h] = m;
+    s[h] = lo + hi;
   }
+  const float s_own = quad_transpose_reduce(s, lane, [](float x, float y) { return x + y; });
+  const float mx_own = quad_transpose_reduce(rmax, lane, [](float x, float y) { return fmaxf(x, y); });
+  p.rowpart[(static_cast<long long>(jt / SIM_BN) * p.N + n) * p.Lp + i0 + 8 * own] = s_own;  // rows that do not exist hold 0
+  if (lane == 0) p.tile_ref[(static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / SIM_BN) + jt / SIM_BN] = empty ? kNegInf : T;
   // candidate capture: conf_ij > thr needs e_ij > thr * (row sum), and the part of the row this warp has seen so far
   // bounds that sum from below, i.e. acc_ij > vlim_i in raw accumulator units -- one compare per element on a second
   // sweep over TMEM, taken only when some row of the warp has its maximum above the limit
-  float vlim[4];
-  bool trig = false;
   if (!empty) {
-    if (st.run_m != m_tile) {
-      st.run_m = m_tile, st.run_T = T;
-#pragma unroll
-      for (int h = 0; h < 4; ++h) st.run_s[h] = 0.f;
-    }
     // (clamps keep it a finite lower bound when the reference moves far down)
-    const float f = ptx::ex2(fminf(st.run_T - T, 60.f));
+    st.run_s = fminf(st.run_s * ptx::ex2(fminf(st.run_T - T, 60.f)), 1e30f) + s_own;
     st.run_T = T;
+    const float lim = p.thr_lim * st.run_s;
+    const bool rv_own = !RAGGED || i0 + 8 * own < p.L;
+    const float vlim_own = (rv_own && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
+    const bool trig = !released && mx_own > vlim_own;
 #pragma unroll
-    for (int h = 0; h < 4; ++h) {
-      st.run_s[h] = fminf(st.run_s[h] * f, 1e30f) + s[h];
-      const float lim = p.thr_lim * st.run_s[h];
-      vlim[h] = (rv[h] && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
-      trig |= mx[h] > vlim[h];
-    }
-  }
-  if (__any_sync(0xffffffffu, trig)) {
+    for (int h = 0; h < 4; ++h) st.vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
+    if (__any_sync(0xffffffffu, trig)) {
 #pragma unroll 1
-    for (int ch = 0; ch < SIM_BN / 32; ++ch) {
-      uint32_t va[16], vb[16];
-      ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
-      ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
-      ptx::tmem_ld_wait();
-      bool any = false;
+      for (int ch = 0; ch < SIM_BN / 32; ++ch) {
+        uint32_t va[16], vb[16];
+        ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
+        ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
+        ptx::tmem_ld_wait();
+        bool any = false;
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
+        for (int k = 0; k < 4; ++k)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          any |= __uint_as_float(va[4 * k + q]) > vlim[q >> 1];
-          any |= __uint_as_float(vb[4 * k + q]) > vlim[2 + (q >> 1)];
-        }
-      if (!__any_sync(0xffffffffu, any)) continue;
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const int h = q >> 1, b = q & 1;
-          const float val = __uint_as_float(h < 2 ? va[4 * k + 2 * h + b] : vb[4 * k + 2 * (h - 2) + b]);
-          const int j = jt + ch * 32 + 8 * k + cq + b;
-          if (val > vlim[h] && (!RAGGED || j < p.S)) {
-            const int slot = atomicAdd(p.cand_count, 1);
-            if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i0 + 8 * h, j, __fmul_rn(val, p.c), p.cand_tag};
+          for (int q = 0; q < 4; ++q) {
+            any |= __uint_as_float(va[4 * k + q]) > st.vlim[q >> 1];
+            any |= __uint_as_float(vb[4 * k + q]) > st.vlim[2 + (q >> 1)];
           }
-        }
+        if (!__any_sync(0xffffffffu, any)) continue;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const int h = q >> 1, b = q & 1;
+            const float val = __uint_as_float(h < 2 ? va[4 * k + 2 * h + b] : vb[4 * k + 2 * (h - 2) + b]);
+            const int j = jt + ch * 32 + 8 * k + cq + b;
+            if (val > st.vlim[h] && (!RAGGED || j < p.S)) {
+              const int slot = atomicAdd(p.cand_count, 1);
+              if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i0 + 8 * h, j, __fmul_rn(val, p.c), p.cand_tag};
+            }
+          }
+      }
     }
+    st.T = ymax;  // the next tile's guess
   }
-  // the accumulator is no longer needed: hand the TMEM stage back before the bookkeeping below
-  ptx::tc_fence_before();
-  __syncwarp();
-  if (lane == 0) ptx::mbar_arrive(tempty_bar);
-  {
-    const int h = lane & 3;
-    const float sv = h == 0 ? s[0] : (h == 1 ? s[1] : (h == 2 ? s[2] : s[3]));
-    p.rowpart[(static_cast<long long>(jt / SIM_BN) * p.N + n) * p.Lp + i0 + 8 * h] = sv;  // rows that do not exist hold 0
-  }
-  if (lane == 0) p.tile_ref[(static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / SIM_BN) + jt / SIM_BN] = empty ? kNegInf : T;
-  if (!empty) st.T = ymax;  // the next tile's guess
+  if (!released) release();
 }
 
 template <bool SCREEN>
@@ -679,7 +702,8 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
         for (int kb = 0; kb < FAST_KB; ++kb) {
           ptx::mbar_wait(&b_full[stage], phase);
           const uint64_t bh = b_desc0 + static_cast<uint64_t>((stage * FAST_BSTAGE_BYTES) >> 4);
-          if (SCREEN) {
+          if (p.debug == 2) {
+          } else if (SCREEN) {
 #pragma unroll
             for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, a_desc[0][kb] + 2 * k, bh + 2 * k, idesc, (kb | k) != 0);
           } else {
@@ -721,7 +745,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
       ptx::mbar_wait(&tfull[tstage], round & 1);
       ptx::tc_fence_after();
       const int jt = n_tile * BN + half * SIM_BN;
-      if (jt < p.Sp) {  // (the odd half of the last tile lies outside the padded width)
+      if (jt < p.Sp && p.debug != 1) {  // (the odd half of the last tile lies outside the padded width)
         const uint32_t tacc = tmem_base + tstage * BN + half * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);
         const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || (jt + SIM_BN > p.S);
         if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage]);
@@ -1216,6 +1240,10 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     fp.c = scale * kLog2e;
     fp.thr_lim = (screen ? 0.9f : 0.99f) * thr;
     fp.cand_tag = screen ? 2 : 1;
+    {
+      static const int dbg = getenv("OPB200_SIM_DEBUG") ? atoi(getenv("OPB200_SIM_DEBUG")) : 0;
+      fp.debug = dbg;
+    }
     fp.rowpart = reinterpret_cast<float*>(w.rowpart), fp.colpart = reinterpret_cast<float*>(w.colpart);
     fp.tile_ref = w.tile_ref;
     fp.cand = w.cand, fp.cand_count = w.counters, fp.cand_cap = w.cand_cap;
