@@ -343,6 +343,8 @@ struct SimFastParams {
   int total_tiles;  // N * (Lp/128) * n_tiles, m-major
   float c;          // scale * log2(e)  (> 0)
   float thr_lim;    // 0.99 * thr (slack for the approximate exponentials); 0.9 * thr when screening
+  long long* trace; // debug (opb200_debug_trace): per CTA and every fourth tile {MMA issue start, MMA issued, accumulator
+                    // seen full by one epilogue warp of its stage, that warp's release} SM-clock stamps
   int debug;        // OPB200_SIM_DEBUG: 1 = epilogue warps only hand the accumulators back, 2 = no MMAs are issued (timing experiments)
   int cand_tag;     // Candidate::pad of captured elements: 1 = y is final, 2 = y is the screening value (rescore)
   float* rowpart;   // [Sp/128][N*Lp]        sum_j e_ij over the 128 columns of a tile
@@ -405,7 +407,7 @@ __device__ __forceinline__ float quad_transpose_reduce(const float (&v)[4], int 
 template <bool RAGGED>
 __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32_t tmem_acc, int m_tile, int n, int mt_in_batch,
                                                   int jt, int quarter, int lane, FastWarpState& st,
-                                                  uint64_t* __restrict__ tempty_bar) {
+                                                  uint64_t* __restrict__ tempty_bar, long long* trace_slot) {
   float T = st.T;
   const int cq = (lane & 3) * 2;
   const int i0 = mt_in_batch * BLOCK_M + quarter * 32 + (lane >> 2);  // this thread's rows: i0 + 8h
@@ -427,6 +429,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     ptx::tc_fence_before();
     __syncwarp();
     if (lane == 0) ptx::mbar_arrive(tempty_bar);
+    if (trace_slot != nullptr) *trace_slot = clock64();
     released = true;
   };
 #pragma unroll 1
@@ -697,6 +700,8 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
         const int acc = it % TSTAGES;
         ptx::mbar_wait(&tempty[acc], ((it / TSTAGES) & 1) ^ 1);
         ptx::tc_fence_after();
+        const bool tr = p.trace != nullptr && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta;
+        if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 0] = clock64();
         const uint32_t d_tmem = tmem_base + acc * BN;
 #pragma unroll
         for (int kb = 0; kb < FAST_KB; ++kb) {
@@ -723,6 +728,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
           }
         }
         ptx::mma_commit(&tfull[acc]);
+        if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 1] = clock64();
         const bool last_n = ++n_tile == p.n_tiles;
         if (last_n || t + 1 == t_end) ptx::mma_commit(a_empty);
         if (last_n) n_tile = 0, new_a = true;
@@ -744,12 +750,17 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
       }
       ptx::mbar_wait(&tfull[tstage], round & 1);
       ptx::tc_fence_after();
+      const int it_e = t - t_begin;
+      const bool tr = p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta && half == 0 && quarter == 2 && lane == 0;
+      if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 2] = clock64();
       const int jt = n_tile * BN + half * SIM_BN;
       if (jt < p.Sp && p.debug != 1) {  // (the odd half of the last tile lies outside the padded width)
         const uint32_t tacc = tmem_base + tstage * BN + half * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);
         const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || (jt + SIM_BN > p.S);
-        if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage]);
-        else sim_fast_epilogue<false>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage]);
+        if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage],
+                                                tr ? &p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 3] : nullptr);
+        else sim_fast_epilogue<false>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage],
+                                                tr ? &p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 3] : nullptr);
       } else {
         ptx::tc_fence_before();
         __syncwarp();
@@ -786,6 +797,7 @@ __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict
     const int n = static_cast<int>(idx / Lp), i = static_cast<int>(idx - static_cast<long long>(n) * Lp);
     exists = i < L;
     const float* tr = tile_ref + ((static_cast<long long>(n) * mtb + i / BLOCK_M) * 4 + (i % BLOCK_M) / 32) * ntb;
+#pragma unroll 4
     for (int k = slice; k < ntb; k += 8) {
       const float T = tr[k], v = rowpart[k * n_rows + idx];
       if (T > kNegInf) {
@@ -798,6 +810,7 @@ __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict
     const int n = static_cast<int>(idx / Sp), j = static_cast<int>(idx - static_cast<long long>(n) * Sp);
     exists = j < S;
     const float* tr = tile_ref + static_cast<long long>(n) * mtb * 4 * ntb + j / SIM_BN;
+#pragma unroll 4
     for (int k = slice; k < 4 * mtb; k += 8) {  // k = (m tile, quarter)
       const float T = tr[static_cast<long long>(k) * ntb], v = colpart[(static_cast<long long>(k) * N + n) * Sp + j];
       if (T > kNegInf) {
@@ -1240,6 +1253,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     fp.c = scale * kLog2e;
     fp.thr_lim = (screen ? 0.9f : 0.99f) * thr;
     fp.cand_tag = screen ? 2 : 1;
+    fp.trace = next_trace_slot(num_sms());
     {
       static const int dbg = getenv("OPB200_SIM_DEBUG") ? atoi(getenv("OPB200_SIM_DEBUG")) : 0;
       fp.debug = dbg;
@@ -1324,6 +1338,12 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
                                                      fast ? 1 : 0, w.agg, w.ticket);
   count_launch(3);
   OPB_CHECK_CUDA(cudaGetLastError());
+  if (fast && getenv("OPB200_SIM_DEBUG_COUNT") != nullptr) {  // debug: how many candidates the sweep captured
+    int hc = 0;
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(&hc, w.counters, sizeof(hc), cudaMemcpyDeviceToHost);
+    fprintf(stderr, "opb200_coarse_match: %d candidates captured (%d slots)\n", hc, w.cand_cap);
+  }
   return OPB_OK;
 }
 

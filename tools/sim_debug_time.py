@@ -16,3 +16,20 @@ for _ in range(10):
     e0.record(); ops.coarse_match(f3d, f2d, **kw); e1.record(); torch.cuda.synchronize()
     ts.append(e0.elapsed_time(e1))
 print("debug", os.environ.get("OPB200_SIM_DEBUG", "0"), "coarse_match call ms (min, median):", min(ts), sorted(ts)[5])
+
+if os.environ.get("OPB200_SIM_TRACE"):
+    import ctypes
+    from onepose_st_b200 import _lib
+    slot = 148 * 32 * 4
+    buf = torch.zeros(slot, dtype=torch.int64, device="cuda")
+    lib = _lib.lib()
+    lib.opb200_debug_trace(ctypes.c_void_p(buf.data_ptr()), ctypes.c_longlong(buf.numel() * 8))
+    ops.coarse_match(f3d, f2d, **kw)
+    torch.cuda.synchronize()
+    lib.opb200_debug_trace(ctypes.c_void_p(0), ctypes.c_longlong(0))
+    x = buf.view(148, 32, 4).cpu()
+    for cta in (0, 77):
+        t0 = int(x[cta, 0, 0])
+        print(f"CTA {cta}: every 4th tile: MMA issue start, MMA issued, epilogue sees full, epilogue releases (SM clocks from the first stamp)")
+        for it in range(30):
+            print(f"  {it:2d}: " + " ".join(f"{int(v) - t0:8d}" for v in x[cta, it]))
