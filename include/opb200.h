@@ -126,6 +126,13 @@ int opb200_coarse_match_planes(const void* a_hi, const void* a_lo, const void* b
                                int* count_and_overflow, float* conf_matrix, void* workspace, size_t workspace_bytes,
                                int precision, int algo, void* stream);
 
+/* Measurement hook (bench.py roofline): while armed, every single-pass opb200_coarse_match call brackets its similarity
+ * sweep kernel (sim_fast_kernel, the dominant kernel of the call) with a pair of CUDA events recorded on the call's
+ * stream.  opb200_coarse_kernel_ms waits for the recorded pairs, returns the summed kernel time and their number, and
+ * forgets them.  Not for use under CUDA-graph capture. */
+int opb200_coarse_kernel_timing(int enable);
+int opb200_coarse_kernel_ms(double* total_ms, long long* launches);
+
 /* ---- Fine level --------------------------------------------------------------------------------------
  * opb200_fine_gather replaces F.unfold + index in FinePreprocess (OnePosePlus fine_preprocess.py:43-53,
  * LoFTR fine_preprocess.py:40-47): out[m, wy*W+wx, c] = feat[b_ids[m], c, 4r - W/2 + wy, 4c - W/2 + wx]

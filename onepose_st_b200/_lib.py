@@ -67,6 +67,18 @@ def launch_count() -> int:
     return int(l.opb200_launch_count())
 
 
+def coarse_kernel_timing(enable: bool) -> None:
+    """Arm / disarm the CUDA-event bracket around CoarseMatching's sweep kernel (bench.py roofline)."""
+    check(lib().opb200_coarse_kernel_timing(ctypes.c_int(1 if enable else 0)), "opb200_coarse_kernel_timing")
+
+
+def coarse_kernel_ms():
+    """(summed device time in ms, number of launches) of the sweep kernels recorded since the last call."""
+    tot, n = ctypes.c_double(0.0), ctypes.c_longlong(0)
+    check(lib().opb200_coarse_kernel_ms(ctypes.byref(tot), ctypes.byref(n)), "opb200_coarse_kernel_ms")
+    return float(tot.value), int(n.value)
+
+
 def check(status: int, what: str) -> None:
     if status != 0:
         msg = lib().opb200_last_error()

@@ -1159,6 +1159,14 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
 
 using namespace opb;
 
+#include <mutex>
+#include <vector>
+namespace {
+std::mutex g_kt_mutex;
+bool g_kt_armed = false;
+std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_kt_events;
+}  // namespace
+
 extern "C" {
 
 size_t opb200_coarse_match_workspace_bytes(int n_batch, int L, int S, int C, float thr) {
@@ -1268,10 +1276,20 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       configured = true;
     }
     const int grid = fp.total_tiles < num_sms() ? fp.total_tiles : num_sms();
+    cudaEvent_t kt0 = nullptr, kt1 = nullptr;
+    {
+      std::lock_guard<std::mutex> lk(g_kt_mutex);
+      if (g_kt_armed && cudaEventCreate(&kt0) == cudaSuccess && cudaEventCreate(&kt1) == cudaSuccess) cudaEventRecord(kt0, stream);
+    }
     if (screen) sim_fast_kernel<true><<<grid, 64 + 128 * FAST_GROUPS, FastCfg<true>::SMEM, stream>>>(fp);
     else sim_fast_kernel<false><<<grid, 64 + 128 * FAST_GROUPS, FastCfg<false>::SMEM, stream>>>(fp);
     count_launch();
     OPB_CHECK_CUDA(cudaGetLastError());
+    if (kt1 != nullptr) {
+      cudaEventRecord(kt1, stream);
+      std::lock_guard<std::mutex> lk(g_kt_mutex);
+      g_kt_events.emplace_back(kt0, kt1);
+    }
     const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
     merge_fast_kernel<<<static_cast<unsigned>(nr / 32 + nc / 32), 256, 0, stream>>>(fp.rowpart, fp.colpart, w.tile_ref, N, L, S, Lp, Sp,
                                                                                     w.lse_row, w.lse_col, w.counters + 2);
@@ -1370,6 +1388,33 @@ int opb200_coarse_match_planes(const void* a_hi, const void* a_lo, const void* b
   return coarse_match_impl(nullptr, nullptr, ext, mask_a, mask_b, mask_fill, n_batch, L, S, C, scale, thr, border_rm,
                            border_mode, h0, w0, h1, w1, valid_hw, b_ids, i_ids, j_ids, mconf, capacity, count_and_overflow,
                            conf_matrix, workspace, workspace_bytes, precision, algo, stream);
+}
+
+int opb200_coarse_kernel_timing(int enable) {
+  std::lock_guard<std::mutex> lk(g_kt_mutex);
+  g_kt_armed = enable != 0;
+  return OPB_OK;
+}
+
+int opb200_coarse_kernel_ms(double* total_ms, long long* launches) {
+  OPB_CHECK_ARG(total_ms && launches, "null pointer");
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> evs;
+  {
+    std::lock_guard<std::mutex> lk(g_kt_mutex);
+    evs.swap(g_kt_events);
+  }
+  double tot = 0.0;
+  for (auto& e : evs) {
+    float ms = 0.f;
+    OPB_CHECK_CUDA(cudaEventSynchronize(e.second));
+    OPB_CHECK_CUDA(cudaEventElapsedTime(&ms, e.first, e.second));
+    tot += ms;
+    cudaEventDestroy(e.first);
+    cudaEventDestroy(e.second);
+  }
+  *total_ms = tot;
+  *launches = static_cast<long long>(evs.size());
+  return OPB_OK;
 }
 
 }  // extern "C"
