@@ -105,6 +105,8 @@ int opb200_transformer_planes(void* workspace, int d_model, int n_batch, int len
  * fp16 x fp16 product; every captured element is then re-evaluated from the split planes in fp32 and its term in
  * the row / column sums replaced by the exact one (confidences within the 1e-3 contract, measured 6e-4).
  * algo 2 = the same single pass on the three bf16 split products (fp32-grade everywhere, 3x the tensor work).
+ * algo 3 = algo 0 with the register-buffered epilogue (128x256 MMAs, every epilogue warp on every tile, accumulator
+ * stages handed back as soon as they are read): same results contract as algo 0, kept for measurement.
  * If the pass cannot be trusted it sets the rerun flag, the outputs are then undefined and the caller must call
  * again: flag 1 (a partial sum near the flush-to-zero range, or a full candidate list) -> algo 1 = the two-pass
  * path (per-row / per-column maxima, no dynamic-range limit); flag 2 (a feature beyond +-1024, outside the range

@@ -840,6 +840,424 @@ __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict
   }
 }
 
+// ================================================================================================
+// SWEEP KERNEL (algo 0, the default): the same single pass as sim_fast_kernel<true>, re-cut so that the tensor pipe
+// and the epilogue no longer take turns on an accumulator stage.
+//
+//   * MMAs are 128 x 256 x 16 (half the instructions of the issuing thread per flop, 96 instead of 128 bytes of shared
+//     memory per clock), two accumulator stages of 256 TMEM columns.
+//   * ALL sixteen epilogue warps work on every tile: warp (quarter q, column block c) owns rows 32q .. 32q+31 and
+//     columns 64c .. 64c+63.  It reads its two 32 x 32 chunks into registers and arrives on the stage's barrier as soon
+//     as the second read has landed, so a stage is held for about one chunk of arithmetic, not for a tile's whole
+//     epilogue, and the MMA thread refills it while the warps are still exponentiating.
+//   * Everything a warp keeps is per (32 rows, its columns): the reference exponent T (guess = the last chunk's
+//     maximum, verified on the registers; when it moves by more than the window the running row sums are written out
+//     as one record and a new run starts -- no rescaling, no second TMEM pass), the row sums of the current run, and a
+//     lower bound of each row's full sum (all of the row this warp has seen) from which the candidate limit is taken.
+//     The limit includes the chunk itself and the candidates are captured from the registers.
+//   * Records: column sums per (warp block, chunk) with their reference in col_ref; row sums per run in one of 128
+//     slots (n tile, chunk and column block of the run's first chunk), references in row_ref (NaN = slot unused,
+//     cleared by a memset per call).  merge_sweep_kernel folds them.
+// ================================================================================================
+constexpr int SW_BN = 256;
+constexpr int SW_BSTAGES = 4;
+constexpr int SW_TSTAGES = 2;
+constexpr int SW_A_BYTES = FAST_KB * FAST_SUB;       // 64 KB: the resident 128-row A block (fp16)
+constexpr int SW_BSTAGE_BYTES = 2 * FAST_SUB;        // 32 KB: 256 rows x 64 of B
+constexpr int SW_SMEM = 1024 + SW_A_BYTES + SW_BSTAGES * SW_BSTAGE_BYTES + 256;
+constexpr int SW_ROW_SLOTS = 128;                    // (n tile of 256: up to 16) x (chunk 0/1) x (column block c)
+constexpr int SW_MAX_NTILES = SW_ROW_SLOTS / 8;
+
+struct SimSweepParams {
+  CUtensorMap a, b;   // fp16 operand planes [rows, 256], box 128 x 64, 128B swizzle
+  int N, L, S, Lp, Sp;
+  int n_tiles;        // ceil(Sp / 256)
+  int total_tiles;    // N * (Lp/128) * n_tiles, m-major
+  float c;            // scale * log2(e)  (> 0)
+  float thr_lim;      // 0.9 * thr
+  float* colpart;     // [4*Lp/128][N*Sp]          sum_i e_ij over the 32 rows of a warp block
+  float* col_ref;     // [N*Lp/128][4][Sp/32]      reference of that sum (-inf: nothing there)
+  float* rowpart;     // [SW_ROW_SLOTS][N*Lp]      sum_j e_ij over one run of a warp
+  float* row_ref;     // [SW_ROW_SLOTS][N*Lp/32]   reference of the run (NaN: slot unused)
+  Candidate* cand;
+  int* cand_count;
+  int cand_cap;
+  long long* trace;   // debug: per CTA and every fourth tile {MMA issue start, MMA issued, warp (2,0) sees full, releases}
+  int debug;          // OPB200_SIM_DEBUG: 1 = epilogue warps only hand the accumulators back, 2 = no MMAs are issued
+};
+
+__global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(const __grid_constant__ SimSweepParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;                // [kb][128 x 64]
+  uint8_t* smem_b = smem + SW_A_BYTES;   // [stage][256 x 64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + SW_BSTAGES * SW_BSTAGE_BYTES);
+  uint64_t* a_full = bars;
+  uint64_t* a_empty = bars + 1;
+  uint64_t* b_full = bars + 2;
+  uint64_t* b_empty = b_full + SW_BSTAGES;
+  uint64_t* tfull = b_empty + SW_BSTAGES;
+  uint64_t* tempty = tfull + SW_TSTAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + SW_TSTAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t_begin = static_cast<int>(static_cast<long long>(p.total_tiles) * blockIdx.x / gridDim.x);
+  const int t_end = static_cast<int>(static_cast<long long>(p.total_tiles) * (blockIdx.x + 1) / gridDim.x);
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&p.a);
+    ptx::prefetch_tmap(&p.b);
+    ptx::mbar_init(a_full, 1);
+    ptx::mbar_init(a_empty, 1);
+    for (int s = 0; s < SW_BSTAGES; ++s) {
+      ptx::mbar_init(&b_full[s], 1);
+      ptx::mbar_init(&b_empty[s], 1);
+    }
+    for (int g = 0; g < SW_TSTAGES; ++g) {
+      ptx::mbar_init(&tfull[g], 1);
+      ptx::mbar_init(&tempty[g], 4 * FAST_GROUPS);  // every epilogue warp
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int tiles_per_batch = p.Lp / BLOCK_M;
+  const int m_first = t_begin / p.n_tiles, n_first = t_begin - m_first * p.n_tiles;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer (one thread)
+    if (ptx::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0, a_phase = 0;
+      int m_tile = m_first, n_tile = n_first;
+      int b_row0 = (m_tile / tiles_per_batch) * p.Sp, mt_in_batch = m_tile % tiles_per_batch;
+      bool new_a = true;
+      for (int t = t_begin; t < t_end; ++t) {
+        if (new_a) {
+          ptx::mbar_wait(a_empty, a_phase ^ 1);
+          ptx::mbar_arrive_expect_tx(a_full, SW_A_BYTES);
+#pragma unroll
+          for (int kb = 0; kb < FAST_KB; ++kb) ptx::tma_load_2d(smem_a + kb * FAST_SUB, &p.a, a_full, kb * BLOCK_K, m_tile * BLOCK_M);
+          a_phase ^= 1;
+          new_a = false;
+        }
+        const int b_row = b_row0 + n_tile * SW_BN;
+#pragma unroll
+        for (int kb = 0; kb < FAST_KB; ++kb) {
+          ptx::mbar_wait(&b_empty[stage], phase ^ 1);
+          ptx::mbar_arrive_expect_tx(&b_full[stage], SW_BSTAGE_BYTES);
+          uint8_t* sb = smem_b + stage * SW_BSTAGE_BYTES;
+          // two 128-row boxes; rows past the tensor (odd half of the last tile) arrive as zeros and are never read back
+          ptx::tma_load_2d(sb, &p.b, &b_full[stage], kb * BLOCK_K, b_row);
+          ptx::tma_load_2d(sb + FAST_SUB, &p.b, &b_full[stage], kb * BLOCK_K, b_row + SIM_BN);
+          if (++stage == SW_BSTAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        if (++n_tile == p.n_tiles) {
+          n_tile = 0, ++m_tile, new_a = true;
+          if (++mt_in_batch == tiles_per_batch) mt_in_batch = 0, b_row0 += p.Sp;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (one thread)
+    if (ptx::elect_one()) {
+      constexpr uint32_t idesc = ptx::make_idesc_f16(BLOCK_M, SW_BN);
+      uint64_t a_desc[FAST_KB];
+#pragma unroll
+      for (int kb = 0; kb < FAST_KB; ++kb) a_desc[kb] = ptx::make_desc_sw128(ptx::smem_u32(smem_a + kb * FAST_SUB));
+      const uint64_t b_desc0 = ptx::make_desc_sw128(ptx::smem_u32(smem_b));  // + (byte offset >> 4): the start-address field
+      int stage = 0;
+      uint32_t phase = 0, a_phase = 0;
+      int n_tile = n_first;
+      bool new_a = true;
+      for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
+        if (new_a) {
+          ptx::mbar_wait(a_full, a_phase);
+          a_phase ^= 1;
+          new_a = false;
+        }
+        const int acc = it & 1;
+        ptx::mbar_wait(&tempty[acc], ((it >> 1) & 1) ^ 1);
+        ptx::tc_fence_after();
+        const bool tr = p.trace != nullptr && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta;
+        if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 0] = clock64();
+        const uint32_t d_tmem = tmem_base + acc * SW_BN;
+#pragma unroll
+        for (int kb = 0; kb < FAST_KB; ++kb) {
+          ptx::mbar_wait(&b_full[stage], phase);
+          const uint64_t bd = b_desc0 + static_cast<uint64_t>((stage * SW_BSTAGE_BYTES) >> 4);
+          if (p.debug != 2) {
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, a_desc[kb] + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+          }
+          ptx::mma_commit(&b_empty[stage]);
+          if (++stage == SW_BSTAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        ptx::mma_commit(&tfull[acc]);
+        if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 1] = clock64();
+        const bool last_n = ++n_tile == p.n_tiles;
+        if (last_n || t + 1 == t_end) ptx::mma_commit(a_empty);
+        if (last_n) n_tile = 0, new_a = true;
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps: (quarter, column block)
+    const int cb = (warp - 2) >> 2;   // columns 64 cb .. 64 cb + 63 of every tile
+    const int quarter = warp & 3;     // TMEM lanes 32 quarter .. + 31
+    const int cq = (lane & 3) * 2;
+    const int own = lane & 3;
+    const uint64_t c2 = ptx::pack_f32x2(p.c, p.c);
+    // the run of chunks that share the reference T: row sums of the thread's four rows, where the run began
+    float T = INFINITY;
+    uint64_t racc[4] = {0ull, 0ull, 0ull, 0ull};
+    int run_slot = -1;                 // -1: no run open
+    // lower bound of the full row sums (owner lane: row lane/4 + 8 (lane%4)) and the limits taken from it
+    float run_s = 0.f, run_T = 0.f;
+    float vlim[4] = {kNegInf, kNegInf, kNegInf, kNegInf};
+    int m_tile = m_first, n_tile = n_first;
+    int n_batch = m_tile / tiles_per_batch, mt_in_batch = m_tile % tiles_per_batch;
+
+    auto flush_run = [&](int n, int mtb) {  // the open run -> one record per row
+      if (run_slot < 0) return;
+      float s4[4];
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        float lo, hi;
+        ptx::unpack_f32x2(racc[h], lo, hi);
+        s4[h] = lo + hi;
+        racc[h] = 0ull;
+      }
+      const float s_own = quad_transpose_reduce(s4, lane, [](float x, float y) { return x + y; });
+      const long long row0 = static_cast<long long>(n) * p.Lp + mtb * BLOCK_M + quarter * 32;
+      p.rowpart[static_cast<long long>(run_slot) * p.N * p.Lp + row0 + (lane >> 2) + 8 * own] = s_own;  // rows that do not exist hold 0
+      if (lane == 0) p.row_ref[static_cast<long long>(run_slot) * (p.N * p.Lp / 32) + row0 / 32] = T;
+      run_slot = -1;
+    };
+
+    for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
+      const int stage = it & 1;
+      ptx::mbar_wait(&tfull[stage], (it >> 1) & 1);
+      ptx::tc_fence_after();
+      const bool tr = p.trace != nullptr && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta && warp == 4 && lane == 0;
+      if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 2] = clock64();
+      const int jt = n_tile * SW_BN + cb * 64;
+      const bool valid = jt < p.Sp && p.debug != 1;  // (the odd half of the last tile lies outside the padded width)
+      const int i0 = mt_in_batch * BLOCK_M + quarter * 32 + (lane >> 2);  // this thread's rows: i0 + 8h
+      const bool rows_ragged = (mt_in_batch + 1) * BLOCK_M > p.L;
+      const uint32_t tacc = tmem_base + stage * SW_BN + cb * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
+#pragma unroll 1
+      for (int hc = 0; hc < 2; ++hc) {
+        uint32_t va[16], vb[16];
+        if (valid) {
+          ptx::tmem_ld_16x256b_x4(tacc + hc * 32, va);
+          ptx::tmem_ld_16x256b_x4(tacc + (16u << 16) + hc * 32, vb);
+          ptx::tmem_ld_wait();
+        }
+        if (hc == 1 || !valid) {  // both chunks are in registers: the stage goes back to the MMA thread
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tempty[stage]);
+          if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 3] = clock64();
+        }
+        if (!valid) break;
+        const int j0 = jt + hc * 32;
+        if (rows_ragged || j0 + 32 > p.S) {  // rows / columns that do not exist: -inf, i.e. e = 0 and no say in the maximum
+#pragma unroll
+          for (int q = 0; q < 16; ++q) {
+            const bool cv = j0 + 8 * (q >> 2) + cq + (q & 1) < p.S;
+            if (!cv || i0 + 8 * ((q >> 1) & 1) >= p.L) va[q] = __float_as_uint(kNegInf);
+            if (!cv || i0 + 8 * (2 + ((q >> 1) & 1)) >= p.L) vb[q] = __float_as_uint(kNegInf);
+          }
+        }
+        float cmax[4] = {kNegInf, kNegInf, kNegInf, kNegInf};  // raw maxima of the chunk per row
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          cmax[0] = ptx::max3(cmax[0], __uint_as_float(va[4 * k]), __uint_as_float(va[4 * k + 1]));
+          cmax[1] = ptx::max3(cmax[1], __uint_as_float(va[4 * k + 2]), __uint_as_float(va[4 * k + 3]));
+          cmax[2] = ptx::max3(cmax[2], __uint_as_float(vb[4 * k]), __uint_as_float(vb[4 * k + 1]));
+          cmax[3] = ptx::max3(cmax[3], __uint_as_float(vb[4 * k + 2]), __uint_as_float(vb[4 * k + 3]));
+        }
+        const float tm = fmaxf(fmaxf(cmax[0], cmax[1]), fmaxf(cmax[2], cmax[3]));
+        const float ymax = key_float(__reduce_max_sync(0xffffffffu, float_key(tm))) * p.c;
+        float* __restrict__ colp = p.colpart + ((static_cast<long long>(mt_in_batch) * 4 + quarter) * p.N + n_batch) * p.Sp + j0;
+        float* __restrict__ cref = p.col_ref + (static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / 32) + j0 / 32;
+        if (ymax == kNegInf) {  // ragged edge: nothing exists in this chunk
+          colp[lane] = 0.f;
+          if (lane == 0) *cref = kNegInf;
+          continue;
+        }
+        if (!(fabsf(ymax - T) <= kRefWindow)) {  // the guess does not hold: close the run, start one at this chunk
+          flush_run(n_batch, mt_in_batch);
+          T = ymax;
+        }
+        if (run_slot < 0) run_slot = ((n_tile * 2 + hc) * 4 + cb);
+        const uint64_t t2 = ptx::pack_f32x2(-T, -T);
+        uint64_t rc[4] = {0ull, 0ull, 0ull, 0ull};  // this chunk's row sums
+        float f[4][2];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t e0 = exp2_pair(va[4 * k], va[4 * k + 1], c2, t2), e1 = exp2_pair(va[4 * k + 2], va[4 * k + 3], c2, t2);
+          const uint64_t e2 = exp2_pair(vb[4 * k], vb[4 * k + 1], c2, t2), e3 = exp2_pair(vb[4 * k + 2], vb[4 * k + 3], c2, t2);
+          rc[0] = ptx::add_f32x2(rc[0], e0);
+          rc[1] = ptx::add_f32x2(rc[1], e1);
+          rc[2] = ptx::add_f32x2(rc[2], e2);
+          rc[3] = ptx::add_f32x2(rc[3], e3);
+          ptx::unpack_f32x2(ptx::add_f32x2(ptx::add_f32x2(e0, e1), ptx::add_f32x2(e2, e3)), f[k][0], f[k][1]);
+        }
+        // column sums: halving butterfly over the row bits of the lane id (16, 8, 4): 4 + 2 + 1 shuffles
+        float g[2][2], hh[2];
+        {
+          const bool up = (lane & 16) != 0;
+#pragma unroll
+          for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+              const float keep = up ? f[kk + 2][b] : f[kk][b];
+              const float send = up ? f[kk][b] : f[kk + 2][b];
+              g[kk][b] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+            }
+        }
+        {
+          const bool up = (lane & 8) != 0;
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            const float keep = up ? g[1][b] : g[0][b];
+            const float send = up ? g[0][b] : g[1][b];
+            hh[b] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+          }
+        }
+        const bool up4 = (lane & 4) != 0;
+        const float cs = (up4 ? hh[1] : hh[0]) + __shfl_xor_sync(0xffffffffu, up4 ? hh[0] : hh[1], 4);
+        colp[((lane >> 3) & 3) * 8 + cq + ((lane >> 2) & 1)] = cs;  // lane bits 4,3 select k, bit 2 the column of the pair
+        if (lane == 0) *cref = T;
+        // row sums: into the run, and (owner lanes) into the lower bound of the full row sum
+        float s4[4];
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          racc[h] = ptx::add_f32x2(racc[h], rc[h]);
+          float lo, hi;
+          ptx::unpack_f32x2(rc[h], lo, hi);
+          s4[h] = lo + hi;
+        }
+        const float s_own = quad_transpose_reduce(s4, lane, [](float x, float y) { return x + y; });
+        // candidate capture: conf_ij > thr needs e_ij > thr * (row sum) and the part of the row this warp has seen,
+        // this chunk included, bounds that sum from below: acc_ij > vlim_i in raw accumulator units
+        run_s = fminf(run_s * ptx::ex2(fminf(run_T - T, 60.f)), 1e30f) + s_own;  // (clamps keep it a finite lower bound)
+        run_T = T;
+        const float lim = p.thr_lim * run_s;
+        const float vlim_own = (i0 + 8 * own < p.L && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
+#pragma unroll
+        for (int h = 0; h < 4; ++h) vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
+        if (cmax[0] > vlim[0] || cmax[1] > vlim[1] || cmax[2] > vlim[2] || cmax[3] > vlim[3]) {  // only the lanes that hold one
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const int h = q >> 1, b = q & 1;
+              const float val = __uint_as_float(h < 2 ? va[4 * k + 2 * h + b] : vb[4 * k + 2 * (h - 2) + b]);
+              if (val > vlim[h]) {  // (-inf where nothing exists)
+                const int slot = atomicAdd(p.cand_count, 1);
+                if (slot < p.cand_cap)
+                  p.cand[slot] = Candidate{n_batch * p.L + i0 + 8 * h, j0 + 8 * k + cq + b, __fmul_rn(val, p.c), 2};
+              }
+            }
+        }
+      }
+      if (++n_tile == p.n_tiles) {  // the next tile belongs to another block of rows
+        flush_run(n_batch, mt_in_batch);
+        n_tile = 0, ++m_tile;
+        if (++mt_in_batch == tiles_per_batch) mt_in_batch = 0, ++n_batch;
+        run_s = 0.f, run_T = 0.f;
+#pragma unroll
+        for (int h = 0; h < 4; ++h) vlim[h] = kNegInf;
+      }
+    }
+    flush_run(n_batch, mt_in_batch);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// Records of sim_sweep_kernel -> (reference, log2 sum) per row and per column.  Block = 32 outputs x 8 slices of the
+// part list, slices combined through shared memory in a fixed order.  A finished sum of an existing row / column that
+// is not safely above the flush-to-zero range (or is NaN / inf) raises bit 0 of *needs_robust.
+__global__ void __launch_bounds__(256) merge_sweep_kernel(const float* __restrict__ rowpart, const float* __restrict__ row_ref,
+                                                          const float* __restrict__ colpart, const float* __restrict__ col_ref,
+                                                          int N, int L, int S, int Lp, int Sp, float2* __restrict__ lse_row,
+                                                          float2* __restrict__ lse_col, int* __restrict__ needs_robust) {
+  __shared__ float2 sm[8][33];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const long long n_rows = static_cast<long long>(N) * Lp, n_cols = static_cast<long long>(N) * Sp;
+  const long long row_blocks = n_rows / 32;  // Lp and Sp are multiples of 128
+  const bool is_row = blockIdx.x < row_blocks;
+  const long long idx = (is_row ? blockIdx.x : blockIdx.x - row_blocks) * 32ll + lane;
+  const int mtb = Lp / BLOCK_M;
+  float M = kNegInf, Sm = 0.f;
+  bool exists;
+  if (is_row) {
+    exists = static_cast<int>(idx % Lp) < L;
+    const long long blk = idx / 32;  // = blockIdx.x: one 32-row warp block per thread block
+#pragma unroll 4
+    for (int k = slice; k < SW_ROW_SLOTS; k += 8) {
+      const float T = row_ref[k * (n_rows / 32) + blk];
+      if (T > -3e38f) {  // (false for the NaN of an unused slot)
+        const float v = rowpart[k * n_rows + idx];
+        const float Mn = fmaxf(M, T);
+        Sm = Sm * exp2f(M - Mn) + v * exp2f(T - Mn);  // exp2f(-inf) = 0 covers the first term
+        M = Mn;
+      }
+    }
+  } else {
+    const int n = static_cast<int>(idx / Sp), j = static_cast<int>(idx - static_cast<long long>(n) * Sp);
+    exists = j < S;
+    const float* tr = col_ref + static_cast<long long>(n) * mtb * 4 * (Sp / 32) + j / 32;
+#pragma unroll 4
+    for (int k = slice; k < 4 * mtb; k += 8) {  // k = (m tile, quarter)
+      const float T = tr[static_cast<long long>(k) * (Sp / 32)];
+      if (T > -3e38f) {
+        const float v = colpart[(static_cast<long long>(k) * N + n) * Sp + j];
+        const float Mn = fmaxf(M, T);
+        Sm = Sm * exp2f(M - Mn) + v * exp2f(T - Mn);
+        M = Mn;
+      }
+    }
+  }
+  sm[slice][lane] = make_float2(M, Sm);
+  __syncthreads();
+  if (slice == 0) {
+    float Mt = kNegInf;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) Mt = fmaxf(Mt, sm[q][lane].x);
+    float St = 0.f;
+    if (Mt > kNegInf) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float2 pq = sm[q][lane];
+        if (pq.x > kNegInf) St += pq.y * exp2f(pq.x - Mt);
+      }
+    }
+    const bool ok = exists && Mt > kNegInf;
+    (is_row ? lse_row : lse_col)[idx] = make_float2(ok ? Mt : kNegInf, ok ? log2f(St) : 0.f);
+    if (ok && !(St >= kTinySum && St < 3e38f)) atomicOr(needs_robust, 1);
+  }
+}
+
 struct BorderRule {
   int mode;    // 0: OnePosePlus (query grid, top/left only); 1: LoFTR (both grids, four sides)
   int b;       // border_rm
@@ -1101,7 +1519,8 @@ struct CoarseWs {
   unsigned long long *rowdelta, *coldelta;     // [N*Lp], [N*Sp] fixed-point LSE corrections (cleared per call)
   float2 *rowpart, *colpart;                   // two-pass: (max, sum) records; single pass: plain float sums
   float2 *lse_row, *lse_col;
-  float* tile_ref;                             // single pass: reference exponent per (m tile, quarter, n tile)
+  float* tile_ref;                             // single pass: reference exponent per (m tile, quarter, n tile | 32-column chunk)
+  float* row_ref;                              // sweep kernel: reference of each row-sum record (0xff-filled per call)
   unsigned long long* agg;                     // [COMPACT_BLOCKS] look-back words of the compaction (cleared per call)
   int* ticket;
   Candidate* cand;
@@ -1130,9 +1549,13 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.b_lo = static_cast<__nv_bfloat16*>(take(rb * C * 2));
   w.a_f16 = static_cast<__half*>(take(ra * C * 2));
   w.b_f16 = static_cast<__half*>(take(rb * C * 2));
-  w.rowpart = static_cast<float2*>(take(static_cast<size_t>(w.Sp / SIM_BN) * ra * 8));
+  {
+    const size_t two_pass = static_cast<size_t>(w.Sp / SIM_BN) * ra * 8, sweep = static_cast<size_t>(SW_ROW_SLOTS) * ra * 4;
+    w.rowpart = static_cast<float2*>(take(two_pass > sweep ? two_pass : sweep));
+  }
   w.colpart = static_cast<float2*>(take(static_cast<size_t>(w.Lp / BLOCK_M) * rb * 16));  // single pass: 4 float rows per m tile
-  w.tile_ref = static_cast<float*>(take(ra / BLOCK_M * 4 * (w.Sp / SIM_BN) * 4));
+  w.tile_ref = static_cast<float*>(take(ra / BLOCK_M * 4 * (w.Sp / 32) * 4));  // (one per 32 columns for the sweep kernel)
+  w.row_ref = static_cast<float*>(take(static_cast<size_t>(SW_ROW_SLOTS) * (ra / 32) * 4));
   w.lse_row = static_cast<float2*>(take(ra * 8));
   w.lse_col = static_cast<float2*>(take(rb * 8));
   const double bound = std::ceil(static_cast<double>(N) * (L < S ? L : S) / (thr > 1e-6f ? thr : 1e-6f)) + 64;
@@ -1184,9 +1607,9 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
                              int precision, int algo, void* stream_) {
   if (int r = check_device()) return r;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  OPB_CHECK_ARG(algo >= 0 && algo <= 2,
-                "algo must be 0 (auto: single-pass with the fp16 screening sweep where legal), 1 (two-pass) or 2 (single-pass, "
-                "three split products)");
+  OPB_CHECK_ARG(algo >= 0 && algo <= 3,
+                "algo must be 0 (auto: single-pass with the fp16 screening sweep where legal), 1 (two-pass), 2 (single-pass, "
+                "three split products) or 3 (screening sweep, register-buffered epilogue variant)");
   OPB_CHECK_ARG(((feat_a && feat_b) || ext) && b_ids && i_ids && j_ids && mconf && count_and_overflow && workspace, "null pointer");
   OPB_CHECK_ARG(n_batch >= 1 && L >= 1 && S >= 1, "empty input");
   OPB_CHECK_ARG(C % BLOCK_K == 0 && C >= BLOCK_K, "feature dim must be a positive multiple of 64");
@@ -1232,7 +1655,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
   const int m_tiles = N * (Lp / BLOCK_M), n_tiles = Sp / SIM_BN;
 
   const bool fast = algo != 1 && x3 && C == FAST_C && mask_a == nullptr && mask_b == nullptr && conf_matrix == nullptr;
-  const bool screen = fast && algo == 0;
+  const bool screen = fast && (algo == 0 || algo == 3);
   if (fast) {
     SimFastParams fp;
     int r;
@@ -1255,6 +1678,47 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       if ((r = make_tmap_bf16(&fp.b_hi, w.b_hi, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
       if ((r = make_tmap_bf16(&fp.b_lo, w.b_lo, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
     }
+    // algo 3: the register-buffered variant (sim_sweep_kernel); measured slower than sim_fast_kernel<true> on the bench
+    // workload (275 vs 200 us at 8 x 8000 x 4096), kept selectable and parity-tested.  Wider grids run out of row-record slots.
+    const bool sweep = screen && algo == 3 && (Sp + SW_BN - 1) / SW_BN <= SW_MAX_NTILES;
+    static const int dbg = getenv("OPB200_SIM_DEBUG") ? atoi(getenv("OPB200_SIM_DEBUG")) : 0;
+    cudaEvent_t kt0 = nullptr, kt1 = nullptr;
+    {
+      std::lock_guard<std::mutex> lk(g_kt_mutex);
+      if (g_kt_armed && cudaEventCreate(&kt0) == cudaSuccess && cudaEventCreate(&kt1) == cudaSuccess) cudaEventRecord(kt0, stream);
+    }
+    if (sweep) {
+      SimSweepParams sp;
+      sp.a = fp.a_hi, sp.b = fp.b_hi;
+      sp.N = N, sp.L = L, sp.S = S, sp.Lp = Lp, sp.Sp = Sp;
+      sp.n_tiles = (Sp + SW_BN - 1) / SW_BN;
+      sp.total_tiles = m_tiles * sp.n_tiles;
+      sp.c = scale * kLog2e, sp.thr_lim = 0.9f * thr;
+      sp.colpart = reinterpret_cast<float*>(w.colpart), sp.col_ref = w.tile_ref;
+      sp.rowpart = reinterpret_cast<float*>(w.rowpart), sp.row_ref = w.row_ref;
+      sp.cand = w.cand, sp.cand_count = w.counters, sp.cand_cap = w.cand_cap;
+      sp.trace = next_trace_slot(num_sms());
+      sp.debug = dbg;
+      static bool configured_sweep = false;
+      if (!configured_sweep) {
+        OPB_CHECK_CUDA(cudaFuncSetAttribute(sim_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SW_SMEM));
+        configured_sweep = true;
+      }
+      OPB_CHECK_CUDA(cudaMemsetAsync(w.row_ref, 0xff, static_cast<size_t>(SW_ROW_SLOTS) * (static_cast<size_t>(N) * Lp / 32) * 4, stream));
+      const int grid = sp.total_tiles < num_sms() ? sp.total_tiles : num_sms();
+      sim_sweep_kernel<<<grid, 64 + 128 * FAST_GROUPS, SW_SMEM, stream>>>(sp);
+      count_launch();
+      OPB_CHECK_CUDA(cudaGetLastError());
+      if (kt1 != nullptr) {
+        cudaEventRecord(kt1, stream);
+        std::lock_guard<std::mutex> lk(g_kt_mutex);
+        g_kt_events.emplace_back(kt0, kt1);
+      }
+      const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
+      merge_sweep_kernel<<<static_cast<unsigned>(nr / 32 + nc / 32), 256, 0, stream>>>(sp.rowpart, sp.row_ref, sp.colpart, sp.col_ref, N, L, S,
+                                                                                       Lp, Sp, w.lse_row, w.lse_col, w.counters + 2);
+      count_launch();
+    } else {
     fp.N = N, fp.L = L, fp.S = S, fp.Lp = Lp, fp.Sp = Sp;
     fp.n_tiles = screen ? (Sp + FastCfg<true>::BN - 1) / FastCfg<true>::BN : (Sp + FastCfg<false>::BN - 1) / FastCfg<false>::BN;
     fp.total_tiles = m_tiles * fp.n_tiles;
@@ -1262,10 +1726,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     fp.thr_lim = (screen ? 0.9f : 0.99f) * thr;
     fp.cand_tag = screen ? 2 : 1;
     fp.trace = next_trace_slot(num_sms());
-    {
-      static const int dbg = getenv("OPB200_SIM_DEBUG") ? atoi(getenv("OPB200_SIM_DEBUG")) : 0;
-      fp.debug = dbg;
-    }
+    fp.debug = dbg;
     fp.rowpart = reinterpret_cast<float*>(w.rowpart), fp.colpart = reinterpret_cast<float*>(w.colpart);
     fp.tile_ref = w.tile_ref;
     fp.cand = w.cand, fp.cand_count = w.counters, fp.cand_cap = w.cand_cap;
@@ -1276,11 +1737,6 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       configured = true;
     }
     const int grid = fp.total_tiles < num_sms() ? fp.total_tiles : num_sms();
-    cudaEvent_t kt0 = nullptr, kt1 = nullptr;
-    {
-      std::lock_guard<std::mutex> lk(g_kt_mutex);
-      if (g_kt_armed && cudaEventCreate(&kt0) == cudaSuccess && cudaEventCreate(&kt1) == cudaSuccess) cudaEventRecord(kt0, stream);
-    }
     if (screen) sim_fast_kernel<true><<<grid, 64 + 128 * FAST_GROUPS, FastCfg<true>::SMEM, stream>>>(fp);
     else sim_fast_kernel<false><<<grid, 64 + 128 * FAST_GROUPS, FastCfg<false>::SMEM, stream>>>(fp);
     count_launch();
@@ -1294,6 +1750,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     merge_fast_kernel<<<static_cast<unsigned>(nr / 32 + nc / 32), 256, 0, stream>>>(fp.rowpart, fp.colpart, w.tile_ref, N, L, S, Lp, Sp,
                                                                                     w.lse_row, w.lse_col, w.counters + 2);
     count_launch();
+    }
   } else {
     fill_sim_row_base<<<(m_tiles + 255) / 256, 256, 0, stream>>>(w.row_base, Lp / BLOCK_M, N, Sp);
     count_launch();

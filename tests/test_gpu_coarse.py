@@ -119,7 +119,7 @@ def test_large_no_materialize_matches_materialize(L, S, hw):
     assert (conf[0] - ref).abs().max().item() < CONF_TOL
     # single-pass: algo 2 = three split products (same precision as two-pass), algo 0 = default, fp16 screening sweep
     # with exact re-evaluation of every captured element (confidence contract: max-abs CONF_TOL)
-    for algo, tol in ((2, 1e-5), (0, CONF_TOL)):
+    for algo, tol in ((2, 1e-5), (0, CONF_TOL), (3, CONF_TOL)):
         f = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=algo, **kw)
         got, want = _sets(f[0], f[1], f[2]), _sets(a[0], a[1], a[2])
         for (bb, ii, jj) in got ^ want:  # only threshold-straddling entries may differ
@@ -141,7 +141,7 @@ def test_single_pass_small_and_batched(n, L, S, hw):
     f3d, f2d = cases.planted_pair(33, n, L, S, 256, min(100, L // 2), hw[0], hw[1], 2, gain=0.6)
     kw = dict(scale=1.0 / (256 * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=hw)
     a = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=1, **kw)
-    for algo, tol in ((2, 1e-5), (0, CONF_TOL)):
+    for algo, tol in ((2, 1e-5), (0, CONF_TOL), (3, CONF_TOL)):
         f = ops.coarse_match(f3d.to(dev), f2d.to(dev), algo=algo, **kw)
         assert torch.equal(f[0], a[0]) and torch.equal(f[1], a[1]) and torch.equal(f[2], a[2])
         err = (f[3] - a[3]).abs().max().item()
