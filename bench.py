@@ -335,7 +335,7 @@ def run_ours(args):
         stages[name] = {"calls": len(evs), "ms_per_frame": tot / frames_rank}
     m_per_frame = res["matches"] / max(1, res["units"])
     rooflines = {}
-    traffic = None  # DRAM bytes per launch of the dominant coarse kernel, from the committed ncu --set full capture
+    traffic = None  # DRAM bytes per launch of sim_fast_kernel, from the committed ncu --set full capture (profiles/r01_coarse_match_ncu_full_summary.txt)
     tpath = os.path.join(REPO, "profiles", "r01_traffic.json")
     if os.path.exists(tpath) and args.batch == 8 and args.points == 8000 and args.size == 512:
         with open(tpath) as f:
