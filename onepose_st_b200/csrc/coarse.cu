@@ -290,22 +290,23 @@ struct EpiSimSelect {
 // ================================================================================================
 // FAST PATH: one pass over the similarity tiles (no masks, conf matrix not requested, C == 256).
 //
-//   * The 128-row A block (bf16 hi + lo planes, all of K = 256: 128 KB) stays RESIDENT in shared memory
-//     while the CTA sweeps its n tiles; only B (hi + lo k-blocks, 32 KB per stage) streams through a
-//     3-stage TMA ring.  Shared-memory fill per 128x128 tile drops from 384 KB to 128 KB, which is what
-//     keeps the tcgen05 pipe from starving on L2 bandwidth ("sim GEMM").
-//   * Four epilogue groups (4 warps each) own one TMEM accumulator stage each, so up to four tiles are in
-//     their epilogue while the MMA warp works on the next one.
-//   * Epilogue, per warp = 32 rows x 128 columns, no shared memory and no block barrier:
-//       e_ij = 2^(y_ij - T) with T a warp-uniform running reference (block max);   y = acc * scale * log2(e)
-//       row partial  (T, sum_j e_ij)  -> rowpart[n_tile][row]
-//       col partial  (T, sum_i e_ij)  -> colpart[m_tile*4 + quarter][col]   (31-shuffle transpose-reduce)
-//     Any partial that is not safely above the flush-to-zero range raises *needs_robust (the caller then
-//     reruns the two-pass path, which keeps a separate maximum per row / column).
-//   * Candidates are captured in the SAME pass: conf_ij > thr requires 2^(y_ij - LSErow_i) > thr, and the
-//     row sum over this tile only under-estimates the full row sum, so  e_ij > thr * (tile row sum)  is a
-//     necessary condition.  (row, col, y) of the few survivors go to the candidate list; their exact
-//     confidence is evaluated once the LSEs are final, with the same conf_from() as the two-pass path.
+//   * The 128-row A block (all of K = 256: 64 KB as one fp16 plane, 128 KB as bf16 hi + lo planes) stays RESIDENT in
+//     shared memory while the CTA sweeps its n tiles; only B streams through a TMA ring of 64-wide k-blocks.  CTAs
+//     take contiguous, balanced ranges of the m-major tile list (109 tiles each at 8 frames x 8000 x 4096).
+//   * One TMA thread, one MMA thread (tcgen05.mma 128x128x16 into four TMEM accumulator stages), four epilogue
+//     groups of four warps; group g owns stage g, so up to four tiles are in their epilogue while the MMA thread
+//     works on the next one.
+//   * Epilogue, per warp = 32 rows x 128 columns, no shared memory, no barrier with other warps (sim_fast_epilogue):
+//       e_ij = 2^(y_ij - T),  y = acc * scale * log2(e),  T = one reference exponent for the warp's whole block
+//       row sums    -> rowpart[n_tile][row]                 (float; registers until the tile ends)
+//       column sums -> colpart[m_tile*4 + quarter][col]     (float; 7-shuffle butterfly per 32-column chunk)
+//       T           -> tile_ref[m_tile][quarter][n_tile]
+//     merge_fast_kernel folds the records; a finished sum that is not safely above the flush-to-zero range raises
+//     *needs_robust (the caller then reruns the two-pass path, which keeps a separate maximum per row / column).
+//   * Candidates are captured in the SAME pass: conf_ij > thr requires 2^(y_ij - LSErow_i) > thr, and whatever part
+//     of the row the warp has already summed under-estimates the full row sum, so  e_ij > thr * (that sum)  is a
+//     necessary condition.  (row, col, y) of the few survivors go to the candidate list; their exact confidence is
+//     evaluated once the LSEs are final, with the same conf_from() as the two-pass path.
 // ================================================================================================
 //
 // SCREEN variant (the default single-pass mode): the sweep over all L x S similarities runs ONE fp16 x fp16 product
@@ -315,8 +316,8 @@ struct EpiSimSelect {
 // hi + lo planes in fp32 (cand_rescore_kernel) and its term in the two log-sum-exps is REPLACED by the exact one
 // (fixed-point integer atomics, so the result does not depend on the order of arrival).  The confidence of a match is
 // therefore exact in its own similarity and in every other large term of its row and column; the remaining error is
-// the fp16-operand error of the many small terms, which averages out (measured max 6e-4 on the bench workload
-// against the 1e-3 contract; tests/test_gpu_coarse.py).
+// the fp16-operand error of the many small terms, which averages out (measured max 1.2e-5 against the two-pass path,
+// contract 1e-3; tests/test_gpu_coarse.py).
 constexpr int FAST_GROUPS = 4;
 constexpr int FAST_C = 256;
 constexpr int FAST_KB = FAST_C / BLOCK_K;           // 4 k-blocks
