@@ -345,8 +345,9 @@ struct SimFastParams {
   float c;          // scale * log2(e)  (> 0)
   float thr_lim;    // 0.99 * thr (slack for the approximate exponentials); 0.9 * thr when screening
   long long* trace; // debug (opb200_debug_trace): per CTA and every fourth tile {MMA issue start, MMA issued, accumulator
-                    // seen full by one epilogue warp of its stage, that warp's release} SM-clock stamps
-  int debug;        // OPB200_SIM_DEBUG: 1 = epilogue warps only hand the accumulators back, 2 = no MMAs are issued (timing experiments)
+                    // seen full by one epilogue warp of its stage, last release among the stage's four warps} SM-clock stamps
+  int debug;        // OPB200_SIM_DEBUG timing experiments (results are garbage): 1 = epilogue warps only hand the accumulators back,
+                    // 2 = no MMAs are issued, 3 = epilogue reads TMEM only, 4 = epilogue arithmetic without the TMEM reads
   int cand_tag;     // Candidate::pad of captured elements: 1 = y is final, 2 = y is the screening value (rescore)
   float* rowpart;   // [Sp/128][N*Lp]        sum_j e_ij over the 128 columns of a tile
   float* colpart;   // [4*Lp/128][N*Sp]      sum_i e_ij over the 32 rows of a warp's block
@@ -430,7 +431,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     ptx::tc_fence_before();
     __syncwarp();
     if (lane == 0) ptx::mbar_arrive(tempty_bar);
-    if (trace_slot != nullptr) *trace_slot = clock64();
+    if (trace_slot != nullptr) atomicMax(reinterpret_cast<unsigned long long*>(trace_slot), static_cast<unsigned long long>(clock64()));
     released = true;
   };
 #pragma unroll 1
@@ -752,8 +753,8 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
       ptx::mbar_wait(&tfull[tstage], round & 1);
       ptx::tc_fence_after();
       const int it_e = t - t_begin;
-      const bool tr = p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta && half == 0 && quarter == 2 && lane == 0;
-      if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 2] = clock64();
+      const bool tr = p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta && half == 0 && lane == 0;  // all four warps: first / last
+      if (tr && quarter == 2) p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 2] = clock64();
       const int jt = n_tile * BN + half * SIM_BN;
       if (jt < p.Sp && p.debug != 1) {  // (the odd half of the last tile lies outside the padded width)
         const uint32_t tacc = tmem_base + tstage * BN + half * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);

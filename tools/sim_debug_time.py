@@ -1,6 +1,11 @@
 #!/usr/bin/env python
-"""Times opb200_coarse_match's kernels at the bench shape (8 frames x 8000 points x 4096 cells) on random features,
-with the OPB200_SIM_DEBUG experiment modes of the sweep kernel; CUDA events around the whole call."""
+"""Times opb200_coarse_match at the bench shape (8 frames x 8000 points x 4096 cells) on planted random features.
+
+OPB200_SIM_DEBUG=1|2|3|4 selects an experiment mode of the sweep kernel (1: epilogue warps only hand the accumulators
+back = MMA + TMA alone; 2: no MMAs are issued = epilogue alone; 3: TMEM reads only; 4: arithmetic without TMEM reads --
+results are garbage in these modes, run under `ncu -k regex:sim_fast` for the kernel time).  OPB200_SIM_TRACE=1 prints
+the per-tile SM-clock stamps of two CTAs (opb200_debug_trace).  OPB200_SIM_DEBUG_COUNT=1 prints the number of captured
+candidates per call."""
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from onepose_st_b200 import ops, synthetic
@@ -30,6 +35,6 @@ if os.environ.get("OPB200_SIM_TRACE"):
     x = buf.view(148, 32, 4).cpu()
     for cta in (0, 77):
         t0 = int(x[cta, 0, 0])
-        print(f"CTA {cta}: every 4th tile: MMA issue start, MMA issued, epilogue sees full, epilogue releases (SM clocks from the first stamp)")
+        print(f"CTA {cta}: every 4th tile: MMA issue start, MMA issued, an epilogue warp sees full, last release of the stage (SM clocks from the first stamp)")
         for it in range(30):
             print(f"  {it:2d}: " + " ".join(f"{int(v) - t0:8d}" for v in x[cta, it]))
