@@ -1030,6 +1030,18 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
     float vlim[4] = {kNegInf, kNegInf, kNegInf, kNegInf};
     int m_tile = m_first, n_tile = n_first;
     int n_batch = m_tile / tiles_per_batch, mt_in_batch = m_tile % tiles_per_batch;
+    // per block of rows (recomputed when m_tile changes): the thread's first row, raggedness, record bases
+    int i0;
+    bool rows_ragged;
+    float* col_base;
+    float* cref_base;
+    auto enter_rows = [&]() {
+      i0 = mt_in_batch * BLOCK_M + quarter * 32 + (lane >> 2);  // this thread's rows: i0 + 8h
+      rows_ragged = (mt_in_batch + 1) * BLOCK_M > p.L;
+      col_base = p.colpart + ((static_cast<long long>(mt_in_batch) * 4 + quarter) * p.N + n_batch) * p.Sp;
+      cref_base = p.col_ref + (static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / 32);
+    };
+    enter_rows();
 
     auto flush_run = [&](int n, int mtb) {  // the open run -> one record per row
       if (run_slot < 0) return;
@@ -1056,8 +1068,6 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
       if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 2] = clock64();
       const int jt = n_tile * SW_BN + cb * 64;
       const bool valid = jt < p.Sp && p.debug != 1;  // (the odd half of the last tile lies outside the padded width)
-      const int i0 = mt_in_batch * BLOCK_M + quarter * 32 + (lane >> 2);  // this thread's rows: i0 + 8h
-      const bool rows_ragged = (mt_in_batch + 1) * BLOCK_M > p.L;
       const uint32_t tacc = tmem_base + stage * SW_BN + cb * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll 1
       for (int hc = 0; hc < 2; ++hc) {
@@ -1093,8 +1103,8 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
         }
         const float tm = fmaxf(fmaxf(cmax[0], cmax[1]), fmaxf(cmax[2], cmax[3]));
         const float ymax = key_float(__reduce_max_sync(0xffffffffu, float_key(tm))) * p.c;
-        float* __restrict__ colp = p.colpart + ((static_cast<long long>(mt_in_batch) * 4 + quarter) * p.N + n_batch) * p.Sp + j0;
-        float* __restrict__ cref = p.col_ref + (static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / 32) + j0 / 32;
+        float* __restrict__ colp = col_base + j0;
+        float* __restrict__ cref = cref_base + (j0 >> 5);
         if (ymax == kNegInf) {  // ragged edge: nothing exists in this chunk
           colp[lane] = 0.f;
           if (lane == 0) *cref = kNegInf;
@@ -1181,6 +1191,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
         flush_run(n_batch, mt_in_batch);
         n_tile = 0, ++m_tile;
         if (++mt_in_batch == tiles_per_batch) mt_in_batch = 0, ++n_batch;
+        enter_rows();
         run_s = 0.f, run_T = 0.f;
 #pragma unroll
         for (int h = 0; h < 4; ++h) vlim[h] = kNegInf;

@@ -11,7 +11,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from onepose_st_b200 import ops, synthetic
 N, L, S, C = 8, 8000, 4096, 256
 f3d, f2d = synthetic.planted_coarse_pair(21, N, L, S, C, 1000, 64, 64, device="cuda")
-kw = dict(scale=1.0 / (C * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=(64, 64))
+kw = dict(scale=1.0 / (C * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=(64, 64),
+          algo=int(os.environ.get("OPB200_ALGO", "0")))  # 3 = the register-buffered variant (sim_sweep_kernel)
 for _ in range(3):
     ops.coarse_match(f3d, f2d, **kw)
 torch.cuda.synchronize()
