@@ -395,6 +395,7 @@ struct FastWarpState {
   float run_T = 0.f;      // owner lane: reference of run_s
   float run_s = 0.f;      // owner lane: running sum of its row
   float vlim[4] = {kNegInf, kNegInf, kNegInf, kNegInf};
+  int dbg_flags = 0;      // debug trace: 1 = the tile took the second (candidate) sweep, 2 = it was re-swept for its reference
 };
 
 // lane t <- reduction over its quad (lanes t ^ 1, t ^ 2, t ^ 3) of v[t % 4]
@@ -516,6 +517,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
       colp[ch * 32 + ((lane >> 3) & 3) * 8 + cq + ((lane >> 2) & 1)] = cs;  // (a repeated sweep overwrites it)
     }
     if (!redo) break;
+    st.dbg_flags |= 2;
     T = ymax;
   }
   const bool empty = ymax == kNegInf;  // ragged edge: no existing element in this warp's block
@@ -545,20 +547,24 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
 #pragma unroll
     for (int h = 0; h < 4; ++h) st.vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
     if (__any_sync(0xffffffffu, trig)) {
+      st.dbg_flags |= 1;
 #pragma unroll 1
       for (int ch = 0; ch < SIM_BN / 32; ++ch) {
         uint32_t va[16], vb[16];
         ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
         ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
         ptx::tmem_ld_wait();
-        bool any = false;
+        // (the epilogue warps are issue-bound while four of them share a scheduler: the per-row maxima cost 16 + 4
+        // instructions where a compare per element costs 64, and most chunks hold no candidate)
+        float cm[4] = {kNegInf, kNegInf, kNegInf, kNegInf};
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            any |= __uint_as_float(va[4 * k + q]) > st.vlim[q >> 1];
-            any |= __uint_as_float(vb[4 * k + q]) > st.vlim[2 + (q >> 1)];
-          }
+        for (int k = 0; k < 4; ++k) {
+          cm[0] = ptx::max3(cm[0], __uint_as_float(va[4 * k]), __uint_as_float(va[4 * k + 1]));
+          cm[1] = ptx::max3(cm[1], __uint_as_float(va[4 * k + 2]), __uint_as_float(va[4 * k + 3]));
+          cm[2] = ptx::max3(cm[2], __uint_as_float(vb[4 * k]), __uint_as_float(vb[4 * k + 1]));
+          cm[3] = ptx::max3(cm[3], __uint_as_float(vb[4 * k + 2]), __uint_as_float(vb[4 * k + 3]));
+        }
+        const bool any = cm[0] > st.vlim[0] || cm[1] > st.vlim[1] || cm[2] > st.vlim[2] || cm[3] > st.vlim[3];
         if (!__any_sync(0xffffffffu, any)) continue;
 #pragma unroll
         for (int k = 0; k < 4; ++k)
@@ -702,7 +708,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
         const int acc = it % TSTAGES;
         ptx::mbar_wait(&tempty[acc], ((it / TSTAGES) & 1) ^ 1);
         ptx::tc_fence_after();
-        const bool tr = p.trace != nullptr && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta;
+        const bool tr = p.debug != 5 && p.trace != nullptr && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta;
         if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 0] = clock64();
         const uint32_t d_tmem = tmem_base + acc * BN;
 #pragma unroll
@@ -753,16 +759,21 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
       ptx::mbar_wait(&tfull[tstage], round & 1);
       ptx::tc_fence_after();
       const int it_e = t - t_begin;
-      const bool tr = p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta && half == 0 && lane == 0;  // all four warps: first / last
+      const bool tr = p.debug != 5 && p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta && half == 0 && lane == 0;  // all four warps: first / last
       if (tr && quarter == 2) p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 2] = clock64();
       const int jt = n_tile * BN + half * SIM_BN;
       if (jt < p.Sp && p.debug != 1) {  // (the odd half of the last tile lies outside the padded width)
         const uint32_t tacc = tmem_base + tstage * BN + half * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);
         const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || (jt + SIM_BN > p.S);
+        const bool tr5 = p.debug == 5 && p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta && half == 0;
+        const long long t5 = tr5 ? clock64() : 0;
+        st.dbg_flags = 0;
         if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage],
                                                 tr ? &p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 3] : nullptr);
         else sim_fast_epilogue<false>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage],
                                                 tr ? &p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 3] : nullptr);
+        if (tr5 && lane == 0)  // mode 5: the slot holds, per quarter, this warp's epilogue time and flags instead of the four stamps
+          p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + quarter] = (clock64() - t5) | (static_cast<long long>(st.dbg_flags) << 48);
       } else {
         ptx::tc_fence_before();
         __syncwarp();

@@ -38,4 +38,7 @@ if os.environ.get("OPB200_SIM_TRACE"):
         t0 = int(x[cta, 0, 0])
         print(f"CTA {cta}: every 4th tile: MMA issue start, MMA issued, an epilogue warp sees full, last release of the stage (SM clocks from the first stamp)")
         for it in range(30):
-            print(f"  {it:2d}: " + " ".join(f"{int(v) - t0:8d}" for v in x[cta, it]))
+            if os.environ.get("OPB200_SIM_DEBUG") == "5":  # per quarter: epilogue clocks of that warp, flags (1 = second sweep, 2 = re-swept)
+                print(f"  {it:2d}: " + " ".join(f"{int(v) & ((1 << 48) - 1):6d}/{int(v) >> 48}" for v in x[cta, it]))
+            else:
+                print(f"  {it:2d}: " + " ".join(f"{int(v) - t0:8d}" for v in x[cta, it]))
