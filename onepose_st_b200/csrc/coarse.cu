@@ -566,18 +566,23 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
         }
         const bool any = cm[0] > st.vlim[0] || cm[1] > st.vlim[1] || cm[2] > st.vlim[2] || cm[3] > st.vlim[3];
         if (!__any_sync(0xffffffffu, any)) continue;
+        // row by row, so that the warp only walks the eight elements of rows that do hold a candidate
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
+        for (int h = 0; h < 4; ++h) {
+          if (cm[h] > st.vlim[h]) {
 #pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const int h = q >> 1, b = q & 1;
-            const float val = __uint_as_float(h < 2 ? va[4 * k + 2 * h + b] : vb[4 * k + 2 * (h - 2) + b]);
-            const int j = jt + ch * 32 + 8 * k + cq + b;
-            if (val > st.vlim[h] && (!RAGGED || j < p.S)) {
-              const int slot = atomicAdd(p.cand_count, 1);
-              if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i0 + 8 * h, j, __fmul_rn(val, p.c), p.cand_tag};
-            }
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+              for (int b = 0; b < 2; ++b) {
+                const float val = __uint_as_float(h < 2 ? va[4 * k + 2 * h + b] : vb[4 * k + 2 * (h - 2) + b]);
+                const int j = jt + ch * 32 + 8 * k + cq + b;
+                if (val > st.vlim[h] && (!RAGGED || j < p.S)) {
+                  const int slot = atomicAdd(p.cand_count, 1);
+                  if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i0 + 8 * h, j, __fmul_rn(val, p.c), p.cand_tag};
+                }
+              }
           }
+        }
       }
     }
     st.T = ymax;  // the next tile's guess
