@@ -186,17 +186,22 @@ int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels,
  *        align_corners=True) before the activation -- the FPN top-down add (resnet.py:155-162) fused into the lateral
  *        1x1 convolution
  *   y16  [n, Ho, Wo, cout_s] fp16 and/or y32 (same shape, fp32); at least one non-NULL
- *   act  0 none, 1 ReLU, 2 LeakyReLU(slope) */
+ *   act  0 none, 1 ReLU, 2 LeakyReLU(slope)
+ *   range_flag  nullable device int: bit 0 is set (atomically, never cleared) when a value written to y16 leaves the
+ *        fp16 range (|v| > 65504, i.e. it was stored as +-inf).  fp16 activations have the significand of the
+ *        reference's TF32 convolutions but not their exponent range; the host side reads the flag at the forward's one
+ *        host sync and repeats the backbone on the exact-fp32 executor when it is set. */
 int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride,
                            int cout_s, const float* bias, const void* res, const void* up, void* y16, float* y32, int act,
-                           float slope, void* stream);
+                           float slope, int* range_flag, void* stream);
 /* Option of opb200_conv2d_nhwc_f16: run as clusters of two CTAs that multicast the weight slabs to each other (TMA
  * multicast; halves the L2 -> SM weight traffic).  on = 1 / 0 sets it, on < 0 only queries; returns the previous
  * setting.  Default off (no gain measured on B200, see csrc/conv.cu); also settable with OPB200_CONV_CLUSTER=1. */
 int opb200_conv_cluster(int on);
-/* fp16-output variant of opb200_stem_conv7x7_s2_relu_nhwc and fp16 variant of opb200_upsample2x_add_nhwc (C % 8 == 0). */
+/* fp16-output variant of opb200_stem_conv7x7_s2_relu_nhwc (range_flag as above; also set by a non-finite or
+ * out-of-range image value) and fp16 variant of opb200_upsample2x_add_nhwc (C % 8 == 0). */
 int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight_tap_major, const float* bias, int n_batch,
-                                         int H, int W, int Cout, void* out_f16, void* stream);
+                                         int H, int W, int Cout, void* out_f16, int* range_flag, void* stream);
 int opb200_upsample2x_add_nhwc_f16(const void* src, int n_batch, int Hs, int Ws, int C, void* dst, void* stream);
 
 #ifdef __cplusplus

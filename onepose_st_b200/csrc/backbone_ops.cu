@@ -190,7 +190,8 @@ __global__ void __launch_bounds__(128) stem_conv7x7_s2_kernel(const float* __res
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) stem_tc_kernel(const float* __restrict__ img, const float* __restrict__ w,
                                                       const float* __restrict__ bias, int H, int W, int Ho, int Wo,
-                                                      int tiles_x, int tiles_y, int num_tiles, __half* __restrict__ out) {
+                                                      int tiles_x, int tiles_y, int num_tiles, __half* __restrict__ out,
+                                                      int* __restrict__ range_flag) {
   __shared__ __align__(1024) uint8_t a_tile[128 * 128];
   __shared__ __align__(1024) uint8_t b_tile[128 * 128];
   __shared__ float patch[21][40];
@@ -230,6 +231,7 @@ __global__ void __launch_bounds__(128) stem_tc_kernel(const float* __restrict__ 
   float bv[4];  // bias is re-read per 4 columns below; keep nothing resident
   (void)bv;
   uint32_t phase = 0;
+  float amax = 0.f;  // largest magnitude read from the image or stored as fp16 by this thread (range_flag)
   for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
     const int n = tile / (tiles_x * tiles_y);
     const int r = tile - n * tiles_x * tiles_y;
@@ -240,7 +242,9 @@ __global__ void __launch_bounds__(128) stem_tc_kernel(const float* __restrict__ 
     for (int i = t; i < 21 * 37; i += 128) {
       const int yy = i / 37, xx = i - yy * 37;
       const int y = iy0 + yy, x = ix0 + xx;
-      patch[yy][xx] = (y >= 0 && y < H && x >= 0 && x < W) ? __ldg(im + static_cast<long long>(y) * W + x) : 0.f;
+      const float pv = (y >= 0 && y < H && x >= 0 && x < W) ? __ldg(im + static_cast<long long>(y) * W + x) : 0.f;
+      amax = pv == pv ? fmaxf(amax, fabsf(pv)) : INFINITY;
+      patch[yy][xx] = pv;
     }
     __syncthreads();
 #pragma unroll
@@ -285,6 +289,7 @@ __global__ void __launch_bounds__(128) stem_tc_kernel(const float* __restrict__ 
         const float2 b2 = __ldg(reinterpret_cast<const float2*>(bias + c0));
         const float v0 = fmaxf(__uint_as_float(i < 16 ? r0[2 * i] : r1[2 * i - 32]) + b2.x, 0.f);
         const float v1 = fmaxf(__uint_as_float(i < 16 ? r0[2 * i + 1] : r1[2 * i - 31]) + b2.y, 0.f);
+        amax = fmaxf(fmaxf(amax, v0), v1);
         const __half2 hh = __floats2half2_rn(v0, v1);
         it[i >> 3][i & 7] = *reinterpret_cast<const uint32_t*>(&hh);
       }
@@ -302,6 +307,7 @@ __global__ void __launch_bounds__(128) stem_tc_kernel(const float* __restrict__ 
     ptx::tc_fence_before();
     __syncthreads();  // TMEM accumulator, A tile and patch are free for the next tile
   }
+  if (range_flag != nullptr && !(amax <= 65504.f)) atomicOr(range_flag, 1);
   if (warp == 0) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, 128);
@@ -363,7 +369,7 @@ int opb200_stem_conv7x7_s2_relu_nhwc(const float* image, const float* weight_tap
 }
 
 int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight_tap_major, const float* bias, int n_batch,
-                                         int H, int W, int Cout, void* out_f16, void* stream_) {
+                                         int H, int W, int Cout, void* out_f16, int* range_flag, void* stream_) {
   if (int r = check_device()) return r;
   OPB_CHECK_ARG(image && weight_tap_major && bias && out_f16, "null pointer");
   OPB_CHECK_ARG(n_batch >= 1 && H >= 1 && W >= 1, "bad shape");
@@ -376,7 +382,7 @@ int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight
   const int num_tiles = n_batch * tiles_x * tiles_y;
   const int ctas = num_tiles < 4 * num_sms() ? num_tiles : 4 * num_sms();
   stem_tc_kernel<<<ctas, 128, 12 * 1024 /* unused: caps residency at 4 CTAs per SM = 4 x 128 TMEM columns */, static_cast<cudaStream_t>(stream_)>>>(image, weight_tap_major, bias, H, W, Ho, Wo, tiles_x,
-                                                                      tiles_y, num_tiles, static_cast<__half*>(out_f16));
+                                                                      tiles_y, num_tiles, static_cast<__half*>(out_f16), range_flag);
   count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;

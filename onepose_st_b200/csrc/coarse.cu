@@ -335,6 +335,28 @@ struct FastCfg {
   static constexpr int BSTAGE_BYTES = PLANES * HALVES * FAST_SUB; // one B k-block: [plane][BN rows x 64]
   static constexpr int SMEM = 1024 + A_BYTES + BSTAGES * BSTAGE_BYTES + 256;
 };
+// What the screening sweep does with the bound delta on its similarity error (derived at pack_f16_kernel, below).  Capture: conf_ij > thr needs e_ij / R_i > thr; the screening sweep sees
+// y_s >= y - delta and a partial row sum R_s <= 2^delta R, so testing against thr * 2^(-2 delta) (times 0.99 for the
+// approximate exponentials) loses no element that can reach thr -- rigorous.  Diffuse part of the sums (everything not
+// captured and therefore not re-evaluated exactly): its terms carry independent relative errors of at most
+// 2^delta - 1, a match's confidence moves by at most ~0.2 of the relative error of that remainder, and the remainder
+// of a row that holds a match consists of at least 1 / thr_lim terms; screening is therefore only used while
+// delta <= kScreenMaxDelta (0.25 octave), beyond which the call is repeated on the three split products (algo 2).
+constexpr float kScreenMaxDelta = 0.25f;
+constexpr float kScreenMaxNorm = 60000.f;  // |x| <= |row| must stay below the largest fp16 (65504)
+struct ScreenPlan {
+  bool ok;
+  float thr_lim;
+};
+__device__ __forceinline__ ScreenPlan screen_plan(const unsigned* __restrict__ norm_sq, float c, float thr) {
+  const float na = sqrtf(__uint_as_float(norm_sq[0])), nb = sqrtf(__uint_as_float(norm_sq[1]));
+  const float delta = c * (9.768e-4f * na * nb + 2.9802322e-8f * 16.f * (na + nb));  // 2^-10 (1 + 2^-12), 2^-25 sqrt(256)
+  ScreenPlan sp;
+  sp.ok = na <= kScreenMaxNorm && nb <= kScreenMaxNorm && delta <= kScreenMaxDelta;  // (false for NaN / inf)
+  sp.thr_lim = 0.99f * thr * exp2f(-2.f * delta);
+  return sp;
+}
+
 constexpr double kDeltaScale = 1099511627776.0;     // 2^40: fixed-point unit of the LSE corrections
 
 struct SimFastParams {
@@ -343,7 +365,10 @@ struct SimFastParams {
   int n_tiles;      // ceil(Sp / BN) column tiles of the sweep
   int total_tiles;  // N * (Lp/128) * n_tiles, m-major
   float c;          // scale * log2(e)  (> 0)
-  float thr_lim;    // 0.99 * thr (slack for the approximate exponentials); 0.9 * thr when screening
+  float thr_lim;    // 0.99 * thr (slack for the approximate exponentials); the screening sweep takes its own from screen_plan()
+  float thr;
+  const unsigned* norm_sq;  // SCREEN: bits of the largest squared row norm of each side (pack_f16_kernel)
+  int* needs_robust;        // SCREEN: bit 1 <- the bound does not allow screening (the caller repeats with algo 2)
   long long* trace; // debug (opb200_debug_trace): per CTA and every fourth tile {MMA issue start, MMA issued, accumulator
                     // seen full by one epilogue warp of its stage, last release among the stage's four warps} SM-clock stamps
   int debug;        // OPB200_SIM_DEBUG timing experiments (results are garbage): 1 = epilogue warps only hand the accumulators back,
@@ -396,6 +421,7 @@ struct FastWarpState {
   float run_s = 0.f;      // owner lane: running sum of its row
   float vlim[4] = {kNegInf, kNegInf, kNegInf, kNegInf};
   int dbg_flags = 0;      // debug trace: 1 = the tile took the second (candidate) sweep, 2 = it was re-swept for its reference
+  float thr_lim = 0.f;    // candidate limit relative to the row sum
 };
 
 // lane t <- reduction over its quad (lanes t ^ 1, t ^ 2, t ^ 3) of v[t % 4]
@@ -540,7 +566,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     // (clamps keep it a finite lower bound when the reference moves far down)
     st.run_s = fminf(st.run_s * ptx::ex2(fminf(st.run_T - T, 60.f)), 1e30f) + s_own;
     st.run_T = T;
-    const float lim = p.thr_lim * st.run_s;
+    const float lim = st.thr_lim * st.run_s;
     const bool rv_own = !RAGGED || i0 + 8 * own < p.L;
     const float vlim_own = (rv_own && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
     const bool trig = !released && mx_own > vlim_own;
@@ -610,6 +636,15 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + TSTAGES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float thr_lim = p.thr_lim;
+  if (SCREEN) {  // every CTA derives the same plan from the operand norms; no screening -> nothing to do here
+    const ScreenPlan plan = screen_plan(p.norm_sq, p.c, p.thr);
+    if (!plan.ok) {
+      if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(p.needs_robust, 2);
+      return;
+    }
+    thr_lim = plan.thr_lim;
+  }
   // contiguous, balanced range of the m-major tile list: at most two A blocks per CTA at these sizes
   const int t_begin = static_cast<int>(static_cast<long long>(p.total_tiles) * blockIdx.x / gridDim.x);
   const int t_end = static_cast<int>(static_cast<long long>(p.total_tiles) * (blockIdx.x + 1) / gridDim.x);
@@ -754,6 +789,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
     const int tstage = group / HALVES, half = group % HALVES;
     const int quarter = warp & 3;
     FastWarpState st;
+    st.thr_lim = thr_lim;
     int m_tile = m_first, n_tile = n_first + tstage;
     int n_batch = m_tile / tiles_per_batch, mt_in_batch = m_tile % tiles_per_batch;
     for (int t = t_begin + tstage, round = 0; t < t_end; t += TSTAGES, n_tile += TSTAGES, ++round) {
@@ -892,7 +928,9 @@ struct SimSweepParams {
   int n_tiles;        // ceil(Sp / 256)
   int total_tiles;    // N * (Lp/128) * n_tiles, m-major
   float c;            // scale * log2(e)  (> 0)
-  float thr_lim;      // 0.9 * thr
+  float thr;
+  const unsigned* norm_sq;  // bits of the largest squared row norm of each side (pack_f16_kernel)
+  int* needs_robust;        // bit 1 <- the bound does not allow screening (the caller repeats with algo 2)
   float* colpart;     // [4*Lp/128][N*Sp]          sum_i e_ij over the 32 rows of a warp block
   float* col_ref;     // [N*Lp/128][4][Sp/32]      reference of that sum (-inf: nothing there)
   float* rowpart;     // [SW_ROW_SLOTS][N*Lp]      sum_j e_ij over one run of a warp
@@ -921,6 +959,12 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t_begin = static_cast<int>(static_cast<long long>(p.total_tiles) * blockIdx.x / gridDim.x);
   const int t_end = static_cast<int>(static_cast<long long>(p.total_tiles) * (blockIdx.x + 1) / gridDim.x);
+  const ScreenPlan plan = screen_plan(p.norm_sq, p.c, p.thr);
+  if (!plan.ok) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(p.needs_robust, 2);
+    return;
+  }
+  const float thr_lim = plan.thr_lim;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.a);
@@ -1184,7 +1228,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
         // this chunk included, bounds that sum from below: acc_ij > vlim_i in raw accumulator units
         run_s = fminf(run_s * ptx::ex2(fminf(run_T - T, 60.f)), 1e30f) + s_own;  // (clamps keep it a finite lower bound)
         run_T = T;
-        const float lim = p.thr_lim * run_s;
+        const float lim = thr_lim * run_s;
         const float vlim_own = (i0 + 8 * own < p.L && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
 #pragma unroll
         for (int h = 0; h < 4; ++h) vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
@@ -1309,36 +1353,45 @@ __device__ __forceinline__ bool border_keep(const BorderRule& br, int n, int i, 
 }
 
 // fp16 operand planes of the screening sweep from the bf16 hi + lo planes, both sides in one launch (8 elements per
-// thread).  fp16 keeps 11 significant bits only between 2^-14 and 65504: a feature above kScreenMaxAbs (whose partner's
-// sub-normal rounding error of 2^-25 would then matter) sets bit 1 of *needs_robust and the caller repeats the call
-// with algo 2.
-constexpr float kScreenMaxAbs = 1024.f;
+// thread, one warp per 256-wide row).  The same pass reduces what the soundness of the screening rests on: the largest
+// L2 norm of an existing row of each side (as the bits of its square, atomicMax into norm_sq[0 / 1]).  With operands
+// rounded to fp16 (relative error <= 2^-11, absolute error <= 2^-25 in the sub-normal range) the screening similarity
+// y_s = c * sum_k a_k b_k differs from the exact one by at most
+//     delta = c * (2^-10 (1 + 2^-12) |a| |b|  +  2^-25 sqrt(C) (|a| + |b|))           (Cauchy-Schwarz, in octaves)
+// screen_plan() turns that bound into the candidate limit of the sweep, or into the decision not to screen at all.
 struct PackSide {
   const uint4* hi;
   const uint4* lo;
   uint4* out;
   long long n_vec;
+  int rows_valid, rows_padded;  // per batch element: rows beyond rows_valid are padding and have no say in the norm
 };
-__global__ void __launch_bounds__(256) pack_f16_kernel(PackSide sa, PackSide sb, int blocks_a, int* __restrict__ needs_robust) {
+__global__ void __launch_bounds__(256) pack_f16_kernel(PackSide sa, PackSide sb, int blocks_a, unsigned* __restrict__ norm_sq) {
   const bool second = static_cast<int>(blockIdx.x) >= blocks_a;
   const PackSide& sd = second ? sb : sa;
   const long long bid = second ? blockIdx.x - blocks_a : blockIdx.x, nblk = second ? gridDim.x - blocks_a : blocks_a;
-  bool big = false;
-  for (long long t = bid * 256 + threadIdx.x; t < sd.n_vec; t += nblk * 256) {
+  float worst = 0.f;
+  for (long long t = bid * 256 + threadIdx.x; t < sd.n_vec; t += nblk * 256) {  // (n_vec is a multiple of 32: whole warps)
     const uint4 h = sd.hi[t], l = sd.lo[t];
     const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
     uint32_t ow[4];
+    float sq = 0.f;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const float x0 = __uint_as_float(hw[q] << 16) + __uint_as_float(lw[q] << 16);
       const float x1 = __uint_as_float(hw[q] & 0xffff0000u) + __uint_as_float(lw[q] & 0xffff0000u);
-      big |= !(fabsf(x0) <= kScreenMaxAbs) || !(fabsf(x1) <= kScreenMaxAbs);
+      sq = fmaf(x0, x0, fmaf(x1, x1, sq));
       const __half2 v = __floats2half2_rn(x0, x1);
       ow[q] = *reinterpret_cast<const uint32_t*>(&v);
     }
     sd.out[t] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    const long long row = t / (FAST_C / 8);
+    if (static_cast<int>(row % sd.rows_padded) < sd.rows_valid)
+      worst = fmaxf(worst, sq <= 3e38f ? sq : INFINITY);  // (a NaN norm must not vanish in the maximum: it counts as +inf)
   }
-  if (big) atomicOr(needs_robust, 2);
+  if ((threadIdx.x & 31) == 0 && worst > 0.f) atomicMax(&norm_sq[second ? 1 : 0], __float_as_uint(worst));
 }
 
 // One warp per captured element of the screening sweep: the similarity again from the hi + lo planes in fp32, and the
@@ -1554,7 +1607,7 @@ struct CoarseWs {
   int* ticket;
   Candidate* cand;
   unsigned *rowmax, *colmax;
-  int *rowj, *row_base, *counters;  // counters: [0] cand_count, [1] overflow
+  int *rowj, *row_base, *counters;  // counters: [0] cand_count, [2] rerun flags, [4], [5] largest squared row norms (bits)
   int cand_cap;
   int Lp, Sp;
   size_t zero_begin, zero_bytes;  // region that must be cleared per call (rowmax, colmax, counters)
@@ -1597,7 +1650,7 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.zero_begin = off;
   w.rowmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * L * 4));
   w.colmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * S * 4));
-  w.counters = static_cast<int*>(take(16));
+  w.counters = static_cast<int*>(take(32));
   w.agg = static_cast<unsigned long long*>(take(COMPACT_BLOCKS * 8));
   w.ticket = static_cast<int*>(take(4));
   w.rowdelta = static_cast<unsigned long long*>(take(ra * 8));
@@ -1690,11 +1743,11 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     int r;
     if (screen) {  // fp16 operand planes of the sweep
       const long long va = static_cast<long long>(N) * Lp * C / 8, vb = static_cast<long long>(N) * Sp * C / 8;
-      PackSide sa{reinterpret_cast<const uint4*>(w.a_hi), reinterpret_cast<const uint4*>(w.a_lo), reinterpret_cast<uint4*>(w.a_f16), va};
-      PackSide sb{reinterpret_cast<const uint4*>(w.b_hi), reinterpret_cast<const uint4*>(w.b_lo), reinterpret_cast<uint4*>(w.b_f16), vb};
+      PackSide sa{reinterpret_cast<const uint4*>(w.a_hi), reinterpret_cast<const uint4*>(w.a_lo), reinterpret_cast<uint4*>(w.a_f16), va, L, Lp};
+      PackSide sb{reinterpret_cast<const uint4*>(w.b_hi), reinterpret_cast<const uint4*>(w.b_lo), reinterpret_cast<uint4*>(w.b_f16), vb, S, Sp};
       const int ba = static_cast<int>((va + 255) / 256 < 8 * num_sms() ? (va + 255) / 256 : 8 * num_sms());
       const int bb = static_cast<int>((vb + 255) / 256 < 4 * num_sms() ? (vb + 255) / 256 : 4 * num_sms());
-      pack_f16_kernel<<<ba + bb, 256, 0, stream>>>(sa, sb, ba, w.counters + 2);
+      pack_f16_kernel<<<ba + bb, 256, 0, stream>>>(sa, sb, ba, reinterpret_cast<unsigned*>(w.counters + 4));
       count_launch();
     }
     if (screen) {  // the data type of a tensor map only matters for its fill value
@@ -1722,17 +1775,14 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       sp.N = N, sp.L = L, sp.S = S, sp.Lp = Lp, sp.Sp = Sp;
       sp.n_tiles = (Sp + SW_BN - 1) / SW_BN;
       sp.total_tiles = m_tiles * sp.n_tiles;
-      sp.c = scale * kLog2e, sp.thr_lim = 0.9f * thr;
+      sp.c = scale * kLog2e, sp.thr = thr, sp.norm_sq = reinterpret_cast<const unsigned*>(w.counters + 4), sp.needs_robust = w.counters + 2;
       sp.colpart = reinterpret_cast<float*>(w.colpart), sp.col_ref = w.tile_ref;
       sp.rowpart = reinterpret_cast<float*>(w.rowpart), sp.row_ref = w.row_ref;
       sp.cand = w.cand, sp.cand_count = w.counters, sp.cand_cap = w.cand_cap;
       sp.trace = next_trace_slot(num_sms());
       sp.debug = dbg;
-      static bool configured_sweep = false;
-      if (!configured_sweep) {
-        OPB_CHECK_CUDA(cudaFuncSetAttribute(sim_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SW_SMEM));
-        configured_sweep = true;
-      }
+      static std::atomic<unsigned long long> configured_sweep{0};
+      if (int rr = opt_in_dyn_smem(sim_sweep_kernel, SW_SMEM, configured_sweep)) return rr;
       OPB_CHECK_CUDA(cudaMemsetAsync(w.row_ref, 0xff, static_cast<size_t>(SW_ROW_SLOTS) * (static_cast<size_t>(N) * Lp / 32) * 4, stream));
       const int grid = sp.total_tiles < num_sms() ? sp.total_tiles : num_sms();
       sim_sweep_kernel<<<grid, 64 + 128 * FAST_GROUPS, SW_SMEM, stream>>>(sp);
@@ -1752,19 +1802,17 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     fp.n_tiles = screen ? (Sp + FastCfg<true>::BN - 1) / FastCfg<true>::BN : (Sp + FastCfg<false>::BN - 1) / FastCfg<false>::BN;
     fp.total_tiles = m_tiles * fp.n_tiles;
     fp.c = scale * kLog2e;
-    fp.thr_lim = (screen ? 0.9f : 0.99f) * thr;
+    fp.thr_lim = 0.99f * thr, fp.thr = thr;
+    fp.norm_sq = reinterpret_cast<const unsigned*>(w.counters + 4), fp.needs_robust = w.counters + 2;
     fp.cand_tag = screen ? 2 : 1;
     fp.trace = next_trace_slot(num_sms());
     fp.debug = dbg;
     fp.rowpart = reinterpret_cast<float*>(w.rowpart), fp.colpart = reinterpret_cast<float*>(w.colpart);
     fp.tile_ref = w.tile_ref;
     fp.cand = w.cand, fp.cand_count = w.counters, fp.cand_cap = w.cand_cap;
-    static bool configured = false;
-    if (!configured) {
-      OPB_CHECK_CUDA(cudaFuncSetAttribute(sim_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FastCfg<false>::SMEM));
-      OPB_CHECK_CUDA(cudaFuncSetAttribute(sim_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FastCfg<true>::SMEM));
-      configured = true;
-    }
+    static std::atomic<unsigned long long> configured_split{0}, configured_screen{0};
+    if (int rr = opt_in_dyn_smem(sim_fast_kernel<false>, FastCfg<false>::SMEM, configured_split)) return rr;
+    if (int rr = opt_in_dyn_smem(sim_fast_kernel<true>, FastCfg<true>::SMEM, configured_screen)) return rr;
     const int grid = fp.total_tiles < num_sms() ? fp.total_tiles : num_sms();
     if (screen) sim_fast_kernel<true><<<grid, 64 + 128 * FAST_GROUPS, FastCfg<true>::SMEM, stream>>>(fp);
     else sim_fast_kernel<false><<<grid, 64 + 128 * FAST_GROUPS, FastCfg<false>::SMEM, stream>>>(fp);

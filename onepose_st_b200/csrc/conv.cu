@@ -45,6 +45,9 @@ struct ConvEpi {
   // FPN top-down path fused in: y += bilinear x2 (align_corners = True) of up [n, Ho/2, Wo/2, BN] fp16 (null = off)
   const __half* up;
   float up_ry, up_rx;
+  // nullable: bit 0 is set when a value stored as fp16 leaves the fp16 range (|v| > 65504): the caller must not trust
+  // this executor's result for these inputs (the host side repeats the backbone in fp32)
+  int* range_flag;
 };
 
 struct UpTaps {  // the four source pixels (element offsets) and weights of one output pixel
@@ -78,7 +81,7 @@ struct ConvCfg {
 
 // 16 accumulator columns of one pixel: bias, residual, activation, stores.
 __device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const ConvEpi& ep, long long off, int c0,
-                                               const UpTaps& ut) {
+                                               const UpTaps& ut, float& amax) {
   float v[16];
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
@@ -126,6 +129,7 @@ __device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const Co
     uint32_t h[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
+      amax = fmaxf(fmaxf(amax, fabsf(v[2 * i])), fabsf(v[2 * i + 1]));  // (all inputs were finite: see ConvEpi::range_flag)
       const __half2 p = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
       h[i] = *reinterpret_cast<const uint32_t*>(&p);
     }
@@ -284,6 +288,7 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
     const int row = quarter * 32 + lane;  // GEMM row inside the sub-tile
     const int hy = row / CONV_TW, wx = row - hy * CONV_TW;
     int it = 0;
+    float amax = 0.f;  // largest magnitude this thread stored as fp16
     for (int tq = t_first; tq < plan.num_tiles; tq += t_step, ++it) {
       const int acc = it % Cfg::ACC_STAGES;
       const uint32_t acc_phase = (it / Cfg::ACC_STAGES) & 1;
@@ -322,21 +327,22 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
         ptx::tmem_ld16(taddr + c * 16 + 16, r1);
         ptx::tmem_ld_wait();
         if (valid) {
-          conv_epi_chunk(r0, ep, off, c * 16, ut);
-          conv_epi_chunk(r1, ep, off, c * 16 + 16, ut);
+          conv_epi_chunk(r0, ep, off, c * 16, ut, amax);
+          conv_epi_chunk(r1, ep, off, c * 16 + 16, ut, amax);
         }
       }
       if (c < ch_end) {
         uint32_t r0[16];
         ptx::tmem_ld16(taddr + c * 16, r0);
         ptx::tmem_ld_wait();
-        if (valid) conv_epi_chunk(r0, ep, off, c * 16, ut);
+        if (valid) conv_epi_chunk(r0, ep, off, c * 16, ut, amax);
       }
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty_bar[acc]);
       if (tr) plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 3] = clock64();
     }
+    if (ep.range_flag != nullptr && !(amax <= 65504.f)) atomicOr(ep.range_flag, 1);
   }
 
   ptx::tc_fence_before();
@@ -353,10 +359,12 @@ static int launch_conv(const ConvPlan& plan_in, const ConvEpi& ep, cudaStream_t 
   using Cfg = ConvCfg<BN, MSUB>;
   auto kern = conv_kernel<BN, MSUB, CL2>;
   static_assert(Cfg::SMEM <= 227 * 1024, "shared memory budget exceeded");
-  static bool configured = false;
-  static int max_clusters = 0;
-  if (!configured) {
-    OPB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+  static std::atomic<unsigned long long> configured_dev{0};
+  if (int r = opt_in_dyn_smem(kern, Cfg::SMEM, configured_dev)) return r;
+  static std::atomic<int> max_clusters_a{0};  // (all devices of a box are the same part)
+  int max_clusters = max_clusters_a.load();
+  if (max_clusters == 0) {
+    max_clusters = 1;
     if (CL2) {
       cudaLaunchConfig_t q = {};
       q.gridDim = dim3(2 * num_sms());
@@ -372,7 +380,7 @@ static int launch_conv(const ConvPlan& plan_in, const ConvEpi& ep, cudaStream_t 
       OPB_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &q));
       if (max_clusters < 1) max_clusters = 1;
     }
-    configured = true;
+    max_clusters_a.store(max_clusters);
   }
   ConvPlan plan = plan_in;
   cudaLaunchConfig_t cfg = {};
@@ -466,7 +474,7 @@ int opb200_conv_cluster(int on) {
 
 int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride, int cout_s,
                            const float* bias, const void* res, const void* up, void* y16, float* y32, int act, float slope,
-                           void* stream_) {
+                           int* range_flag, void* stream_) {
   if (int r = check_device()) return r;
   OPB_CHECK_ARG(x && w && (y16 || y32), "null pointer");
   OPB_CHECK_ARG(n_img >= 1 && Hi >= 1 && Wi >= 1, "bad shape");
@@ -496,6 +504,7 @@ int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, 
   ep.slope = slope;
   ep.up = static_cast<const __half*>(up);
   ep.up_ry = ep.up_rx = 0.f;
+  ep.range_flag = range_flag;
   if (up != nullptr) {
     OPB_CHECK_ARG(plan.Ho % 2 == 0 && plan.Wo % 2 == 0, "fused x2 upsampling needs even output sides");
     OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(up) & 31) == 0, "up must be 32-byte aligned");

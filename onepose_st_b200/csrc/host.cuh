@@ -1,6 +1,7 @@
 // Host-side helpers shared by the C-ABI translation units: error reporting, TMA descriptor encoding,
 // GEMM plan construction and launch.
 #pragma once
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -112,17 +113,28 @@ struct PlanBuilder {
   }
 };
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute of a kernel: opt in once per (kernel, device).
+// ``done`` is the call site's bitmask of devices already configured (one static per kernel instantiation).
+template <typename Kern>
+inline int opt_in_dyn_smem(Kern kern, int bytes, std::atomic<unsigned long long>& done) {
+  int dev = 0;
+  OPB_CHECK_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (!(done.load(std::memory_order_acquire) & bit)) {
+    OPB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    done.fetch_or(bit, std::memory_order_release);
+  }
+  return OPB_OK;
+}
+
 template <int BN, int STAGES, int GROUPS, class Epi, int SPLIT = 1, bool F3 = false>
 int launch_gemm(const GemmPlan& plan, const typename Epi::Params& ep, cudaStream_t stream, int max_ctas = 0) {
   if (plan.num_tiles <= 0) return OPB_OK;
   auto kern = gemm_kernel<BN, STAGES, GROUPS, SPLIT, Epi, F3>;
   constexpr int smem = gemm_smem_bytes(BN, STAGES, GROUPS * Epi::kSmemBytes);
   static_assert(smem <= 227 * 1024, "shared memory budget exceeded");
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    OPB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
-  }
+  static std::atomic<unsigned long long> configured{0};  // per instantiation
+  if (int r = opt_in_dyn_smem(kern, smem, configured)) return r;
   int grid = num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   // the fewest CTAs that finish in the same number of tile waves: SMs a launch cannot use anyway stay free for

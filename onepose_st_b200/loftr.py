@@ -87,7 +87,7 @@ class CoarseMatching(nn.Module):
     def forward(self, feat_c0, feat_c1, data, mask_c0=None, mask_c1=None):
         self.finish(self.launch(feat_c0, feat_c1, data, mask_c0, mask_c1), data)
 
-    def launch(self, feat_c0, feat_c1, data, mask_c0=None, mask_c1=None) -> "ops.CoarseLaunch":
+    def launch(self, feat_c0, feat_c1, data, mask_c0=None, mask_c1=None, _status=None) -> "ops.CoarseLaunch":
         """Enqueue the matching kernels (no host sync; needs data['hw0_c'] / data['hw1_c'])."""
         if self.training:
             raise NotImplementedError("training-time coarse matching is out of scope of the inference path")
@@ -104,7 +104,7 @@ class CoarseMatching(nn.Module):
         return ops.coarse_match_launch(
             feat_c0, feat_c1, scale=1.0 / (C * self.temperature), thr=self.thr, border_rm=self.border_rm, border_mode=1,
             grid_a=(h0, w0), grid_b=(h1, w1), mask_a=mask_c0, mask_b=mask_c1, mask_fill=1, valid_hw=vhw,
-            materialize_conf=self.materialize_conf_matrix, precision=self.precision, planes=planes)
+            materialize_conf=self.materialize_conf_matrix, precision=self.precision, planes=planes, status=_status)
 
     def finish(self, handle: "ops.CoarseLaunch", data, copy: bool = False):
         """Read the match count (the forward's host sync) and fill the reference's coarse-level ``data`` keys."""
@@ -211,20 +211,23 @@ class LoFTR_for_OnePose_Plus(nn.Module):
         st["_graphs"] = HeadGraphs()
         return st
 
-    def _head(self, data, image0, image1, coarse):
+    def _head(self, data, image0, image1, coarse, conv_precision=None):
         """Backbone of both images (+ coarse LoFTR stack and coarse matching kernels when ``coarse``): everything before
-        the forward's host sync.  Returns ((feat_c0, feat_c1, feat_f0, feat_f1), launch handle | None, hw dict) and
+        the forward's host sync.  Returns ((feat_c0, feat_c1, feat_f0, feat_f1), launch handle | status words, hw dict) and
         sets the hw*_c / hw*_f keys of ``data``."""
+        # status words of the forward's one device -> host copy: [0..2] coarse matching, [3] fp16 range flag of the backbone
+        status = torch.zeros(4, dtype=torch.int32, device=image0.device) if image0.is_cuda else None
+        bkw = dict(_precision=conv_precision, _range_flag=None if status is None else status[3:])
         if image0.shape[2:] == image1.shape[2:]:
-            feats_c, feats_f = self.backbone(torch.cat([image0, image1], dim=0))
+            feats_c, feats_f = self.backbone(torch.cat([image0, image1], dim=0), **bkw)
             (feat_c0, feat_c1), (feat_f0, feat_f1) = feats_c.split(image0.size(0)), feats_f.split(image0.size(0))
         else:
-            (feat_c0, feat_f0), (feat_c1, feat_f1) = self.backbone(image0), self.backbone(image1)
+            (feat_c0, feat_f0), (feat_c1, feat_f1) = self.backbone(image0, **bkw), self.backbone(image1, **bkw)
         hw = {"hw0_c": tuple(feat_c0.shape[2:]), "hw1_c": tuple(feat_c1.shape[2:]), "hw0_f": tuple(feat_f0.shape[2:]),
               "hw1_f": tuple(feat_f1.shape[2:])}
         data.update({"hw0_c": feat_c0.shape[2:], "hw1_c": feat_c1.shape[2:], "hw0_f": feat_f0.shape[2:],
                      "hw1_f": feat_f1.shape[2:]})
-        handle = None
+        handle = status  # fine-only entry: no coarse launch, the caller reads the range flag from the status words
         if coarse:
             s0 = feat_c0.flatten(2).permute(0, 2, 1)
             s1 = feat_c1.flatten(2).permute(0, 2, 1)
@@ -234,7 +237,7 @@ class LoFTR_for_OnePose_Plus(nn.Module):
             if "mask0" in data:
                 mask_c0, mask_c1 = data["mask0"].flatten(-2), data["mask1"].flatten(-2)
             planes = self.loftr_coarse(s0, s1, mask_c0, mask_c1, _add0=add0, _add1=add1, _planes_only=True)
-            handle = self.coarse_matching.launch(planes, None, data, mask_c0=mask_c0, mask_c1=mask_c1)
+            handle = self.coarse_matching.launch(planes, None, data, mask_c0=mask_c0, mask_c1=mask_c1, _status=status)
         return (feat_c0, feat_c1, feat_f0, feat_f1), handle, hw
 
     @torch.no_grad()
@@ -245,7 +248,7 @@ class LoFTR_for_OnePose_Plus(nn.Module):
         coarse = "mkpts0_c" not in data
         if self.cuda_graph and coarse and "mask0" not in data and data["image0"].is_cuda:
             key = (self.coarse_matching.precision, getattr(self.loftr_coarse, "precision", ops.PREC_BF16X3),
-                   torch.backends.cudnn.allow_tf32, self.coarse_matching.materialize_conf_matrix)
+                   self.backbone.conv_precision, self.coarse_matching.materialize_conf_matrix)
             proto = {k: data[k] for k in ("bs", "hw0_i", "hw1_i")}
             feats, handle, hw = self._graphs.run(key, (data["image0"], data["image1"]),
                                                  lambda i0, i1: self._head(dict(proto), i0, i1, True))
@@ -254,6 +257,18 @@ class LoFTR_for_OnePose_Plus(nn.Module):
             self.coarse_matching.finish(handle, data, copy=True)
         else:
             (feat_c0, feat_c1, feat_f0, feat_f1), handle, _ = self._head(data, data["image0"], data["image1"], coarse)
+            if coarse:
+                self.coarse_matching.finish(handle, data)
+        out_of_range = (handle.extra and handle.extra[0]) if coarse else (handle is not None and int(handle[3].item()))
+        if out_of_range:
+            # the fp16 backbone stored a value beyond the fp16 range: repeat the head with exact-fp32 convolutions
+            if not self.__dict__.get("_warned_fp16_range"):
+                import logging
+                logging.getLogger("onepose_st_b200").warning(
+                    "backbone activations left the fp16 range; repeating this forward with conv_precision='fp32' "
+                    "(set model.backbone.conv_precision = 'fp32' to avoid the repeated work)")
+                self.__dict__["_warned_fp16_range"] = True
+            (feat_c0, feat_c1, feat_f0, feat_f1), handle, _ = self._head(data, data["image0"], data["image1"], coarse, "fp32")
             if coarse:
                 self.coarse_matching.finish(handle, data)
         if not coarse:

@@ -15,6 +15,17 @@ import torch.nn.functional as F
 
 from . import _lib, ops
 
+_cache_lock = threading.RLock()  # check-then-set of the per-sequence caches (host threads of pipeline.StreamPipeline)
+
+
+def tensor_key(t: torch.Tensor):
+    """Identity of a tensor's current contents for the per-sequence caches: (address, version counter, shape, strides).
+    Only meaningful while the cache entry holds a reference to ``t`` (the address cannot be recycled then).  ``None``
+    for inference tensors, which track no version: callers must not cache on them."""
+    if t.is_inference():
+        return None
+    return (t.data_ptr(), t._version, tuple(t.shape), tuple(t.stride()))
+
 
 # --------------------------------------------------------------------------------------------------
 # Backbone: ResNetFPN_8_2 (reference: src/models/OnePosePlus/backbone/resnet.py:85-164 and
@@ -68,9 +79,12 @@ class ResNetFPN_8_2(nn.Module):
         return nn.Sequential(nn.Conv2d(cin, cmid, 3, 1, 1, bias=False), nn.BatchNorm2d(cmid), nn.LeakyReLU(),
                              nn.Conv2d(cmid, cout, 3, 1, 1, bias=False))
 
-    def forward(self, x):
+    def forward(self, x, _precision: Optional[str] = None, _range_flag: Optional[torch.Tensor] = None):
+        """``_precision`` overrides ``conv_precision`` for this call; ``_range_flag`` (int32 [1] on the device, optional)
+        receives bit 0 when the fp16 executor had to store a value outside the fp16 range (see ``conv_precision``)."""
         if x.is_cuda and not self.training and not torch.is_grad_enabled():
-            return self.fused()(x)
+            fb = self.fused(_precision)
+            return fb(x, _range_flag) if isinstance(fb, FusedBackboneF16) else fb(x)
         x1 = self.layer1(self.relu(self.bn1(self.conv1(x))))
         x2 = self.layer2(x1)
         x3 = self.layer3(x2)
@@ -80,21 +94,33 @@ class ResNetFPN_8_2(nn.Module):
         c1 = self.layer1_outconv2(self.layer1_outconv(x1) + up(c2))
         return c3, c1
 
-    # "auto": follow torch.backends.cudnn.allow_tf32, the switch that decides the precision of the reference's own
-    # convolutions on a GPU -- True (torch's default): fp16-operand tcgen05 convolutions (same 11-bit significand as
-    # TF32); False: exact-fp32 cuDNN executor.  "f16" / "fp32" force one.
-    conv_precision = "auto"
+    # Precision of the inference executor, an explicit per-module (or per-class) setting -- no global switch decides it:
+    #   "f16"  (default) own tcgen05 implicit-GEMM convolutions on fp16 operands with fp32 accumulation: the 11-bit
+    #          significand of the TF32 operands the reference's cuDNN convolutions use on a GPU, but fp16's exponent
+    #          range (|x| <= 65504).  The kernels flag any stored value that leaves that range and the matchers then
+    #          repeat the backbone with "fp32" for that call (OnePosePlus_model / LoFTR_for_OnePose_Plus.forward).
+    #   "fp32" exact-fp32 cuDNN executor (library code; what the fp32-grade parity tests select).
+    conv_precision = "f16"
 
-    def fused(self):
+    def fused(self, precision: Optional[str] = None):
         """Inference executor (BN folded into the convolutions, NHWC): ``FusedBackboneF16`` (own tcgen05 implicit-GEMM
         convolutions) or ``FusedBackbone`` (cuDNN fp32); rebuilt whenever a parameter or buffer changes."""
-        f16 = self.conv_precision == "f16" or (self.conv_precision == "auto" and torch.backends.cudnn.allow_tf32)
-        f16 = f16 and FusedBackboneF16.supports(self)
-        key = (f16,) + tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers()))
-        fb = self.__dict__.get("_fused_cache")
+        precision = precision or self.conv_precision
+        if precision not in ("f16", "fp32"):
+            raise ValueError(f"conv_precision must be 'f16' or 'fp32', got {precision!r}")
+        f16 = precision == "f16" and FusedBackboneF16.supports(self)
+        key = tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers()))
+        cache = self.__dict__.setdefault("_fused_cache", {})
+        fb = cache.get(f16)
         if fb is None or fb[0] != key:
-            fb = (key, FusedBackboneF16(self) if f16 else FusedBackbone(self))
-            self.__dict__["_fused_cache"] = fb
+            with _cache_lock:
+                fb = cache.get(f16)
+                if fb is None or fb[0] != key:
+                    fb = (key, FusedBackboneF16(self) if f16 else FusedBackbone(self))
+                    dev = self.conv1.weight.device
+                    if dev.type == "cuda":
+                        torch.cuda.current_stream(dev).synchronize()  # folded weights are read from other streams too
+                    cache[f16] = fb
         return fb[1]
 
     def __getstate__(self):
@@ -232,35 +258,38 @@ class FusedBackboneF16:
                       m.layer1_outconv2[2].negative_slope)
 
     @staticmethod
-    def _block(x, blk):
+    def _block(x, blk, rf):
         (w1, b1), (w2, b2), ds, stride = blk
-        y = ops.conv2d_nhwc_f16(x, w1, 3, stride, b1, None, 1)
+        y = ops.conv2d_nhwc_f16(x, w1, 3, stride, b1, None, 1, range_flag=rf)
         if ds is not None:
-            x = ops.conv2d_nhwc_f16(x, ds[0], 1, stride, ds[1], None, 0)
-        return ops.conv2d_nhwc_f16(y, w2, 3, 1, b2, x, 1)
+            x = ops.conv2d_nhwc_f16(x, ds[0], 1, stride, ds[1], None, 0, range_flag=rf)
+        return ops.conv2d_nhwc_f16(y, w2, 3, 1, b2, x, 1, range_flag=rf)
 
     @staticmethod
-    def _head(x, head, out_f32):
+    def _head(x, head, out_f32, rf):
         (w0, b0), (w1, b1), slope = head
-        y = ops.conv2d_nhwc_f16(x, w0, 3, 1, b0, None, 2, slope)
-        return ops.conv2d_nhwc_f16(y, w1, 3, 1, b1, None, 0, out_f16=not out_f32, out_f32=out_f32)
+        y = ops.conv2d_nhwc_f16(x, w0, 3, 1, b0, None, 2, slope, range_flag=rf)
+        return ops.conv2d_nhwc_f16(y, w1, 3, 1, b1, None, 0, out_f16=not out_f32, out_f32=out_f32, range_flag=rf)
 
-    def __call__(self, x):
+    def __call__(self, x, range_flag: Optional[torch.Tensor] = None):
+        """``range_flag``: int32 [1] device tensor that collects the kernels' "value left the fp16 range" bit."""
         if x.shape[2] % 8 or x.shape[3] % 8:
             raise NotImplementedError("ResNetFPN_8_2 on CUDA needs image sides that are multiples of 8")
-        x = ops.stem_conv_relu_f16(x, self.stem[0], self.stem[1])
+        rf = range_flag
+        x = ops.stem_conv_relu_f16(x, self.stem[0], self.stem[1], rf)
         feats = []
         for i, blk in enumerate(self.blocks):
-            x = self._block(x, blk)
+            x = self._block(x, blk, rf)
             if i % 2 == 1:
                 feats.append(x)
         x1, x2, x3 = feats
-        c3_16, c3 = ops.conv2d_nhwc_f16(x3, self.l3_out[0], 1, 1, self.l3_out[1], None, 0, out_f16=True, out_f32=True)
+        c3_16, c3 = ops.conv2d_nhwc_f16(x3, self.l3_out[0], 1, 1, self.l3_out[1], None, 0, out_f16=True, out_f32=True,
+                                        range_flag=rf)
         # lateral 1x1 convolution + bilinear x2 of the coarser level, one kernel per FPN level
-        l2 = ops.conv2d_nhwc_f16(x2, self.l2_out[0], 1, 1, self.l2_out[1], None, 0, up=c3_16)
-        c2 = self._head(l2, self.head2, False)
-        l1 = ops.conv2d_nhwc_f16(x1, self.l1_out[0], 1, 1, self.l1_out[1], None, 0, up=c2)
-        c1 = self._head(l1, self.head1, True)
+        l2 = ops.conv2d_nhwc_f16(x2, self.l2_out[0], 1, 1, self.l2_out[1], None, 0, up=c3_16, range_flag=rf)
+        c2 = self._head(l2, self.head2, False, rf)
+        l1 = ops.conv2d_nhwc_f16(x1, self.l1_out[0], 1, 1, self.l1_out[1], None, 0, up=c2, range_flag=rf)
+        c1 = self._head(l1, self.head1, True, rf)
         return c3.permute(0, 3, 1, 2), c1.permute(0, 3, 1, 2)
 
 
@@ -277,11 +306,27 @@ class HeadGraphs:
     _serial = 0
 
     def __init__(self, max_entries: int = 16):
-        self.entries = {}
+        self.entries = {}  # insertion / use ordered: the first key is the least recently used
         self.max_entries = max_entries
 
     def __len__(self):
         return len(self.entries)
+
+    def _drop(self, key):
+        """Forget one graph and free the workspaces it owned (they live in the graph's private memory pool)."""
+        ent = self.entries.pop(key, None)
+        if ent is not None:
+            ops.workspaces.drop_scope(ent[5])
+
+    def clear(self):
+        for key in list(self.entries):
+            self._drop(key)
+
+    def __del__(self):
+        try:
+            self.clear()
+        except Exception:  # interpreter shutdown
+            pass
 
     def run(self, key, inputs, fn, guard=None):
         """``fn(*static_inputs)`` replayed on the current stream with ``inputs`` copied into the static buffers.
@@ -291,6 +336,7 @@ class HeadGraphs:
         key = (torch.cuda.current_stream(dev).cuda_stream, dev.index) + tuple(key) + tuple(tuple(t.shape) for t in inputs)
         ent = self.entries.get(key)
         if ent is not None and guard is not None and ent[4] != guard():
+            self._drop(key)
             ent = None
         if ent is None:
             static = [torch.empty_like(t, memory_format=torch.contiguous_format) for t in inputs]
@@ -300,17 +346,19 @@ class HeadGraphs:
             torch.cuda.current_stream(dev).synchronize()
             with HeadGraphs._lock:
                 HeadGraphs._serial += 1
+                scope = ("graph", HeadGraphs._serial)
                 g = torch.cuda.CUDAGraph()
                 l0 = _lib.launch_count()
-                with ops.workspaces.scope(("graph", HeadGraphs._serial)), \
-                        torch.cuda.graph(g, capture_error_mode="thread_local"):
+                with ops.workspaces.scope(scope), torch.cuda.graph(g, capture_error_mode="thread_local"):
                     out = fn(*static)
                 n_launch = _lib.launch_count() - l0  # this library's kernels inside one replay
-            ent = (g, static, out, n_launch, None if guard is None else guard())
-            if len(self.entries) >= self.max_entries:
-                self.entries.clear()
+            ent = (g, static, out, n_launch, None if guard is None else guard(), scope)
+            while len(self.entries) >= self.max_entries:
+                self._drop(next(iter(self.entries)))  # least recently used
             self.entries[key] = ent
-        g, static, out, n_launch, _ = ent
+        else:
+            self.entries[key] = self.entries.pop(key)  # mark as most recently used
+        g, static, out, n_launch = ent[:4]
         for st, t in zip(static, inputs):
             st.copy_(t, non_blocking=True)
         g.replay()
@@ -346,10 +394,15 @@ class PositionEncodingSine(nn.Module):
         key = (h, w, self.pe.device)
         t = self._tables.get(key)
         if t is None:
-            t = self.pe[0, :, :h, :w].reshape(self.pe.shape[1], h * w).t().contiguous()
-            if len(self._tables) >= 8:  # tables stay alive (CUDA graphs of the matcher head read them by address)
-                self._tables = {}
-            self._tables[key] = t
+            with _cache_lock:
+                t = self._tables.get(key)
+                if t is None:
+                    t = self.pe[0, :, :h, :w].reshape(self.pe.shape[1], h * w).t().contiguous()
+                    if t.is_cuda:
+                        torch.cuda.current_stream(t.device).synchronize()  # other streams may read it right away
+                    if len(self._tables) >= 8:  # tables stay alive (CUDA graphs of the matcher head read them by address)
+                        self._tables = {}
+                    self._tables[key] = t
         return t
 
 
@@ -409,8 +462,11 @@ class LoFTREncoderLayer(nn.Module):
         ps = self._params()
         key = tuple((p.data_ptr(), p._version, str(p.device)) for p in ps)
         if self._packed is None or key != self._packed_key:
-            self._packed = ops.pack_layer_weights(*ps)
-            self._packed_key = key
+            with _cache_lock:
+                if self._packed is None or key != self._packed_key:
+                    packed = ops.pack_layer_weights(*ps)
+                    torch.cuda.current_stream(packed.device).synchronize()  # other streams may read it right away
+                    self._packed, self._packed_key = packed, key
         return self._packed
 
     def __getstate__(self):  # the packed buffer is a cache: rebuild after unpickling (Ray ships models by pickle)
@@ -456,17 +512,20 @@ class _TransformerBase(nn.Module):
         # fixed 3D model of a sequence matched against many frames) its output is computed once and reused for every
         # forward until the tensor, the layer's weights or the precision change.
         if (self.reuse_static_stream0 and self.schedule == 0 and kinds and kinds[0] == 0 and mask0 is None
-                and x0.dim() == 3 and x0.shape[0] > 1 and x0.stride(0) == 0 and self.d_model == 256):
-            key = (x0.data_ptr(), x0._version, tuple(x0.shape), tuple(x0.stride()), prec,
-                   None if add0 is None else (add0.data_ptr(), add0._version),
+                and x0.dim() == 3 and x0.shape[0] > 1 and x0.stride(0) == 0 and self.d_model == 256
+                and tensor_key(x0) is not None and (add0 is None or tensor_key(add0) is not None)):
+            key = (tensor_key(x0), prec, None if add0 is None else tensor_key(add0),
                    tuple((p.data_ptr(), p._version) for p in layers[0].parameters()))
-            hit = self.__dict__.get("_stream0_cache")
-            if hit is None or hit[0] != key:
-                y0, _ = ops.transformer([layers[0].packed()], [3], 0, self.d_model, self.nhead, x0[:1],
-                                        x0.new_zeros(1, 128, self.d_model), add0=add0, big_groups=True, precision=prec)
-                torch.cuda.current_stream(x0.device).synchronize()  # other streams may consume the cached tensor
-                hit = (key, y0)
-                self.__dict__["_stream0_cache"] = hit
+            with _cache_lock:
+                hit = self.__dict__.get("_stream0_cache")
+                if hit is None or hit[0] != key:
+                    y0, _ = ops.transformer([layers[0].packed()], [3], 0, self.d_model, self.nhead, x0[:1],
+                                            x0.new_zeros(1, 128, self.d_model), add0=add0, big_groups=True, precision=prec)
+                    torch.cuda.current_stream(x0.device).synchronize()  # other streams may consume the cached tensor
+                    # the entry keeps x0 / add0 alive: while it is current no other tensor can take their addresses, so an
+                    # equal (address, version) key means the same contents; the serial tells CUDA graphs of a rebuild
+                    hit = (key, y0, x0, add0, (hit[4] + 1) if hit is not None else 1)
+                    self.__dict__["_stream0_cache"] = hit
             x0, add0, kinds = hit[1].expand(x0.shape[0], -1, -1), None, [2] + kinds[1:]
         return ops.transformer([l.packed() for l in layers], kinds, self.schedule, self.d_model, self.nhead, x0, x1,
                                add0=add0, add1=add1, mask0=mask0, mask1=mask1, big_groups=(self.d_model == 256),

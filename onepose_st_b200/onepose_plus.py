@@ -15,7 +15,7 @@ import torch.nn as nn
 
 from . import _lib, ops
 from .nn_common import (HeadGraphs, LinearAttention, LoFTREncoderLayer, PositionEncodingSine, ResNetFPN_8_2,
-                        _TransformerBase, fine_expectation)
+                        _TransformerBase, _cache_lock, fine_expectation, tensor_key)
 
 logger = logging.getLogger("onepose_st_b200")
 
@@ -157,7 +157,7 @@ class CoarseMatching(nn.Module):
     def forward(self, feat_db_3d, feat_query, data, mask_query=None):
         self.finish(self.launch(feat_db_3d, feat_query, data, mask_query), data)
 
-    def launch(self, feat_db_3d, feat_query, data, mask_query=None) -> "ops.CoarseLaunch":
+    def launch(self, feat_db_3d, feat_query, data, mask_query=None, _status=None) -> "ops.CoarseLaunch":
         """Enqueue the matching kernels (no host sync; needs data['q_hw_c'])."""
         if self.training:
             raise NotImplementedError("training-time coarse matching (GT padding) is out of scope of the inference path")
@@ -171,7 +171,7 @@ class CoarseMatching(nn.Module):
             return ops.coarse_match_launch(
                 feat_db_3d, feat_query, scale=scale, thr=self.thr, border_rm=self.border_rm, border_mode=0, grid_a=None,
                 grid_b=(hc, wc), mask_b=mask_query, mask_fill=0, materialize_conf=self.materialize_conf_matrix,
-                precision=self.precision, planes=planes)
+                precision=self.precision, planes=planes, status=_status)
 
     def finish(self, handle: "ops.CoarseLaunch", data, copy: bool = False):
         """Read the match count (the forward's host sync) and fill the reference's coarse-level ``data`` keys."""
@@ -300,18 +300,31 @@ class OnePosePlus_model(nn.Module):
         if self.kpt_3d_pos_encoding is None:
             return desc
         kp = data["keypoints3d"]
-        key = (kp.data_ptr(), kp._version, tuple(kp.shape), tuple(kp.stride()), desc.data_ptr(), desc._version,
-               tuple(desc.shape), tuple(desc.stride()),
-               tuple(p._version for p in self.kpt_3d_pos_encoding.parameters()))
-        if self._kpt_cache is None or self._kpt_cache[0] != key:
+
+        def encode():
             if kp.shape[0] > 1 and kp.stride(0) == 0 and desc.stride(0) == 0:
                 # one 3D model broadcast over the batch: encode it once, hand out a broadcast view (stride 0), which is
                 # also what lets the coarse transformer reuse its first self layer on this stream
-                enc = self.kpt_3d_pos_encoding(normalize_3d_keypoints(kp[:1]), desc[:1]).expand(kp.shape[0], -1, -1)
-            else:
-                enc = self.kpt_3d_pos_encoding(normalize_3d_keypoints(kp), desc)
-            self._kpt_cache = (key, enc)
-        return self._kpt_cache[1]
+                return self.kpt_3d_pos_encoding(normalize_3d_keypoints(kp[:1]), desc[:1]).expand(kp.shape[0], -1, -1)
+            return self.kpt_3d_pos_encoding(normalize_3d_keypoints(kp), desc)
+
+        if tensor_key(kp) is None or tensor_key(desc) is None:  # inference tensors track no version: never cached
+            return encode()
+        key = (tensor_key(kp), tensor_key(desc),
+               tuple((p.data_ptr(), p._version) for p in self.kpt_3d_pos_encoding.parameters()))
+        hit = self._kpt_cache
+        if hit is None or hit[0] != key:
+            with _cache_lock:
+                hit = self._kpt_cache
+                if hit is None or hit[0] != key:
+                    enc = encode()
+                    if enc.is_cuda:
+                        torch.cuda.current_stream(enc.device).synchronize()  # other streams read it too
+                    # the entry holds kp and desc: while it is current their addresses cannot be handed to other tensors
+                    # (a freed-and-reallocated 3D model of the same shape must not hit), and a serial for the CUDA graphs
+                    hit = (key, enc, kp, desc, (hit[4] + 1) if hit is not None else 1)
+                    self._kpt_cache = hit
+        return hit[1]
 
     def __getstate__(self):
         st = self.__dict__.copy()
@@ -319,10 +332,12 @@ class OnePosePlus_model(nn.Module):
         st["_graphs"] = HeadGraphs()
         return st
 
-    def _head(self, data, img, qmask):
+    def _head(self, data, img, qmask, conv_precision=None):
         """Backbone -> coarse LoFTR stack -> coarse matching kernels: everything before the forward's host sync.
         Returns (coarse launch handle, fine feature map, (hc, wc)); sets data['q_hw_c']."""
-        feat_c, feat_f = self.backbone(img)
+        # status words of the forward's one device -> host copy: [0..2] coarse matching, [3] fp16 range flag of the backbone
+        status = torch.zeros(4, dtype=torch.int32, device=img.device) if img.is_cuda else None
+        feat_c, feat_f = self.backbone(img, _precision=conv_precision, _range_flag=None if status is None else status[3:])
         data.update({"q_hw_c": feat_c.shape[2:]})
         n, c, hc, wc = feat_c.shape
         # 'n c h w -> n (h w) c' (+ PE) happens inside the transformer's stage-in kernel
@@ -331,7 +346,7 @@ class OnePosePlus_model(nn.Module):
         desc3d = self._encode_3d(data)
         # the coarse features are consumed by CoarseMatching only: hand them over as bf16 planes
         planes = self.loftr_coarse(desc3d, q2d, query_mask=qmask, _add2d=add2d, _planes_only=True)
-        return self.coarse_matching.launch(planes, None, data, mask_query=qmask), feat_f, feat_c.shape[2:]
+        return self.coarse_matching.launch(planes, None, data, mask_query=qmask, _status=status), feat_f, feat_c.shape[2:]
 
     # ---- CUDA graph of the head (nn_common.HeadGraphs) ----------------------------------------------------------
     # Opt-in: a replay reuses static buffers and assumes the weights are not modified in place between forwards.
@@ -340,14 +355,16 @@ class OnePosePlus_model(nn.Module):
     def _graphed_head(self, data, img):
         kp = data["keypoints3d"]
         desc = data["descriptors3d_coarse_db"] if "descriptors3d_coarse_db" in data else data["descriptors3d_db"]
-        key = (kp.data_ptr(), kp._version, tuple(kp.shape), tuple(kp.stride()), desc.data_ptr(), desc._version,
-               tuple(desc.shape), tuple(desc.stride()), self.coarse_matching.precision,
-               getattr(self.loftr_coarse, "precision", ops.PREC_BF16X3), torch.backends.cudnn.allow_tf32,
+        # the per-sequence cache is consulted on every forward (a replay never reaches _head): a new 3D model rebuilds it
+        # here, which changes the serial in cache_ids() below and drops the graphs captured for the previous model
+        self._encode_3d(data)
+        key = (tuple(kp.shape), tuple(kp.stride()), tuple(desc.shape), tuple(desc.stride()), self.coarse_matching.precision,
+               getattr(self.loftr_coarse, "precision", ops.PREC_BF16X3), self.backbone.conv_precision,
                self.coarse_matching.materialize_conf_matrix)
 
-        def cache_ids():  # tensors the captured kernels read by address besides the weights
+        def cache_ids():  # tensors the captured kernels read by address besides the weights: (address, rebuild serial)
             c0, k0 = self.loftr_coarse.__dict__.get("_stream0_cache"), self._kpt_cache
-            return (None if c0 is None else c0[1].data_ptr(), None if k0 is None else k0[1].data_ptr())
+            return (None if c0 is None else (c0[1].data_ptr(), c0[4]), None if k0 is None else (k0[1].data_ptr(), k0[4]))
 
         def head(static_img):
             handle, feat_f, hw_c = self._head(dict(data), static_img, None)
@@ -363,12 +380,24 @@ class OnePosePlus_model(nn.Module):
         img = data["query_image"]
         data.update({"bs": img.size(0), "q_hw_i": img.shape[2:]})
         qmask = data["query_image_mask"].flatten(-2) if "query_image_mask" in data else None
-        if self.cuda_graph and qmask is None and img.is_cuda:
+        cacheable = tensor_key(data["keypoints3d"]) is not None and tensor_key(data["descriptors3d_db"]) is not None \
+            and ("descriptors3d_coarse_db" not in data or tensor_key(data["descriptors3d_coarse_db"]) is not None)
+        if self.cuda_graph and qmask is None and img.is_cuda and cacheable:
             handle, feat_f, hw_c = self._graphed_head(data, img)
             data.update({"q_hw_c": hw_c, "q_hw_f": feat_f.shape[2:]})
             self.coarse_matching.finish(handle, data, copy=True)
         else:
             handle, feat_f, hw_c = self._head(data, img, qmask)
+            data.update({"q_hw_f": feat_f.shape[2:]})
+            self.coarse_matching.finish(handle, data)
+        if handle.extra and handle.extra[0]:
+            # the fp16 backbone stored a value beyond the fp16 range (unnormalised images, very large folded BatchNorm
+            # gains): its maps cannot be trusted for this input -- the head is repeated with exact-fp32 convolutions
+            if not self.__dict__.get("_warned_fp16_range"):
+                logger.warning("backbone activations left the fp16 range; repeating this forward with conv_precision='fp32' "
+                               "(set model.backbone.conv_precision = 'fp32' to avoid the repeated work)")
+                self.__dict__["_warned_fp16_range"] = True
+            handle, feat_f, hw_c = self._head(data, img, qmask, conv_precision="fp32")
             data.update({"q_hw_f": feat_f.shape[2:]})
             self.coarse_matching.finish(handle, data)
         if not self.config["fine_matching"]["enable"]:

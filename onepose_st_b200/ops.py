@@ -185,15 +185,20 @@ class CoarseLaunch:
 
     def __init__(self, outs, cnt, conf, cap, retry):
         self.outs, self.cnt, self.conf, self.cap, self.retry = outs, cnt, conf, cap, retry
+        self.extra = []  # status words beyond the first three, filled by coarse_match_finish
 
 
 def coarse_match_launch(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: float, thr: float, border_rm: int,
                         border_mode: int, grid_a, grid_b, mask_a: Optional[torch.Tensor] = None,
                         mask_b: Optional[torch.Tensor] = None, mask_fill: int = 0,
                         valid_hw: Optional[torch.Tensor] = None, materialize_conf: bool = False,
-                        precision: int = PREC_BF16X3, algo: int = 0, planes: Optional[FeaturePlanes] = None) -> CoarseLaunch:
+                        precision: int = PREC_BF16X3, algo: int = 0, planes: Optional[FeaturePlanes] = None,
+                        status: Optional[torch.Tensor] = None) -> CoarseLaunch:
     """Enqueues the dual-softmax + mutual-NN kernels on the current stream; no host synchronisation (capturable in
-    a CUDA graph).  With ``planes`` (from ``transformer(..., planes_only=True)``) feat_a / feat_b are ignored."""
+    a CUDA graph).  With ``planes`` (from ``transformer(..., planes_only=True)``) feat_a / feat_b are ignored.
+    ``status`` (optional, zeroed int32 [>= 3]): where the call leaves (match count, overflow, rerun code); words beyond the
+    third belong to the caller (the matchers keep the backbone's fp16 range flag there) and reach the host with the same
+    copy, as ``CoarseLaunch.extra`` after ``coarse_match_finish``."""
     if planes is not None:
         n, L, S, C = planes.n, planes.len0, planes.len1, planes.c
         if planes.padded != ((L + 127) // 128 * 128, (S + 127) // 128 * 128):
@@ -216,7 +221,7 @@ def coarse_match_launch(feat_a: torch.Tensor, feat_b: torch.Tensor, *, scale: fl
     i_ids = torch.empty(cap, dtype=torch.int64, device=dev)
     j_ids = torch.empty(cap, dtype=torch.int64, device=dev)
     mconf = torch.empty(cap, dtype=torch.float32, device=dev)
-    cnt = torch.zeros(3, dtype=torch.int32, device=dev)
+    cnt = status if status is not None else torch.zeros(3, dtype=torch.int32, device=dev)
     conf = torch.empty(n, L, S, dtype=torch.float32, device=dev) if materialize_conf else None
 
     def m8(m, length):
@@ -252,7 +257,9 @@ def coarse_match_finish(h: CoarseLaunch, copy: bool = False):
     """The one host sync of the matcher (reading the match count; the reference syncs at the same point through
     torch.where).  Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None); ``copy`` detaches the results from the
     launch's buffers (needed when those are the static buffers of a CUDA graph)."""
-    m, overflow, rerun = h.cnt.tolist()
+    words = h.cnt.tolist()
+    (m, overflow, rerun), h.extra = words[:3], words[3:]
+    h.rerun = rerun  # 0: the launched algorithm's result stands; 1 / 2: it asked for the two-pass / split-product repeat
     if rerun:  # 1: the single-pass statistics hit their dynamic-range guard -> two-pass path;
         kw = dict(h.retry)  # 2: features outside the fp16 screening range -> single pass on the three split products
         a, b = kw.pop("feat_a"), kw.pop("feat_b")
@@ -270,10 +277,14 @@ def coarse_match_finish(h: CoarseLaunch, copy: bool = False):
     return b_ids[:m], i_ids[:m], j_ids[:m], mconf[:m], h.conf
 
 
-def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, **kw):
+def coarse_match(feat_a: torch.Tensor, feat_b: torch.Tensor, _info: Optional[dict] = None, **kw):
     """Dual-softmax + mutual-NN selection: ``coarse_match_launch`` + ``coarse_match_finish``.
-    Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None)."""
-    return coarse_match_finish(coarse_match_launch(feat_a, feat_b, **kw))
+    Returns (b_ids, i_ids, j_ids, mconf, conf_matrix|None).  ``_info`` (tests): receives {'rerun': code}."""
+    h = coarse_match_launch(feat_a, feat_b, **kw)
+    out = coarse_match_finish(h)
+    if _info is not None:
+        _info["rerun"] = h.rerun
+    return out
 
 
 def _err_flag(dev) -> torch.Tensor:
@@ -411,9 +422,12 @@ def linear_attention(q, k, v, q_mask=None, kv_mask=None, eps: float = 1e-6) -> t
 # ------------------------------------------------------------------------------------------------
 def conv2d_nhwc_f16(x: torch.Tensor, w: torch.Tensor, ksize: int, stride: int = 1, bias: Optional[torch.Tensor] = None,
                     res: Optional[torch.Tensor] = None, act: int = 0, slope: float = 0.0, out_f16: bool = True,
-                    out_f32: bool = False, stage: str = "backbone_conv", up: Optional[torch.Tensor] = None):
+                    out_f32: bool = False, stage: str = "backbone_conv", up: Optional[torch.Tensor] = None,
+                    range_flag: Optional[torch.Tensor] = None):
     """y = act(conv_k(x) + bias + res): x [N,Hi,Wi,Cin_s] fp16, w [k*k*Cout_s, Cin_s] fp16 tap-major, bias [Cout_s] fp32,
-    res [N,Ho,Wo,Cout_s] fp16, up [N,Ho/2,Wo/2,Cout_s] fp16 (bilinear x2, align_corners=True, added before act).  Returns the fp16 output, the fp32 output, or (fp16, fp32) when both are asked."""
+    res [N,Ho,Wo,Cout_s] fp16, up [N,Ho/2,Wo/2,Cout_s] fp16 (bilinear x2, align_corners=True, added before act).  Returns the
+    fp16 output, the fp32 output, or (fp16, fp32) when both are asked.  ``range_flag`` (int32 [1], optional): bit 0 is set
+    by the kernel when a value leaves the fp16 range on its way into the fp16 output."""
     _need_cuda(x, w, bias, res)
     if x.dtype != torch.float16 or w.dtype != torch.float16 or not x.is_contiguous() or not w.is_contiguous() or x.dim() != 4:
         raise _lib.Opb200Error("conv2d_nhwc_f16: contiguous fp16 [N,H,W,C] input and fp16 weights required")
@@ -435,14 +449,15 @@ def conv2d_nhwc_f16(x: torch.Tensor, w: torch.Tensor, ksize: int, stride: int = 
     with _Stage(stage):
         st = _lib.lib().opb200_conv2d_nhwc_f16(_lib.ptr(x), n, hi, wi, cin_s, _lib.ptr(w), ksize, stride, cout_s, _lib.ptr(bias),
                                                _lib.ptr(res), _lib.ptr(up), _lib.ptr(y16), _lib.ptr(y32), act, ctypes.c_float(slope),
-                                               _lib.stream_ptr())
+                                               _lib.ptr(range_flag), _lib.stream_ptr())
     _lib.check(st, "opb200_conv2d_nhwc_f16")
     if out_f16 and out_f32:
         return y16, y32
     return y16 if out_f16 else y32
 
 
-def stem_conv_relu_f16(image: torch.Tensor, weight_tap_major: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
+def stem_conv_relu_f16(image: torch.Tensor, weight_tap_major: torch.Tensor, bias: torch.Tensor,
+                       range_flag: Optional[torch.Tensor] = None) -> torch.Tensor:
     """image [N,1,H,W] fp32 -> relu(conv7x7/2(image) + bias) as [N,Ho,Wo,Cout] fp16."""
     _need_cuda(image, weight_tap_major, bias)
     n, cin, h, w = image.shape
@@ -454,7 +469,7 @@ def stem_conv_relu_f16(image: torch.Tensor, weight_tap_major: torch.Tensor, bias
     out = torch.empty(n, ho, wo, cout, dtype=torch.float16, device=image.device)
     with _Stage("backbone_glue"):
         st = _lib.lib().opb200_stem_conv7x7_s2_relu_nhwc_f16(_lib.ptr(image), _lib.ptr(weight_tap_major), _lib.ptr(bias), n, h, w,
-                                                             cout, _lib.ptr(out), _lib.stream_ptr())
+                                                             cout, _lib.ptr(out), _lib.ptr(range_flag), _lib.stream_ptr())
     _lib.check(st, "opb200_stem_conv7x7_s2_relu_nhwc_f16")
     return out
 

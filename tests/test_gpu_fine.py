@@ -107,13 +107,9 @@ def test_backbone_fused_vs_plain_module(golden):
     m = ResNetFPN_8_2({"block_type": "BasicBlock", "initial_dim": 128, "block_dims": [128, 196, 256]})
     m.load_state_dict({k[len("backbone."):]: v for k, v in c["sd"].items()}, strict=True)
     m = m.cuda().eval()
-    old = torch.backends.cudnn.allow_tf32
-    torch.backends.cudnn.allow_tf32 = False
-    try:
-        with torch.no_grad():
-            fc, ff = m(c["image"].cuda())
-    finally:
-        torch.backends.cudnn.allow_tf32 = old
+    from conftest import backbone_precision
+    with backbone_precision("fp32"), torch.no_grad():
+        fc, ff = m(c["image"].cuda())
     g = golden("backbone")
     gc, gf = g["feat_c"], g["feat_f_sub"]
     ec = (fc.cpu() - gc).abs().max().item() / gc.abs().max().item()
@@ -123,7 +119,7 @@ def test_backbone_fused_vs_plain_module(golden):
 
 
 def test_backbone_f16_tensor_core_path_is_tf32_grade(golden):
-    """The tcgen05 fp16 backbone (what runs when torch.backends.cudnn.allow_tf32 is True, torch's default) against the
+    """The tcgen05 fp16 backbone (conv_precision="f16", the default) against the
     reference's golden fp32 maps: its error must be of the size of the error the reference's own cuDNN TF32
     convolutions make on the same input (both have 11-bit operand significands)."""
     import cases
@@ -143,12 +139,18 @@ def test_backbone_f16_tensor_core_path_is_tf32_grade(golden):
     try:
         torch.backends.cudnn.allow_tf32 = True
         with torch.no_grad():
+            assert m.conv_precision == "f16"                        # the default, whatever the global TF32 switch says
             ex = m.fused()
             assert isinstance(ex, FusedBackboneF16)
-            e16 = errs(*m(c["image"].cuda()))
+            flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+            e16 = errs(*m(c["image"].cuda(), _range_flag=flag))
+            assert int(flag.item()) == 0                            # nothing left the fp16 range
             etf = errs(*FusedBackbone(m)(c["image"].cuda()))       # cuDNN executor with TF32 convolutions
         torch.backends.cudnn.allow_tf32 = False
         with torch.no_grad():
+            assert isinstance(m.fused(), FusedBackboneF16)          # the global switch does not pick the executor
+            assert isinstance(m.fused("fp32"), FusedBackbone)
+            m.conv_precision = "fp32"
             assert isinstance(m.fused(), FusedBackbone)
     finally:
         torch.backends.cudnn.allow_tf32 = old
@@ -184,3 +186,46 @@ def test_backbone_f16_vs_fp32_executor_other_sizes(hw, n):
     ef = (gf - rf).abs().max().item() / rf.abs().max().item()
     print(f"backbone {hw} x{n}: rel err coarse {ec:.2e} fine {ef:.2e}")
     assert ec < 5e-3 and ef < 5e-3
+
+
+def test_backbone_f16_range_flag_and_fp32_repeat():
+    """fp16 activations have TF32's significand but not its exponent range: an input that drives an activation beyond
+    65504 must raise the kernels' range flag, and the matcher must then repeat the forward on the exact-fp32 executor
+    (same result as a model configured with conv_precision='fp32')."""
+    import copy
+    import cases
+    from onepose_st_b200.nn_common import ResNetFPN_8_2
+    from onepose_st_b200.onepose_plus import OnePosePlus_model
+    from conftest import backbone_precision
+    torch.manual_seed(5)
+    m = ResNetFPN_8_2({"block_type": "BasicBlock", "initial_dim": 128, "block_dims": [128, 196, 256]}).cuda().eval()
+    img = torch.rand(1, 1, 64, 64, device="cuda")
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    with torch.no_grad():
+        m(img, _range_flag=flag)
+        assert int(flag.item()) == 0
+        m(img * 3.0e5, _range_flag=flag)          # stem output ~ 1e5 x the normal activations: beyond fp16
+        assert int(flag.item()) == 1
+        flag.zero_()
+        bad = img.clone()
+        bad[0, 0, 5, 5] = float("inf")
+        m(bad, _range_flag=flag)
+        assert int(flag.item()) == 1
+    # model level: the flagged forward equals the fp32-configured forward
+    c = cases.case_onepose_full()
+    model = OnePosePlus_model(copy.deepcopy(c["cfg"]))
+    model.load_state_dict(c["sd"], strict=True)
+    model = model.cuda().eval()
+    data = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in c["data"].items()}
+    data["query_image"] = data["query_image"] * 3.0e5
+    ref = dict(data)
+    with backbone_precision("f16"):
+        model(data)
+        assert model.__dict__.get("_warned_fp16_range")
+    with backbone_precision("fp32"):
+        m2 = OnePosePlus_model(copy.deepcopy(c["cfg"]))
+        m2.load_state_dict(c["sd"], strict=True)
+        m2 = m2.cuda().eval()
+        m2(ref)
+    assert torch.equal(data["i_ids"], ref["i_ids"]) and torch.equal(data["j_ids"], ref["j_ids"])
+    assert torch.equal(data["mconf"], ref["mconf"])

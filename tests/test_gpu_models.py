@@ -28,11 +28,11 @@ def build_onepose(c, materialize=True):
 
 @pytest.fixture(autouse=True)
 def _fp32_convs():
-    # the backbone stays PyTorch/cuDNN; compare it in true fp32 so differences come from OUR kernels only
-    old = torch.backends.cudnn.allow_tf32
-    torch.backends.cudnn.allow_tf32 = False
-    yield
-    torch.backends.cudnn.allow_tf32 = old
+    # exact-fp32 (cuDNN) backbone here, so that differences against the fp32 golden vectors come from the matcher
+    # kernels only; the default fp16 tcgen05 backbone is compared in test_gpu_bench_config.py / test_gpu_pose.py
+    from conftest import backbone_precision
+    with backbone_precision("fp32"):
+        yield
 
 
 @pytest.mark.parametrize("name,kw", [("onepose_full", {}), ("onepose_full_mask", {"with_mask": True})])

@@ -148,3 +148,99 @@ def test_loftr_cuda_graph_head_matches_eager():
             assert torch.equal(w[k], g_[k]), k
         assert (w["mconf"] - g_["mconf"]).abs().max().item() < 1e-5
         assert (w["mkpts1_f"] - g_["mkpts1_f"]).abs().max().item() < 1e-3
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_new_3d_model_at_a_recycled_address_is_not_served_from_the_caches(graph):
+    """The usual evaluation loop `for batch in loader: batch = to_cuda(batch); model(batch)` frees one object's tensors
+    and allocates the next object's, of the same shape, at the same addresses with version counter 0.  The per-sequence
+    caches (encoded 3D descriptors, first self layer of the 3D stream, CUDA-graph guard) must not mistake the new
+    object for the old one: they hold references to the tensors they were built from."""
+    from onepose_st_b200 import synthetic
+    from onepose_st_b200.onepose_plus import OnePosePlus_model
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    model = OnePosePlus_model(synthetic.onepose_plus_cfg()).eval()
+    model.load_state_dict(synthetic.calibrate_onepose_state_dict(model.state_dict()), strict=True)
+    model = model.to(dev)
+    B = 2
+    seqs = [synthetic.make_onepose_sequence(model, 1500, B, 256, 256, 300, seed=s, device=dev) for s in (0, 77)]
+    host = [{k: seq[k].cpu() for k in ("keypoints3d", "descriptors3d_db", "descriptors3d_coarse_db", "frames")} for seq in seqs]
+
+    def forward(h, cached):
+        # fresh device tensors every time, as a data loader produces them
+        kp, d_f, d_c = h["keypoints3d"].to(dev), h["descriptors3d_db"].to(dev), h["descriptors3d_coarse_db"].to(dev)
+        f = (lambda t: t.expand(B, -1, -1)) if cached else (lambda t: t.expand(B, -1, -1).contiguous())
+        data = {"keypoints3d": f(kp), "descriptors3d_db": f(d_f), "descriptors3d_coarse_db": f(d_c),
+                "query_image": h["frames"].to(dev)}
+        model(data)
+        return {k: data[k].clone() for k in ("b_ids", "i_ids", "j_ids", "mconf")}
+
+    with torch.no_grad():
+        model.cuda_graph = False
+        model.loftr_coarse.reuse_static_stream0 = False
+        want = [forward(h, False) for h in host]           # no broadcast, no graph: nothing is cached
+        assert not torch.equal(want[0]["i_ids"], want[1]["i_ids"])
+        model.loftr_coarse.reuse_static_stream0 = True
+        model.cuda_graph = graph
+        for rnd in range(3):                                # objects alternate; every forward allocates anew
+            for h, w in zip(host, want):
+                got = forward(h, True)
+                torch.cuda.synchronize()
+                assert torch.equal(got["i_ids"], w["i_ids"]) and torch.equal(got["j_ids"], w["j_ids"]), rnd
+                assert (got["mconf"] - w["mconf"]).abs().max().item() < 1e-4
+
+
+def test_inference_mode_inputs_bypass_the_caches():
+    """Tensors created under torch.inference_mode() track no version counter: the forward must neither raise nor cache."""
+    from onepose_st_b200 import synthetic
+    from onepose_st_b200.onepose_plus import OnePosePlus_model
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    model = OnePosePlus_model(synthetic.onepose_plus_cfg()).eval()
+    model.load_state_dict(synthetic.calibrate_onepose_state_dict(model.state_dict()), strict=True)
+    model = model.to(dev)
+    B = 2
+    seq = synthetic.make_onepose_sequence(model, 1500, B, 256, 256, 300, device=dev)
+    keys = ("keypoints3d", "descriptors3d_db", "descriptors3d_coarse_db")
+    with torch.no_grad():
+        plain = {k: seq[k].expand(B, -1, -1) for k in keys}
+        plain["query_image"] = seq["frames"]
+        model(plain)
+    for graph in (False, True):
+        model.cuda_graph = graph
+        model._kpt_cache = None
+        with torch.inference_mode():
+            data = {k: (seq[k] + 0).expand(B, -1, -1) for k in keys}   # (+ 0: new tensors born in inference mode)
+            assert data["keypoints3d"].is_inference()
+            data["query_image"] = seq["frames"] + 0
+            model(data)
+            assert model._kpt_cache is None
+            assert torch.equal(data["i_ids"], plain["i_ids"]) and torch.equal(data["j_ids"], plain["j_ids"])
+
+
+def test_head_graphs_release_their_workspaces():
+    """Dropping a graph (guard mismatch, LRU eviction, clear) frees the scratch buffers it owned."""
+    from onepose_st_b200 import ops
+    from onepose_st_b200.nn_common import HeadGraphs
+    hg = HeadGraphs(max_entries=2)
+    x = torch.ones(4, device="cuda")
+
+    def fn(t):
+        ws = ops.workspaces.get(t.device, "probe", 1 << 20)
+        return t * 2 + ws[0]
+
+    def scopes():
+        return {k[1] for k in ops.workspaces._bufs if isinstance(k[1], tuple) and k[1][0] == "scope"}
+
+    before = scopes()
+    for i in range(4):
+        hg.run((i,), (x,), fn)
+    assert len(hg) == 2 and len(scopes() - before) == 2       # least recently used graphs were dropped with their scratch
+    state = {"v": 0}
+    hg.run((99,), (x,), fn, guard=lambda: state["v"])
+    state["v"] = 1
+    hg.run((99,), (x,), fn, guard=lambda: state["v"])        # guard mismatch: recaptured, old scratch released
+    assert len(hg) == 2 and len(scopes() - before) == 2
+    hg.clear()
+    assert len(hg) == 0 and scopes() == before

@@ -75,16 +75,13 @@ def test_pnp_pose_parity_with_oracle():
     ref = {k: v.clone() for k, v in data.items()}
     with torch.no_grad():
         R.onepose_plus_forward(sd, cfg, ref)
-    old = torch.backends.cudnn.allow_tf32
-    torch.backends.cudnn.allow_tf32 = False
-    try:
+    from conftest import backbone_precision
+    with backbone_precision("fp32"):
         model = OnePosePlus_model(copy.deepcopy(cfg))
         model.load_state_dict(sd, strict=True)
         model = model.cuda().eval()
         ours = {k: v.cuda() for k, v in data.items()}
         model(ours)
-    finally:
-        torch.backends.cudnn.allow_tf32 = old
     m_ref, m_ours = len(ref["mconf"]), len(ours["mconf"])
     print(f"matches: ours {m_ours}, oracle {m_ref}")
     assert m_ref >= 100 and abs(m_ours - m_ref) <= 2
@@ -98,7 +95,7 @@ def test_pnp_pose_parity_with_oracle():
 
 
 def test_pnp_pose_parity_tf32_grade_backbone():
-    """Same scene with torch's default allow_tf32=True, i.e. the fp16-operand tcgen05 backbone (the configuration
+    """Same scene with the default conv_precision="f16", i.e. the fp16-operand tcgen05 backbone (the configuration
     bench.py times): the pose must still agree with the fp32 oracle within north_star's 1 cm / 1 degree, and the
     match set must be essentially the oracle's."""
     pytest.importorskip("cv2")
@@ -108,17 +105,14 @@ def test_pnp_pose_parity_tf32_grade_backbone():
     ref = {k: v.clone() for k, v in data.items()}
     with torch.no_grad():
         R.onepose_plus_forward(sd, cfg, ref)
-    old = torch.backends.cudnn.allow_tf32
-    torch.backends.cudnn.allow_tf32 = True
-    try:
+    from conftest import backbone_precision
+    with backbone_precision("f16"):
         model = OnePosePlus_model(copy.deepcopy(cfg))
         model.load_state_dict(sd, strict=True)
         model = model.cuda().eval()
         ours = {k: v.cuda() for k, v in data.items()}
         model(ours)
         assert isinstance(model.backbone.fused(), FusedBackboneF16)
-    finally:
-        torch.backends.cudnn.allow_tf32 = old
     ref_pairs = set(zip(ref["i_ids"].tolist(), ref["j_ids"].tolist()))
     our_pairs = set(zip(ours["i_ids"].cpu().tolist(), ours["j_ids"].cpu().tolist()))
     common = len(ref_pairs & our_pairs)
