@@ -4,7 +4,14 @@
 Workload (BASELINE.json configs[1]): spot_demo-shaped synthetic sequence -- 512x512 query frames against one
 8k-point 3D model, random-init weights of the reference architecture (calibrated + planted so that matches
 exist, onepose_st_b200/synthetic.py), frames sharded round-robin over the GPUs (weak scaling: every rank
-processes ``--frames-per-step`` frames per step), matches gathered once at the end over NCCL.
+processes ``--frames-per-step`` frames per step), matches gathered once at the end over NCCL.  Every timed
+region is repeated ``--repeats`` times (the JSON line carries the median; all repeats are in ``diag``).
+
+Besides the headline the line carries: ``parity`` (the timed configuration checked frame by frame against the CPU
+oracle on the same inputs), ``strong_scaling`` (the literal configs[1]: the same 500 frames split over the ranks, with a
+checksum of the gathered match rows that must not depend on the number of GPUs), ``gpu_eager_baseline`` (the
+reference algorithm's eager PyTorch port on this GPU: fp32, TF32 off), and ``secondary`` (configs[3]: LoFTR pairs/s
+sharded by pair; configs[2]: the 30k-point CoarseMatching stage).
 
 One JSON line on stdout (rank 0).  ``value`` = frames/s with frames resident in HBM; ``e2e`` = frames/s through
 ``OnePosePlus_model.forward(data)`` with the frame copied from pinned host memory and the matches copied back
@@ -38,7 +45,12 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--points", type=int, default=8000, help="3D points of the object model (L)")
     ap.add_argument("--size", type=int, default=512, help="query crop side (pixels)")
-    ap.add_argument("--frames-per-step", type=int, default=16, help="frames each rank processes per step")
+    ap.add_argument("--frames-per-step", type=int, default=128, help="frames each rank processes per step")
+    ap.add_argument("--repeats", type=int, default=3, help="timed regions of --steps steps per arm (median reported)")
+    ap.add_argument("--no-extras", action="store_true", help="skip strong_scaling / gpu_eager_baseline / secondary / parity")
+    ap.add_argument("--loftr-pairs", type=int, default=256, help="secondary: LoFTR pairs per rank (0 = skip)")
+    ap.add_argument("--backbone", default="f16", choices=["f16", "fp32"],
+                    help="ResNetFPN_8_2.conv_precision: f16 = own tcgen05 convolutions (default), fp32 = exact cuDNN executor")
     ap.add_argument("--batch", type=int, default=8, help="frames per forward call (dict contract N)")
     ap.add_argument("--pool", type=int, default=500, help="frames of the synthetic sequence")
     ap.add_argument("--plant", type=int, default=1000, help="planted 2D-3D correspondences")
@@ -113,12 +125,20 @@ def config_dict(args, n_gpus):
                         f"{args.points}-point 3D model (BASELINE.json configs[1])",
             "points": args.points, "image": [args.size, args.size], "coarse_grid": [args.size // 8, args.size // 8],
             "frames_per_step_per_gpu": args.frames_per_step, "frames_per_forward": args.batch,
-            "planted_matches": args.plant, "precision": "bf16x3-split (fp32-grade)" if args.precision == 3 else "bf16",
+            "planted_matches": args.plant,
+            "precision": {"coarse_matching_sweep": "ONE fp16 x fp16 product, fp32 accumulation (screening: bounded by the row norms); "
+                                                   "every captured element re-evaluated from the bf16 hi+lo planes in fp32",
+                          "encoder_gemms": "bf16x3 split products (fp32-grade)" if args.precision == 3 else "bf16",
+                          "backbone": "fp16 operands, fp32 accumulation (own tcgen05 convolutions)" if args.backbone == "f16"
+                                      else "exact fp32 (cuDNN)",
+                          "io": "fp32"},
             "sharding": f"frames round-robin over {n_gpus} GPU(s); one NCCL gather of matches at the end",
             "host_pipeline": f"{args.streams} host threads x CUDA streams per GPU pull frame batches from one queue "
                              "(onepose_st_b200.pipeline.StreamPipeline)",
             "cuda_graph": bool(args.cuda_graph),
-            "l2": "256 MiB buffer written between steps (inside the timed region)"}
+            "repeats": args.repeats,
+            "l2": "256 MiB buffer written between steps (inside the timed region); a step's frames (134 MB at 128 frames) "
+                  "and activations exceed the 126 MB L2 as well"}
 
 
 # ------------------------------------------------------------------------------------------------ CPU reference
@@ -174,10 +194,12 @@ def run_reference(args):
 
 # ------------------------------------------------------------------------------------------------ GPU arm
 def run_ours(args):
+    import hashlib
     import torch
     import torch.distributed as dist
     import threading
     from onepose_st_b200 import _lib, ops, pipeline, sharding, synthetic
+    from onepose_st_b200.nn_common import ResNetFPN_8_2
     from onepose_st_b200.onepose_plus import OnePosePlus_model
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -193,6 +215,7 @@ def run_ours(args):
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's banner / warnings off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
+    ResNetFPN_8_2.conv_precision = args.backbone
 
     torch.manual_seed(0)
     cfg = synthetic.onepose_plus_cfg()
@@ -212,8 +235,7 @@ def run_ours(args):
     d_c = seq["descriptors3d_coarse_db"].expand(B, -1, -1)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     tl = threading.local()  # per host thread: device staging buffer of the end-to-end arm
-    ragged = sharding.RaggedRows(6, dev, capacity_rows=1 << 18)
-    n_units_total = world * F * (args.steps + args.warmup)
+    ragged = sharding.RaggedRows(6, dev, capacity_rows=1 << 20)
 
     def unit_frames(step, b0):
         # global unit id -> frame of the pool; rank r owns units r, r+G, ...
@@ -265,10 +287,14 @@ def run_ours(args):
 
     pipes = {}
 
-    def timed(e2e, n_streams, stage_events=False):
+    def get_pipe(n_streams):
         pipe = pipes.get(n_streams)
         if pipe is None:
             pipe = pipes[n_streams] = pipeline.StreamPipeline(n_streams, dev)
+        return pipe
+
+    def timed(e2e, n_streams, stage_events=False, repeats=1):
+        pipe = get_pipe(n_streams)
         # CUDA graph of the forward's head (one launch instead of ~85); the per-op event pass runs eagerly
         model.cuda_graph = bool(args.cuda_graph) and not stage_events
         ragged.reset()
@@ -276,53 +302,57 @@ def run_ours(args):
         torch.cuda.synchronize()
         pipe.warm(lambda: one_forward((0, B if F > B else 0, e2e)))  # per-stream workspaces / CUDA graphs
         run_steps(0, args.warmup, e2e, pipe)
-        # the gather is warmed up too (first NCCL all_gather sets up channels; first sort/scatter compiles nothing but allocates)
-        # at the size of the timed region (the warm-up rows repeated), so that the timed gather finds its buffers in the
-        # caching allocator instead of calling cudaMalloc
-        rep_ = max(1, -(-args.steps // max(1, args.warmup))) + 1  # a little larger: bigger cached blocks serve smaller requests
+        # the gather is warmed up too (first NCCL all_gather sets up channels) at (nearly) the timed shape, so that NCCL meets
+        # the timed message size and the caching allocator the timed block sizes before the clock starts
+        rep_ = max(1, -(-args.steps // max(1, args.warmup))) + 1
         sharding.gather_matches(ragged.rows().repeat(rep_, 1), list(ragged.counts) * rep_, world * F * args.warmup * rep_)
-        # ... and once more at (nearly) exactly the timed shape: the first F * steps units of the repeated rows, so that
-        # NCCL meets the timed message size and the allocator the timed block sizes before the clock starts
         cl_ = (list(ragged.counts) * rep_)[: F * args.steps]
         sharding.gather_matches(ragged.rows().repeat(rep_, 1)[: sum(cl_)], cl_, world * len(cl_))
-        ragged.reset()
-        ops.stage_events = {} if stage_events else None
-        sampler = ClockSampler(local_rank)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        sampler.start()
-        l0 = _lib.launch_count()
-        mallocs0 = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
-        ev0, ev1, evg = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-        if stage_events:
-            _lib.coarse_kernel_ms()  # forget the sweep-kernel brackets of the warm-up launches
-        ev0.record()
-        d2h = run_steps(args.warmup, args.steps, e2e, pipe)
-        n_units = world * F * args.steps
-        evg.record()
-        rows_all, counts_all = sharding.gather_matches(ragged.rows(), ragged.counts, n_units)
-        ev1.record()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        launches = _lib.launch_count() - l0
-        clocks = sampler.stop()
-        ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
-        per_rank = [float(ms.item())]
-        if world > 1:
-            allms = torch.empty(world, device=dev)
-            dist.all_gather_into_tensor(allms, ms)
-            per_rank = [round(v, 2) for v in allms.tolist()]
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        events, ops.stage_events = ops.stage_events, None
-        diag = {"ms_per_rank": per_rank, "gather_ms_rank0": round(evg.elapsed_time(ev1), 3),
-                "cuda_mallocs_in_timed_region": torch.cuda.memory_stats(dev).get("num_device_alloc", 0) - mallocs0}
-        return {"ms": float(ms.item()), "launches": launches, "clocks": clocks, "events": events, "d2h": d2h,
-                "matches": int(rows_all.shape[0]), "units": n_units, "diag": diag}
+        runs = []
+        for rp in range(max(1, repeats)):
+            ragged.reset()
+            ops.stage_events = {} if stage_events else None
+            sampler = ClockSampler(local_rank)
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            sampler.start()
+            l0 = _lib.launch_count()
+            mallocs0 = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
+            ev0, ev1, evg = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            if stage_events:
+                _lib.coarse_kernel_ms()  # forget the sweep-kernel brackets of the warm-up launches
+            ev0.record()
+            d2h = run_steps(args.warmup, args.steps, e2e, pipe)
+            n_units = world * F * args.steps
+            evg.record()
+            rows_all, counts_all = sharding.gather_matches(ragged.rows(), ragged.counts, n_units)
+            ev1.record()
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            launches = _lib.launch_count() - l0
+            clocks = sampler.stop()
+            ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+            per_rank = [float(ms.item())]
+            if world > 1:
+                allms = torch.empty(world, device=dev)
+                dist.all_gather_into_tensor(allms, ms)
+                per_rank = [round(v, 2) for v in allms.tolist()]
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            events, ops.stage_events = ops.stage_events, None
+            diag = {"ms_per_rank": per_rank, "gather_ms_rank0": round(evg.elapsed_time(ev1), 3),
+                    "cuda_mallocs_in_timed_region": torch.cuda.memory_stats(dev).get("num_device_alloc", 0) - mallocs0}
+            runs.append({"ms": float(ms.item()), "launches": launches, "clocks": clocks, "events": events, "d2h": d2h,
+                         "matches": int(rows_all.shape[0]), "units": n_units, "diag": diag})
+        runs_sorted = sorted(runs, key=lambda r: r["ms"])
+        med = dict(runs_sorted[len(runs_sorted) // 2])  # the median repeat is the one reported
+        med["diag"] = dict(med["diag"], repeats_ms=[round(r["ms"], 2) for r in runs], min_ms=round(runs_sorted[0]["ms"], 2),
+                           median_ms=round(med["ms"], 2))
+        return med
 
-    res = timed(e2e=False, n_streams=args.streams)
-    res_e2e = None if args.no_e2e else timed(e2e=True, n_streams=args.streams)
+    res = timed(e2e=False, n_streams=args.streams, repeats=args.repeats)
+    res_e2e = None if args.no_e2e else timed(e2e=True, n_streams=args.streams, repeats=args.repeats)
     # per-op device time: the same K steps once more on ONE stream, so that the CUDA-event bracket around each C-ABI
     # call (recorded on the launching stream, inside this timed region) holds that call's kernels only -- with two
     # streams in flight a bracket would also span the other stream's kernels.
@@ -339,11 +369,13 @@ def run_ours(args):
         stages[name] = {"calls": len(evs), "ms_per_frame": tot / frames_rank}
     m_per_frame = res["matches"] / max(1, res["units"])
     rooflines = {}
-    traffic = None  # DRAM bytes per launch of sim_fast_kernel, from the committed ncu --set full capture (profiles/r01_coarse_match_ncu_full_summary.txt)
-    tpath = os.path.join(REPO, "profiles", "r01_traffic.json")
-    if os.path.exists(tpath) and args.batch == 8 and args.points == 8000 and args.size == 512:
-        with open(tpath) as f:
-            traffic = json.load(f)["sim_fast_kernel"]["dram_bytes_per_launch"]
+    traffic = None  # DRAM bytes per launch of the sweep kernel, from the committed ncu --set full capture of this command
+    for tname in ("r02_traffic.json", "r01_traffic.json"):
+        tpath = os.path.join(REPO, "profiles", tname)
+        if os.path.exists(tpath) and args.batch == 8 and args.points == 8000 and args.size == 512:
+            with open(tpath) as f:
+                traffic = json.load(f)["sim_fast_kernel"]["dram_bytes_per_launch"]
+            break
     if "coarse_match" in stages:
         t_op = stages["coarse_match"]["ms_per_frame"] * 1e-3
         flops = 2.0 * L * S * C
@@ -354,8 +386,8 @@ def run_ours(args):
         t_k = (sim_ms / sim_n) * 1e-3 if sim_n else None  # all recorded launches have the same shape
         executed = 1  # the sweep runs ONE fp16 x fp16 product; captured elements are re-evaluated from the split planes
         op = {"achieved": flops / t_op / 1e12, "frac": flops / t_op / 1e12 / peak, "avg_ms_per_call": t_op * 1e3 * B,
-              "note": "the whole opb200_coarse_match call: fp16 operand pack, sweep, partial merge, exact re-evaluation of the "
-                      "captured elements, mutual-NN resolve, ordered compaction"}
+              "note": "the whole opb200_coarse_match call: fp16 operand pack + row norms, sweep, partial merge, exact "
+                      "re-evaluation of the captured elements, mutual-NN resolve, ordered compaction"}
         if t_k is not None:
             ach = flops * B / t_k / 1e12
             rooflines["coarse_match"] = {
@@ -365,18 +397,21 @@ def run_ours(args):
                 "kernel": "sim_fast_kernel<true>: single-pass dual-softmax sweep of CoarseMatching (tcgen05 fp16 similarity tiles, "
                           "row/column softmax sums and candidate capture in the epilogue)",
                 "algorithmic": f"2*L*S*C = {flops / 1e9:.1f} GFLOP per frame (one similarity GEMM)",
-                "executed_flop_multiple": executed, "peak_source": peaks["source"] + " bf16 sustained", "op_level": op}
+                "executed_flop_multiple": executed, "peak_source": peaks["source"] + " bf16 sustained",
+                "frac_of_burst_peak": ach / peaks["bf16_tflops"], "op_level": op}
         else:  # the two-pass path ran (masks / conf matrix requested): only the call-level figure exists
             rooflines["coarse_match"] = {"bound": "tensor", "achieved": op["achieved"], "peak": peak, "unit": "TFLOP/s",
                                          "frac": op["frac"], "traffic": None, "kernel": "opb200_coarse_match (two-pass path)",
                                          "algorithmic": f"2*L*S*C = {flops / 1e9:.1f} GFLOP per frame", "op_level": op}
     if "transformer256" in stages:
         t = stages["transformer256"]["ms_per_frame"] * 1e-3
-        flops = 120.0 * (L + S) * C * C
+        # 6 layer steps of F_layer on both streams = 120 (L+S) C^2; the first self layer of the 3D stream (20 L C^2) is
+        # served from the per-sequence cache for every frame but the first, so it is NOT counted as work done per frame
+        flops = 120.0 * (L + S) * C * C - 20.0 * L * C * C
         peak = peaks["bf16_tflops_sustained"]
         rooflines["transformer256"] = {"bound": "tensor", "achieved": flops / t / 1e12, "peak": peak, "unit": "TFLOP/s",
                                        "frac": flops / t / 1e12 / peak, "traffic": None,
-                                       "algorithmic": f"120*(L+S)*C^2 = {flops / 1e9:.1f} GFLOP per frame",
+                                       "algorithmic": f"120*(L+S)*C^2 - 20*L*C^2 (cached first 3D self layer) = {flops / 1e9:.1f} GFLOP per frame",
                                        "executed_flop_multiple": (3 if args.precision == 3 else 1)}
     if "backbone_conv" in stages:
         t = stages["backbone_conv"]["ms_per_frame"] * 1e-3
@@ -390,12 +425,153 @@ def run_ours(args):
                                       "kernel": "conv_kernel: fp16-operand tcgen05 implicit GEMM, 23 convolutions of ResNetFPN_8_2",
                                       "algorithmic": f"sum 2*Ho*Wo*k*k*Cin*Cout = {flops / 1e9:.1f} GFLOP per frame",
                                       "executed_flop_multiple": 1}
-    if "fine_match" in stages and m_per_frame > 0:
-        t = stages["fine_match"]["ms_per_frame"] * 1e-3
-        by = m_per_frame * (4 * 128 * (25 + 1) + 20)
-        rooflines["fine_match"] = {"bound": "hbm", "achieved": by / t / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                                   "frac": by / t / 1e9 / peaks["hbm_gbs"], "traffic": None,
-                                   "algorithmic": "4*Cf*(WW+1)+20 bytes per match"}
+    for nm in ("fine_match", "fine_fused"):
+        if nm in stages and m_per_frame > 0:
+            t = stages[nm]["ms_per_frame"] * 1e-3
+            by = m_per_frame * (4 * 128 * (25 + 1) + 20)
+            rooflines[nm] = {"bound": "hbm", "achieved": by / t / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                             "frac": by / t / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                             "algorithmic": "4*Cf*(WW+1)+20 bytes per match"}
+
+    # ------------------------------------------------------------------ strong scaling on the literal configs[1]
+    def strong_scaling():
+        """The same ``--pool`` frames (500) split over the ranks in batches of B consecutive frames, batch u on rank u mod G;
+        rows gathered in unit order; the checksum of the gathered rows must not depend on G."""
+        model.cuda_graph = bool(args.cuda_graph)
+        pipe = get_pipe(args.streams)
+        n_batches = -(-args.pool // B)
+        mine = sharding.shard_units(n_batches, rank, world)
+        idx = {}
+        for u in mine:
+            fr = [min(u * B + i, args.pool - 1) for i in range(B)]  # the last batch repeats its last frame (rows dropped below)
+            idx[u] = (torch.tensor(fr, device=dev), min(B, args.pool - u * B))
+
+        def job(u):
+            ids, n_valid = idx[u]
+            data = forward(frames_dev.index_select(0, ids))
+            rows = sharding.rows_onepose(data)
+            keep = data["b_ids"] < n_valid
+            return rows[keep], int(keep.sum().item())
+
+        def run():
+            rg = sharding.RaggedRows(6, dev, capacity_rows=1 << 18)
+            for rows, c in pipe.map(job, mine):
+                rows.record_stream(torch.cuda.current_stream())
+                rg.append(rows)
+            return sharding.gather_matches(rg.rows(), rg.counts, n_batches)
+
+        run()  # warm-up at the timed shapes (graphs for this batch shape exist already)
+        times = []
+        for _ in range(max(1, args.repeats)):
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rows_all, counts_all = run()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+            if world > 1:
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            times.append(float(ms.item()))
+        digest = hashlib.sha256(rows_all.cpu().numpy().tobytes() + counts_all.cpu().numpy().tobytes()).hexdigest()[:16]
+        med = sorted(times)[len(times) // 2]
+        return {"frames": args.pool, "value": args.pool / (med * 1e-3), "unit": UNIT, "scaling": "strong",
+                "ms": round(med, 2), "repeats_ms": [round(t, 2) for t in times], "matches": int(rows_all.shape[0]),
+                "checksum": digest,
+                "note": "the same frames and the same batches of consecutive frames for every GPU count: checksum (sha256 of the "
+                        "gathered [sum M, 6] rows + per-batch counts, first 16 hex digits) and matches must be equal at N = 1/2/4/8"}
+
+    # ------------------------------------------------------------------ secondary workloads (configs[3], configs[2])
+    def loftr_pairs():
+        """configs[3]: LoFTR wsize9 pair matching, 512x512 pairs sharded round-robin by pair, 4 pairs per forward,
+        rows_loftr [M,5] gathered over NCCL at the end (weak scaling: --loftr-pairs pairs per rank)."""
+        from onepose_st_b200.loftr import LoFTR_for_OnePose_Plus, default_cfg
+        torch.manual_seed(0)
+        lm = LoFTR_for_OnePose_Plus(default_cfg, enable_fine_matching=True).eval()
+        lm.load_state_dict(synthetic.calibrate_loftr_state_dict(lm.state_dict(), args.size, args.size))
+        lm = lm.to(dev)
+        lm.cuda_graph = bool(args.cuda_graph)
+        PB = 4
+        n_fw = max(1, args.loftr_pairs // PB)
+        gn = torch.Generator(device=dev).manual_seed(4242 + rank)
+        noise = 0.01 * torch.randn(PB, 1, args.size, args.size, device=dev, generator=gn)
+        one = torch.ones(PB, 2, device=dev)
+        pipe = get_pipe(args.streams)
+
+        def job(k):
+            ids = torch.tensor([((k * PB + i) * world + rank) % args.pool for i in range(PB)], device=dev)
+            i0 = frames_dev.index_select(0, ids)
+            d = {"image0": i0, "image1": (i0 + noise).clamp_(0, 1), "scale0": one, "scale1": one}
+            lm(d)
+            return sharding.rows_loftr(d), torch.bincount(d["b_ids"], minlength=PB).tolist()
+
+        def run():
+            rg = sharding.RaggedRows(5, dev, capacity_rows=1 << 18)
+            for rows, counts in pipe.map(job, range(n_fw)):
+                rows.record_stream(torch.cuda.current_stream())
+                off = 0
+                for c in counts:
+                    rg.append(rows[off: off + c])
+                    off += c
+            return sharding.gather_matches(rg.rows(), rg.counts, world * n_fw * PB)
+
+        job(0)
+        torch.cuda.synchronize()
+        pipe.warm(lambda: job(1))
+        run()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rows_all, _ = run()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        pairs = world * n_fw * PB
+        del lm
+        return {"metric": "LoFTR wsize9 matched pairs/sec (coarse + fine)", "value": pairs / (float(ms.item()) * 1e-3),
+                "unit": "pairs/s", "pairs": pairs, "pairs_per_forward": PB, "scaling": "weak", "ms": round(float(ms.item()), 2),
+                "matches_per_pair": rows_all.shape[0] / pairs,
+                "workload": f"BASELINE.json configs[3]: {args.size}x{args.size} image pairs (frame vs noisy copy), sharded by pair, "
+                            "one NCCL gather of [M,5] rows"}
+
+    def coarse_30k():
+        """configs[2]: CoarseMatching stage at 30k points x 64x64 cells, one frame per call (rank 0)."""
+        f3d, f2d = synthetic.planted_coarse_pair(21, 1, 30000, 4096, 256, 3000, 64, 64, device=dev)
+        kw = dict(scale=1.0 / (256 * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=(64, 64))
+        for _ in range(3):
+            out = ops.coarse_match(f3d, f2d, **kw)
+        torch.cuda.synchronize()
+        n = 20
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            h = ops.coarse_match_launch(f3d, f2d, **kw)
+        e1.record()
+        torch.cuda.synchronize()
+        ops.coarse_match_finish(h)
+        ms = e0.elapsed_time(e1) / n
+        fl = 2.0 * 30000 * 4096 * 256
+        return {"metric": "CoarseMatching stage, 30k points x 4096 cells, one frame per call", "ms_per_call": round(ms, 4),
+                "matches": int(out[0].shape[0]), "achieved_tflops": fl / (ms * 1e-3) / 1e12,
+                "frac_of_sustained_peak": fl / (ms * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"],
+                "frac_of_burst_peak": fl / (ms * 1e-3) / 1e12 / peaks["bf16_tflops"],
+                "workload": "BASELINE.json configs[2] (fp32 feature inputs: split + pack + sweep + resolve per call)"}
+
+    extras = {}
+    if not args.no_extras:
+        extras["strong_scaling"] = strong_scaling()
+        sec = {}
+        if args.loftr_pairs > 0:
+            sec["loftr_pairs"] = loftr_pairs()
+        if rank == 0:
+            sec["coarse_match_30k"] = coarse_30k()
+        extras["secondary"] = sec
 
     out = None
     if rank == 0:
@@ -403,9 +579,8 @@ def run_ours(args):
         value = total_frames / (res["ms"] * 1e-3)
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": res["ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-               "dtype": ("bf16x3 split products (matcher), " if args.precision == 3 else "bf16 (matcher), ")
-               + ("fp16 operands (backbone convolutions, TF32-grade like the reference on a GPU), "
-                  if torch.backends.cudnn.allow_tf32 else "fp32 cuDNN backbone, ") + "f32 accumulate/IO",
+               "dtype": "fp16 x fp16 -> f32 (CoarseMatching sweep, backbone convolutions) + bf16x3 split -> f32 (encoder GEMMs); f32 I/O"
+               if args.backbone == "f16" else "fp16 x fp16 -> f32 (CoarseMatching sweep) + bf16x3 split -> f32 (encoder GEMMs) + fp32 cuDNN backbone",
                "data": "synthetic", "config": config_dict(args, world),
                "matches_per_frame": m_per_frame, "gpu_launches": res["launches"], "clocks": res["clocks"],
                "streams": args.streams, "diag": res["diag"],
@@ -414,6 +589,7 @@ def run_ours(args):
                "stages_ms_per_frame": {k: round(v["ms_per_frame"], 4) for k, v in stages.items()},
                "roofline": rooflines.get("coarse_match"),
                "roofline_other": {k: v for k, v in rooflines.items() if k != "coarse_match"}}
+        out.update(extras)
         if res_e2e is not None:
             out["e2e"] = {"value": total_frames / (res_e2e["ms"] * 1e-3), "unit": UNIT,
                           "h2d_bytes_per_step": F * args.size * args.size * 4,
@@ -421,20 +597,73 @@ def run_ours(args):
                           "ms_per_step": res_e2e["ms"] / args.steps, "gpu_launches": res_e2e["launches"],
                           "clocks": res_e2e["clocks"], "diag": res_e2e["diag"],
                           "api": "OnePosePlus_model.forward(data): pinned-host frame -> H2D -> forward -> D2H of [M,6] match rows"}
-    # CPU baseline: the reference algorithm's CPU port on this box's host cores (rank 0, N=1 only)
+    # CPU baseline + parity + eager-GPU baseline (rank 0, N=1 only): the reference algorithm's CPU port on this box's host
+    # cores, fed the SAME inputs as the GPU arm (its 3D model and frames), so that each timed CPU frame doubles as the
+    # oracle of the parity block; then the same port moved to the GPU (eager PyTorch, fp32, TF32 off)
     if rank == 0 and world == 1 and args.cpu_sample_frames > 0:
+        from oracle import parity as P
         from oracle import ref_ops as R
         torch.set_num_threads(os.cpu_count() or 1)
-        ccfg, csd, cseq = cpu_reference_setup(args)
-        cpu_reference_frame(R, ccfg, csd, cseq, 0)
+        csd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+        cseq = {k: seq[k].cpu() for k in ("keypoints3d", "descriptors3d_db", "descriptors3d_coarse_db")}
+        nfr = args.cpu_sample_frames
+
+        def cpu_frame(f):
+            d = dict(cseq, query_image=frames_host[f][None].clone())
+            with torch.no_grad():
+                R.onepose_plus_forward(csd, cfg, d)
+            return d
+
+        cpu_frame(0)
         t0 = time.perf_counter()
-        for f in range(args.cpu_sample_frames):
-            cpu_reference_frame(R, ccfg, csd, cseq, f + 1)
+        refs = [cpu_frame(f) for f in range(nfr)]
         dt = time.perf_counter() - t0
-        out["cpu_baseline"] = {"value": args.cpu_sample_frames / dt, "unit": UNIT, "cores": torch.get_num_threads(),
-                               "kind": "port",
-                               "sample": f"{args.cpu_sample_frames} frames of the same workload after 1 warm-up frame, "
-                                         "N=1 forward each, torch CPU fp32"}
+        out["cpu_baseline"] = {"value": nfr / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": f"{nfr} frames of the same workload (the GPU arm's own 3D model and frames) after 1 "
+                                         "warm-up frame, N=1 forward each, torch CPU fp32"}
+        if not args.no_extras:
+            # parity of the TIMED configuration: frames 0..B-1 through the same model object (fp16 backbone unless
+            # --backbone fp32, default single-pass CoarseMatching, CUDA-graph head, B frames per forward)
+            model.cuda_graph = bool(args.cuda_graph)
+            with torch.no_grad():
+                got = forward(frames_dev[:B].contiguous())
+            gcpu = {k: got[k].cpu() for k in ("b_ids", "i_ids", "j_ids", "mconf", "mkpts_query_f")}
+            thr = cfg["coarse_matching"]["thr"]
+            rep = P.merge_reports([P.onepose_frame_report(refs[f], gcpu, thr, batch_index=f) for f in range(min(nfr, B))])
+            rep["oracle"] = "oracle/ref_ops.onepose_plus_forward (torch CPU fp32), same weights, 3D model and frames"
+            rep["configuration"] = (f"backbone {args.backbone}, CoarseMatching default (algo 0), cuda_graph={bool(args.cuda_graph)}, "
+                                    f"{B} frames per forward")
+            rep["contract"] = "north_star: confidences max-abs 1e-3 (fp32), index sets equal given the same confidence matrix"
+            rep["green"] = bool(rep["mconf_max_abs_err"] < 1e-3 and rep["set_diff_max_margin"] < 1e-3)
+            out["parity"] = rep
+            # eager-GPU baseline: the same port with every tensor on this GPU (what the reference's modules do on a GPU)
+            old_tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+            torch.backends.cudnn.allow_tf32 = False
+            torch.backends.cuda.matmul.allow_tf32 = False
+            try:
+                gsd = {k: v.detach() for k, v in model.state_dict().items()}
+                gseq = {k: seq[k] for k in ("keypoints3d", "descriptors3d_db", "descriptors3d_coarse_db")}
+
+                def gpu_frame(f):
+                    d = dict(gseq, query_image=frames_dev[f][None])
+                    with torch.no_grad():
+                        R.onepose_plus_forward(gsd, cfg, d)
+                    return d["mkpts_query_f"].cpu()
+
+                for f in range(3):
+                    gpu_frame(f)
+                torch.cuda.synchronize()
+                n_e = 32
+                t0 = time.perf_counter()
+                for f in range(n_e):
+                    gpu_frame(f)
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t0
+                out["gpu_eager_baseline"] = {"value": n_e / dt, "unit": UNIT, "kind": "port on cuda (eager PyTorch, fp32, TF32 off)",
+                                             "sample": f"{n_e} frames, N=1 forward each, frames resident in HBM, D2H of the keypoints",
+                                             "note": "reported next to cpu_baseline; the reference ships no CUDA of its own on this path"}
+            finally:
+                torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old_tf32
     elif rank == 0:
         out["cpu_baseline"] = None
     if rank == 0:

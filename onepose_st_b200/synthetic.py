@@ -54,24 +54,38 @@ def calibrate_onepose_state_dict(sd: Dict[str, torch.Tensor]) -> Dict[str, torch
     return out
 
 
-def calibrate_loftr_state_dict(sd: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
-    """norm2 x50 / norm1 x0.05 in the coarse stack, fine norm2 x0.05, layer3_outconv x0.1,
-    layer1_outconv2.3 x0.25: identical images then give mutual matches (tests/golden/cases.py)."""
+@torch.no_grad()
+def calibrate_loftr_state_dict(sd: Dict[str, torch.Tensor], height: int = 512, width: int = 512,
+                               gain: float = 3.5, lam_rel: float = 1e-2) -> Dict[str, torch.Tensor]:
+    """Random-init LoFTR weights calibrated so that an image matched against a noisy copy of itself gives mutual matches
+    with confidences spread over (thr, 1) while the features stay O(1..10) (same recipe as tests/golden/cases.py):
+    ``layer3_outconv`` (1x1) is composed with the whitening map sqrt(T) (X^T X + lam I)^-1/2 of the coarse features X of
+    a seeded calibration image of the given size, T = gain x the number of coarse cells (random-conv features share a
+    large common component; whitened, <f_i, f_j> is T x the leverage matrix, which peaks on the diagonal); norm2 x0.05
+    in both stacks keeps the random transformer from washing that structure out; layer1_outconv2.3 x0.25 keeps the fine
+    logits O(10).  Runs the backbone once on the CPU (plain PyTorch modules)."""
+    from .nn_common import ResNetFPN_8_2
     out = {}
     for k, v in sd.items():
-        v = v.clone()
-        if k.startswith("loftr_coarse.") and ".norm2." in k:
-            v = v * 50.0
-        if k.startswith("loftr_coarse.") and ".norm1." in k:
+        v = v.detach().clone().cpu()
+        if ".norm2." in k and (k.startswith("loftr_coarse.") or k.startswith("loftr_fine.")):
             v = v * 0.05
-        if k.startswith("loftr_fine.") and ".norm2." in k:
-            v = v * 0.05
-        if k == "backbone.layer3_outconv.weight":
-            v = v * 0.1
         if k == "backbone.layer1_outconv2.3.weight":
             v = v * 0.25
         out[k] = v
-    return out
+    bb = ResNetFPN_8_2({"block_type": "BasicBlock", "initial_dim": 128, "block_dims": [128, 196, 256]})
+    bb.load_state_dict({k[len("backbone."):]: v for k, v in out.items() if k.startswith("backbone.")}, strict=True)
+    g = torch.Generator().manual_seed(999)
+    fc, _ = bb.eval()(torch.rand(1, 1, height, width, generator=g))
+    x = fc.flatten(2)[0].t().double()  # [S, C]
+    sg = x.t() @ x
+    ev, u = torch.linalg.eigh(sg + lam_rel * sg.diag().mean() * torch.eye(x.shape[1], dtype=torch.double))
+    wm = (u * ev.rsqrt()[None, :]) @ u.t()
+    w = out["backbone.layer3_outconv.weight"][:, :, 0, 0].double()
+    temp = gain * x.shape[0]
+    out["backbone.layer3_outconv.weight"] = ((temp ** 0.5) * (wm @ w)).float()[:, :, None, None].contiguous()
+    dev = next(iter(sd.values())).device
+    return {k: v.to(dev) for k, v in out.items()}
 
 
 def _whitened(feat_sc: torch.Tensor, cells: torch.Tensor, gains: torch.Tensor) -> torch.Tensor:

@@ -246,21 +246,26 @@ def case_onepose_full(H=128, W=128, L=400, n_plant=150, seed=0, with_mask=False)
     return dict(cfg=cfg, sd=sd, data=data)
 
 
-def calibrated_loftr_sd(seed=0):
-    """Random-init LoFTR weights rescaled so that identical images give a few mutual matches:
-    norm2 x50 (features become sums of equal-norm LayerNorm'd messages), norm1 x0.05 (small
-    attention message), layer3_outconv x0.1.  Same recipe as ``synthetic.calibrate_loftr_state_dict``."""
+def calibrated_loftr_sd(seed=0, H=96, W=128, temp=400.0, lam_rel=1e-2):
+    """Random-init LoFTR weights calibrated so that an image matched against itself gives mutual matches with
+    confidences spread over (thr, 1) while the features stay O(1..10) (well conditioned in fp32):
+    the 1x1 ``layer3_outconv`` is composed with the whitening map sqrt(temp) (X^T X + lam I)^-1/2 of the coarse
+    features X of a seeded calibration image (random-conv features share a large common component; whitened,
+    <f_i, f_j> is temp x the leverage matrix, which peaks on the diagonal), and norm2 x0.05 in both stacks keeps the
+    random transformer from washing that structure out.  Same recipe as ``synthetic.calibrate_loftr_state_dict``."""
     sd = R.init_loftr_state_dict(seed=seed)
     for k in sd:
-        if k.startswith("loftr_coarse.") and ".norm2." in k:
-            sd[k] = sd[k] * 50.0
-        if k.startswith("loftr_coarse.") and ".norm1." in k:
+        if ".norm2." in k and (k.startswith("loftr_coarse.") or k.startswith("loftr_fine.")):
             sd[k] = sd[k] * 0.05
-        if k.startswith("loftr_fine.") and ".norm2." in k:
-            sd[k] = sd[k] * 0.05  # keeps the fine logits O(10) so the test is well conditioned
-    sd["backbone.layer3_outconv.weight"] = sd["backbone.layer3_outconv.weight"] * 0.1
-    for k in ("backbone.layer1_outconv2.3.weight",):
-        sd[k] = sd[k] * 0.25
+    sd["backbone.layer1_outconv2.3.weight"] = sd["backbone.layer1_outconv2.3.weight"] * 0.25  # fine logits O(10)
+    with torch.no_grad():
+        fc, _ = R.resnet_fpn_8_2(sd, "backbone.", rand(999, 1, 1, H, W))
+    x = fc.flatten(2)[0].t().double()  # [S, C]
+    sg = x.t() @ x
+    ev, u = torch.linalg.eigh(sg + lam_rel * sg.diag().mean() * torch.eye(x.shape[1], dtype=torch.double))
+    wm = (u * ev.rsqrt()[None, :]) @ u.t()
+    w = sd["backbone.layer3_outconv.weight"][:, :, 0, 0].double()
+    sd["backbone.layer3_outconv.weight"] = ((temp ** 0.5) * (wm @ w)).float()[:, :, None, None].contiguous()
     return sd
 
 
@@ -268,7 +273,7 @@ def case_loftr_full(H=96, W=128, seed=0, mode="full"):
     """mode: 'full' (coarse+fine), 'coarse' (enable_fine_matching=False), 'fine_only'
     (caller supplies mkpts0_c/mkpts1_c), 'extract' (fine_only + feature extraction)."""
     cfg = copy.deepcopy(R.LOFTR_CFG)
-    sd = calibrated_loftr_sd(seed)
+    sd = calibrated_loftr_sd(seed, H, W)
     img0 = rand(2000 + 2 * seed, 1, 1, H, W)
     img1 = img0.clone() if mode in ("full", "coarse") else rand(2001 + 2 * seed, 1, 1, H, W)
     data = dict(image0=img0, image1=img1, scale0=torch.tensor([[1.0, 1.0]]), scale1=torch.tensor([[1.0, 1.0]]))

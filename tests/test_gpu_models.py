@@ -96,12 +96,15 @@ def test_onepose_model_no_matches():
     assert data["b_ids"].dtype == torch.int64
 
 
+@pytest.mark.parametrize("materialize", [True, False])
 @pytest.mark.parametrize("mode", ["full", "coarse", "fine_only", "extract"])
-def test_loftr_model_vs_golden(golden, mode):
+def test_loftr_model_vs_golden(golden, mode, materialize):
+    """Both routes of CoarseMatching against the reference's golden outputs: ``materialize`` = two-pass path that also
+    writes conf_matrix; default = the single-pass screening sweep (what LoFTR callers and tools/stage_bench.py run)."""
     from onepose_st_b200.loftr import LoFTR_for_OnePose_Plus
     c = cases.case_loftr_full(mode=mode)
     cfg = copy.deepcopy(c["cfg"])
-    cfg["match_coarse"]["materialize_conf_matrix"] = True
+    cfg["match_coarse"]["materialize_conf_matrix"] = materialize
     m = LoFTR_for_OnePose_Plus(cfg, enable_fine_matching=(mode != "coarse"))
     m.load_state_dict(c["sd"], strict=True)
     m = m.to(DEV).eval()
@@ -110,11 +113,26 @@ def test_loftr_model_vs_golden(golden, mode):
     m(data, **kw)
     g = golden(f"loftr_{mode}")
     if "conf_matrix" in g:
-        # the calibrated LoFTR weights (norm2 x50) make |features| ~ 1e3: sim ~ 1e4 and one fp32 ulp of sim is
-        # ~1e-3, so confidences of near-saturated cells can only be compared loosely; ids are what is pinned
+        assert ("conf_matrix" in data) == materialize
+        assert len(g["mconf"]) > 30 and g["mconf"].min() < 0.3 and g["mconf"].max() > 0.9  # a spread, not saturation
+        if materialize:
+            err = (data["conf_matrix"].cpu() - g["conf_matrix"]).abs().max().item()
+            print(f"loftr {mode}: conf_matrix max abs err {err:.2e}")
+            assert err < 1e-3
+        got = set(zip(data["i_ids"].tolist(), data["j_ids"].tolist()))
+        ref = set(zip(g["i_ids"].tolist(), g["j_ids"].tolist()))
+        for (i, j) in got ^ ref:  # only where the reference sits within 1e-3 of the threshold
+            assert abs(g["conf_matrix"][0, i, j].item() - 0.2) < 1e-3, (i, j, g["conf_matrix"][0, i, j].item())
+        assert len(got ^ ref) <= 1
+        if got != ref:
+            pytest.skip("a threshold-straddling pair differs; the remaining keys cannot be compared row by row")
         assert torch.equal(data["i_ids"].cpu(), g["i_ids"]) and torch.equal(data["j_ids"].cpu(), g["j_ids"])
-        assert (data["mconf"].cpu() - g["mconf"]).abs().max().item() < 5e-2
+        err = (data["mconf"].cpu() - g["mconf"]).abs().max().item()
+        print(f"loftr {mode} ({'two-pass' if materialize else 'default single-pass'}): mconf max abs err {err:.2e}")
+        assert err < 1e-3  # north_star: confidence values within max-abs 1e-3
     for k, v in g.items():
+        if k == "conf_matrix" and not materialize:
+            continue
         assert k in data, k
         if k in ("conf_matrix", "mconf"):
             continue

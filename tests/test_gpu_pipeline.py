@@ -122,7 +122,7 @@ def test_loftr_cuda_graph_head_matches_eager():
     from onepose_st_b200.loftr import LoFTR_for_OnePose_Plus, default_cfg
     torch.manual_seed(0)
     m = LoFTR_for_OnePose_Plus(default_cfg, enable_fine_matching=True).eval()
-    m.load_state_dict(synthetic.calibrate_loftr_state_dict(m.state_dict()))
+    m.load_state_dict(synthetic.calibrate_loftr_state_dict(m.state_dict(), 256, 256))
     m = m.cuda()
     g = torch.Generator().manual_seed(11)
     pairs = []

@@ -144,7 +144,7 @@ def run_loftr(a):
     torch.manual_seed(0)
     for fine in (False, True):
         m = LoFTR_for_OnePose_Plus(default_cfg, enable_fine_matching=fine).eval()
-        m.load_state_dict(synthetic.calibrate_loftr_state_dict(m.state_dict()))
+        m.load_state_dict(synthetic.calibrate_loftr_state_dict(m.state_dict(), a.size, a.size))
         m = m.cuda()
         for nb in a.pair_batch:
             g = torch.Generator().manual_seed(2000)
