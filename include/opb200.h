@@ -173,6 +173,17 @@ int opb200_stem_conv7x7_s2_relu_nhwc(const float* image, const float* weight_tap
 /* x[p, c] = leaky_relu(x[p, c] + bias[c], slope): folded-BatchNorm shift + nn.LeakyReLU of the FPN heads. */
 int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels, int C, float slope, void* stream);
 
+/* Screening sweep of the default single-pass CoarseMatching: the largest bound delta (octaves) on the fp16 similarity error,
+ * c * 2^-10 * max|a_i| * max|b_j|, up to which the sweep is allowed to run on ONE fp16 product (default 0.75; beyond it,
+ * or when the exact re-evaluation of the captured elements measures an error above 0.05 octave, the call asks for the
+ * repeat on the three split products).  max_delta < 0 only queries.  Returns the previous value. */
+float opb200_coarse_screen_max_delta(float max_delta);
+/* Diagnostics of the last default-path call that used ``workspace`` (synchronises the stream): the largest row norms the
+ * pack pass found on each side, the number of candidates the sweep captured, and the largest |exact - screening|
+ * similarity (octaves) their re-evaluation measured. */
+int opb200_coarse_norms(const void* workspace, int n_batch, int L, int S, int C, float thr, float* norm_a, float* norm_b,
+                        int* candidates, float* observed, void* stream);
+
 /* ---- Backbone convolutions on tcgen05 (NHWC fp16 activations, fp32 accumulation) ----------------------
  * Conv2d(k in {1,3}, stride in {1,2}, padding k/2, no dilation/groups) with BatchNorm folded into the weights, plus the
  * BasicBlock / FPN-head tails: y = act(conv(x) + bias + res).  Replaces conv3x3/conv1x1 + BatchNorm2d + ReLU /
@@ -203,6 +214,39 @@ int opb200_conv_cluster(int on);
 int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight_tap_major, const float* bias, int n_batch,
                                          int H, int W, int Cout, void* out_f16, int* range_flag, void* stream);
 int opb200_upsample2x_add_nhwc_f16(const void* src, int n_batch, int Hs, int Ws, int C, void* dst, void* stream);
+
+/* ---- RANSAC-PnP on the device ------------------------------------------------------
+ * Replaces ransac_PnP (src/utils/metric_utils.py:121-209; call sites inference.py:181-189, 328-336): the reference copies
+ * the matches of a frame to the host and runs OpenCV solvePnPRansac (EPnP, 5 px, 10000 iterations) or pycolmap's
+ * absolute_pose_estimation there.  Here a whole batch of frames is solved where the match rows lie:
+ *   pts3d / pts2d   device fp32, point k of the batch at pts3d + k * stride3 (x, y, z) and pts2d + k * stride2 (u, v) --
+ *                   e.g. columns 0..2 and 3..4 of the matcher's [sum M, 6] rows (stride3 = stride2 = 6)
+ *   offsets         device int [n_frames + 1]: frame f owns points offsets[f] .. offsets[f + 1] - 1
+ *   intrinsics      device double [n_frames][4] = (fx, fy, cx, cy) of each frame's (crop) camera
+ *   iterations      minimal samples (hypotheses) per frame; seed selects them (counter-based hash: deterministic)
+ *   pose            device double [n_frames][3][4] = [R | t] (world -> camera), identity when the frame has fewer than 4
+ *                   points or no hypothesis with >= 4 inliers (the reference returns np.eye(4)[:3] then)
+ *   inlier_mask     device uint8 [sum M]; counts device int [n_frames][2] = (inliers of the refined pose, best RANSAC score)
+ * P3P (Grunert) hypotheses in fp64, inlier counting in fp32, Gauss-Newton refinement on the inliers in fp64. */
+size_t opb200_ransac_pnp_workspace_bytes(int n_frames, int iterations);
+int opb200_ransac_pnp(const float* pts3d, int stride3, const float* pts2d, int stride2, const int* offsets, int n_frames,
+                      const double* intrinsics, float reproj_error_px, int iterations, unsigned seed, double* pose,
+                      unsigned char* inlier_mask, int* counts, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- Keypoint-Free SfM match post-processing -----------------------------------------
+ * Replaces Match2Pts2D / agg_groupby_2d (src/KeypointFreeSfM/coarse_match/utils.py:5-60) and points2D_worker /
+ * update_matches / transform_points2D (src/KeypointFreeSfM/coarse_match/coarse_match_worker.py:87-184).
+ *   rows         device fp32 [n_rows][5] = (u0, v0, u1, v1, conf), the pairs' match rows back to back in pair order
+ *   pair_of_row  device int [n_rows]; pair_images device int [n_pairs][2] = (image0, image1) ids
+ *   keys         device int64 [2 * n_rows]: entry 2 r + side -> (image << 40) | (int(u) << 20) | int(v)
+ *   bad_flag     device int: set when a coordinate is negative, NaN or >= 2^20 (the entry gets the largest key)
+ * opb200_sfm_group_sums: after a STABLE sort of the keys (order[k] = entry id at sorted position k) and the start
+ * offsets of the groups of equal keys (group_start [n_groups + 1]), sums[g] = the group's confidences added in fp64 in
+ * entry order -- the arithmetic of np.bincount(weights=), so the score ranking is bit-identical to the reference's. */
+int opb200_sfm_keys(const float* rows, long long n_rows, const int* pair_of_row, const int* pair_images, long long* keys,
+                    int* bad_flag, void* stream);
+int opb200_sfm_group_sums(const float* rows, const long long* order, const long long* group_start, long long n_groups,
+                          double* sums, void* stream);
 
 #ifdef __cplusplus
 }

@@ -342,18 +342,24 @@ struct FastCfg {
 // 2^delta - 1, a match's confidence moves by at most ~0.2 of the relative error of that remainder, and the remainder
 // of a row that holds a match consists of at least 1 / thr_lim terms; screening is therefore only used while
 // delta <= kScreenMaxDelta (0.25 octave), beyond which the call is repeated on the three split products (algo 2).
-constexpr float kScreenMaxDelta = 0.25f;
+constexpr float kScreenMaxDelta = 0.75f;
+// ... and the sweep checks its own work: every captured element is evaluated twice (screening value, exact value); the
+// largest difference seen is the measured counterpart of the bound, and a call whose measured error exceeds
+// kScreenMaxObserved octaves is repeated on the split products as well.
+constexpr float kScreenMaxObserved = 0.05f;
 constexpr float kScreenMaxNorm = 60000.f;  // |x| <= |row| must stay below the largest fp16 (65504)
 struct ScreenPlan {
   bool ok;
   float thr_lim;
+  float delta;
 };
-__device__ __forceinline__ ScreenPlan screen_plan(const unsigned* __restrict__ norm_sq, float c, float thr) {
+__device__ __forceinline__ ScreenPlan screen_plan(const unsigned* __restrict__ norm_sq, float c, float thr, float max_delta) {
   const float na = sqrtf(__uint_as_float(norm_sq[0])), nb = sqrtf(__uint_as_float(norm_sq[1]));
   const float delta = c * (9.768e-4f * na * nb + 2.9802322e-8f * 16.f * (na + nb));  // 2^-10 (1 + 2^-12), 2^-25 sqrt(256)
   ScreenPlan sp;
-  sp.ok = na <= kScreenMaxNorm && nb <= kScreenMaxNorm && delta <= kScreenMaxDelta;  // (false for NaN / inf)
+  sp.ok = na <= kScreenMaxNorm && nb <= kScreenMaxNorm && delta <= max_delta;  // (false for NaN / inf)
   sp.thr_lim = 0.99f * thr * exp2f(-2.f * delta);
+  sp.delta = delta;
   return sp;
 }
 
@@ -366,7 +372,8 @@ struct SimFastParams {
   int total_tiles;  // N * (Lp/128) * n_tiles, m-major
   float c;          // scale * log2(e)  (> 0)
   float thr_lim;    // 0.99 * thr (slack for the approximate exponentials); the screening sweep takes its own from screen_plan()
-  float thr;
+  float thr, max_delta, lim_scale;
+  const float* row_lb;      // SCREEN: [N*Lp] log2 of a lower bound of each row's full sum (Jensen; pack_f16_kernel), nullable
   const unsigned* norm_sq;  // SCREEN: bits of the largest squared row norm of each side (pack_f16_kernel)
   int* needs_robust;        // SCREEN: bit 1 <- the bound does not allow screening (the caller repeats with algo 2)
   long long* trace; // debug (opb200_debug_trace): per CTA and every fourth tile {MMA issue start, MMA issued, accumulator
@@ -422,6 +429,8 @@ struct FastWarpState {
   float vlim[4] = {kNegInf, kNegInf, kNegInf, kNegInf};
   int dbg_flags = 0;      // debug trace: 1 = the tile took the second (candidate) sweep, 2 = it was re-swept for its reference
   float thr_lim = 0.f;    // candidate limit relative to the row sum
+  float seed_shift = 0.f; // SCREEN: log2(2^delta * 0.99): what turns row_lb into a bound of the screened sums
+  float seed_l2 = kNegInf;  // owner lane: log2 of the a-priori lower bound of its row's sum
 };
 
 // lane t <- reduction over its quad (lanes t ^ 1, t ^ 2, t ^ 3) of v[t % 4]
@@ -445,10 +454,14 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
 #pragma unroll
   for (int h = 0; h < 4; ++h) rv[h] = !RAGGED || i0 + 8 * h < p.L;
   float* __restrict__ colp = p.colpart + ((static_cast<long long>(mt_in_batch) * 4 + quarter) * p.N + n) * p.Sp + jt;
-  if (st.run_m != m_tile) {  // a new block of rows: nothing known about their sums yet
+  if (st.run_m != m_tile) {  // a new block of rows: all that is known about their sums is the a-priori lower bound
     st.run_m = m_tile, st.run_s = 0.f, st.run_T = 0.f;
+    const int own0 = lane & 3;
+    const bool rv0 = !RAGGED || i0 + 8 * own0 < p.L;
+    st.seed_l2 = (p.row_lb != nullptr && rv0) ? p.row_lb[static_cast<long long>(n) * p.Lp + i0 + 8 * own0] + st.seed_shift : kNegInf;
+    const float v0 = st.seed_l2 > kNegInf ? __fdividef(__log2f(st.thr_lim) + st.seed_l2, p.c) : kNegInf;
 #pragma unroll
-    for (int h = 0; h < 4; ++h) st.vlim[h] = kNegInf;
+    for (int h = 0; h < 4; ++h) st.vlim[h] = __shfl_sync(0xffffffffu, v0, (lane & ~3) + h);
   }
   uint64_t racc[4];
   float rmax[4];  // raw accumulator maxima per row
@@ -568,7 +581,8 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     st.run_T = T;
     const float lim = st.thr_lim * st.run_s;
     const bool rv_own = !RAGGED || i0 + 8 * own < p.L;
-    const float vlim_own = (rv_own && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
+    // log2 of the limit: the part of the row seen so far or the a-priori bound, whichever is larger
+    const float vlim_own = (rv_own && lim > 0.f) ? __fdividef(fmaxf(__log2f(lim) + T, __log2f(st.thr_lim) + st.seed_l2), p.c) : INFINITY;
     const bool trig = !released && mx_own > vlim_own;
 #pragma unroll
     for (int h = 0; h < 4; ++h) st.vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
@@ -636,14 +650,17 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + TSTAGES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float thr_lim = p.thr_lim;
+  float thr_lim = p.thr_lim, seed_shift = 0.f;
   if (SCREEN) {  // every CTA derives the same plan from the operand norms; no screening -> nothing to do here
-    const ScreenPlan plan = screen_plan(p.norm_sq, p.c, p.thr);
+    const ScreenPlan plan = screen_plan(p.norm_sq, p.c, p.thr, p.max_delta);
     if (!plan.ok) {
       if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(p.needs_robust, 2);
       return;
     }
-    thr_lim = plan.thr_lim;
+    thr_lim = plan.thr_lim * p.lim_scale;
+    // e_s > thr 2^-delta R and R >= R_jensen: in units of thr_lim = 0.99 thr 2^(-2 delta) the seed is 2^delta R_jensen
+    // (the 0.99 of thr_lim also covers the rounding of the bound itself)
+    seed_shift = plan.delta;
   }
   // contiguous, balanced range of the m-major tile list: at most two A blocks per CTA at these sizes
   const int t_begin = static_cast<int>(static_cast<long long>(p.total_tiles) * blockIdx.x / gridDim.x);
@@ -790,6 +807,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
     const int quarter = warp & 3;
     FastWarpState st;
     st.thr_lim = thr_lim;
+    st.seed_shift = seed_shift;
     int m_tile = m_first, n_tile = n_first + tstage;
     int n_batch = m_tile / tiles_per_batch, mt_in_batch = m_tile % tiles_per_batch;
     for (int t = t_begin + tstage, round = 0; t < t_end; t += TSTAGES, n_tile += TSTAGES, ++round) {
@@ -830,53 +848,84 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   }
 }
 
-// Partial sums of the single-pass sweep -> (reference, log2 sum) per row and per column.  Block = 32 outputs x 8 slices
-// of the part list (coalesced along the output index), slices combined through shared memory in a fixed order.  The
-// reference of a part is that of the warp block it came from (tile_ref).  A finished sum of an existing row / column
-// that is not safely above the flush-to-zero range (or is NaN) raises bit 0 of *needs_robust.
+// Partial sums of the single-pass sweep -> (reference, log2 sum) per row and per column.  The reference of a part is
+// that of the warp block it came from (tile_ref) and is the same for the 32 consecutive rows / columns a warp owns, so a
+// warp first takes the maximum M of its references (lane k holds T_k), turns them into weights 2^(T_k - M) once, and
+// then adds the parts with independent FMAs (no rescaling chain; loads coalesced along the output index, many in
+// flight).  Rows: one warp per 32 rows over all n tiles.  Columns: 8 warps per 32 columns, each over a slice of the
+// (m tile, quarter) list, combined through shared memory in a fixed order (deterministic).  A finished sum of an
+// existing row / column that is not safely above the flush-to-zero range (or is NaN) raises bit 0 of *needs_robust.
 __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict__ rowpart, const float* __restrict__ colpart,
                                                          const float* __restrict__ tile_ref, int N, int L, int S, int Lp, int Sp,
                                                          float2* __restrict__ lse_row, float2* __restrict__ lse_col,
                                                          int* __restrict__ needs_robust) {
   __shared__ float2 sm[8][33];
-  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long n_rows = static_cast<long long>(N) * Lp, n_cols = static_cast<long long>(N) * Sp;
-  const long long row_blocks = n_rows / 32;  // Lp and Sp are multiples of 128
-  const bool is_row = blockIdx.x < row_blocks;
-  const long long idx = (is_row ? blockIdx.x : blockIdx.x - row_blocks) * 32ll + lane;
+  const int row_blocks = static_cast<int>(n_rows / 256 + ((n_rows % 256) != 0));  // Lp is a multiple of 128
   const int mtb = Lp / BLOCK_M, ntb = Sp / SIM_BN;
-  float M = kNegInf, Sm = 0.f;
-  bool exists;
-  if (is_row) {
-    const int n = static_cast<int>(idx / Lp), i = static_cast<int>(idx - static_cast<long long>(n) * Lp);
-    exists = i < L;
-    const float* tr = tile_ref + ((static_cast<long long>(n) * mtb + i / BLOCK_M) * 4 + (i % BLOCK_M) / 32) * ntb;
-#pragma unroll 4
-    for (int k = slice; k < ntb; k += 8) {
-      const float T = tr[k], v = rowpart[k * n_rows + idx];
-      if (T > kNegInf) {
-        const float Mn = fmaxf(M, T);
-        Sm = Sm * exp2f(M - Mn) + v * exp2f(T - Mn);  // exp2f(-inf) = 0 covers the first term
-        M = Mn;
+  if (static_cast<int>(blockIdx.x) < row_blocks) {
+    const long long idx0 = (static_cast<long long>(blockIdx.x) * 8 + warp) * 32;  // this warp's 32 rows
+    if (idx0 >= n_rows) return;
+    const long long idx = idx0 + lane;
+    const int n = static_cast<int>(idx0 / Lp), i0 = static_cast<int>(idx0 - static_cast<long long>(n) * Lp);
+    const float* tr = tile_ref + ((static_cast<long long>(n) * mtb + i0 / BLOCK_M) * 4 + (i0 % BLOCK_M) / 32) * ntb;
+    float M = kNegInf;
+    for (int k0 = 0; k0 < ntb; k0 += 32) {
+      const float T = k0 + lane < ntb ? tr[k0 + lane] : kNegInf;
+      M = fmaxf(M, key_float(__reduce_max_sync(0xffffffffu, float_key(T))));
+    }
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    if (M > kNegInf) {
+      for (int k0 = 0; k0 < ntb; k0 += 32) {
+        const float T = k0 + lane < ntb ? tr[k0 + lane] : kNegInf;
+        const float w = T > kNegInf ? exp2f(T - M) : 0.f;
+        const int kn = min(32, ntb - k0);
+#pragma unroll 8
+        for (int k = 0; k < kn; ++k) {
+          const float wk = __shfl_sync(0xffffffffu, w, k);
+          const float v = __ldcs(rowpart + static_cast<long long>(k0 + k) * n_rows + idx);
+          acc[k & 3] = fmaf(wk > 0.f ? v : 0.f, wk, acc[k & 3]);  // (a part without a reference holds nothing valid)
+        }
       }
     }
-  } else {
-    const int n = static_cast<int>(idx / Sp), j = static_cast<int>(idx - static_cast<long long>(n) * Sp);
-    exists = j < S;
-    const float* tr = tile_ref + static_cast<long long>(n) * mtb * 4 * ntb + j / SIM_BN;
-#pragma unroll 4
-    for (int k = slice; k < 4 * mtb; k += 8) {  // k = (m tile, quarter)
-      const float T = tr[static_cast<long long>(k) * ntb], v = colpart[(static_cast<long long>(k) * N + n) * Sp + j];
-      if (T > kNegInf) {
-        const float Mn = fmaxf(M, T);
-        Sm = Sm * exp2f(M - Mn) + v * exp2f(T - Mn);
-        M = Mn;
+    const float St = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    const bool ok = (i0 + lane) < L && M > kNegInf;
+    lse_row[idx] = make_float2(ok ? M : kNegInf, ok ? log2f(St) : 0.f);
+    if (ok && !(St >= kTinySum)) atomicOr(needs_robust, 1);
+    return;
+  }
+  // ---- columns: 32 per block, 8 slices of the (m tile, quarter) list
+  const long long idx = (static_cast<long long>(blockIdx.x) - row_blocks) * 32 + lane;
+  const long long idx0 = idx - lane;
+  const int n = static_cast<int>(idx0 / Sp), j0 = static_cast<int>(idx0 - static_cast<long long>(n) * Sp);
+  const int j = j0 + lane;
+  const int nparts = 4 * mtb;
+  const int per = (nparts + 7) / 8;
+  const int kb = warp * per, ke = min(nparts, kb + per);
+  const float* tr = tile_ref + static_cast<long long>(n) * nparts * ntb + j0 / SIM_BN;
+  float M = kNegInf;
+  for (int k0 = kb; k0 < ke; k0 += 32) {
+    const float T = k0 + lane < ke ? tr[static_cast<long long>(k0 + lane) * ntb] : kNegInf;
+    M = fmaxf(M, key_float(__reduce_max_sync(0xffffffffu, float_key(T))));
+  }
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  if (M > kNegInf) {
+    for (int k0 = kb; k0 < ke; k0 += 32) {
+      const float T = k0 + lane < ke ? tr[static_cast<long long>(k0 + lane) * ntb] : kNegInf;
+      const float w = T > kNegInf ? exp2f(T - M) : 0.f;
+      const int kn = min(32, ke - k0);
+#pragma unroll 8
+      for (int k = 0; k < kn; ++k) {
+        const float wk = __shfl_sync(0xffffffffu, w, k);
+        const float v = __ldcs(colpart + (static_cast<long long>(k0 + k) * N + n) * Sp + j);
+        acc[k & 3] = fmaf(wk > 0.f ? v : 0.f, wk, acc[k & 3]);
       }
     }
   }
-  sm[slice][lane] = make_float2(M, Sm);
+  sm[warp][lane] = make_float2(M, (acc[0] + acc[1]) + (acc[2] + acc[3]));
   __syncthreads();
-  if (slice == 0) {
+  if (warp == 0) {
     float Mt = kNegInf;
 #pragma unroll
     for (int q = 0; q < 8; ++q) Mt = fmaxf(Mt, sm[q][lane].x);
@@ -888,8 +937,8 @@ __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict
         if (pq.x > kNegInf) St += pq.y * exp2f(pq.x - Mt);
       }
     }
-    const bool ok = exists && Mt > kNegInf;
-    (is_row ? lse_row : lse_col)[idx] = make_float2(ok ? Mt : kNegInf, ok ? log2f(St) : 0.f);
+    const bool ok = j < S && Mt > kNegInf;
+    lse_col[idx] = make_float2(ok ? Mt : kNegInf, ok ? log2f(St) : 0.f);
     if (ok && !(St >= kTinySum)) atomicOr(needs_robust, 1);
   }
 }
@@ -928,7 +977,8 @@ struct SimSweepParams {
   int n_tiles;        // ceil(Sp / 256)
   int total_tiles;    // N * (Lp/128) * n_tiles, m-major
   float c;            // scale * log2(e)  (> 0)
-  float thr;
+  float thr, max_delta;
+  const float* row_lb;      // [N*Lp] log2 of the a-priori (Jensen) lower bound of each row's full sum (pack_f16_kernel)
   const unsigned* norm_sq;  // bits of the largest squared row norm of each side (pack_f16_kernel)
   int* needs_robust;        // bit 1 <- the bound does not allow screening (the caller repeats with algo 2)
   float* colpart;     // [4*Lp/128][N*Sp]          sum_i e_ij over the 32 rows of a warp block
@@ -959,12 +1009,13 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t_begin = static_cast<int>(static_cast<long long>(p.total_tiles) * blockIdx.x / gridDim.x);
   const int t_end = static_cast<int>(static_cast<long long>(p.total_tiles) * (blockIdx.x + 1) / gridDim.x);
-  const ScreenPlan plan = screen_plan(p.norm_sq, p.c, p.thr);
+  const ScreenPlan plan = screen_plan(p.norm_sq, p.c, p.thr, p.max_delta);
   if (!plan.ok) {
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(p.needs_robust, 2);
     return;
   }
   const float thr_lim = plan.thr_lim;
+  const float seed_shift = plan.delta;  // (see sim_fast_kernel)
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.a);
@@ -1095,11 +1146,13 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
     bool rows_ragged;
     float* col_base;
     float* cref_base;
+    float seed_l2 = kNegInf;  // owner lane: log2 of the a-priori lower bound of its row's sum (in units of the screened sums)
     auto enter_rows = [&]() {
       i0 = mt_in_batch * BLOCK_M + quarter * 32 + (lane >> 2);  // this thread's rows: i0 + 8h
       rows_ragged = (mt_in_batch + 1) * BLOCK_M > p.L;
       col_base = p.colpart + ((static_cast<long long>(mt_in_batch) * 4 + quarter) * p.N + n_batch) * p.Sp;
       cref_base = p.col_ref + (static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / 32);
+      seed_l2 = (i0 + 8 * own < p.L && n_batch < p.N) ? p.row_lb[static_cast<long long>(n_batch) * p.Lp + i0 + 8 * own] + seed_shift : kNegInf;
     };
     enter_rows();
 
@@ -1229,7 +1282,8 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
         run_s = fminf(run_s * ptx::ex2(fminf(run_T - T, 60.f)), 1e30f) + s_own;  // (clamps keep it a finite lower bound)
         run_T = T;
         const float lim = thr_lim * run_s;
-        const float vlim_own = (i0 + 8 * own < p.L && lim > 0.f) ? __fdividef(__log2f(lim) + T, p.c) : INFINITY;
+        const float vlim_own = (i0 + 8 * own < p.L && lim > 0.f)
+                                   ? __fdividef(fmaxf(__log2f(lim) + T, __log2f(thr_lim) + seed_l2), p.c) : INFINITY;
 #pragma unroll
         for (int h = 0; h < 4; ++h) vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
         if (cmax[0] > vlim[0] || cmax[1] > vlim[1] || cmax[2] > vlim[2] || cmax[3] > vlim[3]) {  // only the lanes that hold one
@@ -1366,7 +1420,47 @@ struct PackSide {
   long long n_vec;
   int rows_valid, rows_padded;  // per batch element: rows beyond rows_valid are padding and have no say in the norm
 };
-__global__ void __launch_bounds__(256) pack_f16_kernel(PackSide sa, PackSide sb, int blocks_a, unsigned* __restrict__ norm_sq) {
+
+// Column mean of side b per batch element (fp32, deterministic: fixed chunks, the block that finishes last adds the
+// chunk sums in chunk order).  It gives every row of side a an a-priori lower bound of its softmax sum before the sweep
+// has seen a single column:  sum_j 2^(y_ij) >= S 2^(mean_j y_ij) = S 2^(c a_i . mean_j b_j)  (Jensen).  For the rows
+// that hold no match -- nearly all of them -- this bound is within a small factor of the sum, which keeps the first
+// column tiles of a row block from flooding the candidate list (their own partial sum is a poor bound).
+constexpr int MEAN_CHUNKS = 16;
+__global__ void __launch_bounds__(256) colmean_kernel(const __nv_bfloat16* __restrict__ hi, const __nv_bfloat16* __restrict__ lo,
+                                                      int S, int Sp, float* __restrict__ part /* [N][MEAN_CHUNKS][256] */,
+                                                      float* __restrict__ mean /* [N][256] */, int* __restrict__ done /* [N] */) {
+  const int n = blockIdx.x / MEAN_CHUNKS, ch = blockIdx.x % MEAN_CHUNKS, c = threadIdx.x;
+  const int per = (S + MEAN_CHUNKS - 1) / MEAN_CHUNKS;
+  const int j0 = ch * per, j1 = min(S, j0 + per);
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  const long long base = static_cast<long long>(n) * Sp * FAST_C + c;
+  for (int j = j0; j < j1; j += 4) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (j + u < j1) {
+        const long long o = base + static_cast<long long>(j + u) * FAST_C;
+        acc[u] += __bfloat162float(hi[o]) + __bfloat162float(lo[o]);
+      }
+  }
+  part[(static_cast<long long>(n) * MEAN_CHUNKS + ch) * FAST_C + c] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+  __threadfence();
+  __shared__ int last;
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(&done[n], 1) == MEAN_CHUNKS - 1;
+  __syncthreads();
+  if (last) {
+    __threadfence();
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < MEAN_CHUNKS; ++k) t += __ldcg(&part[(static_cast<long long>(n) * MEAN_CHUNKS + k) * FAST_C + c]);
+    mean[n * FAST_C + c] = t / static_cast<float>(S);
+  }
+}
+
+__global__ void __launch_bounds__(256) pack_f16_kernel(PackSide sa, PackSide sb, int blocks_a, unsigned* __restrict__ norm_sq,
+                                                       const float* __restrict__ mean_b, float c, int S,
+                                                       float* __restrict__ row_lb) {
   const bool second = static_cast<int>(blockIdx.x) >= blocks_a;
   const PackSide& sd = second ? sb : sa;
   const long long bid = second ? blockIdx.x - blocks_a : blockIdx.x, nblk = second ? gridDim.x - blocks_a : blocks_a;
@@ -1375,21 +1469,34 @@ __global__ void __launch_bounds__(256) pack_f16_kernel(PackSide sa, PackSide sb,
     const uint4 h = sd.hi[t], l = sd.lo[t];
     const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
     uint32_t ow[4];
-    float sq = 0.f;
+    float sq = 0.f, dot = 0.f;
+    const long long row = t / (FAST_C / 8);
+    const int nb = static_cast<int>(row / sd.rows_padded);
+    const bool valid = static_cast<int>(row - static_cast<long long>(nb) * sd.rows_padded) < sd.rows_valid;
+    float mu[8];
+    if (!second && row_lb != nullptr) {
+      const float4* m4 = reinterpret_cast<const float4*>(mean_b + nb * FAST_C + (threadIdx.x & 31) * 8);
+      const float4 m0 = m4[0], m1 = m4[1];
+      mu[0] = m0.x, mu[1] = m0.y, mu[2] = m0.z, mu[3] = m0.w, mu[4] = m1.x, mu[5] = m1.y, mu[6] = m1.z, mu[7] = m1.w;
+    }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const float x0 = __uint_as_float(hw[q] << 16) + __uint_as_float(lw[q] << 16);
       const float x1 = __uint_as_float(hw[q] & 0xffff0000u) + __uint_as_float(lw[q] & 0xffff0000u);
       sq = fmaf(x0, x0, fmaf(x1, x1, sq));
+      if (!second && row_lb != nullptr) dot = fmaf(x0, mu[2 * q], fmaf(x1, mu[2 * q + 1], dot));
       const __half2 v = __floats2half2_rn(x0, x1);
       ow[q] = *reinterpret_cast<const uint32_t*>(&v);
     }
     sd.out[t] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
-    const long long row = t / (FAST_C / 8);
-    if (static_cast<int>(row % sd.rows_padded) < sd.rows_valid)
-      worst = fmaxf(worst, sq <= 3e38f ? sq : INFINITY);  // (a NaN norm must not vanish in the maximum: it counts as +inf)
+    for (int o = 16; o > 0; o >>= 1) {
+      sq += __shfl_xor_sync(0xffffffffu, sq, o);
+      dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    }
+    if (valid) worst = fmaxf(worst, sq <= 3e38f ? sq : INFINITY);  // (a NaN norm must not vanish in the maximum: it counts as +inf)
+    if (!second && row_lb != nullptr && (threadIdx.x & 31) == 0)  // log2(S 2^(c a . mean b)); a non-finite one is no bound
+      row_lb[row] = (valid && fabsf(dot) <= 3e38f) ? fmaf(c, dot, __log2f(static_cast<float>(S))) : kNegInf;
   }
   if ((threadIdx.x & 31) == 0 && worst > 0.f) atomicMax(&norm_sq[second ? 1 : 0], __float_as_uint(worst));
 }
@@ -1404,7 +1511,9 @@ __global__ void __launch_bounds__(256) cand_rescore_kernel(Candidate* __restrict
                                                            const __nv_bfloat16* __restrict__ b_lo, float c,
                                                            const float2* __restrict__ lse_row, const float2* __restrict__ lse_col,
                                                            unsigned long long* __restrict__ rowdelta,
-                                                           unsigned long long* __restrict__ coldelta) {
+                                                           unsigned long long* __restrict__ coldelta,
+                                                           unsigned* __restrict__ observed /* bits of max |y - y_screen| */,
+                                                           int* __restrict__ needs_robust) {
   const int n_c = min(*count, cap);
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
@@ -1438,6 +1547,9 @@ __global__ void __launch_bounds__(256) cand_rescore_kernel(Candidate* __restrict
       const float dc = exp2f((y - lc.x) - lc.y) - exp2f((cd.conf - lc.x) - lc.y);
       atomicAdd(&rowdelta[ra], static_cast<unsigned long long>(__double2ll_rn(static_cast<double>(dr) * kDeltaScale)));
       atomicAdd(&coldelta[rb], static_cast<unsigned long long>(__double2ll_rn(static_cast<double>(dc) * kDeltaScale)));
+      const float obs = fabsf(y - cd.conf);
+      if (obs > __uint_as_float(*observed)) atomicMax(observed, __float_as_uint(obs));  // (non-negative floats order like their bits)
+      if (!(obs <= kScreenMaxObserved)) atomicOr(needs_robust, 2);
       cand[t].conf = y;
     }
   }
@@ -1554,9 +1666,10 @@ __global__ void __launch_bounds__(256) compact_kernel(const int* __restrict__ ro
       const bool cand_over = *cand_count > cand_cap;
       // fast path: a full candidate list or an FTZ-endangered sum asks for the two-pass rerun instead
       overflow[0] = (!fast && cand_over) || (total > capacity);
-      // rerun code: 1 = take the two-pass path, 2 = repeat single-pass with the three split products (fp16 range)
+      // rerun code: 2 = the screening sweep declined (operand norms): repeat single-pass on the three split products -- it
+      // wrote no statistics, so bit 0 means nothing then; 1 = take the two-pass path (dynamic range, candidate list full)
       const int flag = cand_count[2];
-      overflow[1] = !fast ? 0 : ((cand_over || (flag & 1)) ? 1 : ((flag & 2) ? 2 : 0));
+      overflow[1] = !fast ? 0 : ((flag & 2) ? 2 : ((cand_over || (flag & 1)) ? 1 : 0));
     }
   }
   __syncthreads();
@@ -1603,11 +1716,14 @@ struct CoarseWs {
   float2 *lse_row, *lse_col;
   float* tile_ref;                             // single pass: reference exponent per (m tile, quarter, n tile | 32-column chunk)
   float* row_ref;                              // sweep kernel: reference of each row-sum record (0xff-filled per call)
+  float *row_lb, *mean_part, *mean_b;          // screening: Jensen lower bound per row; column mean of side b
+  int* mean_done;                              // [N] chunk counters of colmean_kernel (cleared per call)
   unsigned long long* agg;                     // [COMPACT_BLOCKS] look-back words of the compaction (cleared per call)
   int* ticket;
   Candidate* cand;
   unsigned *rowmax, *colmax;
-  int *rowj, *row_base, *counters;  // counters: [0] cand_count, [2] rerun flags, [4], [5] largest squared row norms (bits)
+  int *rowj, *row_base, *counters;  // counters: [0] cand_count, [2] rerun flags, [4], [5] largest squared row norms (bits),
+                                    // [6] largest |exact - screening| similarity seen by the rescore pass (bits, octaves)
   int cand_cap;
   int Lp, Sp;
   size_t zero_begin, zero_bytes;  // region that must be cleared per call (rowmax, colmax, counters)
@@ -1638,6 +1754,9 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.colpart = static_cast<float2*>(take(static_cast<size_t>(w.Lp / BLOCK_M) * rb * 16));  // single pass: 4 float rows per m tile
   w.tile_ref = static_cast<float*>(take(ra / BLOCK_M * 4 * (w.Sp / 32) * 4));  // (one per 32 columns for the sweep kernel)
   w.row_ref = static_cast<float*>(take(static_cast<size_t>(SW_ROW_SLOTS) * (ra / 32) * 4));
+  w.row_lb = static_cast<float*>(take(ra * 4));
+  w.mean_part = static_cast<float*>(take(static_cast<size_t>(N) * MEAN_CHUNKS * FAST_C * 4));
+  w.mean_b = static_cast<float*>(take(static_cast<size_t>(N) * FAST_C * 4));
   w.lse_row = static_cast<float2*>(take(ra * 8));
   w.lse_col = static_cast<float2*>(take(rb * 8));
   const double bound = std::ceil(static_cast<double>(N) * (L < S ? L : S) / (thr > 1e-6f ? thr : 1e-6f)) + 64;
@@ -1651,6 +1770,7 @@ static CoarseWs carve_coarse(void* base, int N, int L, int S, int C, float thr) 
   w.rowmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * L * 4));
   w.colmax = static_cast<unsigned*>(take(static_cast<size_t>(N) * S * 4));
   w.counters = static_cast<int*>(take(32));
+  w.mean_done = static_cast<int*>(take(static_cast<size_t>(N) * 4));
   w.agg = static_cast<unsigned long long*>(take(COMPACT_BLOCKS * 8));
   w.ticket = static_cast<int*>(take(4));
   w.rowdelta = static_cast<unsigned long long*>(take(ra * 8));
@@ -1669,6 +1789,8 @@ using namespace opb;
 namespace {
 std::mutex g_kt_mutex;
 bool g_kt_armed = false;
+float g_screen_max_delta = opb::kScreenMaxDelta;
+float g_screen_lim_scale = getenv("OPB200_SCREEN_LIM_SCALE") ? static_cast<float>(atof(getenv("OPB200_SCREEN_LIM_SCALE"))) : 1.f;
 std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_kt_events;
 }  // namespace
 
@@ -1747,8 +1869,10 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       PackSide sb{reinterpret_cast<const uint4*>(w.b_hi), reinterpret_cast<const uint4*>(w.b_lo), reinterpret_cast<uint4*>(w.b_f16), vb, S, Sp};
       const int ba = static_cast<int>((va + 255) / 256 < 8 * num_sms() ? (va + 255) / 256 : 8 * num_sms());
       const int bb = static_cast<int>((vb + 255) / 256 < 4 * num_sms() ? (vb + 255) / 256 : 4 * num_sms());
-      pack_f16_kernel<<<ba + bb, 256, 0, stream>>>(sa, sb, ba, reinterpret_cast<unsigned*>(w.counters + 4));
-      count_launch();
+      colmean_kernel<<<N * MEAN_CHUNKS, 256, 0, stream>>>(w.b_hi, w.b_lo, S, Sp, w.mean_part, w.mean_b, w.mean_done);
+      pack_f16_kernel<<<ba + bb, 256, 0, stream>>>(sa, sb, ba, reinterpret_cast<unsigned*>(w.counters + 4), w.mean_b,
+                                                   scale * kLog2e, S, w.row_lb);
+      count_launch(2);
     }
     if (screen) {  // the data type of a tensor map only matters for its fill value
       if ((r = make_tmap_bf16(&fp.a_hi, w.a_f16, static_cast<uint64_t>(N) * Lp, C, C, BLOCK_M))) return r;
@@ -1775,7 +1899,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       sp.N = N, sp.L = L, sp.S = S, sp.Lp = Lp, sp.Sp = Sp;
       sp.n_tiles = (Sp + SW_BN - 1) / SW_BN;
       sp.total_tiles = m_tiles * sp.n_tiles;
-      sp.c = scale * kLog2e, sp.thr = thr, sp.norm_sq = reinterpret_cast<const unsigned*>(w.counters + 4), sp.needs_robust = w.counters + 2;
+      sp.c = scale * kLog2e, sp.thr = thr, sp.max_delta = g_screen_max_delta, sp.row_lb = w.row_lb, sp.norm_sq = reinterpret_cast<const unsigned*>(w.counters + 4), sp.needs_robust = w.counters + 2;
       sp.colpart = reinterpret_cast<float*>(w.colpart), sp.col_ref = w.tile_ref;
       sp.rowpart = reinterpret_cast<float*>(w.rowpart), sp.row_ref = w.row_ref;
       sp.cand = w.cand, sp.cand_count = w.counters, sp.cand_cap = w.cand_cap;
@@ -1802,8 +1926,10 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     fp.n_tiles = screen ? (Sp + FastCfg<true>::BN - 1) / FastCfg<true>::BN : (Sp + FastCfg<false>::BN - 1) / FastCfg<false>::BN;
     fp.total_tiles = m_tiles * fp.n_tiles;
     fp.c = scale * kLog2e;
-    fp.thr_lim = 0.99f * thr, fp.thr = thr;
+    fp.thr_lim = 0.99f * thr, fp.thr = thr, fp.max_delta = g_screen_max_delta;
     fp.norm_sq = reinterpret_cast<const unsigned*>(w.counters + 4), fp.needs_robust = w.counters + 2;
+    fp.row_lb = screen ? w.row_lb : nullptr;
+    fp.lim_scale = g_screen_lim_scale;
     fp.cand_tag = screen ? 2 : 1;
     fp.trace = next_trace_slot(num_sms());
     fp.debug = dbg;
@@ -1824,7 +1950,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       g_kt_events.emplace_back(kt0, kt1);
     }
     const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
-    merge_fast_kernel<<<static_cast<unsigned>(nr / 32 + nc / 32), 256, 0, stream>>>(fp.rowpart, fp.colpart, w.tile_ref, N, L, S, Lp, Sp,
+    merge_fast_kernel<<<static_cast<unsigned>((nr + 255) / 256 + nc / 32), 256, 0, stream>>>(fp.rowpart, fp.colpart, w.tile_ref, N, L, S, Lp, Sp,
                                                                                     w.lse_row, w.lse_col, w.counters + 2);
     count_launch();
     }
@@ -1877,7 +2003,8 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
   const int cb = (w.cand_cap + 255) / 256 < 592 ? (w.cand_cap + 255) / 256 : 592;
   if (screen) {
     cand_rescore_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, Lp, Sp, w.a_hi, w.a_lo, w.b_hi, w.b_lo,
-                                                scale * kLog2e, w.lse_row, w.lse_col, w.rowdelta, w.coldelta);
+                                                scale * kLog2e, w.lse_row, w.lse_col, w.rowdelta, w.coldelta,
+                                                reinterpret_cast<unsigned*>(w.counters + 6), w.counters + 2);
     count_launch();
   }
   cand_max_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.lse_row, w.lse_col, Lp, Sp, thr, w.rowdelta,
@@ -1922,6 +2049,30 @@ int opb200_coarse_match_planes(const void* a_hi, const void* a_lo, const void* b
   return coarse_match_impl(nullptr, nullptr, ext, mask_a, mask_b, mask_fill, n_batch, L, S, C, scale, thr, border_rm,
                            border_mode, h0, w0, h1, w1, valid_hw, b_ids, i_ids, j_ids, mconf, capacity, count_and_overflow,
                            conf_matrix, workspace, workspace_bytes, precision, algo, stream);
+}
+
+float opb200_coarse_screen_max_delta(float max_delta) {
+  const float prev = g_screen_max_delta;
+  if (max_delta >= 0.f) g_screen_max_delta = max_delta;
+  return prev;
+}
+
+int opb200_coarse_norms(const void* workspace, int n_batch, int L, int S, int C, float thr, float* norm_a, float* norm_b,
+                        int* candidates, float* observed, void* stream) {
+  OPB_CHECK_ARG(workspace && norm_a && norm_b && candidates && observed, "null pointer");
+  CoarseWs w = carve_coarse(const_cast<void*>(workspace), n_batch, L, S, C, thr);
+  int words[8];
+  OPB_CHECK_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  OPB_CHECK_CUDA(cudaMemcpy(words, w.counters, sizeof(words), cudaMemcpyDeviceToHost));
+  unsigned ua, ub;
+  std::memcpy(&ua, &words[4], 4);
+  std::memcpy(&ub, &words[5], 4);
+  float fa, fb;
+  std::memcpy(&fa, &ua, 4);
+  std::memcpy(&fb, &ub, 4);
+  *norm_a = std::sqrt(fa), *norm_b = std::sqrt(fb), *candidates = words[0];
+  std::memcpy(observed, &words[6], 4);
+  return OPB_OK;
 }
 
 int opb200_coarse_kernel_timing(int enable) {

@@ -57,7 +57,7 @@ class _Workspaces:
         # one buffer per (device, stream | scope, tag): forwards in flight on different streams never share scratch
         sc = getattr(self._tl, "scope", None)
         owner = ("scope", sc) if sc is not None else torch.cuda.current_stream(device).cuda_stream
-        key = (device.index, owner, tag)
+        key = (device.index if device.index is not None else torch.cuda.current_device(), owner, tag)
         buf = self._bufs.get(key)
         if buf is None or buf.numel() < nbytes:
             buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
@@ -485,3 +485,25 @@ def upsample2x_add_f16_(dst: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
         st = _lib.lib().opb200_upsample2x_add_nhwc_f16(_lib.ptr(src), n, hs, ws, c, _lib.ptr(dst), _lib.stream_ptr())
     _lib.check(st, "opb200_upsample2x_add_nhwc_f16")
     return dst
+
+
+def coarse_screen_max_delta(max_delta: float = -1.0) -> float:
+    """Set (>= 0) or query (< 0) the bound on the fp16 similarity error up to which the default CoarseMatching sweeps ONE
+    fp16 product (include/opb200.h: opb200_coarse_screen_max_delta).  Returns the previous value."""
+    l = _lib.lib()
+    l.opb200_coarse_screen_max_delta.restype = ctypes.c_float
+    return float(l.opb200_coarse_screen_max_delta(ctypes.c_float(max_delta)))
+
+
+def coarse_diagnostics(device, n: int, L: int, S: int, C: int, thr: float):
+    """(largest row norm of side a, of side b, candidates captured, largest measured |exact - screening| similarity in
+    octaves) of the last default-path coarse_match call on the current stream with these sizes (synchronises)."""
+    l = _lib.lib()
+    l.opb200_coarse_match_workspace_bytes.restype = _c_sz
+    nbytes = int(l.opb200_coarse_match_workspace_bytes(n, L, S, C, ctypes.c_float(thr)))
+    ws = workspaces.get(device, "coarse", nbytes)
+    na, nb, nc, ob = ctypes.c_float(0), ctypes.c_float(0), ctypes.c_int(0), ctypes.c_float(0)
+    st = l.opb200_coarse_norms(_lib.ptr(ws), n, L, S, C, ctypes.c_float(thr), ctypes.byref(na), ctypes.byref(nb),
+                               ctypes.byref(nc), ctypes.byref(ob), _lib.stream_ptr())
+    _lib.check(st, "opb200_coarse_norms")
+    return float(na.value), float(nb.value), int(nc.value), float(ob.value)
