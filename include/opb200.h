@@ -153,6 +153,15 @@ int opb200_gather_rows(const float* src, int64_t sn, int64_t sc, int64_t sl, int
  * over the kornia-0.4.1 normalised W x W grid.  q row m starts at q + m*q_stride. */
 int opb200_fine_match(const float* q, int64_t q_stride, const float* win, int M, int W, int Cf, float* expec_f,
                       void* stream);
+/* bf16 arm of the fine level (BASELINE.json configs[4]): windows / query vectors stored as bf16 (half the bytes of this
+ * HBM-bound stage), widened exactly and accumulated in fp32.  opb200_fine_gather_bf16 writes bf16 windows from the fp32
+ * fine map; opb200_fine_match_bf16 reads bf16 q [M, Cf] (row stride q_stride elements) and win [M, W*W, Cf].  Error
+ * against the fp32 / fp64 evaluation: profiles/r02_stage_fine.jsonl, tests/test_gpu_fine.py (expec_f < 2e-2). */
+int opb200_fine_gather_bf16(const float* feat, int64_t sn, int64_t sc, int64_t sh, int64_t sw, int n_batch, int Cf, int Hf,
+                            int Wf, const int64_t* b_ids, const int64_t* cell_ids, int M, int W, int stride, int Hc, int Wc,
+                            void* out_bf16, int* err_flag, void* stream);
+int opb200_fine_match_bf16(const void* q, int64_t q_stride, const void* win, int M, int W, int Cf, float* expec_f,
+                           void* stream);
 
 /* ---- Standalone LinearAttention.forward (linear_attention.py:29-61 / LoFTR :20-47) -----------------
  * q [n, L, H, D], k, v [n, S, H, D] fp32 contiguous; masks nullable bytes [n, L] / [n, S]; out [n, L, H, D]. */
@@ -214,6 +223,20 @@ int opb200_conv_cluster(int on);
 int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight_tap_major, const float* bias, int n_batch,
                                          int H, int W, int Cout, void* out_f16, int* range_flag, void* stream);
 int opb200_upsample2x_add_nhwc_f16(const void* src, int n_batch, int Hs, int Ws, int C, void* dst, void* stream);
+
+/* ---- 3D keypoint position encoding ----------------------------------------------------
+ * Replaces normalize_3d_keypoints (src/models/OnePosePlus/utils/normalize.py:17-28) + KeypointEncoding_linear.forward
+ * (src/models/OnePosePlus/utils/position_encoding.py:46-79) with keypoints_encoder [32, 64, 128], descriptor_dim 256 and
+ * norm_method "instancenorm" (statistics over the channels of each point, biased variance, eps 1e-5):
+ *   out[n, c, l] = desc[n, c, l] + MLP((kpts[n, l] - mean_l kpts[n]) / (0.6 * max extent of kpts[0]))[c]
+ *   kpts [n, L, 3] and desc [n, 256, L] with element strides (kn, kl, kc) / (dn, dc, dl) -- broadcast views allowed;
+ *   packed_w: opb200_keypoint_encode_packed_floats() floats = W1^T [3][32], b1, W2^T [32][64], b2, W3^T [64][128], b3,
+ *   W4^T [128][256], b4 (input-major weights);  normalize = 0 skips the normalisation (kpts are normalised already);
+ *   out [n, 256, L] contiguous fp32;  stats_ws: 4 * n_batch floats of scratch. */
+size_t opb200_keypoint_encode_packed_floats(void);
+int opb200_keypoint_encode(const float* kpts, int64_t kn, int64_t kl, int64_t kc, const float* desc, int64_t dn, int64_t dc,
+                           int64_t dl, const float* packed_w, int n_batch, int L, int normalize, float* out, float* stats_ws,
+                           void* stream);
 
 /* ---- RANSAC-PnP on the device ------------------------------------------------------
  * Replaces ransac_PnP (src/utils/metric_utils.py:121-209; call sites inference.py:181-189, 328-336): the reference copies

@@ -15,18 +15,22 @@
 namespace opb {
 
 // one block per match, one thread per channel; coalesced when the feature map is channels-last (sc == 1)
+__device__ __forceinline__ void store_feat(float* p, float v) { *p = v; }
+__device__ __forceinline__ void store_feat(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+
+template <typename OutT>
 __global__ void fine_gather_kernel(const float* __restrict__ feat, long long sn, long long sc, long long sh, long long sw,
                                    int N, int Cf, int Hf, int Wf, const long long* __restrict__ b_ids,
                                    const long long* __restrict__ cell_ids, int M, int W, int stride, int Wc, int n_cells,
-                                   float* __restrict__ out, int* __restrict__ err_flag) {
+                                   OutT* __restrict__ out, int* __restrict__ err_flag) {
   const int m = blockIdx.x;
   if (m >= M) return;
   const long long b = b_ids[m], cell = cell_ids[m];
   const int WW = W * W;
-  float* o = out + static_cast<long long>(m) * WW * Cf;
+  OutT* o = out + static_cast<long long>(m) * WW * Cf;
   if (b < 0 || b >= N || cell < 0 || cell >= n_cells) {  // the reference raises IndexError here
     if (threadIdx.x == 0) atomicExch(err_flag, 1);
-    for (int idx = threadIdx.x; idx < WW * Cf; idx += blockDim.x) o[idx] = 0.f;
+    for (int idx = threadIdx.x; idx < WW * Cf; idx += blockDim.x) store_feat(o + idx, 0.f);
     return;
   }
   const int r = static_cast<int>(cell) / Wc, c = static_cast<int>(cell) % Wc;
@@ -39,7 +43,7 @@ __global__ void fine_gather_kernel(const float* __restrict__ feat, long long sn,
         const int x = x0 + wx;
         float v = 0.f;  // F.unfold zero padding
         if (y >= 0 && y < Hf && x >= 0 && x < Wf) v = __ldg(fb + ch * sc + y * sh + x * sw);
-        o[(wy * W + wx) * Cf + ch] = v;
+        store_feat(o + (wy * W + wx) * Cf + ch, v);
       }
     }
   }
@@ -60,20 +64,28 @@ __global__ void gather_rows_kernel(const float* __restrict__ src, long long sn, 
 
 // one block (4 warps) per match: warp w correlates window rows w, w+4, ... with the query vector
 // (float4 per lane, Cf = 128), then warp 0 does the softmax expectation over the WW scores.
-template <int CF>
-__global__ void __launch_bounds__(128) fine_match_kernel(const float* __restrict__ q, long long q_stride,
-                                                         const float* __restrict__ win, int M, int W,
+// four consecutive channels of a feature row: fp32 (16 bytes) or bf16 (8 bytes, widened exactly)
+__device__ __forceinline__ float4 load4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 load4(const __nv_bfloat16* p) {
+  const uint2 w = __ldg(reinterpret_cast<const uint2*>(p));
+  return make_float4(__uint_as_float(w.x << 16), __uint_as_float(w.x & 0xffff0000u), __uint_as_float(w.y << 16),
+                     __uint_as_float(w.y & 0xffff0000u));
+}
+
+template <int CF, typename InT>
+__global__ void __launch_bounds__(128) fine_match_kernel(const InT* __restrict__ q, long long q_stride,
+                                                         const InT* __restrict__ win, int M, int W,
                                                          float* __restrict__ expec_f) {
-  static_assert(CF == 128, "one float4 per lane");
+  static_assert(CF == 128, "four channels per lane");
   const int m = blockIdx.x;
   if (m >= M) return;
   __shared__ float sim[128];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int WW = W * W;
-  const float4 qv = reinterpret_cast<const float4*>(q + m * q_stride)[lane];
-  const float4* wbase = reinterpret_cast<const float4*>(win + static_cast<long long>(m) * WW * CF);
+  const float4 qv = load4(q + m * q_stride + 4 * lane);
+  const InT* wbase = win + static_cast<long long>(m) * WW * CF;
   for (int r = warp; r < WW; r += 4) {
-    const float4 wv = __ldg(wbase + r * (CF / 4) + lane);
+    const float4 wv = load4(wbase + r * CF + 4 * lane);
     float d = qv.x * wv.x;
     d = fmaf(qv.y, wv.y, d);
     d = fmaf(qv.z, wv.z, d);
@@ -148,9 +160,25 @@ int opb200_fine_gather(const float* feat, int64_t sn, int64_t sc, int64_t sh, in
   OPB_CHECK_ARG(feat && b_ids && cell_ids && out && err_flag, "null pointer");
   OPB_CHECK_ARG(W >= 1 && (W & 1) == 1 && W <= 11, "window size must be odd and <= 11");
   OPB_CHECK_ARG(stride >= 1 && Hc >= 1 && Wc >= 1, "bad grid");
-  fine_gather_kernel<<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
+  fine_gather_kernel<float><<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
       feat, sn, sc, sh, sw, n_batch, Cf, Hf, Wf, reinterpret_cast<const long long*>(b_ids),
       reinterpret_cast<const long long*>(cell_ids), M, W, stride, Wc, Hc * Wc, out, err_flag);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_fine_gather_bf16(const float* feat, int64_t sn, int64_t sc, int64_t sh, int64_t sw, int n_batch, int Cf, int Hf,
+                            int Wf, const int64_t* b_ids, const int64_t* cell_ids, int M, int W, int stride, int Hc, int Wc,
+                            void* out_bf16, int* err_flag, void* stream_) {
+  if (int r = check_device()) return r;
+  if (M <= 0) return OPB_OK;
+  OPB_CHECK_ARG(feat && b_ids && cell_ids && out_bf16 && err_flag, "null pointer");
+  OPB_CHECK_ARG(W >= 1 && (W & 1) == 1 && W <= 11, "window size must be odd and <= 11");
+  OPB_CHECK_ARG(stride >= 1 && Hc >= 1 && Wc >= 1, "bad grid");
+  fine_gather_kernel<__nv_bfloat16><<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
+      feat, sn, sc, sh, sw, n_batch, Cf, Hf, Wf, reinterpret_cast<const long long*>(b_ids),
+      reinterpret_cast<const long long*>(cell_ids), M, W, stride, Wc, Hc * Wc, static_cast<__nv_bfloat16*>(out_bf16), err_flag);
   count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
@@ -178,7 +206,23 @@ int opb200_fine_match(const float* q, int64_t q_stride, const float* win, int M,
   OPB_CHECK_ARG(W >= 3 && (W & 1) == 1 && W * W <= 128, "window size must be odd with W*W <= 128");
   OPB_CHECK_ARG(q_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(q) & 15) == 0 && (reinterpret_cast<uintptr_t>(win) & 15) == 0,
                 "q / win must be 16-byte aligned");
-  fine_match_kernel<128><<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(q, q_stride, win, M, W, expec_f);
+  fine_match_kernel<128, float><<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(q, q_stride, win, M, W, expec_f);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_fine_match_bf16(const void* q, int64_t q_stride, const void* win, int M, int W, int Cf, float* expec_f,
+                           void* stream_) {
+  if (int r = check_device()) return r;
+  if (M <= 0) return OPB_OK;
+  OPB_CHECK_ARG(q && win && expec_f, "null pointer");
+  OPB_CHECK_ARG(Cf == 128, "fine feature dim must be 128");
+  OPB_CHECK_ARG(W >= 3 && (W & 1) == 1 && W * W <= 128, "window size must be odd with W*W <= 128");
+  OPB_CHECK_ARG(q_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(q) & 7) == 0 && (reinterpret_cast<uintptr_t>(win) & 7) == 0,
+                "q / win must be 8-byte aligned");
+  fine_match_kernel<128, __nv_bfloat16><<<M, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const __nv_bfloat16*>(q), q_stride, static_cast<const __nv_bfloat16*>(win), M, W, expec_f);
   count_launch();
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;

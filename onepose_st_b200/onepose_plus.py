@@ -91,8 +91,40 @@ class KeypointEncoding_linear(nn.Module):
                 x = m(x)
         return x
 
+    def _kernel_ok(self, kpts, descriptors):
+        lin = [m for m in self.encoder if isinstance(m, nn.Linear)]
+        return (kpts.is_cuda and descriptors.is_cuda and not self.training and not torch.is_grad_enabled()
+                and self.norm_method == "instancenorm" and [tuple(m.weight.shape) for m in lin] == [(32, 3), (64, 32), (128, 64), (256, 128)]
+                and kpts.dim() == 3 and kpts.shape[-1] == 3 and descriptors.dim() == 3 and descriptors.shape[1] == 256
+                and descriptors.shape[2] == kpts.shape[1] and descriptors.shape[0] == kpts.shape[0])
+
+    def _packed(self):
+        lin = [m for m in self.encoder if isinstance(m, nn.Linear)]
+        ps = [t for m in lin for t in (m.weight, m.bias)]
+        key = tuple((p.data_ptr(), p._version, str(p.device)) for p in ps)
+        hit = self.__dict__.get("_packed_cache")
+        if hit is None or hit[0] != key:
+            with _cache_lock:
+                flat = torch.cat([t for m in lin for t in (m.weight.detach().float().t().contiguous().flatten(),
+                                                           m.bias.detach().float().flatten())])
+                torch.cuda.current_stream(flat.device).synchronize()
+                hit = (key, flat)
+                self.__dict__["_packed_cache"] = hit
+        return hit[1]
+
+    def encode(self, kpts, descriptors, normalize: bool):
+        """descriptors + MLP(kpts)^T on the fused kernel (csrc/kptenc.cu); ``normalize`` folds normalize_3d_keypoints in."""
+        return ops.keypoint_encode(kpts, descriptors, self._packed(), normalize)
+
     def forward(self, kpts, descriptors):
+        if self._kernel_ok(kpts, descriptors):
+            return self.encode(kpts, descriptors, False)
         return descriptors + self.mlp(kpts).transpose(2, 1)
+
+    def __getstate__(self):
+        st = self.__dict__.copy()
+        st.pop("_packed_cache", None)
+        return st
 
 
 class LocalFeatureTransformer(_TransformerBase):
@@ -302,11 +334,14 @@ class OnePosePlus_model(nn.Module):
         kp = data["keypoints3d"]
 
         def encode():
+            enc = self.kpt_3d_pos_encoding
+            fused = enc._kernel_ok(kp, desc)  # normalisation + MLP + add in one kernel (else: eager PyTorch on the GPU)
             if kp.shape[0] > 1 and kp.stride(0) == 0 and desc.stride(0) == 0:
                 # one 3D model broadcast over the batch: encode it once, hand out a broadcast view (stride 0), which is
                 # also what lets the coarse transformer reuse its first self layer on this stream
-                return self.kpt_3d_pos_encoding(normalize_3d_keypoints(kp[:1]), desc[:1]).expand(kp.shape[0], -1, -1)
-            return self.kpt_3d_pos_encoding(normalize_3d_keypoints(kp), desc)
+                one = enc.encode(kp[:1], desc[:1], True) if fused else enc(normalize_3d_keypoints(kp[:1]), desc[:1])
+                return one.expand(kp.shape[0], -1, -1)
+            return enc.encode(kp, desc, True) if fused else enc(normalize_3d_keypoints(kp), desc)
 
         if tensor_key(kp) is None or tensor_key(desc) is None:  # inference tensors track no version: never cached
             return encode()

@@ -292,21 +292,25 @@ def _err_flag(dev) -> torch.Tensor:
 
 
 def fine_gather(feat: torch.Tensor, b_ids: torch.Tensor, cell_ids: torch.Tensor, W: int, stride: int, hc: int, wc: int,
-                err_flag: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """feat [N,Cf,Hf,Wf] (any memory format) -> windows [M, W*W, Cf] of the coarse cells cell_ids."""
+                err_flag: Optional[torch.Tensor] = None, dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """feat [N,Cf,Hf,Wf] (any memory format) -> windows [M, W*W, Cf] of the coarse cells cell_ids, as fp32 or (``dtype``
+    = torch.bfloat16) bf16 windows (half the bytes; BASELINE.json configs[4])."""
     _need_cuda(feat, b_ids, cell_ids)
+    if dtype not in (torch.float32, torch.bfloat16):
+        raise _lib.Opb200Error("fine_gather: dtype must be torch.float32 or torch.bfloat16")
     feat = _f32(feat)
     n, cf, hf, wf = feat.shape
     m = int(b_ids.shape[0])
-    out = torch.empty(m, W * W, cf, dtype=torch.float32, device=feat.device)
+    out = torch.empty(m, W * W, cf, dtype=dtype, device=feat.device)
     if m == 0:
         return out
     flag = err_flag if err_flag is not None else _err_flag(feat.device)
     b_ids, cell_ids = b_ids.long().contiguous(), cell_ids.long().contiguous()
     with _Stage("fine_gather"):
-        st = _lib.lib().opb200_fine_gather(_lib.ptr(feat), _c_i64(feat.stride(0)), _c_i64(feat.stride(1)), _c_i64(feat.stride(2)),
-                                       _c_i64(feat.stride(3)), n, cf, hf, wf, _lib.ptr(b_ids), _lib.ptr(cell_ids), m, int(W),
-                                       int(stride), int(hc), int(wc), _lib.ptr(out), _lib.ptr(flag), _lib.stream_ptr())
+        fn = _lib.lib().opb200_fine_gather if dtype == torch.float32 else _lib.lib().opb200_fine_gather_bf16
+        st = fn(_lib.ptr(feat), _c_i64(feat.stride(0)), _c_i64(feat.stride(1)), _c_i64(feat.stride(2)),
+                _c_i64(feat.stride(3)), n, cf, hf, wf, _lib.ptr(b_ids), _lib.ptr(cell_ids), m, int(W),
+                int(stride), int(hc), int(wc), _lib.ptr(out), _lib.ptr(flag), _lib.stream_ptr())
     _lib.check(st, "opb200_fine_gather")
     return out
 
@@ -330,8 +334,23 @@ def gather_rows(src_ncl: torch.Tensor, b_ids: torch.Tensor, i_ids: torch.Tensor,
 
 
 def fine_match(q: torch.Tensor, win: torch.Tensor) -> torch.Tensor:
-    """q [M, Cf] (row stride free), win [M, WW, Cf] contiguous -> expec_f [M, 3]."""
+    """q [M, Cf] (row stride free), win [M, WW, Cf] contiguous -> expec_f [M, 3].  bf16 windows (``fine_gather(...,
+    dtype=torch.bfloat16)``) take the bf16 arm: q is rounded to bf16 too, products and sums stay fp32."""
     _need_cuda(q, win)
+    if win.dtype == torch.bfloat16:
+        q, win = q.to(torch.bfloat16), win.contiguous()
+        m, ww, cf = win.shape
+        w = int(round(ww ** 0.5))
+        if q.stride(1) != 1:
+            q = q.contiguous()
+        out = torch.empty(m, 3, dtype=torch.float32, device=win.device)
+        if m == 0:
+            return out
+        with _Stage("fine_match"):
+            st = _lib.lib().opb200_fine_match_bf16(_lib.ptr(q), _c_i64(q.stride(0)), _lib.ptr(win), m, w, cf, _lib.ptr(out),
+                                                   _lib.stream_ptr())
+        _lib.check(st, "opb200_fine_match_bf16")
+        return out
     q, win = _f32(q), _f32(win).contiguous()
     m, ww, cf = win.shape
     w = int(round(ww ** 0.5))
@@ -507,3 +526,24 @@ def coarse_diagnostics(device, n: int, L: int, S: int, C: int, thr: float):
                                ctypes.byref(nc), ctypes.byref(ob), _lib.stream_ptr())
     _lib.check(st, "opb200_coarse_norms")
     return float(na.value), float(nb.value), int(nc.value), float(ob.value)
+
+
+def keypoint_encode(kpts: torch.Tensor, desc: torch.Tensor, packed_w: torch.Tensor, normalize: bool) -> torch.Tensor:
+    """kpts [N, L, 3], desc [N, 256, L] (views allowed), packed_w from KeypointEncoding_linear._packed() -> [N, 256, L]
+    = desc + MLP(normalised kpts)^T (include/opb200.h: opb200_keypoint_encode)."""
+    _need_cuda(kpts, desc, packed_w)
+    kpts, desc = _f32(kpts), _f32(desc)
+    n, L, _ = kpts.shape
+    l = _lib.lib()
+    l.opb200_keypoint_encode_packed_floats.restype = _c_sz
+    if packed_w.numel() != int(l.opb200_keypoint_encode_packed_floats()) or packed_w.dtype != torch.float32:
+        raise _lib.Opb200Error("keypoint_encode: packed weights have the wrong size")
+    out = torch.empty(n, 256, L, dtype=torch.float32, device=kpts.device)
+    stats = torch.empty(4 * n, dtype=torch.float32, device=kpts.device)
+    with _Stage("keypoint_encode"):
+        st = l.opb200_keypoint_encode(_lib.ptr(kpts), _c_i64(kpts.stride(0)), _c_i64(kpts.stride(1)), _c_i64(kpts.stride(2)),
+                                      _lib.ptr(desc), _c_i64(desc.stride(0)), _c_i64(desc.stride(1)), _c_i64(desc.stride(2)),
+                                      _lib.ptr(packed_w), n, L, int(bool(normalize)), _lib.ptr(out), _lib.ptr(stats),
+                                      _lib.stream_ptr())
+    _lib.check(st, "opb200_keypoint_encode")
+    return out

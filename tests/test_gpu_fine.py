@@ -229,3 +229,30 @@ def test_backbone_f16_range_flag_and_fp32_repeat():
         m2(ref)
     assert torch.equal(data["i_ids"], ref["i_ids"]) and torch.equal(data["j_ids"], ref["j_ids"])
     assert torch.equal(data["mconf"], ref["mconf"])
+
+
+@pytest.mark.parametrize("W", [5, 9])
+def test_fine_bf16_arm_tolerance(W):
+    """BASELINE.json configs[4] bf16 arm: bf16 windows / query vectors (half the bytes), fp32 accumulation, against the fp32
+    kernel and an fp64 evaluation of the same planted inputs.  Stated tolerance: expec_f (x, y) < 2e-2 of the window
+    half-width (bf16 keeps 8 significant bits of every feature; the logits of a 128-channel correlation move by ~1e-2)."""
+    from onepose_st_b200 import ops, synthetic
+    q, win, r = synthetic.planted_fine_windows(31, 3000, W, 128, device="cuda")
+    e32 = ops.fine_match(q, win)
+    e16 = ops.fine_match(q.to(torch.bfloat16), win.to(torch.bfloat16))
+    sim = torch.einsum("mc,mrc->mr", q.double(), win.double()) / 128 ** 0.5
+    p = torch.softmax(sim, 1)
+    g = torch.linspace(-1, 1, W, dtype=torch.double, device="cuda")
+    gx, gy = g.repeat(W), g.repeat_interleave(W)
+    ref = torch.stack([(p * gx).sum(1), (p * gy).sum(1)], 1)
+    err32 = (e32[:, :2].double() - ref).abs().max().item()
+    err16 = (e16[:, :2].double() - ref).abs().max().item()
+    print(f"W={W}: expec_f (x, y) max abs err vs fp64: fp32 kernel {err32:.2e}, bf16 arm {err16:.2e}")
+    assert err32 < 1e-4 and err16 < 2e-2
+    # the gather's bf16 output is the rounded fp32 output
+    feat = torch.randn(2, 128, 32, 32, device="cuda")
+    b = torch.randint(0, 2, (50,), device="cuda")
+    j = torch.randint(0, 64, (50,), device="cuda")
+    w32 = ops.fine_gather(feat, b, j, W, 4, 8, 8)
+    w16 = ops.fine_gather(feat, b, j, W, 4, 8, 8, dtype=torch.bfloat16)
+    assert w16.dtype == torch.bfloat16 and torch.equal(w32.to(torch.bfloat16), w16)

@@ -177,3 +177,27 @@ def test_ops_fail_loudly_without_cuda_tensors():
     from onepose_st_b200 import ops, _lib
     with pytest.raises(_lib.Opb200Error):
         ops.fine_match(torch.randn(3, 128), torch.randn(3, 25, 128))
+
+
+def test_keypoint_encoding_kernel_vs_golden(golden):
+    """normalize_3d_keypoints + KeypointEncoding_linear on the fused kernel (csrc/kptenc.cu) against the
+    reference's golden output; both entry points -- the module's forward (keypoints already normalised) and the model's
+    fused route (normalisation inside the kernel, broadcast 3D model included)."""
+    from onepose_st_b200.onepose_plus import KeypointEncoding_linear, normalize_3d_keypoints
+    c = cases.case_kpt_encoding()
+    g = golden("kpt_encoding")
+    enc = KeypointEncoding_linear(3, 256, [32, 64, 128], norm_method="instancenorm")
+    enc.load_state_dict({k[len("kpt_3d_pos_encoding."):]: v for k, v in c["sd"].items()}, strict=True)
+    enc = enc.to(DEV).eval()
+    kp, desc = c["kpts"].to(DEV), c["desc"].to(DEV)
+    with torch.no_grad():
+        assert enc._kernel_ok(kp, desc)
+        a = enc(normalize_3d_keypoints(kp), desc)                  # forward(kpts_normalised, descriptors)
+        b = enc.encode(kp, desc, True)                             # fused normalisation
+        eager = desc + enc.mlp(normalize_3d_keypoints(kp)).transpose(2, 1)
+        one = enc.encode(kp[:1].expand(3, -1, -1), desc[:1].expand(3, -1, -1), True)   # stride-0 batch views
+    for name, t in (("forward", a), ("fused", b), ("eager", eager)):
+        err = (t.cpu() - g["out"]).abs().max().item()
+        print(f"keypoint encoding {name}: max abs err vs golden {err:.2e}")
+        assert err < 2e-5
+    assert (one[2] - b[0]).abs().max().item() < 1e-6 and one.shape == (3, 256, 77)

@@ -111,16 +111,12 @@ def run_transformer(a):
 
 
 def run_fine(a):
+    """BASELINE config 5: fine-level sweep W in {5, 9} x M, fp32 and bf16 arms, error of each against an fp64 evaluation and
+    of the bf16 arm against the fp32 one (the "bf16 vs fp32 tolerance report")."""
     hbm, tf, src = peaks()
     for W in (5, 9):
         for M in a.matches:
             q, win, r = synthetic.planted_fine_windows(31, M, W, device="cuda")
-            ops.stage_events = {}
-            time_op(lambda: ops.fine_match(q, win), a.iters, warmup=0 if a.iters == 1 else 3)
-            evs = ops.stage_events["fine_match"][-a.iters:]
-            ops.stage_events = None
-            dev_ms = sorted(x.elapsed_time(y) for x, y in evs)[len(evs) // 2]
-            got = ops.fine_match(q, win).double()
             # fp64 evaluation of the same formula (torch, on the device) for the error report
             sim = torch.einsum("mc,mrc->mr", q.double(), win.double()) / math.sqrt(128.0)
             heat = torch.softmax(sim, dim=1)
@@ -130,11 +126,26 @@ def run_fine(a):
             vx = (heat @ (gx * gx) - ex * ex).clamp_min(1e-10)
             vy = (heat @ (gy * gy) - ey * ey).clamp_min(1e-10)
             ref = torch.stack([ex, ey, vx.sqrt() + vy.sqrt()], 1)
-            by = M * (4.0 * 128 * (W * W + 1) + 20)
-            print(json.dumps({"op": "fine_match", "W": W, "M": M, "ms_device": dev_ms, "algorithmic_mb": by / 1e6,
-                              "gbs": by / dev_ms / 1e6, "frac_hbm": by / dev_ms / 1e6 / hbm,
-                              "max_abs_err_vs_fp64": (got - ref).abs().max().item(),
-                              "peak": f"{hbm} GB/s ({src})"}), flush=True)
+            del sim, heat
+            got32 = None
+            for dt, nm, bpe in ((torch.float32, "fp32", 4.0), (torch.bfloat16, "bf16", 2.0)):
+                qq, ww = q.to(dt), win.to(dt)
+                ops.stage_events = {}
+                time_op(lambda: ops.fine_match(qq, ww), a.iters, warmup=0 if a.iters == 1 else 3)
+                evs = ops.stage_events["fine_match"][-a.iters:]
+                ops.stage_events = None
+                dev_ms = sorted(x.elapsed_time(y) for x, y in evs)[len(evs) // 2]
+                got = ops.fine_match(qq, ww).double()
+                if got32 is None:
+                    got32 = got
+                by = M * (bpe * 128 * (W * W + 1) + 20)
+                print(json.dumps({"op": "fine_match", "dtype": nm, "W": W, "M": M, "ms_device": dev_ms, "algorithmic_mb": by / 1e6,
+                                  "gbs": by / dev_ms / 1e6, "frac_hbm": by / dev_ms / 1e6 / hbm,
+                                  "max_abs_err_vs_fp64": (got - ref).abs().max().item(),
+                                  "max_abs_err_xy_vs_fp64": (got[:, :2] - ref[:, :2]).abs().max().item(),
+                                  "max_abs_err_vs_fp32_kernel": (got - got32).abs().max().item(),
+                                  "mkpts_err_px_at_scale2": (got[:, :2] - ref[:, :2]).abs().max().item() * (W // 2) * 2,
+                                  "peak": f"{hbm} GB/s ({src})"}), flush=True)
 
 
 def run_loftr(a):
