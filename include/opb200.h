@@ -224,6 +224,19 @@ int opb200_stem_conv7x7_s2_relu_nhwc_f16(const float* image, const float* weight
                                          int H, int W, int Cout, void* out_f16, int* range_flag, void* stream);
 int opb200_upsample2x_add_nhwc_f16(const void* src, int n_batch, int Hs, int Ws, int C, void* dst, void* stream);
 
+/* ---- Feature sampling and aggregation for Keypoint-Free SfM ------------------------------
+ * opb200_sample_features replaces sample_feature_from_featuremap in point mode (src/KeypointFreeSfM/loftr_for_sfm/utils/
+ * sample_feature_from_featuremap.py:28-81; loftr.py:130-166): out[m, c] = grid_sample(feat, kpts[m]) with
+ * align_corners=True and zero padding, bilinear = 0 (nearest, round half to even) or 1; feat is ONE image's map with
+ * element strides (sc, sh, sw) for (channel, row, column); kpts [M, 2] (x, y) in the (scaled) image whose size is
+ * (img_h, img_w); normalize = 1 applies F.normalize(p=2, dim=-1).
+ * opb200_track_feature_mean replaces the per-track np.mean of feature_aggregation_and_update (src/KeypointFreeSfM/
+ * post_optimization/feature_aggregation.py:140-160): rows [R, C] fp32 grouped by track (track t owns rows
+ * track_start[t] .. track_start[t + 1] - 1), out [n_tracks, C] = fp32 sum in row order / count. */
+int opb200_sample_features(const float* feat, int64_t sc, int64_t sh, int64_t sw, int C, int Hf, int Wf, const float* kpts, int M,
+                           float img_h, float img_w, int bilinear, int normalize, float* out, void* stream);
+int opb200_track_feature_mean(const float* rows, const int64_t* track_start, int n_tracks, int C, float* out, void* stream);
+
 /* ---- 3D keypoint position encoding ----------------------------------------------------
  * Replaces normalize_3d_keypoints (src/models/OnePosePlus/utils/normalize.py:17-28) + KeypointEncoding_linear.forward
  * (src/models/OnePosePlus/utils/position_encoding.py:46-79) with keypoints_encoder [32, 64, 128], descriptor_dim 256 and

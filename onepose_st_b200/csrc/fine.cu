@@ -146,11 +146,109 @@ __global__ void __launch_bounds__(128) fine_match_kernel(const InT* __restrict__
   }
 }
 
+// Feature sampling at M sub-pixel keypoints (sample_feature_from_featuremap, point mode: F.grid_sample with
+// align_corners=True and zero padding; src/KeypointFreeSfM/loftr_for_sfm/utils/sample_feature_from_featuremap.py:28-81,
+// called from loftr.py:130-166 with mode "nearest" for the coarse map and "bilinear" for the fine map).  The coordinate
+// arithmetic repeats the reference's fp32 operations one by one (coord_normalization :6-25, then ATen's
+// grid_sampler_unnormalize: ((g + 1) / 2) * (size - 1)); one block per keypoint, one thread per channel.
+__global__ void sample_features_kernel(const float* __restrict__ feat, long long sc, long long sh, long long sw, int C, int Hf,
+                                       int Wf, const float* __restrict__ kpts, int M, float img_h, float img_w, int bilinear,
+                                       int normalize, float* __restrict__ out) {
+  const int m = blockIdx.x;
+  if (m >= M) return;
+  float g[2], px[2];
+  const float res[2] = {__fmul_rn(img_w - 1.f, 1.f), __fmul_rn(img_h - 1.f, 1.f)};
+  const float size1[2] = {static_cast<float>(Wf - 1), static_cast<float>(Hf - 1)};
+#pragma unroll
+  for (int a = 0; a < 2; ++a) {
+    g[a] = __fadd_rn(__fsub_rn(kpts[2 * m + a], 0.5f), 0.5f);             // keypoints - scale / 2 + 0.5, scale = 1
+    g[a] = __fsub_rn(__fmul_rn(__fdiv_rn(g[a], res[a]), 2.f), 1.f);      // / ((w - 1) * scale) * 2 - 1
+    px[a] = __fmul_rn(__fdiv_rn(__fadd_rn(g[a], 1.f), 2.f), size1[a]);   // align_corners=True un-normalisation
+  }
+  __shared__ float red[32];
+  float sq = 0.f;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float* fc = feat + c * sc;
+    float v;
+    if (!bilinear) {
+      const float xr = nearbyintf(px[0]), yr = nearbyintf(px[1]);          // round half to even, as ATen
+      const bool in = xr >= 0.f && xr <= size1[0] && yr >= 0.f && yr <= size1[1];
+      v = in ? __ldg(fc + static_cast<long long>(yr) * sh + static_cast<long long>(xr) * sw) : 0.f;
+    } else {
+      const float x0 = floorf(px[0]), y0 = floorf(px[1]);
+      const float x1 = x0 + 1.f, y1 = y0 + 1.f;
+      const float nw = __fmul_rn(x1 - px[0], y1 - px[1]), ne = __fmul_rn(px[0] - x0, y1 - px[1]);
+      const float sw_ = __fmul_rn(x1 - px[0], px[1] - y0), se = __fmul_rn(px[0] - x0, px[1] - y0);
+      auto at = [&](float x, float y) -> float {
+        return (x >= 0.f && x <= size1[0] && y >= 0.f && y <= size1[1])
+                   ? __ldg(fc + static_cast<long long>(y) * sh + static_cast<long long>(x) * sw) : 0.f;
+      };
+      v = 0.f;
+      v = fmaf(at(x0, y0), nw, v);
+      v = fmaf(at(x1, y0), ne, v);
+      v = fmaf(at(x0, y1), sw_, v);
+      v = fmaf(at(x1, y1), se, v);
+    }
+    out[static_cast<long long>(m) * C + c] = v;
+    sq = fmaf(v, v, sq);
+  }
+  if (!normalize) return;
+  // F.normalize(p=2, dim=-1): v / max(|v|_2, 1e-12)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sq;
+  __syncthreads();
+  float tot = 0.f;
+  for (int w = 0; w < static_cast<int>(blockDim.x + 31) / 32; ++w) tot += red[w];
+  const float inv = 1.f / fmaxf(sqrtf(tot), 1e-12f);
+  for (int c = threadIdx.x; c < C; c += blockDim.x) out[static_cast<long long>(m) * C + c] *= inv;
+}
+
+// Track-wise feature aggregation (feature_aggregation_and_update, src/KeypointFreeSfM/post_optimization/
+// feature_aggregation.py:140-160, aggregation_method "avg"): out[t] = mean of the rows of track t, added one by one in fp32
+// in row order and divided by the count -- the arithmetic of np.mean(stack, axis=0) on float32 rows.
+__global__ void track_mean_kernel(const float* __restrict__ rows, const long long* __restrict__ start, int T, int C,
+                                  float* __restrict__ out) {
+  const int t = blockIdx.x;
+  if (t >= T) return;
+  const long long r0 = start[t], r1 = start[t + 1];
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (long long r = r0; r < r1; ++r) s = __fadd_rn(s, rows[r * C + c]);
+    out[static_cast<long long>(t) * C + c] = r1 > r0 ? __fdiv_rn(s, static_cast<float>(r1 - r0)) : 0.f;
+  }
+}
+
 }  // namespace opb
 
 using namespace opb;
 
 extern "C" {
+
+int opb200_sample_features(const float* feat, int64_t sc, int64_t sh, int64_t sw, int C, int Hf, int Wf, const float* kpts, int M,
+                           float img_h, float img_w, int bilinear, int normalize, float* out, void* stream_) {
+  if (int r = check_device()) return r;
+  if (M <= 0) return OPB_OK;
+  OPB_CHECK_ARG(feat && kpts && out, "null pointer");
+  OPB_CHECK_ARG(C >= 1 && Hf >= 1 && Wf >= 1 && img_h > 1.f && img_w > 1.f, "bad shape");
+  const int threads = C >= 256 ? 256 : (C >= 128 ? 128 : 64);
+  sample_features_kernel<<<M, threads, 0, static_cast<cudaStream_t>(stream_)>>>(feat, sc, sh, sw, C, Hf, Wf, kpts, M, img_h, img_w,
+                                                                                bilinear, normalize, out);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_track_feature_mean(const float* rows, const int64_t* track_start, int n_tracks, int C, float* out, void* stream_) {
+  if (int r = check_device()) return r;
+  if (n_tracks <= 0) return OPB_OK;
+  OPB_CHECK_ARG(rows && track_start && out && C >= 1, "null pointer / bad shape");
+  track_mean_kernel<<<n_tracks, C >= 128 ? 128 : 64, 0, static_cast<cudaStream_t>(stream_)>>>(
+      rows, reinterpret_cast<const long long*>(track_start), n_tracks, C, out);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
 
 int opb200_fine_gather(const float* feat, int64_t sn, int64_t sc, int64_t sh, int64_t sw, int n_batch, int Cf, int Hf,
                        int Wf, const int64_t* b_ids, const int64_t* cell_ids, int M, int W, int stride, int Hc, int Wc,

@@ -171,13 +171,16 @@ class FineMatching(nn.Module):
 def sample_feature_from_featuremap(feature_map, kpts, imghw, norm_feature=False, patch_feature_size=None,
                                    sample_mode="bilinear"):
     """src/KeypointFreeSfM/loftr_for_sfm/utils/sample_feature_from_featuremap.py:28-81, point mode
-    (what loftr.py:130-166 calls).  M-sized grid_sample on the pre-transformer backbone maps (PyTorch)."""
+    (what loftr.py:130-166 calls): M-point sampling of the pre-transformer backbone maps on the own kernel
+    (csrc/fine.cu sample_features_kernel: the reference's fp32 coordinate arithmetic + grid_sample align_corners=True)."""
     if patch_feature_size is not None:
         raise NotImplementedError("patch sampling is not used by the matcher")
     if feature_map.dim() == 4:
         assert feature_map.shape[0] == 1, "batch should to be 1"
     else:
         feature_map = feature_map.unsqueeze(0)
+    if feature_map.is_cuda and sample_mode in ("bilinear", "nearest"):
+        return ops.sample_features(feature_map[0], kpts, float(imghw[0]), float(imghw[1]), sample_mode == "bilinear", norm_feature)
     h, w = imghw[0], imghw[1]
     grid = kpts[None, :, None, :] - 1 / 2 + 0.5
     rescale = torch.stack([(w - 1) * 1, (h - 1) * 1]).to(grid)

@@ -547,3 +547,38 @@ def keypoint_encode(kpts: torch.Tensor, desc: torch.Tensor, packed_w: torch.Tens
                                       _lib.stream_ptr())
     _lib.check(st, "opb200_keypoint_encode")
     return out
+
+
+def sample_features(feature_map: torch.Tensor, kpts: torch.Tensor, img_h: float, img_w: float, bilinear: bool,
+                    normalize: bool = False) -> torch.Tensor:
+    """feature_map [C, H, W] (any strides) sampled at kpts [M, 2] (x, y) given in an image of size (img_h, img_w):
+    F.grid_sample(align_corners=True, zero padding) of the reference's sample_feature_from_featuremap -> [M, C]."""
+    _need_cuda(feature_map, kpts)
+    fm = _f32(feature_map)
+    k = _f32(kpts).contiguous()
+    c, h, w = fm.shape
+    m = int(k.shape[0])
+    out = torch.empty(m, c, dtype=torch.float32, device=fm.device)
+    if m == 0:
+        return out
+    with _Stage("sample_features"):
+        st = _lib.lib().opb200_sample_features(_lib.ptr(fm), _c_i64(fm.stride(0)), _c_i64(fm.stride(1)), _c_i64(fm.stride(2)), c, h, w,
+                                               _lib.ptr(k), m, ctypes.c_float(float(img_h)), ctypes.c_float(float(img_w)),
+                                               int(bool(bilinear)), int(bool(normalize)), _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "opb200_sample_features")
+    return out
+
+
+def track_feature_mean(rows: torch.Tensor, track_start: torch.Tensor) -> torch.Tensor:
+    """rows [R, C] fp32 grouped by track, track_start [T + 1] int64 -> [T, C]: per-track mean with the arithmetic of
+    np.mean(axis=0) on float32 rows (sequential fp32 sum in row order, then one division)."""
+    _need_cuda(rows, track_start)
+    rows = _f32(rows).contiguous()
+    ts = track_start.long().contiguous()
+    t = int(ts.numel()) - 1
+    out = torch.empty(max(t, 0), rows.shape[1], dtype=torch.float32, device=rows.device)
+    if t <= 0:
+        return out
+    st = _lib.lib().opb200_track_feature_mean(_lib.ptr(rows), _lib.ptr(ts), t, int(rows.shape[1]), _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "opb200_track_feature_mean")
+    return out

@@ -256,3 +256,68 @@ def test_fine_bf16_arm_tolerance(W):
     w32 = ops.fine_gather(feat, b, j, W, 4, 8, 8)
     w16 = ops.fine_gather(feat, b, j, W, 4, 8, 8, dtype=torch.bfloat16)
     assert w16.dtype == torch.bfloat16 and torch.equal(w32.to(torch.bfloat16), w16)
+
+
+@pytest.mark.parametrize("mode", ["nearest", "bilinear"])
+def test_sample_features_vs_grid_sample(mode):
+    """the M-point sampling of sample_feature_from_featuremap on the own kernel against the reference's
+    formulation (coord_normalization + F.grid_sample, align_corners=True), channels-first and channels-last maps, points on
+    and beyond the border, optional L2 normalisation."""
+    import torch.nn.functional as F
+    from onepose_st_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(4)
+    C, H, W = (256, 12, 16) if mode == "nearest" else (128, 48, 64)
+    fm = torch.randn(1, C, H, W, device="cuda", generator=g)
+    img_h, img_w = 96.0, 128.0
+    k = torch.rand(500, 2, device="cuda", generator=g) * torch.tensor([img_w + 6, img_h + 6], device="cuda") - 3
+    k[:4] = torch.tensor([[0.0, 0.0], [img_w - 1, img_h - 1], [img_w - 1, 0.0], [63.5, 47.5]], device="cuda")
+    grid = k[None, :, None, :] - 1 / 2 + 0.5
+    rescale = torch.tensor([(img_w - 1) * 1, (img_h - 1) * 1], device="cuda")
+    grid = grid / rescale[None, None, None] * 2 - 1
+    want = F.grid_sample(fm, grid.float(), mode=mode, align_corners=True)[0, :, :, 0].t()
+    for feat in (fm[0], fm.contiguous(memory_format=torch.channels_last)[0]):
+        got = ops.sample_features(feat, k, img_h, img_w, mode == "bilinear")
+        err = (got - want).abs().max().item()
+        print(f"sample_features {mode}: max abs err vs F.grid_sample {err:.2e}")
+        assert err < (1e-6 if mode == "nearest" else 2e-5)
+    gn = ops.sample_features(fm[0], k, img_h, img_w, mode == "bilinear", normalize=True)
+    assert (gn - F.normalize(want, p=2, dim=-1)).abs().max().item() < 1e-5
+
+
+def test_track_feature_mean_is_numpy_mean():
+    """per-track np.mean(stack(features), axis=0) of feature_aggregation_and_update, bit for bit (fp32, row order)."""
+    import numpy as np
+    from onepose_st_b200 import ops
+    rng = np.random.default_rng(2)
+    counts = rng.integers(1, 9, 300)
+    counts[5] = 0
+    start = np.concatenate([[0], np.cumsum(counts)])
+    rows = rng.normal(size=(start[-1], 128)).astype(np.float32)
+    got = ops.track_feature_mean(torch.from_numpy(rows).cuda(), torch.from_numpy(start).cuda()).cpu().numpy()
+    for t in range(len(counts)):
+        if counts[t]:
+            want = np.mean(np.stack([rows[r] for r in range(start[t], start[t + 1])], axis=0), axis=0, keepdims=False)
+            assert np.array_equal(got[t], want), t
+    assert not got[5].any()
+
+
+def test_detector_batched_matching_equals_per_view_loop():
+    """match_query_to_references: all reference views in one LoFTR forward give the matches of the reference's per-view loop."""
+    from onepose_st_b200 import synthetic
+    from onepose_st_b200.detector import match_query_to_references
+    from onepose_st_b200.loftr import LoFTR_for_OnePose_Plus, default_cfg
+    torch.manual_seed(0)
+    m = LoFTR_for_OnePose_Plus(default_cfg, enable_fine_matching=True).eval()
+    m.load_state_dict(synthetic.calibrate_loftr_state_dict(m.state_dict(), 128, 160))
+    m = m.cuda()
+    g = torch.Generator().manual_seed(21)
+    query = torch.rand(1, 1, 128, 160, generator=g).cuda()
+    refs = [(query + 0.02 * torch.randn(query.shape, generator=g).cuda()).clamp(0, 1) for _ in range(5)]
+    refs.append(torch.rand(1, 1, 96, 128, generator=g).cuda())          # a view of another size: its own forward
+    batched = match_query_to_references(m, query, refs)
+    for k, r in enumerate(refs):
+        d = {"image0": r, "image1": query}
+        m(d)
+        assert torch.equal(batched[k]["mkpts0_f"], d["mkpts0_f"]) and torch.equal(batched[k]["mconf"], d["mconf"]), k
+        assert (batched[k]["mkpts1_f"] - d["mkpts1_f"]).abs().max().item() < 1e-4 if len(d["mconf"]) else True
+    assert sum(len(b["mconf"]) for b in batched[:5]) > 50
