@@ -49,7 +49,7 @@ def parse_args():
     ap.add_argument("--repeats", type=int, default=3, help="timed regions of --steps steps per arm (median reported)")
     ap.add_argument("--no-extras", action="store_true", help="skip strong_scaling / gpu_eager_baseline / secondary / parity")
     ap.add_argument("--loftr-pairs", type=int, default=256, help="secondary: LoFTR pairs per rank (0 = skip)")
-    ap.add_argument("--backbone", default="f16", choices=["f16", "fp32"],
+    ap.add_argument("--backbone", default="f16", choices=["f16", "f16x3", "fp32"],
                     help="ResNetFPN_8_2.conv_precision: f16 = own tcgen05 convolutions (default), fp32 = exact cuDNN executor")
     ap.add_argument("--batch", type=int, default=8, help="frames per forward call (dict contract N)")
     ap.add_argument("--pool", type=int, default=500, help="frames of the synthetic sequence")
@@ -129,8 +129,10 @@ def config_dict(args, n_gpus):
             "precision": {"coarse_matching_sweep": "ONE fp16 x fp16 product, fp32 accumulation (screening: bounded by the row norms); "
                                                    "every captured element re-evaluated from the bf16 hi+lo planes in fp32",
                           "encoder_gemms": "bf16x3 split products (fp32-grade)" if args.precision == 3 else "bf16",
-                          "backbone": "fp16 operands, fp32 accumulation (own tcgen05 convolutions)" if args.backbone == "f16"
-                                      else "exact fp32 (cuDNN)",
+                          "backbone": {"f16": "fp16 operands, fp32 accumulation (own tcgen05 convolutions)",
+                                       "f16x3": "split fp16 hi+lo operands, three products, fp32 accumulation (own tcgen05 "
+                                                "convolutions, fp32-grade)",
+                                       "fp32": "exact fp32 (cuDNN)"}[args.backbone],
                           "io": "fp32"},
             "sharding": f"frames round-robin over {n_gpus} GPU(s); one NCCL gather of matches at the end",
             "host_pipeline": f"{args.streams} host threads x CUDA streams per GPU pull frame batches from one queue "
@@ -579,8 +581,9 @@ def run_ours(args):
         value = total_frames / (res["ms"] * 1e-3)
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": res["ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-               "dtype": "fp16 x fp16 -> f32 (CoarseMatching sweep, backbone convolutions) + bf16x3 split -> f32 (encoder GEMMs); f32 I/O"
-               if args.backbone == "f16" else "fp16 x fp16 -> f32 (CoarseMatching sweep) + bf16x3 split -> f32 (encoder GEMMs) + fp32 cuDNN backbone",
+               "dtype": {"f16": "fp16 x fp16 -> f32 (CoarseMatching sweep, backbone convolutions) + bf16x3 split -> f32 (encoder GEMMs); f32 I/O",
+                         "f16x3": "fp16 x fp16 -> f32 (CoarseMatching sweep) + fp16x3 split -> f32 (backbone) + bf16x3 split -> f32 (encoder GEMMs); f32 I/O",
+                         "fp32": "fp16 x fp16 -> f32 (CoarseMatching sweep) + bf16x3 split -> f32 (encoder GEMMs) + fp32 cuDNN backbone"}[args.backbone],
                "data": "synthetic", "config": config_dict(args, world),
                "matches_per_frame": m_per_frame, "gpu_launches": res["launches"], "clocks": res["clocks"],
                "streams": args.streams, "diag": res["diag"],

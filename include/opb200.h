@@ -214,6 +214,17 @@ int opb200_coarse_norms(const void* workspace, int n_batch, int L, int S, int C,
 int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride,
                            int cout_s, const float* bias, const void* res, const void* up, void* y16, float* y32, int act,
                            float slope, int* range_flag, void* stream);
+/* Split-precision variant ("f16x3", fp32-grade): x, w, res, up and y16 hold TWO fp16 planes side by side along the channel
+ * axis, v = hi + lo with hi = rn(v), lo = rn(v - hi) -- x [n, Hi, Wi, 2 * cin_s], w [k*k][cout_s][2 * cin_s],
+ * res / y16 [n, Ho, Wo, 2 * cout_s], up [n, Ho/2, Wo/2, 2 * cout_s] -- and every k-block is issued for the three products
+ * hi*hi, lo*hi, hi*lo (fp32 accumulation in TMEM).  The accumulator is multiplied by acc_scale before bias / residual /
+ * activation: the weights are packed times a power of two (1 / acc_scale) that keeps their lo plane in fp16's normal range.
+ * y32 stays [n, Ho, Wo, cout_s] fp32.  Same tail options and range_flag as above. */
+int opb200_conv2d_nhwc_f16x3(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride,
+                             int cout_s, const float* bias, const void* res, const void* up, void* y16, float* y32, int act,
+                             float slope, float acc_scale, int* range_flag, void* stream);
+/* fp32 NHWC [n_pixels, C] -> fp16 [n_pixels, 2 * C] = [hi | lo] planes (the input format of opb200_conv2d_nhwc_f16x3). */
+int opb200_split_f16_planes(const float* x, long long n_pixels, int C, void* out, int* range_flag, void* stream);
 /* Option of opb200_conv2d_nhwc_f16: run as clusters of two CTAs that multicast the weight slabs to each other (TMA
  * multicast; halves the L2 -> SM weight traffic).  on = 1 / 0 sets it, on < 0 only queries; returns the previous
  * setting.  Default off (no gain measured on B200, see csrc/conv.cu); also settable with OPB200_CONV_CLUSTER=1. */

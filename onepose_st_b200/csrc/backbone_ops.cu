@@ -314,11 +314,52 @@ __global__ void __launch_bounds__(128) stem_tc_kernel(const float* __restrict__ 
   }
 }
 
+// fp32 NHWC [P, C] -> fp16 [P, 2C] = [hi | lo], hi = rn(x), lo = rn(x - hi): the activation format of the split-precision
+// convolutions (conv.cu, terms = 3); 8 channels per thread
+__global__ void __launch_bounds__(256) split_f16_planes_kernel(const float4* __restrict__ x, long long n_vec, int C8,
+                                                               uint4* __restrict__ out, int* __restrict__ range_flag) {
+  float amax = 0.f;
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n_vec; t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long p = t / C8;
+    const int c8 = static_cast<int>(t - p * C8);
+    const float4 a = x[2 * t], b = x[2 * t + 1];
+    const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      amax = fmaxf(fmaxf(amax, fabsf(v[2 * q])), fabsf(v[2 * q + 1]));
+      const __half2 h = __floats2half2_rn(v[2 * q], v[2 * q + 1]);
+      const float2 hf = __half22float2(h);
+      const __half2 l = __floats2half2_rn(v[2 * q] - hf.x, v[2 * q + 1] - hf.y);
+      hi[q] = *reinterpret_cast<const uint32_t*>(&h);
+      lo[q] = *reinterpret_cast<const uint32_t*>(&l);
+    }
+    out[p * 2 * C8 + c8] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    out[p * 2 * C8 + C8 + c8] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  }
+  if (range_flag != nullptr && !(amax <= 65504.f)) atomicOr(range_flag, 1);
+}
+
 }  // namespace opb
 
 using namespace opb;
 
 extern "C" {
+
+int opb200_split_f16_planes(const float* x, long long n_pixels, int C, void* out, int* range_flag, void* stream_) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(x && out, "null pointer");
+  OPB_CHECK_ARG(n_pixels >= 1 && C >= 8 && C % 8 == 0, "bad shape (C must be a multiple of 8)");
+  OPB_CHECK_ARG((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0, "16-byte alignment");
+  const long long n_vec = n_pixels * (C / 8);
+  const long long blocks = (n_vec + 255) / 256;
+  const int grid = static_cast<int>(blocks < num_sms() * 16LL ? blocks : num_sms() * 16LL);
+  split_f16_planes_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(reinterpret_cast<const float4*>(x), n_vec, C / 8,
+                                                                                reinterpret_cast<uint4*>(out), range_flag);
+  count_launch();
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
 
 int opb200_upsample2x_add_nhwc(const float* src, int n_batch, int Hs, int Ws, int C, float* dst, void* stream_) {
   if (int r = check_device()) return r;

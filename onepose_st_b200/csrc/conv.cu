@@ -32,6 +32,11 @@ struct ConvPlan {
   int ksize, pad, stride;
   int nchunks;  // 64-channel chunks per tap
   int nk_last;  // K=16 MMAs in the last chunk (1..4)
+  // Split precision ("f16x3"): activations and weights are stored as two fp16 planes side by side along the channel axis,
+  // x = [hi | lo] with hi = rn(v), lo = rn(v - hi) (22 significant bits together), and every (tap, chunk) k-block is
+  // issued for the three products hi*hi, lo*hi, hi*lo -- fp32-grade convolutions on the fp16 tensor pipe (terms = 3,
+  // plane = channels of one plane); plain fp16 mode: terms = 1.
+  int terms, plane;
   long long* trace;  // debug (opb200_debug_trace): per CTA and tile {first TMA, MMA start, accumulator full, epilogue done}
 };
 
@@ -48,6 +53,10 @@ struct ConvEpi {
   // nullable: bit 0 is set when a value stored as fp16 leaves the fp16 range (|v| > 65504): the caller must not trust
   // this executor's result for these inputs (the host side repeats the backbone in fp32)
   int* range_flag;
+  // split precision: y16 / res / up hold [hi | lo] planes of BN channels each (pixel stride 2 * BN); acc_scale undoes the
+  // power-of-two scaling that keeps the lo plane of the weights in fp16's normal range
+  int split;
+  float acc_scale;
 };
 
 struct UpTaps {  // the four source pixels (element offsets) and weights of one output pixel
@@ -80,25 +89,62 @@ struct ConvCfg {
 };
 
 // 16 accumulator columns of one pixel: bias, residual, activation, stores.
-__device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const ConvEpi& ep, long long off, int c0,
+// 16 fp16 values at p (+ the lo plane BN further on when split) as floats
+template <int BN>
+__device__ __forceinline__ void load16_planes(const __half* p, bool split, float (&f)[16]) {
+  uint32_t h[8];
+  ptx::ld_global_v8(p, h);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&h[i]));
+    f[2 * i] = t.x, f[2 * i + 1] = t.y;
+  }
+  if (split) {
+    ptx::ld_global_v8(p + BN, h);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&h[i]));
+      f[2 * i] += t.x, f[2 * i + 1] += t.y;
+    }
+  }
+}
+
+template <int BN, bool SPLIT>
+__device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const ConvEpi& ep, long long off16, long long off32, int c0,
                                                const UpTaps& ut, float& amax) {
   float v[16];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+  for (int i = 0; i < 16; ++i) v[i] = SPLIT ? __uint_as_float(r[i]) * ep.acc_scale : __uint_as_float(r[i]);
   if (ep.up != nullptr) {
-    uint32_t a[8], b[8], c[8], d[8];
-    ptx::ld_global_v8(ep.up + ut.o00 + c0, a);
-    ptx::ld_global_v8(ep.up + ut.o01 + c0, b);
-    ptx::ld_global_v8(ep.up + ut.o10 + c0, c);
-    ptx::ld_global_v8(ep.up + ut.o11 + c0, d);
+    if constexpr (SPLIT) {  // one source pixel at a time (hi + lo planes): registers
+      float t[16];
+      load16_planes<BN>(ep.up + ut.o00 + c0, true, t);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float2 fa = __half22float2(*reinterpret_cast<const __half2*>(&a[i]));
-      const float2 fb = __half22float2(*reinterpret_cast<const __half2*>(&b[i]));
-      const float2 fc = __half22float2(*reinterpret_cast<const __half2*>(&c[i]));
-      const float2 fd = __half22float2(*reinterpret_cast<const __half2*>(&d[i]));
-      v[2 * i] += ut.w00 * fa.x + ut.w01 * fb.x + ut.w10 * fc.x + ut.w11 * fd.x;
-      v[2 * i + 1] += ut.w00 * fa.y + ut.w01 * fb.y + ut.w10 * fc.y + ut.w11 * fd.y;
+      for (int i = 0; i < 16; ++i) v[i] = fmaf(ut.w00, t[i], v[i]);
+      load16_planes<BN>(ep.up + ut.o01 + c0, true, t);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = fmaf(ut.w01, t[i], v[i]);
+      load16_planes<BN>(ep.up + ut.o10 + c0, true, t);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = fmaf(ut.w10, t[i], v[i]);
+      load16_planes<BN>(ep.up + ut.o11 + c0, true, t);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = fmaf(ut.w11, t[i], v[i]);
+    } else {
+      uint32_t a[8], b[8], c[8], d[8];
+      ptx::ld_global_v8(ep.up + ut.o00 + c0, a);
+      ptx::ld_global_v8(ep.up + ut.o01 + c0, b);
+      ptx::ld_global_v8(ep.up + ut.o10 + c0, c);
+      ptx::ld_global_v8(ep.up + ut.o11 + c0, d);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float2 fa = __half22float2(*reinterpret_cast<const __half2*>(&a[i]));
+        const float2 fb = __half22float2(*reinterpret_cast<const __half2*>(&b[i]));
+        const float2 fc = __half22float2(*reinterpret_cast<const __half2*>(&c[i]));
+        const float2 fd = __half22float2(*reinterpret_cast<const __half2*>(&d[i]));
+        v[2 * i] += ut.w00 * fa.x + ut.w01 * fb.x + ut.w10 * fc.x + ut.w11 * fd.x;
+        v[2 * i + 1] += ut.w00 * fa.y + ut.w01 * fb.y + ut.w10 * fc.y + ut.w11 * fd.y;
+      }
     }
   }
   if (ep.bias != nullptr) {
@@ -110,12 +156,19 @@ __device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const Co
     }
   }
   if (ep.res != nullptr) {
-    uint32_t h[8];
-    ptx::ld_global_v8(ep.res + off + c0, h);
+    if constexpr (SPLIT) {
+      float f[16];
+      load16_planes<BN>(ep.res + off16 + c0, true, f);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&h[i]));
-      v[2 * i] += f.x, v[2 * i + 1] += f.y;
+      for (int i = 0; i < 16; ++i) v[i] += f[i];
+    } else {
+      uint32_t h[8];
+      ptx::ld_global_v8(ep.res + off16 + c0, h);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&h[i]));
+        v[2 * i] += f.x, v[2 * i + 1] += f.y;
+      }
     }
   }
   if (ep.act == 1) {
@@ -133,10 +186,19 @@ __device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const Co
       const __half2 p = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
       h[i] = *reinterpret_cast<const uint32_t*>(&p);
     }
-    ptx::st_global_v8(ep.y16 + off + c0, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+    ptx::st_global_v8(ep.y16 + off16 + c0, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+    if constexpr (SPLIT) {  // lo plane: what the hi plane's rounding left over
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&h[i]));
+        const __half2 p = __floats2half2_rn(v[2 * i] - hi.x, v[2 * i + 1] - hi.y);
+        h[i] = *reinterpret_cast<const uint32_t*>(&p);
+      }
+      ptx::st_global_v8(ep.y16 + off16 + BN + c0, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+    }
   }
   if (ep.y32 != nullptr) {
-    float* d = ep.y32 + off + c0;
+    float* d = ep.y32 + off32 + c0;
 #pragma unroll
     for (int q = 0; q < 2; ++q)
       ptx::st_global_v8(d + 8 * q, __float_as_uint(v[8 * q]), __float_as_uint(v[8 * q + 1]), __float_as_uint(v[8 * q + 2]),
@@ -149,7 +211,7 @@ __device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const Co
 // the weight slab and multicasts it into both CTAs' shared memory, so the L2 -> SM weight traffic per flop halves
 // (the BN = 208 layers are bound by that fill, not by the tensor pipe).  A stage is refilled only after the MMAs of
 // both CTAs have read it (empty barriers count two multicast commits).
-template <int BN, int MSUB, bool CL2>
+template <int BN, int MSUB, bool CL2, bool SPLIT>
 __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant__ ConvPlan plan, const ConvEpi ep) {
   using Cfg = ConvCfg<BN, MSUB>;
   constexpr int STAGES = Cfg::STAGES;
@@ -214,20 +276,23 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
         }
         for (int tap = 0; tap < taps; ++tap) {
           const int ky = tap / plan.ksize, kx = tap - ky * plan.ksize;
-          for (int ch = 0; ch < plan.nchunks; ++ch) {
-            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-            ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-            uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
-            tma_load_4d(sa, &plan.x_map, &full_bar[stage], ch * BLOCK_K, ix0 + kx, iy0 + ky, n);
-            if constexpr (CL2) {
-              ptx::tma_load_2d_multicast(sa + Cfg::A_BYTES + crank * (Cfg::B_BYTES / 2), &plan.w_map, &full_bar[stage],
-                                         ch * BLOCK_K, tap * BN + crank * (BN / 2), 3);
-            } else {
-              ptx::tma_load_2d(sa + Cfg::A_BYTES, &plan.w_map, &full_bar[stage], ch * BLOCK_K, tap * BN);
-            }
-            if (++stage == STAGES) {
-              stage = 0;
-              phase ^= 1;
+          for (int term = 0; term < plan.terms; ++term) {  // hi*hi | lo*hi | hi*lo (plane offsets along the channel axis)
+            const int a0 = term == 1 ? plan.plane : 0, b0 = term == 2 ? plan.plane : 0;
+            for (int ch = 0; ch < plan.nchunks; ++ch) {
+              ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+              ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+              uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+              tma_load_4d(sa, &plan.x_map, &full_bar[stage], a0 + ch * BLOCK_K, ix0 + kx, iy0 + ky, n);
+              if constexpr (CL2) {
+                ptx::tma_load_2d_multicast(sa + Cfg::A_BYTES + crank * (Cfg::B_BYTES / 2), &plan.w_map, &full_bar[stage],
+                                           b0 + ch * BLOCK_K, tap * BN + crank * (BN / 2), 3);
+              } else {
+                ptx::tma_load_2d(sa + Cfg::A_BYTES, &plan.w_map, &full_bar[stage], b0 + ch * BLOCK_K, tap * BN);
+              }
+              if (++stage == STAGES) {
+                stage = 0;
+                phase ^= 1;
+              }
             }
           }
         }
@@ -239,7 +304,7 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
-    const int total_kb = taps * plan.nchunks;
+    const int total_kb = taps * plan.terms * plan.nchunks;
     for (int tq = t_first; tq < plan.num_tiles; tq += t_step, ++it) {
       const int acc = it % Cfg::ACC_STAGES;
       const uint32_t acc_phase = (it / Cfg::ACC_STAGES) & 1;
@@ -299,8 +364,10 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
       const int ty = r / plan.tiles_x, tx = r - ty * plan.tiles_x;
       const int oy = ty * (CONV_TH * MSUB) + sub * CONV_TH + hy, ox = tx * CONV_TW + wx;
       const bool valid = oy < plan.Ho && ox < plan.Wo && !ghost;
-      const long long off = ((static_cast<long long>(n) * plan.Ho + oy) * plan.Wo + ox) * BN;
-      if (valid && ep.res != nullptr) ptx::prefetch_l2(ep.res + off + ch_begin * 16);
+      const long long pix = (static_cast<long long>(n) * plan.Ho + oy) * plan.Wo + ox;
+      constexpr int st16 = SPLIT ? 2 * BN : BN;  // channels per pixel of the fp16 tensors
+      const long long off = pix * BN, off16 = pix * st16;
+      if (valid && ep.res != nullptr) ptx::prefetch_l2(ep.res + off16 + ch_begin * 16);
       UpTaps ut = {};
       if (ep.up != nullptr && valid) {  // torch's align_corners=True source index: src = dst * (in - 1) / (out - 1)
         const int Hs = plan.Ho >> 1, Ws = plan.Wo >> 1;
@@ -309,10 +376,10 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
         const int y1 = y0 + (y0 < Hs - 1), x1 = x0 + (x0 < Ws - 1);
         const float ly1 = sy - y0, lx1 = sx - x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
         const long long base = static_cast<long long>(n) * Hs * Ws;
-        ut.o00 = (base + static_cast<long long>(y0) * Ws + x0) * BN;
-        ut.o01 = (base + static_cast<long long>(y0) * Ws + x1) * BN;
-        ut.o10 = (base + static_cast<long long>(y1) * Ws + x0) * BN;
-        ut.o11 = (base + static_cast<long long>(y1) * Ws + x1) * BN;
+        ut.o00 = (base + static_cast<long long>(y0) * Ws + x0) * st16;
+        ut.o01 = (base + static_cast<long long>(y0) * Ws + x1) * st16;
+        ut.o10 = (base + static_cast<long long>(y1) * Ws + x0) * st16;
+        ut.o11 = (base + static_cast<long long>(y1) * Ws + x1) * st16;
         ut.w00 = ly0 * lx0, ut.w01 = ly0 * lx1, ut.w10 = ly1 * lx0, ut.w11 = ly1 * lx1;
       }
       ptx::mbar_wait(&tfull_bar[acc], acc_phase);
@@ -327,15 +394,15 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
         ptx::tmem_ld16(taddr + c * 16 + 16, r1);
         ptx::tmem_ld_wait();
         if (valid) {
-          conv_epi_chunk(r0, ep, off, c * 16, ut, amax);
-          conv_epi_chunk(r1, ep, off, c * 16 + 16, ut, amax);
+          conv_epi_chunk<BN, SPLIT>(r0, ep, off16, off, c * 16, ut, amax);
+          conv_epi_chunk<BN, SPLIT>(r1, ep, off16, off, c * 16 + 16, ut, amax);
         }
       }
       if (c < ch_end) {
         uint32_t r0[16];
         ptx::tmem_ld16(taddr + c * 16, r0);
         ptx::tmem_ld_wait();
-        if (valid) conv_epi_chunk(r0, ep, off, c * 16, ut, amax);
+        if (valid) conv_epi_chunk<BN, SPLIT>(r0, ep, off16, off, c * 16, ut, amax);
       }
       ptx::tc_fence_before();
       __syncwarp();
@@ -354,10 +421,10 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
   }
 }
 
-template <int BN, int MSUB, bool CL2>
+template <int BN, int MSUB, bool CL2, bool SPLIT = false>
 static int launch_conv(const ConvPlan& plan_in, const ConvEpi& ep, cudaStream_t stream) {
   using Cfg = ConvCfg<BN, MSUB>;
-  auto kern = conv_kernel<BN, MSUB, CL2>;
+  auto kern = conv_kernel<BN, MSUB, CL2, SPLIT>;
   static_assert(Cfg::SMEM <= 227 * 1024, "shared memory budget exceeded");
   static std::atomic<unsigned long long> configured_dev{0};
   if (int r = opt_in_dyn_smem(kern, Cfg::SMEM, configured_dev)) return r;
@@ -440,22 +507,22 @@ static int conv_dispatch(ConvPlan& plan, const ConvEpi& ep, const void* x, int H
   plan.tiles_y = (plan.Ho + msub * CONV_TH - 1) / (msub * CONV_TH);
   plan.num_tiles = plan.n_img * plan.tiles_x * plan.tiles_y;
   // clusters of two CTAs sharing the weight slab pay off once every SM has tiles to walk in lockstep
-  const bool cl2 = conv_use_cluster() && plan.num_tiles >= 2 * num_sms();
+  const bool cl2 = !ep.split && conv_use_cluster() && plan.num_tiles >= 2 * num_sms();
   const uint32_t s = static_cast<uint32_t>(plan.stride);
-  const uint64_t gdim[4] = {static_cast<uint64_t>(cin_s), static_cast<uint64_t>(Wi), static_cast<uint64_t>(Hi),
-                            static_cast<uint64_t>(plan.n_img)};
-  const uint64_t gstr[3] = {static_cast<uint64_t>(cin_s) * 2, static_cast<uint64_t>(cin_s) * 2 * Wi,
-                            static_cast<uint64_t>(cin_s) * 2 * Wi * Hi};
+  const uint64_t cst = static_cast<uint64_t>(cin_s) * (plan.terms == 3 ? 2 : 1);  // channels per pixel in memory
+  const uint64_t gdim[4] = {cst, static_cast<uint64_t>(Wi), static_cast<uint64_t>(Hi), static_cast<uint64_t>(plan.n_img)};
+  const uint64_t gstr[3] = {cst * 2, cst * 2 * Wi, cst * 2 * Wi * Hi};
   const uint32_t box[4] = {BLOCK_K, CONV_TW * s, static_cast<uint32_t>(CONV_TH * msub) * s, 1};
   const uint32_t estr[4] = {1, s, s, 1};
   if (int r = encode_tmap_16bit(&plan.x_map, true, 4, x, gdim, gstr, box, estr)) return r;
   {
-    const uint64_t wdim[2] = {static_cast<uint64_t>(cin_s), static_cast<uint64_t>(plan.ksize) * plan.ksize * BN};
-    const uint64_t wstr[1] = {static_cast<uint64_t>(cin_s) * 2};
+    const uint64_t wdim[2] = {cst, static_cast<uint64_t>(plan.ksize) * plan.ksize * BN};
+    const uint64_t wstr[1] = {cst * 2};
     const uint32_t wbox[2] = {BLOCK_K, static_cast<uint32_t>(cl2 ? BN / 2 : BN)};
     const uint32_t westr[2] = {1, 1};
     if (int r = encode_tmap_16bit(&plan.w_map, true, 2, w, wdim, wstr, wbox, westr)) return r;
   }
+  if (ep.split) return two ? launch_conv<BN, 2, false, true>(plan, ep, stream) : launch_conv<BN, 1, false, true>(plan, ep, stream);
   if (cl2) return two ? launch_conv<BN, 2, true>(plan, ep, stream) : launch_conv<BN, 1, true>(plan, ep, stream);
   return two ? launch_conv<BN, 2, false>(plan, ep, stream) : launch_conv<BN, 1, false>(plan, ep, stream);
 }
@@ -472,9 +539,9 @@ int opb200_conv_cluster(int on) {
   return prev;
 }
 
-int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride, int cout_s,
-                           const float* bias, const void* res, const void* up, void* y16, float* y32, int act, float slope,
-                           int* range_flag, void* stream_) {
+static int conv2d_impl(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride, int cout_s,
+                       const float* bias, const void* res, const void* up, void* y16, float* y32, int act, float slope,
+                       int* range_flag, int split, float acc_scale, void* stream_) {
   if (int r = check_device()) return r;
   OPB_CHECK_ARG(x && w && (y16 || y32), "null pointer");
   OPB_CHECK_ARG(n_img >= 1 && Hi >= 1 && Wi >= 1, "bad shape");
@@ -495,7 +562,11 @@ int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, 
   plan.Wo = (Wi + 2 * plan.pad - ksize) / stride + 1;
   plan.nchunks = (cin_s + BLOCK_K - 1) / BLOCK_K;
   plan.nk_last = (cin_s - (plan.nchunks - 1) * BLOCK_K) / 16;
+  plan.terms = split ? 3 : 1;
+  plan.plane = cin_s;
   ConvEpi ep;
+  ep.split = split ? 1 : 0;
+  ep.acc_scale = acc_scale;
   ep.bias = bias;
   ep.res = static_cast<const __half*>(res);
   ep.y16 = static_cast<__half*>(y16);
@@ -518,6 +589,20 @@ int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, 
     case 208: return conv_dispatch<208>(plan, ep, x, Hi, Wi, cin_s, w, stream);
     default: return conv_dispatch<256>(plan, ep, x, Hi, Wi, cin_s, w, stream);
   }
+}
+
+int opb200_conv2d_nhwc_f16(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride, int cout_s,
+                           const float* bias, const void* res, const void* up, void* y16, float* y32, int act, float slope,
+                           int* range_flag, void* stream) {
+  return conv2d_impl(x, n_img, Hi, Wi, cin_s, w, ksize, stride, cout_s, bias, res, up, y16, y32, act, slope, range_flag, 0, 1.f, stream);
+}
+
+int opb200_conv2d_nhwc_f16x3(const void* x, int n_img, int Hi, int Wi, int cin_s, const void* w, int ksize, int stride, int cout_s,
+                             const float* bias, const void* res, const void* up, void* y16, float* y32, int act, float slope,
+                             float acc_scale, int* range_flag, void* stream) {
+  OPB_CHECK_ARG(acc_scale > 0.f, "acc_scale must be positive");
+  return conv2d_impl(x, n_img, Hi, Wi, cin_s, w, ksize, stride, cout_s, bias, res, up, y16, y32, act, slope, range_flag, 1, acc_scale,
+                     stream);
 }
 
 }  // extern "C"

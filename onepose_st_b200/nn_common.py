@@ -84,7 +84,7 @@ class ResNetFPN_8_2(nn.Module):
         receives bit 0 when the fp16 executor had to store a value outside the fp16 range (see ``conv_precision``)."""
         if x.is_cuda and not self.training and not torch.is_grad_enabled():
             fb = self.fused(_precision)
-            return fb(x, _range_flag) if isinstance(fb, FusedBackboneF16) else fb(x)
+            return fb(x, _range_flag) if isinstance(fb, (FusedBackboneF16, FusedBackboneF16x3)) else fb(x)
         x1 = self.layer1(self.relu(self.bn1(self.conv1(x))))
         x2 = self.layer2(x1)
         x3 = self.layer3(x2)
@@ -99,6 +99,9 @@ class ResNetFPN_8_2(nn.Module):
     #          significand of the TF32 operands the reference's cuDNN convolutions use on a GPU, but fp16's exponent
     #          range (|x| <= 65504).  The kernels flag any stored value that leaves that range and the matchers then
     #          repeat the backbone with "fp32" for that call (OnePosePlus_model / LoFTR_for_OnePose_Plus.forward).
+    #   "f16x3" the same kernels on split operands ([hi | lo] fp16 planes, three products per k-block): fp32-grade feature
+    #          maps on own kernels at ~3x the convolution time -- the configuration in which the whole forward holds the
+    #          fp32 contract without library code (bench.py --backbone f16x3).
     #   "fp32" exact-fp32 cuDNN executor (library code; what the fp32-grade parity tests select).
     conv_precision = "f16"
 
@@ -106,9 +109,9 @@ class ResNetFPN_8_2(nn.Module):
         """Inference executor (BN folded into the convolutions, NHWC): ``FusedBackboneF16`` (own tcgen05 implicit-GEMM
         convolutions) or ``FusedBackbone`` (cuDNN fp32); rebuilt whenever a parameter or buffer changes."""
         precision = precision or self.conv_precision
-        if precision not in ("f16", "fp32"):
-            raise ValueError(f"conv_precision must be 'f16' or 'fp32', got {precision!r}")
-        f16 = precision == "f16" and FusedBackboneF16.supports(self)
+        if precision not in ("f16", "f16x3", "fp32"):
+            raise ValueError(f"conv_precision must be 'f16', 'f16x3' or 'fp32', got {precision!r}")
+        f16 = precision if (precision != "fp32" and FusedBackboneF16.supports(self)) else False
         key = tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers()))
         cache = self.__dict__.setdefault("_fused_cache", {})
         fb = cache.get(f16)
@@ -116,7 +119,7 @@ class ResNetFPN_8_2(nn.Module):
             with _cache_lock:
                 fb = cache.get(f16)
                 if fb is None or fb[0] != key:
-                    fb = (key, FusedBackboneF16(self) if f16 else FusedBackbone(self))
+                    fb = (key, FusedBackboneF16x3(self) if f16 == "f16x3" else (FusedBackboneF16(self) if f16 else FusedBackbone(self)))
                     dev = self.conv1.weight.device
                     if dev.type == "cuda":
                         torch.cuda.current_stream(dev).synchronize()  # folded weights are read from other streams too
@@ -160,6 +163,29 @@ def pack_conv_f16(w: torch.Tensor, b: Optional[torch.Tensor]):
         bp = torch.zeros(cout_s, dtype=torch.float32, device=w.device)
         bp[:cout] = b.detach().float()
     return wp.reshape(k * k * cout_s, cin_s).half().contiguous(), bp
+
+
+def pack_conv_f16x3(w: torch.Tensor, b: Optional[torch.Tensor]):
+    """Split-precision packing: [Cout, Cin, k, k] fp32 -> ([k*k*Cout_s, 2*Cin_s] fp16 = [hi | lo] planes of s*w, bias,
+    s) with s the largest power of two keeping max|s*w| <= 1024 (so that the lo plane, ~2^-11 of the hi plane, stays in
+    fp16's normal range for all but negligible weights; the kernel multiplies the accumulator by 1/s)."""
+    cout, cin, k, _ = w.shape
+    cin_s, cout_s = _cs(cin), _cs(cout)
+    wf = w.detach().float()
+    wmax = float(wf.abs().max().item())
+    s = 2.0 ** math.floor(math.log2(1024.0 / wmax)) if wmax > 0 else 1.0
+    s = min(max(s, 2.0 ** -10), 2.0 ** 20)
+    ws = (wf * s).permute(2, 3, 0, 1).reshape(k * k, cout, cin)
+    hi = ws.half()
+    lo = (ws - hi.float()).half()
+    wp = torch.zeros(k * k, cout_s, 2 * cin_s, dtype=torch.float16, device=w.device)
+    wp[:, :cout, :cin] = hi
+    wp[:, :cout, cin_s: cin_s + cin] = lo
+    bp = None
+    if b is not None:
+        bp = torch.zeros(cout_s, dtype=torch.float32, device=w.device)
+        bp[:cout] = b.detach().float()
+    return wp.reshape(k * k * cout_s, 2 * cin_s).contiguous(), bp, s
 
 
 class FusedBackbone:
@@ -289,6 +315,69 @@ class FusedBackboneF16:
         l2 = ops.conv2d_nhwc_f16(x2, self.l2_out[0], 1, 1, self.l2_out[1], None, 0, up=c3_16, range_flag=rf)
         c2 = self._head(l2, self.head2, False, rf)
         l1 = ops.conv2d_nhwc_f16(x1, self.l1_out[0], 1, 1, self.l1_out[1], None, 0, up=c2, range_flag=rf)
+        c1 = self._head(l1, self.head1, True, rf)
+        return c3.permute(0, 3, 1, 2), c1.permute(0, 3, 1, 2)
+
+
+class FusedBackboneF16x3:
+    """Inference-only executor of a ``ResNetFPN_8_2`` on the SPLIT-PRECISION tcgen05 convolutions (csrc/conv.cu, terms = 3):
+    every activation and weight travels as two fp16 planes [hi | lo] (22 significant bits) and each k-block is issued for
+    hi*hi + lo*hi + hi*lo with fp32 accumulation -- fp32-grade feature maps on own kernels (conv_precision = "f16x3"), at
+    three times the tensor work and twice the activation traffic of "f16".  The 7x7 stem runs on the exact fp32 CUDA-core
+    kernel and is split once; the rest mirrors ``FusedBackboneF16``."""
+
+    supports = staticmethod(lambda m: FusedBackboneF16.supports(m))
+
+    def __init__(self, m: "ResNetFPN_8_2"):
+        w, b = _fold_bn(m.conv1, m.bn1)
+        self.stem = (w.reshape(128, 49).t().contiguous(), b)
+        pk = lambda conv, bn: pack_conv_f16x3(*_fold_bn(conv, bn)) if (bn is not None or conv.bias is not None) \
+            else pack_conv_f16x3(conv.weight, None)
+        self.blocks = []
+        for layer in (m.layer1, m.layer2, m.layer3):
+            for blk in layer:
+                ds = pk(blk.downsample[0], blk.downsample[1]) if blk.downsample is not None else None
+                self.blocks.append((pk(blk.conv1, blk.bn1), pk(blk.conv2, blk.bn2), ds, blk.conv1.stride[0]))
+        self.l3_out, self.l2_out, self.l1_out = pk(m.layer3_outconv, None), pk(m.layer2_outconv, None), pk(m.layer1_outconv, None)
+        self.head2 = (pk(m.layer2_outconv2[0], m.layer2_outconv2[1]), pk(m.layer2_outconv2[3], None),
+                      m.layer2_outconv2[2].negative_slope)
+        self.head1 = (pk(m.layer1_outconv2[0], m.layer1_outconv2[1]), pk(m.layer1_outconv2[3], None),
+                      m.layer1_outconv2[2].negative_slope)
+
+    @staticmethod
+    def _conv(x, p, k, stride, res, act, rf, slope=0.0, up=None, out_f16=True, out_f32=False):
+        w, b, s = p
+        return ops.conv2d_nhwc_f16(x, w, k, stride, b, res, act, slope, out_f16=out_f16, out_f32=out_f32, up=up, range_flag=rf,
+                                   split_scale=s)
+
+    def _block(self, x, blk, rf):
+        c1, c2, ds, stride = blk
+        y = self._conv(x, c1, 3, stride, None, 1, rf)
+        if ds is not None:
+            x = self._conv(x, ds, 1, stride, None, 0, rf)
+        return self._conv(y, c2, 3, 1, x, 1, rf)
+
+    def _head(self, x, head, out_f32, rf):
+        c0, c1, slope = head
+        y = self._conv(x, c0, 3, 1, None, 2, rf, slope)
+        return self._conv(y, c1, 3, 1, None, 0, rf, out_f16=not out_f32, out_f32=out_f32)
+
+    def __call__(self, x, range_flag: Optional[torch.Tensor] = None):
+        if x.shape[2] % 8 or x.shape[3] % 8:
+            raise NotImplementedError("ResNetFPN_8_2 on CUDA needs image sides that are multiples of 8")
+        rf = range_flag
+        s32 = ops.stem_conv_relu(x, self.stem[0], self.stem[1])                       # [N,128,Ho,Wo] channels-last fp32
+        x = ops.split_f16_planes(s32.permute(0, 2, 3, 1), rf)                          # NHWC view -> [hi | lo] fp16
+        feats = []
+        for i, blk in enumerate(self.blocks):
+            x = self._block(x, blk, rf)
+            if i % 2 == 1:
+                feats.append(x)
+        x1, x2, x3 = feats
+        c3_16, c3 = self._conv(x3, self.l3_out, 1, 1, None, 0, rf, out_f16=True, out_f32=True)
+        l2 = self._conv(x2, self.l2_out, 1, 1, None, 0, rf, up=c3_16)
+        c2 = self._head(l2, self.head2, False, rf)
+        l1 = self._conv(x1, self.l1_out, 1, 1, None, 0, rf, up=c2)
         c1 = self._head(l1, self.head1, True, rf)
         return c3.permute(0, 3, 1, 2), c1.permute(0, 3, 1, 2)
 

@@ -442,33 +442,46 @@ def linear_attention(q, k, v, q_mask=None, kv_mask=None, eps: float = 1e-6) -> t
 def conv2d_nhwc_f16(x: torch.Tensor, w: torch.Tensor, ksize: int, stride: int = 1, bias: Optional[torch.Tensor] = None,
                     res: Optional[torch.Tensor] = None, act: int = 0, slope: float = 0.0, out_f16: bool = True,
                     out_f32: bool = False, stage: str = "backbone_conv", up: Optional[torch.Tensor] = None,
-                    range_flag: Optional[torch.Tensor] = None):
+                    range_flag: Optional[torch.Tensor] = None, split_scale: Optional[float] = None):
     """y = act(conv_k(x) + bias + res): x [N,Hi,Wi,Cin_s] fp16, w [k*k*Cout_s, Cin_s] fp16 tap-major, bias [Cout_s] fp32,
     res [N,Ho,Wo,Cout_s] fp16, up [N,Ho/2,Wo/2,Cout_s] fp16 (bilinear x2, align_corners=True, added before act).  Returns the
     fp16 output, the fp32 output, or (fp16, fp32) when both are asked.  ``range_flag`` (int32 [1], optional): bit 0 is set
-    by the kernel when a value leaves the fp16 range on its way into the fp16 output."""
+    by the kernel when a value leaves the fp16 range on its way into the fp16 output.
+    ``split_scale`` (float, optional) selects the split-precision kernel (opb200_conv2d_nhwc_f16x3): every fp16 tensor then
+    carries [hi | lo] planes along its last axis (x [N,Hi,Wi,2*Cin_s], w [k*k*Cout_s, 2*Cin_s], res / up / fp16 output
+    [.., 2*Cout_s]) and ``split_scale`` is the power of two the packed weights were multiplied by."""
     _need_cuda(x, w, bias, res)
     if x.dtype != torch.float16 or w.dtype != torch.float16 or not x.is_contiguous() or not w.is_contiguous() or x.dim() != 4:
         raise _lib.Opb200Error("conv2d_nhwc_f16: contiguous fp16 [N,H,W,C] input and fp16 weights required")
     n, hi, wi, cin_s = x.shape
-    if w.dim() != 2 or w.shape[1] != cin_s or w.shape[0] % (ksize * ksize):
+    planes = 1 if split_scale is None else 2
+    if cin_s % planes:
+        raise _lib.Opb200Error("conv2d_nhwc_f16: split input needs an even channel count ([hi | lo])")
+    cin_s //= planes
+    if w.dim() != 2 or w.shape[1] != planes * cin_s or w.shape[0] % (ksize * ksize):
         raise _lib.Opb200Error(f"conv2d_nhwc_f16: weight shape {tuple(w.shape)} does not fit k={ksize}, Cin_s={cin_s}")
     cout_s = w.shape[0] // (ksize * ksize)
     pad = ksize // 2
     ho, wo = (hi + 2 * pad - ksize) // stride + 1, (wi + 2 * pad - ksize) // stride + 1
-    if res is not None and (res.dtype != torch.float16 or tuple(res.shape) != (n, ho, wo, cout_s) or not res.is_contiguous()):
+    if res is not None and (res.dtype != torch.float16 or tuple(res.shape) != (n, ho, wo, planes * cout_s) or not res.is_contiguous()):
         raise _lib.Opb200Error("conv2d_nhwc_f16: residual must be contiguous fp16 [N,Ho,Wo,Cout_s]")
     if up is not None and (up.dtype != torch.float16 or not up.is_contiguous() or ho % 2 or wo % 2
-                           or tuple(up.shape) != (n, ho // 2, wo // 2, cout_s)):
+                           or tuple(up.shape) != (n, ho // 2, wo // 2, planes * cout_s)):
         raise _lib.Opb200Error("conv2d_nhwc_f16: up must be contiguous fp16 [N,Ho/2,Wo/2,Cout_s]")
     if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout_s):
         raise _lib.Opb200Error("conv2d_nhwc_f16: bias must be fp32 [Cout_s]")
-    y16 = torch.empty(n, ho, wo, cout_s, dtype=torch.float16, device=x.device) if out_f16 else None
+    y16 = torch.empty(n, ho, wo, planes * cout_s, dtype=torch.float16, device=x.device) if out_f16 else None
     y32 = torch.empty(n, ho, wo, cout_s, dtype=torch.float32, device=x.device) if out_f32 else None
     with _Stage(stage):
-        st = _lib.lib().opb200_conv2d_nhwc_f16(_lib.ptr(x), n, hi, wi, cin_s, _lib.ptr(w), ksize, stride, cout_s, _lib.ptr(bias),
-                                               _lib.ptr(res), _lib.ptr(up), _lib.ptr(y16), _lib.ptr(y32), act, ctypes.c_float(slope),
-                                               _lib.ptr(range_flag), _lib.stream_ptr())
+        if split_scale is None:
+            st = _lib.lib().opb200_conv2d_nhwc_f16(_lib.ptr(x), n, hi, wi, cin_s, _lib.ptr(w), ksize, stride, cout_s, _lib.ptr(bias),
+                                                   _lib.ptr(res), _lib.ptr(up), _lib.ptr(y16), _lib.ptr(y32), act,
+                                                   ctypes.c_float(slope), _lib.ptr(range_flag), _lib.stream_ptr())
+        else:
+            st = _lib.lib().opb200_conv2d_nhwc_f16x3(_lib.ptr(x), n, hi, wi, cin_s, _lib.ptr(w), ksize, stride, cout_s,
+                                                     _lib.ptr(bias), _lib.ptr(res), _lib.ptr(up), _lib.ptr(y16), _lib.ptr(y32), act,
+                                                     ctypes.c_float(slope), ctypes.c_float(1.0 / split_scale),
+                                                     _lib.ptr(range_flag), _lib.stream_ptr())
     _lib.check(st, "opb200_conv2d_nhwc_f16")
     if out_f16 and out_f32:
         return y16, y32
@@ -581,4 +594,18 @@ def track_feature_mean(rows: torch.Tensor, track_start: torch.Tensor) -> torch.T
         return out
     st = _lib.lib().opb200_track_feature_mean(_lib.ptr(rows), _lib.ptr(ts), t, int(rows.shape[1]), _lib.ptr(out), _lib.stream_ptr())
     _lib.check(st, "opb200_track_feature_mean")
+    return out
+
+
+def split_f16_planes(x_nhwc: torch.Tensor, range_flag: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp32 [N,H,W,C] contiguous -> fp16 [N,H,W,2C] = [hi | lo] planes (input format of the split-precision convolutions)."""
+    _need_cuda(x_nhwc)
+    if x_nhwc.dtype != torch.float32 or not x_nhwc.is_contiguous() or x_nhwc.dim() != 4 or x_nhwc.shape[3] % 8:
+        raise _lib.Opb200Error("split_f16_planes: contiguous fp32 [N,H,W,C] with C % 8 == 0 required")
+    n, h, w, c = x_nhwc.shape
+    out = torch.empty(n, h, w, 2 * c, dtype=torch.float16, device=x_nhwc.device)
+    with _Stage("backbone_glue"):
+        st = _lib.lib().opb200_split_f16_planes(_lib.ptr(x_nhwc), ctypes.c_longlong(n * h * w), c, _lib.ptr(out), _lib.ptr(range_flag),
+                                                _lib.stream_ptr())
+    _lib.check(st, "opb200_split_f16_planes")
     return out

@@ -144,3 +144,70 @@ def test_conv_cluster_multicast_option_is_bit_identical():
         finally:
             lib.opb200_conv_cluster(prev)
         assert torch.equal(plain, clustered)
+
+
+@pytest.mark.parametrize("n,H,W,cin,cout,k,stride,use_res", [(2, 32, 48, 128, 128, 3, 1, True), (1, 40, 24, 128, 196, 3, 2, False),
+                                                            (1, 24, 24, 196, 256, 1, 2, False), (2, 16, 16, 256, 256, 3, 1, True)])
+def test_conv_split_precision_is_fp32_grade(n, H, W, cin, cout, k, stride, use_res):
+    """Split-precision convolution (opb200_conv2d_nhwc_f16x3: [hi | lo] fp16 planes, three products) against torch fp32 on the
+    SAME fp32 inputs -- no pre-rounding of the reference's operands: the error must be fp32-grade (~1e-6 relative), three
+    orders below the single-product fp16 kernel's."""
+    from onepose_st_b200 import ops
+    from onepose_st_b200.nn_common import pack_conv_f16x3, pack_conv_f16, _cs
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        g = torch.Generator(device="cuda").manual_seed(77 + cin + cout)
+        cin_s, cout_s = _cs(cin), _cs(cout)
+        x = torch.randn(n, H, W, cin, device="cuda", generator=g)
+        w = torch.randn(cout, cin, k, k, device="cuda", generator=g) / (cin * k * k) ** 0.5
+        b = torch.randn(cout, device="cuda", generator=g)
+        xs = torch.zeros(n, H, W, cin_s, device="cuda")
+        xs[..., :cin] = x
+        x2 = ops.split_f16_planes(xs)
+        assert (x2[..., :cin_s].float() + x2[..., cin_s:].float() - xs).abs().max().item() < 1e-6
+        wp, bp, s = pack_conv_f16x3(w, b)
+        Ho, Wo = (H + 2 * (k // 2) - k) // stride + 1, (W + 2 * (k // 2) - k) // stride + 1
+        res2 = None
+        want = F.conv2d(x.permute(0, 3, 1, 2), w, b, stride, k // 2).permute(0, 2, 3, 1)
+        if use_res:
+            r = torch.zeros(n, Ho, Wo, cout_s, device="cuda")
+            r[..., :cout] = torch.randn(n, Ho, Wo, cout, device="cuda", generator=g)
+            res2 = ops.split_f16_planes(r)
+            want = want + r[..., :cout]
+        want = F.relu(want)
+        y16, y32 = ops.conv2d_nhwc_f16(x2, wp, k, stride, bp, res2, 1, out_f16=True, out_f32=True, split_scale=s)
+        err = (y32[..., :cout] - want).abs().max().item() / want.abs().max().item()
+        rec = (y16[..., :cout_s].float() + y16[..., cout_s:].float() - y32).abs().max().item()
+        # the single-product kernel on the same inputs, for scale
+        wp1, bp1 = pack_conv_f16(w, b)
+        y1 = ops.conv2d_nhwc_f16(xs.half(), wp1, k, stride, bp1, None if res2 is None else r.half(), 1, out_f16=False, out_f32=True)
+        err1 = (y1[..., :cout] - want).abs().max().item() / want.abs().max().item()
+        print(f"conv {cin}->{cout} k{k} s{stride}: split rel err {err:.2e} (single fp16 product {err1:.2e}), hi+lo reconstruction {rec:.2e}")
+        assert err < 5e-6 and rec < 2e-6 * max(1.0, want.abs().max().item())
+        if cout_s > cout:
+            assert (y32[..., cout:] == 0).all() and (y16[..., cout:cout_s] == 0).all()
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+
+
+def test_backbone_split_precision_vs_golden(golden):
+    """conv_precision='f16x3': the whole ResNetFPN_8_2 on the own split-precision convolutions against the reference's fp32
+    golden maps -- fp32-grade (the same bound the cuDNN fp32 executor is held to)."""
+    import cases
+    from onepose_st_b200.nn_common import ResNetFPN_8_2, FusedBackboneF16x3
+    c = cases.case_backbone()
+    m = ResNetFPN_8_2({"block_type": "BasicBlock", "initial_dim": 128, "block_dims": [128, 196, 256]})
+    m.load_state_dict({k[len("backbone."):]: v for k, v in c["sd"].items()}, strict=True)
+    m = m.cuda().eval()
+    m.conv_precision = "f16x3"
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    with torch.no_grad():
+        assert isinstance(m.fused(), FusedBackboneF16x3)
+        fc, ff = m(c["image"].cuda(), _range_flag=flag)
+    g = golden("backbone")
+    gc, gf = g["feat_c"], g["feat_f_sub"]
+    ec = (fc.cpu() - gc).abs().max().item() / gc.abs().max().item()
+    ef = (ff.cpu()[:, ::8, ::4, ::4] - gf).abs().max().item() / gf.abs().max().item()
+    print(f"split-precision backbone rel err coarse {ec:.2e} fine {ef:.2e}")
+    assert int(flag.item()) == 0 and ec < 1e-4 and ef < 1e-4
