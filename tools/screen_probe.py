@@ -74,6 +74,24 @@ def main():
                           "set_diff_max_dist_to_thr": marg, "mconf_err_vs_two_pass": e2, "mconf_err_vs_fp64_frame0": e64,
                           "norms_candidates": diag, "ms_per_call_launch_only": e0.elapsed_time(e1) / 10}))
     ops.coarse_screen_max_delta(0.75)
+    # the sweep kernel by itself (event bracket inside opb200_coarse_match), default kernel vs the register-buffered variant
+    from onepose_st_b200 import _lib
+    for algo in (0, 3, 2):
+        _lib.coarse_kernel_timing(True)
+        for _ in range(3):
+            ops.coarse_match_launch(f3d, f2d, algo=algo, **kw)
+        torch.cuda.synchronize()
+        _lib.coarse_kernel_ms()
+        for _ in range(20):
+            h = ops.coarse_match_launch(f3d, f2d, algo=algo, **kw)
+        torch.cuda.synchronize()
+        ms, n = _lib.coarse_kernel_ms()
+        _lib.coarse_kernel_timing(False)
+        out = ops.coarse_match_finish(h)
+        diag = ops.coarse_diagnostics(dev, N, L, S, 256, thr)
+        fl = 2.0 * N * L * S * 256
+        print(json.dumps({"algo": algo, "sweep_kernel_us": 1e3 * ms / max(n, 1), "launches": n, "tflops": fl / (ms / max(n, 1) * 1e-3) / 1e12,
+                          "M": int(out[0].shape[0]), "candidates": diag[2], "observed_err": diag[3]}))
 
 
 if __name__ == "__main__":
