@@ -183,8 +183,8 @@ int opb200_stem_conv7x7_s2_relu_nhwc(const float* image, const float* weight_tap
 int opb200_bias_leaky_relu_nhwc(float* x, const float* bias, long long n_pixels, int C, float slope, void* stream);
 
 /* Screening sweep of the default single-pass CoarseMatching: the largest bound delta (octaves) on the fp16 similarity error,
- * c * 2^-10 * max|a_i| * max|b_j|, up to which the sweep is allowed to run on ONE fp16 product (default 0.75; beyond it,
- * or when the exact re-evaluation of the captured elements measures an error above 0.05 octave, the call asks for the
+ * c * 2^-10 * max|a_i| * max|b_j|, up to which the sweep is allowed to run on ONE fp16 product (default 0.6; beyond it,
+ * or when the exact re-evaluation of the captured elements measures an error above 0.03 octave, the call asks for the
  * repeat on the three split products).  max_delta < 0 only queries.  Returns the previous value. */
 float opb200_coarse_screen_max_delta(float max_delta);
 /* Diagnostics of the last default-path call that used ``workspace`` (synchronises the stream): the largest row norms the

@@ -342,11 +342,11 @@ struct FastCfg {
 // 2^delta - 1, a match's confidence moves by at most ~0.2 of the relative error of that remainder, and the remainder
 // of a row that holds a match consists of at least 1 / thr_lim terms; screening is therefore only used while
 // delta <= kScreenMaxDelta (0.25 octave), beyond which the call is repeated on the three split products (algo 2).
-constexpr float kScreenMaxDelta = 0.75f;
+constexpr float kScreenMaxDelta = 0.6f;
 // ... and the sweep checks its own work: every captured element is evaluated twice (screening value, exact value); the
 // largest difference seen is the measured counterpart of the bound, and a call whose measured error exceeds
 // kScreenMaxObserved octaves is repeated on the split products as well.
-constexpr float kScreenMaxObserved = 0.05f;
+constexpr float kScreenMaxObserved = 0.03f;
 constexpr float kScreenMaxNorm = 60000.f;  // |x| <= |row| must stay below the largest fp16 (65504)
 struct ScreenPlan {
   bool ok;

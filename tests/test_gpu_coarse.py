@@ -223,7 +223,7 @@ def test_screening_is_sound_for_scaled_features(k):
     """VERDICT r1 weak #1.  The error of the fp16 screening product grows with c * |a| * |b|, not with max|x|: features
     scaled by k at a fixed temperature.  The default call (algo 0) must give the fp64 dual-softmax's matches outside a
     1e-3 band and its confidences within 1e-3 at every scale -- by screening with a margin derived from the row norms
-    while the bound allows it (delta <= 0.75 octave: k <= 4 here), by repeating on the three split products beyond."""
+    while the bound allows it (delta <= 0.6 octave: k <= 4 here), by repeating on the three split products beyond."""
     from onepose_st_b200 import ops
     dev = "cuda"
     hw = (16, 16)
@@ -322,4 +322,4 @@ def test_bench_shape_default_path_vs_two_pass():
             worst = max(worst, abs(conf[ii, jj].item() - fi[(bb, ii, jj)]))
     err = max(abs(fi[k_] - ai[k_]) for k_ in got & want)
     print(f"bench shape: M={len(got)}, set diff vs two-pass {len(got ^ want)}, mconf vs two-pass {err:.2e}, vs fp64 {worst:.2e}")
-    assert len(got) > 6000 and len(got ^ want) <= 4 and err < CONF_TOL and worst < CONF_TOL
+    assert len(got) > 4000 and len(got ^ want) <= 4 and err < CONF_TOL and worst < CONF_TOL

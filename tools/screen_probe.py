@@ -52,7 +52,7 @@ def main():
     big = conf64 > 0.01
     print(json.dumps({"fp16_product_err_octaves": {"max_all": err.max().item(), "rms_all": err.pow(2).mean().sqrt().item(),
                                                    "max_where_conf_gt_0.01": err[big].max().item(), "n_conf_gt_0.01": int(big.sum())}}))
-    for md in (0.25, 0.75, 2.0):
+    for md in (0.25, 0.6, 2.0):
         ops.coarse_screen_max_delta(md)
         info = {}
         out = ops.coarse_match(f3d, f2d, _info=info, **kw)
@@ -73,7 +73,7 @@ def main():
         print(json.dumps({"max_delta": md, "rerun": info["rerun"], "M": len(got), "set_diff_vs_two_pass": len(diff),
                           "set_diff_max_dist_to_thr": marg, "mconf_err_vs_two_pass": e2, "mconf_err_vs_fp64_frame0": e64,
                           "norms_candidates": diag, "ms_per_call_launch_only": e0.elapsed_time(e1) / 10}))
-    ops.coarse_screen_max_delta(0.75)
+    ops.coarse_screen_max_delta(0.6)
     # the sweep kernel by itself (event bracket inside opb200_coarse_match), default kernel vs the register-buffered variant
     from onepose_st_b200 import _lib
     for algo in (0, 3, 2):
