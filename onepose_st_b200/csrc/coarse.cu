@@ -1426,24 +1426,25 @@ struct PackSide {
 // has seen a single column:  sum_j 2^(y_ij) >= S 2^(mean_j y_ij) = S 2^(c a_i . mean_j b_j)  (Jensen).  For the rows
 // that hold no match -- nearly all of them -- this bound is within a small factor of the sum, which keeps the first
 // column tiles of a row block from flooding the candidate list (their own partial sum is a poor bound).
-constexpr int MEAN_CHUNKS = 16;
+constexpr int MEAN_CHUNKS = 128;  // 32 rows per block at S = 4096: the loads of a thread are few and all in flight
 __global__ void __launch_bounds__(256) colmean_kernel(const __nv_bfloat16* __restrict__ hi, const __nv_bfloat16* __restrict__ lo,
                                                       int S, int Sp, float* __restrict__ part /* [N][MEAN_CHUNKS][256] */,
                                                       float* __restrict__ mean /* [N][256] */, int* __restrict__ done /* [N] */) {
   const int n = blockIdx.x / MEAN_CHUNKS, ch = blockIdx.x % MEAN_CHUNKS, c = threadIdx.x;
   const int per = (S + MEAN_CHUNKS - 1) / MEAN_CHUNKS;
   const int j0 = ch * per, j1 = min(S, j0 + per);
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   const long long base = static_cast<long long>(n) * Sp * FAST_C + c;
-  for (int j = j0; j < j1; j += 4) {
+  for (int j = j0; j < j1; j += 8) {
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < 8; ++u)
       if (j + u < j1) {
         const long long o = base + static_cast<long long>(j + u) * FAST_C;
         acc[u] += __bfloat162float(hi[o]) + __bfloat162float(lo[o]);
       }
   }
-  part[(static_cast<long long>(n) * MEAN_CHUNKS + ch) * FAST_C + c] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+  part[(static_cast<long long>(n) * MEAN_CHUNKS + ch) * FAST_C + c] =
+      ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
   __threadfence();
   __shared__ int last;
   __syncthreads();
@@ -1451,10 +1452,10 @@ __global__ void __launch_bounds__(256) colmean_kernel(const __nv_bfloat16* __res
   __syncthreads();
   if (last) {
     __threadfence();
-    float t = 0.f;
-#pragma unroll
-    for (int k = 0; k < MEAN_CHUNKS; ++k) t += __ldcg(&part[(static_cast<long long>(n) * MEAN_CHUNKS + k) * FAST_C + c]);
-    mean[n * FAST_C + c] = t / static_cast<float>(S);
+    float t4[4] = {0.f, 0.f, 0.f, 0.f};  // fixed order: chunk k goes to slot k % 4
+#pragma unroll 8
+    for (int k = 0; k < MEAN_CHUNKS; ++k) t4[k & 3] += __ldcg(&part[(static_cast<long long>(n) * MEAN_CHUNKS + k) * FAST_C + c]);
+    mean[n * FAST_C + c] = ((t4[0] + t4[1]) + (t4[2] + t4[3])) / static_cast<float>(S);
   }
 }
 

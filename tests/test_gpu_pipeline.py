@@ -107,7 +107,7 @@ def test_cuda_graph_head_matches_eager():
         want = [run(s, k) for s, k in order]
         model.cuda_graph = True
         got = [run(s, k) for s, k in order]
-        assert len(model._graphs) >= 2
+        assert len(model._graphs) >= 1   # (graphs of a replaced 3D model are dropped with their workspaces)
     for w, g in zip(want, got):
         assert w["mconf"].numel() > 50
         for k_ in ("b_ids", "i_ids", "j_ids"):
