@@ -1426,27 +1426,38 @@ struct PackSide {
 // has seen a single column:  sum_j 2^(y_ij) >= S 2^(mean_j y_ij) = S 2^(c a_i . mean_j b_j)  (Jensen).  For the rows
 // that hold no match -- nearly all of them -- this bound is within a small factor of the sum, which keeps the first
 // column tiles of a row block from flooding the candidate list (their own partial sum is a poor bound).
-constexpr int MEAN_CHUNKS = 128;  // 32 rows per block at S = 4096: the loads of a thread are few and all in flight
+constexpr int MEAN_CHUNKS = 64;
+// thread = (8 channels, row lane): 16-byte loads of the hi and lo planes, 8 rows of a chunk in flight per block step
 __global__ void __launch_bounds__(256) colmean_kernel(const __nv_bfloat16* __restrict__ hi, const __nv_bfloat16* __restrict__ lo,
                                                       int S, int Sp, float* __restrict__ part /* [N][MEAN_CHUNKS][256] */,
                                                       float* __restrict__ mean /* [N][256] */, int* __restrict__ done /* [N] */) {
-  const int n = blockIdx.x / MEAN_CHUNKS, ch = blockIdx.x % MEAN_CHUNKS, c = threadIdx.x;
+  __shared__ float red[8][FAST_C];
+  __shared__ int last;
+  const int n = blockIdx.x / MEAN_CHUNKS, ch = blockIdx.x % MEAN_CHUNKS;
+  const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int per = (S + MEAN_CHUNKS - 1) / MEAN_CHUNKS;
   const int j0 = ch * per, j1 = min(S, j0 + per);
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  const long long base = static_cast<long long>(n) * Sp * FAST_C + c;
-  for (int j = j0; j < j1; j += 8) {
+  const long long base = static_cast<long long>(n) * Sp * FAST_C + cg * 8;
+  for (int j = j0 + rl; j < j1; j += 8) {  // fixed assignment of rows to row lanes: deterministic
+    const uint4 h = *reinterpret_cast<const uint4*>(hi + base + static_cast<long long>(j) * FAST_C);
+    const uint4 l = *reinterpret_cast<const uint4*>(lo + base + static_cast<long long>(j) * FAST_C);
+    const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
-      if (j + u < j1) {
-        const long long o = base + static_cast<long long>(j + u) * FAST_C;
-        acc[u] += __bfloat162float(hi[o]) + __bfloat162float(lo[o]);
-      }
+    for (int q = 0; q < 4; ++q) {
+      acc[2 * q] += __uint_as_float(hw[q] << 16) + __uint_as_float(lw[q] << 16);
+      acc[2 * q + 1] += __uint_as_float(hw[q] & 0xffff0000u) + __uint_as_float(lw[q] & 0xffff0000u);
+    }
   }
-  part[(static_cast<long long>(n) * MEAN_CHUNKS + ch) * FAST_C + c] =
-      ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
+#pragma unroll
+  for (int q = 0; q < 8; ++q) red[rl][cg * 8 + q] = acc[q];
+  __syncthreads();
+  const int c = threadIdx.x;
+  float t = 0.f;
+#pragma unroll
+  for (int r = 0; r < 8; ++r) t += red[r][c];
+  part[(static_cast<long long>(n) * MEAN_CHUNKS + ch) * FAST_C + c] = t;
   __threadfence();
-  __shared__ int last;
   __syncthreads();
   if (threadIdx.x == 0) last = atomicAdd(&done[n], 1) == MEAN_CHUNKS - 1;
   __syncthreads();

@@ -184,7 +184,7 @@ def test_conv_split_precision_is_fp32_grade(n, H, W, cin, cout, k, stride, use_r
         y1 = ops.conv2d_nhwc_f16(xs.half(), wp1, k, stride, bp1, None if res2 is None else r.half(), 1, out_f16=False, out_f32=True)
         err1 = (y1[..., :cout] - want).abs().max().item() / want.abs().max().item()
         print(f"conv {cin}->{cout} k{k} s{stride}: split rel err {err:.2e} (single fp16 product {err1:.2e}), hi+lo reconstruction {rec:.2e}")
-        assert err < 1e-5 and err < 0.02 * err1 and rec < 2e-6 * max(1.0, want.abs().max().item())
+        assert err < 1e-5 and err < 0.05 * err1 and rec < 2e-6 * max(1.0, want.abs().max().item())
         if cout_s > cout:
             assert (y32[..., cout:] == 0).all() and (y16[..., cout:cout_s] == 0).all()
     finally:
