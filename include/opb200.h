@@ -262,6 +262,19 @@ int opb200_keypoint_encode(const float* kpts, int64_t kn, int64_t kl, int64_t kc
                            int64_t dl, const float* packed_w, int n_batch, int L, int normalize, float* out, float* stats_ws,
                            void* stream);
 
+/* ---- keypoint encoding without any allocation ------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments and result as
+ * opb200_keypoint_encode minus stats_ws: the statistics scratch is a file-scope __device__ array inside the library
+ * (16 KB, held by every GPU that loads the library until exit), so the call allocates nothing (no cudaMalloc / cudaFree,
+ * no allocating library routine).  Limit: n_batch <= opb200_keypoint_encode_static_max_batch() (1024); larger batches
+ * return the argument error (-1) with a message in opb200_last_error().  All calls on a device share the one array:
+ * calls that overlap on the GPU (different streams without ordering) race; calls ordered on one stream do not. */
+int opb200_keypoint_encode_static_max_batch(void);
+int opb200_keypoint_encode_static(const float* kpts, int64_t kn, int64_t kl, int64_t kc, const float* desc, int64_t dn,
+                                  int64_t dc, int64_t dl, const float* packed_w, int n_batch, int L, int normalize, float* out,
+                                  void* stream);
+
 /* ---- RANSAC-PnP on the device ------------------------------------------------------
  * Replaces ransac_PnP (src/utils/metric_utils.py:121-209; call sites inference.py:181-189, 328-336): the reference copies
  * the matches of a frame to the host and runs OpenCV solvePnPRansac (EPnP, 5 px, 10000 iterations) or pycolmap's

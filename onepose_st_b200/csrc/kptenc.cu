@@ -145,6 +145,33 @@ __global__ void __launch_bounds__(256) kpt_encode_kernel(const float* __restrict
       out[(static_cast<long long>(n) * KE_D4 + c) * L + l] = desc[n * dn + c * dc + l * dl] + res[c][lane];
 }
 
+// ---- scratch of the entry point that allocates nothing (opb200_keypoint_encode_static) -------------------------
+// The [n_batch][4] statistics block of up to KE_STATIC_MAX_BATCH batch elements, resident in every GPU that loads the
+// library until the process exits (16 KB).  In host code the NAME below is a host-side stand-in, not a device address:
+// the address a kernel may be given comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int KE_STATIC_MAX_BATCH = 1024;
+static __device__ __align__(256) float g_ke_static_stats[4 * KE_STATIC_MAX_BATCH];
+
+constexpr int KE_MAX_DEVICES = 64;
+static std::atomic<float*> g_ke_static_ptr[KE_MAX_DEVICES];
+
+// device address of g_ke_static_stats on the CURRENT device (looked up on first use per device, then cached)
+static int ke_static_scratch(float** out) {
+  int dev = 0;
+  OPB_CHECK_CUDA(cudaGetDevice(&dev));
+  OPB_CHECK_ARG(dev >= 0 && dev < KE_MAX_DEVICES, "device ordinal beyond the static scratch table (64)");
+  float* p = g_ke_static_ptr[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {
+    void* sym = nullptr;
+    OPB_CHECK_CUDA(cudaGetSymbolAddress(&sym, g_ke_static_stats));
+    OPB_CHECK_ARG(sym != nullptr, "cudaGetSymbolAddress returned a null address for the static scratch");
+    p = static_cast<float*>(sym);
+    g_ke_static_ptr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return OPB_OK;
+}
+
 }  // namespace opb
 
 using namespace opb;
@@ -162,6 +189,34 @@ int opb200_keypoint_encode(const float* kpts, int64_t kn, int64_t kl, int64_t kc
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   kpt_stats_kernel<<<n_batch, 256, 0, stream>>>(kpts, kn, kl, kc, L, normalize, stats_ws);
   kpt_encode_kernel<<<dim3((L + 31) / 32, n_batch), 256, 0, stream>>>(kpts, kn, kl, kc, desc, dn, dc, dl, packed_w, stats_ws, L, out);
+  count_launch(2);
+  OPB_CHECK_CUDA(cudaGetLastError());
+  return OPB_OK;
+}
+
+int opb200_keypoint_encode_static_max_batch(void) { return KE_STATIC_MAX_BATCH; }
+
+// Same result as opb200_keypoint_encode, no allocation anywhere and no scratch argument: the statistics block lives in
+// g_ke_static_stats.  Every call on a device shares that array (it keeps the last call's contents; nothing in it has to
+// start at zero because kpt_stats_kernel writes every word kpt_encode_kernel reads): calls that overlap on the GPU
+// (different streams, no ordering between them) race on it.
+int opb200_keypoint_encode_static(const float* kpts, int64_t kn, int64_t kl, int64_t kc, const float* desc, int64_t dn,
+                                  int64_t dc, int64_t dl, const float* packed_w, int n_batch, int L, int normalize, float* out,
+                                  void* stream_) {
+  if (int r = check_device()) return r;
+  OPB_CHECK_ARG(kpts && desc && packed_w && out, "null pointer");
+  OPB_CHECK_ARG(n_batch >= 1 && L >= 1, "empty input");
+  if (n_batch > KE_STATIC_MAX_BATCH) {
+    set_last_error("argument error: opb200_keypoint_encode_static: n_batch " + std::to_string(n_batch) +
+                   " exceeds the static scratch (" + std::to_string(KE_STATIC_MAX_BATCH) +
+                   " batch elements); use opb200_keypoint_encode with a caller-provided stats_ws");
+    return OPB_ERR_ARG;
+  }
+  float* stats = nullptr;
+  if (int r = ke_static_scratch(&stats)) return r;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  kpt_stats_kernel<<<n_batch, 256, 0, stream>>>(kpts, kn, kl, kc, L, normalize, stats);
+  kpt_encode_kernel<<<dim3((L + 31) / 32, n_batch), 256, 0, stream>>>(kpts, kn, kl, kc, desc, dn, dc, dl, packed_w, stats, L, out);
   count_launch(2);
   OPB_CHECK_CUDA(cudaGetLastError());
   return OPB_OK;
