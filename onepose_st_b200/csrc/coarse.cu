@@ -330,10 +330,10 @@ struct FastCfg {
   static constexpr int BN = 128;
   static constexpr int HALVES = BN / SIM_BN;                      // 128-column halves of an accumulator, one per epilogue group
   static constexpr int TSTAGES = 512 / BN;                        // accumulator stages in TMEM
-  static constexpr int BSTAGES = SCREEN ? 6 : 2;
+  static constexpr int BSTAGES = SCREEN ? 8 : 2;                  // SCREEN: two tiles' worth of 16 KB k-blocks (static schedule of the MMA warp)
   static constexpr int A_BYTES = PLANES * FAST_KB * FAST_SUB;     // the resident A block
   static constexpr int BSTAGE_BYTES = PLANES * HALVES * FAST_SUB; // one B k-block: [plane][BN rows x 64]
-  static constexpr int SMEM = 1024 + A_BYTES + BSTAGES * BSTAGE_BYTES + 256;
+  static constexpr int SMEM = 1024 + A_BYTES + BSTAGES * BSTAGE_BYTES + 512;  // + barriers, TMEM slot, tile slots
 };
 // What the screening sweep does with the bound delta on its similarity error (derived at pack_f16_kernel, below).  Capture: conf_ij > thr needs e_ij / R_i > thr; the screening sweep sees
 // y_s >= y - delta and a partial row sum R_s <= 2^delta R, so testing against thr * 2^(-2 delta) (times 0.99 for the
@@ -379,7 +379,9 @@ struct SimFastParams {
   long long* trace; // debug (opb200_debug_trace): per CTA and every fourth tile {MMA issue start, MMA issued, accumulator
                     // seen full by one epilogue warp of its stage, last release among the stage's four warps} SM-clock stamps
   int debug;        // OPB200_SIM_DEBUG timing experiments (results are garbage): 1 = epilogue warps only hand the accumulators back,
-                    // 2 = no MMAs are issued, 3 = epilogue reads TMEM only, 4 = epilogue arithmetic without the TMEM reads
+                    // 2 = no MMAs are issued, 3 = epilogue reads TMEM only, 4 = epilogue arithmetic without the TMEM reads,
+                    // 6 = mode 1 without the B loads (MMAs on whatever the stages hold), 7 = mode 1 without the MMAs (TMA alone),
+                    // 8 = one warp's tile profile instead of the stamps, 9 = accumulator stages taken strictly in turn
   int cand_tag;     // Candidate::pad of captured elements: 1 = y is final, 2 = y is the screening value (rescore)
   float* rowpart;   // [Sp/128][N*Lp]        sum_j e_ij over the 128 columns of a tile
   float* colpart;   // [4*Lp/128][N*Sp]      sum_i e_ij over the 32 rows of a warp's block
@@ -396,6 +398,10 @@ __device__ __forceinline__ uint64_t exp2_pair(uint32_t v0, uint32_t v1, uint64_t
   return ptx::pack_f32x2(ptx::ex2(x0), ptx::ex2(x1));
 }
 
+// (Measured and dropped: a share of the exponentials on the FMA pipe -- magic-number floor, cubic for 2^frac, exponent
+// added to the bits: 5 packed FMA-pipe instructions + 2 FMNMX + 2 LEA per pair instead of 2 MUFU.  With 1 / 2 / 3 / 4 of
+// every four pairs on that route the sweep took 188 / 195 / 206 / 218 us against 182.5: the epilogue warps are bound by
+// the latency of their dependent chain at four warps per scheduler, not by the MUFU pipe or by issue slots.)
 // order-preserving map of a float's bits to a signed integer (for redux.sync.max)
 __device__ __forceinline__ int float_key(float v) {
   const int b = __float_as_int(v);
@@ -442,11 +448,13 @@ __device__ __forceinline__ float quad_transpose_reduce(const float (&v)[4], int 
   return op(b1 ? a1 : a0, __shfl_xor_sync(0xffffffffu, b1 ? a0 : a1, 2));
 }
 
-template <bool RAGGED>
+template <bool RAGGED, int NCH>
 __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32_t tmem_acc, int m_tile, int n, int mt_in_batch,
                                                   int jt, int quarter, int lane, FastWarpState& st,
                                                   uint64_t* __restrict__ tempty_bar, long long* trace_slot) {
   float T = st.T;
+  const bool prof = p.debug == 8 && trace_slot != nullptr;  // debug: where a warp's tile time goes (SM clocks since entry)
+  const long long prof_t0 = prof ? clock64() : 0;
   const int cq = (lane & 3) * 2;
   const int i0 = mt_in_batch * BLOCK_M + quarter * 32 + (lane >> 2);  // this thread's rows: i0 + 8h
   const uint64_t c2 = ptx::pack_f32x2(p.c, p.c);
@@ -471,7 +479,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     ptx::tc_fence_before();
     __syncwarp();
     if (lane == 0) ptx::mbar_arrive(tempty_bar);
-    if (trace_slot != nullptr) atomicMax(reinterpret_cast<unsigned long long*>(trace_slot), static_cast<unsigned long long>(clock64()));
+    if (trace_slot != nullptr && !prof) atomicMax(reinterpret_cast<unsigned long long*>(trace_slot), static_cast<unsigned long long>(clock64()));
     released = true;
   };
 #pragma unroll 1
@@ -481,12 +489,13 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
 #pragma unroll
     for (int h = 0; h < 4; ++h) racc[h] = 0ull, rmax[h] = kNegInf;
 #pragma unroll 1
-    for (int ch = 0; ch < SIM_BN / 32; ++ch) {
+    for (int ch = 0; ch < NCH; ++ch) {
       uint32_t va[16], vb[16];
       if (p.debug != 4) {
         ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
         ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
         ptx::tmem_ld_wait();
+        if (prof && ch == 0 && lane == 0) trace_slot[0] = clock64() - prof_t0;
       } else {
 #pragma unroll
         for (int q = 0; q < 16; ++q) va[q] = vb[q] = __float_as_uint(static_cast<float>(q + ch + lane));
@@ -507,7 +516,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
         rmax[2] = ptx::max3(rmax[2], __uint_as_float(vb[4 * k]), __uint_as_float(vb[4 * k + 1]));
         rmax[3] = ptx::max3(rmax[3], __uint_as_float(vb[4 * k + 2]), __uint_as_float(vb[4 * k + 3]));
       }
-      if (ch == SIM_BN / 32 - 1) {
+      if (ch == NCH - 1) {
         // Everything of the tile is in registers or behind us.  Its maximum decides whether T held (else: once more
         // with T = the maximum), and if no element beats even the limits known before this tile -- which can only
         // have risen since -- nothing here can become a candidate: the accumulator goes back right away.
@@ -559,6 +568,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     st.dbg_flags |= 2;
     T = ymax;
   }
+  if (prof && lane == 0) trace_slot[1] = clock64() - prof_t0;
   const bool empty = ymax == kNegInf;  // ragged edge: no existing element in this warp's block
   const int own = lane & 3;
   float s[4];
@@ -570,8 +580,8 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
   }
   const float s_own = quad_transpose_reduce(s, lane, [](float x, float y) { return x + y; });
   const float mx_own = quad_transpose_reduce(rmax, lane, [](float x, float y) { return fmaxf(x, y); });
-  p.rowpart[(static_cast<long long>(jt / SIM_BN) * p.N + n) * p.Lp + i0 + 8 * own] = s_own;  // rows that do not exist hold 0
-  if (lane == 0) p.tile_ref[(static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / SIM_BN) + jt / SIM_BN] = empty ? kNegInf : T;
+  p.rowpart[(static_cast<long long>(jt / (32 * NCH)) * p.N + n) * p.Lp + i0 + 8 * own] = s_own;  // rows that do not exist hold 0
+  if (lane == 0) p.tile_ref[(static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / (32 * NCH)) + jt / (32 * NCH)] = empty ? kNegInf : T;
   // candidate capture: conf_ij > thr needs e_ij > thr * (row sum), and the part of the row this warp has seen so far
   // bounds that sum from below, i.e. acc_ij > vlim_i in raw accumulator units -- one compare per element on a second
   // sweep over TMEM, taken only when some row of the warp has its maximum above the limit
@@ -586,10 +596,11 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     const bool trig = !released && mx_own > vlim_own;
 #pragma unroll
     for (int h = 0; h < 4; ++h) st.vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
+    if (prof && lane == 0) trace_slot[2] = clock64() - prof_t0;
     if (__any_sync(0xffffffffu, trig)) {
       st.dbg_flags |= 1;
 #pragma unroll 1
-      for (int ch = 0; ch < SIM_BN / 32; ++ch) {
+      for (int ch = 0; ch < NCH; ++ch) {
         uint32_t va[16], vb[16];
         ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
         ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
@@ -628,6 +639,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     st.T = ymax;  // the next tile's guess
   }
   if (!released) release();
+  if (prof && lane == 0) trace_slot[3] = clock64() - prof_t0;
 }
 
 template <bool SCREEN>
@@ -648,6 +660,9 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   uint64_t* tfull = b_empty + FAST_BSTAGES;  // TSTAGES
   uint64_t* tempty = tfull + TSTAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + TSTAGES);
+  // SCREEN: which tile an accumulator stage holds -- (m_tile, n_tile, position in the CTA's list, -) written by the MMA
+  // thread before it issues the tile; m_tile < 0 tells the stage's epilogue group that the list is exhausted
+  volatile int4* tile_slot = reinterpret_cast<volatile int4*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float thr_lim = p.thr_lim, seed_shift = 0.f;
@@ -723,6 +738,9 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
 #pragma unroll
         for (int kb = 0; kb < FAST_KB; ++kb) {
           ptx::mbar_wait(&b_empty[stage], phase ^ 1);
+          if (p.debug == 6) {  // experiment: the B stages are declared full without loading anything
+            ptx::mbar_arrive(&b_full[stage]);
+          } else {
           ptx::mbar_arrive_expect_tx(&b_full[stage], FAST_BSTAGE_BYTES);
           uint8_t* sb = smem_b + stage * FAST_BSTAGE_BYTES;
           // 128-row boxes; rows past the tensor (odd half of the last tile) arrive as zeros and are never read back
@@ -730,6 +748,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
           for (int hf = 0; hf < HALVES; ++hf) {
             ptx::tma_load_2d(sb + hf * FAST_SUB, &p.b_hi, &b_full[stage], kb * BLOCK_K, b_row + hf * SIM_BN);
             if (!SCREEN) ptx::tma_load_2d(sb + (HALVES + hf) * FAST_SUB, &p.b_lo, &b_full[stage], kb * BLOCK_K, b_row + hf * SIM_BN);
+          }
           }
           if (++stage == FAST_BSTAGES) {
             stage = 0;
@@ -739,6 +758,103 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
         if (++n_tile == p.n_tiles) {
           n_tile = 0, ++m_tile, new_a = true;
           if (++mt_in_batch == tiles_per_batch) mt_in_batch = 0, b_row0 += p.Sp;
+        }
+      }
+    }
+  } else if (warp == 1 && SCREEN) {
+    // ------------------------------------------------------------------ MMA issuer of the screening sweep (one thread)
+    // * B ring: the list is walked two tiles at a time so that the B stage ((it % 2) * 4 + kb of the 8-stage ring) and
+    //   the parity of its full barrier ((it / 2) % 2) are compile-time constants: a k-block is one wait, four MMAs
+    //   whose descriptors are base + constant, one commit (tools/probes/mma_pipe.cu: this loop alone issues a tile in
+    //   1080 clk against 1024 clk of tensor work; the rolled loop with run-time stage / phase arithmetic needed 1700, a
+    //   whole-warp loop with one issuing lane 1530).
+    // * Accumulators: a tile goes to WHICHEVER of the four stages is free (probed round-robin), not to stage it % 4: an
+    //   epilogue group that is late (a second sweep for candidates, a re-swept reference) then only skips a turn
+    //   instead of holding up the three tiles queued behind it.  The stage's tile slot tells its group what it got.
+    //   (Measured and dropped: two groups of eight warps alternating between two stages each, so that a group never
+    //   waits for a refill -- 190 us against 181: the two warps of a group that share a scheduler move in step and
+    //   their MUFU bursts collide, 1300 clk per 32 x 32 chunk against 950 with four groups on four different tiles.)
+    if constexpr (SCREEN) {
+      static_assert(FAST_BSTAGES == 2 * FAST_KB && TSTAGES == 4, "the unrolled schedule assumes an 8-stage B ring and 4 accumulators");
+      if (ptx::elect_one()) {
+        constexpr uint32_t idesc = ptx::make_idesc_f16(BLOCK_M, BN);
+        constexpr int kDescPerStage = FAST_BSTAGE_BYTES >> 4;
+        const uint64_t a_desc0 = ptx::make_desc_sw128(ptx::smem_u32(smem_a));
+        const uint64_t b_desc0 = ptx::make_desc_sw128(ptx::smem_u32(smem_b));
+        const bool no_mma = p.debug == 2 || p.debug == 7;
+        const bool trace_on = p.debug != 5 && p.debug != 8 && p.trace != nullptr;
+        const int n_it = t_end - t_begin;
+        uint32_t a_phase = 0;
+        uint32_t te_par = 0xfu;  // per stage: the parity of its empty barrier that means "free" (a fresh barrier passes parity 1)
+        int g = 3;               // last stage taken
+        int m_tile = m_first, n_tile = n_first;
+        bool new_a = true;
+        auto take_stage = [&]() {
+          if (p.debug == 9) {  // experiment: stages strictly in turn (what the kernel did before the tile slots)
+            const int c = (g + 1) & (TSTAGES - 1);
+            ptx::mbar_wait(&tempty[c], (te_par >> c) & 1u);
+            g = c;
+            te_par ^= 1u << c;
+            return;
+          }
+          uint32_t spins = 0;
+          for (;;) {
+#pragma unroll
+            for (int q = 1; q <= TSTAGES; ++q) {
+              const int c = (g + q) & (TSTAGES - 1);
+              if (ptx::mbar_test_wait(&tempty[c], (te_par >> c) & 1u)) {
+                g = c;
+                te_par ^= 1u << c;
+                return;
+              }
+            }
+            if (++spins > (1u << 24)) __trap();
+            __nanosleep(32);  // every stage is with its epilogue group: the operand reads of the MMAs in flight want the shared-memory port
+          }
+        };
+        for (int it0 = 0; it0 < n_it; it0 += 2) {
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int it = it0 + u;
+            if (it >= n_it) break;
+            if (new_a) {
+              ptx::mbar_wait(a_full, a_phase);
+              a_phase ^= 1;
+              new_a = false;
+            }
+            take_stage();
+            ptx::tc_fence_after();
+            tile_slot[g].x = m_tile, tile_slot[g].y = n_tile, tile_slot[g].z = it;
+            __threadfence_block();
+            const bool tr = trace_on && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta;
+            if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 0] = clock64();
+            const uint32_t d_tmem = tmem_base + g * BN;
+#pragma unroll
+            for (int kb = 0; kb < FAST_KB; ++kb) {
+              const int stage = u * FAST_KB + kb;
+              ptx::mbar_wait(&b_full[stage], static_cast<uint32_t>((it0 >> 1) & 1));
+              ptx::tc_fence_after();
+              if (!no_mma) {
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / 16; ++k)
+                  ptx::mma_bf16(d_tmem, a_desc0 + static_cast<uint64_t>(kb * (FAST_SUB >> 4) + 2 * k),
+                                b_desc0 + static_cast<uint64_t>(stage * kDescPerStage + 2 * k), idesc, (kb | k) != 0);
+              }
+              ptx::mma_commit(&b_empty[stage]);
+            }
+            ptx::mma_commit(&tfull[g]);
+            if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 1] = clock64();
+            const bool last_n = ++n_tile == p.n_tiles;
+            if (last_n || it + 1 == n_it) ptx::mma_commit(a_empty);
+            if (last_n) n_tile = 0, ++m_tile, new_a = true;
+          }
+        }
+        // the list is exhausted: every group gets the end marker once its stage is free again
+        for (int q = 0; q < TSTAGES; ++q) {
+          ptx::mbar_wait(&tempty[q], (te_par >> q) & 1u);
+          tile_slot[q].x = -1;
+          __threadfence_block();
+          ptx::mbar_arrive(&tfull[q]);
         }
       }
     }
@@ -802,41 +918,71 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   } else {
     // ------------------------------------------------------------------ epilogue groups
     const int ew = warp - 2;
-    const int group = ew >> 2;                          // owns half (group % HALVES) of accumulator stage (group / HALVES)
-    const int tstage = group / HALVES, half = group % HALVES;
     const int quarter = warp & 3;
     FastWarpState st;
     st.thr_lim = thr_lim;
     st.seed_shift = seed_shift;
-    int m_tile = m_first, n_tile = n_first + tstage;
-    int n_batch = m_tile / tiles_per_batch, mt_in_batch = m_tile % tiles_per_batch;
-    for (int t = t_begin + tstage, round = 0; t < t_end; t += TSTAGES, n_tile += TSTAGES, ++round) {
-      while (n_tile >= p.n_tiles) {
-        n_tile -= p.n_tiles, ++m_tile;
-        if (++mt_in_batch == tiles_per_batch) mt_in_batch = 0, ++n_batch;
+    if constexpr (SCREEN) {
+      // group g = the four warps that own accumulator stage g; the stage's tile slot says which tile the MMA thread put
+      // there (tiles reach a group in list order, but not every fourth one)
+      const int tstage = ew >> 2;
+      int m_tile = -1, n_batch = 0, mt_in_batch = 0;
+      for (int cnt = 0;; ++cnt) {
+        ptx::mbar_wait(&tfull[tstage], cnt & 1);
+        ptx::tc_fence_after();
+        const int mt = tile_slot[tstage].x;
+        if (mt < 0) break;
+        const int n_tile = tile_slot[tstage].y, it_e = tile_slot[tstage].z;
+        if (mt != m_tile) m_tile = mt, n_batch = mt / tiles_per_batch, mt_in_batch = mt - n_batch * tiles_per_batch;
+        const bool tr = p.debug != 5 && p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta &&
+                        (p.debug != 8 || quarter == 0);  // all four warps: first / last (mode 8: one warp's profile)
+        if (tr && quarter == 2 && lane == 0 && p.debug != 8) p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 2] = clock64();
+        const int jt = n_tile * BN;
+        if (p.debug != 1 && (p.debug < 6 || p.debug >= 8)) {
+          const uint32_t tacc = tmem_base + tstage * BN + (static_cast<uint32_t>(quarter * 32) << 16);
+          const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || (jt + SIM_BN > p.S);
+          const bool tr5 = p.debug == 5 && p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta;
+          const long long t5 = tr5 ? clock64() : 0;
+          st.dbg_flags = 0;
+          long long* tslot = tr ? &p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + (p.debug == 8 ? 0 : 3)] : nullptr;
+          if (ragged) sim_fast_epilogue<true, 4>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage], tslot);
+          else sim_fast_epilogue<false, 4>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage], tslot);
+          if (tr5 && lane == 0)  // mode 5: the slot holds, per quarter, this warp's epilogue time and flags instead of the four stamps
+            p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + quarter] = (clock64() - t5) | (static_cast<long long>(st.dbg_flags) << 48);
+        } else {
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tempty[tstage]);
+        }
       }
-      ptx::mbar_wait(&tfull[tstage], round & 1);
-      ptx::tc_fence_after();
-      const int it_e = t - t_begin;
-      const bool tr = p.debug != 5 && p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta && half == 0 && lane == 0;  // all four warps: first / last
-      if (tr && quarter == 2) p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 2] = clock64();
-      const int jt = n_tile * BN + half * SIM_BN;
-      if (jt < p.Sp && p.debug != 1) {  // (the odd half of the last tile lies outside the padded width)
-        const uint32_t tacc = tmem_base + tstage * BN + half * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);
-        const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || (jt + SIM_BN > p.S);
-        const bool tr5 = p.debug == 5 && p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta && half == 0;
-        const long long t5 = tr5 ? clock64() : 0;
-        st.dbg_flags = 0;
-        if (ragged) sim_fast_epilogue<true>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage],
-                                                tr ? &p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 3] : nullptr);
-        else sim_fast_epilogue<false>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage],
-                                                tr ? &p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 3] : nullptr);
-        if (tr5 && lane == 0)  // mode 5: the slot holds, per quarter, this warp's epilogue time and flags instead of the four stamps
-          p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + quarter] = (clock64() - t5) | (static_cast<long long>(st.dbg_flags) << 48);
-      } else {
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&tempty[tstage]);
+    } else {
+      const int group = ew >> 2;                          // owns half (group % HALVES) of accumulator stage (group / HALVES)
+      const int tstage = group / HALVES, half = group % HALVES;
+      int m_tile = m_first, n_tile = n_first + tstage;
+      int n_batch = m_tile / tiles_per_batch, mt_in_batch = m_tile % tiles_per_batch;
+      for (int t = t_begin + tstage, round = 0; t < t_end; t += TSTAGES, n_tile += TSTAGES, ++round) {
+        while (n_tile >= p.n_tiles) {
+          n_tile -= p.n_tiles, ++m_tile;
+          if (++mt_in_batch == tiles_per_batch) mt_in_batch = 0, ++n_batch;
+        }
+        ptx::mbar_wait(&tfull[tstage], round & 1);
+        ptx::tc_fence_after();
+        const int it_e = t - t_begin;
+        const bool tr = p.debug != 5 && p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta && half == 0 && lane == 0;  // all four warps: first / last
+        if (tr && quarter == 2) p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 2] = clock64();
+        const int jt = n_tile * BN + half * SIM_BN;
+        if (jt < p.Sp && p.debug != 1 && p.debug < 6) {  // (the odd half of the last tile lies outside the padded width)
+          const uint32_t tacc = tmem_base + tstage * BN + half * SIM_BN + (static_cast<uint32_t>(quarter * 32) << 16);
+          const bool ragged = ((mt_in_batch + 1) * BLOCK_M > p.L) || (jt + SIM_BN > p.S);
+          st.dbg_flags = 0;
+          long long* tslot = tr ? &p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + 3] : nullptr;
+          if (ragged) sim_fast_epilogue<true, 4>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage], tslot);
+          else sim_fast_epilogue<false, 4>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage], tslot);
+        } else {
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tempty[tstage]);
+        }
       }
     }
   }
@@ -858,12 +1004,12 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
 __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict__ rowpart, const float* __restrict__ colpart,
                                                          const float* __restrict__ tile_ref, int N, int L, int S, int Lp, int Sp,
                                                          float2* __restrict__ lse_row, float2* __restrict__ lse_col,
-                                                         int* __restrict__ needs_robust) {
+                                                         int* __restrict__ needs_robust, int part_w /* columns per row part: 128 | 64 */) {
   __shared__ float2 sm[8][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long n_rows = static_cast<long long>(N) * Lp, n_cols = static_cast<long long>(N) * Sp;
   const int row_blocks = static_cast<int>(n_rows / 256 + ((n_rows % 256) != 0));  // Lp is a multiple of 128
-  const int mtb = Lp / BLOCK_M, ntb = Sp / SIM_BN;
+  const int mtb = Lp / BLOCK_M, ntb = Sp / part_w;
   if (static_cast<int>(blockIdx.x) < row_blocks) {
     const long long idx0 = (static_cast<long long>(blockIdx.x) * 8 + warp) * 32;  // this warp's 32 rows
     if (idx0 >= n_rows) return;
@@ -903,7 +1049,7 @@ __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict
   const int nparts = 4 * mtb;
   const int per = (nparts + 7) / 8;
   const int kb = warp * per, ke = min(nparts, kb + per);
-  const float* tr = tile_ref + static_cast<long long>(n) * nparts * ntb + j0 / SIM_BN;
+  const float* tr = tile_ref + static_cast<long long>(n) * nparts * ntb + j0 / part_w;
   float M = kNegInf;
   for (int k0 = kb; k0 < ke; k0 += 32) {
     const float T = k0 + lane < ke ? tr[static_cast<long long>(k0 + lane) * ntb] : kNegInf;
@@ -944,37 +1090,38 @@ __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict
 }
 
 // ================================================================================================
-// SWEEP KERNEL (algo 0, the default): the same single pass as sim_fast_kernel<true>, re-cut so that the tensor pipe
-// and the epilogue no longer take turns on an accumulator stage.
+// SWEEP KERNEL (algo 3): the same single pass as sim_fast_kernel<true>, re-cut so that the tensor pipe and the epilogue
+// no longer take turns on an accumulator stage.
 //
-//   * MMAs are 128 x 256 x 16 (half the instructions of the issuing thread per flop, 96 instead of 128 bytes of shared
-//     memory per clock), two accumulator stages of 256 TMEM columns.
+//   * Tiles are 128 x 128 (MMAs 128 x 128 x 16) in four accumulator stages; the MMA thread runs the statically
+//     scheduled loop of sim_fast_kernel (8-stage B ring, stage / parity compile-time constants).
 //   * ALL sixteen epilogue warps work on every tile: warp (quarter q, column block c) owns rows 32q .. 32q+31 and
-//     columns 64c .. 64c+63.  It reads its two 32 x 32 chunks into registers and arrives on the stage's barrier as soon
-//     as the second read has landed, so a stage is held for about one chunk of arithmetic, not for a tile's whole
-//     epilogue, and the MMA thread refills it while the warps are still exponentiating.
-//   * Everything a warp keeps is per (32 rows, its columns): the reference exponent T (guess = the last chunk's
-//     maximum, verified on the registers; when it moves by more than the window the running row sums are written out
-//     as one record and a new run starts -- no rescaling, no second TMEM pass), the row sums of the current run, and a
-//     lower bound of each row's full sum (all of the row this warp has seen) from which the candidate limit is taken.
-//     The limit includes the chunk itself and the candidates are captured from the registers.
+//     columns 32c .. 32c+31.  It reads its 32 x 32 chunk into registers and arrives on the stage's barrier as soon as
+//     the read has landed: a stage is held for one TMEM read, not for a tile's epilogue, so the MMA thread is never
+//     held up by a warp that is late, and the warps drift apart over the four stages instead of moving in step.
+//   * Everything a warp keeps is per (32 rows, its 32 columns of every tile): the reference exponent T (guess = the
+//     last chunk's maximum, verified on the registers; when it moves by more than the window the running row sums are
+//     written out as one record and a new run starts -- no rescaling, no second TMEM pass), the row sums of the
+//     current run, and a lower bound of each row's full sum (the a-priori Jensen bound of pack_f16_kernel or all of the
+//     row this warp has seen, whichever is larger) from which the candidate limit is taken.  The limit includes the
+//     chunk itself and the candidates are captured from the registers.
 //   * Records: column sums per (warp block, chunk) with their reference in col_ref; row sums per run in one of 128
-//     slots (n tile, chunk and column block of the run's first chunk), references in row_ref (NaN = slot unused,
-//     cleared by a memset per call).  merge_sweep_kernel folds them.
+//     slots (n tile and column block of the run's first chunk), references in row_ref (NaN = slot unused, cleared by a
+//     memset per call).  merge_sweep_kernel folds them.
 // ================================================================================================
-constexpr int SW_BN = 256;
-constexpr int SW_BSTAGES = 4;
-constexpr int SW_TSTAGES = 2;
+constexpr int SW_BN = 128;
+constexpr int SW_BSTAGES = 2 * FAST_KB;              // two tiles' worth of 16 KB k-blocks
+constexpr int SW_TSTAGES = 4;
 constexpr int SW_A_BYTES = FAST_KB * FAST_SUB;       // 64 KB: the resident 128-row A block (fp16)
-constexpr int SW_BSTAGE_BYTES = 2 * FAST_SUB;        // 32 KB: 256 rows x 64 of B
+constexpr int SW_BSTAGE_BYTES = FAST_SUB;            // 16 KB: 128 rows x 64 of B
 constexpr int SW_SMEM = 1024 + SW_A_BYTES + SW_BSTAGES * SW_BSTAGE_BYTES + 256;
-constexpr int SW_ROW_SLOTS = 128;                    // (n tile of 256: up to 16) x (chunk 0/1) x (column block c)
-constexpr int SW_MAX_NTILES = SW_ROW_SLOTS / 8;
+constexpr int SW_ROW_SLOTS = 128;                    // (n tile of 128: up to 32) x (column block c)
+constexpr int SW_MAX_NTILES = SW_ROW_SLOTS / 4;
 
 struct SimSweepParams {
   CUtensorMap a, b;   // fp16 operand planes [rows, 256], box 128 x 64, 128B swizzle
   int N, L, S, Lp, Sp;
-  int n_tiles;        // ceil(Sp / 256)
+  int n_tiles;        // Sp / 128
   int total_tiles;    // N * (Lp/128) * n_tiles, m-major
   float c;            // scale * log2(e)  (> 0)
   float thr, max_delta;
@@ -996,7 +1143,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;                // [kb][128 x 64]
-  uint8_t* smem_b = smem + SW_A_BYTES;   // [stage][256 x 64]
+  uint8_t* smem_b = smem + SW_A_BYTES;   // [stage][128 x 64]
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + SW_BSTAGES * SW_BSTAGE_BYTES);
   uint64_t* a_full = bars;
   uint64_t* a_empty = bars + 1;
@@ -1042,6 +1189,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
   const uint32_t tmem_base = *tmem_slot;
   const int tiles_per_batch = p.Lp / BLOCK_M;
   const int m_first = t_begin / p.n_tiles, n_first = t_begin - m_first * p.n_tiles;
+  const int n_it = t_end - t_begin;
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (one thread)
@@ -1065,10 +1213,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
         for (int kb = 0; kb < FAST_KB; ++kb) {
           ptx::mbar_wait(&b_empty[stage], phase ^ 1);
           ptx::mbar_arrive_expect_tx(&b_full[stage], SW_BSTAGE_BYTES);
-          uint8_t* sb = smem_b + stage * SW_BSTAGE_BYTES;
-          // two 128-row boxes; rows past the tensor (odd half of the last tile) arrive as zeros and are never read back
-          ptx::tma_load_2d(sb, &p.b, &b_full[stage], kb * BLOCK_K, b_row);
-          ptx::tma_load_2d(sb + FAST_SUB, &p.b, &b_full[stage], kb * BLOCK_K, b_row + SIM_BN);
+          ptx::tma_load_2d(smem_b + stage * SW_BSTAGE_BYTES, &p.b, &b_full[stage], kb * BLOCK_K, b_row);
           if (++stage == SW_BSTAGES) {
             stage = 0;
             phase ^= 1;
@@ -1081,53 +1226,55 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (one thread)
+    // ------------------------------------------------------------------ MMA issuer (one thread; see sim_fast_kernel)
     if (ptx::elect_one()) {
       constexpr uint32_t idesc = ptx::make_idesc_f16(BLOCK_M, SW_BN);
-      uint64_t a_desc[FAST_KB];
-#pragma unroll
-      for (int kb = 0; kb < FAST_KB; ++kb) a_desc[kb] = ptx::make_desc_sw128(ptx::smem_u32(smem_a + kb * FAST_SUB));
-      const uint64_t b_desc0 = ptx::make_desc_sw128(ptx::smem_u32(smem_b));  // + (byte offset >> 4): the start-address field
-      int stage = 0;
-      uint32_t phase = 0, a_phase = 0;
-      int n_tile = n_first;
+      constexpr int kDescPerStage = SW_BSTAGE_BYTES >> 4;
+      const uint64_t a_desc0 = ptx::make_desc_sw128(ptx::smem_u32(smem_a));
+      const uint64_t b_desc0 = ptx::make_desc_sw128(ptx::smem_u32(smem_b));
+      const bool no_mma = p.debug == 2;
+      uint32_t a_phase = 0;
+      int n_left = p.n_tiles - n_first;  // tiles left in the current block of rows
       bool new_a = true;
-      for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
-        if (new_a) {
-          ptx::mbar_wait(a_full, a_phase);
-          a_phase ^= 1;
-          new_a = false;
-        }
-        const int acc = it & 1;
-        ptx::mbar_wait(&tempty[acc], ((it >> 1) & 1) ^ 1);
-        ptx::tc_fence_after();
-        const bool tr = p.trace != nullptr && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta;
-        if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 0] = clock64();
-        const uint32_t d_tmem = tmem_base + acc * SW_BN;
+      for (int it0 = 0; it0 < n_it; it0 += SW_TSTAGES) {
+        const uint32_t te_parity = ((it0 >> 2) & 1) ^ 1;
 #pragma unroll
-        for (int kb = 0; kb < FAST_KB; ++kb) {
-          ptx::mbar_wait(&b_full[stage], phase);
-          const uint64_t bd = b_desc0 + static_cast<uint64_t>((stage * SW_BSTAGE_BYTES) >> 4);
-          if (p.debug != 2) {
+        for (int u = 0; u < SW_TSTAGES; ++u) {
+          if (it0 + u >= n_it) break;
+          if (new_a) {
+            ptx::mbar_wait(a_full, a_phase);
+            a_phase ^= 1;
+            new_a = false;
+          }
+          ptx::mbar_wait(&tempty[u], te_parity);
+          ptx::tc_fence_after();
+          const bool tr = p.trace != nullptr && u == 0 && (it0 >> 2) < kTraceTilesPerCta;
+          if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it0 >> 2)) * 4 + 0] = clock64();
+          const uint32_t d_tmem = tmem_base + u * SW_BN;
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / 16; ++k) ptx::mma_bf16(d_tmem, a_desc[kb] + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+          for (int kb = 0; kb < FAST_KB; ++kb) {
+            const int stage = (u & 1) * FAST_KB + kb;
+            ptx::mbar_wait(&b_full[stage], static_cast<uint32_t>(u >> 1));
+            ptx::tc_fence_after();
+            if (!no_mma) {
+#pragma unroll
+              for (int k = 0; k < BLOCK_K / 16; ++k)
+                ptx::mma_bf16(d_tmem, a_desc0 + static_cast<uint64_t>(kb * (FAST_SUB >> 4) + 2 * k),
+                              b_desc0 + static_cast<uint64_t>(stage * kDescPerStage + 2 * k), idesc, (kb | k) != 0);
+            }
+            ptx::mma_commit(&b_empty[stage]);
           }
-          ptx::mma_commit(&b_empty[stage]);
-          if (++stage == SW_BSTAGES) {
-            stage = 0;
-            phase ^= 1;
-          }
+          ptx::mma_commit(&tfull[u]);
+          if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it0 >> 2)) * 4 + 1] = clock64();
+          const bool last_n = --n_left == 0;
+          if (last_n || it0 + u + 1 == n_it) ptx::mma_commit(a_empty);
+          if (last_n) n_left = p.n_tiles, new_a = true;
         }
-        ptx::mma_commit(&tfull[acc]);
-        if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 1] = clock64();
-        const bool last_n = ++n_tile == p.n_tiles;
-        if (last_n || t + 1 == t_end) ptx::mma_commit(a_empty);
-        if (last_n) n_tile = 0, new_a = true;
       }
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps: (quarter, column block)
-    const int cb = (warp - 2) >> 2;   // columns 64 cb .. 64 cb + 63 of every tile
+    const int cb = (warp - 2) >> 2;   // columns 32 cb .. 32 cb + 31 of every tile
     const int quarter = warp & 3;     // TMEM lanes 32 quarter .. + 31
     const int cq = (lane & 3) * 2;
     const int own = lane & 3;
@@ -1173,31 +1320,27 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
       run_slot = -1;
     };
 
-    for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
-      const int stage = it & 1;
-      ptx::mbar_wait(&tfull[stage], (it >> 1) & 1);
+    for (int it = 0; it < n_it; ++it) {
+      const int stage = it & (SW_TSTAGES - 1);
+      ptx::mbar_wait(&tfull[stage], (it >> 2) & 1);
       ptx::tc_fence_after();
       const bool tr = p.trace != nullptr && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta && warp == 4 && lane == 0;
       if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 2] = clock64();
-      const int jt = n_tile * SW_BN + cb * 64;
-      const bool valid = jt < p.Sp && p.debug != 1;  // (the odd half of the last tile lies outside the padded width)
-      const uint32_t tacc = tmem_base + stage * SW_BN + cb * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
-#pragma unroll 1
-      for (int hc = 0; hc < 2; ++hc) {
-        uint32_t va[16], vb[16];
-        if (valid) {
-          ptx::tmem_ld_16x256b_x4(tacc + hc * 32, va);
-          ptx::tmem_ld_16x256b_x4(tacc + (16u << 16) + hc * 32, vb);
-          ptx::tmem_ld_wait();
-        }
-        if (hc == 1 || !valid) {  // both chunks are in registers: the stage goes back to the MMA thread
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(&tempty[stage]);
-          if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 3] = clock64();
-        }
-        if (!valid) break;
-        const int j0 = jt + hc * 32;
+      const int j0 = n_tile * SW_BN + cb * 32;
+      const uint32_t tacc = tmem_base + stage * SW_BN + cb * 32 + (static_cast<uint32_t>(quarter * 32) << 16);
+      uint32_t va[16], vb[16];
+      if (p.debug != 1) {
+        ptx::tmem_ld_16x256b_x4(tacc, va);
+        ptx::tmem_ld_16x256b_x4(tacc + (16u << 16), vb);
+        ptx::tmem_ld_wait();
+      }
+      {  // the chunk is in registers: the stage goes back to the MMA thread
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&tempty[stage]);
+        if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 3] = clock64();
+      }
+      if (p.debug != 1) {
         if (rows_ragged || j0 + 32 > p.S) {  // rows / columns that do not exist: -inf, i.e. e = 0 and no say in the maximum
 #pragma unroll
           for (int q = 0; q < 16; ++q) {
@@ -1221,84 +1364,84 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_sweep_kernel(co
         if (ymax == kNegInf) {  // ragged edge: nothing exists in this chunk
           colp[lane] = 0.f;
           if (lane == 0) *cref = kNegInf;
-          continue;
-        }
-        if (!(fabsf(ymax - T) <= kRefWindow)) {  // the guess does not hold: close the run, start one at this chunk
-          flush_run(n_batch, mt_in_batch);
-          T = ymax;
-        }
-        if (run_slot < 0) run_slot = ((n_tile * 2 + hc) * 4 + cb);
-        const uint64_t t2 = ptx::pack_f32x2(-T, -T);
-        uint64_t rc[4] = {0ull, 0ull, 0ull, 0ull};  // this chunk's row sums
-        float f[4][2];
+        } else {
+          if (!(fabsf(ymax - T) <= kRefWindow)) {  // the guess does not hold: close the run, start one at this chunk
+            flush_run(n_batch, mt_in_batch);
+            T = ymax;
+          }
+          if (run_slot < 0) run_slot = n_tile * 4 + cb;
+          const uint64_t t2 = ptx::pack_f32x2(-T, -T);
+          uint64_t rc[4] = {0ull, 0ull, 0ull, 0ull};  // this chunk's row sums
+          float f[4][2];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint64_t e0 = exp2_pair(va[4 * k], va[4 * k + 1], c2, t2), e1 = exp2_pair(va[4 * k + 2], va[4 * k + 3], c2, t2);
-          const uint64_t e2 = exp2_pair(vb[4 * k], vb[4 * k + 1], c2, t2), e3 = exp2_pair(vb[4 * k + 2], vb[4 * k + 3], c2, t2);
-          rc[0] = ptx::add_f32x2(rc[0], e0);
-          rc[1] = ptx::add_f32x2(rc[1], e1);
-          rc[2] = ptx::add_f32x2(rc[2], e2);
-          rc[3] = ptx::add_f32x2(rc[3], e3);
-          ptx::unpack_f32x2(ptx::add_f32x2(ptx::add_f32x2(e0, e1), ptx::add_f32x2(e2, e3)), f[k][0], f[k][1]);
-        }
-        // column sums: halving butterfly over the row bits of the lane id (16, 8, 4): 4 + 2 + 1 shuffles
-        float g[2][2], hh[2];
-        {
-          const bool up = (lane & 16) != 0;
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t e0 = exp2_pair(va[4 * k], va[4 * k + 1], c2, t2), e1 = exp2_pair(va[4 * k + 2], va[4 * k + 3], c2, t2);
+            const uint64_t e2 = exp2_pair(vb[4 * k], vb[4 * k + 1], c2, t2), e3 = exp2_pair(vb[4 * k + 2], vb[4 * k + 3], c2, t2);
+            rc[0] = ptx::add_f32x2(rc[0], e0);
+            rc[1] = ptx::add_f32x2(rc[1], e1);
+            rc[2] = ptx::add_f32x2(rc[2], e2);
+            rc[3] = ptx::add_f32x2(rc[3], e3);
+            ptx::unpack_f32x2(ptx::add_f32x2(ptx::add_f32x2(e0, e1), ptx::add_f32x2(e2, e3)), f[k][0], f[k][1]);
+          }
+          // column sums: halving butterfly over the row bits of the lane id (16, 8, 4): 4 + 2 + 1 shuffles
+          float g[2][2], hh[2];
+          {
+            const bool up = (lane & 16) != 0;
 #pragma unroll
-          for (int kk = 0; kk < 2; ++kk)
+            for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+              for (int b = 0; b < 2; ++b) {
+                const float keep = up ? f[kk + 2][b] : f[kk][b];
+                const float send = up ? f[kk][b] : f[kk + 2][b];
+                g[kk][b] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+              }
+          }
+          {
+            const bool up = (lane & 8) != 0;
 #pragma unroll
             for (int b = 0; b < 2; ++b) {
-              const float keep = up ? f[kk + 2][b] : f[kk][b];
-              const float send = up ? f[kk][b] : f[kk + 2][b];
-              g[kk][b] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+              const float keep = up ? g[1][b] : g[0][b];
+              const float send = up ? g[0][b] : g[1][b];
+              hh[b] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
             }
-        }
-        {
-          const bool up = (lane & 8) != 0;
-#pragma unroll
-          for (int b = 0; b < 2; ++b) {
-            const float keep = up ? g[1][b] : g[0][b];
-            const float send = up ? g[0][b] : g[1][b];
-            hh[b] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
           }
-        }
-        const bool up4 = (lane & 4) != 0;
-        const float cs = (up4 ? hh[1] : hh[0]) + __shfl_xor_sync(0xffffffffu, up4 ? hh[0] : hh[1], 4);
-        colp[((lane >> 3) & 3) * 8 + cq + ((lane >> 2) & 1)] = cs;  // lane bits 4,3 select k, bit 2 the column of the pair
-        if (lane == 0) *cref = T;
-        // row sums: into the run, and (owner lanes) into the lower bound of the full row sum
-        float s4[4];
+          const bool up4 = (lane & 4) != 0;
+          const float cs = (up4 ? hh[1] : hh[0]) + __shfl_xor_sync(0xffffffffu, up4 ? hh[0] : hh[1], 4);
+          colp[((lane >> 3) & 3) * 8 + cq + ((lane >> 2) & 1)] = cs;  // lane bits 4,3 select k, bit 2 the column of the pair
+          if (lane == 0) *cref = T;
+          // row sums: into the run, and (owner lanes) into the lower bound of the full row sum
+          float s4[4];
 #pragma unroll
-        for (int h = 0; h < 4; ++h) {
-          racc[h] = ptx::add_f32x2(racc[h], rc[h]);
-          float lo, hi;
-          ptx::unpack_f32x2(rc[h], lo, hi);
-          s4[h] = lo + hi;
-        }
-        const float s_own = quad_transpose_reduce(s4, lane, [](float x, float y) { return x + y; });
-        // candidate capture: conf_ij > thr needs e_ij > thr * (row sum) and the part of the row this warp has seen,
-        // this chunk included, bounds that sum from below: acc_ij > vlim_i in raw accumulator units
-        run_s = fminf(run_s * ptx::ex2(fminf(run_T - T, 60.f)), 1e30f) + s_own;  // (clamps keep it a finite lower bound)
-        run_T = T;
-        const float lim = thr_lim * run_s;
-        const float vlim_own = (i0 + 8 * own < p.L && lim > 0.f)
-                                   ? __fdividef(fmaxf(__log2f(lim) + T, __log2f(thr_lim) + seed_l2), p.c) : INFINITY;
+          for (int h = 0; h < 4; ++h) {
+            racc[h] = ptx::add_f32x2(racc[h], rc[h]);
+            float lo, hi;
+            ptx::unpack_f32x2(rc[h], lo, hi);
+            s4[h] = lo + hi;
+          }
+          const float s_own = quad_transpose_reduce(s4, lane, [](float x, float y) { return x + y; });
+          // candidate capture: conf_ij > thr needs e_ij > thr * (row sum) and the part of the row this warp has seen,
+          // this chunk included, bounds that sum from below: acc_ij > vlim_i in raw accumulator units
+          run_s = fminf(run_s * ptx::ex2(fminf(run_T - T, 60.f)), 1e30f) + s_own;  // (clamps keep it a finite lower bound)
+          run_T = T;
+          const float lim = thr_lim * run_s;
+          const float vlim_own = (i0 + 8 * own < p.L && lim > 0.f)
+                                     ? __fdividef(fmaxf(__log2f(lim) + T, __log2f(thr_lim) + seed_l2), p.c) : INFINITY;
 #pragma unroll
-        for (int h = 0; h < 4; ++h) vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
-        if (cmax[0] > vlim[0] || cmax[1] > vlim[1] || cmax[2] > vlim[2] || cmax[3] > vlim[3]) {  // only the lanes that hold one
+          for (int h = 0; h < 4; ++h) vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
+          if (cmax[0] > vlim[0] || cmax[1] > vlim[1] || cmax[2] > vlim[2] || cmax[3] > vlim[3]) {  // only the lanes that hold one
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < 4; ++k)
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              const int h = q >> 1, b = q & 1;
-              const float val = __uint_as_float(h < 2 ? va[4 * k + 2 * h + b] : vb[4 * k + 2 * (h - 2) + b]);
-              if (val > vlim[h]) {  // (-inf where nothing exists)
-                const int slot = atomicAdd(p.cand_count, 1);
-                if (slot < p.cand_cap)
-                  p.cand[slot] = Candidate{n_batch * p.L + i0 + 8 * h, j0 + 8 * k + cq + b, __fmul_rn(val, p.c), 2};
+              for (int q = 0; q < 8; ++q) {
+                const int h = q >> 1, b = q & 1;
+                const float val = __uint_as_float(h < 2 ? va[4 * k + 2 * h + b] : vb[4 * k + 2 * (h - 2) + b]);
+                if (val > vlim[h]) {  // (-inf where nothing exists)
+                  const int slot = atomicAdd(p.cand_count, 1);
+                  if (slot < p.cand_cap)
+                    p.cand[slot] = Candidate{n_batch * p.L + i0 + 8 * h, j0 + 8 * k + cq + b, __fmul_rn(val, p.c), 2};
+                }
               }
-            }
+          }
         }
       }
       if (++n_tile == p.n_tiles) {  // the next tile belongs to another block of rows
@@ -1896,8 +2039,10 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       if ((r = make_tmap_bf16(&fp.b_hi, w.b_hi, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
       if ((r = make_tmap_bf16(&fp.b_lo, w.b_lo, static_cast<uint64_t>(N) * Sp, C, C, SIM_BN))) return r;
     }
-    // algo 3: the register-buffered variant (sim_sweep_kernel); measured slower than sim_fast_kernel<true> on the bench
-    // workload (275 vs 200 us at 8 x 8000 x 4096), kept selectable and parity-tested.  Wider grids run out of row-record slots.
+    // algo 3: the register-buffered variant (sim_sweep_kernel: every epilogue warp on every tile, stage handed back right
+    // after the TMEM read); measured slower than sim_fast_kernel<true> on the bench workload (196 vs 181 us at
+    // 8 x 8000 x 4096: a warp's 32 x 32 chunk with its per-chunk bookkeeping takes ~2400 clk), kept selectable and
+    // parity-tested.  Wider grids run out of row-record slots.
     const bool sweep = screen && algo == 3 && (Sp + SW_BN - 1) / SW_BN <= SW_MAX_NTILES;
     static const int dbg = getenv("OPB200_SIM_DEBUG") ? atoi(getenv("OPB200_SIM_DEBUG")) : 0;
     cudaEvent_t kt0 = nullptr, kt1 = nullptr;
@@ -1963,7 +2108,7 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     }
     const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
     merge_fast_kernel<<<static_cast<unsigned>((nr + 255) / 256 + nc / 32), 256, 0, stream>>>(fp.rowpart, fp.colpart, w.tile_ref, N, L, S, Lp, Sp,
-                                                                                    w.lse_row, w.lse_col, w.counters + 2);
+                                                                                    w.lse_row, w.lse_col, w.counters + 2, SIM_BN);
     count_launch();
     }
   } else {

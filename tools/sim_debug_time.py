@@ -22,6 +22,15 @@ for _ in range(10):
     e0.record(); ops.coarse_match(f3d, f2d, **kw); e1.record(); torch.cuda.synchronize()
     ts.append(e0.elapsed_time(e1))
 print("debug", os.environ.get("OPB200_SIM_DEBUG", "0"), "coarse_match call ms (min, median):", min(ts), sorted(ts)[5])
+from onepose_st_b200 import _lib
+_lib.coarse_kernel_timing(True)  # event bracket around the sweep kernel alone (inside opb200_coarse_match)
+for _ in range(20):
+    ops.coarse_match(f3d, f2d, **kw)
+torch.cuda.synchronize()
+_lib.coarse_kernel_timing(False)
+k_ms, k_n = _lib.coarse_kernel_ms()
+print("debug", os.environ.get("OPB200_SIM_DEBUG", "0"), "algo", kw["algo"], "sweep kernel us (mean of %d back-to-back calls):" % k_n, 1e3 * k_ms / max(k_n, 1),
+      "-> TFLOP/s", 2.0 * N * L * S * C / (k_ms / max(k_n, 1)) / 1e9)
 
 if os.environ.get("OPB200_SIM_TRACE"):
     import ctypes
@@ -38,7 +47,9 @@ if os.environ.get("OPB200_SIM_TRACE"):
         t0 = int(x[cta, 0, 0])
         print(f"CTA {cta}: every 4th tile: MMA issue start, MMA issued, an epilogue warp sees full, last release of the stage (SM clocks from the first stamp)")
         for it in range(30):
-            if os.environ.get("OPB200_SIM_DEBUG") == "5":  # per quarter: epilogue clocks of that warp, flags (1 = second sweep, 2 = re-swept)
+            if os.environ.get("OPB200_SIM_DEBUG") == "8":  # one warp's profile: first TMEM read landed, chunk loop done, tail done, end (clocks since entry)
+                print(f"  {it:2d}: " + " ".join(f"{int(v):6d}" for v in x[cta, it]))
+            elif os.environ.get("OPB200_SIM_DEBUG") == "5":  # per quarter: epilogue clocks of that warp, flags (1 = second sweep, 2 = re-swept)
                 print(f"  {it:2d}: " + " ".join(f"{int(v) & ((1 << 48) - 1):6d}/{int(v) >> 48}" for v in x[cta, it]))
             else:
                 print(f"  {it:2d}: " + " ".join(f"{int(v) - t0:8d}" for v in x[cta, it]))
