@@ -330,9 +330,11 @@ struct FastCfg {
   static constexpr int BN = 128;
   static constexpr int HALVES = BN / SIM_BN;                      // 128-column halves of an accumulator, one per epilogue group
   static constexpr int TSTAGES = 512 / BN;                        // accumulator stages in TMEM
-  static constexpr int BSTAGES = SCREEN ? 8 : 2;                  // SCREEN: two tiles' worth of 16 KB k-blocks (static schedule of the MMA warp)
+  static constexpr int BSTAGES = 2;
   static constexpr int A_BYTES = PLANES * FAST_KB * FAST_SUB;     // the resident A block
-  static constexpr int BSTAGE_BYTES = PLANES * HALVES * FAST_SUB; // one B k-block: [plane][BN rows x 64]
+  // one B stage: SCREEN: a whole tile [kb][BN rows x 64] = 64 KB (one wait and one commit per tile for the MMA thread);
+  // split variant: one k-block [plane][BN rows x 64]
+  static constexpr int BSTAGE_BYTES = SCREEN ? FAST_KB * FAST_SUB : PLANES * HALVES * FAST_SUB;
   static constexpr int SMEM = 1024 + A_BYTES + BSTAGES * BSTAGE_BYTES + 512;  // + barriers, TMEM slot, tile slots
 };
 // What the screening sweep does with the bound delta on its similarity error (derived at pack_f16_kernel, below).  Capture: conf_ij > thr needs e_ij / R_i > thr; the screening sweep sees
@@ -409,6 +411,7 @@ __device__ __forceinline__ int float_key(float v) {
 }
 __device__ __forceinline__ float key_float(int k) { return __int_as_float(k ^ ((k >> 31) & 0x7fffffff)); }
 
+constexpr int kFastPipe = 2;  // epilogue schedule of sim_fast_kernel<true> (see sim_fast_epilogue)
 constexpr float kRefWindow = 60.f;  // a tile keeps its reference exponent while its maximum stays within +-60 octaves of it
 
 // Epilogue of one warp = 32 rows x 128 columns of a tile, read in the mma C-fragment layout (tmem_ld_16x256b_x4):
@@ -448,7 +451,9 @@ __device__ __forceinline__ float quad_transpose_reduce(const float (&v)[4], int 
   return op(b1 ? a1 : a0, __shfl_xor_sync(0xffffffffu, b1 ? a0 : a1, 2));
 }
 
-template <bool RAGGED, int NCH>
+// PIPE: 0 = the steps of a chunk one after the other, 1 = TMEM read of the next chunk and column butterfly of the
+// previous one overlapped with the exponentials (two register sets), 2 = only the butterfly overlapped (one set)
+template <bool RAGGED, int NCH, int PIPE = 0>
 __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32_t tmem_acc, int m_tile, int n, int mt_in_batch,
                                                   int jt, int quarter, int lane, FastWarpState& st,
                                                   uint64_t* __restrict__ tempty_bar, long long* trace_slot) {
@@ -473,6 +478,7 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
   }
   uint64_t racc[4];
   float rmax[4];  // raw accumulator maxima per row
+  uint32_t cmask = 0;  // chunks in which this thread saw an element above the limits of the previous tiles
   float ymax = kNegInf;
   bool released = false;
   auto release = [&]() {  // the accumulator is no longer needed: hand the TMEM stage back
@@ -488,19 +494,13 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     bool redo = false;
 #pragma unroll
     for (int h = 0; h < 4; ++h) racc[h] = 0ull, rmax[h] = kNegInf;
-#pragma unroll 1
-    for (int ch = 0; ch < NCH; ++ch) {
-      uint32_t va[16], vb[16];
-      if (p.debug != 4) {
-        ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
-        ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
-        ptx::tmem_ld_wait();
-        if (prof && ch == 0 && lane == 0) trace_slot[0] = clock64() - prof_t0;
-      } else {
-#pragma unroll
-        for (int q = 0; q < 16; ++q) va[q] = vb[q] = __float_as_uint(static_cast<float>(q + ch + lane));
-      }
-      if (p.debug == 3) continue;
+    cmask = 0;
+    // the four steps of a 32-column chunk
+    auto load = [&](int ch, uint32_t (&va)[16], uint32_t (&vb)[16]) {
+      ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
+      ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
+    };
+    auto head = [&](int ch, uint32_t (&va)[16], uint32_t (&vb)[16]) {  // masks, row maxima, (last chunk) the tile's verdict
       if (RAGGED) {  // rows / columns that do not exist: -inf, i.e. e = 0 and no say in the maximum
 #pragma unroll
         for (int q = 0; q < 16; ++q) {
@@ -509,13 +509,20 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
           if (!cv || !rv[2 + ((q >> 1) & 1)]) vb[q] = __float_as_uint(kNegInf);
         }
       }
+      // per-row maxima of the chunk; a chunk with an element above the limits known before this tile is remembered: only
+      // those chunks can hold a candidate (the limits only rise), so only they are read again by the candidate sweep
+      float cm[4] = {fmaxf(__uint_as_float(va[0]), __uint_as_float(va[1])), fmaxf(__uint_as_float(va[2]), __uint_as_float(va[3])),
+                     fmaxf(__uint_as_float(vb[0]), __uint_as_float(vb[1])), fmaxf(__uint_as_float(vb[2]), __uint_as_float(vb[3]))};
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        rmax[0] = ptx::max3(rmax[0], __uint_as_float(va[4 * k]), __uint_as_float(va[4 * k + 1]));
-        rmax[1] = ptx::max3(rmax[1], __uint_as_float(va[4 * k + 2]), __uint_as_float(va[4 * k + 3]));
-        rmax[2] = ptx::max3(rmax[2], __uint_as_float(vb[4 * k]), __uint_as_float(vb[4 * k + 1]));
-        rmax[3] = ptx::max3(rmax[3], __uint_as_float(vb[4 * k + 2]), __uint_as_float(vb[4 * k + 3]));
+      for (int k = 1; k < 4; ++k) {
+        cm[0] = ptx::max3(cm[0], __uint_as_float(va[4 * k]), __uint_as_float(va[4 * k + 1]));
+        cm[1] = ptx::max3(cm[1], __uint_as_float(va[4 * k + 2]), __uint_as_float(va[4 * k + 3]));
+        cm[2] = ptx::max3(cm[2], __uint_as_float(vb[4 * k]), __uint_as_float(vb[4 * k + 1]));
+        cm[3] = ptx::max3(cm[3], __uint_as_float(vb[4 * k + 2]), __uint_as_float(vb[4 * k + 3]));
       }
+#pragma unroll
+      for (int h = 0; h < 4; ++h) rmax[h] = fmaxf(rmax[h], cm[h]);
+      if (cm[0] > st.vlim[0] || cm[1] > st.vlim[1] || cm[2] > st.vlim[2] || cm[3] > st.vlim[3]) cmask |= 1u << ch;
       if (ch == NCH - 1) {
         // Everything of the tile is in registers or behind us.  Its maximum decides whether T held (else: once more
         // with T = the maximum), and if no element beats even the limits known before this tile -- which can only
@@ -526,7 +533,8 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
         const bool maybe = rmax[0] > st.vlim[0] || rmax[1] > st.vlim[1] || rmax[2] > st.vlim[2] || rmax[3] > st.vlim[3];
         if (!redo && !__any_sync(0xffffffffu, maybe)) release();
       }
-      float f[4][2];
+    };
+    auto exps = [&](const uint32_t (&va)[16], const uint32_t (&vb)[16], float (&f)[4][2]) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const uint64_t e0 = exp2_pair(va[4 * k], va[4 * k + 1], c2, t2), e1 = exp2_pair(va[4 * k + 2], va[4 * k + 3], c2, t2);
@@ -537,6 +545,8 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
         racc[3] = ptx::add_f32x2(racc[3], e3);
         ptx::unpack_f32x2(ptx::add_f32x2(ptx::add_f32x2(e0, e1), ptx::add_f32x2(e2, e3)), f[k][0], f[k][1]);
       }
+    };
+    auto cols = [&](int ch, const float (&f)[4][2]) {
       // halving butterfly over the row bits of the lane id (16, 8, 4): 4 + 2 + 1 shuffles
       float g[2][2], hh[2];
       {
@@ -563,6 +573,56 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
       const float cs = (up4 ? hh[1] : hh[0]) + __shfl_xor_sync(0xffffffffu, up4 ? hh[0] : hh[1], 4);
       // lane bits 4,3 select k, bit 2 selects the column of the pair
       colp[ch * 32 + ((lane >> 3) & 3) * 8 + cq + ((lane >> 2) & 1)] = cs;  // (a repeated sweep overwrites it)
+    };
+    if constexpr (PIPE == 1) {
+      // Software pipeline over two register sets: the TMEM read of chunk ch + 1 is in flight while chunk ch is
+      // exponentiated, and the column butterfly of chunk ch - 1 (shuffle latency) runs between its MUFU instructions.
+      // A warp alone needs ~1250 clk for a chunk when the three steps run one after the other -- latency, not
+      // throughput -- and twelve to sixteen warps per SM are too few to hide that from each other.
+      uint32_t v[2][2][16];
+      float f[2][4][2];
+      load(0, v[0][0], v[0][1]);
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch) {
+        ptx::tmem_ld_wait();
+        if (prof && ch == 0 && lane == 0) trace_slot[0] = clock64() - prof_t0;
+        if (ch + 1 < NCH) load(ch + 1, v[(ch + 1) & 1][0], v[(ch + 1) & 1][1]);
+        head(ch, v[ch & 1][0], v[ch & 1][1]);
+        exps(v[ch & 1][0], v[ch & 1][1], f[ch & 1]);
+        if (ch > 0) cols(ch - 1, f[(ch - 1) & 1]);
+      }
+      cols(NCH - 1, f[(NCH - 1) & 1]);
+    } else if constexpr (PIPE == 2) {
+      float f[2][4][2];
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch) {
+        uint32_t va[16], vb[16];
+        load(ch, va, vb);
+        ptx::tmem_ld_wait();
+        if (prof && ch == 0 && lane == 0) trace_slot[0] = clock64() - prof_t0;
+        head(ch, va, vb);
+        exps(va, vb, f[ch & 1]);
+        if (ch > 0) cols(ch - 1, f[(ch - 1) & 1]);
+      }
+      cols(NCH - 1, f[(NCH - 1) & 1]);
+    } else {
+#pragma unroll 1
+      for (int ch = 0; ch < NCH; ++ch) {
+        uint32_t va[16], vb[16];
+        if (p.debug != 4) {
+          load(ch, va, vb);
+          ptx::tmem_ld_wait();
+          if (prof && ch == 0 && lane == 0) trace_slot[0] = clock64() - prof_t0;
+        } else {
+#pragma unroll
+          for (int q = 0; q < 16; ++q) va[q] = vb[q] = __float_as_uint(static_cast<float>(q + ch + lane));
+        }
+        if (p.debug == 3) continue;
+        head(ch, va, vb);
+        float f[4][2];
+        exps(va, vb, f);
+        cols(ch, f);
+      }
     }
     if (!redo) break;
     st.dbg_flags |= 2;
@@ -584,7 +644,8 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
   if (lane == 0) p.tile_ref[(static_cast<long long>(m_tile) * 4 + quarter) * (p.Sp / (32 * NCH)) + jt / (32 * NCH)] = empty ? kNegInf : T;
   // candidate capture: conf_ij > thr needs e_ij > thr * (row sum), and the part of the row this warp has seen so far
   // bounds that sum from below, i.e. acc_ij > vlim_i in raw accumulator units -- one compare per element on a second
-  // sweep over TMEM, taken only when some row of the warp has its maximum above the limit
+  // read of the flagged chunks, taken only when some row of the warp has its maximum above the new limit
+  bool sweep = false;
   if (!empty) {
     // (clamps keep it a finite lower bound when the reference moves far down)
     st.run_s = fminf(st.run_s * ptx::ex2(fminf(st.run_T - T, 60.f)), 1e30f) + s_own;
@@ -597,46 +658,49 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
 #pragma unroll
     for (int h = 0; h < 4; ++h) st.vlim[h] = __shfl_sync(0xffffffffu, vlim_own, (lane & ~3) + h);
     if (prof && lane == 0) trace_slot[2] = clock64() - prof_t0;
-    if (__any_sync(0xffffffffu, trig)) {
-      st.dbg_flags |= 1;
+    sweep = __any_sync(0xffffffffu, trig);
+    st.T = ymax;  // the next tile's guess
+  }
+  if (sweep) {
+    st.dbg_flags |= 1;
 #pragma unroll 1
-      for (int ch = 0; ch < NCH; ++ch) {
-        uint32_t va[16], vb[16];
-        ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, va);
-        ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, vb);
-        ptx::tmem_ld_wait();
-        // (the epilogue warps are issue-bound while four of them share a scheduler: the per-row maxima cost 16 + 4
-        // instructions where a compare per element costs 64, and most chunks hold no candidate)
-        float cm[4] = {kNegInf, kNegInf, kNegInf, kNegInf};
+    for (uint32_t todo = __reduce_or_sync(0xffffffffu, cmask); todo != 0; todo &= todo - 1) {
+      const int ch = __ffs(todo) - 1;
+      uint32_t sa[16], sb[16];
+      ptx::tmem_ld_16x256b_x4(tmem_acc + ch * 32, sa);
+      ptx::tmem_ld_16x256b_x4(tmem_acc + (16u << 16) + ch * 32, sb);
+      ptx::tmem_ld_wait();
+      if ((todo & (todo - 1)) == 0) release();  // the last flagged chunk is in registers: the accumulator goes back before the walk
+      // (the per-row maxima cost 16 + 4 instructions where a compare per element costs 64, and a flagged chunk need not
+      // hold an element above the NEW limits)
+      float cm[4] = {kNegInf, kNegInf, kNegInf, kNegInf};
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          cm[0] = ptx::max3(cm[0], __uint_as_float(va[4 * k]), __uint_as_float(va[4 * k + 1]));
-          cm[1] = ptx::max3(cm[1], __uint_as_float(va[4 * k + 2]), __uint_as_float(va[4 * k + 3]));
-          cm[2] = ptx::max3(cm[2], __uint_as_float(vb[4 * k]), __uint_as_float(vb[4 * k + 1]));
-          cm[3] = ptx::max3(cm[3], __uint_as_float(vb[4 * k + 2]), __uint_as_float(vb[4 * k + 3]));
-        }
-        const bool any = cm[0] > st.vlim[0] || cm[1] > st.vlim[1] || cm[2] > st.vlim[2] || cm[3] > st.vlim[3];
-        if (!__any_sync(0xffffffffu, any)) continue;
-        // row by row, so that the warp only walks the eight elements of rows that do hold a candidate
+      for (int k = 0; k < 4; ++k) {
+        cm[0] = ptx::max3(cm[0], __uint_as_float(sa[4 * k]), __uint_as_float(sa[4 * k + 1]));
+        cm[1] = ptx::max3(cm[1], __uint_as_float(sa[4 * k + 2]), __uint_as_float(sa[4 * k + 3]));
+        cm[2] = ptx::max3(cm[2], __uint_as_float(sb[4 * k]), __uint_as_float(sb[4 * k + 1]));
+        cm[3] = ptx::max3(cm[3], __uint_as_float(sb[4 * k + 2]), __uint_as_float(sb[4 * k + 3]));
+      }
+      const bool any = cm[0] > st.vlim[0] || cm[1] > st.vlim[1] || cm[2] > st.vlim[2] || cm[3] > st.vlim[3];
+      if (!__any_sync(0xffffffffu, any)) continue;
+      // row by row, so that the warp only walks the eight elements of rows that do hold a candidate
 #pragma unroll
-        for (int h = 0; h < 4; ++h) {
-          if (cm[h] > st.vlim[h]) {
+      for (int h = 0; h < 4; ++h) {
+        if (cm[h] > st.vlim[h]) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+          for (int k = 0; k < 4; ++k)
 #pragma unroll
-              for (int b = 0; b < 2; ++b) {
-                const float val = __uint_as_float(h < 2 ? va[4 * k + 2 * h + b] : vb[4 * k + 2 * (h - 2) + b]);
-                const int j = jt + ch * 32 + 8 * k + cq + b;
-                if (val > st.vlim[h] && (!RAGGED || j < p.S)) {
-                  const int slot = atomicAdd(p.cand_count, 1);
-                  if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i0 + 8 * h, j, __fmul_rn(val, p.c), p.cand_tag};
-                }
+            for (int b = 0; b < 2; ++b) {
+              const float val = __uint_as_float(h < 2 ? sa[4 * k + 2 * h + b] : sb[4 * k + 2 * (h - 2) + b]);
+              const int j = jt + ch * 32 + 8 * k + cq + b;
+              if (val > st.vlim[h] && (!RAGGED || j < p.S)) {
+                const int slot = atomicAdd(p.cand_count, 1);
+                if (slot < p.cand_cap) p.cand[slot] = Candidate{n * p.L + i0 + 8 * h, j, __fmul_rn(val, p.c), p.cand_tag};
               }
-          }
+            }
         }
       }
     }
-    st.T = ymax;  // the next tile's guess
   }
   if (!released) release();
   if (prof && lane == 0) trace_slot[3] = clock64() - prof_t0;
@@ -735,6 +799,21 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
           new_a = false;
         }
         const int b_row = b_row0 + n_tile * BN;
+        if constexpr (SCREEN) {  // one stage = the tile's four k-blocks
+          ptx::mbar_wait(&b_empty[stage], phase ^ 1);
+          if (p.debug == 6) {  // experiment: the B stages are declared full without loading anything
+            ptx::mbar_arrive(&b_full[stage]);
+          } else {
+            ptx::mbar_arrive_expect_tx(&b_full[stage], FAST_BSTAGE_BYTES);
+#pragma unroll
+            for (int kb = 0; kb < FAST_KB; ++kb)
+              ptx::tma_load_2d(smem_b + stage * FAST_BSTAGE_BYTES + kb * FAST_SUB, &p.b_hi, &b_full[stage], kb * BLOCK_K, b_row);
+          }
+          if (++stage == FAST_BSTAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        } else {
 #pragma unroll
         for (int kb = 0; kb < FAST_KB; ++kb) {
           ptx::mbar_wait(&b_empty[stage], phase ^ 1);
@@ -754,6 +833,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
             stage = 0;
             phase ^= 1;
           }
+        }
         }
         if (++n_tile == p.n_tiles) {
           n_tile = 0, ++m_tile, new_a = true;
@@ -775,13 +855,13 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
     //   waits for a refill -- 190 us against 181: the two warps of a group that share a scheduler move in step and
     //   their MUFU bursts collide, 1300 clk per 32 x 32 chunk against 950 with four groups on four different tiles.)
     if constexpr (SCREEN) {
-      static_assert(FAST_BSTAGES == 2 * FAST_KB && TSTAGES == 4, "the unrolled schedule assumes an 8-stage B ring and 4 accumulators");
+      static_assert(FAST_BSTAGES == 2 && TSTAGES == 4, "the unrolled schedule assumes two B stages and 4 accumulators");
       if (ptx::elect_one()) {
         constexpr uint32_t idesc = ptx::make_idesc_f16(BLOCK_M, BN);
         constexpr int kDescPerStage = FAST_BSTAGE_BYTES >> 4;
         const uint64_t a_desc0 = ptx::make_desc_sw128(ptx::smem_u32(smem_a));
         const uint64_t b_desc0 = ptx::make_desc_sw128(ptx::smem_u32(smem_b));
-        const bool no_mma = p.debug == 2 || p.debug == 7;
+        const uint32_t slot_a = ptx::smem_u32(const_cast<int4*>(tile_slot));
         const bool trace_on = p.debug != 5 && p.debug != 8 && p.trace != nullptr;
         const int n_it = t_end - t_begin;
         uint32_t a_phase = 0;
@@ -824,24 +904,21 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
             }
             take_stage();
             ptx::tc_fence_after();
-            tile_slot[g].x = m_tile, tile_slot[g].y = n_tile, tile_slot[g].z = it;
-            __threadfence_block();
+            // (plain store: the group reads the slot after the stage's full barrier, which the commit below arrives on
+            // once the MMAs issued after this store have completed)
+            ptx::st_shared_v4(slot_a + 16 * g, m_tile, n_tile, it, 0);
             const bool tr = trace_on && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta;
             if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 0] = clock64();
             const uint32_t d_tmem = tmem_base + g * BN;
+            ptx::mbar_wait(&b_full[u], static_cast<uint32_t>((it0 >> 1) & 1));
+            ptx::tc_fence_after();
 #pragma unroll
-            for (int kb = 0; kb < FAST_KB; ++kb) {
-              const int stage = u * FAST_KB + kb;
-              ptx::mbar_wait(&b_full[stage], static_cast<uint32_t>((it0 >> 1) & 1));
-              ptx::tc_fence_after();
-              if (!no_mma) {
+            for (int kb = 0; kb < FAST_KB; ++kb)
 #pragma unroll
-                for (int k = 0; k < BLOCK_K / 16; ++k)
-                  ptx::mma_bf16(d_tmem, a_desc0 + static_cast<uint64_t>(kb * (FAST_SUB >> 4) + 2 * k),
-                                b_desc0 + static_cast<uint64_t>(stage * kDescPerStage + 2 * k), idesc, (kb | k) != 0);
-              }
-              ptx::mma_commit(&b_empty[stage]);
-            }
+              for (int k = 0; k < BLOCK_K / 16; ++k)
+                ptx::mma_bf16(d_tmem, a_desc0 + static_cast<uint64_t>(kb * (FAST_SUB >> 4) + 2 * k),
+                              b_desc0 + static_cast<uint64_t>(u * kDescPerStage + kb * (FAST_SUB >> 4) + 2 * k), idesc, (kb | k) != 0);
+            ptx::mma_commit(&b_empty[u]);
             ptx::mma_commit(&tfull[g]);
             if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 1] = clock64();
             const bool last_n = ++n_tile == p.n_tiles;
@@ -852,7 +929,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
         // the list is exhausted: every group gets the end marker once its stage is free again
         for (int q = 0; q < TSTAGES; ++q) {
           ptx::mbar_wait(&tempty[q], (te_par >> q) & 1u);
-          tile_slot[q].x = -1;
+          ptx::st_shared_v4(slot_a + 16 * q, -1, 0, 0, 0);
           __threadfence_block();
           ptx::mbar_arrive(&tfull[q]);
         }
@@ -930,9 +1007,10 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
       for (int cnt = 0;; ++cnt) {
         ptx::mbar_wait(&tfull[tstage], cnt & 1);
         ptx::tc_fence_after();
-        const int mt = tile_slot[tstage].x;
+        const int4 slot = ptx::ld_shared_v4(ptx::smem_u32(const_cast<int4*>(tile_slot)) + 16 * tstage);
+        const int mt = slot.x;
         if (mt < 0) break;
-        const int n_tile = tile_slot[tstage].y, it_e = tile_slot[tstage].z;
+        const int n_tile = slot.y, it_e = slot.z;
         if (mt != m_tile) m_tile = mt, n_batch = mt / tiles_per_batch, mt_in_batch = mt - n_batch * tiles_per_batch;
         const bool tr = p.debug != 5 && p.trace != nullptr && (it_e & 3) == 0 && (it_e >> 2) < kTraceTilesPerCta &&
                         (p.debug != 8 || quarter == 0);  // all four warps: first / last (mode 8: one warp's profile)
@@ -946,7 +1024,7 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
           st.dbg_flags = 0;
           long long* tslot = tr ? &p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + (p.debug == 8 ? 0 : 3)] : nullptr;
           if (ragged) sim_fast_epilogue<true, 4>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage], tslot);
-          else sim_fast_epilogue<false, 4>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage], tslot);
+          else sim_fast_epilogue<false, 4, kFastPipe>(p, tacc, m_tile, n_batch, mt_in_batch, jt, quarter, lane, st, &tempty[tstage], tslot);
           if (tr5 && lane == 0)  // mode 5: the slot holds, per quarter, this warp's epilogue time and flags instead of the four stamps
             p.trace[(blockIdx.x * kTraceTilesPerCta + (it_e >> 2)) * 4 + quarter] = (clock64() - t5) | (static_cast<long long>(st.dbg_flags) << 48);
         } else {
@@ -993,6 +1071,13 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
     ptx::tmem_dealloc(tmem_base, 512);
   }
 }
+
+// (Measured and dropped -- "mailbox" variant: THREE epilogue groups on the four accumulator stages, tiles addressed to a
+// group through a two-deep mailbox so that the fourth stage refills while three are in work, 512 threads = 128 registers,
+// the epilogue fully software-pipelined over two register sets (TMEM read of chunk ch + 1 in flight, butterfly of chunk
+// ch - 1 between the MUFU instructions).  A warp's tile fell from ~5000 to ~3000 clk, the kernel went from 184 to
+// 217-233 us: with epilogue warps that issue densely the single MMA-issuing thread gets its instructions in later
+// (1600-1800 clk per tile instead of 1200) and becomes the limit.)
 
 // Partial sums of the single-pass sweep -> (reference, log2 sum) per row and per column.  The reference of a part is
 // that of the warp block it came from (tile_ref) and is the same for the 32 consecutive rows / columns a warp owns, so a

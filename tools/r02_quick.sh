@@ -10,3 +10,4 @@ d=json.load(open('gpurun_out/quick_bench.json'))
 print("value", round(d["value"],1), "e2e", round(d["e2e"]["value"],1), "roofline", round(d["roofline"]["frac"],4), "kernel ms", round(d["roofline"]["launch"]["avg_ms_per_launch"],5), "op", round(d["roofline"]["op_level"].get("frac",0),4))
 print(d["stages_ms_per_frame"]); print("parity", d.get("parity"))
 P
+for d in 0 1; do timeout 120 python tools/clock_probe.py $d 2>&1 | tail -1; done

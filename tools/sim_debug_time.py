@@ -8,6 +8,9 @@ the per-tile SM-clock stamps of two CTAs (opb200_debug_trace).  OPB200_SIM_DEBUG
 candidates per call."""
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from onepose_st_b200 import _lib as _lib0
+if os.environ.get("OPB200_LIB_ALT"):  # A/B on one box: another build of the library
+    _lib0.LIB_PATH = os.path.abspath(os.environ["OPB200_LIB_ALT"])
 from onepose_st_b200 import ops, synthetic
 N, L, S, C = 8, 8000, 4096, 256
 f3d, f2d = synthetic.planted_coarse_pair(21, N, L, S, C, 1000, 64, 64, device="cuda")
@@ -46,7 +49,7 @@ if os.environ.get("OPB200_SIM_TRACE"):
     for cta in (0, 77):
         t0 = int(x[cta, 0, 0])
         print(f"CTA {cta}: every 4th tile: MMA issue start, MMA issued, an epilogue warp sees full, last release of the stage (SM clocks from the first stamp)")
-        for it in range(30):
+        for it in range(32):
             if os.environ.get("OPB200_SIM_DEBUG") == "8":  # one warp's profile: first TMEM read landed, chunk loop done, tail done, end (clocks since entry)
                 print(f"  {it:2d}: " + " ".join(f"{int(v):6d}" for v in x[cta, it]))
             elif os.environ.get("OPB200_SIM_DEBUG") == "5":  # per quarter: epilogue clocks of that warp, flags (1 = second sweep, 2 = re-swept)
