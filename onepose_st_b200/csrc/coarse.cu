@@ -1072,6 +1072,10 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   }
 }
 
+// (Measured and dropped once more in round 2, with the Jensen seed in place and only the 8000 genuine candidates left to
+// capture: taking the candidates from the registers of the main pass, against the limits known before the tile, so that
+// no accumulator is ever read twice -- 256 us against 181, same box: the walk inside the chunk loop costs the hot path
+// its registers (96 bytes of spills) although it runs for about one chunk in thirty.)
 // (Measured and dropped -- "mailbox" variant: THREE epilogue groups on the four accumulator stages, tiles addressed to a
 // group through a two-deep mailbox so that the fourth stage refills while three are in work, 512 threads = 128 registers,
 // the epilogue fully software-pipelined over two register sets (TMEM read of chunk ch + 1 in flight, butterfly of chunk
