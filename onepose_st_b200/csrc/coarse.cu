@@ -440,6 +440,7 @@ struct FastWarpState {
   float thr_lim = 0.f;    // candidate limit relative to the row sum
   float seed_shift = 0.f; // SCREEN: log2(2^delta * 0.99): what turns row_lb into a bound of the screened sums
   float seed_l2 = kNegInf;  // owner lane: log2 of the a-priori lower bound of its row's sum
+  float T_rows = 0.f;     // SCREEN: the reference guess of the current block of rows (a function of the rows alone)
 };
 
 // lane t <- reduction over its quad (lanes t ^ 1, t ^ 2, t ^ 3) of v[t % 4]
@@ -475,7 +476,18 @@ __device__ __forceinline__ void sim_fast_epilogue(const SimFastParams& p, uint32
     const float v0 = st.seed_l2 > kNegInf ? __fdividef(__log2f(st.thr_lim) + st.seed_l2, p.c) : kNegInf;
 #pragma unroll
     for (int h = 0; h < 4; ++h) st.vlim[h] = __shfl_sync(0xffffffffu, v0, (lane & ~3) + h);
+    // Reference guess of the screening sweep: the largest MEAN similarity among the warp's 32 rows (what the Jensen
+    // bound is made of) plus 8 octaves.  It depends on the rows alone -- not on which tile this warp happened to
+    // process before, which the tile slots leave to chance -- so the sums, and with them every confidence, come out
+    // bit-identical from run to run and for any number of GPUs; a block whose maximum lies outside T - 60 .. T + 60 is
+    // swept again with T = that maximum (data-determined as well).
+    if (p.row_lb != nullptr) {
+      const float mean_y = st.seed_l2 > kNegInf ? st.seed_l2 - st.seed_shift - __log2f(static_cast<float>(p.S)) : kNegInf;
+      const float top = key_float(__reduce_max_sync(0xffffffffu, float_key(mean_y)));
+      st.T_rows = top > kNegInf ? top + 8.f : 0.f;
+    }
   }
+  if (p.row_lb != nullptr) T = st.T_rows;
   uint64_t racc[4];
   float rmax[4];  // raw accumulator maxima per row
   uint32_t cmask = 0;  // chunks in which this thread saw an element above the limits of the previous tiles
@@ -1757,10 +1769,12 @@ __global__ void __launch_bounds__(256) cand_rescore_kernel(Candidate* __restrict
                                                            unsigned long long* __restrict__ rowdelta,
                                                            unsigned long long* __restrict__ coldelta,
                                                            unsigned* __restrict__ observed /* bits of max |y - y_screen| */,
-                                                           int* __restrict__ needs_robust) {
+                                                           int* __restrict__ needs_robust, const unsigned* __restrict__ norm_sq,
+                                                           float thr, float max_delta) {
   const int n_c = min(*count, cap);
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
+  const float log2_thr_lim = log2f(screen_plan(norm_sq, c, thr, max_delta).thr_lim);
   for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < n_c; t += warps) {
     const Candidate cd = cand[t];
     if (cd.pad != 2) continue;
@@ -1787,6 +1801,14 @@ __global__ void __launch_bounds__(256) cand_rescore_kernel(Candidate* __restrict
     if (lane == 0) {
       const float y = __fmul_rn(acc, c);
       const float2 lr = lse_row[ra], lc = lse_col[rb];
+      // Which near misses the sweep listed depends on the order in which its warps met the tiles; what is exchanged
+      // must not.  An element that can reach thr has its screening row-softmax above thr_lim (the sweep's own capture
+      // condition, here against the FINAL row sum): everything else is dropped, so the exchanged set -- and every sum
+      // and confidence after it -- is a function of the data alone.
+      if (!((cd.conf - lr.x) - lr.y > log2_thr_lim)) {
+        cand[t].conf = kNegInf;
+        continue;
+      }
       const float dr = exp2f((y - lr.x) - lr.y) - exp2f((cd.conf - lr.x) - lr.y);
       const float dc = exp2f((y - lc.x) - lc.y) - exp2f((cd.conf - lc.x) - lc.y);
       atomicAdd(&rowdelta[ra], static_cast<unsigned long long>(__double2ll_rn(static_cast<double>(dr) * kDeltaScale)));
@@ -2250,7 +2272,8 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
   if (screen) {
     cand_rescore_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, Lp, Sp, w.a_hi, w.a_lo, w.b_hi, w.b_lo,
                                                 scale * kLog2e, w.lse_row, w.lse_col, w.rowdelta, w.coldelta,
-                                                reinterpret_cast<unsigned*>(w.counters + 6), w.counters + 2);
+                                                reinterpret_cast<unsigned*>(w.counters + 6), w.counters + 2,
+                                                reinterpret_cast<const unsigned*>(w.counters + 4), thr, g_screen_max_delta);
     count_launch();
   }
   cand_max_kernel<<<cb, 256, 0, stream>>>(w.cand, w.counters, w.cand_cap, L, S, w.lse_row, w.lse_col, Lp, Sp, thr, w.rowdelta,

@@ -323,3 +323,30 @@ def test_bench_shape_default_path_vs_two_pass():
     err = max(abs(fi[k_] - ai[k_]) for k_ in got & want)
     print(f"bench shape: M={len(got)}, set diff vs two-pass {len(got ^ want)}, mconf vs two-pass {err:.2e}, vs fp64 {worst:.2e}")
     assert len(got) > 4000 and len(got ^ want) <= 4 and err < CONF_TOL and worst < CONF_TOL
+
+
+def test_default_sweep_is_reproducible_bitwise():
+    """The default single-pass sweep hands its accumulator stages to whichever epilogue group is free, so the order in
+    which a warp meets the tiles differs from call to call.  Nothing it outputs may depend on that order: the reference
+    exponent of a block of rows is a function of the rows (their mean similarity), and the set of captured elements
+    whose terms are exchanged in the sums is canonical.  Repeated calls -- and a call that is disturbed by another
+    kernel running beside it -- must return bit-identical ids and confidences (what lets the N-GPU gather be compared
+    with the 1-GPU one by a checksum)."""
+    from onepose_st_b200 import ops
+    dev = "cuda"
+    f3d, f2d = cases.planted_pair(33, 4, 4000, 4096, 256, 1500, 64, 64, 2, gain=0.6)
+    f3d, f2d = f3d.to(dev), f2d.to(dev)
+    kw = dict(scale=1.0 / (256 * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=(64, 64), algo=0)
+    first = [t.clone() for t in ops.coarse_match(f3d, f2d, **kw)[:4]]
+    assert len(first[0]) > 1000
+    side = torch.cuda.Stream()
+    busy = torch.randn(4096, 4096, device=dev)
+    for rep in range(6):
+        if rep % 2:  # a second stream keeps some SMs busy: the sweep's CTAs then run with different timing
+            with torch.cuda.stream(side):
+                for _ in range(4):
+                    busy = busy @ busy * 1e-3
+        got = ops.coarse_match(f3d, f2d, **kw)[:4]
+        torch.cuda.synchronize()
+        for x, y in zip(first, got):
+            assert torch.equal(x, y), f"call {rep} differs from the first one"
