@@ -52,6 +52,7 @@ struct EpiQKV {
     float* q_f32;                // phi(Q) fp32 [R,C]   (small groups)
     float *k_f32, *v_f32;        // phi(K), V fp32 [R,C]
     const uint8_t* row_mask;     // [R], 1 = valid
+    __nv_bfloat16 *k_hi, *k_lo, *v_hi, *v_lo;  // big groups, tensor-core KV: phi(K), V as bf16 planes [R,C] instead of fp32
   };
   static constexpr int kSmemBytes = 0;
   static constexpr int CPT = C / EPI_SPLIT;
@@ -72,6 +73,9 @@ struct EpiQKV {
       }
       if (ctx.n_tile == 0 && p.q_f32 == nullptr) {
         store_planes32_v8(v, p.q_hi + row * C + c0, p.q_lo ? p.q_lo + row * C + c0 : nullptr);
+      } else if (ctx.n_tile != 0 && p.k_hi != nullptr) {
+        if (ctx.n_tile == 1) store_planes32_v8(v, p.k_hi + row * C + c0, p.k_lo ? p.k_lo + row * C + c0 : nullptr);
+        else store_planes32_v8(v, p.v_hi + row * C + c0, p.v_lo ? p.v_lo + row * C + c0 : nullptr);
       } else {
         store_f32x32_v8(v, (ctx.n_tile == 0 ? p.q_f32 : ctx.n_tile == 1 ? p.k_f32 : p.v_f32) + row * C + c0);
       }
@@ -397,6 +401,162 @@ __global__ void __launch_bounds__(128) kv_partial_kernel(const float* __restrict
   out[32 * 128] = make_float2(ksum0, ksum1);
 }
 
+// ------------------------------------------------------------------------------------------------
+// KV = phi(K)^T V and Ksum on the tensor cores (north_star (a); replaces kv_partial_kernel for the coarse level).
+//
+// The contraction runs over the TOKENS, i.e. over the rows of the row-major [R, 256] planes, so both operands are
+// MN-major: a TMA box {64 channels, 64 tokens} with the 128-byte swizzle is exactly the canonical MN-major tile
+// (row = token = 128 bytes, eight tokens per swizzle atom; LBO = 8192 = distance to the next 64 channels, SBO = 1024,
+// 16 tokens = +2048 bytes per MMA; tools/probes/mn_major_probe.cu).  One CTA = (split of the token range, group,
+// half of the heads): D[128 d-channels x 128 v-channels] += phi(K)^T V over its tokens with the three split products
+// (hi*hi + lo*hi + hi*lo), of which the four diagonal 32 x 32 blocks are the KV of heads 4*half .. 4*half+3 (the
+// off-diagonal blocks are the price of a 128-row MMA: 4x the flops of an op that is HBM-bound at 8 flop/B anyway), and
+// D[:, 128..143] += phi(K)^T 1 against a constant K-major tile of ones = Ksum.  Partials go to the same
+// [g][split][33][256] records kv_pack_kernel folds (deterministic: fixed split ranges, fixed order).
+//   warp 0: TMA thread (8 boxes = 64 KB per 64-token stage, 3 stages), warp 1: MMA thread, warps 2-5: epilogue.
+constexpr int KVT_STAGES = 3;
+constexpr int KVT_BOX = 64 * 128;                 // one box: 64 tokens x 64 channels x 2 B
+constexpr int KVT_STAGE_BYTES = 8 * KVT_BOX;      // {K hi, K lo, V hi, V lo} x two boxes of 64 channels
+constexpr int KVT_ONES_BYTES = 16 * 128;          // K-major [16 x 64] tile of ones
+constexpr int KVT_SMEM = 1024 + KVT_STAGES * KVT_STAGE_BYTES + KVT_ONES_BYTES + 256;
+
+struct KvTcParams {
+  CUtensorMap k_hi, k_lo, v_hi, v_lo;  // [R, 256] bf16, box {64 channels, 64 tokens}, 128B swizzle
+  GroupTable gt;
+  unsigned long long group_sel;
+  float* partial;
+  int max_chunks, n_splits, x3;
+};
+
+__device__ __forceinline__ uint64_t make_desc_mn_sw128(uint32_t smem_addr) {  // MN-major, two 64-wide boxes 8192 B apart
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>(8192 >> 4) << 16;
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+
+__global__ void __launch_bounds__(192, 1) kv_tc_kernel(const __grid_constant__ KvTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* ones = smem + KVT_STAGES * KVT_STAGE_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(ones + KVT_ONES_BYTES);
+  uint64_t* empty = full + KVT_STAGES;
+  uint64_t* done = empty + KVT_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int split = blockIdx.x, g = blockIdx.y, half = blockIdx.z;
+  if (!((p.group_sel >> g) & 1ull)) return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nkb = (p.gt.len[g] + 63) / 64;  // 64-token blocks of the group (its rows are padded to 128 with zeros)
+  const int kb0 = static_cast<int>(static_cast<long long>(nkb) * split / p.n_splits);
+  const int kb1 = static_cast<int>(static_cast<long long>(nkb) * (split + 1) / p.n_splits);
+  float* out = p.partial + (static_cast<long long>(g) * p.max_chunks + split) * (KV_REC * 256) + half * 128;
+  if (kb1 <= kb0) {  // nothing to add: the record still has to exist
+    for (int i = threadIdx.x; i < KV_REC * 128; i += blockDim.x) out[(i >> 7) * 256 + (i & 127)] = 0.f;
+    return;
+  }
+  for (int i = threadIdx.x; i < KVT_ONES_BYTES / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(ones)[i] = 0x3F803F80u;  // bf16 1.0
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&p.k_hi);
+    ptx::prefetch_tmap(&p.v_hi);
+    for (int s = 0; s < KVT_STAGES; ++s) {
+      ptx::mbar_init(&full[s], 1);
+      ptx::mbar_init(&empty[s], 1);
+    }
+    ptx::mbar_init(done, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, 256);
+    ptx::tmem_relinquish();
+  }
+  ptx::fence_proxy_async();  // the ones tile is read by the tensor core (async proxy)
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int row0 = p.gt.row_start[g];
+  const int planes = p.x3 ? 4 : 2;
+
+  if (warp == 0) {
+    if (ptx::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        ptx::mbar_wait(&empty[stage], phase ^ 1);
+        ptx::mbar_arrive_expect_tx(&full[stage], planes * 2 * KVT_BOX);
+        uint8_t* st = smem + stage * KVT_STAGE_BYTES;
+        const int tok = row0 + kb * 64;
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          const int ch = half * 128 + b * 64;
+          ptx::tma_load_2d(st + (0 + b) * KVT_BOX, &p.k_hi, &full[stage], ch, tok);
+          ptx::tma_load_2d(st + (4 + b) * KVT_BOX, &p.v_hi, &full[stage], ch, tok);
+          if (p.x3) {
+            ptx::tma_load_2d(st + (2 + b) * KVT_BOX, &p.k_lo, &full[stage], ch, tok);
+            ptx::tma_load_2d(st + (6 + b) * KVT_BOX, &p.v_lo, &full[stage], ch, tok);
+          }
+        }
+        if (++stage == KVT_STAGES) stage = 0, phase ^= 1;
+      }
+    }
+  } else if (warp == 1) {
+    if (ptx::elect_one()) {
+      constexpr uint32_t kMN = (1u << 15) | (1u << 16);  // a_major, b_major = MN
+      constexpr uint32_t idesc_kv = ptx::make_idesc_bf16(BLOCK_M, 128) | kMN;
+      constexpr uint32_t idesc_ks = ptx::make_idesc_bf16(BLOCK_M, 16) | (1u << 15);  // A MN-major, B (ones) K-major
+      const uint64_t ones_desc = ptx::make_desc_sw128(ptx::smem_u32(ones));
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        ptx::mbar_wait(&full[stage], phase);
+        ptx::tc_fence_after();
+        const uint32_t sa = ptx::smem_u32(smem + stage * KVT_STAGE_BYTES);
+        const uint64_t kh = make_desc_mn_sw128(sa), kl = make_desc_mn_sw128(sa + 2 * KVT_BOX);
+        const uint64_t vh = make_desc_mn_sw128(sa + 4 * KVT_BOX), vl = make_desc_mn_sw128(sa + 6 * KVT_BOX);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {  // 16 tokens per MMA: +2048 bytes in the MN-major tiles, +32 bytes in the ones tile
+          const bool first = kb == kb0 && k == 0;
+          if (p.x3) {
+            ptx::mma_bf16(tmem_base, kh + 128 * k, vl + 128 * k, idesc_kv, !first);
+            ptx::mma_bf16(tmem_base, kl + 128 * k, vh + 128 * k, idesc_kv, 1);
+            ptx::mma_bf16(tmem_base, kh + 128 * k, vh + 128 * k, idesc_kv, 1);
+            ptx::mma_bf16(tmem_base + 128, kl + 128 * k, ones_desc + 2 * k, idesc_ks, !first);
+            ptx::mma_bf16(tmem_base + 128, kh + 128 * k, ones_desc + 2 * k, idesc_ks, 1);
+          } else {
+            ptx::mma_bf16(tmem_base, kh + 128 * k, vh + 128 * k, idesc_kv, !first);
+            ptx::mma_bf16(tmem_base + 128, kh + 128 * k, ones_desc + 2 * k, idesc_ks, !first);
+          }
+        }
+        ptx::mma_commit(&empty[stage]);
+        if (++stage == KVT_STAGES) stage = 0, phase ^= 1;
+      }
+      ptx::mma_commit(done);
+    }
+  } else {
+    // epilogue: TMEM lanes 32q .. 32q+31 = the d channels of head 4*half + q; its KV block are the columns 32q .. 32q+31
+    const int q = warp & 3;
+    ptx::mbar_wait(done, 0);
+    ptx::tc_fence_after();
+    uint32_t kv[32], ks[16];
+    ptx::tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + q * 32, kv);
+    ptx::tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 128, ks);
+    ptx::tmem_ld_wait();
+    float* o = out + q * 32 + lane;  // record j, thread index t = head * 32 + d
+#pragma unroll
+    for (int j = 0; j < 32; ++j) o[j * 256] = __uint_as_float(kv[j]);
+    o[32 * 256] = __uint_as_float(ks[0]);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 256);
+  }
+}
+
 // grid = (33, G), block = 256 (thread t = head*32 + d).  Sums the chunk partials of record j = blockIdx.x in a
 // fixed order (deterministic) and writes the bf16 planes of the block-diagonal B operand of the ATTN GEMM.
 // Per (group, half) the operand is 144 rows (n) x 128 (k):
@@ -405,10 +565,11 @@ __global__ void __launch_bounds__(128) kv_partial_kernel(const float* __restrict
 // The zero entries are written once per transformer call (memset), never here.
 __global__ void __launch_bounds__(256) kv_pack_kernel(const float* __restrict__ partial, GroupTable gt,
                                                       unsigned long long group_sel, int max_chunks,
-                                                      __nv_bfloat16* __restrict__ b_hi, __nv_bfloat16* __restrict__ b_lo) {
+                                                      __nv_bfloat16* __restrict__ b_hi, __nv_bfloat16* __restrict__ b_lo,
+                                                      int n_splits /* > 0: that many partials per group (kv_tc_kernel) */) {
   const int g = blockIdx.y, j = blockIdx.x;
   if (!((group_sel >> g) & 1ull)) return;
-  const int nchunks = (gt.len[g] + KV_ROWS_PER_BLOCK - 1) / KV_ROWS_PER_BLOCK;
+  const int nchunks = n_splits > 0 ? n_splits : (gt.len[g] + KV_ROWS_PER_BLOCK - 1) / KV_ROWS_PER_BLOCK;
   const int t = threadIdx.x;
   const float* src = partial + static_cast<long long>(g) * max_chunks * (KV_REC * 256) + j * 256 + t;
   float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
@@ -788,7 +949,15 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
 
   // ---- 1. QKV
   {
-    typename EpiQKV<C>::Params ep{w.qh, x3 ? w.ql : nullptr, g.big ? nullptr : w.qf, w.kf, w.vf, w.row_mask};
+    // big groups (coarse level): phi(K), V leave as bf16 planes for the tensor-core KV kernel, in the space of the fp32 buffers
+    static const bool kv_tc_env = getenv("OPB200_KV_TC") ? atoi(getenv("OPB200_KV_TC")) != 0 : true;
+    const bool kv_tc = kv_tc_env && g.big && C == 256;
+    __nv_bfloat16* kh = reinterpret_cast<__nv_bfloat16*>(w.kf);
+    __nv_bfloat16* vh = reinterpret_cast<__nv_bfloat16*>(w.vf);
+    const size_t plane = static_cast<size_t>(R) * C;
+    typename EpiQKV<C>::Params ep{w.qh, x3 ? w.ql : nullptr, g.big ? nullptr : w.qf, w.kf, w.vf, w.row_mask,
+                                  kv_tc ? kh : nullptr, kv_tc && x3 ? kh + plane : nullptr,
+                                  kv_tc ? vh : nullptr, kv_tc && x3 ? vh + plane : nullptr};
     auto launch = [&](int mb, int mc, int nb, int nc) -> int {
       if (mc <= 0) return OPB_OK;
       PlanBuilder pb(x3);
@@ -828,8 +997,36 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
         gt.len[i] = s == 0 ? g.len0 : g.len1;
         if (src_streams & (1 << s)) sel |= 1ull << i;
       }
-      kv_partial_kernel<<<dim3(g.max_chunks, g.G), 128, 0, stream>>>(w.kf, w.vf, gt, sel, w.kv_partial, g.max_chunks);
-      kv_pack_kernel<<<dim3(KV_REC, g.G), 256, 0, stream>>>(w.kv_partial, gt, sel, g.max_chunks, w.kvb_h, x3 ? w.kvb_l : nullptr);
+      static const bool kv_tc = getenv("OPB200_KV_TC") ? atoi(getenv("OPB200_KV_TC")) != 0 : true;
+      if (kv_tc) {
+        KvTcParams kp;
+        const __nv_bfloat16* kh = reinterpret_cast<const __nv_bfloat16*>(w.kf);
+        const __nv_bfloat16* vh = reinterpret_cast<const __nv_bfloat16*>(w.vf);
+        const size_t plane = static_cast<size_t>(R) * C;
+        int r;
+        if ((r = make_tmap_bf16(&kp.k_hi, kh, R, C, C, 64))) return r;
+        if ((r = make_tmap_bf16(&kp.v_hi, vh, R, C, C, 64))) return r;
+        if ((r = make_tmap_bf16(&kp.k_lo, x3 ? kh + plane : kh, R, C, C, 64))) return r;
+        if ((r = make_tmap_bf16(&kp.v_lo, x3 ? vh + plane : vh, R, C, C, 64))) return r;
+        kp.gt = gt, kp.group_sel = sel, kp.partial = w.kv_partial, kp.max_chunks = g.max_chunks, kp.x3 = x3 ? 1 : 0;
+        // two waves of CTAs over the selected groups x 2 halves, at least 4 token blocks each, no more splits than records
+        int n_sel = 0, min_len = 1 << 30;
+        for (int i = 0; i < g.G; ++i)
+          if ((sel >> i) & 1ull) ++n_sel, min_len = gt.len[i] < min_len ? gt.len[i] : min_len;
+        int splits = (2 * num_sms() + 2 * n_sel - 1) / (2 * (n_sel > 0 ? n_sel : 1));
+        const int most = (min_len + 255) / 256;
+        splits = splits > most ? most : splits;
+        splits = splits > g.max_chunks ? g.max_chunks : splits;
+        splits = splits < 1 ? 1 : splits;
+        kp.n_splits = splits;
+        static std::atomic<unsigned long long> configured_kvt{0};
+        if (int rr = opt_in_dyn_smem(kv_tc_kernel, KVT_SMEM, configured_kvt)) return rr;
+        kv_tc_kernel<<<dim3(splits, g.G, 2), 192, KVT_SMEM, stream>>>(kp);
+        kv_pack_kernel<<<dim3(KV_REC, g.G), 256, 0, stream>>>(w.kv_partial, gt, sel, g.max_chunks, w.kvb_h, x3 ? w.kvb_l : nullptr, splits);
+      } else {
+        kv_partial_kernel<<<dim3(g.max_chunks, g.G), 128, 0, stream>>>(w.kf, w.vf, gt, sel, w.kv_partial, g.max_chunks);
+        kv_pack_kernel<<<dim3(KV_REC, g.G), 256, 0, stream>>>(w.kv_partial, gt, sel, g.max_chunks, w.kvb_h, x3 ? w.kvb_l : nullptr, 0);
+      }
       count_launch(2);
       OPB_CHECK_CUDA(cudaGetLastError());
       PlanBuilder pb;
