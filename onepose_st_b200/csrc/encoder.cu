@@ -313,6 +313,238 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual str
 // ------------------------------------------------------------------------------------------------
 // KV reduction for big groups (coarse level: C = 256, H = 8, D = 32)
 // ------------------------------------------------------------------------------------------------
+// ------------------------------------------------------------------------------------------------
+// Fused MLP of a coarse encoder layer (C = 256, split precision):
+//   x <- x + LayerNorm2( relu([x | msg] W1^T) W2^T )
+// in ONE launch: the [128 x 512] hidden tile of an m tile never leaves the SM (as separate GEMMs its bf16 hi / lo planes make
+// a 400 MB round trip through HBM per layer step at 8 frames).
+//   * TMEM: D1 = columns 0..255 (one 256-wide half of the hidden tile at a time), D2 = columns 256..511 (the output).
+//   * Per m tile and half h: phase 1 = 16 k-blocks (32 wide: x then msg) of [x | msg] x W1[256 h .. 256 h + 255] into D1 with
+//     the three split products; the 16 epilogue warps read D1, apply the ReLU, split to bf16 hi / lo and write the half
+//     into shared memory as the A operand of phase 2 ([8 k-blocks][hi, lo][128 rows x 64 B], 64-byte swizzle: 128 KB);
+//     phase 2 = 8 k-blocks of that operand x W2[:, 256 h ..] accumulated into D2.  After both halves the warps run the
+//     LayerNorm2 + residual epilogue of the unfused path (EpiLNRes) on D2.
+//   * One TMA thread streams {A planes, W1 slab} / {W2 slab} through two 48 KB stages in exactly the order the MMA
+//     thread consumes them; the next tile's phase 1 runs while the LayerNorm epilogue of this one is at work.
+// Measured (8 frames x (8064 + 4096) rows, same box): transformer256 0.398 ms per frame with this kernel against 0.372
+// with the two GEMM launches -- correct (the transformer / model / bench-configuration parity tests pass with it) but
+// not faster yet: the 128 KB operand buffer leaves room for two stages only (a k-block of 768 clk of tensor work in
+// flight against ~1 us of L2 latency), the tensor pipe idles while the epilogue warps convert a half (2 x ~3000 clk per
+// ~46 000 clk tile), and 760 whole tiles over 148 CTAs end in a sixth round that is 14 % full.  Kept selectable
+// (OPB200_MLP_FUSED=1); the default is the two-launch path.
+constexpr bool kMlpFusedDefault = false;  // parity-green, not faster yet: see the note above (OPB200_MLP_FUSED=1 selects it)
+constexpr int MF_STAGES = 2;
+constexpr int MF_APL = BLOCK_M * 32 * 2;          // one A plane of a 32-wide k-block: 8 KB
+constexpr int MF_BPL = 256 * 32 * 2;              // one B plane: 16 KB
+constexpr int MF_STAGE_BYTES = 2 * MF_APL + 2 * MF_BPL;  // 48 KB
+constexpr int MF_A2_BYTES = 8 * 2 * MF_APL;       // the hidden half as phase-2 operand: 128 KB
+constexpr int MF_SMEM = 1024 + MF_STAGES * MF_STAGE_BYTES + MF_A2_BYTES + 256;
+
+struct MlpFusedParams {
+  CUtensorMap x_hi, x_lo, m_hi, m_lo;  // [R, 256] planes, box {32, 128}, 64-byte swizzle
+  CUtensorMap w1_hi, w1_lo;            // [512, 512], box {32, 256}
+  CUtensorMap w2_hi, w2_lo;            // [256, 512], box {32, 256}
+  EpiLNRes<256>::Params ln;
+  int m_tile_begin, num_tiles;
+};
+
+__global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(const __grid_constant__ MlpFusedParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* stages = smem;
+  uint8_t* a2 = smem + MF_STAGES * MF_STAGE_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(a2 + MF_A2_BYTES);
+  uint64_t* empty = full + MF_STAGES;
+  uint64_t* d1_full = empty + MF_STAGES;
+  uint64_t* d1_empty = d1_full + 1;
+  uint64_t* a2_full = d1_empty + 1;
+  uint64_t* a2_empty = a2_full + 1;
+  uint64_t* d2_full = a2_empty + 1;
+  uint64_t* d2_empty = d2_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d2_empty + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int kEpiWarps = 4 * EPI_SPLIT;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&p.x_hi);
+    ptx::prefetch_tmap(&p.w1_hi);
+    ptx::prefetch_tmap(&p.w2_hi);
+    for (int s = 0; s < MF_STAGES; ++s) {
+      ptx::mbar_init(&full[s], 1);
+      ptx::mbar_init(&empty[s], 1);
+    }
+    ptx::mbar_init(d1_full, 1);
+    ptx::mbar_init(d1_empty, kEpiWarps);
+    ptx::mbar_init(a2_full, kEpiWarps);
+    ptx::mbar_init(a2_empty, 1);
+    ptx::mbar_init(d2_full, 1);
+    ptx::mbar_init(d2_empty, kEpiWarps);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (ptx::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      auto next = [&]() {
+        if (++stage == MF_STAGES) stage = 0, phase ^= 1;
+      };
+      for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
+        const int row = (p.m_tile_begin + t) * BLOCK_M;
+        for (int half = 0; half < 2; ++half) {
+          for (int kb = 0; kb < 16; ++kb) {  // phase 1: [x | msg] and the W1 slab of this half
+            ptx::mbar_wait(&empty[stage], phase ^ 1);
+            ptx::mbar_arrive_expect_tx(&full[stage], MF_STAGE_BYTES);
+            uint8_t* st = stages + stage * MF_STAGE_BYTES;
+            const int ka = (kb & 7) * 32;
+            ptx::tma_load_2d(st, kb < 8 ? &p.x_hi : &p.m_hi, &full[stage], ka, row);
+            ptx::tma_load_2d(st + MF_APL, kb < 8 ? &p.x_lo : &p.m_lo, &full[stage], ka, row);
+            ptx::tma_load_2d(st + 2 * MF_APL, &p.w1_hi, &full[stage], kb * 32, half * 256);
+            ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.w1_lo, &full[stage], kb * 32, half * 256);
+            next();
+          }
+          for (int kb = 0; kb < 8; ++kb) {  // phase 2: the W2 slab that meets this half of the hidden tile
+            ptx::mbar_wait(&empty[stage], phase ^ 1);
+            ptx::mbar_arrive_expect_tx(&full[stage], 2 * MF_BPL);
+            uint8_t* st = stages + stage * MF_STAGE_BYTES;
+            ptx::tma_load_2d(st + 2 * MF_APL, &p.w2_hi, &full[stage], half * 256 + kb * 32, 0);
+            ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.w2_lo, &full[stage], half * 256 + kb * 32, 0);
+            next();
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (ptx::elect_one()) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, 256);
+      const uint32_t d1 = tmem_base, d2 = tmem_base + 256;
+      const uint32_t a2_addr = ptx::smem_u32(a2);
+      int stage = 0;
+      uint32_t phase = 0;
+      auto next = [&]() {
+        if (++stage == MF_STAGES) stage = 0, phase ^= 1;
+      };
+      auto three = [&](uint32_t d, uint64_t a_hi, uint64_t a_lo, uint64_t b_hi, uint64_t b_lo, bool first) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k) ptx::mma_bf16(d, a_hi + 2 * k, b_hi + 2 * k, idesc, !(first && k == 0));
+#pragma unroll
+        for (int k = 0; k < 2; ++k) ptx::mma_bf16(d, a_lo + 2 * k, b_hi + 2 * k, idesc, 1);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) ptx::mma_bf16(d, a_hi + 2 * k, b_lo + 2 * k, idesc, 1);
+      };
+      int it = 0;
+      for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
+        for (int half = 0; half < 2; ++half) {
+          const uint32_t u1 = static_cast<uint32_t>(it * 2 + half);
+          ptx::mbar_wait(d1_empty, (u1 & 1) ^ 1);  // the epilogue has read the previous contents of D1
+          ptx::tc_fence_after();
+          for (int kb = 0; kb < 16; ++kb) {
+            ptx::mbar_wait(&full[stage], phase);
+            ptx::tc_fence_after();
+            const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
+            three(d1, ptx::make_desc_sw64(sa), ptx::make_desc_sw64(sa + MF_APL), ptx::make_desc_sw64(sa + 2 * MF_APL),
+                  ptx::make_desc_sw64(sa + 2 * MF_APL + MF_BPL), kb == 0);
+            ptx::mma_commit(&empty[stage]);
+            next();
+          }
+          ptx::mma_commit(d1_full);
+          if (half == 0) ptx::mbar_wait(d2_empty, (static_cast<uint32_t>(it) & 1) ^ 1);  // the previous tile's output has been read
+          ptx::mbar_wait(a2_full, u1 & 1);  // this half of the hidden tile is in shared memory
+          ptx::tc_fence_after();
+          for (int kb = 0; kb < 8; ++kb) {
+            ptx::mbar_wait(&full[stage], phase);
+            ptx::tc_fence_after();
+            const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
+            three(d2, ptx::make_desc_sw64(a2_addr + (2 * kb) * MF_APL), ptx::make_desc_sw64(a2_addr + (2 * kb + 1) * MF_APL),
+                  ptx::make_desc_sw64(sa + 2 * MF_APL), ptx::make_desc_sw64(sa + 2 * MF_APL + MF_BPL), half == 0 && kb == 0);
+            ptx::mma_commit(&empty[stage]);
+            next();
+          }
+          ptx::mma_commit(a2_empty);
+        }
+        ptx::mma_commit(d2_full);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps: (column part, TMEM lane quarter)
+    EpiCtx ctx;
+    ctx.quarter = warp & 3;
+    ctx.lane = lane;
+    ctx.epi_warp = (warp - 2) & 3;
+    ctx.group = 0;
+    ctx.part = (warp - 2) >> 2;
+    ctx.n_tile = 0;
+    ctx.scratch = a2;  // LayerNorm scratch: the operand buffer is idle while D2 is normalised (see the barrier below)
+    const int r = ctx.quarter * 32 + lane;  // row of the tile
+    const uint32_t lane_field = static_cast<uint32_t>(ctx.quarter * 32) << 16;
+    int it = 0;
+    for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
+      ctx.m_tile = p.m_tile_begin + t;
+      ptx::named_bar_sync(5, 32 * kEpiWarps);  // every warp is done with the previous tile's LayerNorm scratch
+      for (int half = 0; half < 2; ++half) {
+        const uint32_t u1 = static_cast<uint32_t>(it * 2 + half);
+        ptx::mbar_wait(d1_full, u1 & 1);
+        ptx::tc_fence_after();
+        ptx::mbar_wait(a2_empty, (u1 & 1) ^ 1);  // phase 2 of the previous half has read the operand buffer
+#pragma unroll 1
+        for (int j = 0; j < 2; ++j) {  // this warp's 64 columns = k-blocks 2 part, 2 part + 1 of the half
+          const int kb = ctx.part * 2 + j;
+          float v[32];
+          load_acc32(tmem_base + lane_field + kb * 32, v);
+          uint32_t h[16], l[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            __nv_bfloat16 h0, l0, h1, l1;
+            split_bf16(fmaxf(v[2 * i], 0.f), h0, l0);
+            split_bf16(fmaxf(v[2 * i + 1], 0.f), h1, l1);
+            h[i] = pack_bf16(h0, h1);
+            l[i] = pack_bf16(l0, l1);
+          }
+          uint8_t* th = a2 + (2 * kb) * MF_APL + r * 64;
+          uint8_t* tl = th + MF_APL;
+          const int sw = (r >> 1) & 3;  // 64-byte swizzle: 16-byte chunk index ^ address bits 7..8
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            *reinterpret_cast<uint4*>(th + ((c ^ sw) << 4)) = make_uint4(h[4 * c], h[4 * c + 1], h[4 * c + 2], h[4 * c + 3]);
+            *reinterpret_cast<uint4*>(tl + ((c ^ sw) << 4)) = make_uint4(l[4 * c], l[4 * c + 1], l[4 * c + 2], l[4 * c + 3]);
+          }
+        }
+        ptx::fence_proxy_async();  // the tensor core reads these generic-proxy stores
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          ptx::mbar_arrive(a2_full);
+          ptx::mbar_arrive(d1_empty);
+        }
+      }
+      EpiLNRes<256>::prefetch(p.ln, ctx);
+      ptx::mbar_wait(d2_full, static_cast<uint32_t>(it) & 1);
+      ptx::tc_fence_after();
+      ctx.tmem_acc = tmem_base + 256 + lane_field;
+      EpiLNRes<256>::run(p.ln, ctx);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(d2_empty);
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
 constexpr int KV_ROWS_PER_BLOCK = 128;
 constexpr int KV_REC = 33;  // per (head, d): 32 KV values + Ksum
 
@@ -1097,6 +1329,34 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     if (int r = x3 ? launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLN<C>, EPI_SPLIT, true>(pb.plan, ep, stream)
                    : launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLN<C>, EPI_SPLIT>(pb.plan, ep, stream))
       return r;
+  }
+  // ---- 6 + 7 in one launch (coarse level, split precision): the hidden tile stays on the SM
+  static const bool mlp_fused_env = getenv("OPB200_MLP_FUSED") ? atoi(getenv("OPB200_MLP_FUSED")) != 0 : kMlpFusedDefault;
+  if (mlp_fused_env && C == 256 && x3) {
+    if constexpr (C == 256) {
+      MlpFusedParams fp;
+      PlanBuilder tb(true);
+      int r;
+      if ((r = tb.make(&fp.x_hi, w.xh, R, C, C, BLOCK_M))) return r;
+      if ((r = tb.make(&fp.x_lo, w.xl, R, C, C, BLOCK_M))) return r;
+      if ((r = tb.make(&fp.m_hi, w.mh, R, C, C, BLOCK_M))) return r;
+      if ((r = tb.make(&fp.m_lo, w.ml, R, C, C, BLOCK_M))) return r;
+      if ((r = tb.make(&fp.w1_hi, lw.w1_hi, 2 * C, 2 * C, 2 * C, 256))) return r;
+      if ((r = tb.make(&fp.w1_lo, lw.w1_lo, 2 * C, 2 * C, 2 * C, 256))) return r;
+      if ((r = tb.make(&fp.w2_hi, lw.w2_hi, C, 2 * C, 2 * C, 256))) return r;
+      if ((r = tb.make(&fp.w2_lo, lw.w2_lo, C, 2 * C, 2 * C, 256))) return r;
+      fp.ln = typename EpiLNRes<256>::Params{lw.ln2_g, lw.ln2_b, w.xh, w.xl};
+      fp.m_tile_begin = ub, fp.num_tiles = uc;
+      if (uc > 0) {
+        static std::atomic<unsigned long long> configured_mf{0};
+        if (int rr = opt_in_dyn_smem(mlp_fused_kernel, MF_SMEM, configured_mf)) return rr;
+        const int grid = uc < num_sms() ? uc : num_sms();
+        mlp_fused_kernel<<<grid, 64 + 128 * EPI_SPLIT, MF_SMEM, stream>>>(fp);
+        count_launch();
+        OPB_CHECK_CUDA(cudaGetLastError());
+      }
+      return OPB_OK;
+    }
   }
   // ---- 6. MLP1 + ReLU   (K = [x | msg], N = 2C as two tiles of C)
   {
