@@ -1,0 +1,23 @@
+"""GPU parity of the code paths that are selected per process by an environment switch (read once by the library):
+the fused MLP kernel of the coarse encoder layer (OPB200_MLP_FUSED=1) and the CUDA-core KV kernel that the tensor-core
+one replaced (OPB200_KV_TC=0).  Each variant runs the encoder / model parity tests in a child process."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("env", [{"OPB200_MLP_FUSED": "1"}, {"OPB200_KV_TC": "0"}], ids=["mlp_fused", "kv_cuda_cores"])
+def test_encoder_variant_passes_the_parity_tests(env):
+    res = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", "-p", "no:cacheprovider",
+                          os.path.join(REPO, "tests", "test_gpu_transformer.py"),
+                          os.path.join(REPO, "tests", "test_gpu_models.py")],
+                         cwd=REPO, env=dict(os.environ, **env), capture_output=True, text=True, timeout=900)
+    tail = (res.stdout + res.stderr)[-1500:]
+    assert res.returncode == 0, tail
+    assert " passed" in res.stdout and " failed" not in res.stdout, tail
