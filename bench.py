@@ -52,7 +52,7 @@ def parse_args():
     ap.add_argument("--loftr-pairs", type=int, default=256, help="secondary: LoFTR pairs per rank (0 = skip)")
     ap.add_argument("--backbone", default="f16", choices=["f16", "f16x3", "fp32"],
                     help="ResNetFPN_8_2.conv_precision: f16 = own tcgen05 convolutions (default), fp32 = exact cuDNN executor")
-    ap.add_argument("--batch", type=int, default=8, help="frames per forward call (dict contract N)")
+    ap.add_argument("--batch", type=int, default=32, help="frames per forward call (dict contract N; at most 32)")
     ap.add_argument("--pool", type=int, default=500, help="frames of the synthetic sequence")
     ap.add_argument("--plant", type=int, default=1000, help="planted 2D-3D correspondences")
     ap.add_argument("--precision", type=int, default=3, choices=[1, 3], help="3 = bf16x3 split (fp32-grade), 1 = bf16")
@@ -375,10 +375,12 @@ def run_ours(args):
     traffic = None  # DRAM bytes per launch of the sweep kernel, from the committed ncu --set full capture of this command
     for tname in ("r02_traffic.json", "r01_traffic.json"):
         tpath = os.path.join(REPO, "profiles", tname)
-        if os.path.exists(tpath) and args.batch == 8 and args.points == 8000 and args.size == 512:
+        if os.path.exists(tpath) and args.points == 8000 and args.size == 512:
             with open(tpath) as f:
-                traffic = json.load(f)["sim_fast_kernel"]["dram_bytes_per_launch"]
-            break
+                tj = json.load(f)
+            if tj.get("frames_per_launch") == args.batch:  # the capture must be of this launch shape
+                traffic = tj["sim_fast_kernel"]["dram_bytes_per_launch"]
+                break
     if "coarse_match" in stages:
         t_op = stages["coarse_match"]["ms_per_frame"] * 1e-3
         flops = 2.0 * L * S * C
