@@ -1103,13 +1103,17 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
 // flight).  Rows: one warp per 32 rows over all n tiles.  Columns: 8 warps per 32 columns, each over a slice of the
 // (m tile, quarter) list, combined through shared memory in a fixed order (deterministic).  A finished sum of an
 // existing row / column that is not safely above the flush-to-zero range (or is NaN) raises bit 0 of *needs_robust.
+// CV = columns per lane of the column blocks: 4 (16-byte loads, 128 columns per block) when that still fills the GPU,
+// else 1.  (Round 2: the 32-frame launch ran at 1.7 TB/s with 4-byte loads and accumulators indexed by a run-time
+// counter, which the compiler kept in local memory.)
+template <int CV>
 __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict__ rowpart, const float* __restrict__ colpart,
                                                          const float* __restrict__ tile_ref, int N, int L, int S, int Lp, int Sp,
                                                          float2* __restrict__ lse_row, float2* __restrict__ lse_col,
                                                          int* __restrict__ needs_robust, int part_w /* columns per row part: 128 | 64 */) {
-  __shared__ float2 sm[8][33];
+  __shared__ float2 sm[8][32 * CV + 1];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const long long n_rows = static_cast<long long>(N) * Lp, n_cols = static_cast<long long>(N) * Sp;
+  const long long n_rows = static_cast<long long>(N) * Lp;
   const int row_blocks = static_cast<int>(n_rows / 256 + ((n_rows % 256) != 0));  // Lp is a multiple of 128
   const int mtb = Lp / BLOCK_M, ntb = Sp / part_w;
   if (static_cast<int>(blockIdx.x) < row_blocks) {
@@ -1123,70 +1127,124 @@ __global__ void __launch_bounds__(256) merge_fast_kernel(const float* __restrict
       const float T = k0 + lane < ntb ? tr[k0 + lane] : kNegInf;
       M = fmaxf(M, key_float(__reduce_max_sync(0xffffffffu, float_key(T))));
     }
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (M > kNegInf) {
       for (int k0 = 0; k0 < ntb; k0 += 32) {
         const float T = k0 + lane < ntb ? tr[k0 + lane] : kNegInf;
         const float w = T > kNegInf ? exp2f(T - M) : 0.f;
         const int kn = min(32, ntb - k0);
-#pragma unroll 8
-        for (int k = 0; k < kn; ++k) {
+        const float* src = rowpart + static_cast<long long>(k0) * n_rows + idx;
+        int k = 0;
+        for (; k + 8 <= kn; k += 8) {
+          float v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) v[u] = __ldcs(src + static_cast<long long>(k + u) * n_rows);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const float wk = __shfl_sync(0xffffffffu, w, k + u);
+            acc[u] = fmaf(wk > 0.f ? v[u] : 0.f, wk, acc[u]);  // (a part without a reference holds nothing valid)
+          }
+        }
+        for (; k < kn; ++k) {
           const float wk = __shfl_sync(0xffffffffu, w, k);
-          const float v = __ldcs(rowpart + static_cast<long long>(k0 + k) * n_rows + idx);
-          acc[k & 3] = fmaf(wk > 0.f ? v : 0.f, wk, acc[k & 3]);  // (a part without a reference holds nothing valid)
+          const float v = __ldcs(src + static_cast<long long>(k) * n_rows);
+          acc[0] = fmaf(wk > 0.f ? v : 0.f, wk, acc[0]);
         }
       }
     }
-    const float St = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    const float St = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
     const bool ok = (i0 + lane) < L && M > kNegInf;
     lse_row[idx] = make_float2(ok ? M : kNegInf, ok ? log2f(St) : 0.f);
     if (ok && !(St >= kTinySum)) atomicOr(needs_robust, 1);
     return;
   }
-  // ---- columns: 32 per block, 8 slices of the (m tile, quarter) list
-  const long long idx = (static_cast<long long>(blockIdx.x) - row_blocks) * 32 + lane;
-  const long long idx0 = idx - lane;
+  // ---- columns: 32 * CV per block (a lane owns CV consecutive ones), 8 slices of the (m tile, quarter) list; the
+  // block's columns lie in one tile of part_w columns, or in two (part_w = 64, CV = 4: lanes 16.. are in the second)
+  const long long idx0 = (static_cast<long long>(blockIdx.x) - row_blocks) * (32 * CV);
   const int n = static_cast<int>(idx0 / Sp), j0 = static_cast<int>(idx0 - static_cast<long long>(n) * Sp);
-  const int j = j0 + lane;
+  const int jl = j0 + CV * lane;
+  const int tile0 = j0 / part_w;
+  const bool second = jl / part_w != tile0;
+  const bool two = (j0 + 32 * CV - 1) / part_w != tile0;
   const int nparts = 4 * mtb;
   const int per = (nparts + 7) / 8;
   const int kb = warp * per, ke = min(nparts, kb + per);
-  const float* tr = tile_ref + static_cast<long long>(n) * nparts * ntb + j0 / part_w;
-  float M = kNegInf;
+  const float* tr = tile_ref + static_cast<long long>(n) * nparts * ntb + tile0;
+  float M0 = kNegInf, M1 = kNegInf;
   for (int k0 = kb; k0 < ke; k0 += 32) {
-    const float T = k0 + lane < ke ? tr[static_cast<long long>(k0 + lane) * ntb] : kNegInf;
-    M = fmaxf(M, key_float(__reduce_max_sync(0xffffffffu, float_key(T))));
+    const bool in = k0 + lane < ke;
+    const float T0 = in ? tr[static_cast<long long>(k0 + lane) * ntb] : kNegInf;
+    const float T1 = (in && two) ? tr[static_cast<long long>(k0 + lane) * ntb + 1] : kNegInf;
+    M0 = fmaxf(M0, key_float(__reduce_max_sync(0xffffffffu, float_key(T0))));
+    M1 = fmaxf(M1, key_float(__reduce_max_sync(0xffffffffu, float_key(T1))));
   }
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  if (M > kNegInf) {
+  const float M = second ? M1 : M0;
+  float acc[2][CV];
+#pragma unroll
+  for (int c = 0; c < CV; ++c) acc[0][c] = acc[1][c] = 0.f;
+  if (M0 > kNegInf || M1 > kNegInf) {  // warp-uniform
     for (int k0 = kb; k0 < ke; k0 += 32) {
-      const float T = k0 + lane < ke ? tr[static_cast<long long>(k0 + lane) * ntb] : kNegInf;
-      const float w = T > kNegInf ? exp2f(T - M) : 0.f;
+      const bool in = k0 + lane < ke;
+      const float T0 = in ? tr[static_cast<long long>(k0 + lane) * ntb] : kNegInf;
+      const float T1 = (in && two) ? tr[static_cast<long long>(k0 + lane) * ntb + 1] : kNegInf;
+      const float w0 = T0 > kNegInf ? exp2f(T0 - M0) : 0.f;
+      const float w1 = T1 > kNegInf ? exp2f(T1 - M1) : 0.f;
       const int kn = min(32, ke - k0);
-#pragma unroll 8
-      for (int k = 0; k < kn; ++k) {
-        const float wk = __shfl_sync(0xffffffffu, w, k);
-        const float v = __ldcs(colpart + (static_cast<long long>(k0 + k) * N + n) * Sp + j);
-        acc[k & 3] = fmaf(wk > 0.f ? v : 0.f, wk, acc[k & 3]);
+      const float* src = colpart + (static_cast<long long>(k0) * N + n) * Sp + jl;
+      const long long pstride = static_cast<long long>(N) * Sp;
+      int k = 0;
+      for (; k + 8 <= kn; k += 8) {
+        float v[8][CV];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if constexpr (CV == 4) {
+            const float4 t = __ldcs(reinterpret_cast<const float4*>(src + (k + u) * pstride));
+            v[u][0] = t.x, v[u][1] = t.y, v[u][2] = t.z, v[u][3] = t.w;
+          } else {
+            v[u][0] = __ldcs(src + (k + u) * pstride);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const float wa = __shfl_sync(0xffffffffu, w0, k + u), wb = __shfl_sync(0xffffffffu, w1, k + u);
+          const float wk = second ? wb : wa;
+#pragma unroll
+          for (int c = 0; c < CV; ++c) acc[u & 1][c] = fmaf(wk > 0.f ? v[u][c] : 0.f, wk, acc[u & 1][c]);
+        }
+      }
+      for (; k < kn; ++k) {
+        const float wa = __shfl_sync(0xffffffffu, w0, k), wb = __shfl_sync(0xffffffffu, w1, k);
+        const float wk = second ? wb : wa;
+        float v[CV];
+        if constexpr (CV == 4) {
+          const float4 t = __ldcs(reinterpret_cast<const float4*>(src + k * pstride));
+          v[0] = t.x, v[1] = t.y, v[2] = t.z, v[3] = t.w;
+        } else {
+          v[0] = __ldcs(src + k * pstride);
+        }
+#pragma unroll
+        for (int c = 0; c < CV; ++c) acc[0][c] = fmaf(wk > 0.f ? v[c] : 0.f, wk, acc[0][c]);
       }
     }
   }
-  sm[warp][lane] = make_float2(M, (acc[0] + acc[1]) + (acc[2] + acc[3]));
+#pragma unroll
+  for (int c = 0; c < CV; ++c) sm[warp][CV * lane + c] = make_float2(M, acc[0][c] + acc[1][c]);
   __syncthreads();
-  if (warp == 0) {
+  if (threadIdx.x < 32 * CV) {
+    const int c = threadIdx.x;
     float Mt = kNegInf;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) Mt = fmaxf(Mt, sm[q][lane].x);
+    for (int q = 0; q < 8; ++q) Mt = fmaxf(Mt, sm[q][c].x);
     float St = 0.f;
     if (Mt > kNegInf) {
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
-        const float2 pq = sm[q][lane];
+        const float2 pq = sm[q][c];
         if (pq.x > kNegInf) St += pq.y * exp2f(pq.x - Mt);
       }
     }
-    const bool ok = j < S && Mt > kNegInf;
-    lse_col[idx] = make_float2(ok ? Mt : kNegInf, ok ? log2f(St) : 0.f);
+    const bool ok = (j0 + c) < S && Mt > kNegInf;
+    lse_col[idx0 + c] = make_float2(ok ? Mt : kNegInf, ok ? log2f(St) : 0.f);
     if (ok && !(St >= kTinySum)) atomicOr(needs_robust, 1);
   }
 }
@@ -2219,8 +2277,12 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       g_kt_events.emplace_back(kt0, kt1);
     }
     const long long nr = static_cast<long long>(N) * Lp, nc = static_cast<long long>(N) * Sp;
-    merge_fast_kernel<<<static_cast<unsigned>((nr + 255) / 256 + nc / 32), 256, 0, stream>>>(fp.rowpart, fp.colpart, w.tile_ref, N, L, S, Lp, Sp,
-                                                                                    w.lse_row, w.lse_col, w.counters + 2, SIM_BN);
+    if (nc / 128 >= num_sms())  // 16-byte loads when 128-column blocks still fill the GPU
+      merge_fast_kernel<4><<<static_cast<unsigned>((nr + 255) / 256 + nc / 128), 256, 0, stream>>>(fp.rowpart, fp.colpart, w.tile_ref, N, L, S, Lp, Sp,
+                                                                                           w.lse_row, w.lse_col, w.counters + 2, SIM_BN);
+    else
+      merge_fast_kernel<1><<<static_cast<unsigned>((nr + 255) / 256 + nc / 32), 256, 0, stream>>>(fp.rowpart, fp.colpart, w.tile_ref, N, L, S, Lp, Sp,
+                                                                                          w.lse_row, w.lse_col, w.counters + 2, SIM_BN);
     count_launch();
     }
   } else {

@@ -12,7 +12,7 @@ from onepose_st_b200 import _lib as _lib0
 if os.environ.get("OPB200_LIB_ALT"):  # A/B on one box: another build of the library
     _lib0.LIB_PATH = os.path.abspath(os.environ["OPB200_LIB_ALT"])
 from onepose_st_b200 import ops, synthetic
-N, L, S, C = 8, 8000, 4096, 256
+N, L, S, C = int(os.environ.get("OPB200_N", "8")), 8000, 4096, 256
 f3d, f2d = synthetic.planted_coarse_pair(21, N, L, S, C, 1000, 64, 64, device="cuda")
 kw = dict(scale=1.0 / (C * 0.0801), thr=0.1, border_rm=2, border_mode=0, grid_a=None, grid_b=(64, 64),
           algo=int(os.environ.get("OPB200_ALGO", "0")))  # 3 = the register-buffered variant (sim_sweep_kernel)
