@@ -1731,9 +1731,13 @@ struct PackSide {
 // column tiles of a row block from flooding the candidate list (their own partial sum is a poor bound).
 constexpr int MEAN_CHUNKS = 64;
 // thread = (8 channels, row lane): 16-byte loads of the hi and lo planes, 8 rows of a chunk in flight per block step
+// The same pass writes side b's fp16 operand plane of the screening sweep and takes its largest row norm (out / norm_sq
+// non-null): side b is read once, not once for the mean and once for the pack.
 __global__ void __launch_bounds__(256) colmean_kernel(const __nv_bfloat16* __restrict__ hi, const __nv_bfloat16* __restrict__ lo,
                                                       int S, int Sp, float* __restrict__ part /* [N][MEAN_CHUNKS][256] */,
-                                                      float* __restrict__ mean /* [N][256] */, int* __restrict__ done /* [N] */) {
+                                                      float* __restrict__ mean /* [N][256] */, int* __restrict__ done /* [N] */,
+                                                      __half* __restrict__ out /* [N][Sp][256] or null */,
+                                                      unsigned* __restrict__ norm_sq /* bits of the largest squared row norm */) {
   __shared__ float red[8][FAST_C];
   __shared__ int last;
   const int n = blockIdx.x / MEAN_CHUNKS, ch = blockIdx.x % MEAN_CHUNKS;
@@ -1741,17 +1745,36 @@ __global__ void __launch_bounds__(256) colmean_kernel(const __nv_bfloat16* __res
   const int per = (S + MEAN_CHUNKS - 1) / MEAN_CHUNKS;
   const int j0 = ch * per, j1 = min(S, j0 + per);
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float worst = 0.f;
   const long long base = static_cast<long long>(n) * Sp * FAST_C + cg * 8;
-  for (int j = j0 + rl; j < j1; j += 8) {  // fixed assignment of rows to row lanes: deterministic
+  auto one_row = [&](int j, bool valid) {
     const uint4 h = *reinterpret_cast<const uint4*>(hi + base + static_cast<long long>(j) * FAST_C);
     const uint4 l = *reinterpret_cast<const uint4*>(lo + base + static_cast<long long>(j) * FAST_C);
     const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
+    uint32_t ow[4];
+    float sq = 0.f;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      acc[2 * q] += __uint_as_float(hw[q] << 16) + __uint_as_float(lw[q] << 16);
-      acc[2 * q + 1] += __uint_as_float(hw[q] & 0xffff0000u) + __uint_as_float(lw[q] & 0xffff0000u);
+      const float x0 = __uint_as_float(hw[q] << 16) + __uint_as_float(lw[q] << 16);
+      const float x1 = __uint_as_float(hw[q] & 0xffff0000u) + __uint_as_float(lw[q] & 0xffff0000u);
+      if (valid) acc[2 * q] += x0, acc[2 * q + 1] += x1;
+      sq = fmaf(x0, x0, fmaf(x1, x1, sq));
+      const __half2 v = __floats2half2_rn(x0, x1);
+      ow[q] = *reinterpret_cast<const uint32_t*>(&v);
     }
-  }
+    if (out != nullptr) {
+      *reinterpret_cast<uint4*>(out + base + static_cast<long long>(j) * FAST_C) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);  // (a warp = one row)
+      if (valid) worst = fmaxf(worst, sq <= 3e38f ? sq : INFINITY);  // (a NaN norm counts as +inf, as in pack_f16_kernel)
+    }
+  };
+#pragma unroll 4
+  for (int j = j0 + rl; j < j1; j += 8) one_row(j, true);  // fixed assignment of rows to row lanes: deterministic
+  // the padding rows S .. Sp - 1 are packed by the last chunk; they have no say in the mean or the norm
+  if (out != nullptr && ch == MEAN_CHUNKS - 1)
+    for (int j = S + rl; j < Sp; j += 8) one_row(j, false);
+  if (norm_sq != nullptr && cg == 0 && worst > 0.f) atomicMax(norm_sq, __float_as_uint(worst));
 #pragma unroll
   for (int q = 0; q < 8; ++q) red[rl][cg * 8 + q] = acc[q];
   __syncthreads();
@@ -2193,10 +2216,12 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
       PackSide sa{reinterpret_cast<const uint4*>(w.a_hi), reinterpret_cast<const uint4*>(w.a_lo), reinterpret_cast<uint4*>(w.a_f16), va, L, Lp};
       PackSide sb{reinterpret_cast<const uint4*>(w.b_hi), reinterpret_cast<const uint4*>(w.b_lo), reinterpret_cast<uint4*>(w.b_f16), vb, S, Sp};
       const int ba = static_cast<int>((va + 255) / 256 < 8 * num_sms() ? (va + 255) / 256 : 8 * num_sms());
-      const int bb = static_cast<int>((vb + 255) / 256 < 4 * num_sms() ? (vb + 255) / 256 : 4 * num_sms());
-      colmean_kernel<<<N * MEAN_CHUNKS, 256, 0, stream>>>(w.b_hi, w.b_lo, S, Sp, w.mean_part, w.mean_b, w.mean_done);
-      pack_f16_kernel<<<ba + bb, 256, 0, stream>>>(sa, sb, ba, reinterpret_cast<unsigned*>(w.counters + 4), w.mean_b,
-                                                   scale * kLog2e, S, w.row_lb);
+      // side b: column mean + fp16 plane + largest row norm in one pass; side a: fp16 plane + norm + Jensen bound per row
+      colmean_kernel<<<N * MEAN_CHUNKS, 256, 0, stream>>>(w.b_hi, w.b_lo, S, Sp, w.mean_part, w.mean_b, w.mean_done,
+                                                          reinterpret_cast<__half*>(w.b_f16), reinterpret_cast<unsigned*>(w.counters + 4) + 1);
+      sb.n_vec = 0;
+      pack_f16_kernel<<<ba, 256, 0, stream>>>(sa, sb, ba, reinterpret_cast<unsigned*>(w.counters + 4), w.mean_b,
+                                              scale * kLog2e, S, w.row_lb);
       count_launch(2);
     }
     if (screen) {  // the data type of a tensor map only matters for its fill value
