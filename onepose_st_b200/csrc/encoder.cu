@@ -127,6 +127,7 @@ __device__ __forceinline__ void row_mean_rstd_split(const EpiCtx& ctx, const flo
     s3 += x[i + 3];
   }
   float* slot = red + (ctx.quarter * EPI_SPLIT) * 32 + ctx.lane;
+  if (ctx.scratch_small) ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);  // the previous call's squares have been read
   slot[ctx.part * 32] = (s0 + s1) + (s2 + s3);
   ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);
   float tot = 0.f;
@@ -142,7 +143,8 @@ __device__ __forceinline__ void row_mean_rstd_split(const EpiCtx& ctx, const flo
     q2 = fmaf(d2, d2, q2);
     q3 = fmaf(d3, d3, q3);
   }
-  float* slot2 = slot + 4 * EPI_SPLIT * 32;
+  float* slot2 = ctx.scratch_small ? slot : slot + 4 * EPI_SPLIT * 32;
+  if (ctx.scratch_small) ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);  // the sums have been read: the slots take the squares
   slot2[ctx.part * 32] = (q0 + q1) + (q2 + q3);
   ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);
   float var = 0.f;
@@ -317,43 +319,57 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual str
 // Fused MLP of a coarse encoder layer (C = 256, split precision):
 //   x <- x + LayerNorm2( relu([x | msg] W1^T) W2^T )
 // in ONE launch: the [128 x 512] hidden tile of an m tile never leaves the SM (as separate GEMMs its bf16 hi / lo planes make
-// a 400 MB round trip through HBM per layer step at 8 frames).
-//   * TMEM: D1 = columns 0..255 (one 256-wide half of the hidden tile at a time), D2 = columns 256..511 (the output).
-//   * Per m tile and half h: phase 1 = 16 k-blocks (32 wide: x then msg) of [x | msg] x W1[256 h .. 256 h + 255] into D1 with
-//     the three split products; the 16 epilogue warps read D1, apply the ReLU, split to bf16 hi / lo and write the half
-//     into shared memory as the A operand of phase 2 ([8 k-blocks][hi, lo][128 rows x 64 B], 64-byte swizzle: 128 KB);
-//     phase 2 = 8 k-blocks of that operand x W2[:, 256 h ..] accumulated into D2.  After both halves the warps run the
-//     LayerNorm2 + residual epilogue of the unfused path (EpiLNRes) on D2.
-//   * One TMA thread streams {A planes, W1 slab} / {W2 slab} through two 48 KB stages in exactly the order the MMA
-//     thread consumes them; the next tile's phase 1 runs while the LayerNorm epilogue of this one is at work.
-// Measured (8 frames x (8064 + 4096) rows, same box): transformer256 0.398 ms per frame with this kernel against 0.372
-// with the two GEMM launches -- correct (the transformer / model / bench-configuration parity tests pass with it) but
-// not faster yet: the 128 KB operand buffer leaves room for two stages only (a k-block of 768 clk of tensor work in
-// flight against ~1 us of L2 latency), the tensor pipe idles while the epilogue warps convert a half (2 x ~3000 clk per
-// ~46 000 clk tile), and 760 whole tiles over 148 CTAs end in a sixth round that is 14 % full.  Kept selectable
-// (OPB200_MLP_FUSED=1); the default is the two-launch path.
-constexpr bool kMlpFusedDefault = false;  // parity-green, not faster yet: see the note above (OPB200_MLP_FUSED=1 selects it)
-constexpr int MF_STAGES = 2;
-constexpr int MF_APL = BLOCK_M * 32 * 2;          // one A plane of a 32-wide k-block: 8 KB
-constexpr int MF_BPL = 256 * 32 * 2;              // one B plane: 16 KB
-constexpr int MF_STAGE_BYTES = 2 * MF_APL + 2 * MF_BPL;  // 48 KB
-constexpr int MF_A2_BYTES = 8 * 2 * MF_APL;       // the hidden half as phase-2 operand: 128 KB
-constexpr int MF_SMEM = 1024 + MF_STAGES * MF_STAGE_BYTES + MF_A2_BYTES + 256;
+// a 1.6 GB round trip through HBM per layer step at 32 frames).
+//   * Per m tile and quarter q of the hidden tile: phase 1 = 16 k-blocks (32 wide: x then msg) of [x | msg] x
+//     W1[128 q .. 128 q + 127] into D1 with the three split products; the 16 epilogue warps read D1, apply the ReLU, split
+//     to bf16 hi / lo and write the quarter back INTO TENSOR MEMORY as the A operand of phase 2; phase 2 = 4 k-blocks of that
+//     operand x W2[:, 128 q ..] accumulated into D2.  After the four quarters the warps run the LayerNorm2 + residual
+//     epilogue of the unfused path (EpiLNRes) on D2.
+//   * One TMA thread streams {A planes, W1 rows} / {W2 columns} through seven 32 KB stages in exactly the order the MMA
+//     thread consumes them.
+// History: the first version kept the hidden tile in shared memory as halves (128 KB) -- two 48 KB stages were all that
+// fitted beside it and every stage waited for the latency of its own TMA load: 995 us per layer step at 32 frames (ncu)
+// against 415 + 318 us for the two GEMM launches.  With the operand in tensor memory and phase 2 issued one phase 1 late:
+// 823 us under ncu (tensor pipe 60 % active; the L2 -> SM traffic of 2.5 MB per tile, weights re-streamed per tile and
+// [x | msg] once per quarter, is 77 % of the ~6300 B/clk the L2 delivers chip-wide), and in the bench, where the clocks
+// are set by the power cap and the 1.6 GB that no longer move count: transformer256 0.327-0.330 ms per frame against
+// 0.338-0.343, 1258-1260 frames/s end to end against 1217-1220 (same box, back to back, 32 frames per forward); 8 / 16
+// frames per forward: 0.363 / 0.342 against 0.376 / 0.351.
+constexpr int kMlpFusedMinRounds = 6;  // tiles per CTA from which the fused kernel is the default (OPB200_MLP_FUSED overrides)
+constexpr int MF_STAGES = 7;
+constexpr int MF_APL = BLOCK_M * 32 * 2;     // one A plane of a 32-wide k-block: 8 KB
+constexpr int MF_B1PL = 128 * 32 * 2;        // one W1 plane of a quarter (128 hidden columns): 8 KB
+constexpr int MF_B2PL = 256 * 32 * 2;        // one W2 plane: 16 KB
+constexpr int MF_STAGE_BYTES = 2 * MF_APL + 2 * MF_B1PL;  // 32 KB; phase 2 uses the same 32 KB for the two W2 planes
+static_assert(MF_STAGE_BYTES == 2 * MF_B2PL, "one stage size for both phases");
+constexpr int MF_LN_SCRATCH = kLnScratch / 2;  // (EpiCtx::scratch_small)
+// 64-byte swizzle: 512-byte alignment of the operand tiles is enough
+constexpr int MF_SMEM = 512 + MF_STAGES * MF_STAGE_BYTES + 256 + MF_LN_SCRATCH;
+static_assert(MF_SMEM <= 232448, "shared memory of a CTA");
 
 struct MlpFusedParams {
   CUtensorMap x_hi, x_lo, m_hi, m_lo;  // [R, 256] planes, box {32, 128}, 64-byte swizzle
-  CUtensorMap w1_hi, w1_lo;            // [512, 512], box {32, 256}
+  CUtensorMap w1_hi, w1_lo;            // [512, 512], box {32, 128}
   CUtensorMap w2_hi, w2_lo;            // [256, 512], box {32, 256}
   EpiLNRes<256>::Params ln;
   int m_tile_begin, num_tiles;
 };
 
+// Tensor memory: D1 = columns 0..127 (one 128-wide quarter of the hidden tile, fp32), A2 = columns 128..255 (that quarter
+// after the ReLU as bf16 hi / lo planes, 64 columns each: the A operand of phase 2 is read FROM TENSOR MEMORY, so all of
+// shared memory is left to the operand ring -- seven 32 KB stages; with the hidden half in shared memory (128 KB) only two
+// 48 KB stages fitted and the mainloop ran at the latency of one TMA load per stage: 995 us per layer step at 32 frames
+// against 733 us for the two GEMM launches), D2 = columns 256..511 (the output).
+// Order of work (v = 4 * tile + quarter counts the quarters of the CTA's hidden tiles):
+//   tensor pipe:  G1(0) | G1(1) G2(0) | G1(2) G2(1) | ...   -- phase 2 of a quarter is issued one phase 1 later, so the pipe
+//                 has the next quarter's MMAs to run while the epilogue warps turn D1 into the phase-2 operand
+//   epilogue:     e1(v): D1 -> registers (ReLU, split), D1 handed back at once; wait until G2(v - 1) has read A2; tcgen05.st;
+//                 after e1 of a tile's first quarter: LayerNorm2 + residual of the PREVIOUS tile from D2.
 __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(const __grid_constant__ MlpFusedParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 511) & ~uintptr_t(511));
   uint8_t* stages = smem;
-  uint8_t* a2 = smem + MF_STAGES * MF_STAGE_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(a2 + MF_A2_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + MF_STAGES * MF_STAGE_BYTES);
   uint64_t* empty = full + MF_STAGES;
   uint64_t* d1_full = empty + MF_STAGES;
   uint64_t* d1_empty = d1_full + 1;
@@ -362,8 +378,12 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
   uint64_t* d2_full = a2_empty + 1;
   uint64_t* d2_empty = d2_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d2_empty + 1);
+  uint8_t* ln_scratch = smem + MF_STAGES * MF_STAGE_BYTES + 256;
+  static_assert((2 * MF_STAGES + 6) * 8 + 4 <= 256, "barrier block");
+  static_assert(512 + MF_STAGES * MF_STAGE_BYTES + 256 + MF_LN_SCRATCH <= 232448, "shared memory of a CTA");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int kEpiWarps = 4 * EPI_SPLIT;
+  constexpr uint32_t kD1 = 0, kA2Hi = 128, kA2Lo = 192, kD2 = 256;  // tensor-memory columns
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.x_hi);
@@ -389,91 +409,107 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const int n_it = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const int V = 4 * n_it;  // quarters of this CTA
 
   if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
+    // ------------------------------------------------------------------ TMA producer (same order as the MMA thread)
     if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       auto next = [&]() {
         if (++stage == MF_STAGES) stage = 0, phase ^= 1;
       };
-      for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
-        const int row = (p.m_tile_begin + t) * BLOCK_M;
-        for (int half = 0; half < 2; ++half) {
-          for (int kb = 0; kb < 16; ++kb) {  // phase 1: [x | msg] and the W1 slab of this half
-            ptx::mbar_wait(&empty[stage], phase ^ 1);
-            ptx::mbar_arrive_expect_tx(&full[stage], MF_STAGE_BYTES);
-            uint8_t* st = stages + stage * MF_STAGE_BYTES;
-            const int ka = (kb & 7) * 32;
-            ptx::tma_load_2d(st, kb < 8 ? &p.x_hi : &p.m_hi, &full[stage], ka, row);
-            ptx::tma_load_2d(st + MF_APL, kb < 8 ? &p.x_lo : &p.m_lo, &full[stage], ka, row);
-            ptx::tma_load_2d(st + 2 * MF_APL, &p.w1_hi, &full[stage], kb * 32, half * 256);
-            ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.w1_lo, &full[stage], kb * 32, half * 256);
-            next();
-          }
-          for (int kb = 0; kb < 8; ++kb) {  // phase 2: the W2 slab that meets this half of the hidden tile
-            ptx::mbar_wait(&empty[stage], phase ^ 1);
-            ptx::mbar_arrive_expect_tx(&full[stage], 2 * MF_BPL);
-            uint8_t* st = stages + stage * MF_STAGE_BYTES;
-            ptx::tma_load_2d(st + 2 * MF_APL, &p.w2_hi, &full[stage], half * 256 + kb * 32, 0);
-            ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.w2_lo, &full[stage], half * 256 + kb * 32, 0);
-            next();
-          }
+      auto p1 = [&](int v) {  // [x | msg] and the W1 rows of this quarter
+        const int row = (p.m_tile_begin + static_cast<int>(blockIdx.x) + (v >> 2) * static_cast<int>(gridDim.x)) * BLOCK_M;
+        const int q = v & 3;
+        for (int kb = 0; kb < 16; ++kb) {
+          ptx::mbar_wait(&empty[stage], phase ^ 1);
+          ptx::mbar_arrive_expect_tx(&full[stage], MF_STAGE_BYTES);
+          uint8_t* st = stages + stage * MF_STAGE_BYTES;
+          const int ka = (kb & 7) * 32;
+          ptx::tma_load_2d(st, kb < 8 ? &p.x_hi : &p.m_hi, &full[stage], ka, row);
+          ptx::tma_load_2d(st + MF_APL, kb < 8 ? &p.x_lo : &p.m_lo, &full[stage], ka, row);
+          ptx::tma_load_2d(st + 2 * MF_APL, &p.w1_hi, &full[stage], kb * 32, q * 128);
+          ptx::tma_load_2d(st + 2 * MF_APL + MF_B1PL, &p.w1_lo, &full[stage], kb * 32, q * 128);
+          next();
         }
+      };
+      auto p2 = [&](int v) {  // the W2 columns that meet this quarter of the hidden tile
+        const int q = v & 3;
+        for (int kb = 0; kb < 4; ++kb) {
+          ptx::mbar_wait(&empty[stage], phase ^ 1);
+          ptx::mbar_arrive_expect_tx(&full[stage], MF_STAGE_BYTES);
+          uint8_t* st = stages + stage * MF_STAGE_BYTES;
+          ptx::tma_load_2d(st, &p.w2_hi, &full[stage], q * 128 + kb * 32, 0);
+          ptx::tma_load_2d(st + MF_B2PL, &p.w2_lo, &full[stage], q * 128 + kb * 32, 0);
+          next();
+        }
+      };
+      for (int v = 0; v < V; ++v) {
+        p1(v);
+        if (v >= 1) p2(v - 1);
       }
+      if (V > 0) p2(V - 1);
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (ptx::elect_one()) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, 256);
-      const uint32_t d1 = tmem_base, d2 = tmem_base + 256;
-      const uint32_t a2_addr = ptx::smem_u32(a2);
+      constexpr uint32_t idesc1 = ptx::make_idesc_bf16(BLOCK_M, 128), idesc2 = ptx::make_idesc_bf16(BLOCK_M, 256);
+      const uint32_t d1 = tmem_base + kD1, d2 = tmem_base + kD2;
       int stage = 0;
       uint32_t phase = 0;
       auto next = [&]() {
         if (++stage == MF_STAGES) stage = 0, phase ^= 1;
       };
-      auto three = [&](uint32_t d, uint64_t a_hi, uint64_t a_lo, uint64_t b_hi, uint64_t b_lo, bool first) {
-#pragma unroll
-        for (int k = 0; k < 2; ++k) ptx::mma_bf16(d, a_hi + 2 * k, b_hi + 2 * k, idesc, !(first && k == 0));
-#pragma unroll
-        for (int k = 0; k < 2; ++k) ptx::mma_bf16(d, a_lo + 2 * k, b_hi + 2 * k, idesc, 1);
-#pragma unroll
-        for (int k = 0; k < 2; ++k) ptx::mma_bf16(d, a_hi + 2 * k, b_lo + 2 * k, idesc, 1);
-      };
-      int it = 0;
-      for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
-        for (int half = 0; half < 2; ++half) {
-          const uint32_t u1 = static_cast<uint32_t>(it * 2 + half);
-          ptx::mbar_wait(d1_empty, (u1 & 1) ^ 1);  // the epilogue has read the previous contents of D1
+      auto g1 = [&](int v) {
+        ptx::mbar_wait(d1_empty, (static_cast<uint32_t>(v) & 1) ^ 1);  // the epilogue has taken the previous quarter out of D1
+        ptx::tc_fence_after();
+        for (int kb = 0; kb < 16; ++kb) {
+          ptx::mbar_wait(&full[stage], phase);
           ptx::tc_fence_after();
-          for (int kb = 0; kb < 16; ++kb) {
-            ptx::mbar_wait(&full[stage], phase);
-            ptx::tc_fence_after();
-            const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
-            three(d1, ptx::make_desc_sw64(sa), ptx::make_desc_sw64(sa + MF_APL), ptx::make_desc_sw64(sa + 2 * MF_APL),
-                  ptx::make_desc_sw64(sa + 2 * MF_APL + MF_BPL), kb == 0);
-            ptx::mma_commit(&empty[stage]);
-            next();
-          }
-          ptx::mma_commit(d1_full);
-          if (half == 0) ptx::mbar_wait(d2_empty, (static_cast<uint32_t>(it) & 1) ^ 1);  // the previous tile's output has been read
-          ptx::mbar_wait(a2_full, u1 & 1);  // this half of the hidden tile is in shared memory
-          ptx::tc_fence_after();
-          for (int kb = 0; kb < 8; ++kb) {
-            ptx::mbar_wait(&full[stage], phase);
-            ptx::tc_fence_after();
-            const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
-            three(d2, ptx::make_desc_sw64(a2_addr + (2 * kb) * MF_APL), ptx::make_desc_sw64(a2_addr + (2 * kb + 1) * MF_APL),
-                  ptx::make_desc_sw64(sa + 2 * MF_APL), ptx::make_desc_sw64(sa + 2 * MF_APL + MF_BPL), half == 0 && kb == 0);
-            ptx::mma_commit(&empty[stage]);
-            next();
-          }
-          ptx::mma_commit(a2_empty);
+          const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
+          const uint64_t a_hi = ptx::make_desc_sw64(sa), a_lo = ptx::make_desc_sw64(sa + MF_APL);
+          const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + MF_B1PL);
+#pragma unroll
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_hi + 2 * k, idesc1, !(kb == 0 && k == 0));
+#pragma unroll
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_lo + 2 * k, b_hi + 2 * k, idesc1, 1);
+#pragma unroll
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_lo + 2 * k, idesc1, 1);
+          ptx::mma_commit(&empty[stage]);
+          next();
         }
-        ptx::mma_commit(d2_full);
+        ptx::mma_commit(d1_full);
+      };
+      auto g2 = [&](int v) {
+        const int q = v & 3;
+        if (q == 0) ptx::mbar_wait(d2_empty, (static_cast<uint32_t>(v >> 2) & 1) ^ 1);  // the previous tile's output has been read
+        ptx::mbar_wait(a2_full, static_cast<uint32_t>(v) & 1);  // this quarter of the hidden tile is in tensor memory
+        ptx::tc_fence_after();
+        for (int kb = 0; kb < 4; ++kb) {
+          ptx::mbar_wait(&full[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
+          const uint64_t b_hi = ptx::make_desc_sw64(sa), b_lo = ptx::make_desc_sw64(sa + MF_B2PL);
+          const uint32_t a_hi = tmem_base + kA2Hi + 16 * kb, a_lo = tmem_base + kA2Lo + 16 * kb;
+#pragma unroll
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_hi + 2 * k, idesc2, !(q == 0 && kb == 0 && k == 0));
+#pragma unroll
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_lo + 8 * k, b_hi + 2 * k, idesc2, 1);
+#pragma unroll
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_lo + 2 * k, idesc2, 1);
+          ptx::mma_commit(&empty[stage]);
+          next();
+        }
+        ptx::mma_commit(a2_empty);
+        if (q == 3) ptx::mma_commit(d2_full);
+      };
+      for (int v = 0; v < V; ++v) {
+        g1(v);
+        if (v >= 1) g2(v - 1);
       }
+      if (V > 0) g2(V - 1);
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps: (column part, TMEM lane quarter)
@@ -484,58 +520,52 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
     ctx.group = 0;
     ctx.part = (warp - 2) >> 2;
     ctx.n_tile = 0;
-    ctx.scratch = a2;  // LayerNorm scratch: the operand buffer is idle while D2 is normalised (see the barrier below)
-    const int r = ctx.quarter * 32 + lane;  // row of the tile
+    ctx.scratch = ln_scratch;
+    ctx.scratch_small = 1;
     const uint32_t lane_field = static_cast<uint32_t>(ctx.quarter * 32) << 16;
-    int it = 0;
-    for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
-      ctx.m_tile = p.m_tile_begin + t;
-      ptx::named_bar_sync(5, 32 * kEpiWarps);  // every warp is done with the previous tile's LayerNorm scratch
-      for (int half = 0; half < 2; ++half) {
-        const uint32_t u1 = static_cast<uint32_t>(it * 2 + half);
-        ptx::mbar_wait(d1_full, u1 & 1);
-        ptx::tc_fence_after();
-        ptx::mbar_wait(a2_empty, (u1 & 1) ^ 1);  // phase 2 of the previous half has read the operand buffer
-#pragma unroll 1
-        for (int j = 0; j < 2; ++j) {  // this warp's 64 columns = k-blocks 2 part, 2 part + 1 of the half
-          const int kb = ctx.part * 2 + j;
-          float v[32];
-          load_acc32(tmem_base + lane_field + kb * 32, v);
-          uint32_t h[16], l[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            __nv_bfloat16 h0, l0, h1, l1;
-            split_bf16(fmaxf(v[2 * i], 0.f), h0, l0);
-            split_bf16(fmaxf(v[2 * i + 1], 0.f), h1, l1);
-            h[i] = pack_bf16(h0, h1);
-            l[i] = pack_bf16(l0, l1);
-          }
-          uint8_t* th = a2 + (2 * kb) * MF_APL + r * 64;
-          uint8_t* tl = th + MF_APL;
-          const int sw = (r >> 1) & 3;  // 64-byte swizzle: 16-byte chunk index ^ address bits 7..8
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            *reinterpret_cast<uint4*>(th + ((c ^ sw) << 4)) = make_uint4(h[4 * c], h[4 * c + 1], h[4 * c + 2], h[4 * c + 3]);
-            *reinterpret_cast<uint4*>(tl + ((c ^ sw) << 4)) = make_uint4(l[4 * c], l[4 * c + 1], l[4 * c + 2], l[4 * c + 3]);
-          }
-        }
-        ptx::fence_proxy_async();  // the tensor core reads these generic-proxy stores
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) {
-          ptx::mbar_arrive(a2_full);
-          ptx::mbar_arrive(d1_empty);
-        }
-      }
+    auto layer_norm = [&](int it) {
+      ctx.m_tile = p.m_tile_begin + static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x);
       EpiLNRes<256>::prefetch(p.ln, ctx);
       ptx::mbar_wait(d2_full, static_cast<uint32_t>(it) & 1);
       ptx::tc_fence_after();
-      ctx.tmem_acc = tmem_base + 256 + lane_field;
+      ctx.tmem_acc = tmem_base + kD2 + lane_field;
       EpiLNRes<256>::run(p.ln, ctx);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(d2_empty);
+    };
+    for (int v = 0; v < V; ++v) {
+      const uint32_t v1 = static_cast<uint32_t>(v);
+      ptx::mbar_wait(d1_full, v1 & 1);
+      ptx::tc_fence_after();
+      // this warp's 32 columns of the quarter: out of D1 into registers (ReLU, bf16 hi / lo), D1 goes back at once
+      uint32_t h[16], l[16];
+      {
+        float x[32];
+        load_acc32(tmem_base + kD1 + lane_field + ctx.part * 32, x);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          __nv_bfloat16 h0, l0, h1, l1;
+          split_bf16(fmaxf(x[2 * i], 0.f), h0, l0);
+          split_bf16(fmaxf(x[2 * i + 1], 0.f), h1, l1);
+          h[i] = pack_bf16(h0, h1);
+          l[i] = pack_bf16(l0, l1);
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(d1_empty);
+      ptx::mbar_wait(a2_empty, (v1 & 1) ^ 1);  // phase 2 of the previous quarter has read the operand columns
+      ptx::tc_fence_after();
+      ptx::tmem_st16(tmem_base + kA2Hi + lane_field + ctx.part * 16, h);
+      ptx::tmem_st16(tmem_base + kA2Lo + lane_field + ctx.part * 16, l);
+      ptx::tmem_st_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(a2_full);
+      if ((v & 3) == 0 && v >= 4) layer_norm((v >> 2) - 1);
     }
+    if (n_it > 0) layer_norm(n_it - 1);
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -1331,8 +1361,11 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       return r;
   }
   // ---- 6 + 7 in one launch (coarse level, split precision): the hidden tile stays on the SM
-  static const bool mlp_fused_env = getenv("OPB200_MLP_FUSED") ? atoi(getenv("OPB200_MLP_FUSED")) != 0 : kMlpFusedDefault;
-  if (mlp_fused_env && C == 256 && x3) {
+  // OPB200_MLP_FUSED = 0 / 1 forces the two-launch / the fused path; unset: fused when the CTAs get kMlpFusedMinRounds tiles
+  // each or more (a CTA's tiles run back to back, so a short list ends in a round that is mostly empty)
+  static const int mlp_fused_env = getenv("OPB200_MLP_FUSED") ? atoi(getenv("OPB200_MLP_FUSED")) : -1;
+  const bool mlp_fused = mlp_fused_env >= 0 ? mlp_fused_env != 0 : uc >= kMlpFusedMinRounds * num_sms();
+  if (mlp_fused && C == 256 && x3) {
     if constexpr (C == 256) {
       MlpFusedParams fp;
       PlanBuilder tb(true);
@@ -1341,8 +1374,8 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       if ((r = tb.make(&fp.x_lo, w.xl, R, C, C, BLOCK_M))) return r;
       if ((r = tb.make(&fp.m_hi, w.mh, R, C, C, BLOCK_M))) return r;
       if ((r = tb.make(&fp.m_lo, w.ml, R, C, C, BLOCK_M))) return r;
-      if ((r = tb.make(&fp.w1_hi, lw.w1_hi, 2 * C, 2 * C, 2 * C, 256))) return r;
-      if ((r = tb.make(&fp.w1_lo, lw.w1_lo, 2 * C, 2 * C, 2 * C, 256))) return r;
+      if ((r = tb.make(&fp.w1_hi, lw.w1_hi, 2 * C, 2 * C, 2 * C, 128))) return r;
+      if ((r = tb.make(&fp.w1_lo, lw.w1_lo, 2 * C, 2 * C, 2 * C, 128))) return r;
       if ((r = tb.make(&fp.w2_hi, lw.w2_hi, C, 2 * C, 2 * C, 256))) return r;
       if ((r = tb.make(&fp.w2_lo, lw.w2_lo, C, 2 * C, 2 * C, 256))) return r;
       fp.ln = typename EpiLNRes<256>::Params{lw.ln2_g, lw.ln2_b, w.xh, w.xl};

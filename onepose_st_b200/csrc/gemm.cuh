@@ -83,6 +83,7 @@ struct EpiCtx {
   int group;          // epilogue group (named barriers 1 + 4*group .. 4 + 4*group are reserved for it)
   int part;           // with SPLIT > 1: which slice of the tile's columns this warp handles (0 .. SPLIT-1)
   uint8_t* scratch;   // Epi::kSmemBytes of shared memory private to this epilogue group
+  int scratch_small = 0;  // 1: only half of kLnScratch is there (mlp_fused_kernel): the LayerNorm statistics take two more barriers
 };
 
 // SPLIT = warps per TMEM lane quarter inside one group: the tile's columns are divided among them, so a
