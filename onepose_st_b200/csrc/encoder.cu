@@ -336,12 +336,10 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual str
 // 0.338-0.343, 1258-1260 frames/s end to end against 1217-1220 (same box, back to back, 32 frames per forward); 8 / 16
 // frames per forward: 0.363 / 0.342 against 0.376 / 0.351.
 constexpr int kMlpFusedMinRounds = 6;  // tiles per CTA from which the fused kernel is the default (OPB200_MLP_FUSED overrides)
-constexpr int MF_STAGES = 7;
+constexpr int MF_STAGES = 4;
 constexpr int MF_APL = BLOCK_M * 32 * 2;     // one A plane of a 32-wide k-block: 8 KB
-constexpr int MF_B1PL = 128 * 32 * 2;        // one W1 plane of a quarter (128 hidden columns): 8 KB
-constexpr int MF_B2PL = 256 * 32 * 2;        // one W2 plane: 16 KB
-constexpr int MF_STAGE_BYTES = 2 * MF_APL + 2 * MF_B1PL;  // 32 KB; phase 2 uses the same 32 KB for the two W2 planes
-static_assert(MF_STAGE_BYTES == 2 * MF_B2PL, "one stage size for both phases");
+constexpr int MF_BPL = 256 * 32 * 2;         // one plane of a 256-row weight slab: 16 KB
+constexpr int MF_STAGE_BYTES = 2 * MF_APL + 2 * MF_BPL;  // 48 KB (phase 2 uses the weight part only)
 constexpr int MF_LN_SCRATCH = kLnScratch / 2;  // (EpiCtx::scratch_small)
 // 64-byte swizzle: 512-byte alignment of the operand tiles is enough
 constexpr int MF_SMEM = 512 + MF_STAGES * MF_STAGE_BYTES + 256 + MF_LN_SCRATCH;
@@ -349,22 +347,21 @@ static_assert(MF_SMEM <= 232448, "shared memory of a CTA");
 
 struct MlpFusedParams {
   CUtensorMap x_hi, x_lo, m_hi, m_lo;  // [R, 256] planes, box {32, 128}, 64-byte swizzle
-  CUtensorMap w1_hi, w1_lo;            // [512, 512], box {32, 128}
+  CUtensorMap w1_hi, w1_lo;            // [512, 512], box {32, 256}
   CUtensorMap w2_hi, w2_lo;            // [256, 512], box {32, 256}
   EpiLNRes<256>::Params ln;
   int m_tile_begin, num_tiles;
 };
 
-// Tensor memory: D1 = columns 0..127 (one 128-wide quarter of the hidden tile, fp32), A2 = columns 128..255 (that quarter
-// after the ReLU as bf16 hi / lo planes, 64 columns each: the A operand of phase 2 is read FROM TENSOR MEMORY, so all of
-// shared memory is left to the operand ring -- seven 32 KB stages; with the hidden half in shared memory (128 KB) only two
-// 48 KB stages fitted and the mainloop ran at the latency of one TMA load per stage: 995 us per layer step at 32 frames
-// against 733 us for the two GEMM launches), D2 = columns 256..511 (the output).
-// Order of work (v = 4 * tile + quarter counts the quarters of the CTA's hidden tiles):
-//   tensor pipe:  G1(0) | G1(1) G2(0) | G1(2) G2(1) | ...   -- phase 2 of a quarter is issued one phase 1 later, so the pipe
-//                 has the next quarter's MMAs to run while the epilogue warps turn D1 into the phase-2 operand
-//   epilogue:     e1(v): D1 -> registers (ReLU, split), D1 handed back at once; wait until G2(v - 1) has read A2; tcgen05.st;
-//                 after e1 of a tile's first quarter: LayerNorm2 + residual of the PREVIOUS tile from D2.
+// Tensor memory: D1 = columns 0..255 (one 256-wide half of the hidden tile, fp32), D2 = columns 256..511 (the output).
+// The epilogue warps turn D1 IN PLACE into the A operand of phase 2, one 128-column quarter at a time: quarter a
+// (columns 0..127) becomes bf16 hi (64 columns) | lo (64 columns) of its 128 values, quarter b (128..255) likewise, and
+// phase 2 is a tcgen05.mma that reads A from tensor memory -- all of shared memory is left to the operand ring.
+//   per half u:  G1(u): 16 k-blocks [x | msg] x W1[256 u ..] -> D1 (N = 256)
+//                e1(a) -> G2(a): 4 k-blocks A2a x W2[:, 256 u ..] -> D2;   e1(b) runs under G2(a);   G2(b)
+//   G1(u + 1) overwrites D1 after G2(b) -- the pipe executes a thread's MMAs in order -- so the only time the tensor pipe
+//   waits for the warps is e1(a) (~600 clk per ~18 500 clk half); LayerNorm2 of a tile runs under the next tile's G1.
+// L2 -> SM traffic per tile: [x | msg] twice (0.5 MB) + W1 (1 MB) + W2 (0.5 MB).
 __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(const __grid_constant__ MlpFusedParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 511) & ~uintptr_t(511));
@@ -372,18 +369,15 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + MF_STAGES * MF_STAGE_BYTES);
   uint64_t* empty = full + MF_STAGES;
   uint64_t* d1_full = empty + MF_STAGES;
-  uint64_t* d1_empty = d1_full + 1;
-  uint64_t* a2_full = d1_empty + 1;
-  uint64_t* a2_empty = a2_full + 1;
-  uint64_t* d2_full = a2_empty + 1;
+  uint64_t* a2_full = d1_full + 1;  // [2]: quarters a, b
+  uint64_t* d2_full = a2_full + 2;
   uint64_t* d2_empty = d2_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d2_empty + 1);
   uint8_t* ln_scratch = smem + MF_STAGES * MF_STAGE_BYTES + 256;
-  static_assert((2 * MF_STAGES + 6) * 8 + 4 <= 256, "barrier block");
-  static_assert(512 + MF_STAGES * MF_STAGE_BYTES + 256 + MF_LN_SCRATCH <= 232448, "shared memory of a CTA");
+  static_assert((2 * MF_STAGES + 5) * 8 + 4 <= 256, "barrier block");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int kEpiWarps = 4 * EPI_SPLIT;
-  constexpr uint32_t kD1 = 0, kA2Hi = 128, kA2Lo = 192, kD2 = 256;  // tensor-memory columns
+  constexpr uint32_t kD1 = 0, kD2 = 256;  // tensor-memory columns
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.x_hi);
@@ -394,9 +388,8 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
       ptx::mbar_init(&empty[s], 1);
     }
     ptx::mbar_init(d1_full, 1);
-    ptx::mbar_init(d1_empty, kEpiWarps);
-    ptx::mbar_init(a2_full, kEpiWarps);
-    ptx::mbar_init(a2_empty, 1);
+    ptx::mbar_init(&a2_full[0], kEpiWarps);
+    ptx::mbar_init(&a2_full[1], kEpiWarps);
     ptx::mbar_init(d2_full, 1);
     ptx::mbar_init(d2_empty, kEpiWarps);
     ptx::fence_barrier_init();
@@ -410,7 +403,7 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int n_it = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
-  const int V = 4 * n_it;  // quarters of this CTA
+  const int U = 2 * n_it;  // halves of this CTA
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (same order as the MMA thread)
@@ -420,96 +413,82 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
       auto next = [&]() {
         if (++stage == MF_STAGES) stage = 0, phase ^= 1;
       };
-      auto p1 = [&](int v) {  // [x | msg] and the W1 rows of this quarter
-        const int row = (p.m_tile_begin + static_cast<int>(blockIdx.x) + (v >> 2) * static_cast<int>(gridDim.x)) * BLOCK_M;
-        const int q = v & 3;
-        for (int kb = 0; kb < 16; ++kb) {
+      for (int u = 0; u < U; ++u) {
+        const int row = (p.m_tile_begin + static_cast<int>(blockIdx.x) + (u >> 1) * static_cast<int>(gridDim.x)) * BLOCK_M;
+        const int half = u & 1;
+        for (int kb = 0; kb < 16; ++kb) {  // phase 1: [x | msg] and the W1 slab of this half
           ptx::mbar_wait(&empty[stage], phase ^ 1);
           ptx::mbar_arrive_expect_tx(&full[stage], MF_STAGE_BYTES);
           uint8_t* st = stages + stage * MF_STAGE_BYTES;
           const int ka = (kb & 7) * 32;
           ptx::tma_load_2d(st, kb < 8 ? &p.x_hi : &p.m_hi, &full[stage], ka, row);
           ptx::tma_load_2d(st + MF_APL, kb < 8 ? &p.x_lo : &p.m_lo, &full[stage], ka, row);
-          ptx::tma_load_2d(st + 2 * MF_APL, &p.w1_hi, &full[stage], kb * 32, q * 128);
-          ptx::tma_load_2d(st + 2 * MF_APL + MF_B1PL, &p.w1_lo, &full[stage], kb * 32, q * 128);
+          ptx::tma_load_2d(st + 2 * MF_APL, &p.w1_hi, &full[stage], kb * 32, half * 256);
+          ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.w1_lo, &full[stage], kb * 32, half * 256);
           next();
         }
-      };
-      auto p2 = [&](int v) {  // the W2 columns that meet this quarter of the hidden tile
-        const int q = v & 3;
-        for (int kb = 0; kb < 4; ++kb) {
+        for (int kb = 0; kb < 8; ++kb) {  // phase 2: the W2 columns that meet this half (quarter a: kb 0..3, b: 4..7)
           ptx::mbar_wait(&empty[stage], phase ^ 1);
-          ptx::mbar_arrive_expect_tx(&full[stage], MF_STAGE_BYTES);
+          ptx::mbar_arrive_expect_tx(&full[stage], 2 * MF_BPL);
           uint8_t* st = stages + stage * MF_STAGE_BYTES;
-          ptx::tma_load_2d(st, &p.w2_hi, &full[stage], q * 128 + kb * 32, 0);
-          ptx::tma_load_2d(st + MF_B2PL, &p.w2_lo, &full[stage], q * 128 + kb * 32, 0);
+          ptx::tma_load_2d(st + 2 * MF_APL, &p.w2_hi, &full[stage], half * 256 + kb * 32, 0);
+          ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.w2_lo, &full[stage], half * 256 + kb * 32, 0);
           next();
         }
-      };
-      for (int v = 0; v < V; ++v) {
-        p1(v);
-        if (v >= 1) p2(v - 1);
       }
-      if (V > 0) p2(V - 1);
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (ptx::elect_one()) {
-      constexpr uint32_t idesc1 = ptx::make_idesc_bf16(BLOCK_M, 128), idesc2 = ptx::make_idesc_bf16(BLOCK_M, 256);
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, 256);
       const uint32_t d1 = tmem_base + kD1, d2 = tmem_base + kD2;
       int stage = 0;
       uint32_t phase = 0;
       auto next = [&]() {
         if (++stage == MF_STAGES) stage = 0, phase ^= 1;
       };
-      auto g1 = [&](int v) {
-        ptx::mbar_wait(d1_empty, (static_cast<uint32_t>(v) & 1) ^ 1);  // the epilogue has taken the previous quarter out of D1
-        ptx::tc_fence_after();
+      for (int u = 0; u < U; ++u) {
+        const int half = u & 1;
+        const uint32_t u1 = static_cast<uint32_t>(u);
+        // (D1 is free: G2 of the previous half was issued after the warps had read and rewritten it, and runs before this)
         for (int kb = 0; kb < 16; ++kb) {
           ptx::mbar_wait(&full[stage], phase);
           ptx::tc_fence_after();
           const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
           const uint64_t a_hi = ptx::make_desc_sw64(sa), a_lo = ptx::make_desc_sw64(sa + MF_APL);
-          const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + MF_B1PL);
+          const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + MF_BPL);
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_hi + 2 * k, idesc1, !(kb == 0 && k == 0));
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_hi + 2 * k, idesc, !(kb == 0 && k == 0));
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_lo + 2 * k, b_hi + 2 * k, idesc1, 1);
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_lo + 2 * k, b_hi + 2 * k, idesc, 1);
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_lo + 2 * k, idesc1, 1);
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_lo + 2 * k, idesc, 1);
           ptx::mma_commit(&empty[stage]);
           next();
         }
         ptx::mma_commit(d1_full);
-      };
-      auto g2 = [&](int v) {
-        const int q = v & 3;
-        if (q == 0) ptx::mbar_wait(d2_empty, (static_cast<uint32_t>(v >> 2) & 1) ^ 1);  // the previous tile's output has been read
-        ptx::mbar_wait(a2_full, static_cast<uint32_t>(v) & 1);  // this quarter of the hidden tile is in tensor memory
-        ptx::tc_fence_after();
-        for (int kb = 0; kb < 4; ++kb) {
+        if (half == 0) ptx::mbar_wait(d2_empty, (static_cast<uint32_t>(u >> 1) & 1) ^ 1);  // the previous tile's output has been read
+        for (int kb = 0; kb < 8; ++kb) {
+          if ((kb & 3) == 0) {
+            ptx::mbar_wait(&a2_full[kb >> 2], u1 & 1);  // this quarter of the hidden tile is in tensor memory as bf16 planes
+            ptx::tc_fence_after();
+          }
           ptx::mbar_wait(&full[stage], phase);
           ptx::tc_fence_after();
           const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
-          const uint64_t b_hi = ptx::make_desc_sw64(sa), b_lo = ptx::make_desc_sw64(sa + MF_B2PL);
-          const uint32_t a_hi = tmem_base + kA2Hi + 16 * kb, a_lo = tmem_base + kA2Lo + 16 * kb;
+          const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + MF_BPL);
+          const uint32_t a_hi = tmem_base + kD1 + 128 * (kb >> 2) + 16 * (kb & 3), a_lo = a_hi + 64;
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_hi + 2 * k, idesc2, !(q == 0 && kb == 0 && k == 0));
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_hi + 2 * k, idesc, !(half == 0 && kb == 0 && k == 0));
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_lo + 8 * k, b_hi + 2 * k, idesc2, 1);
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_lo + 8 * k, b_hi + 2 * k, idesc, 1);
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_lo + 2 * k, idesc2, 1);
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_lo + 2 * k, idesc, 1);
           ptx::mma_commit(&empty[stage]);
           next();
         }
-        ptx::mma_commit(a2_empty);
-        if (q == 3) ptx::mma_commit(d2_full);
-      };
-      for (int v = 0; v < V; ++v) {
-        g1(v);
-        if (v >= 1) g2(v - 1);
+        if (half == 1) ptx::mma_commit(d2_full);
       }
-      if (V > 0) g2(V - 1);
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps: (column part, TMEM lane quarter)
@@ -523,49 +502,50 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
     ctx.scratch = ln_scratch;
     ctx.scratch_small = 1;
     const uint32_t lane_field = static_cast<uint32_t>(ctx.quarter * 32) << 16;
-    auto layer_norm = [&](int it) {
-      ctx.m_tile = p.m_tile_begin + static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x);
-      EpiLNRes<256>::prefetch(p.ln, ctx);
-      ptx::mbar_wait(d2_full, static_cast<uint32_t>(it) & 1);
+    const int bar_id = 1 + ctx.quarter;  // the four warps (column parts) of a TMEM lane quarter
+    for (int u = 0; u < U; ++u) {
+      const uint32_t u1 = static_cast<uint32_t>(u);
+      ptx::mbar_wait(d1_full, u1 & 1);
       ptx::tc_fence_after();
-      ctx.tmem_acc = tmem_base + kD2 + lane_field;
-      EpiLNRes<256>::run(p.ln, ctx);
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(d2_empty);
-    };
-    for (int v = 0; v < V; ++v) {
-      const uint32_t v1 = static_cast<uint32_t>(v);
-      ptx::mbar_wait(d1_full, v1 & 1);
-      ptx::tc_fence_after();
-      // this warp's 32 columns of the quarter: out of D1 into registers (ReLU, bf16 hi / lo), D1 goes back at once
-      uint32_t h[16], l[16];
-      {
-        float x[32];
-        load_acc32(tmem_base + kD1 + lane_field + ctx.part * 32, x);
+#pragma unroll 1
+      for (int qq = 0; qq < 2; ++qq) {
+        // this warp's 32 columns of the quarter -> ReLU -> bf16 hi / lo; the planes go back into the quarter's own columns
+        // once the four warps that share these lanes have all read theirs
+        const uint32_t qbase = tmem_base + kD1 + lane_field + 128 * qq;
+        uint32_t h[16], l[16];
+        {
+          float x[32];
+          load_acc32(qbase + ctx.part * 32, x);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          __nv_bfloat16 h0, l0, h1, l1;
-          split_bf16(fmaxf(x[2 * i], 0.f), h0, l0);
-          split_bf16(fmaxf(x[2 * i + 1], 0.f), h1, l1);
-          h[i] = pack_bf16(h0, h1);
-          l[i] = pack_bf16(l0, l1);
+          for (int i = 0; i < 16; ++i) {
+            __nv_bfloat16 h0, l0, h1, l1;
+            split_bf16(fmaxf(x[2 * i], 0.f), h0, l0);
+            split_bf16(fmaxf(x[2 * i + 1], 0.f), h1, l1);
+            h[i] = pack_bf16(h0, h1);
+            l[i] = pack_bf16(l0, l1);
+          }
         }
+        ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);
+        ptx::tmem_st16(qbase + ctx.part * 16, h);
+        ptx::tmem_st16(qbase + 64 + ctx.part * 16, l);
+        ptx::tmem_st_wait();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&a2_full[qq]);
       }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(d1_empty);
-      ptx::mbar_wait(a2_empty, (v1 & 1) ^ 1);  // phase 2 of the previous quarter has read the operand columns
-      ptx::tc_fence_after();
-      ptx::tmem_st16(tmem_base + kA2Hi + lane_field + ctx.part * 16, h);
-      ptx::tmem_st16(tmem_base + kA2Lo + lane_field + ctx.part * 16, l);
-      ptx::tmem_st_wait();
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(a2_full);
-      if ((v & 3) == 0 && v >= 4) layer_norm((v >> 2) - 1);
+      if (u & 1) {  // LayerNorm2 + residual of this tile (its last phase 2 runs now; the next tile's phase 1 follows it)
+        const int it = u >> 1;
+        ctx.m_tile = p.m_tile_begin + static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x);
+        EpiLNRes<256>::prefetch(p.ln, ctx);
+        ptx::mbar_wait(d2_full, static_cast<uint32_t>(it) & 1);
+        ptx::tc_fence_after();
+        ctx.tmem_acc = tmem_base + kD2 + lane_field;
+        EpiLNRes<256>::run(p.ln, ctx);
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(d2_empty);
+      }
     }
-    if (n_it > 0) layer_norm(n_it - 1);
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -1374,8 +1354,8 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       if ((r = tb.make(&fp.x_lo, w.xl, R, C, C, BLOCK_M))) return r;
       if ((r = tb.make(&fp.m_hi, w.mh, R, C, C, BLOCK_M))) return r;
       if ((r = tb.make(&fp.m_lo, w.ml, R, C, C, BLOCK_M))) return r;
-      if ((r = tb.make(&fp.w1_hi, lw.w1_hi, 2 * C, 2 * C, 2 * C, 128))) return r;
-      if ((r = tb.make(&fp.w1_lo, lw.w1_lo, 2 * C, 2 * C, 2 * C, 128))) return r;
+      if ((r = tb.make(&fp.w1_hi, lw.w1_hi, 2 * C, 2 * C, 2 * C, 256))) return r;
+      if ((r = tb.make(&fp.w1_lo, lw.w1_lo, 2 * C, 2 * C, 2 * C, 256))) return r;
       if ((r = tb.make(&fp.w2_hi, lw.w2_hi, C, 2 * C, 2 * C, 256))) return r;
       if ((r = tb.make(&fp.w2_lo, lw.w2_lo, C, 2 * C, 2 * C, 256))) return r;
       fp.ln = typename EpiLNRes<256>::Params{lw.ln2_g, lw.ln2_b, w.xh, w.xl};
