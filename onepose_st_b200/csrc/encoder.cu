@@ -338,18 +338,19 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual str
 constexpr int kMlpFusedMinRounds = 6;  // tiles per CTA from which the fused kernel is the default (OPB200_MLP_FUSED overrides)
 constexpr int MF_STAGES = 4;
 constexpr int MF_APL = BLOCK_M * 32 * 2;     // one A plane of a 32-wide k-block: 8 KB
-constexpr int MF_BPL = 256 * 32 * 2;         // one plane of a 256-row weight slab: 16 KB
+constexpr int MF_BPL = 256 * 32 * 2;         // one plane of a 256-row weight slab: 16 KB (phase 2 at C = 128: 128 rows)
 constexpr int MF_STAGE_BYTES = 2 * MF_APL + 2 * MF_BPL;  // 48 KB (phase 2 uses the weight part only)
 constexpr int MF_LN_SCRATCH = kLnScratch / 2;  // (EpiCtx::scratch_small)
 // 64-byte swizzle: 512-byte alignment of the operand tiles is enough
 constexpr int MF_SMEM = 512 + MF_STAGES * MF_STAGE_BYTES + 256 + MF_LN_SCRATCH;
 static_assert(MF_SMEM <= 232448, "shared memory of a CTA");
 
+template <int C>
 struct MlpFusedParams {
-  CUtensorMap x_hi, x_lo, m_hi, m_lo;  // [R, 256] planes, box {32, 128}, 64-byte swizzle
-  CUtensorMap w1_hi, w1_lo;            // [512, 512], box {32, 256}
-  CUtensorMap w2_hi, w2_lo;            // [256, 512], box {32, 256}
-  EpiLNRes<256>::Params ln;
+  CUtensorMap x_hi, x_lo, m_hi, m_lo;  // [R, C] planes, box {32, 128}, 64-byte swizzle
+  CUtensorMap w1_hi, w1_lo;            // [2C, 2C], box {32, 256}
+  CUtensorMap w2_hi, w2_lo;            // [C, 2C], box {32, C}
+  typename EpiLNRes<C>::Params ln;
   int m_tile_begin, num_tiles;
 };
 
@@ -361,8 +362,13 @@ struct MlpFusedParams {
 //                e1(a) -> G2(a): 4 k-blocks A2a x W2[:, 256 u ..] -> D2;   e1(b) runs under G2(a);   G2(b)
 //   G1(u + 1) overwrites D1 after G2(b) -- the pipe executes a thread's MMAs in order -- so the only time the tensor pipe
 //   waits for the warps is e1(a) (~600 clk per ~18 500 clk half); LayerNorm2 of a tile runs under the next tile's G1.
-// L2 -> SM traffic per tile: [x | msg] twice (0.5 MB) + W1 (1 MB) + W2 (0.5 MB).
-__global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(const __grid_constant__ MlpFusedParams p) {
+// L2 -> SM traffic per tile (C = 256): [x | msg] twice (0.5 MB) + W1 (1 MB) + W2 (0.5 MB).  C = 128 (fine level): the hidden
+// tile is one 256-wide "half", D2 has 128 columns.
+template <int C>
+__global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(const __grid_constant__ MlpFusedParams<C> p) {
+  constexpr int HALVES = 2 * C / 256;  // 256-wide parts of the hidden tile
+  constexpr int KB1 = 2 * C / 32;      // k-blocks of phase 1; the first C / 32 come from x, the rest from msg
+  constexpr int B2PL = C * 32 * 2;     // one W2 plane of a k-block
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 511) & ~uintptr_t(511));
   uint8_t* stages = smem;
@@ -403,7 +409,7 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int n_it = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
-  const int U = 2 * n_it;  // halves of this CTA
+  const int U = HALVES * n_it;  // halves of this CTA
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (same order as the MMA thread)
@@ -414,25 +420,25 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
         if (++stage == MF_STAGES) stage = 0, phase ^= 1;
       };
       for (int u = 0; u < U; ++u) {
-        const int row = (p.m_tile_begin + static_cast<int>(blockIdx.x) + (u >> 1) * static_cast<int>(gridDim.x)) * BLOCK_M;
-        const int half = u & 1;
-        for (int kb = 0; kb < 16; ++kb) {  // phase 1: [x | msg] and the W1 slab of this half
+        const int row = (p.m_tile_begin + static_cast<int>(blockIdx.x) + (u / HALVES) * static_cast<int>(gridDim.x)) * BLOCK_M;
+        const int half = u % HALVES;
+        for (int kb = 0; kb < KB1; ++kb) {  // phase 1: [x | msg] and the W1 slab of this half
           ptx::mbar_wait(&empty[stage], phase ^ 1);
           ptx::mbar_arrive_expect_tx(&full[stage], MF_STAGE_BYTES);
           uint8_t* st = stages + stage * MF_STAGE_BYTES;
-          const int ka = (kb & 7) * 32;
-          ptx::tma_load_2d(st, kb < 8 ? &p.x_hi : &p.m_hi, &full[stage], ka, row);
-          ptx::tma_load_2d(st + MF_APL, kb < 8 ? &p.x_lo : &p.m_lo, &full[stage], ka, row);
+          const int ka = (kb % (C / 32)) * 32;
+          ptx::tma_load_2d(st, kb < C / 32 ? &p.x_hi : &p.m_hi, &full[stage], ka, row);
+          ptx::tma_load_2d(st + MF_APL, kb < C / 32 ? &p.x_lo : &p.m_lo, &full[stage], ka, row);
           ptx::tma_load_2d(st + 2 * MF_APL, &p.w1_hi, &full[stage], kb * 32, half * 256);
           ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.w1_lo, &full[stage], kb * 32, half * 256);
           next();
         }
         for (int kb = 0; kb < 8; ++kb) {  // phase 2: the W2 columns that meet this half (quarter a: kb 0..3, b: 4..7)
           ptx::mbar_wait(&empty[stage], phase ^ 1);
-          ptx::mbar_arrive_expect_tx(&full[stage], 2 * MF_BPL);
+          ptx::mbar_arrive_expect_tx(&full[stage], 2 * B2PL);
           uint8_t* st = stages + stage * MF_STAGE_BYTES;
           ptx::tma_load_2d(st + 2 * MF_APL, &p.w2_hi, &full[stage], half * 256 + kb * 32, 0);
-          ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.w2_lo, &full[stage], half * 256 + kb * 32, 0);
+          ptx::tma_load_2d(st + 2 * MF_APL + B2PL, &p.w2_lo, &full[stage], half * 256 + kb * 32, 0);
           next();
         }
       }
@@ -440,7 +446,7 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (ptx::elect_one()) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, 256);
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(BLOCK_M, 256), idesc2 = ptx::make_idesc_bf16(BLOCK_M, C);
       const uint32_t d1 = tmem_base + kD1, d2 = tmem_base + kD2;
       int stage = 0;
       uint32_t phase = 0;
@@ -448,10 +454,10 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
         if (++stage == MF_STAGES) stage = 0, phase ^= 1;
       };
       for (int u = 0; u < U; ++u) {
-        const int half = u & 1;
+        const int half = u % HALVES;
         const uint32_t u1 = static_cast<uint32_t>(u);
         // (D1 is free: G2 of the previous half was issued after the warps had read and rewritten it, and runs before this)
-        for (int kb = 0; kb < 16; ++kb) {
+        for (int kb = 0; kb < KB1; ++kb) {
           ptx::mbar_wait(&full[stage], phase);
           ptx::tc_fence_after();
           const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
@@ -467,7 +473,7 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
           next();
         }
         ptx::mma_commit(d1_full);
-        if (half == 0) ptx::mbar_wait(d2_empty, (static_cast<uint32_t>(u >> 1) & 1) ^ 1);  // the previous tile's output has been read
+        if (half == 0) ptx::mbar_wait(d2_empty, (static_cast<uint32_t>(u / HALVES) & 1) ^ 1);  // the previous tile's output has been read
         for (int kb = 0; kb < 8; ++kb) {
           if ((kb & 3) == 0) {
             ptx::mbar_wait(&a2_full[kb >> 2], u1 & 1);  // this quarter of the hidden tile is in tensor memory as bf16 planes
@@ -476,18 +482,18 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
           ptx::mbar_wait(&full[stage], phase);
           ptx::tc_fence_after();
           const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
-          const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + MF_BPL);
+          const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + B2PL);
           const uint32_t a_hi = tmem_base + kD1 + 128 * (kb >> 2) + 16 * (kb & 3), a_lo = a_hi + 64;
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_hi + 2 * k, idesc, !(half == 0 && kb == 0 && k == 0));
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_hi + 2 * k, idesc2, !(half == 0 && kb == 0 && k == 0));
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_lo + 8 * k, b_hi + 2 * k, idesc, 1);
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_lo + 8 * k, b_hi + 2 * k, idesc2, 1);
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_lo + 2 * k, idesc, 1);
+          for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d2, a_hi + 8 * k, b_lo + 2 * k, idesc2, 1);
           ptx::mma_commit(&empty[stage]);
           next();
         }
-        if (half == 1) ptx::mma_commit(d2_full);
+        if (half == HALVES - 1) ptx::mma_commit(d2_full);
       }
     }
   } else {
@@ -533,14 +539,14 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&a2_full[qq]);
       }
-      if (u & 1) {  // LayerNorm2 + residual of this tile (its last phase 2 runs now; the next tile's phase 1 follows it)
-        const int it = u >> 1;
+      if (u % HALVES == HALVES - 1) {  // LayerNorm2 + residual of this tile (its last phase 2 runs now; the next tile's phase 1 follows it)
+        const int it = u / HALVES;
         ctx.m_tile = p.m_tile_begin + static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x);
-        EpiLNRes<256>::prefetch(p.ln, ctx);
+        EpiLNRes<C>::prefetch(p.ln, ctx);
         ptx::mbar_wait(d2_full, static_cast<uint32_t>(it) & 1);
         ptx::tc_fence_after();
         ctx.tmem_acc = tmem_base + kD2 + lane_field;
-        EpiLNRes<256>::run(p.ln, ctx);
+        EpiLNRes<C>::run(p.ln, ctx);
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(d2_empty);
@@ -1345,31 +1351,29 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
   // each or more (a CTA's tiles run back to back, so a short list ends in a round that is mostly empty)
   static const int mlp_fused_env = getenv("OPB200_MLP_FUSED") ? atoi(getenv("OPB200_MLP_FUSED")) : -1;
   const bool mlp_fused = mlp_fused_env >= 0 ? mlp_fused_env != 0 : uc >= kMlpFusedMinRounds * num_sms();
-  if (mlp_fused && C == 256 && x3) {
-    if constexpr (C == 256) {
-      MlpFusedParams fp;
-      PlanBuilder tb(true);
-      int r;
-      if ((r = tb.make(&fp.x_hi, w.xh, R, C, C, BLOCK_M))) return r;
-      if ((r = tb.make(&fp.x_lo, w.xl, R, C, C, BLOCK_M))) return r;
-      if ((r = tb.make(&fp.m_hi, w.mh, R, C, C, BLOCK_M))) return r;
-      if ((r = tb.make(&fp.m_lo, w.ml, R, C, C, BLOCK_M))) return r;
-      if ((r = tb.make(&fp.w1_hi, lw.w1_hi, 2 * C, 2 * C, 2 * C, 256))) return r;
-      if ((r = tb.make(&fp.w1_lo, lw.w1_lo, 2 * C, 2 * C, 2 * C, 256))) return r;
-      if ((r = tb.make(&fp.w2_hi, lw.w2_hi, C, 2 * C, 2 * C, 256))) return r;
-      if ((r = tb.make(&fp.w2_lo, lw.w2_lo, C, 2 * C, 2 * C, 256))) return r;
-      fp.ln = typename EpiLNRes<256>::Params{lw.ln2_g, lw.ln2_b, w.xh, w.xl};
-      fp.m_tile_begin = ub, fp.num_tiles = uc;
-      if (uc > 0) {
-        static std::atomic<unsigned long long> configured_mf{0};
-        if (int rr = opt_in_dyn_smem(mlp_fused_kernel, MF_SMEM, configured_mf)) return rr;
-        const int grid = uc < num_sms() ? uc : num_sms();
-        mlp_fused_kernel<<<grid, 64 + 128 * EPI_SPLIT, MF_SMEM, stream>>>(fp);
-        count_launch();
-        OPB_CHECK_CUDA(cudaGetLastError());
-      }
-      return OPB_OK;
+  if (mlp_fused && x3) {
+    MlpFusedParams<C> fp;
+    PlanBuilder tb(true);
+    int r;
+    if ((r = tb.make(&fp.x_hi, w.xh, R, C, C, BLOCK_M))) return r;
+    if ((r = tb.make(&fp.x_lo, w.xl, R, C, C, BLOCK_M))) return r;
+    if ((r = tb.make(&fp.m_hi, w.mh, R, C, C, BLOCK_M))) return r;
+    if ((r = tb.make(&fp.m_lo, w.ml, R, C, C, BLOCK_M))) return r;
+    if ((r = tb.make(&fp.w1_hi, lw.w1_hi, 2 * C, 2 * C, 2 * C, 256))) return r;
+    if ((r = tb.make(&fp.w1_lo, lw.w1_lo, 2 * C, 2 * C, 2 * C, 256))) return r;
+    if ((r = tb.make(&fp.w2_hi, lw.w2_hi, C, 2 * C, 2 * C, C))) return r;
+    if ((r = tb.make(&fp.w2_lo, lw.w2_lo, C, 2 * C, 2 * C, C))) return r;
+    fp.ln = typename EpiLNRes<C>::Params{lw.ln2_g, lw.ln2_b, w.xh, w.xl};
+    fp.m_tile_begin = ub, fp.num_tiles = uc;
+    if (uc > 0) {
+      static std::atomic<unsigned long long> configured_mf{0};
+      if (int rr = opt_in_dyn_smem(mlp_fused_kernel<C>, MF_SMEM, configured_mf)) return rr;
+      const int grid = uc < num_sms() ? uc : num_sms();
+      mlp_fused_kernel<C><<<grid, 64 + 128 * EPI_SPLIT, MF_SMEM, stream>>>(fp);
+      count_launch();
+      OPB_CHECK_CUDA(cudaGetLastError());
     }
+    return OPB_OK;
   }
   // ---- 6. MLP1 + ReLU   (K = [x | msg], N = 2C as two tiles of C)
   {
