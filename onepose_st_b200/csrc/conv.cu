@@ -37,6 +37,7 @@ struct ConvPlan {
   // issued for the three products hi*hi, lo*hi, hi*lo -- fp32-grade convolutions on the fp16 tensor pipe (terms = 3,
   // plane = channels of one plane); plain fp16 mode: terms = 1.
   int terms, plane;
+  CUtensorMap xh_map;  // HALO kernels: the same tensor with boxes two rows taller (8 * MSUB + 2): one box serves the taps ky = 0..2
   long long* trace;  // debug (opb200_debug_trace): per CTA and tile {first TMA, MMA start, accumulator full, epilogue done}
 };
 
@@ -86,6 +87,25 @@ struct ConvCfg {
   static_assert(STAGE_BYTES % 1024 == 0, "stage alignment");
   static_assert(ACC_COLS <= 512, "TMEM");
   static_assert(STAGES >= 3, "ring too shallow");
+};
+
+// HALO (3x3, stride 1): the three taps of one kernel column read the same pixels one row apart, so ONE box of
+// 8 * MSUB + 2 rows at the column's x shift serves ky = 0, 1, 2 -- the A operand of tap ky starts ky rows (2048 bytes: a
+// whole number of swizzle atoms) into it.  The activations cross the L2 -> SM path three times per 64 channels instead of
+// nine; that path, not the tensor pipe, bounds these layers (2.0 GB per 174 us launch = 11.5 TB/s in round 1's ncu capture
+// of the 128-channel layers, the ~6300 B/clk the L2 delivers chip-wide).  Shared memory: three halo buffers + a ring of
+// weight slabs (one per tap), each with its own full / empty barriers.
+template <int BN, int MSUB>
+struct HaloCfg {
+  static constexpr int A_BYTES = (CONV_TH * MSUB + 2) * CONV_TW * BLOCK_K * 2;
+  static constexpr int B_BYTES = BN * BLOCK_K * 2;
+  static constexpr int NA = 3;
+  static constexpr int NB = (222 * 1024 - NA * A_BYTES) / B_BYTES;
+  static constexpr int SMEM = 1024 + NA * A_BYTES + NB * B_BYTES + 256;
+  static_assert(A_BYTES % 1024 == 0 && B_BYTES % 1024 == 0, "swizzle atoms");
+  static_assert(NB >= 3 && NB <= 10, "weight ring");
+  static_assert((2 * NA + 2 * NB + 4) * 8 + 4 <= 256, "barrier block");
+  static_assert(SMEM <= 227 * 1024, "shared memory budget exceeded");
 };
 
 // 16 accumulator columns of one pixel: bias, residual, activation, stores.
@@ -211,17 +231,23 @@ __device__ __forceinline__ void conv_epi_chunk(const uint32_t (&r)[16], const Co
 // the weight slab and multicasts it into both CTAs' shared memory, so the L2 -> SM weight traffic per flop halves
 // (the BN = 208 layers are bound by that fill, not by the tensor pipe).  A stage is refilled only after the MMAs of
 // both CTAs have read it (empty barriers count two multicast commits).
-template <int BN, int MSUB, bool CL2, bool SPLIT>
+template <int BN, int MSUB, bool CL2, bool SPLIT, bool HALO>
 __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant__ ConvPlan plan, const ConvEpi ep) {
   using Cfg = ConvCfg<BN, MSUB>;
-  constexpr int STAGES = Cfg::STAGES;
+  using HCfg = HaloCfg<BN, MSUB>;
+  static_assert(!(CL2 && HALO), "the halo kernels do not multicast");
+  constexpr int STAGES = HALO ? HCfg::NB : Cfg::STAGES;  // HALO: full_bar / empty_bar belong to the weight ring
+  constexpr int NA = HALO ? HCfg::NA : 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint8_t* smem_hb = smem + HCfg::NA * HCfg::A_BYTES;  // HALO: weight ring behind the halo buffers
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(HALO ? smem_hb + HCfg::NB * HCfg::B_BYTES : smem + STAGES * Cfg::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* afull_bar = tempty_bar + 2;   // HALO only
+  uint64_t* aempty_bar = afull_bar + NA;  // HALO only
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty_bar + NA);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -236,6 +262,13 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
       ptx::mbar_init(&tempty_bar[s], 16);
+    }
+    if constexpr (HALO) {
+      ptx::prefetch_tmap(&plan.xh_map);
+      for (int s = 0; s < NA; ++s) {
+        ptx::mbar_init(&afull_bar[s], 1);
+        ptx::mbar_init(&aempty_bar[s], 1);
+      }
     }
     ptx::fence_barrier_init();
   }
@@ -261,8 +294,8 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (ptx::elect_one()) {
-      int stage = 0;
-      uint32_t phase = 0;
+      int stage = 0, astage = 0;
+      uint32_t phase = 0, aphase = 0;
       for (int tq = t_first; tq < plan.num_tiles; tq += t_step) {
         const int t = min(tq + crank, plan.num_tiles - 1);
         const int n = t / tiles_per_img;
@@ -273,6 +306,26 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
         if (plan.trace != nullptr) {
           const int it = (tq - t_first) / t_step;
           if (it < kTraceTilesPerCta) plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 0] = clock64();
+        }
+        if constexpr (HALO) {
+          for (int kx = 0; kx < 3; ++kx) {
+            for (int term = 0; term < plan.terms; ++term) {
+              const int a0 = term == 1 ? plan.plane : 0, b0 = term == 2 ? plan.plane : 0;
+              for (int ch = 0; ch < plan.nchunks; ++ch) {
+                ptx::mbar_wait(&aempty_bar[astage], aphase ^ 1);
+                ptx::mbar_arrive_expect_tx(&afull_bar[astage], HCfg::A_BYTES);
+                tma_load_4d(smem + astage * HCfg::A_BYTES, &plan.xh_map, &afull_bar[astage], a0 + ch * BLOCK_K, ix0 + kx, iy0, n);
+                if (++astage == NA) astage = 0, aphase ^= 1;
+                for (int ky = 0; ky < 3; ++ky) {
+                  ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                  ptx::mbar_arrive_expect_tx(&full_bar[stage], HCfg::B_BYTES);
+                  ptx::tma_load_2d(smem_hb + stage * HCfg::B_BYTES, &plan.w_map, &full_bar[stage], b0 + ch * BLOCK_K, (ky * 3 + kx) * BN);
+                  if (++stage == STAGES) stage = 0, phase ^= 1;
+                }
+              }
+            }
+          }
+          continue;
         }
         for (int tap = 0; tap < taps; ++tap) {
           const int ky = tap / plan.ksize, kx = tap - ky * plan.ksize;
@@ -301,8 +354,8 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     constexpr uint32_t idesc = ptx::make_idesc_f16(BLOCK_M, BN);
-    int stage = 0;
-    uint32_t phase = 0;
+    int stage = 0, astage = 0;
+    uint32_t phase = 0, aphase = 0;
     int it = 0;
     const int total_kb = taps * plan.terms * plan.nchunks;
     for (int tq = t_first; tq < plan.num_tiles; tq += t_step, ++it) {
@@ -313,6 +366,50 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
       const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_COLS;
       if (plan.trace != nullptr && it < kTraceTilesPerCta && lane == 0)
         plan.trace[(blockIdx.x * kTraceTilesPerCta + it) * 4 + 1] = clock64();
+      if constexpr (HALO) {
+        // one elected thread issues the whole tile: the per-k-block warp-wide election and the run-time k loops of the
+        // per-tap path cost ~150 clk per sub-tile, which the 64-clk MMAs of the 128-channel layers do not hide
+        if (ptx::elect_one()) {
+          const int groups = 3 * plan.terms * plan.nchunks;  // (kx, term, chunk): one halo box, three weight slabs
+          int ch = 0;
+          for (int g = 0; g < groups; ++g) {
+            ptx::mbar_wait(&afull_bar[astage], aphase);
+            const bool last_chunk = ch == plan.nchunks - 1;
+            const uint32_t a_addr = ptx::smem_u32(smem + astage * HCfg::A_BYTES);
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky) {
+              ptx::mbar_wait(&full_bar[stage], phase);
+              ptx::tc_fence_after();
+              const uint64_t b_desc = ptx::make_desc_sw128(ptx::smem_u32(smem_hb + stage * HCfg::B_BYTES));
+              // sub-tile s, tap row ky: the operand starts (8 s + ky) pixel rows into the halo box
+              if (!last_chunk || plan.nk_last == BLOCK_K / 16) {
+#pragma unroll
+                for (int s = 0; s < MSUB; ++s) {
+                  const uint64_t a_desc = ptx::make_desc_sw128(a_addr + (s * CONV_TH + ky) * (CONV_TW * BLOCK_K * 2));
+#pragma unroll
+                  for (int k = 0; k < BLOCK_K / 16; ++k)
+                    ptx::mma_bf16(d_tmem + s * BN, a_desc + 2 * k, b_desc + 2 * k, idesc, (g | ky | k) != 0);
+                }
+              } else {
+#pragma unroll
+                for (int s = 0; s < MSUB; ++s) {
+                  const uint64_t a_desc = ptx::make_desc_sw128(a_addr + (s * CONV_TH + ky) * (CONV_TW * BLOCK_K * 2));
+                  for (int k = 0; k < plan.nk_last; ++k)
+                    ptx::mma_bf16(d_tmem + s * BN, a_desc + 2 * k, b_desc + 2 * k, idesc, (g | ky | k) != 0);
+                }
+              }
+              ptx::mma_commit(&empty_bar[stage]);
+              if (ky == 2) ptx::mma_commit(&aempty_bar[astage]);
+              if (g == groups - 1 && ky == 2) ptx::mma_commit(&tfull_bar[acc]);
+              if (++stage == STAGES) stage = 0, phase ^= 1;
+            }
+            if (++astage == NA) astage = 0, aphase ^= 1;
+            if (++ch == plan.nchunks) ch = 0;
+          }
+        }
+        __syncwarp();
+        continue;
+      }
       int ch = 0;
       for (int kb = 0; kb < total_kb; ++kb) {
         ptx::mbar_wait(&full_bar[stage], phase);
@@ -421,13 +518,14 @@ __global__ void __launch_bounds__(64 + 512, 1) conv_kernel(const __grid_constant
   }
 }
 
-template <int BN, int MSUB, bool CL2, bool SPLIT = false>
+template <int BN, int MSUB, bool CL2, bool SPLIT = false, bool HALO = false>
 static int launch_conv(const ConvPlan& plan_in, const ConvEpi& ep, cudaStream_t stream) {
   using Cfg = ConvCfg<BN, MSUB>;
-  auto kern = conv_kernel<BN, MSUB, CL2, SPLIT>;
+  auto kern = conv_kernel<BN, MSUB, CL2, SPLIT, HALO>;
   static_assert(Cfg::SMEM <= 227 * 1024, "shared memory budget exceeded");
+  constexpr int kSmem = HALO ? HaloCfg<BN, MSUB>::SMEM : Cfg::SMEM;
   static std::atomic<unsigned long long> configured_dev{0};
-  if (int r = opt_in_dyn_smem(kern, Cfg::SMEM, configured_dev)) return r;
+  if (int r = opt_in_dyn_smem(kern, kSmem, configured_dev)) return r;
   static std::atomic<int> max_clusters_a{0};  // (all devices of a box are the same part)
   int max_clusters = max_clusters_a.load();
   if (max_clusters == 0) {
@@ -436,7 +534,7 @@ static int launch_conv(const ConvPlan& plan_in, const ConvEpi& ep, cudaStream_t 
       cudaLaunchConfig_t q = {};
       q.gridDim = dim3(2 * num_sms());
       q.blockDim = dim3(64 + 512);
-      q.dynamicSmemBytes = Cfg::SMEM;
+      q.dynamicSmemBytes = kSmem;
       cudaLaunchAttribute a[1];
       a[0].id = cudaLaunchAttributeClusterDimension;
       a[0].val.clusterDim.x = 2;
@@ -472,7 +570,7 @@ static int launch_conv(const ConvPlan& plan_in, const ConvEpi& ep, cudaStream_t 
   }
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(64 + 512);
-  cfg.dynamicSmemBytes = Cfg::SMEM;
+  cfg.dynamicSmemBytes = kSmem;
   cfg.stream = stream;
   if (grid <= 148) plan.trace = next_trace_slot(grid);
   OPB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, plan, ep));
@@ -521,6 +619,14 @@ static int conv_dispatch(ConvPlan& plan, const ConvEpi& ep, const void* x, int H
     const uint32_t wbox[2] = {BLOCK_K, static_cast<uint32_t>(cl2 ? BN / 2 : BN)};
     const uint32_t westr[2] = {1, 1};
     if (int r = encode_tmap_16bit(&plan.w_map, true, 2, w, wdim, wstr, wbox, westr)) return r;
+  }
+  // 3x3, stride 1: one halo box per kernel column instead of one box per tap (OPB200_CONV_HALO=0: the per-tap kernels)
+  static const bool halo_env = std::getenv("OPB200_CONV_HALO") ? std::getenv("OPB200_CONV_HALO")[0] != '0' : true;
+  if (halo_env && plan.ksize == 3 && plan.stride == 1 && !cl2) {
+    const uint32_t hbox[4] = {BLOCK_K, CONV_TW, static_cast<uint32_t>(CONV_TH * msub + 2), 1};
+    if (int r = encode_tmap_16bit(&plan.xh_map, true, 4, x, gdim, gstr, hbox, estr)) return r;
+    if (ep.split) return two ? launch_conv<BN, 2, false, true, true>(plan, ep, stream) : launch_conv<BN, 1, false, true, true>(plan, ep, stream);
+    return two ? launch_conv<BN, 2, false, false, true>(plan, ep, stream) : launch_conv<BN, 1, false, false, true>(plan, ep, stream);
   }
   if (ep.split) return two ? launch_conv<BN, 2, false, true>(plan, ep, stream) : launch_conv<BN, 1, false, true>(plan, ep, stream);
   if (cl2) return two ? launch_conv<BN, 2, true>(plan, ep, stream) : launch_conv<BN, 1, true>(plan, ep, stream);

@@ -125,8 +125,10 @@ def test_lateral_conv_with_fused_upsample_add(n, H, W, cin, cout):
         torch.backends.cudnn.allow_tf32 = old
 
 
-def test_conv_cluster_multicast_option_is_bit_identical():
-    """Clusters of two CTAs multicasting the weight slabs (TMA multicast) must give the same bits as the plain kernel."""
+def test_conv_cluster_multicast_option_matches_the_default():
+    """Clusters of two CTAs multicasting the weight slabs (TMA multicast, one box per tap) against the default kernel (one halo
+    box per kernel column for 3x3 stride 1: the taps are added in another order, so the fp32 sums may round differently
+    before the fp16 store -- at most an fp16 ulp or two apart)."""
     from onepose_st_b200 import _lib, ops
     from onepose_st_b200.nn_common import pack_conv_f16, _cs
     g = torch.Generator(device="cuda").manual_seed(5)
@@ -143,7 +145,8 @@ def test_conv_cluster_multicast_option_is_bit_identical():
             clustered = ops.conv2d_nhwc_f16(x16, wp, 3, 1, bp, None, 1)
         finally:
             lib.opb200_conv_cluster(prev)
-        assert torch.equal(plain, clustered)
+        assert torch.allclose(plain.float(), clustered.float(), rtol=2e-3, atol=2e-3)
+        assert (plain != clustered).float().mean().item() < 0.05
 
 
 @pytest.mark.parametrize("n,H,W,cin,cout,k,stride,use_res", [(2, 32, 48, 128, 128, 3, 1, True), (1, 40, 24, 128, 196, 3, 2, False),
