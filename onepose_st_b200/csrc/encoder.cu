@@ -561,6 +561,219 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// ATTN + MERGE + LayerNorm1 of a coarse encoder layer (C = 256, split precision) in ONE launch:
+//   m <- LayerNorm1( (phi(Q) blockdiag(KV) / (phi(Q) Ksum + eps)) Wm^T )
+// The attention output of a 128-row tile never leaves the SM: per half of the heads (4 heads = 128 value columns + their
+// denominators) the product phi(Q) KV is accumulated into D_attn (tensor-memory columns 0..143), the epilogue warps scale
+// it by 1 / (denominator + eps) and rewrite it IN PLACE as bf16 hi | lo planes, and the merge projection reads it from
+// tensor memory as the A operand of its K half (same technique as mlp_fused_kernel); D_merge = columns 256..511.
+// Per tile: 2 x (4 + 4) k-blocks of 32 through the 48 KB stages of the MLP kernel; the message planes (0.4 GB written and
+// read back per layer step at 32 frames) and one launch go away.
+struct AttnMergeParams {
+  CUtensorMap q_hi, q_lo;      // [R, 256] planes, box {32, 128}, 64-byte swizzle
+  CUtensorMap kv_hi, kv_lo;    // [G * 2 * 144, 128] block-diagonal KV records, box {32, 144}
+  CUtensorMap wm_hi, wm_lo;    // [256, 256], box {32, 256}
+  const int* b_row_base;       // per m tile: first row of its group's KV records
+  EpiLN<256>::Params ln;
+  float eps;
+  int m_tile_begin, num_tiles;
+};
+constexpr int AM_KVPL = 144 * 32 * 2;  // one KV plane of a k-block: 9216 B
+
+__global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) attn_merge_kernel(const __grid_constant__ AttnMergeParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 511) & ~uintptr_t(511));
+  uint8_t* stages = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + MF_STAGES * MF_STAGE_BYTES);
+  uint64_t* empty = full + MF_STAGES;
+  uint64_t* da_full = empty + MF_STAGES;
+  uint64_t* a2_full = da_full + 1;
+  uint64_t* dm_full = a2_full + 1;
+  uint64_t* dm_empty = dm_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dm_empty + 1);
+  uint8_t* ln_scratch = smem + MF_STAGES * MF_STAGE_BYTES + 256;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int kEpiWarps = 4 * EPI_SPLIT;
+  constexpr uint32_t kDA = 0, kDM = 256;  // tensor-memory columns
+  static_assert(EPI_SPLIT == 4, "one epilogue warp per head of a half");
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&p.q_hi);
+    ptx::prefetch_tmap(&p.kv_hi);
+    ptx::prefetch_tmap(&p.wm_hi);
+    for (int s = 0; s < MF_STAGES; ++s) {
+      ptx::mbar_init(&full[s], 1);
+      ptx::mbar_init(&empty[s], 1);
+    }
+    ptx::mbar_init(da_full, 1);
+    ptx::mbar_init(a2_full, kEpiWarps);
+    ptx::mbar_init(dm_full, 1);
+    ptx::mbar_init(dm_empty, kEpiWarps);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int n_it = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer (same order as the MMA thread)
+    if (ptx::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      auto next = [&]() {
+        if (++stage == MF_STAGES) stage = 0, phase ^= 1;
+      };
+      for (int it = 0; it < n_it; ++it) {
+        const int m_tile = p.m_tile_begin + static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x);
+        const int row = m_tile * BLOCK_M;
+        const int kv_row = p.b_row_base[m_tile];
+        for (int h = 0; h < 2; ++h) {
+          for (int kb = 0; kb < 4; ++kb) {  // phi(Q)[:, 128 h ..] and the KV records of these four heads
+            ptx::mbar_wait(&empty[stage], phase ^ 1);
+            ptx::mbar_arrive_expect_tx(&full[stage], 2 * MF_APL + 2 * AM_KVPL);
+            uint8_t* st = stages + stage * MF_STAGE_BYTES;
+            ptx::tma_load_2d(st, &p.q_hi, &full[stage], h * 128 + kb * 32, row);
+            ptx::tma_load_2d(st + MF_APL, &p.q_lo, &full[stage], h * 128 + kb * 32, row);
+            ptx::tma_load_2d(st + 2 * MF_APL, &p.kv_hi, &full[stage], kb * 32, kv_row + h * 144);
+            ptx::tma_load_2d(st + 2 * MF_APL + AM_KVPL, &p.kv_lo, &full[stage], kb * 32, kv_row + h * 144);
+            next();
+          }
+          for (int kb = 0; kb < 4; ++kb) {  // the Wm columns that meet this half of the message
+            ptx::mbar_wait(&empty[stage], phase ^ 1);
+            ptx::mbar_arrive_expect_tx(&full[stage], 2 * MF_BPL);
+            uint8_t* st = stages + stage * MF_STAGE_BYTES;
+            ptx::tma_load_2d(st + 2 * MF_APL, &p.wm_hi, &full[stage], h * 128 + kb * 32, 0);
+            ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.wm_lo, &full[stage], h * 128 + kb * 32, 0);
+            next();
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (ptx::elect_one()) {
+      constexpr uint32_t idesc_a = ptx::make_idesc_bf16(BLOCK_M, 144), idesc_m = ptx::make_idesc_bf16(BLOCK_M, 256);
+      const uint32_t da = tmem_base + kDA, dm = tmem_base + kDM;
+      int stage = 0;
+      uint32_t phase = 0;
+      auto next = [&]() {
+        if (++stage == MF_STAGES) stage = 0, phase ^= 1;
+      };
+      for (int it = 0; it < n_it; ++it) {
+        for (int h = 0; h < 2; ++h) {
+          const uint32_t u1 = static_cast<uint32_t>(2 * it + h);
+          // (D_attn is free: the merge MMAs that read it as their A operand were issued before these and run before them)
+          for (int kb = 0; kb < 4; ++kb) {
+            ptx::mbar_wait(&full[stage], phase);
+            ptx::tc_fence_after();
+            const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
+            const uint64_t a_hi = ptx::make_desc_sw64(sa), a_lo = ptx::make_desc_sw64(sa + MF_APL);
+            const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + AM_KVPL);
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(da, a_hi + 2 * k, b_hi + 2 * k, idesc_a, !(kb == 0 && k == 0));
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(da, a_lo + 2 * k, b_hi + 2 * k, idesc_a, 1);
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(da, a_hi + 2 * k, b_lo + 2 * k, idesc_a, 1);
+            ptx::mma_commit(&empty[stage]);
+            next();
+          }
+          ptx::mma_commit(da_full);
+          if (h == 0) ptx::mbar_wait(dm_empty, (static_cast<uint32_t>(it) & 1) ^ 1);  // the previous tile's output has been read
+          ptx::mbar_wait(a2_full, u1 & 1);  // this half of the message is in tensor memory as bf16 planes
+          ptx::tc_fence_after();
+          for (int kb = 0; kb < 4; ++kb) {
+            ptx::mbar_wait(&full[stage], phase);
+            ptx::tc_fence_after();
+            const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
+            const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + MF_BPL);
+            const uint32_t a_hi = tmem_base + kDA + 16 * kb, a_lo = a_hi + 64;
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(dm, a_hi + 8 * k, b_hi + 2 * k, idesc_m, !(h == 0 && kb == 0 && k == 0));
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(dm, a_lo + 8 * k, b_hi + 2 * k, idesc_m, 1);
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(dm, a_hi + 8 * k, b_lo + 2 * k, idesc_m, 1);
+            ptx::mma_commit(&empty[stage]);
+            next();
+          }
+        }
+        ptx::mma_commit(dm_full);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps: (head of the half, TMEM lane quarter)
+    EpiCtx ctx;
+    ctx.quarter = warp & 3;
+    ctx.lane = lane;
+    ctx.epi_warp = (warp - 2) & 3;
+    ctx.group = 0;
+    ctx.part = (warp - 2) >> 2;
+    ctx.n_tile = 0;
+    ctx.scratch = ln_scratch;
+    ctx.scratch_small = 1;
+    const uint32_t lane_field = static_cast<uint32_t>(ctx.quarter * 32) << 16;
+    const int bar_id = 1 + ctx.quarter;  // the four warps (heads) of a TMEM lane quarter
+    for (int it = 0; it < n_it; ++it) {
+      for (int h = 0; h < 2; ++h) {
+        const uint32_t u1 = static_cast<uint32_t>(2 * it + h);
+        ptx::mbar_wait(da_full, u1 & 1);
+        ptx::tc_fence_after();
+        const uint32_t base = tmem_base + kDA + lane_field;
+        uint32_t hh[16], ll[16];
+        {
+          uint32_t dr[16];
+          ptx::tmem_ld16(base + 128, dr);
+          ptx::tmem_ld_wait();
+          float den = __uint_as_float(dr[0]);
+          den = ctx.part == 1 ? __uint_as_float(dr[1]) : den;
+          den = ctx.part == 2 ? __uint_as_float(dr[2]) : den;
+          den = ctx.part == 3 ? __uint_as_float(dr[3]) : den;
+          const float z = 1.0f / (den + p.eps);
+          float v[32];
+          load_acc32(base + ctx.part * 32, v);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            __nv_bfloat16 h0, l0, h1, l1;
+            split_bf16(v[2 * i] * z, h0, l0);
+            split_bf16(v[2 * i + 1] * z, h1, l1);
+            hh[i] = pack_bf16(h0, h1);
+            ll[i] = pack_bf16(l0, l1);
+          }
+        }
+        ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);  // the four heads' columns have all been read: the planes may land
+        ptx::tmem_st16(base + ctx.part * 16, hh);
+        ptx::tmem_st16(base + 64 + ctx.part * 16, ll);
+        ptx::tmem_st_wait();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(a2_full);
+      }
+      ctx.m_tile = p.m_tile_begin + static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x);
+      ptx::mbar_wait(dm_full, static_cast<uint32_t>(it) & 1);
+      ptx::tc_fence_after();
+      ctx.tmem_acc = tmem_base + kDM + lane_field;
+      EpiLN<256>::run(p.ln, ctx);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(dm_empty);
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
 constexpr int KV_ROWS_PER_BLOCK = 128;
 constexpr int KV_REC = 33;  // per (head, d): 32 KV values + Ksum
 
@@ -1234,6 +1447,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     }
   }
   // ---- 2-4. attention
+  bool merge_done = false;  // attn_merge_kernel has run MERGE + LN1 as well
   if (g.big) {
     if constexpr (C == 256) {
       GroupTable gt;
@@ -1277,6 +1491,30 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       }
       count_launch(2);
       OPB_CHECK_CUDA(cudaGetLastError());
+      // OPB200_ATTN_MERGE_FUSED = 0 / 1 forces the separate launches / the fused kernel; unset: fused from two tiles per CTA on
+      static const int am_env = getenv("OPB200_ATTN_MERGE_FUSED") ? atoi(getenv("OPB200_ATTN_MERGE_FUSED")) : -1;
+      if (x3 && (am_env >= 0 ? am_env != 0 : qc >= kMlpFusedMinRounds * num_sms())) {
+        AttnMergeParams ap;
+        PlanBuilder tb(true);
+        int r;
+        if ((r = tb.make(&ap.q_hi, w.qh, R, C, C, BLOCK_M))) return r;
+        if ((r = tb.make(&ap.q_lo, w.ql, R, C, C, BLOCK_M))) return r;
+        if ((r = tb.make(&ap.kv_hi, w.kvb_h, static_cast<uint64_t>(g.G) * 2 * 144, 128, 128, 144))) return r;
+        if ((r = tb.make(&ap.kv_lo, w.kvb_l, static_cast<uint64_t>(g.G) * 2 * 144, 128, 128, 144))) return r;
+        if ((r = tb.make(&ap.wm_hi, lw.m_hi, C, C, C, 256))) return r;
+        if ((r = tb.make(&ap.wm_lo, lw.m_lo, C, C, C, 256))) return r;
+        ap.b_row_base = cross ? w.base_cross : w.base_self;
+        ap.ln = typename EpiLN<256>::Params{lw.ln1_g, lw.ln1_b, w.mh, w.ml};
+        ap.eps = 1e-6f;
+        ap.m_tile_begin = qb, ap.num_tiles = qc;
+        static std::atomic<unsigned long long> configured_am{0};
+        if (int rr = opt_in_dyn_smem(attn_merge_kernel, MF_SMEM, configured_am)) return rr;
+        const int grid = qc < num_sms() ? qc : num_sms();
+        attn_merge_kernel<<<grid, 64 + 128 * EPI_SPLIT, MF_SMEM, stream>>>(ap);
+        count_launch();
+        OPB_CHECK_CUDA(cudaGetLastError());
+        merge_done = true;
+      } else {
       PlanBuilder pb;
       pb.add_a(w.qh, R, C, C, 0);
       pb.add_b(w.kvb_h, static_cast<uint64_t>(g.G) * 2 * 144, 128, 128, 0, 144);
@@ -1299,6 +1537,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
       pb.plan.b_row_base = cross ? w.base_cross : w.base_self;
       EpiAttn::Params ep{w.aoh, x3 ? w.aol : nullptr, 1e-6f};
       if (int r = launch_gemm<144, 4, 1, EpiAttn, EPI_SPLIT>(pb.plan, ep, stream)) return r;
+      }
     } else {
       set_last_error("big-group attention is implemented for d_model 256 only");
       return OPB_ERR_ARG;
@@ -1326,7 +1565,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
   }
   const int ub = qb, uc = qc;  // only the tiles of the streams being updated run the row-wise GEMMs
   // ---- 5. MERGE + LN1
-  {
+  if (!merge_done) {
     PlanBuilder pb(x3);
     pb.add_a(w.aoh, R, C, C, 0);
     pb.add_b(lw.m_hi, C, C, C, 0, C);

@@ -1,6 +1,7 @@
 """GPU parity of the code paths that are selected per process by an environment switch (read once by the library):
 the fused MLP kernel of the coarse encoder layer (OPB200_MLP_FUSED=1 forces it -- by default it runs from two tiles per
-CTA on, i.e. not at most test shapes -- and =0 forces the two-launch path it replaced) and the CUDA-core KV kernel that
+CTA on, i.e. not at most test shapes -- and =0 forces the two-launch path it replaced), the fused ATTN + MERGE + LayerNorm1 kernel of the coarse level
+(OPB200_ATTN_MERGE_FUSED, same convention) and the CUDA-core KV kernel that
 the tensor-core one replaced (OPB200_KV_TC=0); the per-tap convolution kernels that the halo kernels replaced for 3x3 stride 1
 (OPB200_CONV_HALO=0).  Each variant runs the encoder / model parity tests in a child process."""
 import os
@@ -14,8 +15,9 @@ pytestmark = pytest.mark.gpu
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("env", [{"OPB200_MLP_FUSED": "1"}, {"OPB200_MLP_FUSED": "0"}, {"OPB200_KV_TC": "0"}],
-                         ids=["mlp_fused", "mlp_two_launches", "kv_cuda_cores"])
+@pytest.mark.parametrize("env", [{"OPB200_MLP_FUSED": "1"}, {"OPB200_MLP_FUSED": "0"}, {"OPB200_KV_TC": "0"},
+                                 {"OPB200_ATTN_MERGE_FUSED": "1", "OPB200_MLP_FUSED": "1"}, {"OPB200_ATTN_MERGE_FUSED": "0"}],
+                         ids=["mlp_fused", "mlp_two_launches", "kv_cuda_cores", "attn_merge_fused", "attn_merge_separate"])
 def test_encoder_variant_passes_the_parity_tests(env):
     res = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", "-p", "no:cacheprovider",
                           os.path.join(REPO, "tests", "test_gpu_transformer.py"),
