@@ -381,6 +381,7 @@ struct SimFastParams {
   int* needs_robust;        // SCREEN: bit 1 <- the bound does not allow screening (the caller repeats with algo 2)
   long long* trace; // debug (opb200_debug_trace): per CTA and every fourth tile {MMA issue start, MMA issued, accumulator
                     // seen full by one epilogue warp of its stage, last release among the stage's four warps} SM-clock stamps
+  int pair;         // SCREEN: tiles (n even, n + 1) of a row share 128 x 256 x 16 MMAs (see the MMA issuer)
   int debug;        // OPB200_SIM_DEBUG timing experiments (results are garbage): 1 = epilogue warps only hand the accumulators back,
                     // 2 = no MMAs are issued, 3 = epilogue reads TMEM only, 4 = epilogue arithmetic without the TMEM reads,
                     // 6 = mode 1 without the B loads (MMAs on whatever the stages hold), 7 = mode 1 without the MMAs (TMA alone),
@@ -737,6 +738,8 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
   uint64_t* tfull = b_empty + FAST_BSTAGES;  // TSTAGES
   uint64_t* tempty = tfull + TSTAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + TSTAGES);
+  uint64_t* pfull = bars + 16;   // SCREEN, pair mode: one barrier pair per k-block slot of the B region
+  uint64_t* pempty = bars + 20;
   // SCREEN: which tile an accumulator stage holds -- (m_tile, n_tile, position in the CTA's list, -) written by the MMA
   // thread before it issues the tile; m_tile < 0 tells the stage's epilogue group that the list is exhausted
   volatile int4* tile_slot = reinterpret_cast<volatile int4*>(reinterpret_cast<uint8_t*>(bars) + 256);
@@ -775,6 +778,12 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
       ptx::mbar_init(&tfull[g], 1);
       ptx::mbar_init(&tempty[g], 4 * HALVES);
     }
+    if (SCREEN) {
+      for (int kb = 0; kb < 4; ++kb) {
+        ptx::mbar_init(&pfull[kb], 1);
+        ptx::mbar_init(&pempty[kb], 1);
+      }
+    }
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -799,6 +808,36 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
       int m_tile = m_first, n_tile = n_first;
       int b_row0 = (m_tile / tiles_per_batch) * p.Sp, mt_in_batch = m_tile % tiles_per_batch;
       bool new_a = true;
+      if (SCREEN && p.pair) {
+        // pair mode: the B region is four k-block slots of [256 rows x 128 B]: rows 0..127 = tile n, 128..255 = tile n + 1
+        uint32_t unit = 0;
+        for (int t = t_begin; t < t_end; ++unit) {
+          if (new_a) {
+            ptx::mbar_wait(a_empty, a_phase ^ 1);
+            ptx::mbar_arrive_expect_tx(a_full, FAST_A_BYTES);
+#pragma unroll
+            for (int kb = 0; kb < FAST_KB; ++kb) ptx::tma_load_2d(smem_a + kb * FAST_SUB, &p.a_hi, a_full, kb * BLOCK_K, m_tile * BLOCK_M);
+            a_phase ^= 1;
+            new_a = false;
+          }
+          const bool pr = (n_tile & 1) == 0 && t + 1 < t_end;
+          const int b_row = b_row0 + n_tile * SIM_BN;
+#pragma unroll
+          for (int kb = 0; kb < FAST_KB; ++kb) {
+            ptx::mbar_wait(&pempty[kb], (unit & 1u) ^ 1u);
+            ptx::mbar_arrive_expect_tx(&pfull[kb], pr ? 2 * FAST_SUB : FAST_SUB);
+            ptx::tma_load_2d(smem_b + kb * (2 * FAST_SUB), &p.b_hi, &pfull[kb], kb * BLOCK_K, b_row);
+            if (pr) ptx::tma_load_2d(smem_b + kb * (2 * FAST_SUB) + FAST_SUB, &p.b_hi, &pfull[kb], kb * BLOCK_K, b_row + SIM_BN);
+          }
+          const int adv = pr ? 2 : 1;
+          t += adv;
+          n_tile += adv;
+          if (n_tile == p.n_tiles) {
+            n_tile = 0, ++m_tile, new_a = true;
+            if (++mt_in_batch == tiles_per_batch) mt_in_batch = 0, b_row0 += p.Sp;
+          }
+        }
+      } else
       for (int t = t_begin; t < t_end; ++t) {
         if (new_a) {
           ptx::mbar_wait(a_empty, a_phase ^ 1);
@@ -905,6 +944,73 @@ __global__ void __launch_bounds__(64 + 128 * FAST_GROUPS, 1) sim_fast_kernel(con
             __nanosleep(32);  // every stage is with its epilogue group: the operand reads of the MMAs in flight want the shared-memory port
           }
         };
+        if (p.pair) {
+          // Pair mode: tiles (n even, n + 1) of a row go to an adjacent pair of accumulator stages (0, 1) or (2, 3) with
+          // 128 x 256 x 16 MMAs -- 4 KB of A + 8 KB of B per 128 clk of tensor work (96 B/clk) where two 128-wide MMAs read
+          // 8 KB each per 64 clk (128 B/clk, all an SM's shared memory delivers while the TMA refills the ring through the
+          // same port).  A tile without a partner (odd start or end of the CTA's list) takes any free stage with 128-wide MMAs
+          // on the first half of the slots.
+          constexpr uint32_t idesc2 = ptx::make_idesc_f16(BLOCK_M, 2 * BN);
+          uint32_t unit = 0;
+          int lastp = 1;
+          for (int it = 0; it < n_it; ++unit) {
+            if (new_a) {
+              ptx::mbar_wait(a_full, a_phase);
+              a_phase ^= 1;
+              new_a = false;
+            }
+            const bool pr = (n_tile & 1) == 0 && it + 1 < n_it;
+            if (pr) {
+              uint32_t spins = 0;
+              for (;;) {
+                bool got = false;
+#pragma unroll
+                for (int q = 1; q <= 2; ++q) {
+                  const int pp = (lastp + q) & 1;
+                  if (ptx::mbar_test_wait(&tempty[2 * pp], (te_par >> (2 * pp)) & 1u) &&
+                      ptx::mbar_test_wait(&tempty[2 * pp + 1], (te_par >> (2 * pp + 1)) & 1u)) {
+                    lastp = pp;
+                    te_par ^= 3u << (2 * pp);
+                    got = true;
+                    break;
+                  }
+                }
+                if (got) break;
+                if (++spins > (1u << 24)) __trap();
+                __nanosleep(32);
+              }
+              g = 2 * lastp + 1;  // (the round-robin of the single tiles continues behind the pair)
+            } else {
+              take_stage();
+            }
+            ptx::tc_fence_after();
+            const int g0 = pr ? 2 * lastp : g;
+            ptx::st_shared_v4(slot_a + 16 * g0, m_tile, n_tile, it, 0);
+            if (pr) ptx::st_shared_v4(slot_a + 16 * (g0 + 1), m_tile, n_tile + 1, it + 1, 0);
+            const bool tr = trace_on && (it & 3) == 0 && (it >> 2) < kTraceTilesPerCta;
+            if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 0] = clock64();
+            const uint32_t d_tmem = tmem_base + g0 * BN;
+#pragma unroll
+            for (int kb = 0; kb < FAST_KB; ++kb) {
+              ptx::mbar_wait(&pfull[kb], unit & 1u);
+              ptx::tc_fence_after();
+#pragma unroll
+              for (int k = 0; k < BLOCK_K / 16; ++k)
+                ptx::mma_bf16(d_tmem, a_desc0 + static_cast<uint64_t>(kb * (FAST_SUB >> 4) + 2 * k),
+                              b_desc0 + static_cast<uint64_t>(kb * ((2 * FAST_SUB) >> 4) + 2 * k), pr ? idesc2 : idesc, (kb | k) != 0);
+              ptx::mma_commit(&pempty[kb]);
+            }
+            ptx::mma_commit(&tfull[g0]);
+            if (pr) ptx::mma_commit(&tfull[g0 + 1]);
+            if (tr) p.trace[(blockIdx.x * kTraceTilesPerCta + (it >> 2)) * 4 + 1] = clock64();
+            const int adv = pr ? 2 : 1;
+            it += adv;
+            n_tile += adv;
+            const bool last_n = n_tile == p.n_tiles;
+            if (last_n || it >= n_it) ptx::mma_commit(a_empty);
+            if (last_n) n_tile = 0, ++m_tile, new_a = true;
+          }
+        } else
         for (int it0 = 0; it0 < n_it; it0 += 2) {
 #pragma unroll
           for (int u = 0; u < 2; ++u) {
@@ -2284,6 +2390,8 @@ static int coarse_match_impl(const float* feat_a, const float* feat_b, const voi
     fp.lim_scale = g_screen_lim_scale;
     fp.cand_tag = screen ? 2 : 1;
     fp.trace = next_trace_slot(num_sms());
+    static const int pair_env = getenv("OPB200_SIM_PAIR") ? atoi(getenv("OPB200_SIM_PAIR")) : 0;
+    fp.pair = screen && pair_env != 0 && fp.n_tiles % 2 == 0 ? 1 : 0;
     fp.debug = dbg;
     fp.rowpart = reinterpret_cast<float*>(w.rowpart), fp.colpart = reinterpret_cast<float*>(w.colpart);
     fp.tile_ref = w.tile_ref;

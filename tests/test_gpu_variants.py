@@ -35,3 +35,13 @@ def test_per_tap_convolution_kernels_pass_the_backbone_tests():
     tail = (res.stdout + res.stderr)[-1500:]
     assert res.returncode == 0, tail
     assert " passed" in res.stdout and " failed" not in res.stdout, tail
+
+
+def test_sweep_pair_mode_passes_the_coarse_tests():
+    """OPB200_SIM_PAIR=1: pairs of tiles on 128 x 256 MMAs in the CoarseMatching sweep (measured no faster, kept selectable)."""
+    res = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", "-p", "no:cacheprovider",
+                          os.path.join(REPO, "tests", "test_gpu_coarse.py")],
+                         cwd=REPO, env=dict(os.environ, OPB200_SIM_PAIR="1"), capture_output=True, text=True, timeout=900)
+    tail = (res.stdout + res.stderr)[-1500:]
+    assert res.returncode == 0, tail
+    assert " passed" in res.stdout and " failed" not in res.stdout, tail
