@@ -352,6 +352,12 @@ struct MlpFusedParams {
   CUtensorMap w2_hi, w2_lo;            // [C, 2C], box {32, C}
   typename EpiLNRes<C>::Params ln;
   int m_tile_begin, num_tiles;
+  // phase 0 (C = 128 only, 128 columns of tensor memory are free there): msg = LayerNorm1(attn_out Wm^T) is computed in
+  // the kernel and handed to phase 1 IN TENSOR MEMORY as the A operand of the msg half of K; m_hi / m_lo are not read
+  int phase0;
+  CUtensorMap ao_hi, ao_lo;  // [R, C] attention output planes, box {32, 128}
+  CUtensorMap wm_hi, wm_lo;  // [C, C], box {32, C}
+  const float *ln1_g, *ln1_b;
 };
 
 // Tensor memory: D1 = columns 0..255 (one 256-wide half of the hidden tile, fp32), D2 = columns 256..511 (the output).
@@ -378,12 +384,16 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
   uint64_t* a2_full = d1_full + 1;  // [2]: quarters a, b
   uint64_t* d2_full = a2_full + 2;
   uint64_t* d2_empty = d2_full + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d2_empty + 1);
+  uint64_t* d0_full = d2_empty + 1;
+  uint64_t* m_full = d0_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(m_full + 1);
   uint8_t* ln_scratch = smem + MF_STAGES * MF_STAGE_BYTES + 256;
-  static_assert((2 * MF_STAGES + 5) * 8 + 4 <= 256, "barrier block");
+  static_assert((2 * MF_STAGES + 7) * 8 + 4 <= 256, "barrier block");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int kEpiWarps = 4 * EPI_SPLIT;
-  constexpr uint32_t kD1 = 0, kD2 = 256;  // tensor-memory columns
+  constexpr uint32_t kD1 = 0, kD2 = 256, kD0 = 384;  // tensor-memory columns (D0 / msg operand: phase 0, C = 128)
+  constexpr int B0PL = C * 32 * 2;  // one Wm plane of a k-block (phase 0)
+  const bool phase0 = C == 128 && p.phase0 != 0;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.x_hi);
@@ -398,6 +408,8 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
     ptx::mbar_init(&a2_full[1], kEpiWarps);
     ptx::mbar_init(d2_full, 1);
     ptx::mbar_init(d2_empty, kEpiWarps);
+    ptx::mbar_init(d0_full, 1);
+    ptx::mbar_init(m_full, kEpiWarps);
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -422,13 +434,28 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
       for (int u = 0; u < U; ++u) {
         const int row = (p.m_tile_begin + static_cast<int>(blockIdx.x) + (u / HALVES) * static_cast<int>(gridDim.x)) * BLOCK_M;
         const int half = u % HALVES;
+        if (phase0) {
+          for (int kb = 0; kb < C / 32; ++kb) {  // phase 0: the attention output and Wm
+            ptx::mbar_wait(&empty[stage], phase ^ 1);
+            ptx::mbar_arrive_expect_tx(&full[stage], 2 * MF_APL + 2 * B0PL);
+            uint8_t* st = stages + stage * MF_STAGE_BYTES;
+            ptx::tma_load_2d(st, &p.ao_hi, &full[stage], kb * 32, row);
+            ptx::tma_load_2d(st + MF_APL, &p.ao_lo, &full[stage], kb * 32, row);
+            ptx::tma_load_2d(st + 2 * MF_APL, &p.wm_hi, &full[stage], kb * 32, 0);
+            ptx::tma_load_2d(st + 2 * MF_APL + B0PL, &p.wm_lo, &full[stage], kb * 32, 0);
+            next();
+          }
+        }
         for (int kb = 0; kb < KB1; ++kb) {  // phase 1: [x | msg] and the W1 slab of this half
           ptx::mbar_wait(&empty[stage], phase ^ 1);
-          ptx::mbar_arrive_expect_tx(&full[stage], MF_STAGE_BYTES);
+          const bool a_tm = phase0 && kb >= C / 32;  // the msg half of K comes from tensor memory
+          ptx::mbar_arrive_expect_tx(&full[stage], a_tm ? 2 * MF_BPL : MF_STAGE_BYTES);
           uint8_t* st = stages + stage * MF_STAGE_BYTES;
           const int ka = (kb % (C / 32)) * 32;
-          ptx::tma_load_2d(st, kb < C / 32 ? &p.x_hi : &p.m_hi, &full[stage], ka, row);
-          ptx::tma_load_2d(st + MF_APL, kb < C / 32 ? &p.x_lo : &p.m_lo, &full[stage], ka, row);
+          if (!a_tm) {
+            ptx::tma_load_2d(st, kb < C / 32 ? &p.x_hi : &p.m_hi, &full[stage], ka, row);
+            ptx::tma_load_2d(st + MF_APL, kb < C / 32 ? &p.x_lo : &p.m_lo, &full[stage], ka, row);
+          }
           ptx::tma_load_2d(st + 2 * MF_APL, &p.w1_hi, &full[stage], kb * 32, half * 256);
           ptx::tma_load_2d(st + 2 * MF_APL + MF_BPL, &p.w1_lo, &full[stage], kb * 32, half * 256);
           next();
@@ -456,19 +483,56 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
       for (int u = 0; u < U; ++u) {
         const int half = u % HALVES;
         const uint32_t u1 = static_cast<uint32_t>(u);
+        if (phase0) {
+          // phase 0: D0 = attn_out Wm^T (N = C); the warps normalise it under the x half of phase 1.  (D0 is free: the MMAs
+          // of the previous tile that read the msg operand from these columns were issued before these.)
+          constexpr uint32_t idesc0 = ptx::make_idesc_bf16(BLOCK_M, C);
+          const uint32_t d0 = tmem_base + kD0;
+          for (int kb = 0; kb < C / 32; ++kb) {
+            ptx::mbar_wait(&full[stage], phase);
+            ptx::tc_fence_after();
+            const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
+            const uint64_t a_hi = ptx::make_desc_sw64(sa), a_lo = ptx::make_desc_sw64(sa + MF_APL);
+            const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + B0PL);
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(d0, a_hi + 2 * k, b_hi + 2 * k, idesc0, !(kb == 0 && k == 0));
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(d0, a_lo + 2 * k, b_hi + 2 * k, idesc0, 1);
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(d0, a_hi + 2 * k, b_lo + 2 * k, idesc0, 1);
+            ptx::mma_commit(&empty[stage]);
+            next();
+          }
+          ptx::mma_commit(d0_full);
+        }
         // (D1 is free: G2 of the previous half was issued after the warps had read and rewritten it, and runs before this)
         for (int kb = 0; kb < KB1; ++kb) {
+          const bool a_tm = phase0 && kb >= C / 32;
+          if (a_tm && kb == C / 32) {
+            ptx::mbar_wait(m_full, u1 & 1);  // LayerNorm1(D0) is in tensor memory as bf16 planes
+            ptx::tc_fence_after();
+          }
           ptx::mbar_wait(&full[stage], phase);
           ptx::tc_fence_after();
           const uint32_t sa = ptx::smem_u32(stages + stage * MF_STAGE_BYTES);
-          const uint64_t a_hi = ptx::make_desc_sw64(sa), a_lo = ptx::make_desc_sw64(sa + MF_APL);
           const uint64_t b_hi = ptx::make_desc_sw64(sa + 2 * MF_APL), b_lo = ptx::make_desc_sw64(sa + 2 * MF_APL + MF_BPL);
+          if (a_tm) {
+            const uint32_t a_hi = tmem_base + kD0 + 16 * (kb - C / 32), a_lo = a_hi + 64;
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_hi + 2 * k, idesc, !(kb == 0 && k == 0));
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d1, a_hi + 8 * k, b_hi + 2 * k, idesc, 1);
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_lo + 2 * k, b_hi + 2 * k, idesc, 1);
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d1, a_lo + 8 * k, b_hi + 2 * k, idesc, 1);
 #pragma unroll
-          for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_lo + 2 * k, idesc, 1);
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16_ta(d1, a_hi + 8 * k, b_lo + 2 * k, idesc, 1);
+          } else {
+            const uint64_t a_hi = ptx::make_desc_sw64(sa), a_lo = ptx::make_desc_sw64(sa + MF_APL);
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_hi + 2 * k, idesc, !(kb == 0 && k == 0));
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_lo + 2 * k, b_hi + 2 * k, idesc, 1);
+#pragma unroll
+            for (int k = 0; k < 2; ++k) ptx::mma_bf16(d1, a_hi + 2 * k, b_lo + 2 * k, idesc, 1);
+          }
           ptx::mma_commit(&empty[stage]);
           next();
         }
@@ -511,6 +575,35 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) mlp_fused_kernel(cons
     const int bar_id = 1 + ctx.quarter;  // the four warps (column parts) of a TMEM lane quarter
     for (int u = 0; u < U; ++u) {
       const uint32_t u1 = static_cast<uint32_t>(u);
+      if constexpr (C == 128) {
+        if (phase0) {  // msg = LayerNorm1(D0): this warp's 32 columns of its rows, back into D0's columns as bf16 hi | lo planes
+          ptx::mbar_wait(d0_full, u1 & 1);
+          ptx::tc_fence_after();
+          const uint32_t base0 = tmem_base + kD0 + lane_field;
+          float x[32];
+          load_acc32(base0 + ctx.part * 32, x);
+          float mean, rstd;
+          row_mean_rstd_split<32>(ctx, x, C, mean, rstd);  // (its barriers: every column of these lanes has been read)
+          uint32_t h[16], l[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int c0 = ctx.part * 32 + 2 * i;
+            const float y0 = (x[2 * i] - mean) * rstd * __ldg(p.ln1_g + c0) + __ldg(p.ln1_b + c0);
+            const float y1 = (x[2 * i + 1] - mean) * rstd * __ldg(p.ln1_g + c0 + 1) + __ldg(p.ln1_b + c0 + 1);
+            __nv_bfloat16 h0, l0, h1, l1;
+            split_bf16(y0, h0, l0);
+            split_bf16(y1, h1, l1);
+            h[i] = pack_bf16(h0, h1);
+            l[i] = pack_bf16(l0, l1);
+          }
+          ptx::tmem_st16(base0 + ctx.part * 16, h);
+          ptx::tmem_st16(base0 + 64 + ctx.part * 16, l);
+          ptx::tmem_st_wait();
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(m_full);
+        }
+      }
       ptx::mbar_wait(d1_full, u1 & 1);
       ptx::tc_fence_after();
 #pragma unroll 1
@@ -1564,8 +1657,15 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     }
   }
   const int ub = qb, uc = qc;  // only the tiles of the streams being updated run the row-wise GEMMs
+  // OPB200_MLP_FUSED = 0 / 1 forces the two-launch / the fused path; unset: fused when the CTAs get kMlpFusedMinRounds tiles
+  // each or more (a CTA's tiles run back to back, so a short list ends in a round that is mostly empty)
+  static const int mlp_fused_env = getenv("OPB200_MLP_FUSED") ? atoi(getenv("OPB200_MLP_FUSED")) : -1;
+  const bool mlp_fused = mlp_fused_env >= 0 ? mlp_fused_env != 0 : uc >= kMlpFusedMinRounds * num_sms();
+  // fine level: MERGE + LN1 run inside the fused MLP kernel as its phase 0 (OPB200_MLP_PHASE0=0: as a launch of their own)
+  static const bool phase0_env = getenv("OPB200_MLP_PHASE0") ? atoi(getenv("OPB200_MLP_PHASE0")) != 0 : true;
+  const bool phase0 = C == 128 && mlp_fused && x3 && !merge_done && phase0_env;
   // ---- 5. MERGE + LN1
-  if (!merge_done) {
+  if (!merge_done && !phase0) {
     PlanBuilder pb(x3);
     pb.add_a(w.aoh, R, C, C, 0);
     pb.add_b(lw.m_hi, C, C, C, 0, C);
@@ -1585,11 +1685,7 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
                    : launch_gemm<C, (C == 256 ? 4 : 6), 1, EpiLN<C>, EPI_SPLIT>(pb.plan, ep, stream))
       return r;
   }
-  // ---- 6 + 7 in one launch (coarse level, split precision): the hidden tile stays on the SM
-  // OPB200_MLP_FUSED = 0 / 1 forces the two-launch / the fused path; unset: fused when the CTAs get kMlpFusedMinRounds tiles
-  // each or more (a CTA's tiles run back to back, so a short list ends in a round that is mostly empty)
-  static const int mlp_fused_env = getenv("OPB200_MLP_FUSED") ? atoi(getenv("OPB200_MLP_FUSED")) : -1;
-  const bool mlp_fused = mlp_fused_env >= 0 ? mlp_fused_env != 0 : uc >= kMlpFusedMinRounds * num_sms();
+  // ---- 6 + 7 in one launch (split precision): the hidden tile stays on the SM
   if (mlp_fused && x3) {
     MlpFusedParams<C> fp;
     PlanBuilder tb(true);
@@ -1604,6 +1700,17 @@ static int run_step(const Geometry& g, const Workspace& w, const LayerWeights& l
     if ((r = tb.make(&fp.w2_lo, lw.w2_lo, C, 2 * C, 2 * C, C))) return r;
     fp.ln = typename EpiLNRes<C>::Params{lw.ln2_g, lw.ln2_b, w.xh, w.xl};
     fp.m_tile_begin = ub, fp.num_tiles = uc;
+    fp.phase0 = phase0 ? 1 : 0;
+    fp.ln1_g = lw.ln1_g, fp.ln1_b = lw.ln1_b;
+    if (phase0) {
+      if ((r = tb.make(&fp.ao_hi, w.aoh, R, C, C, BLOCK_M))) return r;
+      if ((r = tb.make(&fp.ao_lo, w.aol, R, C, C, BLOCK_M))) return r;
+      if ((r = tb.make(&fp.wm_hi, lw.m_hi, C, C, C, C))) return r;
+      if ((r = tb.make(&fp.wm_lo, lw.m_lo, C, C, C, C))) return r;
+    } else {
+      fp.ao_hi = fp.ao_lo = fp.x_hi;
+      fp.wm_hi = fp.wm_lo = fp.w2_hi;
+    }
     if (uc > 0) {
       static std::atomic<unsigned long long> configured_mf{0};
       if (int rr = opt_in_dyn_smem(mlp_fused_kernel<C>, MF_SMEM, configured_mf)) return rr;

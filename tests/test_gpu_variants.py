@@ -16,8 +16,10 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.mark.parametrize("env", [{"OPB200_MLP_FUSED": "1"}, {"OPB200_MLP_FUSED": "0"}, {"OPB200_KV_TC": "0"},
-                                 {"OPB200_ATTN_MERGE_FUSED": "1", "OPB200_MLP_FUSED": "1"}, {"OPB200_ATTN_MERGE_FUSED": "0"}],
-                         ids=["mlp_fused", "mlp_two_launches", "kv_cuda_cores", "attn_merge_fused", "attn_merge_separate"])
+                                 {"OPB200_ATTN_MERGE_FUSED": "1", "OPB200_MLP_FUSED": "1"}, {"OPB200_ATTN_MERGE_FUSED": "0"},
+                                 {"OPB200_MLP_FUSED": "1", "OPB200_MLP_PHASE0": "0"}],
+                         ids=["mlp_fused", "mlp_two_launches", "kv_cuda_cores", "attn_merge_fused", "attn_merge_separate",
+                              "mlp_fused_without_phase0"])
 def test_encoder_variant_passes_the_parity_tests(env):
     res = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", "-p", "no:cacheprovider",
                           os.path.join(REPO, "tests", "test_gpu_transformer.py"),
