@@ -4,8 +4,11 @@
 Workload (BASELINE.json configs[1]): spot_demo-shaped synthetic sequence -- 512x512 query frames against one
 8k-point 3D model, random-init weights of the reference architecture (calibrated + planted so that matches
 exist, onepose_st_b200/synthetic.py), frames sharded round-robin over the GPUs (weak scaling: every rank
-processes ``--frames-per-step`` frames per step), matches gathered once at the end over NCCL.  Every timed
-region is repeated ``--repeats`` times (the JSON line carries the median; all repeats are in ``diag``).
+processes ``--frames-per-step`` frames per step, ``--batch`` = 32 of them per forward call: every kernel of the path has
+a fixed cost per launch -- ~30 us for the CoarseMatching sweep -- that larger forwards amortise: 1211 -> 1239 frames/s and
+0.536 -> 0.612 of the sweep's roofline from 8 to 32 frames per forward on one box), matches gathered once at the end over
+NCCL.  Every timed region is repeated ``--repeats`` times after one untimed region of the same shape (the JSON line
+carries the median; all repeats are in ``diag``).
 
 Besides the headline the line carries: ``parity`` (the timed configuration checked frame by frame against the CPU
 oracle on the same inputs), ``contract_grade`` (the end-to-end arm and the parity check repeated with the fp32-grade
