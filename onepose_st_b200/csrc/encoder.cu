@@ -814,50 +814,79 @@ __global__ void __launch_bounds__(64 + 128 * EPI_SPLIT, 1) attn_merge_kernel(con
     ctx.scratch_small = 1;
     const uint32_t lane_field = static_cast<uint32_t>(ctx.quarter * 32) << 16;
     const int bar_id = 1 + ctx.quarter;  // the four warps (heads) of a TMEM lane quarter
-    for (int it = 0; it < n_it; ++it) {
-      for (int h = 0; h < 2; ++h) {
-        const uint32_t u1 = static_cast<uint32_t>(2 * it + h);
-        ptx::mbar_wait(da_full, u1 & 1);
-        ptx::tc_fence_after();
-        const uint32_t base = tmem_base + kDA + lane_field;
-        uint32_t hh[16], ll[16];
-        {
-          uint32_t dr[16];
-          ptx::tmem_ld16(base + 128, dr);
-          ptx::tmem_ld_wait();
-          float den = __uint_as_float(dr[0]);
-          den = ctx.part == 1 ? __uint_as_float(dr[1]) : den;
-          den = ctx.part == 2 ? __uint_as_float(dr[2]) : den;
-          den = ctx.part == 3 ? __uint_as_float(dr[3]) : den;
-          const float z = 1.0f / (den + p.eps);
-          float v[32];
-          load_acc32(base + ctx.part * 32, v);
+    auto convert = [&](int it, int h) {  // e(it, h): D_attn -> scaled bf16 planes in place
+      const uint32_t u1 = static_cast<uint32_t>(2 * it + h);
+      ptx::mbar_wait(da_full, u1 & 1);
+      ptx::tc_fence_after();
+      const uint32_t base = tmem_base + kDA + lane_field;
+      uint32_t hh[16], ll[16];
+      {
+        uint32_t dr[16];
+        ptx::tmem_ld16(base + 128, dr);
+        ptx::tmem_ld_wait();
+        float den = __uint_as_float(dr[0]);
+        den = ctx.part == 1 ? __uint_as_float(dr[1]) : den;
+        den = ctx.part == 2 ? __uint_as_float(dr[2]) : den;
+        den = ctx.part == 3 ? __uint_as_float(dr[3]) : den;
+        const float z = 1.0f / (den + p.eps);
+        float v[32];
+        load_acc32(base + ctx.part * 32, v);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            __nv_bfloat16 h0, l0, h1, l1;
-            split_bf16(v[2 * i] * z, h0, l0);
-            split_bf16(v[2 * i + 1] * z, h1, l1);
-            hh[i] = pack_bf16(h0, h1);
-            ll[i] = pack_bf16(l0, l1);
-          }
+        for (int i = 0; i < 16; ++i) {
+          __nv_bfloat16 h0, l0, h1, l1;
+          split_bf16(v[2 * i] * z, h0, l0);
+          split_bf16(v[2 * i + 1] * z, h1, l1);
+          hh[i] = pack_bf16(h0, h1);
+          ll[i] = pack_bf16(l0, l1);
         }
-        ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);  // the four heads' columns have all been read: the planes may land
-        ptx::tmem_st16(base + ctx.part * 16, hh);
-        ptx::tmem_st16(base + 64 + ctx.part * 16, ll);
-        ptx::tmem_st_wait();
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(a2_full);
       }
+      ptx::named_bar_sync(bar_id, 32 * EPI_SPLIT);  // the four heads' columns have all been read: the planes may land
+      ptx::tmem_st16(base + ctx.part * 16, hh);
+      ptx::tmem_st16(base + 64 + ctx.part * 16, ll);
+      ptx::tmem_st_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(a2_full);
+    };
+    // LayerNorm1 of a tile (EpiLN<256>::run with D_merge handed back as soon as it is in registers)
+    auto layer_norm = [&](int it) {
+      constexpr int CPT = 64;
       ctx.m_tile = p.m_tile_begin + static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x);
       ptx::mbar_wait(dm_full, static_cast<uint32_t>(it) & 1);
       ptx::tc_fence_after();
       ctx.tmem_acc = tmem_base + kDM + lane_field;
-      EpiLN<256>::run(p.ln, ctx);
+      float x[CPT];
+      load_row_slice<CPT>(ctx, x);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(dm_empty);
+      float mean, rstd;
+      row_mean_rstd_split<CPT>(ctx, x, 256, mean, rstd);
+      const int cb = ctx.part * CPT;
+#pragma unroll
+      for (int i = 0; i < CPT; i += 4) {
+        const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.ln.gamma + cb + i));
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.ln.beta + cb + i));
+        x[i + 0] = (x[i + 0] - mean) * rstd * g4.x + b4.x;
+        x[i + 1] = (x[i + 1] - mean) * rstd * g4.y + b4.y;
+        x[i + 2] = (x[i + 2] - mean) * rstd * g4.z + b4.z;
+        x[i + 3] = (x[i + 3] - mean) * rstd * g4.w + b4.w;
+      }
+      const long long wrow0 = static_cast<long long>(ctx.m_tile) * BLOCK_M + ctx.quarter * 32;
+      uint32_t h[4][8], l[4][8];
+      pack_planes64(x, h, l);
+      store_row64_bf16_quad(h, p.ln.o_hi + wrow0 * 256 + cb, 256, ctx.lane);
+      store_row64_bf16_quad(l, p.ln.o_lo + wrow0 * 256 + cb, 256, ctx.lane);
+    };
+    // order: e(t, 0) | LN1(t - 1) | e(t, 1): the first conversion of a tile goes before the previous tile's LayerNorm, so
+    // the tensor pipe gets its operand (and, right after LN1 has loaded D_merge, its accumulator) back without waiting
+    // for the LayerNorm arithmetic and stores
+    for (int it = 0; it < n_it; ++it) {
+      convert(it, 0);
+      if (it > 0) layer_norm(it - 1);
+      convert(it, 1);
     }
+    if (n_it > 0) layer_norm(n_it - 1);
   }
   ptx::tc_fence_before();
   __syncthreads();
