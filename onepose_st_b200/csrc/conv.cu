@@ -91,10 +91,12 @@ struct ConvCfg {
 
 // HALO (3x3, stride 1): the three taps of one kernel column read the same pixels one row apart, so ONE box of
 // 8 * MSUB + 2 rows at the column's x shift serves ky = 0, 1, 2 -- the A operand of tap ky starts ky rows (2048 bytes: a
-// whole number of swizzle atoms) into it.  The activations cross the L2 -> SM path three times per 64 channels instead of
-// nine; that path, not the tensor pipe, bounds these layers (2.0 GB per 174 us launch = 11.5 TB/s in round 1's ncu capture
-// of the 128-channel layers, the ~6300 B/clk the L2 delivers chip-wide).  Shared memory: three halo buffers + a ring of
-// weight slabs (one per tap), each with its own full / empty barriers.
+// whole number of swizzle atoms) into it.  The activations are written into shared memory three times per 64 channels
+// instead of nine.  What that buys is bandwidth of the shared-memory port (128 B/clk per SM), which the operand reads of
+// 128-wide MMAs (8 KB per 64 clk) need all of: with f bytes of TMA fill per clk of tensor work the pipe is busy at most
+// 128 / (128 + f) of the time -- 57 % with one box per tap (f = 96), 70 % with the halo boxes (f = 56); measured 56 % and
+// 63-64 %.  Shared memory: three halo buffers + a ring of weight slabs (one per tap), each with its own
+// full / empty barriers.
 template <int BN, int MSUB>
 struct HaloCfg {
   static constexpr int A_BYTES = (CONV_TH * MSUB + 2) * CONV_TW * BLOCK_K * 2;

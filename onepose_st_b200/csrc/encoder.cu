@@ -320,22 +320,20 @@ struct EpiLNRes {  // MLP2 epilogue: x <- x + LayerNorm2(acc).  The residual str
 //   x <- x + LayerNorm2( relu([x | msg] W1^T) W2^T )
 // in ONE launch: the [128 x 512] hidden tile of an m tile never leaves the SM (as separate GEMMs its bf16 hi / lo planes make
 // a 1.6 GB round trip through HBM per layer step at 32 frames).
-//   * Per m tile and quarter q of the hidden tile: phase 1 = 16 k-blocks (32 wide: x then msg) of [x | msg] x
-//     W1[128 q .. 128 q + 127] into D1 with the three split products; the 16 epilogue warps read D1, apply the ReLU, split
-//     to bf16 hi / lo and write the quarter back INTO TENSOR MEMORY as the A operand of phase 2; phase 2 = 4 k-blocks of that
-//     operand x W2[:, 128 q ..] accumulated into D2.  After the four quarters the warps run the LayerNorm2 + residual
-//     epilogue of the unfused path (EpiLNRes) on D2.
-//   * One TMA thread streams {A planes, W1 rows} / {W2 columns} through seven 32 KB stages in exactly the order the MMA
+//   * Per m tile and 256-wide half of the hidden tile: phase 1 = [x | msg] x W1 rows of the half into D1 (three split
+//     products); the 16 epilogue warps read D1, apply the ReLU, split to bf16 hi / lo and write the planes back INTO THE SAME
+//     TENSOR-MEMORY COLUMNS, one 128-column quarter at a time; phase 2 = a tcgen05.mma whose A operand is read from tensor
+//     memory, x W2 columns of the half, accumulated into D2.  After the last half the warps run the LayerNorm2 + residual
+//     epilogue of the unfused path (EpiLNRes) on D2.  (Details at the kernel.)
+//   * One TMA thread streams {A planes, W1 rows} / {W2 columns} through four 48 KB stages in exactly the order the MMA
 //     thread consumes them.
-// History: the first version kept the hidden tile in shared memory as halves (128 KB) -- two 48 KB stages were all that
-// fitted beside it and every stage waited for the latency of its own TMA load: 995 us per layer step at 32 frames (ncu)
-// against 415 + 318 us for the two GEMM launches.  With the operand in tensor memory and phase 2 issued one phase 1 late:
-// 823 us under ncu (tensor pipe 60 % active; the L2 -> SM traffic of 2.5 MB per tile, weights re-streamed per tile and
-// [x | msg] once per quarter, is 77 % of the ~6300 B/clk the L2 delivers chip-wide), and in the bench, where the clocks
-// are set by the power cap and the 1.6 GB that no longer move count: transformer256 0.327-0.330 ms per frame against
-// 0.338-0.343, 1258-1260 frames/s end to end against 1217-1220 (same box, back to back, 32 frames per forward); 8 / 16
-// frames per forward: 0.363 / 0.342 against 0.376 / 0.351.
-constexpr int kMlpFusedMinRounds = 6;  // tiles per CTA from which the fused kernel is the default (OPB200_MLP_FUSED overrides)
+// History (32 frames per forward, ncu, per layer step; the two GEMM launches: 415 + 318 us): hidden tile in shared memory as
+// 128 KB halves, two 48 KB stages beside it, every stage waiting for the latency of its own TMA load: 995 us.  Operand in
+// separate tensor-memory columns per 128-wide quarter, seven 32 KB stages, [x | msg] read four times per tile: 823 us.
+// In place per 256-wide half (this version): 753-771 us, tensor pipe 65 % active.  In the bench, where the clocks are set
+// by the power cap and the 1.6 GB that no longer move count: transformer256 0.314-0.317 ms per frame against 0.338-0.340;
+// 8 / 16 frames per forward (second version): 0.363 / 0.342 against 0.376 / 0.351.
+constexpr int kMlpFusedMinRounds = 4;  // tiles per CTA from which the fused kernels are the default (OPB200_MLP_FUSED / OPB200_ATTN_MERGE_FUSED override)
 constexpr int MF_STAGES = 4;
 constexpr int MF_APL = BLOCK_M * 32 * 2;     // one A plane of a 32-wide k-block: 8 KB
 constexpr int MF_BPL = 256 * 32 * 2;         // one plane of a 256-row weight slab: 16 KB (phase 2 at C = 128: 128 rows)

@@ -1,5 +1,5 @@
 """GPU parity of the code paths that are selected per process by an environment switch (read once by the library):
-the fused MLP kernel of the coarse encoder layer (OPB200_MLP_FUSED=1 forces it -- by default it runs from two tiles per
+the fused MLP kernel of the coarse encoder layer (OPB200_MLP_FUSED=1 forces it -- by default it runs from four tiles per
 CTA on, i.e. not at most test shapes -- and =0 forces the two-launch path it replaced), the fused ATTN + MERGE + LayerNorm1 kernel of the coarse level
 (OPB200_ATTN_MERGE_FUSED, same convention) and the CUDA-core KV kernel that
 the tensor-core one replaced (OPB200_KV_TC=0); the per-tap convolution kernels that the halo kernels replaced for 3x3 stride 1
